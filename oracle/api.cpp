@@ -1,0 +1,239 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (never shipped, never on the product path).
+// C entry points (ctypes) over the CPU restatement.  Used only by tests/, __graft_entry__.smoke()
+// and bench.py's cpu_baseline / --impl reference legs.  "parity unpinned": the reference repo holds
+// no tests or golden vectors for this path and Ceres/Eigen are absent, so the only
+// external anchors are the Sophus SO3 fixtures and the closed-form spline constants (tests/).
+#include <chrono>
+#include <cstdint>
+#include <cstring>
+#include "lm.h"
+
+using namespace oracle;
+
+extern "C" {
+
+void* orc_create(int order, int64_t dt_ns, int64_t start_t_ns) {
+  if (order != 4 && order != 5 && order != 6) return nullptr;
+  return new SplineProblem(order, dt_ns, start_t_ns);
+}
+void orc_destroy(void* h) { delete (SplineProblem*)h; }
+
+int orc_set_knots(void* h, int n, const double* quat, const double* pos) {
+  auto* p = (SplineProblem*)h;
+  p->so3.assign(quat, quat + 4 * (size_t)n); p->r3.assign(pos, pos + 3 * (size_t)n); p->built = false; return 0;
+}
+int orc_num_knots(void* h) { return (int)((SplineProblem*)h)->numKnots(); }
+int orc_get_knots(void* h, double* quat, double* pos) {
+  auto* p = (SplineProblem*)h;
+  std::memcpy(quat, p->so3.data(), sizeof(double) * p->so3.size()); std::memcpy(pos, p->r3.data(), sizeof(double) * p->r3.size()); return 0;
+}
+int orc_initialize_biases(void* h, double dt_s_bias, const double* a0, const double* g0) {
+  auto* p = (SplineProblem*)h; p->initializeBiases(dt_s_bias, a0, g0); p->built = false; return (int)p->numBiasKnots();
+}
+int orc_num_bias_knots(void* h) { return (int)((SplineProblem*)h)->numBiasKnots(); }
+int orc_set_biases(void* h, const double* acc, const double* gyr) {
+  auto* p = (SplineProblem*)h;
+  std::memcpy(p->acc_bias.data(), acc, sizeof(double) * p->acc_bias.size()); std::memcpy(p->gyr_bias.data(), gyr, sizeof(double) * p->gyr_bias.size()); return 0;
+}
+int orc_get_biases(void* h, double* acc, double* gyr) {
+  auto* p = (SplineProblem*)h;
+  std::memcpy(acc, p->acc_bias.data(), sizeof(double) * p->acc_bias.size()); std::memcpy(gyr, p->gyr_bias.data(), sizeof(double) * p->gyr_bias.size()); return 0;
+}
+int orc_set_landmarks(void* h, int n, const double* xyz) {
+  auto* p = (SplineProblem*)h; p->lm.assign(xyz, xyz + 3 * (size_t)n); p->built = false; return 0;
+}
+int orc_get_landmarks(void* h, double* xyz) {
+  auto* p = (SplineProblem*)h; std::memcpy(xyz, p->lm.data(), sizeof(double) * p->lm.size()); return 0;
+}
+int orc_set_camera(void* h, int model, const double* intr, const double* dist, const double* q_bc, const double* p_bc, double t_offset_cam_imu) {
+  auto* p = (SplineProblem*)h;
+  p->cam.model = model; p->cam.fx = intr[0]; p->cam.fy = intr[1]; p->cam.cx = intr[2]; p->cam.cy = intr[3];
+  for (int i = 0; i < 4; ++i) { p->cam.d[i] = dist[i]; p->cam.q_bc[i] = q_bc[i]; }
+  for (int i = 0; i < 3; ++i) p->cam.p_bc[i] = p_bc[i];
+  p->cam_t_offset_cam_imu = t_offset_cam_imu;
+  p->t_offset_cam_imu_s = t_offset_cam_imu;  // setCameras, bspline_so3r3.h:1899-1903
+  return 0;
+}
+int orc_set_globals(void* h, double scale, const double* p_bp, const double* g, double t_s_gp_s) {
+  auto* p = (SplineProblem*)h;
+  p->scale = scale; for (int i = 0; i < 3; ++i) { p->p_bp[i] = p_bp[i]; p->g[i] = g[i]; }
+  p->t_s_gp_init_s = t_s_gp_s; p->t_s_gp_s = t_s_gp_s; return 0;
+}
+// corr[0]=scale_corr, [1..4]=R_bc_corr xyzw, [5..7]=p_bc_corr, [8]=t_offset_cam_imu_corr, [9]=t_s_gp_corr
+int orc_set_corrections(void* h, const double* c) {
+  auto* p = (SplineProblem*)h;
+  p->scale_corr = c[0]; for (int i = 0; i < 4; ++i) p->R_bc_corr[i] = c[1 + i]; for (int i = 0; i < 3; ++i) p->p_bc_corr[i] = c[5 + i];
+  p->t_offset_cam_imu_corr_s = c[8]; p->t_s_gp_corr_s = c[9]; return 0;
+}
+// out: corr[0..9] as above, [10..12]=p_bp, [13..15]=g, [16]=t_offset_cam_imu_s, [17]=t_s_gp_s, [18]=scale
+int orc_get_globals(void* h, double* o) {
+  auto* p = (SplineProblem*)h;
+  o[0] = p->scale_corr; for (int i = 0; i < 4; ++i) o[1 + i] = p->R_bc_corr[i]; for (int i = 0; i < 3; ++i) o[5 + i] = p->p_bc_corr[i];
+  o[8] = p->t_offset_cam_imu_corr_s; o[9] = p->t_s_gp_corr_s;
+  for (int i = 0; i < 3; ++i) { o[10 + i] = p->p_bp[i]; o[13 + i] = p->g[i]; }
+  o[16] = p->t_offset_cam_imu_s; o[17] = p->t_s_gp_s; o[18] = p->scale; return 0;
+}
+int orc_set_flags(void* h, int opt_scale, int opt_pbp, int opt_gravity, int opt_camimu, int opt_t_gs) {
+  auto* p = (SplineProblem*)h;
+  p->optimize_scale = opt_scale; p->optimize_p_bp = opt_pbp; p->optimize_gravity = opt_gravity;
+  p->optimize_camimu_extrinsics = opt_camimu; p->optimize_t_offset_s_gs = opt_t_gs; p->built = false; return 0;
+}
+int orc_add_frames(void* h, int F, const int64_t* t_ns, const int32_t* obs_begin, const double* uv, const int32_t* lm, double noise) {
+  return ((SplineProblem*)h)->addFrames(F, t_ns, obs_begin, uv, lm, noise);
+}
+int orc_add_imu(void* h, int n, const int64_t* t_ns, const double* acc, const double* gyr, double acc_nd, double gyr_nd) {
+  return ((SplineProblem*)h)->addImu(n, t_ns, acc, gyr, acc_nd, gyr_nd);
+}
+int orc_add_gp(void* h, int n, const int64_t* t_ns, const double* pos, double noise) { return ((SplineProblem*)h)->addGp(n, t_ns, pos, noise); }
+int orc_add_bias_cost(void* h, double freq_hz, double dt_s, double acc_rw, double gyr_rw) { return ((SplineProblem*)h)->addBiasCost(freq_hz, dt_s, acc_rw, gyr_rw); }
+int orc_add_gravity_norm(void* h) { auto* p = (SplineProblem*)h; p->gravity_norm = true; p->built = false; return 0; }
+int orc_relinearize(void* h) { ((SplineProblem*)h)->relinearize(); return 0; }
+
+// counts: [frames, obs, accel, gyro, gp, bias, gravity, tangent columns]
+int orc_counts(void* h, int64_t* c) {
+  auto* p = (SplineProblem*)h; p->build();
+  int64_t obs = 0; for (auto& f : p->frames) obs += (int64_t)f.lm.size();
+  c[0] = (int64_t)p->frames.size(); c[1] = obs; c[2] = (int64_t)p->accel.size(); c[3] = (int64_t)p->gyro.size();
+  c[4] = (int64_t)p->gp.size(); c[5] = (int64_t)p->bias.size(); c[6] = p->gravity_norm ? 1 : 0; c[7] = p->mp.num_cols; return 0;
+}
+
+// Per-kind raw residuals and LOCAL Jacobians (no loss correction), row-major, in the documented
+// layouts of include/ctba.h.  kind: 0 reproj (per observation, 2 x (6N+10)), 1 accel (3 x (6N+16)),
+// 2 gyro (3 x (3N+13)), 3 gp (3 x (6N+5)), 4 bias (3 x 24), 5 gravity (1 x 3).
+// aux[0] receives the max |entry| of every Jacobian column the reference block owns but the layout
+// drops (cross-landmark columns; bias blocks 4..N-1) — must be exactly 0.
+int orc_evaluate(void* h, int kind, double* r_out, double* j_out, double* aux) {
+  auto* p = (SplineProblem*)h; p->build();
+  const int N = p->N;
+  double dropped = 0.0;
+  size_t ro = 0, jo = 0;
+  for (const auto& b : p->mp.blocks) {
+    if (b.kind != kind) continue;
+    EvalBlockOut o;
+    p->mp.evalBlock(b, j_out != nullptr, &o);
+    const int nc = o.ncols_local;
+    if (kind == 0) {
+      const int n = b.nres / 2, W = 6 * N + 10, base = 6 * N + 7;
+      for (int i = 0; i < n; ++i)
+        for (int rr = 0; rr < 2; ++rr) {
+          if (r_out) r_out[ro++] = o.r[2 * i + rr];
+          if (j_out) {
+            const double* row = &o.jl[(size_t)(2 * i + rr) * nc];
+            for (int c = 0; c < base; ++c) j_out[jo++] = row[c];
+            for (int c = 0; c < 3; ++c) j_out[jo++] = row[base + 3 * i + c];
+            for (int c = base; c < nc; ++c) if (c < base + 3 * i || c >= base + 3 * i + 3) dropped = std::max(dropped, std::fabs(row[c]));
+            (void)W;
+          }
+        }
+    } else if (kind == 1 || kind == 2) {
+      // accel block: [3N rot | 3N pos | 3N bias | 3 g | 1 t]; gyro: [3N rot | 3N bias | 1 t]
+      const int pre = kind == 1 ? 6 * N : 3 * N;
+      for (int rr = 0; rr < 3; ++rr) {
+        if (r_out) r_out[ro++] = o.r[rr];
+        if (j_out) {
+          const double* row = &o.jl[(size_t)rr * nc];
+          for (int c = 0; c < pre + 12; ++c) j_out[jo++] = row[c];
+          for (int c = pre + 12; c < pre + 3 * N; ++c) dropped = std::max(dropped, std::fabs(row[c]));
+          for (int c = pre + 3 * N; c < nc; ++c) j_out[jo++] = row[c];
+        }
+      }
+    } else {
+      for (int rr = 0; rr < b.nres; ++rr) {
+        if (r_out) r_out[ro++] = o.r[rr];
+        if (j_out) for (int c = 0; c < nc; ++c) j_out[jo++] = o.jl[(size_t)rr * nc + c];
+      }
+    }
+  }
+  if (aux) aux[0] = dropped;
+  return (int)ro;
+}
+
+// cost[k] = 1/2 sum over blocks of kind k of rho(||r||^2); cost[6] = total
+int orc_cost(void* h, double* cost) {
+  auto* p = (SplineProblem*)h; p->build();
+  for (int k = 0; k < 7; ++k) cost[k] = 0;
+  for (const auto& b : p->mp.blocks) {
+    EvalBlockOut o; p->mp.evalBlock(b, false, &o);
+    double c = 0.5 * o.sq_norm;
+    if (b.cauchy_a > 0) { double rho[3]; cauchy(b.cauchy_a, o.sq_norm, rho); c = 0.5 * rho[0]; }
+    cost[b.kind] += c; cost[6] += c;
+  }
+  return 0;
+}
+
+// summary: [termination_type, initial_cost, final_cost, n_successful, n_unsuccessful, n_iterations_logged]
+// iter_log: n x 7 (cost, cost_change, gradient_max_norm, step_norm, tr_ratio, tr_radius, successful)
+int orc_solve(void* h, int max_iters, int num_threads, double* summary, double* iter_log, int iter_cap) {
+  auto* p = (SplineProblem*)h; p->build();
+  SolveSummary s = solveLM(p->mp, max_iters, num_threads);
+  summary[0] = s.termination_type; summary[1] = s.initial_cost; summary[2] = s.final_cost;
+  summary[3] = s.num_successful_steps; summary[4] = s.num_unsuccessful_steps; summary[5] = (double)s.iterations.size();
+  for (size_t i = 0; i < s.iterations.size() && (int)i < iter_cap; ++i) {
+    const auto& it = s.iterations[i];
+    double* o = iter_log + 7 * i;
+    o[0] = it.cost; o[1] = it.cost_change; o[2] = it.gradient_max_norm; o[3] = it.step_norm; o[4] = it.tr_ratio; o[5] = it.tr_radius; o[6] = it.successful;
+  }
+  return 0;
+}
+
+// Wall time (seconds) of `reps` residual+Jacobian evaluations of every block with the Ceres
+// DynamicAutoDiff schedule (stride-4 Jets, one block per frame) on `num_threads` threads.
+// frame_limit > 0 restricts the run to the first `frame_limit` frame blocks (bounded sample);
+// obs_done receives the reprojection observations evaluated per repetition.
+double orc_time_evaluate(void* h, int num_threads, int reps, int frame_limit, int64_t* obs_done) {
+  auto* p = (SplineProblem*)h; p->build();
+  std::vector<const ResidualBlock*> sel;
+  int nf = 0; int64_t obs = 0;
+  for (const auto& b : p->mp.blocks) {
+    if (b.kind == 0) { if (frame_limit > 0 && nf >= frame_limit) continue; ++nf; obs += b.nres / 2; }
+    sel.push_back(&b);
+  }
+  if (obs_done) *obs_done = obs;
+  auto t0 = std::chrono::steady_clock::now();
+  for (int rep = 0; rep < reps; ++rep) {
+    auto work = [&](int t) {
+      EvalBlockOut o;
+      for (size_t i = t; i < sel.size(); i += num_threads) p->mp.evalBlock(*sel[i], true, &o);
+    };
+    std::vector<std::thread> th;
+    for (int t = 0; t < num_threads; ++t) th.emplace_back(work, t);
+    for (auto& t : th) t.join();
+  }
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+// ---- primitives exposed for known-answer tests (Sophus fixtures, Appendix E constants) ----
+void orc_so3_exp(const double* w, double* q) { auto r = SO3<double>::exp(V3<double>{w[0], w[1], w[2]}); q[0] = r.x; q[1] = r.y; q[2] = r.z; q[3] = r.w; }
+void orc_so3_log(const double* q, double* w) { auto r = SO3<double>{q[0], q[1], q[2], q[3]}.log(); w[0] = r.x; w[1] = r.y; w[2] = r.z; }
+void orc_so3_mul(const double* a, const double* b, double* c) { auto r = SO3<double>{a[0], a[1], a[2], a[3]} * SO3<double>{b[0], b[1], b[2], b[3]}; c[0] = r.x; c[1] = r.y; c[2] = r.z; c[3] = r.w; }
+void orc_so3_matrix(const double* q, double* R) { auto m = SO3<double>{q[0], q[1], q[2], q[3]}.matrix(); for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) R[3 * i + j] = m.m[i][j]; }
+void orc_so3_act(const double* q, const double* p, double* o) { auto r = SO3<double>{q[0], q[1], q[2], q[3]}.act(V3<double>{p[0], p[1], p[2]}); o[0] = r.x; o[1] = r.y; o[2] = r.z; }
+void orc_so3_plus_jacobian(const double* q, double* J) { double PJ[4][3]; SO3<double>{q[0], q[1], q[2], q[3]}.Dx_this_mul_exp_x_at_0(PJ); for (int i = 0; i < 4; ++i) for (int j = 0; j < 3; ++j) J[3 * i + j] = PJ[i][j]; }
+// tables: which 0 blend, 1 cumulative blend, 2 base coefficients; out N*N row-major
+int orc_spline_table(int N, int which, double* out) {
+  auto cp = [&](auto& tb) { const double(*src)[sizeof(tb.blend[0]) / sizeof(double)] = which == 0 ? tb.blend : which == 1 ? tb.cum_blend : tb.base;
+    const int n = (int)(sizeof(tb.blend[0]) / sizeof(double)); for (int i = 0; i < n; ++i) for (int j = 0; j < n; ++j) out[i * n + j] = src[i][j]; };
+  if (N == 4) cp(SplineTables<4>::get()); else if (N == 5) cp(SplineTables<5>::get()); else if (N == 6) cp(SplineTables<6>::get()); else return -1;
+  return 0;
+}
+// spline sample: value R (quat), p, body omega, body omega_dot, world velocity, world accel at (s,u) — fixed-u path
+int orc_sample(void* h, int64_t s, double u, double* out19) {
+  auto* p = (SplineProblem*)h;
+  std::vector<const double*> kn;
+  for (int j = 0; j < p->N; ++j) kn.push_back(&p->so3[4 * (s + j)]);
+  for (int j = 0; j < p->N; ++j) kn.push_back(&p->r3[3 * (s + j)]);
+  SO3<double> R; V3<double> w, wd, jk, pos, vel, acc;
+  auto run = [&](auto tag) {
+    constexpr int NN = decltype(tag)::value;
+    SplineHelper<NN>::template evaluate_lie<double, double>(kn.data(), u, p->inv_dt, &R, &w, &wd, &jk);
+    SplineHelper<NN>::template evaluate<double, 0, double>(kn.data() + NN, u, p->inv_dt, &pos);
+    SplineHelper<NN>::template evaluate<double, 1, double>(kn.data() + NN, u, p->inv_dt, &vel);
+    SplineHelper<NN>::template evaluate<double, 2, double>(kn.data() + NN, u, p->inv_dt, &acc);
+  };
+  if (p->N == 4) run(std::integral_constant<int, 4>()); else if (p->N == 5) run(std::integral_constant<int, 5>()); else run(std::integral_constant<int, 6>());
+  double o[19] = {R.x, R.y, R.z, R.w, pos.x, pos.y, pos.z, w.x, w.y, w.z, wd.x, wd.y, wd.z, vel.x, vel.y, vel.z, acc.x, acc.y, acc.z};
+  std::memcpy(out19, o, sizeof(o));
+  return 0;
+}
+
+}  // extern "C"

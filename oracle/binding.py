@@ -1,0 +1,227 @@
+"""ORACLE — TEST INFRASTRUCTURE ONLY.  ctypes binding of oracle/liboracle.so.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import
+this module.  The method names mirror BSplineSO3R3 (/root/reference include/spline/bspline_so3r3.h)
+so that parity tests read like calls into the reference.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+f64p = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+i64p = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
+i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "liboracle.so")
+    srcs = [os.path.join(_HERE, f) for f in ("api.cpp", "lm.h", "problem.h", "functors.h", "ref_math.h", "jet.h")]
+    if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        subprocess.check_call(["make", "-C", _HERE, "liboracle.so"], stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        so = os.path.join(_HERE, "liboracle.so")
+        if not os.path.exists(so):
+            build()
+        L = C.CDLL(so)
+        L.orc_create.restype = C.c_void_p
+        L.orc_create.argtypes = [C.c_int, C.c_int64, C.c_int64]
+        L.orc_destroy.argtypes = [C.c_void_p]
+        L.orc_time_evaluate.restype = C.c_double
+        _LIB = L
+    return _LIB
+
+
+def _d(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+class OracleSpline:
+    """CPU restatement of BSplineSO3R3<N> + ceres::Solve (see oracle/problem.h, oracle/lm.h)."""
+
+    def __init__(self, order, dt_ns, start_t_ns=0):
+        self.L = lib()
+        self.N = order
+        self.h = C.c_void_p(self.L.orc_create(order, int(dt_ns), int(start_t_ns)))
+        if not self.h:
+            raise ValueError("unsupported spline order")
+
+    def __del__(self):
+        try:
+            self.L.orc_destroy(self.h)
+        except Exception:
+            pass
+
+    def setKnots(self, quat_xyzw, pos):
+        q, p = _d(quat_xyzw), _d(pos)
+        self.L.orc_set_knots(self.h, len(q), q.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p))
+
+    def numKnots(self):
+        return self.L.orc_num_knots(self.h)
+
+    def getKnots(self):
+        n = self.numKnots()
+        q, p = np.zeros((n, 4)), np.zeros((n, 3))
+        self.L.orc_get_knots(self.h, q.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p))
+        return q, p
+
+    def initializeBiases(self, dt_s_bias, acc0, gyr0):
+        a, g = _d(acc0), _d(gyr0)
+        return self.L.orc_initialize_biases(self.h, C.c_double(dt_s_bias), a.ctypes.data_as(C.c_void_p), g.ctypes.data_as(C.c_void_p))
+
+    def numBiasKnots(self):
+        return self.L.orc_num_bias_knots(self.h)
+
+    def setBiases(self, acc, gyr):
+        a, g = _d(acc), _d(gyr)
+        self.L.orc_set_biases(self.h, a.ctypes.data_as(C.c_void_p), g.ctypes.data_as(C.c_void_p))
+
+    def getBiases(self):
+        n = self.numBiasKnots()
+        a, g = np.zeros((n, 3)), np.zeros((n, 3))
+        self.L.orc_get_biases(self.h, a.ctypes.data_as(C.c_void_p), g.ctypes.data_as(C.c_void_p))
+        return a, g
+
+    def set3DPoints(self, xyz):
+        x = _d(xyz)
+        self._nlm = len(x)
+        self.L.orc_set_landmarks(self.h, len(x), x.ctypes.data_as(C.c_void_p))
+
+    def get3DPoints(self):
+        x = np.zeros((self._nlm, 3))
+        self.L.orc_get_landmarks(self.h, x.ctypes.data_as(C.c_void_p))
+        return x
+
+    def setCamera(self, model, intr, dist, q_bc, p_bc, t_offset_cam_imu):
+        a = [_d(v) for v in (intr, dist, q_bc, p_bc)]
+        self.L.orc_set_camera(self.h, int(model), *[v.ctypes.data_as(C.c_void_p) for v in a], C.c_double(t_offset_cam_imu))
+
+    def setGlobals(self, scale, p_bp, g, t_s_gp_s):
+        a, b = _d(p_bp), _d(g)
+        self.L.orc_set_globals(self.h, C.c_double(scale), a.ctypes.data_as(C.c_void_p), b.ctypes.data_as(C.c_void_p), C.c_double(t_s_gp_s))
+
+    def setCorrections(self, corr10):
+        c = _d(corr10)
+        assert c.size == 10
+        self.L.orc_set_corrections(self.h, c.ctypes.data_as(C.c_void_p))
+
+    def getGlobals(self):
+        o = np.zeros(19)
+        self.L.orc_get_globals(self.h, o.ctypes.data_as(C.c_void_p))
+        return o
+
+    def setFlags(self, optimize_scale, optimize_pbp, optimize_gravity, optimize_camimu_extrinsics, optimize_t_offset_s_gs):
+        self.L.orc_set_flags(self.h, int(optimize_scale), int(optimize_pbp), int(optimize_gravity), int(optimize_camimu_extrinsics), int(optimize_t_offset_s_gs))
+
+    def addFrames(self, t_ns, obs_begin, uv, lm_index, sigma_px):
+        t = np.ascontiguousarray(t_ns, dtype=np.int64)
+        ob = np.ascontiguousarray(obs_begin, dtype=np.int32)
+        u = _d(uv)
+        li = np.ascontiguousarray(lm_index, dtype=np.int32)
+        return self.L.orc_add_frames(self.h, len(t), t.ctypes.data_as(C.c_void_p), ob.ctypes.data_as(C.c_void_p), u.ctypes.data_as(C.c_void_p), li.ctypes.data_as(C.c_void_p), C.c_double(sigma_px))
+
+    def addImu(self, t_ns, acc, gyr, acc_noise_density, gyro_noise_density):
+        t = np.ascontiguousarray(t_ns, dtype=np.int64)
+        a, g = _d(acc), _d(gyr)
+        return self.L.orc_add_imu(self.h, len(t), t.ctypes.data_as(C.c_void_p), a.ctypes.data_as(C.c_void_p), g.ctypes.data_as(C.c_void_p), C.c_double(acc_noise_density), C.c_double(gyro_noise_density))
+
+    def addGp(self, t_ns, pos, noise):
+        t = np.ascontiguousarray(t_ns, dtype=np.int64)
+        p = _d(pos)
+        return self.L.orc_add_gp(self.h, len(t), t.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p), C.c_double(noise))
+
+    def addImuBiasCost(self, freq_hz, dt_s, acc_rw, gyr_rw):
+        return self.L.orc_add_bias_cost(self.h, C.c_double(freq_hz), C.c_double(dt_s), C.c_double(acc_rw), C.c_double(gyr_rw))
+
+    def addGravityNormError(self):
+        self.L.orc_add_gravity_norm(self.h)
+
+    def relinearize(self):
+        self.L.orc_relinearize(self.h)
+
+    def counts(self):
+        c = np.zeros(8, dtype=np.int64)
+        self.L.orc_counts(self.h, c.ctypes.data_as(C.c_void_p))
+        return dict(zip(["frames", "obs", "accel", "gyro", "gp", "bias", "gravity", "cols"], [int(v) for v in c]))
+
+    def jac_width(self, kind):
+        N = self.N
+        return [6 * N + 10, 6 * N + 16, 3 * N + 13, 6 * N + 5, 24, 3][kind]
+
+    def evaluate(self, kind, jac=True):
+        c = self.counts()
+        nres = [2 * c["obs"], 3 * c["accel"], 3 * c["gyro"], 3 * c["gp"], 3 * c["bias"], c["gravity"]][kind]
+        r = np.zeros(nres)
+        J = np.zeros((nres, self.jac_width(kind))) if jac else None
+        aux = np.zeros(1)
+        self.L.orc_evaluate(self.h, kind, r.ctypes.data_as(C.c_void_p), J.ctypes.data_as(C.c_void_p) if jac else None, aux.ctypes.data_as(C.c_void_p))
+        return r, J, float(aux[0])
+
+    def cost(self):
+        o = np.zeros(7)
+        self.L.orc_cost(self.h, o.ctypes.data_as(C.c_void_p))
+        return o
+
+    def optimize(self, max_num_iterations, num_threads=1):
+        s = np.zeros(6)
+        cap = max_num_iterations + 2
+        log = np.zeros((cap, 7))
+        self.L.orc_solve(self.h, int(max_num_iterations), int(num_threads), s.ctypes.data_as(C.c_void_p), log.ctypes.data_as(C.c_void_p), cap)
+        n = int(s[5])
+        return dict(termination_type=int(s[0]), initial_cost=s[1], final_cost=s[2], num_successful_steps=int(s[3]),
+                    num_unsuccessful_steps=int(s[4]), iterations=log[:min(n, cap)].copy())
+
+    def timeEvaluate(self, num_threads, reps=1, frame_limit=0):
+        obs = C.c_int64(0)
+        t = self.L.orc_time_evaluate(self.h, int(num_threads), int(reps), int(frame_limit), C.byref(obs))
+        return float(t), int(obs.value)
+
+    def sample(self, s, u):
+        o = np.zeros(19)
+        self.L.orc_sample(self.h, C.c_int64(int(s)), C.c_double(u), o.ctypes.data_as(C.c_void_p))
+        return o
+
+
+# ---- primitives for known-answer tests ----
+def so3_exp(w):
+    q = np.zeros(4); w = _d(w)
+    lib().orc_so3_exp(w.ctypes.data_as(C.c_void_p), q.ctypes.data_as(C.c_void_p)); return q
+
+
+def so3_log(q):
+    w = np.zeros(3); q = _d(q)
+    lib().orc_so3_log(q.ctypes.data_as(C.c_void_p), w.ctypes.data_as(C.c_void_p)); return w
+
+
+def so3_mul(a, b):
+    c = np.zeros(4); a = _d(a); b = _d(b)
+    lib().orc_so3_mul(a.ctypes.data_as(C.c_void_p), b.ctypes.data_as(C.c_void_p), c.ctypes.data_as(C.c_void_p)); return c
+
+
+def so3_matrix(q):
+    R = np.zeros((3, 3)); q = _d(q)
+    lib().orc_so3_matrix(q.ctypes.data_as(C.c_void_p), R.ctypes.data_as(C.c_void_p)); return R
+
+
+def so3_act(q, p):
+    o = np.zeros(3); q = _d(q); p = _d(p)
+    lib().orc_so3_act(q.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p), o.ctypes.data_as(C.c_void_p)); return o
+
+
+def so3_plus_jacobian(q):
+    J = np.zeros((4, 3)); q = _d(q)
+    lib().orc_so3_plus_jacobian(q.ctypes.data_as(C.c_void_p), J.ctypes.data_as(C.c_void_p)); return J
+
+
+def spline_table(N, which):
+    o = np.zeros((N, N))
+    lib().orc_spline_table(int(N), int(which), o.ctypes.data_as(C.c_void_p)); return o
