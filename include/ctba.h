@@ -1,0 +1,139 @@
+/* ctba.h — C ABI of the B200-native continuous-time bundle adjuster.
+ *
+ * Drop-in boundary: everything the reference executes inside
+ *     ceres::Solver::Summary BSplineSO3R3<N>::optimize(int max_num_iterations)
+ *         /root/reference/include/spline/bspline_so3r3.h:1768-1782   (-> ceres::Solve, :1778)
+ * plus the problem-assembly calls that feed it.  Each entry point names the reference interface it
+ * replaces.  Plain pointers and sizes only; no C++ types, no exceptions, no abort() across the ABI.
+ * All floating point data is IEEE binary64.  Quaternions are stored [x y z w] (so3.hpp:185-187).
+ *
+ * The library is CUDA-only (sm_100a): every compute entry point returns CTBA_E_CUDA when no device
+ * is usable.  There is no CPU fallback.
+ */
+#ifndef CTBA_H_
+#define CTBA_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ctba_problem ctba_problem;
+
+enum {
+  CTBA_OK = 0,
+  CTBA_E_ARG = -1,      /* bad argument (replaces GVI_FUSION_ASSERT_STREAM aborts, util/assert.h:65-70) */
+  CTBA_E_CUDA = -2,     /* CUDA runtime failure / no device */
+  CTBA_E_NCCL = -3,
+  CTBA_E_NUMERIC = -4,  /* non-finite values / factorisation breakdown */
+  CTBA_E_OOM = -5,
+  CTBA_E_STATE = -6     /* call order violation (e.g. measurements before knots) */
+};
+
+/* residual kinds (ctba_evaluate) */
+enum { CTBA_REPROJ = 0, CTBA_ACCEL = 1, CTBA_GYRO = 2, CTBA_GP = 3, CTBA_BIAS = 4, CTBA_GRAVITY = 5 };
+
+/* BSplineSO3R3<N>::BSplineSO3R3(time_interval_ns, start_time_ns)      bspline_so3r3.h:75-117
+ * order N in {4,6}; `device` = CUDA ordinal. */
+int ctba_create(int order, int64_t dt_ns, int64_t start_t_ns, int device, ctba_problem** out);
+int ctba_destroy(ctba_problem* p);
+const char* ctba_last_error(const ctba_problem* p);
+/* Use an existing CUDA stream (cudaStream_t passed as void*) for all work of this handle; 0 = own stream. */
+int ctba_set_stream(ctba_problem* p, void* cuda_stream);
+
+/* initializeFromNumTraj / so3_knots_, r3_knots_                        bspline_so3r3.h:336-353, 1936-1939 */
+int ctba_set_knots(ctba_problem* p, int n, const double* quat_xyzw /*4n*/, const double* pos /*3n*/);
+int ctba_num_knots(const ctba_problem* p);
+int ctba_get_knots(ctba_problem* p, double* quat_xyzw, double* pos);
+
+/* initializeBiases(dt_s_bias, init_acc_bias, init_gyro_bias)            bspline_so3r3.h:355-369
+ * returns the number of bias knots (>=0) or an error (<0). */
+int ctba_initialize_biases(ctba_problem* p, double dt_s_bias, const double* acc0, const double* gyr0);
+int ctba_num_bias_knots(const ctba_problem* p);
+int ctba_set_biases(ctba_problem* p, const double* acc /*3nb*/, const double* gyr /*3nb*/);
+int ctba_get_biases(ctba_problem* p, double* acc, double* gyr);
+
+/* set3DPoints (points3D_[id].p_wl); landmark identity is the array index  bspline_so3r3.h:1907-1908, 1982 */
+int ctba_set_landmarks(ctba_problem* p, int n, const double* xyz /*3n*/);
+int ctba_get_landmarks(ctba_problem* p, double* xyz);
+
+/* setCameras (first camera only): COLMAP model id 4|5|7, intr = fx fy cx cy, dist = 4 coefficients,
+ * T_b_c as quaternion + translation, t_offset_cam_imu                   bspline_so3r3.h:1899-1903, sensor/camera.h:41-90 */
+int ctba_set_camera(ctba_problem* p, int model, const double* intr, const double* dist, const double* q_bc, const double* p_bc,
+                    double t_offset_cam_imu_s);
+/* setScale / setPbp / setGravity / setInitSplineGlobSensTimeOffset      bspline_so3r3.h:1792-1798, 1841-1845, 1880 */
+int ctba_set_globals(ctba_problem* p, double scale, const double* p_bp, const double* g, double t_s_gp_s);
+/* corr[10] = scale_corr, R_b_c_corr (xyzw), p_b_c_corr, t_offset_cam_imu_corr_s, t_s_gp_corr_s (members :1955-1973);
+ * only needed to evaluate at a non-default linearisation point. */
+int ctba_set_corrections(ctba_problem* p, const double* corr10);
+/* out[19] = corr[0..9], p_bp[10..12], g[13..15], t_offset_cam_imu_s[16], t_s_gp_s[17], scale_[18]
+ * (getScale/getPbp/getGravity/getImuCamRelTransformationCorr/getSplineImuTimeOffset...  :1792-1881) */
+int ctba_get_globals(ctba_problem* p, double* out19);
+/* setOptimizeScale / setOptimizePbp / setOptimizeGravity / setOptimizeCamImuExtrinsics /
+ * setOptimizeTimeOffsetSplineGlobalSensor                                bspline_so3r3.h:1794-1897 */
+int ctba_set_flags(ctba_problem* p, int optimize_scale, int optimize_pbp, int optimize_gravity, int optimize_camimu_extrinsics,
+                   int optimize_t_offset_s_gs);
+
+/* addImagePointsMeasurement(frame, t_ns, noise) for F frames at once: CSR obs_begin[F+1] over the frames'
+ * VALID reprojections (is_reproj_valid), uv pixels, landmark indices.  CauchyLoss(3.0) per frame.
+ * Returns the number of frames accepted (skip rules :962-973).           bspline_so3r3.h:960-1046 */
+int ctba_add_frames(ctba_problem* p, int F, const int64_t* t_ns, const int32_t* obs_begin, const double* uv /*2M*/,
+                    const int32_t* lm_index /*M*/, double sigma_px);
+/* addAccelMeasurement + addGyroMeasurement for n samples                 bspline_so3r3.h:523-702 */
+int ctba_add_imu(ctba_problem* p, int n, const int64_t* t_ns, const double* acc /*3n*/, const double* gyr /*3n*/,
+                 double acc_noise_density, double gyro_noise_density);
+/* addGlobalPosMeasurement for n samples                                  bspline_so3r3.h:880-958 */
+int ctba_add_gp(ctba_problem* p, int n, const int64_t* t_ns, const double* pos /*3n*/, double noise);
+/* addImuBiasCost(bias_err_freq_hz, bias_err_dt_s); random walks from ImuCalibration   bspline_so3r3.h:706-792 */
+int ctba_add_bias_cost(ctba_problem* p, double freq_hz, double dt_s, double acc_random_walk, double gyro_random_walk);
+/* addGravityNormError()                                                  bspline_so3r3.h:1213-1227 */
+int ctba_add_gravity_norm(ctba_problem* p);
+
+/* counts[8] = frames, observations, accel, gyro, gp, bias blocks, gravity, reduced-system unknowns */
+int ctba_counts(ctba_problem* p, int64_t* counts);
+
+/* Raw residuals and local (tangent-space) Jacobians of one residual kind at the current state, row-major,
+ * without the robust-loss correction (what DynamicAutoDiffCostFunction::Evaluate + LocalParameterization give):
+ *   CTBA_REPROJ  per observation 2 x (6N+10): [3N rot | 3N pos | scale_corr | R_bc_corr 3 | p_bc_corr 3 | landmark 3]
+ *   CTBA_ACCEL   per sample      3 x (6N+16): [3N rot | 3N pos | 4 acc-bias knots | g 3 | t_offset_cam_imu_corr]
+ *   CTBA_GYRO    per sample      3 x (3N+13): [3N rot | 4 gyro-bias knots | t_offset_cam_imu_corr]
+ *   CTBA_GP      per sample      3 x (6N+5) : [3N rot | 3N pos | p_bp 3 | t_s_gp_corr | scale_corr]
+ *   CTBA_BIAS    per block       3 x 24     : [4 knots @s0 | 4 knots @s1]
+ *   CTBA_GRAVITY                 1 x 3
+ * residuals / jacobians may be NULL.  Returns the number of residuals written (>=0) or an error.
+ * Also serves evaluate*Errors (bspline_so3r3.h:1229-1579). */
+int ctba_evaluate(ctba_problem* p, int kind, double* residuals, double* jacobians);
+/* cost[7]: 1/2 sum rho(|r|^2) per kind (Cauchy on reprojection frames), cost[6] = total */
+int ctba_cost(ctba_problem* p, double* cost7);
+
+typedef struct ctba_iteration {
+  double cost, cost_change, gradient_max_norm, step_norm, tr_ratio, tr_radius;
+  int successful;
+} ctba_iteration;
+
+typedef struct ctba_summary {
+  int termination_type; /* 0 CONVERGENCE, 1 NO_CONVERGENCE, 2 FAILURE  (ceres::TerminationType; drivers test == 0) */
+  double initial_cost, final_cost;
+  int num_successful_steps, num_unsuccessful_steps;
+  int num_iterations;            /* entries written to `iterations` (iteration 0 = initial evaluation) */
+  ctba_iteration* iterations;    /* caller-provided array of `iterations_capacity` entries, may be NULL */
+  int iterations_capacity;
+  double time_total_s, time_eval_s, time_build_s, time_solve_s; /* device-side breakdown */
+} ctba_summary;
+
+/* BSplineSO3R3::optimize(max_num_iterations) == ceres::Solve            bspline_so3r3.h:1768-1782
+ * Runs trust-region LM entirely on the device and writes the optimised state back into the handle
+ * (ctba_get_* to read).  Non-convergence is reported in the summary, not as an error. */
+int ctba_solve(ctba_problem* p, int max_num_iterations, ctba_summary* summary);
+
+/* relinearizeSplineImuTimeOffset + relinearizeSplineGlobSensTimeOffset   bspline_so3r3.h:1807-1811, 1853-1857 */
+int ctba_relinearize_time_offsets(ctba_problem* p);
+
+/* Device-only benchmarking hooks (inputs already resident): run `reps` passes of the residual+Jacobian
+ * kernels (which != 0) or of a full LM iteration, return the kernel launch count. */
+int ctba_bench_evaluate(ctba_problem* p, int reps, int64_t* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CTBA_H_ */

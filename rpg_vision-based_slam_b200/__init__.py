@@ -1,0 +1,261 @@
+"""rpg_vision-based_slam_b200 — host-side mirror of the reference's BSplineSO3R3 interface over the
+CUDA C-ABI library (include/ctba.h, csrc/libctba.so).
+
+`BSplineSO3R3` keeps the method names and argument meaning of
+/root/reference/include/spline/bspline_so3r3.h so that tests read like calls into the reference;
+every method forwards to one C-ABI entry point.  There is NO CPU fallback: importing works without
+a GPU (so the symbol table can be checked), but constructing a problem raises if the CUDA library
+or a CUDA device is missing.
+
+The directory name contains a hyphen, so import it with
+    importlib.import_module("rpg_vision-based_slam_b200")
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libctba.so")
+_LIB = None
+
+CTBA_REPROJ, CTBA_ACCEL, CTBA_GYRO, CTBA_GP, CTBA_BIAS, CTBA_GRAVITY = range(6)
+
+EXPORTS = [
+    "ctba_create", "ctba_destroy", "ctba_last_error", "ctba_set_stream", "ctba_set_knots", "ctba_num_knots", "ctba_get_knots",
+    "ctba_initialize_biases", "ctba_num_bias_knots", "ctba_set_biases", "ctba_get_biases", "ctba_set_landmarks", "ctba_get_landmarks",
+    "ctba_set_camera", "ctba_set_globals", "ctba_set_corrections", "ctba_get_globals", "ctba_set_flags", "ctba_add_frames", "ctba_add_imu",
+    "ctba_add_gp", "ctba_add_bias_cost", "ctba_add_gravity_norm", "ctba_counts", "ctba_evaluate", "ctba_cost", "ctba_solve",
+    "ctba_relinearize_time_offsets", "ctba_bench_evaluate",
+]
+
+
+class CtbaError(RuntimeError):
+    pass
+
+
+class _Iteration(C.Structure):
+    _fields_ = [("cost", C.c_double), ("cost_change", C.c_double), ("gradient_max_norm", C.c_double), ("step_norm", C.c_double),
+                ("tr_ratio", C.c_double), ("tr_radius", C.c_double), ("successful", C.c_int)]
+
+
+class _Summary(C.Structure):
+    _fields_ = [("termination_type", C.c_int), ("initial_cost", C.c_double), ("final_cost", C.c_double),
+                ("num_successful_steps", C.c_int), ("num_unsuccessful_steps", C.c_int), ("num_iterations", C.c_int),
+                ("iterations", C.POINTER(_Iteration)), ("iterations_capacity", C.c_int),
+                ("time_total_s", C.c_double), ("time_eval_s", C.c_double), ("time_build_s", C.c_double), ("time_solve_s", C.c_double)]
+
+
+def lib():
+    """Load csrc/libctba.so (built by __graft_entry__.build()).  Fails loudly when it is missing."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise CtbaError(f"CUDA extension missing: {LIB_PATH} (run __graft_entry__.build()); there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        L.ctba_last_error.restype = C.c_char_p
+        L.ctba_last_error.argtypes = [C.c_void_p]
+        _LIB = L
+    return _LIB
+
+
+def _d(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class BSplineSO3R3:
+    """GPU-resident continuous-time problem: state + measurements + LM solve (ctba.h)."""
+
+    def __init__(self, order, dt_ns, start_t_ns=0, device=0):
+        self.L = lib()
+        self.N = int(order)
+        self.h = C.c_void_p()
+        rc = self.L.ctba_create(self.N, C.c_int64(int(dt_ns)), C.c_int64(int(start_t_ns)), int(device), C.byref(self.h))
+        if rc != 0:
+            self.h = None
+            raise CtbaError(f"ctba_create failed with code {rc} (no CUDA device or bad arguments); there is no CPU fallback")
+        self._nlm = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.ctba_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _chk(self, rc):
+        if rc < 0:
+            msg = self.L.ctba_last_error(self.h)
+            raise CtbaError(f"ctba error {rc}: {msg.decode() if msg else ''}")
+        return rc
+
+    def setStream(self, cuda_stream_ptr):
+        self._chk(self.L.ctba_set_stream(self.h, C.c_void_p(cuda_stream_ptr)))
+
+    # ---- state ----
+    def setKnots(self, quat_xyzw, pos):
+        q, p = _d(quat_xyzw), _d(pos)
+        assert q.shape[0] == p.shape[0]
+        self._chk(self.L.ctba_set_knots(self.h, int(q.shape[0]), _p(q), _p(p)))
+
+    def numKnots(self):
+        return self.L.ctba_num_knots(self.h)
+
+    def getKnots(self):
+        n = self.numKnots()
+        q, p = np.zeros((n, 4)), np.zeros((n, 3))
+        self._chk(self.L.ctba_get_knots(self.h, _p(q), _p(p)))
+        return q, p
+
+    def initializeBiases(self, dt_s_bias, acc0, gyr0):
+        a, g = _d(acc0), _d(gyr0)
+        return self._chk(self.L.ctba_initialize_biases(self.h, C.c_double(dt_s_bias), _p(a), _p(g)))
+
+    def numBiasKnots(self):
+        return self.L.ctba_num_bias_knots(self.h)
+
+    def setBiases(self, acc, gyr):
+        a, g = _d(acc), _d(gyr)
+        self._chk(self.L.ctba_set_biases(self.h, _p(a), _p(g)))
+
+    def getBiases(self):
+        n = self.numBiasKnots()
+        a, g = np.zeros((n, 3)), np.zeros((n, 3))
+        self._chk(self.L.ctba_get_biases(self.h, _p(a), _p(g)))
+        return a, g
+
+    def set3DPoints(self, xyz):
+        x = _d(xyz)
+        self._nlm = int(x.shape[0])
+        self._chk(self.L.ctba_set_landmarks(self.h, self._nlm, _p(x)))
+
+    def get3DPoints(self):
+        x = np.zeros((self._nlm, 3))
+        self._chk(self.L.ctba_get_landmarks(self.h, _p(x)))
+        return x
+
+    def setCamera(self, model, intr, dist, q_bc, p_bc, t_offset_cam_imu):
+        a = [_d(v) for v in (intr, dist, q_bc, p_bc)]
+        self._chk(self.L.ctba_set_camera(self.h, int(model), *[_p(v) for v in a], C.c_double(t_offset_cam_imu)))
+
+    def setGlobals(self, scale, p_bp, g, t_s_gp_s):
+        a, b = _d(p_bp), _d(g)
+        self._chk(self.L.ctba_set_globals(self.h, C.c_double(scale), _p(a), _p(b), C.c_double(t_s_gp_s)))
+
+    def setCorrections(self, corr10):
+        c = _d(corr10)
+        assert c.size == 10
+        self._chk(self.L.ctba_set_corrections(self.h, _p(c)))
+
+    def getGlobals(self):
+        o = np.zeros(19)
+        self._chk(self.L.ctba_get_globals(self.h, _p(o)))
+        return o
+
+    def setFlags(self, optimize_scale, optimize_pbp, optimize_gravity, optimize_camimu_extrinsics, optimize_t_offset_s_gs):
+        self._chk(self.L.ctba_set_flags(self.h, int(optimize_scale), int(optimize_pbp), int(optimize_gravity),
+                                        int(optimize_camimu_extrinsics), int(optimize_t_offset_s_gs)))
+
+    # ---- measurements ----
+    def addFrames(self, t_ns, obs_begin, uv, lm_index, sigma_px):
+        t = np.ascontiguousarray(t_ns, dtype=np.int64)
+        ob = np.ascontiguousarray(obs_begin, dtype=np.int32)
+        u = _d(uv)
+        li = np.ascontiguousarray(lm_index, dtype=np.int32)
+        assert ob.size == t.size + 1
+        return self._chk(self.L.ctba_add_frames(self.h, int(t.size), _p(t), _p(ob), _p(u), _p(li), C.c_double(sigma_px)))
+
+    def addImu(self, t_ns, acc, gyr, acc_noise_density, gyro_noise_density):
+        t = np.ascontiguousarray(t_ns, dtype=np.int64)
+        a, g = _d(acc), _d(gyr)
+        return self._chk(self.L.ctba_add_imu(self.h, int(t.size), _p(t), _p(a), _p(g), C.c_double(acc_noise_density), C.c_double(gyro_noise_density)))
+
+    def addGp(self, t_ns, pos, noise):
+        t = np.ascontiguousarray(t_ns, dtype=np.int64)
+        x = _d(pos)
+        return self._chk(self.L.ctba_add_gp(self.h, int(t.size), _p(t), _p(x), C.c_double(noise)))
+
+    def addImuBiasCost(self, freq_hz, dt_s, acc_rw, gyr_rw):
+        return self._chk(self.L.ctba_add_bias_cost(self.h, C.c_double(freq_hz), C.c_double(dt_s), C.c_double(acc_rw), C.c_double(gyr_rw)))
+
+    def addGravityNormError(self):
+        self._chk(self.L.ctba_add_gravity_norm(self.h))
+
+    def counts(self):
+        c = np.zeros(8, dtype=np.int64)
+        self._chk(self.L.ctba_counts(self.h, _p(c)))
+        return dict(zip(["frames", "obs", "accel", "gyro", "gp", "bias", "gravity", "cols"], [int(v) for v in c]))
+
+    # ---- evaluation / solve ----
+    def jac_width(self, kind):
+        N = self.N
+        return [6 * N + 10, 6 * N + 16, 3 * N + 13, 6 * N + 5, 24, 3][kind]
+
+    def evaluate(self, kind, jac=True):
+        c = self.counts()
+        nres = [2 * c["obs"], 3 * c["accel"], 3 * c["gyro"], 3 * c["gp"], 3 * c["bias"], c["gravity"]][kind]
+        r = np.zeros(nres)
+        J = np.zeros((nres, self.jac_width(kind))) if jac else None
+        n = self._chk(self.L.ctba_evaluate(self.h, int(kind), _p(r), _p(J) if jac else None))
+        assert n == nres
+        return r, J
+
+    def cost(self):
+        o = np.zeros(7)
+        self._chk(self.L.ctba_cost(self.h, _p(o)))
+        return o
+
+    def optimize(self, max_num_iterations):
+        cap = max_num_iterations + 2
+        its = (_Iteration * cap)()
+        s = _Summary()
+        s.iterations = C.cast(its, C.POINTER(_Iteration))
+        s.iterations_capacity = cap
+        self._chk(self.L.ctba_solve(self.h, int(max_num_iterations), C.byref(s)))
+        n = min(s.num_iterations, cap)
+        log = np.array([[its[i].cost, its[i].cost_change, its[i].gradient_max_norm, its[i].step_norm, its[i].tr_ratio, its[i].tr_radius,
+                         its[i].successful] for i in range(n)]).reshape(n, 7)
+        return dict(termination_type=s.termination_type, initial_cost=s.initial_cost, final_cost=s.final_cost,
+                    num_successful_steps=s.num_successful_steps, num_unsuccessful_steps=s.num_unsuccessful_steps, iterations=log,
+                    time_total_s=s.time_total_s, time_eval_s=s.time_eval_s, time_build_s=s.time_build_s, time_solve_s=s.time_solve_s)
+
+    def relinearize(self):
+        self._chk(self.L.ctba_relinearize_time_offsets(self.h))
+
+    def benchEvaluate(self, reps):
+        n = C.c_int64(0)
+        self._chk(self.L.ctba_bench_evaluate(self.h, int(reps), C.byref(n)))
+        return int(n.value)
+
+
+def load_scene(prob, sc, with_imu=True, with_gp=True, with_frames=True, with_bias_cost=True):
+    """Feed a synthetic scene (scene.make_scene) into any object with the BSplineSO3R3 method set
+    (the CUDA problem or the CPU oracle), in the reference driver's order
+    (src/optimize_continuous_time.cpp:478-601)."""
+    prob.setCamera(sc["cam_model"], sc["intr"], sc["dist"], sc["q_bc"], sc["p_bc"], sc["t_offset_cam_imu"])
+    prob.setKnots(sc["knot_q"], sc["knot_p"])
+    prob.setGlobals(sc["scale"], sc["p_bp"], sc["g"], sc["t_s_gp"])
+    prob.setFlags(*sc["flags"])
+    prob.set3DPoints(sc["landmarks"])
+    if sc.get("gravity_norm", False):
+        prob.addGravityNormError()
+    n = {}
+    if with_imu and sc["imu_t_ns"].size:
+        prob.initializeBiases(sc["dt_s_bias"], sc["init_acc_bias"], sc["init_gyro_bias"])
+    if with_gp and sc["gp_t_ns"].size:
+        n["gp"] = prob.addGp(sc["gp_t_ns"], sc["gp_pos"], sc["gp_std"])
+    if with_imu and sc["imu_t_ns"].size:
+        n["imu"] = prob.addImu(sc["imu_t_ns"], sc["imu_acc"], sc["imu_gyr"], sc["sigma_acc_c"], sc["sigma_omega_c"])
+    if with_frames and sc["frame_t_ns"].size:
+        n["frames"] = prob.addFrames(sc["frame_t_ns"], sc["obs_begin"], sc["uv"], sc["lm_index"], sc["sigma_reproj_px"])
+    if with_imu and with_bias_cost and sc["imu_t_ns"].size:
+        n["bias"] = prob.addImuBiasCost(sc["bias_err_freq_hz"], sc["bias_err_dt_s"], sc["sigma_acc_bias_c"], sc["sigma_omega_bias_c"])
+    return n

@@ -1,0 +1,453 @@
+// ctba_api.cu — the C ABI (include/ctba.h): problem assembly on the host, device mirrors, evaluate/solve entry points.
+// Problem-assembly semantics (timestamp -> spline window, skip rules, clamps) restate
+// /root/reference/include/spline/bspline_so3r3.h:355-369, 523-1046, 1807-1875 (cited per function in ctba.h).
+#include <cmath>
+#include <cstring>
+#include "ctba_internal.h"
+
+using namespace ctba;
+
+namespace ctba {
+
+int sync_to_device(ctba_problem* p) {
+  cudaStream_t st = p->stream;
+  if (p->meas_dirty) {
+    CTBA_CUDA(p, p->d_f_s.upload(p->f_s, st)); CTBA_CUDA(p, p->d_f_u.upload(p->f_u, st)); CTBA_CUDA(p, p->d_f_inv_std.upload(p->f_inv_std, st));
+    CTBA_CUDA(p, p->d_f_obs_begin.upload(p->f_obs_begin, st));
+    CTBA_CUDA(p, p->d_o_uv.upload(p->o_uv, st)); CTBA_CUDA(p, p->d_o_lm.upload(p->o_lm, st)); CTBA_CUDA(p, p->d_o_frame.upload(p->o_frame, st));
+    CTBA_CUDA(p, p->d_i_s.upload(p->i_s, st)); CTBA_CUDA(p, p->d_i_sb.upload(p->i_sb, st)); CTBA_CUDA(p, p->d_i_st_s.upload(p->i_st_s, st));
+    CTBA_CUDA(p, p->d_i_k.upload(p->i_k, st)); CTBA_CUDA(p, p->d_i_ub.upload(p->i_ub, st)); CTBA_CUDA(p, p->d_i_inv_a.upload(p->i_inv_a, st));
+    CTBA_CUDA(p, p->d_i_inv_g.upload(p->i_inv_g, st)); CTBA_CUDA(p, p->d_i_acc.upload(p->i_acc, st)); CTBA_CUDA(p, p->d_i_gyr.upload(p->i_gyr, st));
+    CTBA_CUDA(p, p->d_g_s.upload(p->g_s, st)); CTBA_CUDA(p, p->d_g_st_s.upload(p->g_st_s, st)); CTBA_CUDA(p, p->d_g_k.upload(p->g_k, st));
+    CTBA_CUDA(p, p->d_g_inv_std.upload(p->g_inv_std, st)); CTBA_CUDA(p, p->d_g_meas.upload(p->g_meas, st));
+    CTBA_CUDA(p, p->d_b_s0.upload(p->b_s0, st)); CTBA_CUDA(p, p->d_b_s1.upload(p->b_s1, st)); CTBA_CUDA(p, p->d_b_which.upload(p->b_which, st));
+    CTBA_CUDA(p, p->d_b_u0.upload(p->b_u0, st)); CTBA_CUDA(p, p->d_b_u1.upload(p->b_u1, st)); CTBA_CUDA(p, p->d_b_inv_std.upload(p->b_inv_std, st));
+    p->meas_dirty = false;
+  }
+  if (p->state_dirty) {
+    // padded copies so that 12-element bias window reads never leave the allocation even with zero bias knots
+    std::vector<double> ba = p->bias_a, bg = p->bias_g;
+    if (ba.size() < 12) { ba.resize(12, 0.0); bg.resize(12, 0.0); }
+    CTBA_CUDA(p, p->dstate.knot_q.upload(p->knot_q, st)); CTBA_CUDA(p, p->dstate.knot_p.upload(p->knot_p, st));
+    CTBA_CUDA(p, p->dstate.bias_a.upload(ba, st)); CTBA_CUDA(p, p->dstate.bias_g.upload(bg, st));
+    std::vector<double> lm = p->lm;
+    if (lm.empty()) lm.resize(3, 0.0);
+    CTBA_CUDA(p, p->dstate.lm.upload(lm, st));
+    std::vector<double> g(p->glb, p->glb + GLB_STATE_SIZE);
+    CTBA_CUDA(p, p->dstate.glb.upload(g, st));
+    CTBA_CUDA(p, cudaStreamSynchronize(st));  // the staging vectors above are temporaries
+    p->state_dirty = false;
+    p->host_state_stale = false;
+  }
+  return CTBA_OK;
+}
+
+int download_state(ctba_problem* p) {
+  if (!p->host_state_stale) return CTBA_OK;
+  cudaStream_t st = p->stream;
+  auto dl = [&](std::vector<double>& h, const DBuf<double>& d) -> cudaError_t {
+    if (h.empty()) return cudaSuccess;
+    return cudaMemcpyAsync(h.data(), d.p, h.size() * sizeof(double), cudaMemcpyDeviceToHost, st);
+  };
+  CTBA_CUDA(p, dl(p->knot_q, p->dstate.knot_q)); CTBA_CUDA(p, dl(p->knot_p, p->dstate.knot_p));
+  CTBA_CUDA(p, dl(p->bias_a, p->dstate.bias_a)); CTBA_CUDA(p, dl(p->bias_g, p->dstate.bias_g));
+  CTBA_CUDA(p, dl(p->lm, p->dstate.lm));
+  CTBA_CUDA(p, cudaMemcpyAsync(p->glb, p->dstate.glb.p, GLB_STATE_SIZE * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CTBA_CUDA(p, cudaStreamSynchronize(st));
+  p->host_state_stale = false;
+  return CTBA_OK;
+}
+
+}  // namespace ctba
+
+#define CHECK_P(p) do { if (!(p)) return CTBA_E_ARG; } while (0)
+static int fail(ctba_problem* p, int code, const char* msg) { p->err = msg; return code; }
+
+extern "C" {
+
+int ctba_create(int order, int64_t dt_ns, int64_t start_t_ns, int device, ctba_problem** out) {
+  if (!out) return CTBA_E_ARG;
+  *out = nullptr;
+  if ((order != 4 && order != 6) || dt_ns <= 0) return CTBA_E_ARG;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) return CTBA_E_CUDA;
+  if (cudaSetDevice(device) != cudaSuccess) return CTBA_E_CUDA;
+  ctba_problem* p = new ctba_problem();
+  p->N = order; p->dt_ns = dt_ns; p->start_t_ns = start_t_ns; p->device = device;
+  p->dt_s = dt_ns * 1e-9;
+  p->inv_dt = 1e9 / dt_ns;
+  if (cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking) != cudaSuccess) { delete p; return CTBA_E_CUDA; }
+  p->own_stream = true;
+  *out = p;
+  return CTBA_OK;
+}
+
+int ctba_destroy(ctba_problem* p) {
+  CHECK_P(p);
+  cudaSetDevice(p->device);
+  cudaStreamSynchronize(p->stream);
+  if (p->solver) solver_free(p->solver);
+  DBuf<double>* dd[] = {&p->dstate.knot_q, &p->dstate.knot_p, &p->dstate.bias_a, &p->dstate.bias_g, &p->dstate.lm, &p->dstate.glb,
+                        &p->d_f_u, &p->d_f_inv_std, &p->d_o_uv, &p->d_i_st_s, &p->d_i_k, &p->d_i_ub, &p->d_i_inv_a, &p->d_i_inv_g, &p->d_i_acc,
+                        &p->d_i_gyr, &p->d_g_st_s, &p->d_g_k, &p->d_g_inv_std, &p->d_g_meas, &p->d_b_u0, &p->d_b_u1, &p->d_b_inv_std,
+                        &p->ev.frame_pose, &p->ev.r_reproj, &p->ev.Jl, &p->ev.f_sq, &p->ev.f_w, &p->ev.f_cost, &p->ev.r_acc, &p->ev.r_gyr,
+                        &p->ev.J_acc, &p->ev.J_gyr, &p->ev.r_gp, &p->ev.J_gp, &p->ev.r_bias, &p->ev.J_bias, &p->ev.r_grav, &p->ev.J_grav,
+                        &p->ev.partial, &p->ev.cost};
+  for (auto* d : dd) d->release();
+  DBuf<int32_t>* di[] = {&p->d_f_s, &p->d_f_obs_begin, &p->d_o_lm, &p->d_o_frame, &p->d_i_s, &p->d_i_sb, &p->d_g_s, &p->d_b_s0, &p->d_b_s1, &p->d_b_which};
+  for (auto* d : di) d->release();
+  if (p->own_stream) cudaStreamDestroy(p->stream);
+  delete p;
+  return CTBA_OK;
+}
+
+const char* ctba_last_error(const ctba_problem* p) { return p ? p->err.c_str() : "null handle"; }
+
+int ctba_set_stream(ctba_problem* p, void* s) {
+  CHECK_P(p);
+  cudaStreamSynchronize(p->stream);
+  if (s) {
+    if (p->own_stream) cudaStreamDestroy(p->stream);
+    p->stream = (cudaStream_t)s; p->own_stream = false;
+  } else if (!p->own_stream) {
+    CTBA_CUDA(p, cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+    p->own_stream = true;
+  }
+  return CTBA_OK;
+}
+
+int ctba_set_knots(ctba_problem* p, int n, const double* q, const double* pos) {
+  CHECK_P(p);
+  if (n < 0 || !q || !pos) return fail(p, CTBA_E_ARG, "set_knots: bad arguments");
+  if (!p->f_s.empty() || !p->i_s.empty() || !p->g_s.empty()) {
+    if ((size_t)n != p->numKnots()) return fail(p, CTBA_E_STATE, "set_knots: knot count cannot change after measurements were added");
+  }
+  p->knot_q.assign(q, q + 4 * (size_t)n); p->knot_p.assign(pos, pos + 3 * (size_t)n);
+  p->state_dirty = true;
+  return CTBA_OK;
+}
+int ctba_num_knots(const ctba_problem* p) { return p ? (int)p->numKnots() : CTBA_E_ARG; }
+int ctba_get_knots(ctba_problem* p, double* q, double* pos) {
+  CHECK_P(p);
+  cudaSetDevice(p->device);
+  int rc = download_state(p); if (rc) return rc;
+  if (q) std::memcpy(q, p->knot_q.data(), p->knot_q.size() * sizeof(double));
+  if (pos) std::memcpy(pos, p->knot_p.data(), p->knot_p.size() * sizeof(double));
+  return CTBA_OK;
+}
+
+int ctba_initialize_biases(ctba_problem* p, double dt_s_bias, const double* a0, const double* g0) {
+  CHECK_P(p);
+  if (!(dt_s_bias > 0) || !a0 || !g0) return fail(p, CTBA_E_ARG, "initialize_biases: bad arguments");
+  if (!p->i_s.empty() || !p->b_s0.empty()) return fail(p, CTBA_E_STATE, "initialize_biases: IMU measurements already added");
+  p->dt_ns_bias = (int64_t) static_cast<uint64_t>(dt_s_bias / 1e-9);  // :363
+  p->inv_dt_bias = 1e9 / p->dt_ns_bias;
+  double d = p->dt_s * (double)(p->knot_p.size() / 3);
+  int num_knots = (int)(d / dt_s_bias);
+  p->bias_a.resize(3 * (size_t)num_knots); p->bias_g.resize(3 * (size_t)num_knots);
+  for (int i = 0; i < num_knots; ++i) for (int c = 0; c < 3; ++c) { p->bias_a[3 * i + c] = a0[c]; p->bias_g[3 * i + c] = g0[c]; }
+  p->state_dirty = true;
+  return num_knots;
+}
+int ctba_num_bias_knots(const ctba_problem* p) { return p ? (int)p->numBiasKnots() : CTBA_E_ARG; }
+int ctba_set_biases(ctba_problem* p, const double* a, const double* g) {
+  CHECK_P(p);
+  if (!a || !g) return CTBA_E_ARG;
+  cudaSetDevice(p->device);
+  int rc = download_state(p); if (rc) return rc;
+  std::memcpy(p->bias_a.data(), a, p->bias_a.size() * sizeof(double)); std::memcpy(p->bias_g.data(), g, p->bias_g.size() * sizeof(double));
+  p->state_dirty = true;
+  return CTBA_OK;
+}
+int ctba_get_biases(ctba_problem* p, double* a, double* g) {
+  CHECK_P(p);
+  cudaSetDevice(p->device);
+  int rc = download_state(p); if (rc) return rc;
+  if (a) std::memcpy(a, p->bias_a.data(), p->bias_a.size() * sizeof(double));
+  if (g) std::memcpy(g, p->bias_g.data(), p->bias_g.size() * sizeof(double));
+  return CTBA_OK;
+}
+
+int ctba_set_landmarks(ctba_problem* p, int n, const double* xyz) {
+  CHECK_P(p);
+  if (n < 0 || !xyz) return fail(p, CTBA_E_ARG, "set_landmarks: bad arguments");
+  for (int32_t l : p->o_lm) if (l >= n) return fail(p, CTBA_E_ARG, "set_landmarks: existing observations reference a landmark beyond n");
+  cudaSetDevice(p->device);
+  int rc = download_state(p); if (rc) return rc;
+  p->lm.assign(xyz, xyz + 3 * (size_t)n);
+  p->state_dirty = true;
+  return CTBA_OK;
+}
+int ctba_get_landmarks(ctba_problem* p, double* xyz) {
+  CHECK_P(p);
+  cudaSetDevice(p->device);
+  int rc = download_state(p); if (rc) return rc;
+  if (xyz) std::memcpy(xyz, p->lm.data(), p->lm.size() * sizeof(double));
+  return CTBA_OK;
+}
+
+int ctba_set_camera(ctba_problem* p, int model, const double* intr, const double* dist, const double* q_bc, const double* p_bc, double t_off) {
+  CHECK_P(p);
+  if (!intr || !dist || !q_bc || !p_bc) return fail(p, CTBA_E_ARG, "set_camera: null pointer");
+  if (model != 4 && model != 5 && model != 7) return fail(p, CTBA_E_ARG, "set_camera: camera model id not supported (camera_calib.h:241)");
+  p->cam.model = model; p->cam.fx = intr[0]; p->cam.fy = intr[1]; p->cam.cx = intr[2]; p->cam.cy = intr[3];
+  for (int i = 0; i < 4; ++i) { p->cam.d[i] = dist[i]; p->q_bc0[i] = q_bc[i]; }
+  for (int i = 0; i < 3; ++i) p->p_bc0[i] = p_bc[i];
+  p->cam_t_offset_cam_imu = t_off;
+  p->t_offset_cam_imu_s = t_off;
+  return CTBA_OK;
+}
+
+int ctba_set_globals(ctba_problem* p, double scale, const double* p_bp, const double* g, double t_s_gp_s) {
+  CHECK_P(p);
+  if (!p_bp || !g) return CTBA_E_ARG;
+  cudaSetDevice(p->device);
+  int rc = download_state(p); if (rc) return rc;
+  p->scale = scale;
+  for (int i = 0; i < 3; ++i) { p->glb[GLB_PBP + i] = p_bp[i]; p->glb[GLB_G + i] = g[i]; }
+  p->t_s_gp_init_s = t_s_gp_s; p->t_s_gp_s = t_s_gp_s;
+  p->state_dirty = true;
+  return CTBA_OK;
+}
+int ctba_set_corrections(ctba_problem* p, const double* c) {
+  CHECK_P(p);
+  if (!c) return CTBA_E_ARG;
+  cudaSetDevice(p->device);
+  int rc = download_state(p); if (rc) return rc;
+  p->glb[GLB_SCALE_CORR] = c[0];
+  for (int i = 0; i < 4; ++i) p->glb[GLB_RBC_CORR + i] = c[1 + i];
+  for (int i = 0; i < 3; ++i) p->glb[GLB_PBC_CORR + i] = c[5 + i];
+  p->glb[GLB_T_CAM_IMU_CORR] = c[8]; p->glb[GLB_T_GP_CORR] = c[9];
+  p->state_dirty = true;
+  return CTBA_OK;
+}
+int ctba_get_globals(ctba_problem* p, double* o) {
+  CHECK_P(p);
+  if (!o) return CTBA_E_ARG;
+  cudaSetDevice(p->device);
+  int rc = download_state(p); if (rc) return rc;
+  o[0] = p->glb[GLB_SCALE_CORR];
+  for (int i = 0; i < 4; ++i) o[1 + i] = p->glb[GLB_RBC_CORR + i];
+  for (int i = 0; i < 3; ++i) o[5 + i] = p->glb[GLB_PBC_CORR + i];
+  o[8] = p->glb[GLB_T_CAM_IMU_CORR]; o[9] = p->glb[GLB_T_GP_CORR];
+  for (int i = 0; i < 3; ++i) { o[10 + i] = p->glb[GLB_PBP + i]; o[13 + i] = p->glb[GLB_G + i]; }
+  o[16] = p->t_offset_cam_imu_s; o[17] = p->t_s_gp_s; o[18] = p->scale;
+  return CTBA_OK;
+}
+int ctba_set_flags(ctba_problem* p, int s, int pbp, int g, int ci, int tgs) {
+  CHECK_P(p);
+  p->optimize_scale = s; p->optimize_p_bp = pbp; p->optimize_gravity = g; p->optimize_camimu_extrinsics = ci; p->optimize_t_offset_s_gs = tgs;
+  return CTBA_OK;
+}
+
+int ctba_add_frames(ctba_problem* p, int F, const int64_t* t_ns, const int32_t* obs_begin, const double* uv, const int32_t* lmi, double noise) {
+  CHECK_P(p);
+  if (F < 0 || !t_ns || !obs_begin || (!uv && F) || (!lmi && F) || !(noise > 0)) return fail(p, CTBA_E_ARG, "add_frames: bad arguments");
+  const int N = p->N;
+  const int64_t L = (int64_t)p->lm.size() / 3;
+  int added = 0;
+  for (int f = 0; f < F; ++f) {
+    if (obs_begin[f + 1] < obs_begin[f]) return fail(p, CTBA_E_ARG, "add_frames: obs_begin not monotone");
+    int64_t st_ns = t_ns[f] - p->start_t_ns;
+    if (st_ns < 0) continue;                                    // :964
+    const int n = obs_begin[f + 1] - obs_begin[f];
+    if (n == 0) continue;                                       // :967
+    int64_t s = st_ns / p->dt_ns;
+    double u = double(st_ns % p->dt_ns) / double(p->dt_ns);     // :969-970
+    if (size_t(s + N) > p->numKnots()) continue;                // :973
+    for (int i = obs_begin[f]; i < obs_begin[f + 1]; ++i)
+      if (lmi[i] < 0 || lmi[i] >= L) return fail(p, CTBA_E_ARG, "add_frames: Point 3D not found (bspline_so3r3.h:1024)");
+    const int fid = (int)p->f_s.size();
+    p->f_s.push_back((int32_t)s); p->f_u.push_back(u); p->f_inv_std.push_back(1.0 / noise);
+    for (int i = obs_begin[f]; i < obs_begin[f + 1]; ++i) {
+      p->o_uv.push_back(uv[2 * (size_t)i]); p->o_uv.push_back(uv[2 * (size_t)i + 1]);
+      p->o_lm.push_back(lmi[i]); p->o_frame.push_back(fid);
+    }
+    p->f_obs_begin.push_back((int32_t)p->o_lm.size());
+    ++added;
+  }
+  p->meas_dirty = true;
+  return added;
+}
+
+static int64_t end_t_ns_bias(const ctba_problem* p) {  // getEndTnsBiasSpline :1870-1875 (N_, not Nb_)
+  int a = (int)p->numBiasKnots() - p->N + 1;
+  int64_t t_end_ns = (int64_t)a * p->dt_ns_bias + p->start_t_ns;
+  return t_end_ns - (int64_t)1e6;
+}
+
+int ctba_add_imu(ctba_problem* p, int n, const int64_t* t_ns, const double* acc, const double* gyr, double acc_nd, double gyr_nd) {
+  CHECK_P(p);
+  if (n < 0 || !t_ns || !acc || !gyr || !(acc_nd > 0) || !(gyr_nd > 0)) return fail(p, CTBA_E_ARG, "add_imu: bad arguments");
+  if ((int)p->numBiasKnots() < p->N) return fail(p, CTBA_E_STATE, "add_imu: initialize_biases first (needs >= N bias knots)");
+  const int N = p->N;
+  int added = 0;
+  for (int i = 0; i < n; ++i) {
+    int64_t t_offset_imu_cam_ns = static_cast<int64_t>(-p->t_offset_cam_imu_s * 1e9);  // :525-526
+    int64_t st_ns = (t_ns[i] + t_offset_imu_cam_ns - p->start_t_ns);
+    double st_s = st_ns * 1e-9;
+    if (st_ns < 0) continue;
+    int64_t s = st_ns / p->dt_ns;
+    int k_int = (int)(st_ns / p->dt_ns);
+    if (size_t(s + N) > p->numKnots()) continue;
+    int64_t st_bias_ns = (t_ns[i] - p->start_t_ns);
+    int64_t s_bias = st_bias_ns / p->dt_ns_bias;
+    double u_bias = double(st_bias_ns % p->dt_ns_bias) / double(p->dt_ns_bias);
+    if (s_bias < 0) return fail(p, CTBA_E_ARG, "add_imu: s_bias < 0 (bspline_so3r3.h:548)");
+    if (size_t(s_bias + N) > p->numBiasKnots()) {  // :557-563
+      st_bias_ns = end_t_ns_bias(p) - p->start_t_ns;
+      s_bias = st_bias_ns / p->dt_ns_bias;
+      u_bias = double(st_bias_ns % p->dt_ns_bias) / double(p->dt_ns_bias);
+      if (s_bias < 0) return fail(p, CTBA_E_ARG, "add_imu: s_bias < 0 after clamp");
+    }
+    p->i_s.push_back((int32_t)s); p->i_sb.push_back((int32_t)s_bias);
+    p->i_st_s.push_back(st_s); p->i_k.push_back((double)k_int); p->i_ub.push_back(u_bias);
+    p->i_inv_a.push_back(1.0 / acc_nd); p->i_inv_g.push_back(1.0 / gyr_nd);
+    for (int c = 0; c < 3; ++c) { p->i_acc.push_back(acc[3 * (size_t)i + c]); p->i_gyr.push_back(gyr[3 * (size_t)i + c]); }
+    ++added;
+  }
+  p->meas_dirty = true;
+  return added;
+}
+
+int ctba_add_gp(ctba_problem* p, int n, const int64_t* t_ns, const double* pos, double noise) {
+  CHECK_P(p);
+  if (n < 0 || !t_ns || !pos || !(noise > 0)) return fail(p, CTBA_E_ARG, "add_gp: bad arguments");
+  const int N = p->N;
+  int added = 0;
+  for (int i = 0; i < n; ++i) {
+    int64_t t_s_gp_init_ns = static_cast<int64_t>(p->t_s_gp_s * 1e9);  // :882
+    int64_t st_ns = (t_ns[i] - p->start_t_ns - t_s_gp_init_ns);
+    double st_s = st_ns * 1e-9;
+    if (st_ns < 0) continue;
+    int64_t s = st_ns / p->dt_ns;
+    int k_int = (int)(st_ns / p->dt_ns);
+    if (size_t(s + N) > p->numKnots()) continue;
+    p->g_s.push_back((int32_t)s); p->g_st_s.push_back(st_s); p->g_k.push_back((double)k_int); p->g_inv_std.push_back(1.0 / noise);
+    for (int c = 0; c < 3; ++c) p->g_meas.push_back(pos[3 * (size_t)i + c]);
+    ++added;
+  }
+  p->meas_dirty = true;
+  return added;
+}
+
+int ctba_add_bias_cost(ctba_problem* p, double freq_hz, double bias_err_dt_s, double acc_rw, double gyr_rw) {
+  CHECK_P(p);
+  if (!(freq_hz > 0) || !(acc_rw > 0) || !(gyr_rw > 0)) return fail(p, CTBA_E_ARG, "add_bias_cost: bad arguments");
+  // the two 4-knot windows of a block must be disjoint (Ceres rejects duplicate parameter blocks;
+  // optimize_vi_continuous_time.cpp:489-490 asserts bias_err_dt_s >= 4*dt_bias)
+  if (bias_err_dt_s * 1e9 < 4.0 * (double)p->dt_ns_bias) return fail(p, CTBA_E_ARG, "add_bias_cost: bias_err_dt_s must be >= 4 * dt_bias");
+  const int Nb = 4;
+  double err_freq_s = 1.0 / freq_hz;
+  double err_freq_ns = (double) static_cast<uint64_t>(err_freq_s / 1e-9);
+  int64_t t_start_ns = p->start_t_ns;
+  int64_t t_end_ns = end_t_ns_bias(p);
+  int64_t bias_err_dt_ns = static_cast<int64_t>(bias_err_dt_s * 1e9);
+  int added = 0;
+  for (int64_t t_ns = t_start_ns; t_ns < t_end_ns; t_ns += err_freq_ns) {
+    int64_t st0 = t_ns - p->start_t_ns, st1 = t_ns + bias_err_dt_ns - p->start_t_ns;
+    int64_t s0 = st0 / p->dt_ns_bias, s1 = st1 / p->dt_ns_bias;
+    double u0 = double(st0 % p->dt_ns_bias) / double(p->dt_ns_bias), u1 = double(st1 % p->dt_ns_bias) / double(p->dt_ns_bias);
+    if (size_t(s0 + Nb) > p->numBiasKnots()) continue;
+    if (size_t(s1 + Nb) > p->numBiasKnots()) continue;
+    for (int which = 0; which < 2; ++which) {
+      p->b_s0.push_back((int32_t)s0); p->b_s1.push_back((int32_t)s1); p->b_which.push_back(which);
+      p->b_u0.push_back(u0); p->b_u1.push_back(u1);
+      p->b_inv_std.push_back(1.0 / (0.001 * (which == 0 ? acc_rw : gyr_rw)));  // :736, :765
+    }
+    ++added;
+  }
+  p->meas_dirty = true;
+  return added;
+}
+
+int ctba_add_gravity_norm(ctba_problem* p) { CHECK_P(p); p->gravity_norm = true; return CTBA_OK; }
+
+int ctba_counts(ctba_problem* p, int64_t* c) {
+  CHECK_P(p);
+  if (!c) return CTBA_E_ARG;
+  c[0] = (int64_t)p->numFrames(); c[1] = (int64_t)p->numObs(); c[2] = (int64_t)p->i_s.size(); c[3] = (int64_t)p->i_s.size();
+  c[4] = (int64_t)p->g_s.size(); c[5] = (int64_t)p->b_s0.size(); c[6] = p->gravity_norm ? 1 : 0;
+  c[7] = solver_num_unknowns(p);
+  return CTBA_OK;
+}
+
+int ctba_evaluate(ctba_problem* p, int kind, double* r_out, double* j_out) {
+  CHECK_P(p);
+  if (kind < 0 || kind > 5) return fail(p, CTBA_E_ARG, "evaluate: unknown residual kind");
+  CTBA_CUDA(p, cudaSetDevice(p->device));
+  int rc = sync_to_device(p); if (rc) return rc;
+  const StatePtrs S = p->dstate.ptrs();
+  rc = launch_evaluate(p, S, true); if (rc) return rc;
+  const int N = p->N;
+  cudaStream_t st = p->stream;
+  size_t nres = 0, width = 0;
+  const double *d_r = nullptr, *d_J = nullptr;
+  DBuf<double> dense;
+  switch (kind) {
+    case CTBA_REPROJ: {
+      nres = 2 * p->numObs(); width = 6 * N + 10; d_r = p->ev.r_reproj.p;
+      if (j_out && nres) {
+        CTBA_CUDA(p, dense.resize(nres * width));
+        rc = expand_reproj_dense(p, S, dense.p); if (rc) { dense.release(); return rc; }
+        d_J = dense.p;
+      }
+      break;
+    }
+    case CTBA_ACCEL: nres = 3 * p->i_s.size(); width = 6 * N + 16; d_r = p->ev.r_acc.p; d_J = p->ev.J_acc.p; break;
+    case CTBA_GYRO: nres = 3 * p->i_s.size(); width = 3 * N + 13; d_r = p->ev.r_gyr.p; d_J = p->ev.J_gyr.p; break;
+    case CTBA_GP: nres = 3 * p->g_s.size(); width = 6 * N + 5; d_r = p->ev.r_gp.p; d_J = p->ev.J_gp.p; break;
+    case CTBA_BIAS: nres = 3 * p->b_s0.size(); width = 24; d_r = p->ev.r_bias.p; d_J = p->ev.J_bias.p; break;
+    case CTBA_GRAVITY: nres = p->gravity_norm ? 1 : 0; width = 3; d_r = p->ev.r_grav.p; d_J = p->ev.J_grav.p; break;
+  }
+  cudaError_t e = cudaSuccess;
+  if (nres && r_out) e = cudaMemcpyAsync(r_out, d_r, nres * sizeof(double), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess && nres && j_out) e = cudaMemcpyAsync(j_out, d_J, nres * width * sizeof(double), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  dense.release();
+  if (e != cudaSuccess) { p->err = cudaGetErrorString(e); return CTBA_E_CUDA; }
+  return (int)nres;
+}
+
+int ctba_cost(ctba_problem* p, double* cost7) {
+  CHECK_P(p);
+  if (!cost7) return CTBA_E_ARG;
+  CTBA_CUDA(p, cudaSetDevice(p->device));
+  int rc = sync_to_device(p); if (rc) return rc;
+  rc = launch_evaluate(p, p->dstate.ptrs(), false); if (rc) return rc;
+  rc = launch_cost(p); if (rc) return rc;
+  CTBA_CUDA(p, cudaMemcpyAsync(cost7, p->ev.cost.p, 7 * sizeof(double), cudaMemcpyDeviceToHost, p->stream));
+  CTBA_CUDA(p, cudaStreamSynchronize(p->stream));
+  return CTBA_OK;
+}
+
+int ctba_solve(ctba_problem* p, int max_num_iterations, ctba_summary* summary) {
+  CHECK_P(p);
+  if (max_num_iterations < 0 || !summary) return fail(p, CTBA_E_ARG, "solve: bad arguments");
+  CTBA_CUDA(p, cudaSetDevice(p->device));
+  int rc = sync_to_device(p); if (rc) return rc;
+  return solver_solve(p, max_num_iterations, summary);
+}
+
+int ctba_relinearize_time_offsets(ctba_problem* p) {
+  CHECK_P(p);
+  cudaSetDevice(p->device);
+  int rc = download_state(p); if (rc) return rc;
+  // :1807-1811, :1853-1857 — bookkeeping only: the work items keep the st_s, k captured when they were added
+  p->t_offset_cam_imu_s += p->glb[GLB_T_CAM_IMU_CORR]; p->glb[GLB_T_CAM_IMU_CORR] = 0.0;
+  p->t_s_gp_s += p->glb[GLB_T_GP_CORR]; p->glb[GLB_T_GP_CORR] = 0.0;
+  p->state_dirty = true;
+  return CTBA_OK;
+}
+
+int ctba_bench_evaluate(ctba_problem* p, int reps, int64_t* launches) {
+  CHECK_P(p);
+  CTBA_CUDA(p, cudaSetDevice(p->device));
+  int rc = sync_to_device(p); if (rc) return rc;
+  const int64_t l0 = p->launches;
+  for (int i = 0; i < reps; ++i) { rc = launch_evaluate(p, p->dstate.ptrs(), true); if (rc) return rc; }
+  if (launches) *launches = p->launches - l0;
+  return CTBA_OK;
+}
+
+}  // extern "C"

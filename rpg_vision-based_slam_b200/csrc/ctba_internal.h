@@ -1,0 +1,129 @@
+// ctba_internal.h — host-side problem object shared by the C-ABI (ctba_api.cu), the evaluation kernels
+// (ctba_eval.cu) and the LM solver (ctba_solve.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/ctba.h"
+#include "ctba_terms.h"
+
+namespace ctba {
+
+template <class T>
+struct DBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  cudaError_t resize(size_t m) {
+    if (m <= n && p) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; n = 0;
+    if (m == 0) return cudaSuccess;
+    cudaError_t e = cudaMalloc((void**)&p, m * sizeof(T));
+    if (e == cudaSuccess) n = m;
+    return e;
+  }
+  cudaError_t upload(const std::vector<T>& h, cudaStream_t s) {
+    cudaError_t e = resize(h.size());
+    if (e != cudaSuccess || h.empty()) return e;
+    return cudaMemcpyAsync(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, s);
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+};
+
+struct StatePtrs {
+  double *knot_q, *knot_p, *bias_a, *bias_g, *lm, *glb;
+};
+
+struct DeviceState {
+  DBuf<double> knot_q, knot_p, bias_a, bias_g, lm, glb;
+  StatePtrs ptrs() const { return {knot_q.p, knot_p.p, bias_a.p, bias_g.p, lm.p, glb.p}; }
+};
+
+// Evaluation outputs (device)
+struct EvalBuffers {
+  DBuf<double> frame_pose;        // F * sizeof(FramePose<N>)/8
+  DBuf<double> r_reproj;          // 2M   (double2 per observation)
+  DBuf<double> Jl;                // 6M   planar: Jl[c*M + i]
+  DBuf<double> f_sq, f_w, f_cost; // per frame: |r|^2, sqrt(rho'), 1/2 rho
+  DBuf<double> r_acc, r_gyr, J_acc, J_gyr;
+  DBuf<double> r_gp, J_gp, r_bias, J_bias, r_grav, J_grav;
+  DBuf<double> partial;           // reduction scratch
+  DBuf<double> cost;              // 8 doubles
+};
+
+struct SolverData;  // ctba_solve.cu
+
+}  // namespace ctba
+
+struct ctba_problem {
+  int N = 6;
+  int64_t dt_ns = 0, start_t_ns = 0;
+  double dt_s = 0, inv_dt = 0;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  std::string err;
+
+  // ---- host state (bspline_so3r3.h:1936-1973) ----
+  std::vector<double> knot_q, knot_p, bias_a, bias_g, lm;
+  double glb[ctba::GLB_STATE_SIZE] = {0, 0, 0, 0, 1, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  double scale = 0, t_offset_cam_imu_s = 0, cam_t_offset_cam_imu = 0, t_s_gp_s = 0, t_s_gp_init_s = 0;
+  int64_t dt_ns_bias = 1000000000;
+  double inv_dt_bias = 1.0;
+  bool optimize_p_bp = true, optimize_gravity = false, optimize_scale = false, optimize_camimu_extrinsics = true,
+       optimize_t_offset_s_gs = true;
+  ctba::Camera cam{4, 1, 1, 0, 0, {0, 0, 0, 0}};
+  double q_bc0[4] = {0, 0, 0, 1}, p_bc0[3] = {0, 0, 0};
+  double cauchy_a = 3.0;
+
+  // ---- host work items ----
+  std::vector<int32_t> f_s, f_obs_begin{0};
+  std::vector<double> f_u, f_inv_std;
+  std::vector<double> o_uv;
+  std::vector<int32_t> o_lm, o_frame;
+  std::vector<int32_t> i_s, i_sb;
+  std::vector<double> i_st_s, i_k, i_ub, i_inv_a, i_inv_g, i_acc, i_gyr;
+  std::vector<int32_t> g_s;
+  std::vector<double> g_st_s, g_k, g_inv_std, g_meas;
+  std::vector<int32_t> b_s0, b_s1, b_which;
+  std::vector<double> b_u0, b_u1, b_inv_std;
+  bool gravity_norm = false;
+
+  // ---- device ----
+  bool meas_dirty = true, state_dirty = true, host_state_stale = false;
+  ctba::DeviceState dstate;
+  ctba::DBuf<int32_t> d_f_s, d_f_obs_begin, d_o_lm, d_o_frame, d_i_s, d_i_sb, d_g_s, d_b_s0, d_b_s1, d_b_which;
+  ctba::DBuf<double> d_f_u, d_f_inv_std, d_o_uv, d_i_st_s, d_i_k, d_i_ub, d_i_inv_a, d_i_inv_g, d_i_acc, d_i_gyr, d_g_st_s, d_g_k,
+      d_g_inv_std, d_g_meas, d_b_u0, d_b_u1, d_b_inv_std;
+  ctba::EvalBuffers ev;
+  ctba::SolverData* solver = nullptr;
+  int64_t launches = 0;  // kernels launched by this handle (bench bookkeeping)
+
+  size_t numKnots() const { return knot_q.size() / 4; }
+  size_t numBiasKnots() const { return bias_a.size() / 3; }
+  size_t numFrames() const { return f_s.size(); }
+  size_t numObs() const { return o_lm.size(); }
+};
+
+namespace ctba {
+Globals make_globals(const ctba_problem* p);
+int sync_to_device(ctba_problem* p);                 // upload dirty measurements/state
+int download_state(ctba_problem* p);                 // device state -> host vectors
+// residual (+Jacobian) evaluation of every term at state S into p->ev; cost7 (device) filled when want_cost
+int launch_evaluate(ctba_problem* p, const StatePtrs& S, bool jac);
+int launch_cost(ctba_problem* p);                    // p->ev.cost[0..6] from the residual buffers
+int expand_reproj_dense(ctba_problem* p, const StatePtrs& S, double* d_out);  // 2M x (6N+10)
+void solver_free(SolverData* s);
+int solver_solve(ctba_problem* p, int max_iters, ctba_summary* out);
+int solver_num_unknowns(ctba_problem* p);
+}  // namespace ctba
+
+#define CTBA_CUDA(p, call)                                                                                   \
+  do {                                                                                                       \
+    cudaError_t e__ = (call);                                                                                \
+    if (e__ != cudaSuccess) {                                                                                \
+      (p)->err = std::string(#call) + ": " + cudaGetErrorString(e__);                                        \
+      return CTBA_E_CUDA;                                                                                    \
+    }                                                                                                        \
+  } while (0)
