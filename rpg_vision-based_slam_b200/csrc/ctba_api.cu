@@ -92,7 +92,10 @@ int ctba_destroy(ctba_problem* p) {
                         &p->d_i_gyr, &p->d_g_st_s, &p->d_g_k, &p->d_g_inv_std, &p->d_g_meas, &p->d_b_u0, &p->d_b_u1, &p->d_b_inv_std,
                         &p->ev.frame_pose, &p->ev.r_reproj, &p->ev.Jl, &p->ev.f_sq, &p->ev.f_w, &p->ev.f_cost, &p->ev.r_acc, &p->ev.r_gyr,
                         &p->ev.J_acc, &p->ev.J_gyr, &p->ev.r_gp, &p->ev.J_gp, &p->ev.r_bias, &p->ev.J_bias, &p->ev.r_grav, &p->ev.J_grav,
-                        &p->ev.partial, &p->ev.cost};
+                        &p->ev.partial, &p->ev.cost,
+                        &p->ev_alt.frame_pose, &p->ev_alt.r_reproj, &p->ev_alt.Jl, &p->ev_alt.f_sq, &p->ev_alt.f_w, &p->ev_alt.f_cost, &p->ev_alt.r_acc,
+                        &p->ev_alt.r_gyr, &p->ev_alt.J_acc, &p->ev_alt.J_gyr, &p->ev_alt.r_gp, &p->ev_alt.J_gp, &p->ev_alt.r_bias, &p->ev_alt.J_bias,
+                        &p->ev_alt.r_grav, &p->ev_alt.J_grav, &p->ev_alt.partial, &p->ev_alt.cost};
   for (auto* d : dd) d->release();
   DBuf<int32_t>* di[] = {&p->d_f_s, &p->d_f_obs_begin, &p->d_o_lm, &p->d_o_frame, &p->d_i_s, &p->d_i_sb, &p->d_g_s, &p->d_b_s0, &p->d_b_s1, &p->d_b_which};
   for (auto* d : di) d->release();
@@ -122,6 +125,7 @@ int ctba_set_knots(ctba_problem* p, int n, const double* q, const double* pos) {
   if (!p->f_s.empty() || !p->i_s.empty() || !p->g_s.empty()) {
     if ((size_t)n != p->numKnots()) return fail(p, CTBA_E_STATE, "set_knots: knot count cannot change after measurements were added");
   }
+  if ((size_t)n != p->numKnots()) p->struct_dirty = true;
   p->knot_q.assign(q, q + 4 * (size_t)n); p->knot_p.assign(pos, pos + 3 * (size_t)n);
   p->state_dirty = true;
   return CTBA_OK;
@@ -144,6 +148,7 @@ int ctba_initialize_biases(ctba_problem* p, double dt_s_bias, const double* a0, 
   p->inv_dt_bias = 1e9 / p->dt_ns_bias;
   double d = p->dt_s * (double)(p->knot_p.size() / 3);
   int num_knots = (int)(d / dt_s_bias);
+  p->struct_dirty = true;
   p->bias_a.resize(3 * (size_t)num_knots); p->bias_g.resize(3 * (size_t)num_knots);
   for (int i = 0; i < num_knots; ++i) for (int c = 0; c < 3; ++c) { p->bias_a[3 * i + c] = a0[c]; p->bias_g[3 * i + c] = g0[c]; }
   p->state_dirty = true;
@@ -174,6 +179,7 @@ int ctba_set_landmarks(ctba_problem* p, int n, const double* xyz) {
   for (int32_t l : p->o_lm) if (l >= n) return fail(p, CTBA_E_ARG, "set_landmarks: existing observations reference a landmark beyond n");
   cudaSetDevice(p->device);
   int rc = download_state(p); if (rc) return rc;
+  if ((size_t)n * 3 != p->lm.size()) p->struct_dirty = true;
   p->lm.assign(xyz, xyz + 3 * (size_t)n);
   p->state_dirty = true;
   return CTBA_OK;
@@ -236,6 +242,7 @@ int ctba_get_globals(ctba_problem* p, double* o) {
 }
 int ctba_set_flags(ctba_problem* p, int s, int pbp, int g, int ci, int tgs) {
   CHECK_P(p);
+  p->struct_dirty = true;
   p->optimize_scale = s; p->optimize_p_bp = pbp; p->optimize_gravity = g; p->optimize_camimu_extrinsics = ci; p->optimize_t_offset_s_gs = tgs;
   return CTBA_OK;
 }
@@ -266,7 +273,7 @@ int ctba_add_frames(ctba_problem* p, int F, const int64_t* t_ns, const int32_t* 
     p->f_obs_begin.push_back((int32_t)p->o_lm.size());
     ++added;
   }
-  p->meas_dirty = true;
+  p->meas_dirty = true; p->struct_dirty = true;
   return added;
 }
 
@@ -306,7 +313,7 @@ int ctba_add_imu(ctba_problem* p, int n, const int64_t* t_ns, const double* acc,
     for (int c = 0; c < 3; ++c) { p->i_acc.push_back(acc[3 * (size_t)i + c]); p->i_gyr.push_back(gyr[3 * (size_t)i + c]); }
     ++added;
   }
-  p->meas_dirty = true;
+  p->meas_dirty = true; p->struct_dirty = true;
   return added;
 }
 
@@ -327,7 +334,7 @@ int ctba_add_gp(ctba_problem* p, int n, const int64_t* t_ns, const double* pos, 
     for (int c = 0; c < 3; ++c) p->g_meas.push_back(pos[3 * (size_t)i + c]);
     ++added;
   }
-  p->meas_dirty = true;
+  p->meas_dirty = true; p->struct_dirty = true;
   return added;
 }
 
@@ -357,11 +364,11 @@ int ctba_add_bias_cost(ctba_problem* p, double freq_hz, double bias_err_dt_s, do
     }
     ++added;
   }
-  p->meas_dirty = true;
+  p->meas_dirty = true; p->struct_dirty = true;
   return added;
 }
 
-int ctba_add_gravity_norm(ctba_problem* p) { CHECK_P(p); p->gravity_norm = true; return CTBA_OK; }
+int ctba_add_gravity_norm(ctba_problem* p) { CHECK_P(p); p->gravity_norm = true; p->struct_dirty = true; return CTBA_OK; }
 
 int ctba_counts(ctba_problem* p, int64_t* c) {
   CHECK_P(p);
@@ -378,7 +385,7 @@ int ctba_evaluate(ctba_problem* p, int kind, double* r_out, double* j_out) {
   CTBA_CUDA(p, cudaSetDevice(p->device));
   int rc = sync_to_device(p); if (rc) return rc;
   const StatePtrs S = p->dstate.ptrs();
-  rc = launch_evaluate(p, S, true); if (rc) return rc;
+  rc = launch_evaluate(p, p->ev, S, true); if (rc) return rc;
   const int N = p->N;
   cudaStream_t st = p->stream;
   size_t nres = 0, width = 0;
@@ -414,8 +421,8 @@ int ctba_cost(ctba_problem* p, double* cost7) {
   if (!cost7) return CTBA_E_ARG;
   CTBA_CUDA(p, cudaSetDevice(p->device));
   int rc = sync_to_device(p); if (rc) return rc;
-  rc = launch_evaluate(p, p->dstate.ptrs(), false); if (rc) return rc;
-  rc = launch_cost(p); if (rc) return rc;
+  rc = launch_evaluate(p, p->ev, p->dstate.ptrs(), false); if (rc) return rc;
+  rc = launch_cost(p, p->ev); if (rc) return rc;
   CTBA_CUDA(p, cudaMemcpyAsync(cost7, p->ev.cost.p, 7 * sizeof(double), cudaMemcpyDeviceToHost, p->stream));
   CTBA_CUDA(p, cudaStreamSynchronize(p->stream));
   return CTBA_OK;
@@ -445,7 +452,7 @@ int ctba_bench_evaluate(ctba_problem* p, int reps, int64_t* launches) {
   CTBA_CUDA(p, cudaSetDevice(p->device));
   int rc = sync_to_device(p); if (rc) return rc;
   const int64_t l0 = p->launches;
-  for (int i = 0; i < reps; ++i) { rc = launch_evaluate(p, p->dstate.ptrs(), true); if (rc) return rc; }
+  for (int i = 0; i < reps; ++i) { rc = launch_evaluate(p, p->ev, p->dstate.ptrs(), true); if (rc) return rc; }
   if (launches) *launches = p->launches - l0;
   return CTBA_OK;
 }

@@ -1,0 +1,1065 @@
+// ctba_assemble.cu — normal-equation assembly on the device (sm_100a, FP64).
+//
+// The reprojection Jacobian of an observation factors as J_o = Jl_o * [ I3 | X_o ], Jl_o = dr/dp_w (2x3, stored by
+// k_reproj) and X_o (3x13) = d p_w-equivalent / d(frame pose 6, reprojection globals 7), computed on the fly from the
+// frame pose record and the landmark.  With A_o = w_f^2 Jl^T Jl (3x3), b_o = w_f^2 Jl^T r:
+//   landmark block   V_l = sum_o A_o,             g_l = sum_o b_o
+//   pose-space block Q_f = sum_o X_o^T A_o X_o,   q_f = sum_o X_o^T b_o          (k_frame_direct -> knot space via the chain D_f)
+//   Schur            S(f,f') -= (A_o X_o)^T (V_l + D_l)^-1 (A_o' X_o')             (k_landmark_schur, warp per landmark, shuffles)
+//   knot space       H(win f, win f') += D_f^T S(f,f') D_f'                       (k_pose_to_knots)
+// IMU / GP / bias / gravity rows are dense local Jacobians and go straight into the band (k_rows_accumulate).
+// Replaces Ceres' J^T J formation + elimination inside SPARSE_NORMAL_CHOLESKY; LossFunction corrector
+// (CauchyLoss(3.0) per frame, bspline_so3r3.h:1032) enters as the per-frame weight w_f = sqrt(rho').
+#include <algorithm>
+#include "ctba_solver.h"
+
+namespace ctba {
+
+static inline int cdiv(size_t a, int b) { return (int)((a + b - 1) / b); }
+
+struct GMask { int a[GT_SIZE]; };
+
+// X_o (3x13): columns [phi_world 3 | p_wb 3 | scale 1 | R_bc_corr 3 | p_bc_corr 3]
+template <int N>
+__device__ __forceinline__ void obs_X(const Globals& G, const double* glb, const FramePose<N>& fp, v3 pw, double X[3][13]) {
+  v3 pwb{fp.p_wb[0], fp.p_wb[1], fp.p_wb[2]};
+  v3 d = pw - pwb;
+  m3 hd = hat(d);
+  m3 Rwb, Rcw;
+#pragma unroll
+  for (int e = 0; e < 9; ++e) { Rwb.a[e] = fp.R_wb[e]; Rcw.a[e] = fp.R_cw[e]; }
+  m3 Rwc = transpose(Rcw);
+  const double s = G.scale + glb[GLB_SCALE_CORR];
+  m3 R0 = quat_matrix(quat{G.q_bc0[0], G.q_bc0[1], G.q_bc0[2], G.q_bc0[3]});
+  v3 pbc = mul(R0, v3{glb[GLB_PBC_CORR], glb[GLB_PBC_CORR + 1], glb[GLB_PBC_CORR + 2]}) + v3{G.p_bc0[0], G.p_bc0[1], G.p_bc0[2]};
+  v3 Rp = mul(Rwb, pbc);
+  v3 pwc = s * Rp + pwb;
+  m3 hc = mul(hat(pw - pwc), Rwc);
+  m3 RR0 = mul(Rwb, R0);
+  const double rp[3] = {Rp.x, Rp.y, Rp.z};
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      X[r][c] = hd.a[3 * r + c];
+      X[r][3 + c] = (r == c) ? -1.0 : 0.0;
+      X[r][7 + c] = hc.a[3 * r + c];
+      X[r][10 + c] = -s * RR0.a[3 * r + c];
+    }
+    X[r][6] = -rp[r];
+  }
+}
+
+// per observation: A (3x3 sym as 6: xx xy xz yy yz zz) and b (3), both including the frame's robust weight
+__device__ __forceinline__ void obs_Ab(const double* __restrict__ Jl, const double2* __restrict__ r, const double* __restrict__ f_w, int M, int o,
+                                       int f, double A[6], double b[3]) {
+  double j[6];
+#pragma unroll
+  for (int c = 0; c < 6; ++c) j[c] = Jl[(size_t)c * M + o];
+  const double w = f_w[f], w2 = w * w;
+  const double2 rr = r[o];
+  A[0] = w2 * (j[0] * j[0] + j[3] * j[3]); A[1] = w2 * (j[0] * j[1] + j[3] * j[4]); A[2] = w2 * (j[0] * j[2] + j[3] * j[5]);
+  A[3] = w2 * (j[1] * j[1] + j[4] * j[4]); A[4] = w2 * (j[1] * j[2] + j[4] * j[5]); A[5] = w2 * (j[2] * j[2] + j[5] * j[5]);
+  b[0] = w2 * (j[0] * rr.x + j[3] * rr.y); b[1] = w2 * (j[1] * rr.x + j[4] * rr.y); b[2] = w2 * (j[2] * rr.x + j[5] * rr.y);
+}
+__device__ __forceinline__ void symmul3(const double A[6], const double v[3], double out[3]) {
+  out[0] = A[0] * v[0] + A[1] * v[1] + A[2] * v[2];
+  out[1] = A[1] * v[0] + A[3] * v[1] + A[4] * v[2];
+  out[2] = A[2] * v[0] + A[4] * v[1] + A[5] * v[2];
+}
+
+// ---- landmark blocks: V0_l, g_l (thread per landmark; obs lists are short) ------------------------------------
+__global__ void k_landmark_blocks(int L, const int32_t* __restrict__ lm_obs_begin, const int32_t* __restrict__ lm_obs,
+                                  const int32_t* __restrict__ o_frame, const double* __restrict__ Jl, const double2* __restrict__ r,
+                                  const double* __restrict__ f_w, int M, double* __restrict__ V0, double* __restrict__ gl) {
+  int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= L) return;
+  double V[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
+  for (int i = lm_obs_begin[l]; i < lm_obs_begin[l + 1]; ++i) {
+    const int o = lm_obs[i];
+    double A[6], b[3];
+    obs_Ab(Jl, r, f_w, M, o, o_frame[o], A, b);
+#pragma unroll
+    for (int c = 0; c < 6; ++c) V[c] += A[c];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) g[c] += b[c];
+  }
+#pragma unroll
+  for (int c = 0; c < 6; ++c) V0[6 * (size_t)l + c] = V[c];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) gl[3 * (size_t)l + c] = g[c];
+}
+
+// ---- pose chain helpers ---------------------------------------------------------------------------------------
+// D_f maps the 6N knot tangents of frame f's window to its pose tangent (phi_world, p_wb):
+//   column a = 6*i + ca (knot i, component ca): ca<3 -> phi rows get Crot_i[:,ca]; ca>=3 -> p row (ca-3) gets cpos_i.
+template <int N>
+__device__ __forceinline__ double chain_apply_T(const FramePose<N>& fp, int a, const double* v6) {  // (D_f^T v)[a]
+  const int i = a / 6, ca = a % 6;
+  if (ca < 3) return fp.Crot[i][ca] * v6[0] + fp.Crot[i][3 + ca] * v6[1] + fp.Crot[i][6 + ca] * v6[2];
+  return fp.cpos[i] * v6[ca];
+}
+
+// ---- direct (non-Schur) reprojection part: warp per frame ------------------------------------------------------
+template <int N>
+__global__ void __launch_bounds__(128) k_frame_direct(const __grid_constant__ Globals G, const double* __restrict__ glb,
+                                                      const FramePose<N>* __restrict__ fps, const double* __restrict__ lm, int F,
+                                                      const int32_t* __restrict__ f_s, const int32_t* __restrict__ obs_begin,
+                                                      const int32_t* __restrict__ o_lm, const double* __restrict__ Jl,
+                                                      const double2* __restrict__ r, const double* __restrict__ f_w, int M,
+                                                      const int32_t* __restrict__ node_of_knot, GMask gm, BandLayout H, double* __restrict__ grad) {
+  __shared__ double shQ[4][13 * 13 + 13];
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int f = blockIdx.x * 4 + wib;
+  if (f >= F) return;
+  const FramePose<N>& fp = fps[f];
+  double Q[91], q[13];
+#pragma unroll
+  for (int e = 0; e < 91; ++e) Q[e] = 0.0;
+#pragma unroll
+  for (int e = 0; e < 13; ++e) q[e] = 0.0;
+  for (int o = obs_begin[f] + lane; o < obs_begin[f + 1]; o += 32) {
+    const int l = o_lm[o];
+    v3 pw{lm[3 * (size_t)l], lm[3 * (size_t)l + 1], lm[3 * (size_t)l + 2]};
+    double X[3][13], A[6], b[3];
+    obs_X<N>(G, glb, fp, pw, X);
+    obs_Ab(Jl, r, f_w, M, o, f, A, b);
+    double Y[3][13];  // A X
+#pragma unroll
+    for (int c = 0; c < 13; ++c) {
+      const double x[3] = {X[0][c], X[1][c], X[2][c]};
+      double y[3];
+      symmul3(A, x, y);
+      Y[0][c] = y[0]; Y[1][c] = y[1]; Y[2][c] = y[2];
+      q[c] += X[0][c] * b[0] + X[1][c] * b[1] + X[2][c] * b[2];
+    }
+    int e = 0;
+#pragma unroll
+    for (int a = 0; a < 13; ++a)
+#pragma unroll
+      for (int c = 0; c <= a; ++c) { Q[e] += X[0][a] * Y[0][c] + X[1][a] * Y[1][c] + X[2][a] * Y[2][c]; ++e; }
+  }
+#pragma unroll
+  for (int e = 0; e < 91; ++e)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) Q[e] += __shfl_xor_sync(0xffffffffu, Q[e], o);
+#pragma unroll
+  for (int e = 0; e < 13; ++e)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) q[e] += __shfl_xor_sync(0xffffffffu, q[e], o);
+  double* sQ = shQ[wib];
+  if (lane == 0) {
+    int e = 0;
+#pragma unroll
+    for (int a = 0; a < 13; ++a)
+#pragma unroll
+      for (int c = 0; c <= a; ++c) { sQ[a * 13 + c] = Q[e]; sQ[c * 13 + a] = Q[e]; ++e; }
+#pragma unroll
+    for (int c = 0; c < 13; ++c) sQ[169 + c] = q[c];
+  }
+  __syncwarp();
+  // expand to knot space: unknown a in [0, 6N) -> knot window, a in [6N, 6N+7) -> reprojection globals
+  const int s = f_s[f];
+  constexpr int W = 6 * N + 7;
+  auto gidx = [&](int a) -> int {
+    if (a < 6 * N) return 6 * node_of_knot[s + a / 6] + a % 6;
+    return H.n_pad + (a - 6 * N);  // GT_SCALE..GT_PBC+2 are border rows 0..6
+  };
+  auto active = [&](int a) -> bool { return a < 6 * N ? true : gm.a[a - 6 * N] != 0; };
+  for (int e = lane; e < W * (W + 1) / 2; e += 32) {
+    // unrank lower-triangular index
+    int a = (int)((sqrt(8.0 * e + 1.0) - 1.0) * 0.5);
+    while ((a + 1) * (a + 2) / 2 <= e) ++a;
+    while (a * (a + 1) / 2 > e) --a;
+    const int c = e - a * (a + 1) / 2;
+    if (!active(a) || !active(c)) continue;
+    // t[m] = sum_n Q[m][n] Dc[n]  (m over 13 pose/global rows)
+    double val;
+    if (c < 6 * N) {
+      double t6[6];
+      const int ic = c / 6, cc = c % 6;
+#pragma unroll
+      for (int m = 0; m < 6; ++m) {
+        if (cc < 3) t6[m] = sQ[m * 13 + 0] * fp.Crot[ic][cc] + sQ[m * 13 + 1] * fp.Crot[ic][3 + cc] + sQ[m * 13 + 2] * fp.Crot[ic][6 + cc];
+        else t6[m] = sQ[m * 13 + cc] * fp.cpos[ic];
+      }
+      if (a < 6 * N) val = chain_apply_T<N>(fp, a, t6);
+      else {
+        const int ga = 6 + (a - 6 * N);
+        if (cc < 3) val = sQ[ga * 13 + 0] * fp.Crot[ic][cc] + sQ[ga * 13 + 1] * fp.Crot[ic][3 + cc] + sQ[ga * 13 + 2] * fp.Crot[ic][6 + cc];
+        else val = sQ[ga * 13 + cc] * fp.cpos[ic];
+      }
+    } else {
+      val = sQ[(6 + a - 6 * N) * 13 + (6 + c - 6 * N)];  // both global (a >= c >= 6N)
+    }
+    add_sym(H, gidx(a), gidx(c), val);
+  }
+  for (int a = lane; a < W; a += 32) {
+    if (!active(a)) continue;
+    double v;
+    if (a < 6 * N) v = chain_apply_T<N>(fp, a, sQ + 169);
+    else v = sQ[169 + 6 + (a - 6 * N)];
+    atomicAdd(grad + gidx(a), v);
+  }
+}
+
+// ---- dense local-Jacobian rows (IMU / GP / bias / gravity) into the band: warp per residual block ----------------
+// kind: 1 accel, 2 gyro, 3 gp, 4 bias, 5 gravity.  cols = width of the row.
+template <int N>
+__global__ void __launch_bounds__(128) k_rows_accumulate(int kind, int n, int width, const double* __restrict__ J, const double* __restrict__ r,
+                                                         const int32_t* __restrict__ i_s, const int32_t* __restrict__ i_sb,
+                                                         const int32_t* __restrict__ b_s1, const int32_t* __restrict__ b_which,
+                                                         const int32_t* __restrict__ node_of_knot, const int32_t* __restrict__ node_of_bias,
+                                                         GMask gm, BandLayout H, double* __restrict__ grad) {
+  __shared__ double shJ[4][3 * 64];
+  __shared__ int shI[4][64];
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int i = blockIdx.x * 4 + wib;
+  if (i >= n) return;
+  const int nres = kind == 5 ? 1 : 3;
+  double* sJ = shJ[wib];
+  int* sI = shI[wib];
+  for (int c = lane; c < width; c += 32) {
+    int idx = -1;
+    if (kind == 1) {  // [3N rot | 3N pos | 12 acc-bias | 3 g | 1 t]
+      if (c < 3 * N) idx = 6 * node_of_knot[i_s[i] + c / 3] + c % 3;
+      else if (c < 6 * N) idx = 6 * node_of_knot[i_s[i] + (c - 3 * N) / 3] + 3 + c % 3;
+      else if (c < 6 * N + 12) idx = 6 * node_of_bias[i_sb[i] + (c - 6 * N) / 3] + (c - 6 * N) % 3;
+      else if (c < 6 * N + 15) idx = gm.a[GT_G] ? H.n_pad + GT_G + (c - 6 * N - 12) : -1;
+      else idx = gm.a[GT_T_CAM_IMU] ? H.n_pad + GT_T_CAM_IMU : -1;
+    } else if (kind == 2) {  // [3N rot | 12 gyro-bias | 1 t]
+      if (c < 3 * N) idx = 6 * node_of_knot[i_s[i] + c / 3] + c % 3;
+      else if (c < 3 * N + 12) idx = 6 * node_of_bias[i_sb[i] + (c - 3 * N) / 3] + 3 + (c - 3 * N) % 3;
+      else idx = gm.a[GT_T_CAM_IMU] ? H.n_pad + GT_T_CAM_IMU : -1;
+    } else if (kind == 3) {  // [3N rot | 3N pos | p_bp 3 | t 1 | scale 1]
+      if (c < 3 * N) idx = 6 * node_of_knot[i_s[i] + c / 3] + c % 3;
+      else if (c < 6 * N) idx = 6 * node_of_knot[i_s[i] + (c - 3 * N) / 3] + 3 + c % 3;
+      else if (c < 6 * N + 3) idx = gm.a[GT_PBP] ? H.n_pad + GT_PBP + (c - 6 * N) : -1;
+      else if (c == 6 * N + 3) idx = gm.a[GT_T_GP] ? H.n_pad + GT_T_GP : -1;
+      else idx = gm.a[GT_SCALE] ? H.n_pad + GT_SCALE : -1;
+    } else if (kind == 4) {  // [4 knots @s0 | 4 knots @s1], acc (which 0) or gyro (which 1)
+      const int off = b_which[i] ? 3 : 0;
+      if (c < 12) idx = 6 * node_of_bias[i_s[i] + c / 3] + off + c % 3;
+      else idx = 6 * node_of_bias[b_s1[i] + (c - 12) / 3] + off + c % 3;
+    } else {  // gravity: g 3
+      idx = gm.a[GT_G] ? H.n_pad + GT_G + c : -1;
+    }
+    sI[c] = idx;
+    for (int rr = 0; rr < nres; ++rr) sJ[rr * 64 + c] = J[((size_t)i * nres + rr) * width + c];
+  }
+  __syncwarp();
+  double res[3] = {0, 0, 0};
+  for (int rr = 0; rr < nres; ++rr) res[rr] = r[(size_t)i * nres + rr];
+  const int npairs = width * (width + 1) / 2;
+  for (int e = lane; e < npairs; e += 32) {
+    int a = (int)((sqrt(8.0 * e + 1.0) - 1.0) * 0.5);
+    while ((a + 1) * (a + 2) / 2 <= e) ++a;
+    while (a * (a + 1) / 2 > e) --a;
+    const int c = e - a * (a + 1) / 2;
+    const int ia = sI[a], ic = sI[c];
+    if (ia < 0 || ic < 0) continue;
+    double v = 0.0;
+    for (int rr = 0; rr < nres; ++rr) v += sJ[rr * 64 + a] * sJ[rr * 64 + c];
+    if (v != 0.0) add_sym(H, ia, ic, v);
+  }
+  for (int c = lane; c < width; c += 32) {
+    if (sI[c] < 0) continue;
+    double v = 0.0;
+    for (int rr = 0; rr < nres; ++rr) v += sJ[rr * 64 + c] * res[rr];
+    if (v != 0.0) atomicAdd(grad + sI[c], v);
+  }
+}
+
+// ---- Schur complement of the landmarks in pose space: warp per landmark -----------------------------------------
+// Sp[(f*(T+1)+df)*36 + 6*m + n] : block (rows pose f, cols pose f+df);  Sb[f*42 + 7*m + g] : pose f x reprojection globals;
+// rp[f*6+m] : pose-space right-hand-side correction;  corner/grad-global corrections go straight to Hw / rhs.
+template <int N>
+__global__ void __launch_bounds__(128) k_landmark_schur(const __grid_constant__ Globals G, const double* __restrict__ glb,
+                                                        const FramePose<N>* __restrict__ fps, const double* __restrict__ lm, int L,
+                                                        const int32_t* __restrict__ lm_obs_begin, const int32_t* __restrict__ lm_obs,
+                                                        const int32_t* __restrict__ o_frame, const double* __restrict__ Jl,
+                                                        const double2* __restrict__ r, const double* __restrict__ f_w, int M,
+                                                        const double* __restrict__ V0, const double* __restrict__ gl,
+                                                        const double* __restrict__ jscale_lm, double radius, int T, GMask gm,
+                                                        double* __restrict__ Sp, double* __restrict__ Sb, double* __restrict__ rp, BandLayout Hw,
+                                                        double* __restrict__ rhs_glob /* 7 */) {
+  const int l = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (l >= L) return;
+  const int b0 = lm_obs_begin[l], t = lm_obs_begin[l + 1] - b0;
+  if (t == 0) return;
+  // damped landmark block and its inverse
+  double V[6], Vi[6], g[3];
+#pragma unroll
+  for (int c = 0; c < 6; ++c) V[c] = V0[6 * (size_t)l + c];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) g[c] = gl[3 * (size_t)l + c];
+  {
+    const int di[3] = {0, 3, 5};
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const double sc = jscale_lm[3 * (size_t)l + c];
+      double dd = V[di[c]] * sc * sc;
+      dd = fmin(fmax(dd, 1e-6), 1e32);
+      V[di[c]] += dd / (radius * sc * sc);
+    }
+    const double c00 = V[3] * V[5] - V[4] * V[4], c01 = V[2] * V[4] - V[1] * V[5], c02 = V[1] * V[4] - V[2] * V[3];
+    const double det = V[0] * c00 + V[1] * c01 + V[2] * c02, id = 1.0 / det;
+    Vi[0] = c00 * id; Vi[1] = c01 * id; Vi[2] = c02 * id;
+    Vi[3] = (V[0] * V[5] - V[2] * V[2]) * id; Vi[4] = (V[1] * V[2] - V[0] * V[4]) * id; Vi[5] = (V[0] * V[3] - V[1] * V[1]) * id;
+  }
+  double vig[3];
+  symmul3(Vi, g, vig);
+  v3 pw{lm[3 * (size_t)l], lm[3 * (size_t)l + 1], lm[3 * (size_t)l + 2]};
+  double Yg_sum[3][7];  // sum over observations of the global part of Y (all lanes end with the full sum)
+#pragma unroll
+  for (int a = 0; a < 3; ++a)
+#pragma unroll
+    for (int c = 0; c < 7; ++c) Yg_sum[a][c] = 0.0;
+
+  for (int base = 0; base < t; base += 32) {   // chunk of "row" observations
+    const int oi = base + lane;
+    const bool have = oi < t;
+    int f = 0;
+    double Yp[3][6], Yg[3][7];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+#pragma unroll
+      for (int c = 0; c < 6; ++c) Yp[a][c] = 0.0;
+#pragma unroll
+      for (int c = 0; c < 7; ++c) Yg[a][c] = 0.0;
+    }
+    if (have) {
+      const int o = lm_obs[b0 + oi];
+      f = o_frame[o];
+      double X[3][13], A[6], b[3];
+      obs_X<N>(G, glb, fps[f], pw, X);
+      obs_Ab(Jl, r, f_w, M, o, f, A, b);
+#pragma unroll
+      for (int c = 0; c < 13; ++c) {
+        const double x[3] = {X[0][c], X[1][c], X[2][c]};
+        double y[3];
+        symmul3(A, x, y);
+        if (c < 6) { Yp[0][c] = y[0]; Yp[1][c] = y[1]; Yp[2][c] = y[2]; }
+        else { Yg[0][c - 6] = y[0]; Yg[1][c - 6] = y[1]; Yg[2][c - 6] = y[2]; }
+      }
+      // right-hand side (pose part): rp(f) -= Yp^T Vi g_l
+#pragma unroll
+      for (int c = 0; c < 6; ++c) atomicAdd(rp + 6 * (size_t)f + c, -(Yp[0][c] * vig[0] + Yp[1][c] * vig[1] + Yp[2][c] * vig[2]));
+    }
+    // accumulate the global-part sum over this chunk (warp reduction, every lane gets it)
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+      for (int c = 0; c < 7; ++c) {
+        double v = Yg[a][c];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        Yg_sum[a][c] += v;
+      }
+    // pairs (row obs in this chunk) x (col obs in chunk cb >= base)
+    for (int cb = base; cb < t; cb += 32) {
+      // column-side data: Z = Vi * Yp of observation cb+lane, and its frame
+      int f2 = 0;
+      double Zp[3][6];
+#pragma unroll
+      for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int c = 0; c < 6; ++c) Zp[a][c] = 0.0;
+      const int oj = cb + lane;
+      if (cb == base) {
+        f2 = f;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          const double y[3] = {Yp[0][c], Yp[1][c], Yp[2][c]};
+          double z[3];
+          symmul3(Vi, y, z);
+          Zp[0][c] = z[0]; Zp[1][c] = z[1]; Zp[2][c] = z[2];
+        }
+      } else if (oj < t) {
+        const int o = lm_obs[b0 + oj];
+        f2 = o_frame[o];
+        double X[3][13], A[6], b[3];
+        obs_X<N>(G, glb, fps[f2], pw, X);
+        obs_Ab(Jl, r, f_w, M, o, f2, A, b);
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          const double x[3] = {X[0][c], X[1][c], X[2][c]};
+          double y[3], z[3];
+          symmul3(A, x, y);
+          symmul3(Vi, y, z);
+          Zp[0][c] = z[0]; Zp[1][c] = z[1]; Zp[2][c] = z[2];
+        }
+      }
+      const int kstart = 0;
+      for (int k = kstart; k < 32; ++k) {
+        // lane pairs with column lane (lane + k) & 31
+        const int src = (lane + k) & 31;
+        const int oj2 = cb + src;
+        const int fj = __shfl_sync(0xffffffffu, f2, src);
+        double Z[3][6];
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+#pragma unroll
+          for (int c = 0; c < 6; ++c) Z[a][c] = __shfl_sync(0xffffffffu, Zp[a][c], src);
+        // ordered pair: require (global obs index of row) <= (global obs index of col)
+        if (!have || oj2 >= t || oj2 < oi) continue;
+        int fr = f, fc = fj;
+        const bool same_obs = (oj2 == oi);
+        // block B[m][n] = - sum_a Yp[a][m] Z[a][n]   (rows: pose of row obs, cols: pose of col obs)
+        if (fc >= fr) {
+          double* dst = Sp + ((size_t)fr * (T + 1) + (fc - fr)) * 36;
+          const bool dup_frame = (!same_obs && fc == fr);
+#pragma unroll
+          for (int m = 0; m < 6; ++m)
+#pragma unroll
+            for (int n = 0; n < 6; ++n) {
+              double v = -(Yp[0][m] * Z[0][n] + Yp[1][m] * Z[1][n] + Yp[2][m] * Z[2][n]);
+              if (dup_frame) v += -(Yp[0][n] * Z[0][m] + Yp[1][n] * Z[1][m] + Yp[2][n] * Z[2][m]);
+              atomicAdd(dst + 6 * m + n, v);
+            }
+        } else {  // observation list not frame-sorted: store the transposed block
+          double* dst = Sp + ((size_t)fc * (T + 1) + (fr - fc)) * 36;
+#pragma unroll
+          for (int m = 0; m < 6; ++m)
+#pragma unroll
+            for (int n = 0; n < 6; ++n) atomicAdd(dst + 6 * n + m, -(Yp[0][m] * Z[0][n] + Yp[1][m] * Z[1][n] + Yp[2][m] * Z[2][n]));
+        }
+      }
+    }
+    // pose x globals border needs the complete Yg_sum: done in a second sweep below
+  }
+  // second sweep: Sb(f) -= Yp^T Vi Yg_sum ; (global x global) and global rhs by lane 0
+  double ViYg[3][7];
+#pragma unroll
+  for (int c = 0; c < 7; ++c) {
+    const double y[3] = {Yg_sum[0][c], Yg_sum[1][c], Yg_sum[2][c]};
+    double z[3];
+    symmul3(Vi, y, z);
+    ViYg[0][c] = z[0]; ViYg[1][c] = z[1]; ViYg[2][c] = z[2];
+  }
+  bool any_g = false;
+#pragma unroll
+  for (int c = 0; c < 7; ++c) any_g |= gm.a[c] != 0;
+  if (any_g) {
+    for (int oi = lane; oi < t; oi += 32) {
+      const int o = lm_obs[b0 + oi];
+      const int f = o_frame[o];
+      double X[3][13], A[6], b[3];
+      obs_X<N>(G, glb, fps[f], pw, X);
+      obs_Ab(Jl, r, f_w, M, o, f, A, b);
+#pragma unroll
+      for (int m = 0; m < 6; ++m) {
+        const double x[3] = {X[0][m], X[1][m], X[2][m]};
+        double y[3];
+        symmul3(A, x, y);
+#pragma unroll
+        for (int c = 0; c < 7; ++c)
+          if (gm.a[c]) atomicAdd(Sb + (size_t)f * 42 + 7 * m + c, -(y[0] * ViYg[0][c] + y[1] * ViYg[1][c] + y[2] * ViYg[2][c]));
+      }
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int a = 0; a < 7; ++a) {
+        if (!gm.a[a]) continue;
+#pragma unroll
+        for (int c = 0; c <= a; ++c) {
+          if (!gm.a[c]) continue;
+          atomicAdd(Hw.corner + a * kBorder + c, -(Yg_sum[0][a] * ViYg[0][c] + Yg_sum[1][a] * ViYg[1][c] + Yg_sum[2][a] * ViYg[2][c]));
+        }
+        atomicAdd(rhs_glob + a, -(Yg_sum[0][a] * vig[0] + Yg_sum[1][a] * vig[1] + Yg_sum[2][a] * vig[2]));
+      }
+    }
+  }
+}
+
+// ---- pose space -> knot space: warp per (frame, df) ---------------------------------------------------------------
+template <int N>
+__global__ void __launch_bounds__(128) k_pose_to_knots(const FramePose<N>* __restrict__ fps, int F, int T, const int32_t* __restrict__ f_s,
+                                                       const int32_t* __restrict__ node_of_knot, const double* __restrict__ Sp,
+                                                       const double* __restrict__ Sb, const double* __restrict__ rp, GMask gm, BandLayout Hw,
+                                                       double* __restrict__ rhs /* n_pad + 16, gradient-like accumulator */) {
+  __shared__ double shS[4][36];
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  if (w >= F * (T + 1)) return;
+  const int f = w / (T + 1), df = w % (T + 1);
+  const int f2 = f + df;
+  if (f2 >= F) return;
+  double* sS = shS[wib];
+  double mx = 0.0;
+  for (int e = lane; e < 36; e += 32) { double v = Sp[(size_t)w * 36 + e]; sS[e] = v; mx = fmax(mx, fabs(v)); }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  __syncwarp();
+  const FramePose<N>& fa = fps[f];
+  const FramePose<N>& fb = fps[f2];
+  const int sa = f_s[f], sb = f_s[f2];
+  if (mx != 0.0) {
+    for (int e = lane; e < 36 * N * N; e += 32) {
+      const int a = e / (6 * N), c = e % (6 * N);
+      if (df == 0 && c > a) continue;
+      // t[m] = sum_n S[m][n] Dc[n]
+      const int ic = c / 6, cc = c % 6;
+      double t6[6];
+#pragma unroll
+      for (int m = 0; m < 6; ++m) {
+        if (cc < 3) t6[m] = sS[6 * m + 0] * fb.Crot[ic][cc] + sS[6 * m + 1] * fb.Crot[ic][3 + cc] + sS[6 * m + 2] * fb.Crot[ic][6 + cc];
+        else t6[m] = sS[6 * m + cc] * fb.cpos[ic];
+      }
+      double v = chain_apply_T<N>(fa, a, t6);
+      const int ra = 6 * node_of_knot[sa + a / 6] + a % 6, cb = 6 * node_of_knot[sb + c / 6] + c % 6;
+      if (df != 0 && ra == cb) v *= 2.0;
+      add_sym(Hw, ra, cb, v);
+    }
+  }
+  if (df == 0) {
+    // border (pose x reprojection globals) and right-hand side
+    for (int e = lane; e < 6 * N * 7; e += 32) {
+      const int a = e / 7, gcol = e % 7;
+      if (!gm.a[gcol]) continue;
+      double v6[6];
+#pragma unroll
+      for (int m = 0; m < 6; ++m) v6[m] = Sb[(size_t)f * 42 + 7 * m + gcol];
+      const double v = chain_apply_T<N>(fa, a, v6);
+      if (v != 0.0) atomicAdd(Hw.border + (size_t)gcol * Hw.n_pad + 6 * node_of_knot[sa + a / 6] + a % 6, v);
+    }
+    for (int a = lane; a < 6 * N; a += 32) {
+      const double v = chain_apply_T<N>(fa, a, rp + 6 * (size_t)f);
+      if (v != 0.0) atomicAdd(rhs + 6 * node_of_knot[sa + a / 6] + a % 6, v);
+    }
+  }
+}
+
+// ---- Jacobi scaling (iteration 0 of each Solve): 1 / (1 + sqrt(diag J^T J)) ---------------------------------------
+__global__ void k_jscale(BandLayout H, int n_band, const double* __restrict__ V0, int L, GMask gm, double* __restrict__ jscale,
+                         double* __restrict__ jscale_lm) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < H.n_pad) {
+    double d = i < n_band ? H.band[band_addr(H, i, i)] : 0.0;
+    jscale[i] = 1.0 / (1.0 + sqrt(fmax(d, 0.0)));
+  } else if (i < H.n_pad + GT_SIZE) {
+    const int t = i - H.n_pad;
+    double d = gm.a[t] ? H.corner[t * kBorder + t] : 0.0;
+    jscale[i] = 1.0 / (1.0 + sqrt(fmax(d, 0.0)));
+  } else if (i < H.n_pad + kBorder) {
+    jscale[i] = 1.0;
+  }
+  const int j = i;
+  if (j < 3 * L) {
+    const int di[3] = {0, 3, 5};
+    jscale_lm[j] = 1.0 / (1.0 + sqrt(fmax(V0[6 * (size_t)(j / 3) + di[j % 3]], 0.0)));
+  }
+}
+
+// Hw = H0 + LM diagonal (in unscaled space: clamp(H_jj s_j^2, 1e-6, 1e32) / (radius s_j^2)); padding rows get identity;
+// inactive globals get identity; rhs row of the border = -grad (band part) ; corner rhs column = -grad (global part)
+__global__ void k_add_damping(BandLayout H0, BandLayout Hw, int n_band, const double* __restrict__ jscale, const double* __restrict__ grad,
+                              double radius, GMask gm, double* __restrict__ dvec /* n_pad+16: D^2 */) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < Hw.n_pad) {
+    const size_t ad = band_addr(Hw, i, i);
+    if (i < n_band) {
+      const double sc = jscale[i], d0 = H0.band[ad];
+      const double dd = fmin(fmax(d0 * sc * sc, 1e-6), 1e32) / (radius * sc * sc);
+      Hw.band[ad] = d0 + dd;   // k_pose_to_knots adds on top atomically afterwards? no: damping is applied LAST (see host order)
+      dvec[i] = dd;
+    } else {
+      Hw.band[ad] = 1.0;
+      dvec[i] = 0.0;
+    }
+  } else if (i < Hw.n_pad + GT_SIZE) {
+    const int t = i - Hw.n_pad;
+    if (gm.a[t]) {
+      const double sc = jscale[i], d0 = H0.corner[t * kBorder + t];
+      const double dd = fmin(fmax(d0 * sc * sc, 1e-6), 1e32) / (radius * sc * sc);
+      atomicAdd(Hw.corner + t * kBorder + t, dd);
+      dvec[i] = dd;
+    } else {
+      Hw.corner[t * kBorder + t] = 1.0;
+      dvec[i] = 0.0;
+    }
+  }
+}
+
+// rhs row of the border (row 15) and rhs column of the corner: -(grad + schur correction accumulated in rhs_acc)
+__global__ void k_set_rhs(BandLayout Hw, const double* __restrict__ grad, const double* __restrict__ rhs_acc, GMask gm) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < Hw.n_pad) {
+    Hw.border[(size_t)kRhsRow * Hw.n_pad + i] = -(grad[i] + rhs_acc[i]);
+  } else if (i < Hw.n_pad + GT_SIZE) {
+    const int t = i - Hw.n_pad;
+    Hw.corner[kRhsRow * kBorder + t] = gm.a[t] ? -(grad[i] + rhs_acc[i]) : 0.0;
+  }
+}
+
+// ---- step application ------------------------------------------------------------------------------------------------
+// pose-space step of each frame: dpose_f = D_f * delta(window f)
+template <int N>
+__global__ void k_frame_dpose(const FramePose<N>* __restrict__ fps, int F, const int32_t* __restrict__ f_s, const int32_t* __restrict__ node_of_knot,
+                              const double* __restrict__ delta, double* __restrict__ dpose) {
+  int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= F) return;
+  const FramePose<N>& fp = fps[f];
+  double out[6] = {0, 0, 0, 0, 0, 0};
+  const int s = f_s[f];
+  for (int i = 0; i < N; ++i) {
+    const double* d = delta + 6 * (size_t)node_of_knot[s + i];
+    for (int m = 0; m < 3; ++m) {
+      out[m] += fp.Crot[i][3 * m] * d[0] + fp.Crot[i][3 * m + 1] * d[1] + fp.Crot[i][3 * m + 2] * d[2];
+      out[3 + m] += fp.cpos[i] * d[3 + m];
+    }
+  }
+  for (int m = 0; m < 6; ++m) dpose[6 * (size_t)f + m] = out[m];
+}
+
+// landmark back-substitution: delta_l = -Vi (g_l + sum_o Y_o [dpose_f ; dglob])   (thread per landmark)
+template <int N>
+__global__ void k_landmark_backsub(const __grid_constant__ Globals G, const double* __restrict__ glb, const FramePose<N>* __restrict__ fps,
+                                   const double* __restrict__ lm, int L, const int32_t* __restrict__ lm_obs_begin,
+                                   const int32_t* __restrict__ lm_obs, const int32_t* __restrict__ o_frame, const double* __restrict__ Jl,
+                                   const double2* __restrict__ r, const double* __restrict__ f_w, int M, const double* __restrict__ V0,
+                                   const double* __restrict__ gl, const double* __restrict__ jscale_lm, double radius, GMask gm,
+                                   const double* __restrict__ dpose, const double* __restrict__ dglob /* 15 */, double* __restrict__ delta_lm,
+                                   double* __restrict__ dvec_lm) {
+  int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= L) return;
+  const int b0 = lm_obs_begin[l], e0 = lm_obs_begin[l + 1];
+  if (b0 == e0) { for (int c = 0; c < 3; ++c) { delta_lm[3 * (size_t)l + c] = 0.0; dvec_lm[3 * (size_t)l + c] = 0.0; } return; }
+  double V[6], Vi[6], acc[3];
+  for (int c = 0; c < 6; ++c) V[c] = V0[6 * (size_t)l + c];
+  for (int c = 0; c < 3; ++c) acc[c] = gl[3 * (size_t)l + c];
+  const int di[3] = {0, 3, 5};
+  for (int c = 0; c < 3; ++c) {
+    const double sc = jscale_lm[3 * (size_t)l + c];
+    double dd = fmin(fmax(V[di[c]] * sc * sc, 1e-6), 1e32) / (radius * sc * sc);
+    V[di[c]] += dd;
+    dvec_lm[3 * (size_t)l + c] = dd;
+  }
+  {
+    const double c00 = V[3] * V[5] - V[4] * V[4], c01 = V[2] * V[4] - V[1] * V[5], c02 = V[1] * V[4] - V[2] * V[3];
+    const double det = V[0] * c00 + V[1] * c01 + V[2] * c02, id = 1.0 / det;
+    Vi[0] = c00 * id; Vi[1] = c01 * id; Vi[2] = c02 * id;
+    Vi[3] = (V[0] * V[5] - V[2] * V[2]) * id; Vi[4] = (V[1] * V[2] - V[0] * V[4]) * id; Vi[5] = (V[0] * V[3] - V[1] * V[1]) * id;
+  }
+  v3 pw{lm[3 * (size_t)l], lm[3 * (size_t)l + 1], lm[3 * (size_t)l + 2]};
+  for (int i = b0; i < e0; ++i) {
+    const int o = lm_obs[i], f = o_frame[o];
+    double X[3][13], A[6], b[3];
+    obs_X<N>(G, glb, fps[f], pw, X);
+    obs_Ab(Jl, r, f_w, M, o, f, A, b);
+    double xd[3] = {0, 0, 0};  // X * [dpose ; dglob(active)]
+    for (int c = 0; c < 6; ++c) { const double dv = dpose[6 * (size_t)f + c]; xd[0] += X[0][c] * dv; xd[1] += X[1][c] * dv; xd[2] += X[2][c] * dv; }
+    for (int c = 0; c < 7; ++c) if (gm.a[c]) { const double dv = dglob[c]; xd[0] += X[0][6 + c] * dv; xd[1] += X[1][6 + c] * dv; xd[2] += X[2][6 + c] * dv; }
+    double y[3];
+    symmul3(A, xd, y);
+    acc[0] += y[0]; acc[1] += y[1]; acc[2] += y[2];
+  }
+  double d[3];
+  symmul3(Vi, acc, d);
+  for (int c = 0; c < 3; ++c) delta_lm[3 * (size_t)l + c] = -d[c];
+}
+
+// candidate state = state (+) delta   (knots / biases: thread per node; landmarks; globals by one thread)
+__global__ void k_apply_nodes(int K, int Kb, const int32_t* __restrict__ node_of_knot, const int32_t* __restrict__ node_of_bias,
+                              const double* __restrict__ delta, StatePtrs S, StatePtrs C) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < K) {
+    const double* d = delta + 6 * (size_t)node_of_knot[i];
+    quat q{S.knot_q[4 * (size_t)i], S.knot_q[4 * (size_t)i + 1], S.knot_q[4 * (size_t)i + 2], S.knot_q[4 * (size_t)i + 3]};
+    quat qn = quat_mul(q, so3_exp(v3{d[0], d[1], d[2]}));  // lie_local_parametrization.h:34-41
+    C.knot_q[4 * (size_t)i] = qn.x; C.knot_q[4 * (size_t)i + 1] = qn.y; C.knot_q[4 * (size_t)i + 2] = qn.z; C.knot_q[4 * (size_t)i + 3] = qn.w;
+    for (int c = 0; c < 3; ++c) C.knot_p[3 * (size_t)i + c] = S.knot_p[3 * (size_t)i + c] + d[3 + c];
+  } else if (i < K + Kb) {
+    const int j = i - K;
+    const double* d = delta + 6 * (size_t)node_of_bias[j];
+    for (int c = 0; c < 3; ++c) {
+      C.bias_a[3 * (size_t)j + c] = S.bias_a[3 * (size_t)j + c] + d[c];
+      C.bias_g[3 * (size_t)j + c] = S.bias_g[3 * (size_t)j + c] + d[3 + c];
+    }
+  }
+}
+__global__ void k_apply_landmarks_globals(int L, const double* __restrict__ delta_lm, const double* __restrict__ dglob, GMask gm, StatePtrs S, StatePtrs C) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 3 * L) C.lm[i] = S.lm[i] + delta_lm[i];
+  if (i == 0) {
+    double g[GLB_STATE_SIZE];
+    for (int c = 0; c < GLB_STATE_SIZE; ++c) g[c] = S.glb[c];
+    if (gm.a[GT_SCALE]) g[GLB_SCALE_CORR] += dglob[GT_SCALE];
+    if (gm.a[GT_RBC]) {
+      quat q{g[GLB_RBC_CORR], g[GLB_RBC_CORR + 1], g[GLB_RBC_CORR + 2], g[GLB_RBC_CORR + 3]};
+      quat qn = quat_mul(q, so3_exp(v3{dglob[GT_RBC], dglob[GT_RBC + 1], dglob[GT_RBC + 2]}));
+      g[GLB_RBC_CORR] = qn.x; g[GLB_RBC_CORR + 1] = qn.y; g[GLB_RBC_CORR + 2] = qn.z; g[GLB_RBC_CORR + 3] = qn.w;
+    }
+    for (int c = 0; c < 3; ++c) {
+      if (gm.a[GT_PBC + c]) g[GLB_PBC_CORR + c] += dglob[GT_PBC + c];
+      if (gm.a[GT_PBP + c]) g[GLB_PBP + c] += dglob[GT_PBP + c];
+      if (gm.a[GT_G + c]) g[GLB_G + c] += dglob[GT_G + c];
+    }
+    if (gm.a[GT_T_CAM_IMU]) g[GLB_T_CAM_IMU_CORR] += dglob[GT_T_CAM_IMU];
+    if (gm.a[GT_T_GP]) g[GLB_T_GP_CORR] += dglob[GT_T_GP];
+    for (int c = 0; c < GLB_STATE_SIZE; ++c) C.glb[c] = g[c];
+  }
+}
+
+// ---- scalars of an LM step (deterministic two-stage reductions) ---------------------------------------------------------
+// item space: [0, nK) knots, [nK, nK+nKb) bias nodes, then landmarks (3 scalars each handled per landmark), then 1 item for globals
+// out partials: per block 4 doubles: model (delta^T D^2 delta - delta^T g), step^2, xnorm^2, gmax
+__device__ __forceinline__ double gmax_quat(quat q, v3 g) {  // max | q - q*exp(-g) |
+  quat qn = quat_mul(q, so3_exp(v3{-g.x, -g.y, -g.z}));
+  return fmax(fmax(fabs(qn.x - q.x), fabs(qn.y - q.y)), fmax(fabs(qn.z - q.z), fabs(qn.w - q.w)));
+}
+__global__ void __launch_bounds__(256) k_step_scalars(int K, int Kb, int L, const int32_t* __restrict__ node_of_knot,
+                                                      const int32_t* __restrict__ node_of_bias, const uint8_t* __restrict__ touch_knot,
+                                                      const uint8_t* __restrict__ touch_bias, const uint8_t* __restrict__ touch_lm, GMask gm, int n_pad,
+                                                      const double* __restrict__ delta, const double* __restrict__ delta_lm,
+                                                      const double* __restrict__ dvec, const double* __restrict__ dvec_lm,
+                                                      const double* __restrict__ grad, const double* __restrict__ gl, StatePtrs S, StatePtrs C,
+                                                      bool have_step, double* __restrict__ partial) {
+  __shared__ double sh[4][256];
+  double model = 0, step2 = 0, xn2 = 0, gmx = 0;
+  const int total = K + Kb + L + 1;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    if (i < K) {
+      const int nd = 6 * node_of_knot[i];
+      const uint8_t tm = touch_knot[i];
+      if (have_step) for (int c = 0; c < 6; ++c) model += delta[nd + c] * (dvec[nd + c] * delta[nd + c] - grad[nd + c]);
+      if (tm & 1) {
+        quat q{S.knot_q[4 * (size_t)i], S.knot_q[4 * (size_t)i + 1], S.knot_q[4 * (size_t)i + 2], S.knot_q[4 * (size_t)i + 3]};
+        xn2 += q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w;
+        gmx = fmax(gmx, gmax_quat(q, v3{grad[nd], grad[nd + 1], grad[nd + 2]}));
+        if (have_step) for (int c = 0; c < 4; ++c) { double d = C.knot_q[4 * (size_t)i + c] - S.knot_q[4 * (size_t)i + c]; step2 += d * d; }
+      }
+      if (tm & 2) {
+        for (int c = 0; c < 3; ++c) {
+          const double x = S.knot_p[3 * (size_t)i + c];
+          xn2 += x * x; gmx = fmax(gmx, fabs(grad[nd + 3 + c]));
+          if (have_step) { double d = C.knot_p[3 * (size_t)i + c] - x; step2 += d * d; }
+        }
+      }
+    } else if (i < K + Kb) {
+      const int j = i - K, nd = 6 * node_of_bias[j];
+      const uint8_t tm = touch_bias[j];
+      if (have_step) for (int c = 0; c < 6; ++c) model += delta[nd + c] * (dvec[nd + c] * delta[nd + c] - grad[nd + c]);
+      for (int c = 0; c < 3; ++c) {
+        if (tm & 1) { const double x = S.bias_a[3 * (size_t)j + c]; xn2 += x * x; gmx = fmax(gmx, fabs(grad[nd + c])); if (have_step) { double d = C.bias_a[3 * (size_t)j + c] - x; step2 += d * d; } }
+        if (tm & 2) { const double x = S.bias_g[3 * (size_t)j + c]; xn2 += x * x; gmx = fmax(gmx, fabs(grad[nd + 3 + c])); if (have_step) { double d = C.bias_g[3 * (size_t)j + c] - x; step2 += d * d; } }
+      }
+    } else if (i < K + Kb + L) {
+      const int l = i - K - Kb;
+      if (!touch_lm[l]) continue;
+      for (int c = 0; c < 3; ++c) {
+        const double x = S.lm[3 * (size_t)l + c], g = gl[3 * (size_t)l + c];
+        xn2 += x * x; gmx = fmax(gmx, fabs(g));
+        if (have_step) {
+          const double dl = delta_lm[3 * (size_t)l + c];
+          model += dl * (dvec_lm[3 * (size_t)l + c] * dl - g);
+          double d = C.lm[3 * (size_t)l + c] - x; step2 += d * d;
+        }
+      }
+    } else {
+      // globals
+      const double* dg = delta + n_pad;
+      const double* gg = grad + n_pad;
+      const double* dv = dvec + n_pad;
+      auto eu = [&](int gt, int gs) {
+        if (!gm.a[gt]) return;
+        const double x = S.glb[gs];
+        xn2 += x * x; gmx = fmax(gmx, fabs(gg[gt]));
+        if (have_step) { model += dg[gt] * (dv[gt] * dg[gt] - gg[gt]); double d = C.glb[gs] - x; step2 += d * d; }
+      };
+      eu(GT_SCALE, GLB_SCALE_CORR);
+      if (gm.a[GT_RBC]) {
+        quat q{S.glb[GLB_RBC_CORR], S.glb[GLB_RBC_CORR + 1], S.glb[GLB_RBC_CORR + 2], S.glb[GLB_RBC_CORR + 3]};
+        xn2 += q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w;
+        gmx = fmax(gmx, gmax_quat(q, v3{gg[GT_RBC], gg[GT_RBC + 1], gg[GT_RBC + 2]}));
+        if (have_step) {
+          for (int c = 0; c < 3; ++c) model += dg[GT_RBC + c] * (dv[GT_RBC + c] * dg[GT_RBC + c] - gg[GT_RBC + c]);
+          for (int c = 0; c < 4; ++c) { double d = C.glb[GLB_RBC_CORR + c] - S.glb[GLB_RBC_CORR + c]; step2 += d * d; }
+        }
+      }
+      for (int c = 0; c < 3; ++c) { eu(GT_PBC + c, GLB_PBC_CORR + c); eu(GT_PBP + c, GLB_PBP + c); eu(GT_G + c, GLB_G + c); }
+      eu(GT_T_CAM_IMU, GLB_T_CAM_IMU_CORR);
+      eu(GT_T_GP, GLB_T_GP_CORR);
+    }
+  }
+  sh[0][threadIdx.x] = model; sh[1][threadIdx.x] = step2; sh[2][threadIdx.x] = xn2; sh[3][threadIdx.x] = gmx;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) {
+      sh[0][threadIdx.x] += sh[0][threadIdx.x + o]; sh[1][threadIdx.x] += sh[1][threadIdx.x + o];
+      sh[2][threadIdx.x] += sh[2][threadIdx.x + o]; sh[3][threadIdx.x] = fmax(sh[3][threadIdx.x], sh[3][threadIdx.x + o]);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) for (int k = 0; k < 4; ++k) partial[4 * blockIdx.x + k] = sh[k][0];
+}
+__global__ void k_step_scalars_final(int nblocks, const double* __restrict__ partial, double* __restrict__ out) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  double model = 0, step2 = 0, xn2 = 0, gmx = 0;
+  for (int b = 0; b < nblocks; ++b) { model += partial[4 * b]; step2 += partial[4 * b + 1]; xn2 += partial[4 * b + 2]; gmx = fmax(gmx, partial[4 * b + 3]); }
+  out[SC_MODEL] = 0.5 * model; out[SC_STEP2] = step2; out[SC_XNORM2] = xn2; out[SC_GMAX] = gmx;
+}
+
+// ================================================== host side =====================================================
+static GMask make_gmask(const SolverData* sd) { GMask g; for (int i = 0; i < GT_SIZE; ++i) g.a[i] = sd->gactive[i]; return g; }
+
+int assemble_structure(ctba_problem* p) {
+  if (!p->solver) p->solver = new SolverData();
+  SolverData* sd = p->solver;
+  const int N = p->N;
+  const int K = (int)p->numKnots(), F = (int)p->numFrames(), M = (int)p->numObs(), L = (int)(p->lm.size() / 3);
+  const bool has_imu = !p->i_s.empty() || !p->b_s0.empty();
+  const int Kb = has_imu ? (int)p->numBiasKnots() : 0;
+  sd->K = K; sd->Kb = Kb; sd->L = L; sd->F = F; sd->has_bias = Kb > 0;
+  // ---- node ordering: knots and bias knots merged by time (knot k at k*dt, bias knot j at j*dt_bias; ties: knot first)
+  sd->node_of_knot.assign(K, 0); sd->node_of_bias.assign(std::max(Kb, 1), 0);
+  {
+    int ik = 0, ib = 0, node = 0;
+    while (ik < K || ib < Kb) {
+      const bool take_knot = ib >= Kb || (ik < K && (int64_t)ik * p->dt_ns <= (int64_t)ib * p->dt_ns_bias);
+      if (take_knot) sd->node_of_knot[ik++] = node++; else sd->node_of_bias[ib++] = node++;
+    }
+    sd->nodes = node;
+  }
+  // ---- half bandwidth in nodes over every coupling group
+  int hbn = N - 1;
+  auto span = [&](int lo, int hi) { hbn = std::max(hbn, hi - lo); };
+  std::vector<uint8_t> tk(std::max(K, 1), 0), tb(std::max(Kb, 1), 0), tl(std::max(L, 1), 0);
+  for (size_t i = 0; i < p->i_s.size(); ++i) {
+    const int s = p->i_s[i], sb = p->i_sb[i];
+    const int lo = std::min(sd->node_of_knot[s], sd->node_of_bias[sb]), hi = std::max(sd->node_of_knot[s + N - 1], sd->node_of_bias[sb + 3]);
+    span(lo, hi);
+    for (int j = 0; j < N; ++j) tk[s + j] |= 3;
+    for (int j = 0; j < 4; ++j) tb[sb + j] |= 3;
+    // the reference registers N_ bias blocks per IMU residual (bspline_so3r3.h:585-588): blocks 4..N-1 are in the problem too
+    for (int j = 4; j < N; ++j) tb[sb + j] |= 3;
+  }
+  for (size_t i = 0; i < p->g_s.size(); ++i) { const int s = p->g_s[i]; span(sd->node_of_knot[s], sd->node_of_knot[s + N - 1]); for (int j = 0; j < N; ++j) tk[s + j] |= 3; }
+  for (size_t i = 0; i < p->b_s0.size(); ++i) {
+    const int a = p->b_s0[i], b = p->b_s1[i];
+    span(sd->node_of_bias[std::min(a, b)], sd->node_of_bias[std::max(a, b) + 3]);
+    for (int j = 0; j < 4; ++j) { tb[a + j] |= (p->b_which[i] ? 2 : 1); tb[b + j] |= (p->b_which[i] ? 2 : 1); }
+  }
+  // landmark -> observation CSR (observations of a landmark in frame order, as they are stored)
+  std::vector<int32_t> lob(L + 1, 0), lobs(M);
+  for (int o = 0; o < M; ++o) lob[p->o_lm[o] + 1]++;
+  for (int l = 0; l < L; ++l) lob[l + 1] += lob[l];
+  {
+    std::vector<int32_t> cur(lob.begin(), lob.end() - 1);
+    for (int o = 0; o < M; ++o) lobs[cur[p->o_lm[o]]++] = o;
+  }
+  int T = 0;
+  for (int l = 0; l < L; ++l) {
+    if (lob[l + 1] == lob[l]) continue;
+    tl[l] = 1;
+    int fmin = 1 << 30, fmax_ = -1, smin = 1 << 30, smax = -1;
+    for (int i = lob[l]; i < lob[l + 1]; ++i) {
+      const int f = p->o_frame[lobs[i]];
+      fmin = std::min(fmin, f); fmax_ = std::max(fmax_, f);
+      smin = std::min(smin, (int)p->f_s[f]); smax = std::max(smax, (int)p->f_s[f]);
+    }
+    T = std::max(T, fmax_ - fmin);
+    span(sd->node_of_knot[smin], sd->node_of_knot[smax + N - 1]);
+  }
+  for (int f = 0; f < F; ++f) { const int s = p->f_s[f]; span(sd->node_of_knot[s], sd->node_of_knot[s + N - 1]); for (int j = 0; j < N; ++j) tk[s + j] |= 3; }
+  // every SO3 knot carries a local parameterisation in the reference and is therefore part of the program (:378-399)
+  for (int k = 0; k < K; ++k) tk[k] |= 1;
+  sd->T = T; sd->hbn = hbn;
+  // ---- which globals are free (constness set inside add*Measurement)
+  const bool anyF = F > 0, anyI = !p->i_s.empty(), anyG = !p->g_s.empty();
+  for (int i = 0; i < GT_SIZE; ++i) sd->gactive[i] = 0;
+  sd->gactive[GT_SCALE] = p->optimize_scale && (anyF || anyG);
+  for (int c = 0; c < 3; ++c) {
+    sd->gactive[GT_RBC + c] = p->optimize_camimu_extrinsics && anyF;
+    sd->gactive[GT_PBC + c] = p->optimize_camimu_extrinsics && anyF;
+    sd->gactive[GT_PBP + c] = p->optimize_p_bp && anyG;
+    sd->gactive[GT_G + c] = (anyI && p->optimize_gravity) || (!anyI && p->gravity_norm);
+  }
+  sd->gactive[GT_T_CAM_IMU] = p->optimize_camimu_extrinsics && anyI;
+  sd->gactive[GT_T_GP] = p->optimize_t_offset_s_gs && anyG;
+
+  const int n_band = 6 * sd->nodes;
+  const int n_pad = ((n_band + kNB - 1) / kNB) * kNB;
+  const int bw = 6 * hbn + 5;
+  const int nbw = std::min((bw + 2 * kNB - 2) / kNB, std::max(n_pad / kNB - 1, 0));
+  BandLayout B{n_band, n_pad, n_pad / kNB, nbw, nullptr, nullptr, nullptr};
+  const size_t be = B.band_elems();
+  CTBA_CUDA(p, sd->band0.resize(be)); CTBA_CUDA(p, sd->bandw.resize(be));
+  CTBA_CUDA(p, sd->border0.resize((size_t)kBorder * n_pad)); CTBA_CUDA(p, sd->borderw.resize((size_t)kBorder * n_pad));
+  CTBA_CUDA(p, sd->corner0.resize(kBorder * kBorder)); CTBA_CUDA(p, sd->cornerw.resize(kBorder * kBorder));
+  sd->H0 = B; sd->H0.band = sd->band0.p; sd->H0.border = sd->border0.p; sd->H0.corner = sd->corner0.p;
+  sd->Hw = B; sd->Hw.band = sd->bandw.p; sd->Hw.border = sd->borderw.p; sd->Hw.corner = sd->cornerw.p;
+  CTBA_CUDA(p, sd->grad.resize(n_pad + kBorder)); CTBA_CUDA(p, sd->delta.resize(n_pad + kBorder));
+  CTBA_CUDA(p, sd->jscale.resize(2 * (size_t)(n_pad + kBorder)));  // second half: D^2 vector
+  CTBA_CUDA(p, sd->V0.resize(6 * (size_t)std::max(L, 1))); CTBA_CUDA(p, sd->gl.resize(3 * (size_t)std::max(L, 1)));
+  CTBA_CUDA(p, sd->jscale_lm.resize(6 * (size_t)std::max(L, 1)));  // second half: D^2 of landmarks
+  CTBA_CUDA(p, sd->delta_lm.resize(3 * (size_t)std::max(L, 1)));
+  CTBA_CUDA(p, sd->Sp.resize((size_t)std::max(F, 1) * (T + 1) * 36)); CTBA_CUDA(p, sd->Sb.resize((size_t)std::max(F, 1) * 42));
+  CTBA_CUDA(p, sd->rp.resize((size_t)std::max(F, 1) * 6 + n_pad + kBorder));  // + rhs accumulator (n_pad+16)
+  CTBA_CUDA(p, sd->dpose.resize((size_t)std::max(F, 1) * 6));
+  CTBA_CUDA(p, sd->scal.resize(SC_COUNT + 4 * 256));
+  CTBA_CUDA(p, sd->flag.resize(4));
+  cudaStream_t st = p->stream;
+  CTBA_CUDA(p, sd->d_node_of_knot.upload(sd->node_of_knot, st)); CTBA_CUDA(p, sd->d_node_of_bias.upload(sd->node_of_bias, st));
+  CTBA_CUDA(p, sd->d_lm_obs_begin.upload(lob, st)); CTBA_CUDA(p, sd->d_lm_obs.upload(lobs, st));
+  CTBA_CUDA(p, sd->d_touch_knot.upload(tk, st)); CTBA_CUDA(p, sd->d_touch_bias.upload(tb, st)); CTBA_CUDA(p, sd->d_touch_lm.upload(tl, st));
+  // candidate state buffers
+  CTBA_CUDA(p, sd->cand.knot_q.resize(p->dstate.knot_q.n)); CTBA_CUDA(p, sd->cand.knot_p.resize(p->dstate.knot_p.n));
+  CTBA_CUDA(p, sd->cand.bias_a.resize(p->dstate.bias_a.n)); CTBA_CUDA(p, sd->cand.bias_g.resize(p->dstate.bias_g.n));
+  CTBA_CUDA(p, sd->cand.lm.resize(p->dstate.lm.n)); CTBA_CUDA(p, sd->cand.glb.resize(p->dstate.glb.n));
+  CTBA_CUDA(p, cudaStreamSynchronize(st));
+  sd->built = true;
+  return CTBA_OK;
+}
+
+template <int N>
+static int assemble_direct_T(ctba_problem* p) {
+  SolverData* sd = p->solver;
+  cudaStream_t st = p->stream;
+  const Globals G = make_globals(p);
+  const GMask gm = make_gmask(sd);
+  const int F = sd->F, M = (int)p->numObs(), L = sd->L;
+  BandLayout& H = sd->H0;
+  CTBA_CUDA(p, cudaMemsetAsync(H.band, 0, H.band_elems() * sizeof(double), st));
+  CTBA_CUDA(p, cudaMemsetAsync(H.border, 0, (size_t)kBorder * H.n_pad * sizeof(double), st));
+  CTBA_CUDA(p, cudaMemsetAsync(H.corner, 0, kBorder * kBorder * sizeof(double), st));
+  CTBA_CUDA(p, cudaMemsetAsync(sd->grad.p, 0, (H.n_pad + kBorder) * sizeof(double), st));
+  const StatePtrs S = p->dstate.ptrs();
+  const FramePose<N>* fps = (const FramePose<N>*)p->ev.frame_pose.p;
+  if (F > 0) {
+    if (L > 0) {
+      k_landmark_blocks<<<cdiv(L, 128), 128, 0, st>>>(L, sd->d_lm_obs_begin.p, sd->d_lm_obs.p, p->d_o_frame.p, p->ev.Jl.p,
+                                                      (const double2*)p->ev.r_reproj.p, p->ev.f_w.p, M, sd->V0.p, sd->gl.p);
+      p->launches++;
+    }
+    k_frame_direct<N><<<cdiv(F, 4), 128, 0, st>>>(G, S.glb, fps, S.lm, F, p->d_f_s.p, p->d_f_obs_begin.p, p->d_o_lm.p, p->ev.Jl.p,
+                                                  (const double2*)p->ev.r_reproj.p, p->ev.f_w.p, M, sd->d_node_of_knot.p, gm, H, sd->grad.p);
+    p->launches++;
+  }
+  const int nI = (int)p->i_s.size(), nG = (int)p->g_s.size(), nB = (int)p->b_s0.size();
+  if (nI > 0) {
+    k_rows_accumulate<N><<<cdiv(nI, 4), 128, 0, st>>>(1, nI, 6 * N + 16, p->ev.J_acc.p, p->ev.r_acc.p, p->d_i_s.p, p->d_i_sb.p, nullptr, nullptr,
+                                                      sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
+    k_rows_accumulate<N><<<cdiv(nI, 4), 128, 0, st>>>(2, nI, 3 * N + 13, p->ev.J_gyr.p, p->ev.r_gyr.p, p->d_i_s.p, p->d_i_sb.p, nullptr, nullptr,
+                                                      sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
+    p->launches += 2;
+  }
+  if (nG > 0) {
+    k_rows_accumulate<N><<<cdiv(nG, 4), 128, 0, st>>>(3, nG, 6 * N + 5, p->ev.J_gp.p, p->ev.r_gp.p, p->d_g_s.p, nullptr, nullptr, nullptr,
+                                                      sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
+    p->launches++;
+  }
+  if (nB > 0) {
+    k_rows_accumulate<N><<<cdiv(nB, 4), 128, 0, st>>>(4, nB, 24, p->ev.J_bias.p, p->ev.r_bias.p, p->d_b_s0.p, nullptr, p->d_b_s1.p, p->d_b_which.p,
+                                                      sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
+    p->launches++;
+  }
+  if (p->gravity_norm) {
+    k_rows_accumulate<N><<<1, 128, 0, st>>>(5, 1, 3, p->ev.J_grav.p, p->ev.r_grav.p, nullptr, nullptr, nullptr, nullptr, sd->d_node_of_knot.p,
+                                            sd->d_node_of_bias.p, gm, H, sd->grad.p);
+    p->launches++;
+  }
+  CTBA_CUDA(p, cudaGetLastError());
+  return CTBA_OK;
+}
+int assemble_direct(ctba_problem* p) { return p->N == 4 ? assemble_direct_T<4>(p) : assemble_direct_T<6>(p); }
+
+int compute_jscale(ctba_problem* p) {
+  SolverData* sd = p->solver;
+  const int n = std::max(sd->H0.n_pad + kBorder, 3 * sd->L);
+  k_jscale<<<cdiv(n, 256), 256, 0, p->stream>>>(sd->H0, sd->H0.n_band, sd->V0.p, sd->L, make_gmask(sd), sd->jscale.p, sd->jscale_lm.p);
+  p->launches++;
+  CTBA_CUDA(p, cudaGetLastError());
+  return CTBA_OK;
+}
+
+template <int N>
+static int assemble_schur_T(ctba_problem* p, double radius) {
+  SolverData* sd = p->solver;
+  cudaStream_t st = p->stream;
+  const Globals G = make_globals(p);
+  const GMask gm = make_gmask(sd);
+  const int F = sd->F, M = (int)p->numObs(), L = sd->L, T = sd->T;
+  BandLayout &H0 = sd->H0, &Hw = sd->Hw;
+  const int n_pad = Hw.n_pad;
+  CTBA_CUDA(p, cudaMemcpyAsync(Hw.band, H0.band, H0.band_elems() * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  CTBA_CUDA(p, cudaMemcpyAsync(Hw.border, H0.border, (size_t)kBorder * n_pad * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  CTBA_CUDA(p, cudaMemcpyAsync(Hw.corner, H0.corner, kBorder * kBorder * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  double* dvec = sd->jscale.p + (n_pad + kBorder);
+  double* rhs_acc = sd->rp.p + (size_t)std::max(F, 1) * 6;  // n_pad + 16 accumulator of Schur right-hand-side corrections
+  CTBA_CUDA(p, cudaMemsetAsync(rhs_acc, 0, (n_pad + kBorder) * sizeof(double), st));
+  // LM diagonal first (it reads the undamped diagonal of H0), Schur terms are then added atomically on top
+  k_add_damping<<<cdiv(n_pad + kBorder, 256), 256, 0, st>>>(H0, Hw, H0.n_band, sd->jscale.p, sd->grad.p, radius, gm, dvec);
+  p->launches++;
+  const StatePtrs S = p->dstate.ptrs();
+  if (F > 0 && L > 0) {
+    const FramePose<N>* fps = (const FramePose<N>*)p->ev.frame_pose.p;
+    CTBA_CUDA(p, cudaMemsetAsync(sd->Sp.p, 0, (size_t)F * (T + 1) * 36 * sizeof(double), st));
+    CTBA_CUDA(p, cudaMemsetAsync(sd->Sb.p, 0, (size_t)F * 42 * sizeof(double), st));
+    CTBA_CUDA(p, cudaMemsetAsync(sd->rp.p, 0, (size_t)F * 6 * sizeof(double), st));
+    k_landmark_schur<N><<<cdiv((size_t)L * 32, 128), 128, 0, st>>>(G, S.glb, fps, S.lm, L, sd->d_lm_obs_begin.p, sd->d_lm_obs.p, p->d_o_frame.p,
+                                                                   p->ev.Jl.p, (const double2*)p->ev.r_reproj.p, p->ev.f_w.p, M, sd->V0.p, sd->gl.p,
+                                                                   sd->jscale_lm.p, radius, T, gm, sd->Sp.p, sd->Sb.p, sd->rp.p, Hw, rhs_acc + n_pad);
+    k_pose_to_knots<N><<<cdiv((size_t)F * (T + 1) * 32, 128), 128, 0, st>>>(fps, F, T, p->d_f_s.p, sd->d_node_of_knot.p, sd->Sp.p, sd->Sb.p, sd->rp.p,
+                                                                            gm, Hw, rhs_acc);
+    p->launches += 2;
+  }
+  k_set_rhs<<<cdiv(n_pad + kBorder, 256), 256, 0, st>>>(Hw, sd->grad.p, rhs_acc, gm);
+  p->launches++;
+  CTBA_CUDA(p, cudaGetLastError());
+  return CTBA_OK;
+}
+int assemble_schur(ctba_problem* p, double radius) { return p->N == 4 ? assemble_schur_T<4>(p, radius) : assemble_schur_T<6>(p, radius); }
+
+template <int N>
+static int backsub_T(ctba_problem* p, const StatePtrs& S, const StatePtrs& C, double radius) {
+  SolverData* sd = p->solver;
+  cudaStream_t st = p->stream;
+  const Globals G = make_globals(p);
+  const GMask gm = make_gmask(sd);
+  const int F = sd->F, M = (int)p->numObs(), L = sd->L;
+  const int n_pad = sd->Hw.n_pad;
+  const FramePose<N>* fps = (const FramePose<N>*)p->ev.frame_pose.p;
+  double* dvec_lm = sd->jscale_lm.p + 3 * (size_t)std::max(L, 1);
+  if (F > 0 && L > 0) {
+    k_frame_dpose<N><<<cdiv(F, 128), 128, 0, st>>>(fps, F, p->d_f_s.p, sd->d_node_of_knot.p, sd->delta.p, sd->dpose.p);
+    k_landmark_backsub<N><<<cdiv(L, 128), 128, 0, st>>>(G, S.glb, fps, S.lm, L, sd->d_lm_obs_begin.p, sd->d_lm_obs.p, p->d_o_frame.p, p->ev.Jl.p,
+                                                        (const double2*)p->ev.r_reproj.p, p->ev.f_w.p, M, sd->V0.p, sd->gl.p, sd->jscale_lm.p,
+                                                        radius, gm, sd->dpose.p, sd->delta.p + n_pad, sd->delta_lm.p, dvec_lm);
+    p->launches += 2;
+  } else if (L > 0) {
+    CTBA_CUDA(p, cudaMemsetAsync(sd->delta_lm.p, 0, 3 * (size_t)L * sizeof(double), st));
+    CTBA_CUDA(p, cudaMemsetAsync(dvec_lm, 0, 3 * (size_t)L * sizeof(double), st));
+  }
+  k_apply_nodes<<<cdiv(sd->K + sd->Kb, 128), 128, 0, st>>>(sd->K, sd->Kb, sd->d_node_of_knot.p, sd->d_node_of_bias.p, sd->delta.p, S, C);
+  k_apply_landmarks_globals<<<cdiv(std::max(3 * L, 1), 256), 256, 0, st>>>(L, sd->delta_lm.p, sd->delta.p + n_pad, gm, S, C);
+  p->launches += 2;
+  if (sd->Kb == 0) {  // bias arrays are unused but keep the candidate mirror defined
+    CTBA_CUDA(p, cudaMemcpyAsync(C.bias_a, S.bias_a, p->dstate.bias_a.n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    CTBA_CUDA(p, cudaMemcpyAsync(C.bias_g, S.bias_g, p->dstate.bias_g.n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  }
+  CTBA_CUDA(p, cudaGetLastError());
+  return CTBA_OK;
+}
+int backsub_and_candidate(ctba_problem* p, const StatePtrs& S, const StatePtrs& C, double radius) {
+  return p->N == 4 ? backsub_T<4>(p, S, C, radius) : backsub_T<6>(p, S, C, radius);
+}
+
+// have_step = (radius > 0): model cost change, step norm; always: |x|^2 and gradient max norm
+int step_scalars(ctba_problem* p, const StatePtrs& S, const StatePtrs& C, double radius) {
+  SolverData* sd = p->solver;
+  const int n_pad = sd->Hw.n_pad;
+  const int L = sd->L;
+  double* dvec = sd->jscale.p + (n_pad + kBorder);
+  double* dvec_lm = sd->jscale_lm.p + 3 * (size_t)std::max(L, 1);
+  const int total = sd->K + sd->Kb + L + 1;
+  const int nb = std::min(256, cdiv(total, 256));
+  k_step_scalars<<<nb, 256, 0, p->stream>>>(sd->K, sd->Kb, L, sd->d_node_of_knot.p, sd->d_node_of_bias.p, sd->d_touch_knot.p, sd->d_touch_bias.p,
+                                            sd->d_touch_lm.p, make_gmask(sd), n_pad, sd->delta.p, sd->delta_lm.p, dvec, dvec_lm, sd->grad.p, sd->gl.p, S, C,
+                                            radius > 0, sd->scal.p + SC_COUNT);
+  k_step_scalars_final<<<1, 32, 0, p->stream>>>(nb, sd->scal.p + SC_COUNT, sd->scal.p);
+  p->launches += 2;
+  CTBA_CUDA(p, cudaGetLastError());
+  return CTBA_OK;
+}
+
+}  // namespace ctba

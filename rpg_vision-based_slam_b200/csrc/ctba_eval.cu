@@ -206,10 +206,9 @@ Globals make_globals(const ctba_problem* p) {
 static inline int cdiv(size_t a, int b) { return (int)((a + b - 1) / b); }
 
 template <int N>
-static int launch_evaluate_T(ctba_problem* p, const StatePtrs& S, bool jac) {
+static int launch_evaluate_T(ctba_problem* p, EvalBuffers& ev, const StatePtrs& S, bool jac) {
   const Globals G = make_globals(p);
   cudaStream_t st = p->stream;
-  EvalBuffers& ev = p->ev;
   const int F = (int)p->numFrames(), M = (int)p->numObs();
   const int nI = (int)p->i_s.size(), nG = (int)p->g_s.size(), nB = (int)p->b_s0.size();
   if (F > 0) {
@@ -271,12 +270,11 @@ static int launch_evaluate_T(ctba_problem* p, const StatePtrs& S, bool jac) {
   return CTBA_OK;
 }
 
-int launch_evaluate(ctba_problem* p, const StatePtrs& S, bool jac) {
-  return p->N == 4 ? launch_evaluate_T<4>(p, S, jac) : launch_evaluate_T<6>(p, S, jac);
+int launch_evaluate(ctba_problem* p, EvalBuffers& ev, const StatePtrs& S, bool jac) {
+  return p->N == 4 ? launch_evaluate_T<4>(p, ev, S, jac) : launch_evaluate_T<6>(p, ev, S, jac);
 }
 
-int launch_cost(ctba_problem* p) {
-  EvalBuffers& ev = p->ev;
+int launch_cost(ctba_problem* p, EvalBuffers& ev) {
   cudaStream_t st = p->stream;
   CTBA_CUDA(p, ev.partial.resize(6 * kRedBlocks));
   CTBA_CUDA(p, ev.cost.resize(8));

@@ -91,12 +91,13 @@ struct ctba_problem {
   bool gravity_norm = false;
 
   // ---- device ----
-  bool meas_dirty = true, state_dirty = true, host_state_stale = false;
+  bool meas_dirty = true, state_dirty = true, host_state_stale = false, struct_dirty = true;
   ctba::DeviceState dstate;
   ctba::DBuf<int32_t> d_f_s, d_f_obs_begin, d_o_lm, d_o_frame, d_i_s, d_i_sb, d_g_s, d_b_s0, d_b_s1, d_b_which;
   ctba::DBuf<double> d_f_u, d_f_inv_std, d_o_uv, d_i_st_s, d_i_k, d_i_ub, d_i_inv_a, d_i_inv_g, d_i_acc, d_i_gyr, d_g_st_s, d_g_k,
       d_g_inv_std, d_g_meas, d_b_u0, d_b_u1, d_b_inv_std;
-  ctba::EvalBuffers ev;
+  ctba::EvalBuffers ev;      // evaluation at the current state (Jacobians used by the assembly kernels)
+  ctba::EvalBuffers ev_alt;  // evaluation at the LM candidate; swapped with `ev` when the step is accepted
   ctba::SolverData* solver = nullptr;
   int64_t launches = 0;  // kernels launched by this handle (bench bookkeeping)
 
@@ -111,8 +112,8 @@ Globals make_globals(const ctba_problem* p);
 int sync_to_device(ctba_problem* p);                 // upload dirty measurements/state
 int download_state(ctba_problem* p);                 // device state -> host vectors
 // residual (+Jacobian) evaluation of every term at state S into p->ev; cost7 (device) filled when want_cost
-int launch_evaluate(ctba_problem* p, const StatePtrs& S, bool jac);
-int launch_cost(ctba_problem* p);                    // p->ev.cost[0..6] from the residual buffers
+int launch_evaluate(ctba_problem* p, EvalBuffers& ev, const StatePtrs& S, bool jac);
+int launch_cost(ctba_problem* p, EvalBuffers& ev);   // ev.cost[0..6] from the residual buffers
 int expand_reproj_dense(ctba_problem* p, const StatePtrs& S, double* d_out);  // 2M x (6N+10)
 void solver_free(SolverData* s);
 int solver_solve(ctba_problem* p, int max_iters, ctba_summary* out);

@@ -1,0 +1,77 @@
+// ctba_solver.h — data layout of the reduced (landmark-eliminated) normal equations on the device.
+//
+// Unknown ordering of the reduced system ("nodes"): spline knots and bias knots merged in time order,
+// 6 scalars per node (knot: rot 3 + pos 3; bias node: acc 3 + gyro 3)  -> block-banded matrix;
+// the <= 15 global parameters form a dense border; landmarks are eliminated per landmark (3x3 Schur).
+//   band    : lower block band, 32x32 scalar blocks, block (ib,jb), 0 <= ib-jb <= nbw, at ((jb*(nbw+1)+(ib-jb))*1024 + (r%32)*32 + (c%32))
+//   border  : 16 rows (15 globals + the right-hand side as a 16th row) x n_pad, row-major
+//   corner  : 16 x 16 (lower part used)
+// This replaces Ceres' SPARSE_NORMAL_CHOLESKY on the full Jacobian (bspline_so3r3.h:1771); the step it
+// produces is the same exact LM step.
+#pragma once
+#include "ctba_internal.h"
+
+namespace ctba {
+
+constexpr int kNB = 32;          // scalar block size of the band
+constexpr int kBorder = 16;      // border rows: GT_SIZE globals + rhs
+constexpr int kRhsRow = 15;
+
+struct BandLayout {
+  int n_band;   // 6 * nodes
+  int n_pad;    // multiple of 32
+  int nbc;      // block columns
+  int nbw;      // block sub-diagonals kept
+  double* band; // device
+  double* border;
+  double* corner;
+  __host__ __device__ size_t band_elems() const { return (size_t)nbc * (nbw + 1) * kNB * kNB; }
+};
+
+__device__ __forceinline__ size_t band_addr(const BandLayout& B, int r, int c) {
+  const int jb = c >> 5, ib = r >> 5;
+  return (((size_t)jb * (B.nbw + 1) + (ib - jb)) << 10) + ((r & 31) << 5) + (c & 31);
+}
+
+// symmetric accumulate of entry (i,j), unified index space: [0,n_pad) band scalars, n_pad + t globals
+__device__ __forceinline__ void add_sym(const BandLayout& B, int i, int j, double v) {
+  int r = i > j ? i : j, c = i > j ? j : i;
+  if (r < B.n_pad) atomicAdd(B.band + band_addr(B, r, c), v);
+  else if (c < B.n_pad) atomicAdd(B.border + (size_t)(r - B.n_pad) * B.n_pad + c, v);
+  else atomicAdd(B.corner + (r - B.n_pad) * kBorder + (c - B.n_pad), v);
+}
+
+struct SolverData {
+  // ---- structure ----
+  int K = 0, Kb = 0, nodes = 0, hbn = 0, L = 0, F = 0, T = 0;
+  bool has_bias = false;
+  std::vector<int32_t> node_of_knot, node_of_bias;
+  DBuf<int32_t> d_node_of_knot, d_node_of_bias, d_lm_obs_begin, d_lm_obs;
+  DBuf<uint8_t> d_touch_knot, d_touch_bias, d_touch_lm;  // bit0 rot/acc, bit1 pos/gyr
+  int gactive[GT_SIZE] = {0};
+  BandLayout H0{}, Hw{};
+  DBuf<double> band0, bandw, border0, borderw, corner0, cornerw;
+  DBuf<double> grad;          // n_pad + 16 : J^T r of the band + global unknowns (no Schur)
+  DBuf<double> V0, gl;        // per landmark: 6 (xx xy xz yy yz zz), 3
+  DBuf<double> Sp, Sb, rp;    // pose-space Schur blocks: F*(T+1)*36, F*42, F*6
+  DBuf<double> jscale, jscale_lm;   // Jacobi scaling (fixed per Solve): n_pad+16, 3L
+  DBuf<double> delta, delta_lm;     // step: n_pad+16, 3L
+  DBuf<double> dpose;               // per frame 6: pose-space step
+  DBuf<double> scal;                // small scalar outputs (see SC_* in ctba_solve.cu)
+  DBuf<int32_t> flag;               // numeric failure flag
+  DeviceState cand;
+  bool built = false;
+};
+
+// assembly kernels (ctba_assemble.cu)
+int assemble_structure(ctba_problem* p);                        // host: nodes, bandwidth, landmark CSR, buffers
+int assemble_direct(ctba_problem* p);                           // H0, grad, V0, gl from the evaluation buffers
+int assemble_schur(ctba_problem* p, double radius);             // Hw = H0 + D^2 - Schur ; rhs row ; uses jscale
+int compute_jscale(ctba_problem* p);
+int backsub_and_candidate(ctba_problem* p, const StatePtrs& S, const StatePtrs& C, double radius);
+int step_scalars(ctba_problem* p, const StatePtrs& S, const StatePtrs& C, double radius);
+int band_factor_solve(ctba_problem* p);                          // ctba_solve.cu
+
+enum { SC_MODEL = 0, SC_STEP2 = 1, SC_XNORM2 = 2, SC_GMAX = 3, SC_COUNT = 8 };
+
+}  // namespace ctba

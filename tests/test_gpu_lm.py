@@ -1,0 +1,96 @@
+"""End-to-end LM parity: ctba_solve (device LM: Schur complement + bordered banded Cholesky) against the oracle LM
+(dense normal equations of the FULL problem incl. landmarks, Jet autodiff).  north_star tolerances: per-iteration
+cost 1e-8 relative, final cost 1e-6 relative, trajectory 1 mm / 0.01 deg."""
+import numpy as np
+import pytest
+from scipy.spatial.transform import Rotation as Rot
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(pkg, oracle, sc, iters, **kw):
+    gpu = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=0)
+    cpu = oracle.OracleSpline(sc["order"], sc["dt_ns"], sc["start_t_ns"])
+    pkg.load_scene(gpu, sc, **kw); pkg.load_scene(cpu, sc, **kw)
+    sg = gpu.optimize(iters)
+    so = cpu.optimize(iters, 8)
+    return gpu, cpu, sg, so
+
+
+def _check(gpu, cpu, sg, so, cost_tol=1e-8):
+    ig, io = sg["iterations"], so["iterations"]
+    assert ig.shape == io.shape, (ig.shape, io.shape, sg["termination_type"], so["termination_type"])
+    assert sg["termination_type"] == so["termination_type"]
+    assert (ig[:, 6] == io[:, 6]).all()                      # same accept/reject sequence
+    np.testing.assert_allclose(ig[:, 0], io[:, 0], rtol=cost_tol)   # per-iteration cost
+    np.testing.assert_allclose(ig[:, 5], io[:, 5], rtol=1e-6)       # trust-region radius trajectory
+    ok = io[:, 6] > 0
+    np.testing.assert_allclose(ig[1:, 3], io[1:, 3], rtol=1e-5, atol=1e-12)  # step norms
+    assert abs(sg["final_cost"] - so["final_cost"]) <= 1e-6 * so["final_cost"]
+    qg, pg = gpu.getKnots(); qo, po = cpu.getKnots()
+    assert np.abs(pg - po).max() < 1e-3                      # 1 mm
+    ang = (Rot.from_quat(qg).inv() * Rot.from_quat(qo)).magnitude()
+    assert np.rad2deg(ang.max()) < 0.01                      # 0.01 deg
+    np.testing.assert_allclose(gpu.get3DPoints(), cpu.get3DPoints(), atol=1e-3)
+    np.testing.assert_allclose(gpu.getGlobals(), cpu.getGlobals(), atol=1e-5)
+    ag, gg = gpu.getBiases(); ao, go = cpu.getBiases()
+    if ao.size:
+        np.testing.assert_allclose(ag, ao, atol=1e-5); np.testing.assert_allclose(gg, go, atol=1e-6)
+
+
+def test_lm_full_gvi(pkg, scene, oracle):
+    """optimize_continuous_time-shaped: vision + IMU + bias spline + GP + gravity norm, every global free."""
+    sc = scene.make_scene(order=6, duration_s=4.0, n_landmarks=120, track_len=12, imu_hz=100, gp_hz=10, dt_s_bias=0.25,
+                          flags=(True, True, True, True, True), gravity_norm=True, outlier_frac=0.02)
+    gpu, cpu, sg, so = _run(pkg, oracle, sc, 12)
+    assert so["num_successful_steps"] >= 5
+    _check(gpu, cpu, sg, so)
+
+
+def test_lm_vi(pkg, scene, oracle):
+    """optimize_vi_continuous_time-shaped: vision + IMU, no GP (gauge left to LM damping)."""
+    sc = scene.make_scene(order=6, duration_s=3.0, n_landmarks=100, track_len=10, imu_hz=100, gp_hz=0, dt_s_bias=0.2, seed=77,
+                          flags=(False, True, True, True, True), gravity_norm=True)
+    gpu, cpu, sg, so = _run(pkg, oracle, sc, 8)
+    _check(gpu, cpu, sg, so)
+
+
+def test_lm_gv_cubic(pkg, scene, oracle):
+    """optimize_gv_continuous_time-shaped with a cubic spline: vision + GP, extrinsics free (ctor default), fisheye camera."""
+    sc = scene.make_scene(order=4, duration_s=3.0, n_landmarks=100, track_len=10, imu_hz=0, gp_hz=10, cam="fpv", seed=5,
+                          flags=(True, True, False, True, True))
+    gpu, cpu, sg, so = _run(pkg, oracle, sc, 8)
+    _check(gpu, cpu, sg, so)
+
+
+def test_lm_fixed_globals_and_first_call(pkg, scene, oracle):
+    """optimize(1) as the drivers' first call (always NO_CONVERGENCE), then a second Solve re-derives the Jacobi scaling;
+    globals constant."""
+    sc = scene.make_scene(order=6, duration_s=2.5, n_landmarks=80, track_len=8, imu_hz=50, gp_hz=10, dt_s_bias=0.2, seed=3,
+                          flags=(False, False, False, False, False))
+    gpu = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=0)
+    cpu = oracle.OracleSpline(sc["order"], sc["dt_ns"], sc["start_t_ns"])
+    pkg.load_scene(gpu, sc); pkg.load_scene(cpu, sc)
+    s1g, s1o = gpu.optimize(1), cpu.optimize(1, 4)
+    assert s1g["termination_type"] == 1 and s1o["termination_type"] == 1
+    gpu.relinearize(); cpu.relinearize()
+    s2g, s2o = gpu.optimize(6), cpu.optimize(6, 4)
+    _check(gpu, cpu, s2g, s2o)
+    g = gpu.getGlobals()
+    assert g[0] == 0.0 and (g[5:10] == 0.0).all()     # constant parameter blocks untouched
+
+
+def test_solve_idempotent_at_convergence(pkg, scene):
+    """Size-independent property: a second Solve from the converged state does not move it (cost decrease < function tol)."""
+    sc = scene.make_scene(order=6, duration_s=6.0, n_landmarks=400, track_len=12, imu_hz=100, gp_hz=10, dt_s_bias=0.25, seed=21)
+    gpu = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=0)
+    pkg.load_scene(gpu, sc)
+    s1 = gpu.optimize(40)
+    assert s1["termination_type"] == 0
+    assert s1["final_cost"] < 0.05 * s1["initial_cost"]
+    s2 = gpu.optimize(5)
+    assert abs(s2["final_cost"] - s1["final_cost"]) <= 1e-5 * s1["final_cost"]
+    q, p = gpu.getKnots()
+    # recovered trajectory close to the ground truth where it is observed (synthetic noise level)
+    inner = slice(3, -4)
+    assert np.abs(p[inner] - sc["gt_knot_p"][inner]).max() < 0.05
