@@ -1,5 +1,16 @@
 #!/usr/bin/env python
-"""bench.py — headline benchmark (BASELINE.json metric) on synthetic scenes.  See DESIGN.md §Measurement."""
+"""bench.py — headline benchmark of the hot path on synthetic scenes (datasets are not available offline).
+
+metric : LM iterations/s of the full-batch continuous-time bundle adjustment (BASELINE.json `metric`), measured on
+         BASELINE configs[1] (optimize_vi_continuous_time, EuRoC MH_01-shaped: 180 s, 20 Hz camera, 200 Hz IMU,
+         ~40k landmarks, ~600k observations).  One "step" = one trust-region LM iteration over the whole batch
+         (residual+Jacobian evaluation of every term, Schur complement, banded solve, candidate evaluation).
+value  : device-resident rate (state and measurements already in HBM), CUDA events on the launching stream.
+e2e    : the same metric through the C-ABI with HOST buffers: every step re-uploads state + measurements
+         (ctba_invalidate_device), runs ctba_solve(1 iteration) and reads the state back.
+extra  : residual+Jacobian Mobs/s of the evaluation kernels alone, with the roofline of the dominant kernel.
+--impl reference : the CPU oracle (restated reference functors, Ceres DynamicAutoDiff schedule) on the host cores.
+"""
 import argparse
 import importlib
 import json
@@ -14,61 +25,188 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 PKG = "rpg_vision-based_slam_b200"
+WORKLOAD = {1: "configs[0] optimize_continuous_time indoor_forward_3-shaped", 2: "configs[1] optimize_vi_continuous_time EuRoC MH_01-shaped",
+            3: "configs[2] optimize_gv_continuous_time 1h/10k frames/5M obs"}
 
 
-def clocks_sampler(stop, out):
-    q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+def clocks_sampler(stop, out, dev):
+    q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
     while not stop.is_set():
         try:
-            o = subprocess.run(["nvidia-smi", "-i", "0", f"--query-gpu={q}", "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-            out.append(o.strip().split(", "))
+            o = subprocess.run(["nvidia-smi", "-i", str(dev), f"--query-gpu={q}", "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                               timeout=5).stdout
+            f = [x.strip() for x in o.strip().split(",")]
+            if len(f) >= 6:
+                out.append(f)
         except Exception:
             pass
         stop.wait(0.2)
 
 
+def clocks_summary(samples):
+    if not samples:
+        return {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+    sm = [float(s[0]) for s in samples]
+    reasons = []
+    for i, name in enumerate(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]):
+        if any(s[2 + i].lower().startswith("active") for s in samples):
+            reasons.append(name)
+    return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(samples[0][1]), "reasons": reasons}
+
+
+def cpu_reference_leg(scene_mod, cfg, steps, warmup, threads, budget_s=20.0):
+    """The reference's CPU path restated (oracle): Jacobian evaluation with the Ceres DynamicAutoDiff schedule (stride-4 Jets,
+    one residual block per frame incl. all its landmarks) + a residual-only candidate evaluation = the evaluation work of one
+    LM iteration.  The sparse Cholesky of Ceres is NOT timed (Ceres is absent; the oracle's exact solver is dense), so the
+    reported LM rate is an UPPER bound of the CPU rate.  Bounded sample: a time slice of the same scene."""
+    from oracle.binding import OracleSpline
+    pkg = importlib.import_module(PKG)
+    slice_s = 3.0
+    dens = scene_mod.config_scene(cfg, duration_s=slice_s, n_landmarks=1)  # cheap call to read rates
+    full = {1: (50.0, 20000), 2: (180.0, 40000), 3: (3600.0, 200000)}[cfg]
+    sc = scene_mod.config_scene(cfg, duration_s=slice_s, n_landmarks=max(int(full[1] * slice_s / full[0]), 50))
+    o = OracleSpline(sc["order"], sc["dt_ns"], sc["start_t_ns"])
+    pkg.load_scene(o, sc)
+    c = o.counts()
+    t1, obs = o.timeEvaluate(threads, 1, 0)   # calibrate
+    reps = max(1, min(int(budget_s / max(t1, 1e-3) / max(steps + warmup, 1)), 3))
+    times = []
+    for i in range(warmup + steps):
+        t, obs = o.timeEvaluate(threads, reps, 0)
+        t0 = time.perf_counter(); o.cost(); tc = time.perf_counter() - t0   # candidate (residual-only) evaluation, 1 thread -> scale
+        if i >= warmup:
+            times.append(t / reps + tc / threads)
+    t_iter_sample = float(np.mean(times))
+    frac = slice_s / full[0]
+    return dict(sample=f"{slice_s:.0f} s slice of the scene ({c['frames']} frames, {c['obs']} observations, {c['accel']} IMU samples), "
+                       f"evaluation work of one LM iteration, linear solve excluded (upper bound)",
+                t_iter_sample=t_iter_sample, obs_sample=c["obs"], lm_per_s=frac / t_iter_sample, mobs_per_s=c["obs"] / (t_iter_sample) / 1e6,
+                threads=threads)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--config", type=int, default=2)
-    ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (debug only)")
     a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    scene_mod = importlib.import_module(PKG + ".scene")
+    threads = os.cpu_count() or 1
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        r = cpu_reference_leg(scene_mod, a.config, a.steps, max(a.warmup, 1), threads)
+        line = {"impl": "reference", "metric": "LM iterations/s", "value": r["lm_per_s"], "unit": "it/s", "n_gpus": a.gpus, "steps": a.steps,
+                "warmup": a.warmup, "ms_per_step": 1e3 / r["lm_per_s"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic", "config": {"workload": WORKLOAD[a.config]},
+                "cpu_baseline": {"value": r["lm_per_s"], "unit": "it/s", "cores": threads, "kind": "port", "sample": r["sample"]},
+                "e2e": {"value": r["lm_per_s"], "unit": "it/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "mobs_per_s": r["mobs_per_s"]}
+        print(json.dumps(line))
+        return
+
     import torch
+    import torch.distributed as dist
     pkg = importlib.import_module(PKG)
-    scene = importlib.import_module(PKG + ".scene")
-    over = {}
-    if a.scale != 1.0:
-        base = dict(duration_s=180.0, n_landmarks=40000)
-        over = dict(duration_s=base["duration_s"] * a.scale, n_landmarks=int(base["n_landmarks"] * a.scale))
-    sc = scene.config_scene(a.config, **over)
-    g = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=0)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    torch.cuda.set_device(local_rank)
+    # weak scaling: every rank owns an independent trajectory segment of the configured shape ("replicas"; the
+    # time-segment-sharded single problem is the next multi-GPU row, see DESIGN.md)
+    sc = scene_mod.config_scene(a.config, seed=20240101 + a.config + rank)
+    g = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=local_rank)
     pkg.load_scene(g, sc)
     n = g.counts()
     stream = torch.cuda.Stream()
     g.setStream(stream.cuda_stream)
-    g.cost()
-    for _ in range(a.warmup):
+    g.setOption("bench_no_termination", 1)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident LM iterations ----
+    g.optimize(max(a.warmup, 3))
+    barrier()
+    stop = threading.Event(); samples = []
+    th = threading.Thread(target=clocks_sampler, args=(stop, samples, local_rank)); th.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    s = g.optimize(a.steps)
+    e1.record(stream)
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    steps_done = s["iterations"].shape[0] - 1
+    assert steps_done == a.steps, (steps_done, a.steps)
+    launches = s["kernel_launches"]
+
+    # ---- residual+Jacobian kernels alone (roofline of the dominant evaluation kernel) ----
+    for _ in range(3):
         g.benchEvaluate(1)
     torch.cuda.synchronize()
-    stop = threading.Event(); samples = []
-    th = threading.Thread(target=clocks_sampler, args=(stop, samples)); th.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with torch.cuda.stream(stream):
-        e0.record(stream)
-        launches = g.benchEvaluate(a.steps)
-        e1.record(stream)
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / a.steps
+    reps = 20
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k0.record(stream); g.benchEvaluate(reps); k1.record(stream); torch.cuda.synchronize()
+    ms_eval = k0.elapsed_time(k1) / reps
     stop.set(); th.join()
-    sm = [float(s[0]) for s in samples if len(s) >= 2]
-    line = {"metric": "residual+Jacobian Mobs/s", "value": n["obs"] / ms / 1e3, "unit": "Mobs/s", "n_gpus": 1, "steps": a.steps, "warmup": a.warmup,
-            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"configs[{a.config - 1}]", **n}, "gpu_launches": launches,
-            "clocks": {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(samples[0][1]) if samples else None}}
+
+    # ---- end to end through the C-ABI with host buffers ----
+    h2d, d2h = g.transferBytes()
+    e2e_steps = max(3, min(a.steps, 10))
+    g.invalidateDevice(); g.optimize(1); g.getKnots()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        g.invalidateDevice()          # state + measurements are uploaded again from host memory
+        g.optimize(1)                 # one LM iteration
+        g.getKnots(); g.get3DPoints()  # result back in host memory
+    torch.cuda.synchronize()
+    t_e2e = (time.perf_counter() - t0) / e2e_steps
+
+    tms = torch.tensor([ms_total, t_e2e * 1e3, ms_eval], dtype=torch.float64, device=f"cuda:{local_rank}")
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    ms_total, e2e_ms, ms_eval = [float(x) for x in tms.cpu()]
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    ms_step = ms_total / a.steps
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    # dominant evaluation kernel k_reproj: algorithmic bytes per observation = 48 B in (uv 16, landmark index 4, frame index 4,
+    # landmark 24) + 64 B out (r 16, Jl = dr/dp_w 48): the pose / global Jacobian blocks are linear maps of Jl and are never
+    # materialised (DESIGN.md §3).  Its duration is measured separately by profiles/ (ncu) — here the whole evaluation pass is timed.
+    alg_bytes = 112.0 * n["obs"]
+    line = {"metric": "LM iterations/s", "value": world * 1e3 / ms_step, "unit": "it/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD[a.config], "l2": "inputs+outputs per step exceed L2 only at config 3; band (49 MB) + Jacobians (38 MB) here", **n},
+            "gpu_launches": int(launches), "clocks": clocks_summary(samples),
+            "e2e": {"value": world * 1e3 / e2e_ms, "unit": "it/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "mobs_per_s": world * n["obs"] / ms_eval / 1e3, "eval_ms": ms_eval,
+            "lm_breakdown_ms": {"eval": 1e3 * s["time_eval_s"] / a.steps, "assemble": 1e3 * s["time_build_s"] / a.steps, "solve": 1e3 * s["time_solve_s"] / a.steps},
+            "roofline": {"kernel": "evaluation pass (k_frame_pose+k_reproj+k_imu+...)", "bound": "hbm", "achieved": alg_bytes / (ms_eval * 1e-3) / 1e9,
+                         "peak": peak, "unit": "GB/s", "frac": alg_bytes / (ms_eval * 1e-3) / 1e9 / peak, "traffic": None,
+                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}}
+    if world == 1:
+        r = cpu_reference_leg(scene_mod, a.config, 2, 1, threads, budget_s=15.0)
+        line["cpu_baseline"] = {"value": r["lm_per_s"], "unit": "it/s", "cores": threads, "kind": "port", "sample": r["sample"], "mobs_per_s": r["mobs_per_s"]}
     print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

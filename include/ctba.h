@@ -119,6 +119,7 @@ typedef struct ctba_summary {
   ctba_iteration* iterations;    /* caller-provided array of `iterations_capacity` entries, may be NULL */
   int iterations_capacity;
   double time_total_s, time_eval_s, time_build_s, time_solve_s; /* device-side breakdown */
+  int64_t kernel_launches;       /* kernels launched by this call */
 } ctba_summary;
 
 /* BSplineSO3R3::optimize(max_num_iterations) == ceres::Solve            bspline_so3r3.h:1768-1782
@@ -128,6 +129,15 @@ int ctba_solve(ctba_problem* p, int max_num_iterations, ctba_summary* summary);
 
 /* relinearizeSplineImuTimeOffset + relinearizeSplineGlobSensTimeOffset   bspline_so3r3.h:1807-1811, 1853-1857 */
 int ctba_relinearize_time_offsets(ctba_problem* p);
+
+/* Options: "bench_no_termination" (1 = ctba_solve runs exactly max_num_iterations LM iterations, convergence tests
+ * disabled; measurement only), "cauchy_a" (CauchyLoss parameter of the reprojection blocks, default 3.0, bspline_so3r3.h:1032). */
+int ctba_set_option(ctba_problem* p, const char* name, double value);
+/* Forget the device mirrors: the next evaluate/solve uploads state and measurements from the host copies again
+ * (used to time the end-to-end path with host buffers). */
+int ctba_invalidate_device(ctba_problem* p);
+/* bytes[2] = host->device bytes of a full upload (state + measurements), device->host bytes of a state read-back */
+int ctba_transfer_bytes(ctba_problem* p, int64_t* bytes2);
 
 /* Device-only benchmarking hooks (inputs already resident): run `reps` passes of the residual+Jacobian
  * kernels (which != 0) or of a full LM iteration, return the kernel launch count. */

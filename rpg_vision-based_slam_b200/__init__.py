@@ -26,7 +26,7 @@ EXPORTS = [
     "ctba_initialize_biases", "ctba_num_bias_knots", "ctba_set_biases", "ctba_get_biases", "ctba_set_landmarks", "ctba_get_landmarks",
     "ctba_set_camera", "ctba_set_globals", "ctba_set_corrections", "ctba_get_globals", "ctba_set_flags", "ctba_add_frames", "ctba_add_imu",
     "ctba_add_gp", "ctba_add_bias_cost", "ctba_add_gravity_norm", "ctba_counts", "ctba_evaluate", "ctba_cost", "ctba_solve",
-    "ctba_relinearize_time_offsets", "ctba_bench_evaluate",
+    "ctba_relinearize_time_offsets", "ctba_bench_evaluate", "ctba_set_option", "ctba_invalidate_device", "ctba_transfer_bytes",
 ]
 
 
@@ -43,7 +43,8 @@ class _Summary(C.Structure):
     _fields_ = [("termination_type", C.c_int), ("initial_cost", C.c_double), ("final_cost", C.c_double),
                 ("num_successful_steps", C.c_int), ("num_unsuccessful_steps", C.c_int), ("num_iterations", C.c_int),
                 ("iterations", C.POINTER(_Iteration)), ("iterations_capacity", C.c_int),
-                ("time_total_s", C.c_double), ("time_eval_s", C.c_double), ("time_build_s", C.c_double), ("time_solve_s", C.c_double)]
+                ("time_total_s", C.c_double), ("time_eval_s", C.c_double), ("time_build_s", C.c_double), ("time_solve_s", C.c_double),
+                ("kernel_launches", C.c_int64)]
 
 
 def lib():
@@ -225,10 +226,22 @@ class BSplineSO3R3:
                          its[i].successful] for i in range(n)]).reshape(n, 7)
         return dict(termination_type=s.termination_type, initial_cost=s.initial_cost, final_cost=s.final_cost,
                     num_successful_steps=s.num_successful_steps, num_unsuccessful_steps=s.num_unsuccessful_steps, iterations=log,
-                    time_total_s=s.time_total_s, time_eval_s=s.time_eval_s, time_build_s=s.time_build_s, time_solve_s=s.time_solve_s)
+                    time_total_s=s.time_total_s, time_eval_s=s.time_eval_s, time_build_s=s.time_build_s, time_solve_s=s.time_solve_s,
+                    kernel_launches=int(s.kernel_launches))
 
     def relinearize(self):
         self._chk(self.L.ctba_relinearize_time_offsets(self.h))
+
+    def setOption(self, name, value):
+        self._chk(self.L.ctba_set_option(self.h, name.encode(), C.c_double(value)))
+
+    def invalidateDevice(self):
+        self._chk(self.L.ctba_invalidate_device(self.h))
+
+    def transferBytes(self):
+        b = np.zeros(2, dtype=np.int64)
+        self._chk(self.L.ctba_transfer_bytes(self.h, _p(b)))
+        return int(b[0]), int(b[1])
 
     def benchEvaluate(self, reps):
         n = C.c_int64(0)

@@ -447,6 +447,36 @@ int ctba_relinearize_time_offsets(ctba_problem* p) {
   return CTBA_OK;
 }
 
+int ctba_set_option(ctba_problem* p, const char* name, double value) {
+  CHECK_P(p);
+  if (!name) return CTBA_E_ARG;
+  if (!std::strcmp(name, "bench_no_termination")) { p->bench_no_termination = value != 0.0; return CTBA_OK; }
+  if (!std::strcmp(name, "cauchy_a")) { if (!(value > 0)) return fail(p, CTBA_E_ARG, "cauchy_a must be > 0"); p->cauchy_a = value; return CTBA_OK; }
+  return fail(p, CTBA_E_ARG, "set_option: unknown option");
+}
+
+int ctba_invalidate_device(ctba_problem* p) {
+  CHECK_P(p);
+  cudaSetDevice(p->device);
+  int rc = download_state(p); if (rc) return rc;
+  p->meas_dirty = true; p->state_dirty = true;
+  return CTBA_OK;
+}
+
+int ctba_transfer_bytes(ctba_problem* p, int64_t* b) {
+  CHECK_P(p);
+  if (!b) return CTBA_E_ARG;
+  const int64_t state = (int64_t)(p->knot_q.size() + p->knot_p.size() + p->bias_a.size() + p->bias_g.size() + p->lm.size() + GLB_STATE_SIZE) * 8;
+  int64_t meas = 0;
+  meas += (int64_t)(p->f_s.size() + p->f_obs_begin.size() + p->o_lm.size() + p->o_frame.size() + p->i_s.size() + p->i_sb.size() + p->g_s.size() +
+                    p->b_s0.size() + p->b_s1.size() + p->b_which.size()) * 4;
+  meas += (int64_t)(p->f_u.size() + p->f_inv_std.size() + p->o_uv.size() + p->i_st_s.size() + p->i_k.size() + p->i_ub.size() + p->i_inv_a.size() +
+                    p->i_inv_g.size() + p->i_acc.size() + p->i_gyr.size() + p->g_st_s.size() + p->g_k.size() + p->g_inv_std.size() + p->g_meas.size() +
+                    p->b_u0.size() + p->b_u1.size() + p->b_inv_std.size()) * 8;
+  b[0] = state + meas; b[1] = state;
+  return CTBA_OK;
+}
+
 int ctba_bench_evaluate(ctba_problem* p, int reps, int64_t* launches) {
   CHECK_P(p);
   CTBA_CUDA(p, cudaSetDevice(p->device));

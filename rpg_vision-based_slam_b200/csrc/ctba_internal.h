@@ -76,6 +76,7 @@ struct ctba_problem {
   ctba::Camera cam{4, 1, 1, 0, 0, {0, 0, 0, 0}};
   double q_bc0[4] = {0, 0, 0, 1}, p_bc0[3] = {0, 0, 0};
   double cauchy_a = 3.0;
+  bool bench_no_termination = false;
 
   // ---- host work items ----
   std::vector<int32_t> f_s, f_obs_begin{0};

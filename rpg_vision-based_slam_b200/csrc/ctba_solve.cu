@@ -277,6 +277,7 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
   const double function_tolerance = 1e-6, gradient_tolerance = 1e-10, parameter_tolerance = 1e-8;
   const int max_consecutive_invalid = 5;
   auto t_begin = std::chrono::steady_clock::now();
+  const int64_t launches0 = p->launches;
   out->time_eval_s = out->time_build_s = out->time_solve_s = 0.0;
   if (!p->solver || !p->solver->built || p->struct_dirty) {
     int rc0 = assemble_structure(p); if (rc0) return rc0;
@@ -327,11 +328,11 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
   double radius = initial_radius, decrease_factor = 2.0;
   int invalid = 0, iter = 0;
   if (!std::isfinite(x_cost)) { out->termination_type = 2; goto done; }
-  if (gmax <= gradient_tolerance) { out->termination_type = 0; goto done; }
+  if (!p->bench_no_termination && gmax <= gradient_tolerance) { out->termination_type = 0; goto done; }
   while (true) {
     if (iter >= max_num_iterations) { out->termination_type = 1; break; }
-    if (radius < min_radius) { out->termination_type = 0; break; }
-    if (invalid > max_consecutive_invalid) { out->termination_type = 2; break; }
+    if (radius < min_radius) { if (p->bench_no_termination) radius = initial_radius; else { out->termination_type = 0; break; } }
+    if (invalid > max_consecutive_invalid && !p->bench_no_termination) { out->termination_type = 2; break; }
     ++iter;
     {
       EvTimer tb(st, &out->time_build_s);
@@ -369,11 +370,11 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
     const double cost_change = x_cost - cand_cost;
     const double ratio = cost_change / model_cost_change;
     // ParameterToleranceReached / FunctionToleranceReached are tested before accept/reject (Ceres 2.x order; same in the oracle)
-    if (step_norm <= parameter_tolerance * (x_norm + parameter_tolerance)) {
+    if (!p->bench_no_termination && step_norm <= parameter_tolerance * (x_norm + parameter_tolerance)) {
       log_it(x_cost, cost_change, gmax, step_norm, ratio, radius, 0);
       out->termination_type = 0; break;
     }
-    if (std::fabs(cost_change) <= function_tolerance * x_cost) {
+    if (!p->bench_no_termination && std::fabs(cost_change) <= function_tolerance * x_cost) {
       log_it(x_cost, cost_change, gmax, step_norm, ratio, radius, 0);
       out->termination_type = 0; break;
     }
@@ -389,7 +390,7 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
       decrease_factor = 2.0;
       out->num_successful_steps++;
       log_it(x_cost, cost_change, gmax, step_norm, ratio, radius, 1);
-      if (gmax <= gradient_tolerance) { out->termination_type = 0; break; }
+      if (!p->bench_no_termination && gmax <= gradient_tolerance) { out->termination_type = 0; break; }
     } else {
       radius /= decrease_factor; decrease_factor *= 2.0;
       out->num_unsuccessful_steps++;
@@ -399,6 +400,7 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
 done:
   out->final_cost = x_cost;
   out->num_iterations = nit;
+  out->kernel_launches = p->launches - launches0;
   CTBA_CUDA(p, cudaStreamSynchronize(st));
   out->time_total_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
   return CTBA_OK;
