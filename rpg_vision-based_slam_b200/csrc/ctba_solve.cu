@@ -6,10 +6,7 @@
 // is solved exactly (Schur complement on the landmarks + bordered banded Cholesky), so the step equals the step of
 // the reference's sparse Cholesky up to rounding.
 //
-//   k_band_column     left-looking block column step (one launch per 32-column block): every CTA redoes the diagonal
-//                     block update + 32x32 Cholesky, then owns one sub-diagonal (or the 16-row border) block: update + TRSM
-//   k_corner_partial / k_corner_solve   Schur complement of the band onto the 15 global parameters, 15x15 solve
-//   k_band_backsolve  single-CTA backward substitution L^T x = y - Lb^T z
+// The factorisation / substitution kernels live in ctba_band.cu (band_factor_solve).
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -20,233 +17,10 @@ namespace ctba {
 
 static inline int cdiv(size_t a, int b) { return (int)((a + b - 1) / b); }
 
-constexpr int kLd = kNB + 1;  // padded leading dimension in shared memory
-
-// C[r][c] -= sum_m A[r][m] * Bm[c][m]  for the 4 rows of this thread (256 threads: tx = col, ty*4.. rows)
-__device__ __forceinline__ void block_mac(const double* sA, const double* sB, int tx, int ty, double acc[4]) {
-#pragma unroll 8
-  for (int m = 0; m < kNB; ++m) {
-    const double b = sB[tx * kLd + m];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) acc[q] -= sA[(ty * 4 + q) * kLd + m] * b;
-  }
-}
-__device__ __forceinline__ void load_block(const double* __restrict__ g, double* s, int tid) {
-#pragma unroll
-  for (int e = tid; e < kNB * kNB; e += 256) s[(e >> 5) * kLd + (e & 31)] = g[e];
-}
-
-__global__ void __launch_bounds__(256) k_band_column(BandLayout B, int j, int32_t* __restrict__ flag) {
-  __shared__ double sD[kNB * kLd], sA[kNB * kLd], sB[kNB * kLd];
-  const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
-  const int nb1 = B.nbw + 1;
-  const int k0 = max(0, j - B.nbw);
-  // ---- diagonal block: D = A(j,j) - sum_k L(j,k) L(j,k)^T ----
-  double accD[4];
-  {
-    const double* Ajj = B.band + ((size_t)j * nb1) * 1024;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) accD[q] = Ajj[(ty * 4 + q) * 32 + tx];
-  }
-  for (int k = k0; k < j; ++k) {
-    __syncthreads();
-    load_block(B.band + ((size_t)k * nb1 + (j - k)) * 1024, sA, tid);
-    __syncthreads();
-    block_mac(sA, sA, tx, ty, accD);
-  }
-  __syncthreads();
-#pragma unroll
-  for (int q = 0; q < 4; ++q) sD[(ty * 4 + q) * kLd + tx] = accD[q];
-  __syncthreads();
-  // ---- 32x32 Cholesky (lower) in shared memory ----
-  for (int c = 0; c < kNB; ++c) {
-    if (tid == 0) {
-      double d = sD[c * kLd + c];
-      if (!(d > 0.0) || !isfinite(d)) { if (blockIdx.x == 0) atomicExch(flag, 1); d = 1.0; }
-      sD[c * kLd + c] = sqrt(d);
-    }
-    __syncthreads();
-    if (tid > c && tid < kNB) sD[tid * kLd + c] /= sD[c * kLd + c];
-    __syncthreads();
-    // trailing update: rows r > c, cols k in (c, r]
-    for (int e = tid; e < kNB * kNB; e += 256) {
-      const int r = e >> 5, k = e & 31;
-      if (k > c && r >= k) sD[r * kLd + k] -= sD[r * kLd + c] * sD[k * kLd + c];
-    }
-    __syncthreads();
-  }
-  const int b = blockIdx.x;
-  if (b == 0) {
-    double* Ljj = B.band + ((size_t)j * nb1) * 1024;
-    for (int e = tid; e < kNB * kNB; e += 256) { const int r = e >> 5, c = e & 31; Ljj[e] = (c <= r) ? sD[r * kLd + c] : 0.0; }
-    return;
-  }
-  const int nrows_band = min(B.nbw, B.nbc - 1 - j);
-  const bool is_border = (b == nrows_band + 1);
-  // ---- off-diagonal (or border) block: acc = A(i,j) - sum_k L(i,k) L(j,k)^T ----
-  double acc[4];
-  if (!is_border) {
-    const int i = j + b;
-    const double* Aij = B.band + ((size_t)j * nb1 + b) * 1024;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) acc[q] = Aij[(ty * 4 + q) * 32 + tx];
-    for (int k = max(0, i - B.nbw); k < j; ++k) {
-      __syncthreads();
-      load_block(B.band + ((size_t)k * nb1 + (i - k)) * 1024, sA, tid);
-      load_block(B.band + ((size_t)k * nb1 + (j - k)) * 1024, sB, tid);
-      __syncthreads();
-      block_mac(sA, sB, tx, ty, acc);
-    }
-  } else {
-    // 16 border rows: rows ty*4+q >= 16 idle
-#pragma unroll
-    for (int q = 0; q < 4; ++q) { const int r = ty * 4 + q; acc[q] = r < kBorder ? B.border[(size_t)r * B.n_pad + j * kNB + tx] : 0.0; }
-    for (int k = k0; k < j; ++k) {
-      __syncthreads();
-      for (int e = tid; e < kNB * kNB; e += 256) { const int r = e >> 5, c = e & 31; sA[r * kLd + c] = r < kBorder ? B.border[(size_t)r * B.n_pad + k * kNB + c] : 0.0; }
-      load_block(B.band + ((size_t)k * nb1 + (j - k)) * 1024, sB, tid);
-      __syncthreads();
-      block_mac(sA, sB, tx, ty, acc);
-    }
-  }
-  __syncthreads();
-#pragma unroll
-  for (int q = 0; q < 4; ++q) sA[(ty * 4 + q) * kLd + tx] = acc[q];
-  __syncthreads();
-  // ---- TRSM: X * Ljj^T = acc, one thread per row ----
-  if (tid < kNB) {
-    const int r = tid;
-    for (int c = 0; c < kNB; ++c) {
-      double v = sA[r * kLd + c];
-      for (int m = 0; m < c; ++m) v -= sA[r * kLd + m] * sD[c * kLd + m];
-      sA[r * kLd + c] = v / sD[c * kLd + c];
-    }
-  }
-  __syncthreads();
-  if (!is_border) {
-    double* Lij = B.band + ((size_t)j * nb1 + b) * 1024;
-    for (int e = tid; e < kNB * kNB; e += 256) Lij[e] = sA[(e >> 5) * kLd + (e & 31)];
-  } else {
-    for (int e = tid; e < kBorder * kNB; e += 256) { const int r = e >> 5, c = e & 31; B.border[(size_t)r * B.n_pad + j * kNB + c] = sA[r * kLd + c]; }
-  }
-}
-
-// partial[blk][a*16+b] = sum over the block's 256 columns of Lb[a][c] Lb[b][c]
-__global__ void __launch_bounds__(256) k_corner_partial(BandLayout B, double* __restrict__ partial) {
-  __shared__ double s[kBorder][257];
-  const int c0 = blockIdx.x * 256;
-  for (int e = threadIdx.x; e < kBorder * 256; e += 256) {
-    const int r = e >> 8, c = e & 255;
-    s[r][c] = (c0 + c < B.n_pad) ? B.border[(size_t)r * B.n_pad + c0 + c] : 0.0;
-  }
-  __syncthreads();
-  const int a = threadIdx.x >> 4, b = threadIdx.x & 15;
-  double v = 0.0;
-  for (int c = 0; c < 256; ++c) v += s[a][c] * s[b][c];
-  partial[(size_t)blockIdx.x * 256 + threadIdx.x] = v;
-}
-// G' = G - Lb Lb^T ; c' = c - Lb y ; z = G'^-1 c'   (15x15, one thread) ; delta[n_pad + t] = z[t]
-__global__ void k_corner_solve(BandLayout B, int nblk, const double* __restrict__ partial, double* __restrict__ delta, int32_t* __restrict__ flag) {
-  __shared__ double Msum[256];
-  {
-    double v = 0.0;
-    for (int k = 0; k < nblk; ++k) v += partial[(size_t)k * 256 + threadIdx.x];
-    Msum[threadIdx.x] = v;
-  }
-  __syncthreads();
-  if (threadIdx.x != 0) return;
-  const int n = GT_SIZE;
-  double Gm[GT_SIZE][GT_SIZE], c[GT_SIZE];
-  for (int a = 0; a < n; ++a) {
-    for (int b = 0; b <= a; ++b) { Gm[a][b] = B.corner[a * kBorder + b] - Msum[a * 16 + b]; Gm[b][a] = Gm[a][b]; }
-    c[a] = B.corner[kRhsRow * kBorder + a] - Msum[kRhsRow * 16 + a];
-  }
-  for (int j = 0; j < n; ++j) {
-    double d = Gm[j][j];
-    for (int k = 0; k < j; ++k) d -= Gm[j][k] * Gm[j][k];
-    if (!(d > 0.0) || !isfinite(d)) { atomicExch(flag, 2); d = 1.0; }
-    d = sqrt(d);
-    Gm[j][j] = d;
-    for (int i = j + 1; i < n; ++i) {
-      double s = Gm[i][j];
-      for (int k = 0; k < j; ++k) s -= Gm[i][k] * Gm[j][k];
-      Gm[i][j] = s / d;
-    }
-  }
-  for (int i = 0; i < n; ++i) { double s = c[i]; for (int k = 0; k < i; ++k) s -= Gm[i][k] * c[k]; c[i] = s / Gm[i][i]; }
-  for (int i = n - 1; i >= 0; --i) { double s = c[i]; for (int k = i + 1; k < n; ++k) s -= Gm[k][i] * c[k]; c[i] = s / Gm[i][i]; }
-  for (int i = 0; i < n; ++i) delta[B.n_pad + i] = c[i];
-  delta[B.n_pad + kRhsRow] = 0.0;
-}
-
-// x = L^-T (y - Lb^T z): single CTA, block columns from last to first.  delta[0..n_pad) receives x.
-__global__ void __launch_bounds__(256) k_band_backsolve(BandLayout B, double* __restrict__ delta) {
-  __shared__ double part[8][kNB];
-  __shared__ double z[GT_SIZE];
-  const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
-  const int nb1 = B.nbw + 1;
-  if (tid < GT_SIZE) z[tid] = delta[B.n_pad + tid];
-  __syncthreads();
-  for (int j = B.nbc - 1; j >= 0; --j) {
-    // partial sums over the rows of the sub-diagonal blocks: sum_i sum_r L(i,j)[r][c] x_i[r]
-    double s = 0.0;
-    const int nrows = min(B.nbw, B.nbc - 1 - j);
-    for (int bi = 1; bi <= nrows; ++bi) {
-      const double* Lij = B.band + ((size_t)j * nb1 + bi) * 1024;
-      const double* xi = delta + (size_t)(j + bi) * kNB;
-#pragma unroll
-      for (int q = 0; q < 4; ++q) { const int r = ty * 4 + q; s += Lij[r * 32 + tx] * xi[r]; }
-    }
-    part[ty][tx] = s;
-    __syncthreads();
-    if (ty == 0) {
-      const int c = j * kNB + tx;
-      double t = B.border[(size_t)kRhsRow * B.n_pad + c];
-      for (int g = 0; g < GT_SIZE; ++g) t -= B.border[(size_t)g * B.n_pad + c] * z[g];
-      for (int q = 0; q < 8; ++q) t -= part[q][tx];
-      // upper-triangular solve with Ljj^T inside the warp
-      const double* Ljj = B.band + ((size_t)j * nb1) * 1024;
-      double x = 0.0;
-      for (int m = kNB - 1; m >= 0; --m) {
-        const double diag = Ljj[m * 32 + m];
-        const double tm = __shfl_sync(0xffffffffu, t, m);
-        const double xm = tm / diag;
-        if (tx == m) x = xm;
-        if (tx < m) t -= Ljj[m * 32 + tx] * xm;
-      }
-      delta[c] = x;
-    }
-    __syncthreads();
-  }
-}
-
-int band_factor_solve(ctba_problem* p) {
-  SolverData* sd = p->solver;
-  cudaStream_t st = p->stream;
-  BandLayout& B = sd->Hw;
-  CTBA_CUDA(p, cudaMemsetAsync(sd->flag.p, 0, 4 * sizeof(int32_t), st));
-  for (int j = 0; j < B.nbc; ++j) {
-    const int nrows = std::min(B.nbw, B.nbc - 1 - j);
-    k_band_column<<<nrows + 2, 256, 0, st>>>(B, j, sd->flag.p);
-  }
-  p->launches += B.nbc;
-  const int nblk = cdiv(B.n_pad, 256);
-  DBuf<double>& scratch = sd->dpose;  // reuse? no: keep a dedicated region at the end of scal
-  (void)scratch;
-  double* partial = sd->Sb.p;  // F*42 doubles are free again after k_pose_to_knots; need nblk*256
-  if ((size_t)nblk * 256 > sd->Sb.n) { CTBA_CUDA(p, sd->Sb.resize((size_t)nblk * 256)); partial = sd->Sb.p; }
-  k_corner_partial<<<nblk, 256, 0, st>>>(B, partial);
-  k_corner_solve<<<1, 256, 0, st>>>(B, nblk, partial, sd->delta.p, sd->flag.p);
-  k_band_backsolve<<<1, 256, 0, st>>>(B, sd->delta.p);
-  p->launches += 3;
-  CTBA_CUDA(p, cudaGetLastError());
-  return CTBA_OK;
-}
-
 void solver_free(SolverData* sd) {
   if (!sd) return;
   DBuf<double>* dd[] = {&sd->band0, &sd->bandw, &sd->border0, &sd->borderw, &sd->corner0, &sd->cornerw, &sd->grad, &sd->V0, &sd->gl, &sd->Sp, &sd->Sb,
-                        &sd->rp, &sd->jscale, &sd->jscale_lm, &sd->delta, &sd->delta_lm, &sd->dpose, &sd->scal, &sd->cand.knot_q, &sd->cand.knot_p,
+                        &sd->rp, &sd->dinv, &sd->jscale, &sd->jscale_lm, &sd->delta, &sd->delta_lm, &sd->dpose, &sd->scal, &sd->cand.knot_q, &sd->cand.knot_p,
                         &sd->cand.bias_a, &sd->cand.bias_g, &sd->cand.lm, &sd->cand.glb};
   for (auto* d : dd) d->release();
   DBuf<int32_t>* di[] = {&sd->d_node_of_knot, &sd->d_node_of_bias, &sd->d_lm_obs_begin, &sd->d_lm_obs, &sd->flag};

@@ -57,6 +57,7 @@ struct SolverData {
   DBuf<double> jscale, jscale_lm;   // Jacobi scaling (fixed per Solve): n_pad+16, 3L
   DBuf<double> delta, delta_lm;     // step: n_pad+16, 3L
   DBuf<double> dpose;               // per frame 6: pose-space step
+  DBuf<double> dinv;                // nbc x 32x32: L_jj^-1 of every diagonal block (backward substitution)
   DBuf<double> scal;                // small scalar outputs (see SC_* in ctba_solve.cu)
   DBuf<int32_t> flag;               // numeric failure flag
   DeviceState cand;
