@@ -805,6 +805,7 @@ static GMask make_gmask(const SolverData* sd) { GMask g; for (int i = 0; i < GT_
 int assemble_structure(ctba_problem* p) {
   if (!p->solver) p->solver = new SolverData();
   SolverData* sd = p->solver;
+  band_graph_release(sd);   // the captured launch sequence refers to the old structure / buffers
   const int N = p->N;
   const int K = (int)p->numKnots(), F = (int)p->numFrames(), M = (int)p->numObs(), L = (int)(p->lm.size() / 3);
   const bool has_imu = !p->i_s.empty() || !p->b_s0.empty();

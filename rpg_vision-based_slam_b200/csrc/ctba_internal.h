@@ -77,6 +77,8 @@ struct ctba_problem {
   double q_bc0[4] = {0, 0, 0, 1}, p_bc0[3] = {0, 0, 0};
   double cauchy_a = 3.0;
   bool bench_no_termination = false;
+  int band_pdl = 2;        // programmatic dependent launch between the block-column kernels (0 off, 1 trigger at entry, 2 after staging)
+  bool band_graph = true;  // replay the factor+solve launch sequence as a CUDA graph
 
   // ---- host work items ----
   std::vector<int32_t> f_s, f_obs_begin{0};
