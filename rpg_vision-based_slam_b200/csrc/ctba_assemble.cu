@@ -5,8 +5,8 @@
 // frame pose record and the landmark.  With A_o = w_f^2 Jl^T Jl (3x3), b_o = w_f^2 Jl^T r:
 //   landmark block   V_l = sum_o A_o,             g_l = sum_o b_o
 //   pose-space block Q_f = sum_o X_o^T A_o X_o,   q_f = sum_o X_o^T b_o          (k_frame_direct -> knot space via the chain D_f)
-//   Schur            S(f,f') -= (A_o X_o)^T (V_l + D_l)^-1 (A_o' X_o')             (k_landmark_schur, warp per landmark, shuffles)
-//   knot space       H(win f, win f') += D_f^T S(f,f') D_f'                       (k_pose_to_knots)
+//   Schur            S(f,f') = - sum_l (A_o X_o)^T (V_l + D_l)^-1 (A_o' X_o')        (k_lm_prepare, k_obs_yz, k_frame_schur: gather, no atomics)
+//   knot space       H(k, k') += sum_{f ni k, f' ni k'} D_f[k]^T S(f,f') D_f'[k']   (k_knot_schur, k_knot_border: one writer per entry)
 // IMU / GP / bias / gravity rows are dense local Jacobians and go straight into the band (k_rows_accumulate).
 // Replaces Ceres' J^T J formation + elimination inside SPARSE_NORMAL_CHOLESKY; LossFunction corrector
 // (CauchyLoss(3.0) per frame, bspline_so3r3.h:1032) enters as the per-frame weight w_f = sqrt(rho').
@@ -270,262 +270,385 @@ __global__ void __launch_bounds__(128) k_rows_accumulate(int kind, int n, int wi
   }
 }
 
-// ---- Schur complement of the landmarks in pose space: warp per landmark -----------------------------------------
-// Sp[(f*(T+1)+df)*36 + 6*m + n] : block (rows pose f, cols pose f+df);  Sb[f*42 + 7*m + g] : pose f x reprojection globals;
-// rp[f*6+m] : pose-space right-hand-side correction;  corner/grad-global corrections go straight to Hw / rhs.
-template <int N>
-__global__ void __launch_bounds__(128) k_landmark_schur(const __grid_constant__ Globals G, const double* __restrict__ glb,
-                                                        const FramePose<N>* __restrict__ fps, const double* __restrict__ lm, int L,
-                                                        const int32_t* __restrict__ lm_obs_begin, const int32_t* __restrict__ lm_obs,
-                                                        const int32_t* __restrict__ o_frame, const double* __restrict__ Jl,
-                                                        const double2* __restrict__ r, const double* __restrict__ f_w, int M,
-                                                        const double* __restrict__ V0, const double* __restrict__ gl,
-                                                        const double* __restrict__ jscale_lm, double radius, int T, GMask gm,
-                                                        double* __restrict__ Sp, double* __restrict__ Sb, double* __restrict__ rp, BandLayout Hw,
-                                                        double* __restrict__ rhs_glob /* 7 */) {
-  const int l = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (l >= L) return;
-  const int b0 = lm_obs_begin[l], t = lm_obs_begin[l + 1] - b0;
-  if (t == 0) return;
-  // damped landmark block and its inverse
-  double V[6], Vi[6], g[3];
+// ---- Schur complement of the landmarks, gather formulation (no atomics, bitwise reproducible) ------------------------------------
+//   k_lm_prepare   thread per landmark : damped V_l, Vi = V_l^-1, vig = Vi g_l; with free reprojection globals also Yg_l = sum_o A_o Xg_o,
+//                                        ViYg_l, and per-block partials of the global x global corner / right-hand side
+//   k_obs_yz       thread per obs      : Y_o = A_o X_o[:, pose 6] (3x6) and Z_o = Vi_l Y_o, AoS 18 doubles each
+//   k_frame_schur  CTA per frame f     : Sp(f, df) = - sum over landmarks seen in f and f+df of Y_a^T Z_b   (warp per df, lanes over the
+//                                        frame's observations, partner found through the landmark's observation list);
+//                                        rp(f) = - sum_a Y_a^T vig, Sb(f) = - sum_a Y_a^T ViYg   (pose x reprojection globals)
+//   k_knot_schur   warp per (knot, dk) : 6x6 knot block  += sum_{f ni k, f' ni k-dk} D_f[k]^T Sfull(f,f') D_f'[k-dk], written by one thread
+//   k_knot_border  thread per knot dof : border rows and right-hand side  D_f[k]^T Sb(f), D_f[k]^T rp(f)
+// Layouts: Sp[(f*(T+1)+df)*36 + 6*m + n] rows pose f, cols pose f+df (df = 0: full symmetric block); Sb[f*42 + 7*m + g]; rp[f*6 + m].
+struct LmPrep { double Vi[6], vig[3]; };
+
+__device__ __forceinline__ void landmark_inverse(const double* __restrict__ V0, const double* __restrict__ jscale_lm, double radius, int l, double Vi[6]) {
+  double V[6];
 #pragma unroll
   for (int c = 0; c < 6; ++c) V[c] = V0[6 * (size_t)l + c];
+  const int di[3] = {0, 3, 5};
 #pragma unroll
-  for (int c = 0; c < 3; ++c) g[c] = gl[3 * (size_t)l + c];
-  {
-    const int di[3] = {0, 3, 5};
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      const double sc = jscale_lm[3 * (size_t)l + c];
-      double dd = V[di[c]] * sc * sc;
-      dd = fmin(fmax(dd, 1e-6), 1e32);
-      V[di[c]] += dd / (radius * sc * sc);
-    }
-    const double c00 = V[3] * V[5] - V[4] * V[4], c01 = V[2] * V[4] - V[1] * V[5], c02 = V[1] * V[4] - V[2] * V[3];
-    const double det = V[0] * c00 + V[1] * c01 + V[2] * c02, id = 1.0 / det;
-    Vi[0] = c00 * id; Vi[1] = c01 * id; Vi[2] = c02 * id;
-    Vi[3] = (V[0] * V[5] - V[2] * V[2]) * id; Vi[4] = (V[1] * V[2] - V[0] * V[4]) * id; Vi[5] = (V[0] * V[3] - V[1] * V[1]) * id;
+  for (int c = 0; c < 3; ++c) {
+    const double sc = jscale_lm[3 * (size_t)l + c];
+    double dd = V[di[c]] * sc * sc;
+    dd = fmin(fmax(dd, 1e-6), 1e32);
+    V[di[c]] += dd / (radius * sc * sc);
   }
-  double vig[3];
-  symmul3(Vi, g, vig);
-  v3 pw{lm[3 * (size_t)l], lm[3 * (size_t)l + 1], lm[3 * (size_t)l + 2]};
-  double Yg_sum[3][7];  // sum over observations of the global part of Y (all lanes end with the full sum)
-#pragma unroll
-  for (int a = 0; a < 3; ++a)
-#pragma unroll
-    for (int c = 0; c < 7; ++c) Yg_sum[a][c] = 0.0;
+  const double c00 = V[3] * V[5] - V[4] * V[4], c01 = V[2] * V[4] - V[1] * V[5], c02 = V[1] * V[4] - V[2] * V[3];
+  const double det = V[0] * c00 + V[1] * c01 + V[2] * c02, id = 1.0 / det;
+  Vi[0] = c00 * id; Vi[1] = c01 * id; Vi[2] = c02 * id;
+  Vi[3] = (V[0] * V[5] - V[2] * V[2]) * id; Vi[4] = (V[1] * V[2] - V[0] * V[4]) * id; Vi[5] = (V[0] * V[3] - V[1] * V[1]) * id;
+}
 
-  for (int base = 0; base < t; base += 32) {   // chunk of "row" observations
-    const int oi = base + lane;
-    const bool have = oi < t;
-    int f = 0;
-    double Yp[3][6], Yg[3][7];
+constexpr int kCornerVals = 28 + 7;   // lower triangle of the 7x7 global block + 7 right-hand-side entries
+template <int N>
+__global__ void __launch_bounds__(128) k_lm_prepare(const __grid_constant__ Globals G, const double* __restrict__ glb,
+                                                    const FramePose<N>* __restrict__ fps, const double* __restrict__ lm, int L,
+                                                    const int32_t* __restrict__ lm_obs_begin, const int32_t* __restrict__ lm_obs,
+                                                    const int32_t* __restrict__ o_frame, const double* __restrict__ Jl,
+                                                    const double2* __restrict__ r, const double* __restrict__ f_w, int M,
+                                                    const double* __restrict__ V0, const double* __restrict__ gl,
+                                                    const double* __restrict__ jscale_lm, double radius, GMask gm, bool any_g,
+                                                    double* __restrict__ Vi_out /*6L*/, double* __restrict__ vig_out /*3L*/,
+                                                    double* __restrict__ ViYg_out /*21L*/, double* __restrict__ corner_partial /*grid x 35*/) {
+  __shared__ double red[4][kCornerVals];
+  const int l = blockIdx.x * blockDim.x + threadIdx.x;
+  double cv[kCornerVals];
 #pragma unroll
-    for (int a = 0; a < 3; ++a) {
+  for (int e = 0; e < kCornerVals; ++e) cv[e] = 0.0;
+  if (l < L && lm_obs_begin[l + 1] > lm_obs_begin[l]) {
+    double Vi[6], g[3], vig[3];
+    landmark_inverse(V0, jscale_lm, radius, l, Vi);
 #pragma unroll
-      for (int c = 0; c < 6; ++c) Yp[a][c] = 0.0;
+    for (int c = 0; c < 3; ++c) g[c] = gl[3 * (size_t)l + c];
+    symmul3(Vi, g, vig);
 #pragma unroll
-      for (int c = 0; c < 7; ++c) Yg[a][c] = 0.0;
-    }
-    if (have) {
-      const int o = lm_obs[b0 + oi];
-      f = o_frame[o];
-      double X[3][13], A[6], b[3];
-      obs_X<N>(G, glb, fps[f], pw, X);
-      obs_Ab(Jl, r, f_w, M, o, f, A, b);
+    for (int c = 0; c < 6; ++c) Vi_out[6 * (size_t)l + c] = Vi[c];
 #pragma unroll
-      for (int c = 0; c < 13; ++c) {
-        const double x[3] = {X[0][c], X[1][c], X[2][c]};
-        double y[3];
-        symmul3(A, x, y);
-        if (c < 6) { Yp[0][c] = y[0]; Yp[1][c] = y[1]; Yp[2][c] = y[2]; }
-        else { Yg[0][c - 6] = y[0]; Yg[1][c - 6] = y[1]; Yg[2][c - 6] = y[2]; }
-      }
-      // right-hand side (pose part): rp(f) -= Yp^T Vi g_l
-#pragma unroll
-      for (int c = 0; c < 6; ++c) atomicAdd(rp + 6 * (size_t)f + c, -(Yp[0][c] * vig[0] + Yp[1][c] * vig[1] + Yp[2][c] * vig[2]));
-    }
-    // accumulate the global-part sum over this chunk (warp reduction, every lane gets it)
-#pragma unroll
-    for (int a = 0; a < 3; ++a)
-#pragma unroll
-      for (int c = 0; c < 7; ++c) {
-        double v = Yg[a][c];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        Yg_sum[a][c] += v;
-      }
-    // pairs (row obs in this chunk) x (col obs in chunk cb >= base)
-    for (int cb = base; cb < t; cb += 32) {
-      // column-side data: Z = Vi * Yp of observation cb+lane, and its frame
-      int f2 = 0;
-      double Zp[3][6];
+    for (int c = 0; c < 3; ++c) vig_out[3 * (size_t)l + c] = vig[c];
+    if (any_g) {
+      v3 pw{lm[3 * (size_t)l], lm[3 * (size_t)l + 1], lm[3 * (size_t)l + 2]};
+      double Yg[3][7];
 #pragma unroll
       for (int a = 0; a < 3; ++a)
 #pragma unroll
-        for (int c = 0; c < 6; ++c) Zp[a][c] = 0.0;
-      const int oj = cb + lane;
-      if (cb == base) {
-        f2 = f;
-#pragma unroll
-        for (int c = 0; c < 6; ++c) {
-          const double y[3] = {Yp[0][c], Yp[1][c], Yp[2][c]};
-          double z[3];
-          symmul3(Vi, y, z);
-          Zp[0][c] = z[0]; Zp[1][c] = z[1]; Zp[2][c] = z[2];
-        }
-      } else if (oj < t) {
-        const int o = lm_obs[b0 + oj];
-        f2 = o_frame[o];
+        for (int c = 0; c < 7; ++c) Yg[a][c] = 0.0;
+      for (int i = lm_obs_begin[l]; i < lm_obs_begin[l + 1]; ++i) {
+        const int o = lm_obs[i], f = o_frame[o];
         double X[3][13], A[6], b[3];
-        obs_X<N>(G, glb, fps[f2], pw, X);
-        obs_Ab(Jl, r, f_w, M, o, f2, A, b);
+        obs_X<N>(G, glb, fps[f], pw, X);
+        obs_Ab(Jl, r, f_w, M, o, f, A, b);
 #pragma unroll
-        for (int c = 0; c < 6; ++c) {
-          const double x[3] = {X[0][c], X[1][c], X[2][c]};
-          double y[3], z[3];
+        for (int c = 0; c < 7; ++c) {
+          const double x[3] = {X[0][6 + c], X[1][6 + c], X[2][6 + c]};
+          double y[3];
           symmul3(A, x, y);
-          symmul3(Vi, y, z);
-          Zp[0][c] = z[0]; Zp[1][c] = z[1]; Zp[2][c] = z[2];
+          Yg[0][c] += y[0]; Yg[1][c] += y[1]; Yg[2][c] += y[2];
         }
       }
-      const int kstart = 0;
-      for (int k = kstart; k < 32; ++k) {
-        // lane pairs with column lane (lane + k) & 31
-        const int src = (lane + k) & 31;
-        const int oj2 = cb + src;
-        const int fj = __shfl_sync(0xffffffffu, f2, src);
-        double Z[3][6];
+      double ViYg[3][7];
 #pragma unroll
-        for (int a = 0; a < 3; ++a)
+      for (int c = 0; c < 7; ++c) {
+        const double y[3] = {Yg[0][c], Yg[1][c], Yg[2][c]};
+        double z[3];
+        symmul3(Vi, y, z);
+        ViYg[0][c] = gm.a[c] ? z[0] : 0.0; ViYg[1][c] = gm.a[c] ? z[1] : 0.0; ViYg[2][c] = gm.a[c] ? z[2] : 0.0;
 #pragma unroll
-          for (int c = 0; c < 6; ++c) Z[a][c] = __shfl_sync(0xffffffffu, Zp[a][c], src);
-        // ordered pair: require (global obs index of row) <= (global obs index of col)
-        if (!have || oj2 >= t || oj2 < oi) continue;
-        int fr = f, fc = fj;
-        const bool same_obs = (oj2 == oi);
-        // block B[m][n] = - sum_a Yp[a][m] Z[a][n]   (rows: pose of row obs, cols: pose of col obs)
-        if (fc >= fr) {
-          double* dst = Sp + ((size_t)fr * (T + 1) + (fc - fr)) * 36;
-          const bool dup_frame = (!same_obs && fc == fr);
-#pragma unroll
-          for (int m = 0; m < 6; ++m)
-#pragma unroll
-            for (int n = 0; n < 6; ++n) {
-              double v = -(Yp[0][m] * Z[0][n] + Yp[1][m] * Z[1][n] + Yp[2][m] * Z[2][n]);
-              if (dup_frame) v += -(Yp[0][n] * Z[0][m] + Yp[1][n] * Z[1][m] + Yp[2][n] * Z[2][m]);
-              atomicAdd(dst + 6 * m + n, v);
-            }
-        } else {  // observation list not frame-sorted: store the transposed block
-          double* dst = Sp + ((size_t)fc * (T + 1) + (fr - fc)) * 36;
-#pragma unroll
-          for (int m = 0; m < 6; ++m)
-#pragma unroll
-            for (int n = 0; n < 6; ++n) atomicAdd(dst + 6 * n + m, -(Yp[0][m] * Z[0][n] + Yp[1][m] * Z[1][n] + Yp[2][m] * Z[2][n]));
-        }
+        for (int a = 0; a < 3; ++a) ViYg_out[21 * (size_t)l + 7 * a + c] = ViYg[a][c];
       }
-    }
-    // pose x globals border needs the complete Yg_sum: done in a second sweep below
-  }
-  // second sweep: Sb(f) -= Yp^T Vi Yg_sum ; (global x global) and global rhs by lane 0
-  double ViYg[3][7];
-#pragma unroll
-  for (int c = 0; c < 7; ++c) {
-    const double y[3] = {Yg_sum[0][c], Yg_sum[1][c], Yg_sum[2][c]};
-    double z[3];
-    symmul3(Vi, y, z);
-    ViYg[0][c] = z[0]; ViYg[1][c] = z[1]; ViYg[2][c] = z[2];
-  }
-  bool any_g = false;
-#pragma unroll
-  for (int c = 0; c < 7; ++c) any_g |= gm.a[c] != 0;
-  if (any_g) {
-    for (int oi = lane; oi < t; oi += 32) {
-      const int o = lm_obs[b0 + oi];
-      const int f = o_frame[o];
-      double X[3][13], A[6], b[3];
-      obs_X<N>(G, glb, fps[f], pw, X);
-      obs_Ab(Jl, r, f_w, M, o, f, A, b);
-#pragma unroll
-      for (int m = 0; m < 6; ++m) {
-        const double x[3] = {X[0][m], X[1][m], X[2][m]};
-        double y[3];
-        symmul3(A, x, y);
-#pragma unroll
-        for (int c = 0; c < 7; ++c)
-          if (gm.a[c]) atomicAdd(Sb + (size_t)f * 42 + 7 * m + c, -(y[0] * ViYg[0][c] + y[1] * ViYg[1][c] + y[2] * ViYg[2][c]));
-      }
-    }
-    if (lane == 0) {
+      int e = 0;
 #pragma unroll
       for (int a = 0; a < 7; ++a) {
-        if (!gm.a[a]) continue;
 #pragma unroll
-        for (int c = 0; c <= a; ++c) {
-          if (!gm.a[c]) continue;
-          atomicAdd(Hw.corner + a * kBorder + c, -(Yg_sum[0][a] * ViYg[0][c] + Yg_sum[1][a] * ViYg[1][c] + Yg_sum[2][a] * ViYg[2][c]));
-        }
-        atomicAdd(rhs_glob + a, -(Yg_sum[0][a] * vig[0] + Yg_sum[1][a] * vig[1] + Yg_sum[2][a] * vig[2]));
+        for (int c = 0; c <= a; ++c) { cv[e] = gm.a[a] ? -(Yg[0][a] * ViYg[0][c] + Yg[1][a] * ViYg[1][c] + Yg[2][a] * ViYg[2][c]) : 0.0; ++e; }
       }
+#pragma unroll
+      for (int a = 0; a < 7; ++a) cv[28 + a] = gm.a[a] ? -(Yg[0][a] * vig[0] + Yg[1][a] * vig[1] + Yg[2][a] * vig[2]) : 0.0;
+    }
+  }
+  if (!any_g) return;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+#pragma unroll
+  for (int e = 0; e < kCornerVals; ++e) {
+    double v = cv[e];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) red[wib][e] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < kCornerVals) corner_partial[(size_t)blockIdx.x * kCornerVals + threadIdx.x] = (red[0][threadIdx.x] + red[1][threadIdx.x]) + (red[2][threadIdx.x] + red[3][threadIdx.x]);
+}
+
+// corner / global right-hand side: deterministic sum of the per-block partials (one CTA)
+__global__ void __launch_bounds__(64) k_corner_reduce(int nblk, const double* __restrict__ partial, BandLayout Hw, double* __restrict__ rhs_glob) {
+  const int e = threadIdx.x;
+  if (e >= kCornerVals) return;
+  double s = 0.0;
+  for (int b = 0; b < nblk; ++b) s += partial[(size_t)b * kCornerVals + e];
+  if (e < 28) {
+    int a = 0;
+    while ((a + 1) * (a + 2) / 2 <= e) ++a;
+    const int c = e - a * (a + 1) / 2;
+    Hw.corner[a * kBorder + c] += s;
+  } else {
+    rhs_glob[e - 28] += s;
+  }
+}
+
+template <int N>
+__global__ void __launch_bounds__(128) k_obs_yz(const __grid_constant__ Globals G, const double* __restrict__ glb, const FramePose<N>* __restrict__ fps,
+                                                const double* __restrict__ lm, int M, const int32_t* __restrict__ o_frame,
+                                                const int32_t* __restrict__ o_lm, const double* __restrict__ Jl, const double2* __restrict__ r,
+                                                const double* __restrict__ f_w, const double* __restrict__ Vi_all, double* __restrict__ Y_out,
+                                                double* __restrict__ Z_out) {
+  const int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= M) return;
+  const int f = o_frame[o], l = o_lm[o];
+  v3 pw{lm[3 * (size_t)l], lm[3 * (size_t)l + 1], lm[3 * (size_t)l + 2]};
+  double X[3][13], A[6], b[3], Vi[6];
+  obs_X<N>(G, glb, fps[f], pw, X);
+  obs_Ab(Jl, r, f_w, M, o, f, A, b);
+#pragma unroll
+  for (int c = 0; c < 6; ++c) Vi[c] = Vi_all[6 * (size_t)l + c];
+  double2* Yo = reinterpret_cast<double2*>(Y_out + 18 * (size_t)o);
+  double2* Zo = reinterpret_cast<double2*>(Z_out + 18 * (size_t)o);
+  double Y[18], Z[18];
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    const double x[3] = {X[0][c], X[1][c], X[2][c]};
+    double y[3], z[3];
+    symmul3(A, x, y);
+    symmul3(Vi, y, z);
+    Y[c] = y[0]; Y[6 + c] = y[1]; Y[12 + c] = y[2];     // Y[a*6 + c]
+    Z[c] = z[0]; Z[6 + c] = z[1]; Z[12 + c] = z[2];
+  }
+#pragma unroll
+  for (int e = 0; e < 9; ++e) { Yo[e] = make_double2(Y[2 * e], Y[2 * e + 1]); Zo[e] = make_double2(Z[2 * e], Z[2 * e + 1]); }
+}
+
+constexpr int kFsThreads = 256;
+__global__ void __launch_bounds__(kFsThreads) k_frame_schur(int F, int T, const int32_t* __restrict__ obs_begin, const int32_t* __restrict__ o_lm,
+                                                            const int32_t* __restrict__ o_frame, const int32_t* __restrict__ o_pos,
+                                                            const int32_t* __restrict__ lm_obs_begin, const int32_t* __restrict__ lm_obs,
+                                                            const double* __restrict__ Yall, const double* __restrict__ Zall,
+                                                            const double* __restrict__ vig_all, const double* __restrict__ ViYg_all, bool any_g,
+                                                            double* __restrict__ Sp, double* __restrict__ Sb, double* __restrict__ rp) {
+  __shared__ double red[kFsThreads / 32][48];
+  const int f = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b0 = obs_begin[f], n = obs_begin[f + 1] - b0;
+  // ---- pose right-hand side and pose x globals block: threads over the frame's observations ----
+  {
+    double acc[48];
+#pragma unroll
+    for (int e = 0; e < 48; ++e) acc[e] = 0.0;
+    for (int i = threadIdx.x; i < n; i += kFsThreads) {
+      const int a = b0 + i, l = o_lm[a];
+      const double* Y = Yall + 18 * (size_t)a;
+      const double v0 = vig_all[3 * (size_t)l], v1 = vig_all[3 * (size_t)l + 1], v2 = vig_all[3 * (size_t)l + 2];
+      double y[18];
+#pragma unroll
+      for (int e = 0; e < 18; ++e) y[e] = Y[e];
+#pragma unroll
+      for (int m = 0; m < 6; ++m) acc[m] -= y[m] * v0 + y[6 + m] * v1 + y[12 + m] * v2;
+      if (any_g) {
+        const double* W = ViYg_all + 21 * (size_t)l;
+#pragma unroll
+        for (int g = 0; g < 7; ++g) {
+          const double w0 = W[g], w1 = W[7 + g], w2 = W[14 + g];
+#pragma unroll
+          for (int m = 0; m < 6; ++m) acc[6 + 7 * m + g] -= y[m] * w0 + y[6 + m] * w1 + y[12 + m] * w2;
+        }
+      }
+    }
+    const int nv = any_g ? 48 : 6;
+#pragma unroll
+    for (int e = 0; e < 48; ++e) {
+      if (e < nv) {
+        double v = acc[e];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) red[warp][e] = v;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < nv) {
+      double v = 0.0;
+#pragma unroll
+      for (int w = 0; w < kFsThreads / 32; ++w) v += red[w][threadIdx.x];
+      if (threadIdx.x < 6) rp[6 * (size_t)f + threadIdx.x] = v;
+      else Sb[42 * (size_t)f + (threadIdx.x - 6)] = v;
+    }
+    if (!any_g && threadIdx.x < 42) Sb[42 * (size_t)f + threadIdx.x] = 0.0;
+  }
+  // ---- pose-space blocks: warp per frame distance ----
+  for (int df = warp; df <= T; df += kFsThreads / 32) {
+    const int f2 = f + df;
+    double acc[36];
+#pragma unroll
+    for (int e = 0; e < 36; ++e) acc[e] = 0.0;
+    if (f2 < F) {
+      for (int i = lane; i < n; i += 32) {
+        const int a = b0 + i, l = o_lm[a];
+        const int lend = lm_obs_begin[l + 1];
+        int pos = o_pos[a];                       // position of a in the landmark's (frame-ordered) observation list
+        bool loaded = false;
+        double y[18];
+        for (; pos < lend; ++pos) {
+          const int b = lm_obs[pos];
+          const int fb = o_frame[b];
+          if (fb > f2) break;
+          if (fb < f2) continue;
+          if (!loaded) {
+            const double2* Y = reinterpret_cast<const double2*>(Yall + 18 * (size_t)a);
+#pragma unroll
+            for (int e = 0; e < 9; ++e) { const double2 v = Y[e]; y[2 * e] = v.x; y[2 * e + 1] = v.y; }
+            loaded = true;
+          }
+          const double2* Zp = reinterpret_cast<const double2*>(Zall + 18 * (size_t)b);
+          double z[18];
+#pragma unroll
+          for (int e = 0; e < 9; ++e) { const double2 v = Zp[e]; z[2 * e] = v.x; z[2 * e + 1] = v.y; }
+          const bool dup = (b != a) && df == 0;    // a second observation of the landmark in the same frame: add the transposed product too
+#pragma unroll
+          for (int m = 0; m < 6; ++m)
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+              double v = y[m] * z[c] + y[6 + m] * z[6 + c] + y[12 + m] * z[12 + c];
+              if (dup) v += y[c] * z[m] + y[6 + c] * z[6 + m] + y[12 + c] * z[12 + m];
+              acc[6 * m + c] += v;
+            }
+        }
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < 36; ++e) {
+      double v = acc[e];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      acc[e] = v;
+    }
+    double* dst = Sp + ((size_t)f * (T + 1) + df) * 36;
+#pragma unroll
+    for (int e = 0; e < 36; ++e) if (lane == e % 32 && (e < 32 || lane < 4)) dst[e] = -acc[e];
+  }
+}
+
+// D_f[k]^T S D_f'[k'] for one frame pair; i / i2 = local knot indices inside the two windows
+template <int N>
+__device__ __forceinline__ void chain_block_acc(const FramePose<N>& fa, int i, const FramePose<N>& fb, int i2, const double* S /*36, [m][n]*/, bool transpose,
+                                                double C[36]) {
+  const double* Ca = fa.Crot[i];
+  const double* Cb = fb.Crot[i2];
+  const double ca = fa.cpos[i], cb = fb.cpos[i2];
+  double Sm[36];
+#pragma unroll
+  for (int m = 0; m < 6; ++m)
+#pragma unroll
+    for (int n = 0; n < 6; ++n) Sm[6 * m + n] = transpose ? S[6 * n + m] : S[6 * m + n];
+  // T = S * Db : columns 0..2 = S[:,0:3] * Cb, columns 3..5 = cb * S[:,3:6]
+  double Tm[36];
+#pragma unroll
+  for (int m = 0; m < 6; ++m) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      Tm[6 * m + c] = Sm[6 * m] * Cb[c] + Sm[6 * m + 1] * Cb[3 + c] + Sm[6 * m + 2] * Cb[6 + c];
+      Tm[6 * m + 3 + c] = cb * Sm[6 * m + 3 + c];
+    }
+  }
+  // C += Da^T * T : rows 0..2 = Ca^T T[0:3,:], rows 3..5 = ca * T[3:6,:]
+#pragma unroll
+  for (int a = 0; a < 3; ++a)
+#pragma unroll
+    for (int n = 0; n < 6; ++n) {
+      C[6 * a + n] += Ca[a] * Tm[n] + Ca[3 + a] * Tm[6 + n] + Ca[6 + a] * Tm[12 + n];
+      C[6 * (3 + a) + n] += ca * Tm[6 * (3 + a) + n];
+    }
+}
+
+template <int N>
+__global__ void __launch_bounds__(128) k_knot_schur(const FramePose<N>* __restrict__ fps, int K, int KD, int T, const int32_t* __restrict__ f_s,
+                                                    const int32_t* __restrict__ kf_begin, const int32_t* __restrict__ kf_list,
+                                                    const int32_t* __restrict__ node_of_knot, const double* __restrict__ Sp, BandLayout Hw) {
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (w >= K * (KD + 1)) return;
+  const int kr = w / (KD + 1), dk = w % (KD + 1);
+  const int kc = kr - dk;
+  if (kc < 0) return;
+  const int rb = kf_begin[kr], nr = kf_begin[kr + 1] - rb;
+  const int cb = kf_begin[kc], nc = kf_begin[kc + 1] - cb;
+  if (nr == 0 || nc == 0) return;
+  double C[36];
+#pragma unroll
+  for (int e = 0; e < 36; ++e) C[e] = 0.0;
+  bool any = false;
+  for (int idx = lane; idx < nr * nc; idx += 32) {
+    const int f = kf_list[rb + idx / nc], f2 = kf_list[cb + idx % nc];
+    const int d = f2 - f;
+    if (d > T || -d > T) continue;
+    const double* S = Sp + ((size_t)(d >= 0 ? f : f2) * (T + 1) + (d >= 0 ? d : -d)) * 36;
+    double Sl[36];
+    const double2* S2 = reinterpret_cast<const double2*>(S);
+#pragma unroll
+    for (int e = 0; e < 18; ++e) { const double2 v = S2[e]; Sl[2 * e] = v.x; Sl[2 * e + 1] = v.y; }
+    chain_block_acc<N>(fps[f], kr - f_s[f], fps[f2], kc - f_s[f2], Sl, d < 0, C);
+    any = true;
+  }
+  if (!__any_sync(0xffffffffu, any)) return;
+#pragma unroll
+  for (int e = 0; e < 36; ++e) {
+    double v = C[e];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    C[e] = v;
+  }
+  const int r0 = 6 * node_of_knot[kr], c0 = 6 * node_of_knot[kc];
+#pragma unroll
+  for (int e = 0; e < 36; ++e) {
+    if (lane == e % 32 && (e < 32 || lane < 4)) {
+      const int a = e / 6, c = e % 6;
+      if (dk > 0 || c <= a) Hw.band[band_addr(Hw, r0 + a, c0 + c)] += C[e];
     }
   }
 }
 
-// ---- pose space -> knot space: warp per (frame, df) ---------------------------------------------------------------
+// border rows (pose x globals mapped to knot dofs) and the Schur right-hand-side correction, thread per (knot, dof)
 template <int N>
-__global__ void __launch_bounds__(128) k_pose_to_knots(const FramePose<N>* __restrict__ fps, int F, int T, const int32_t* __restrict__ f_s,
-                                                       const int32_t* __restrict__ node_of_knot, const double* __restrict__ Sp,
-                                                       const double* __restrict__ Sb, const double* __restrict__ rp, GMask gm, BandLayout Hw,
-                                                       double* __restrict__ rhs /* n_pad + 16, gradient-like accumulator */) {
-  __shared__ double shS[4][36];
-  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  if (w >= F * (T + 1)) return;
-  const int f = w / (T + 1), df = w % (T + 1);
-  const int f2 = f + df;
-  if (f2 >= F) return;
-  double* sS = shS[wib];
-  double mx = 0.0;
-  for (int e = lane; e < 36; e += 32) { double v = Sp[(size_t)w * 36 + e]; sS[e] = v; mx = fmax(mx, fabs(v)); }
+__global__ void k_knot_border(const FramePose<N>* __restrict__ fps, int K, const int32_t* __restrict__ f_s, const int32_t* __restrict__ kf_begin,
+                              const int32_t* __restrict__ kf_list, const int32_t* __restrict__ node_of_knot, const double* __restrict__ Sb,
+                              const double* __restrict__ rp, GMask gm, bool any_g, BandLayout Hw, double* __restrict__ rhs) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= 6 * K) return;
+  const int k = t / 6, a = t % 6;
+  double acc[8];
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-  __syncwarp();
-  const FramePose<N>& fa = fps[f];
-  const FramePose<N>& fb = fps[f2];
-  const int sa = f_s[f], sb = f_s[f2];
-  if (mx != 0.0) {
-    for (int e = lane; e < 36 * N * N; e += 32) {
-      const int a = e / (6 * N), c = e % (6 * N);
-      if (df == 0 && c > a) continue;
-      // t[m] = sum_n S[m][n] Dc[n]
-      const int ic = c / 6, cc = c % 6;
-      double t6[6];
+  for (int e = 0; e < 8; ++e) acc[e] = 0.0;
+  for (int j = kf_begin[k]; j < kf_begin[k + 1]; ++j) {
+    const int f = kf_list[j];
+    const FramePose<N>& fp = fps[f];
+    const int i = k - f_s[f];
+    // row a of D_f[k]^T : rot dof a<3 -> Crot[i][:,a] over pose rows 0..2 ; pos dof -> cpos over pose row a
+    if (a < 3) {
+      const double w0 = fp.Crot[i][a], w1 = fp.Crot[i][3 + a], w2 = fp.Crot[i][6 + a];
+      acc[7] += w0 * rp[6 * (size_t)f] + w1 * rp[6 * (size_t)f + 1] + w2 * rp[6 * (size_t)f + 2];
+      if (any_g) {
 #pragma unroll
-      for (int m = 0; m < 6; ++m) {
-        if (cc < 3) t6[m] = sS[6 * m + 0] * fb.Crot[ic][cc] + sS[6 * m + 1] * fb.Crot[ic][3 + cc] + sS[6 * m + 2] * fb.Crot[ic][6 + cc];
-        else t6[m] = sS[6 * m + cc] * fb.cpos[ic];
+        for (int g = 0; g < 7; ++g) acc[g] += w0 * Sb[42 * (size_t)f + g] + w1 * Sb[42 * (size_t)f + 7 + g] + w2 * Sb[42 * (size_t)f + 14 + g];
       }
-      double v = chain_apply_T<N>(fa, a, t6);
-      const int ra = 6 * node_of_knot[sa + a / 6] + a % 6, cb = 6 * node_of_knot[sb + c / 6] + c % 6;
-      if (df != 0 && ra == cb) v *= 2.0;
-      add_sym(Hw, ra, cb, v);
+    } else {
+      const double c = fp.cpos[i];
+      acc[7] += c * rp[6 * (size_t)f + a];
+      if (any_g) {
+#pragma unroll
+        for (int g = 0; g < 7; ++g) acc[g] += c * Sb[42 * (size_t)f + 7 * a + g];
+      }
     }
   }
-  if (df == 0) {
-    // border (pose x reprojection globals) and right-hand side
-    for (int e = lane; e < 6 * N * 7; e += 32) {
-      const int a = e / 7, gcol = e % 7;
-      if (!gm.a[gcol]) continue;
-      double v6[6];
+  const int idx = 6 * node_of_knot[k] + a;
+  rhs[idx] += acc[7];
+  if (any_g) {
 #pragma unroll
-      for (int m = 0; m < 6; ++m) v6[m] = Sb[(size_t)f * 42 + 7 * m + gcol];
-      const double v = chain_apply_T<N>(fa, a, v6);
-      if (v != 0.0) atomicAdd(Hw.border + (size_t)gcol * Hw.n_pad + 6 * node_of_knot[sa + a / 6] + a % 6, v);
-    }
-    for (int a = lane; a < 6 * N; a += 32) {
-      const double v = chain_apply_T<N>(fa, a, rp + 6 * (size_t)f);
-      if (v != 0.0) atomicAdd(rhs + 6 * node_of_knot[sa + a / 6] + a % 6, v);
-    }
+    for (int g = 0; g < 7; ++g) if (gm.a[g]) Hw.border[(size_t)g * Hw.n_pad + idx] += acc[g];
   }
 }
 
@@ -848,7 +971,9 @@ int assemble_structure(ctba_problem* p) {
     std::vector<int32_t> cur(lob.begin(), lob.end() - 1);
     for (int o = 0; o < M; ++o) lobs[cur[p->o_lm[o]]++] = o;
   }
-  int T = 0;
+  std::vector<int32_t> opos(std::max(M, 1), 0);
+  for (int l = 0; l < L; ++l) for (int i = lob[l]; i < lob[l + 1]; ++i) opos[lobs[i]] = i;
+  int T = 0, KD = N - 1;
   for (int l = 0; l < L; ++l) {
     if (lob[l + 1] == lob[l]) continue;
     tl[l] = 1;
@@ -859,12 +984,21 @@ int assemble_structure(ctba_problem* p) {
       smin = std::min(smin, (int)p->f_s[f]); smax = std::max(smax, (int)p->f_s[f]);
     }
     T = std::max(T, fmax_ - fmin);
+    KD = std::max(KD, smax + N - 1 - smin);
     span(sd->node_of_knot[smin], sd->node_of_knot[smax + N - 1]);
   }
   for (int f = 0; f < F; ++f) { const int s = p->f_s[f]; span(sd->node_of_knot[s], sd->node_of_knot[s + N - 1]); for (int j = 0; j < N; ++j) tk[s + j] |= 3; }
   // every SO3 knot carries a local parameterisation in the reference and is therefore part of the program (:378-399)
   for (int k = 0; k < K; ++k) tk[k] |= 1;
-  sd->T = T; sd->hbn = hbn;
+  sd->T = T; sd->hbn = hbn; sd->KD = KD;
+  // knot -> frames whose window contains it (CSR), for the gather kernels
+  std::vector<int32_t> kfb(K + 1, 0), kfl((size_t)std::max(F, 1) * N);
+  for (int f = 0; f < F; ++f) for (int j = 0; j < N; ++j) kfb[p->f_s[f] + j + 1]++;
+  for (int k = 0; k < K; ++k) kfb[k + 1] += kfb[k];
+  {
+    std::vector<int32_t> cur(kfb.begin(), kfb.end() - 1);
+    for (int f = 0; f < F; ++f) for (int j = 0; j < N; ++j) kfl[cur[p->f_s[f] + j]++] = f;
+  }
   // ---- which globals are free (constness set inside add*Measurement)
   const bool anyF = F > 0, anyI = !p->i_s.empty(), anyG = !p->g_s.empty();
   for (int i = 0; i < GT_SIZE; ++i) sd->gactive[i] = 0;
@@ -902,6 +1036,11 @@ int assemble_structure(ctba_problem* p) {
   cudaStream_t st = p->stream;
   CTBA_CUDA(p, sd->d_node_of_knot.upload(sd->node_of_knot, st)); CTBA_CUDA(p, sd->d_node_of_bias.upload(sd->node_of_bias, st));
   CTBA_CUDA(p, sd->d_lm_obs_begin.upload(lob, st)); CTBA_CUDA(p, sd->d_lm_obs.upload(lobs, st));
+  CTBA_CUDA(p, sd->d_o_pos.upload(opos, st)); CTBA_CUDA(p, sd->d_kf_begin.upload(kfb, st)); CTBA_CUDA(p, sd->d_kf_list.upload(kfl, st));
+  CTBA_CUDA(p, sd->Vi.resize(6 * (size_t)std::max(L, 1))); CTBA_CUDA(p, sd->vig.resize(3 * (size_t)std::max(L, 1)));
+  CTBA_CUDA(p, sd->ViYg.resize(21 * (size_t)std::max(L, 1)));
+  CTBA_CUDA(p, sd->Yo.resize(18 * (size_t)std::max(M, 1))); CTBA_CUDA(p, sd->Zo.resize(18 * (size_t)std::max(M, 1)));
+  CTBA_CUDA(p, sd->lm_corner_partial.resize((size_t)cdiv(std::max(L, 1), 128) * 35));
   CTBA_CUDA(p, sd->d_touch_knot.upload(tk, st)); CTBA_CUDA(p, sd->d_touch_bias.upload(tb, st)); CTBA_CUDA(p, sd->d_touch_lm.upload(tl, st));
   // candidate state buffers
   CTBA_CUDA(p, sd->cand.knot_q.resize(p->dstate.knot_q.n)); CTBA_CUDA(p, sd->cand.knot_p.resize(p->dstate.knot_p.n));
@@ -994,15 +1133,22 @@ static int assemble_schur_T(ctba_problem* p, double radius) {
   const StatePtrs S = p->dstate.ptrs();
   if (F > 0 && L > 0) {
     const FramePose<N>* fps = (const FramePose<N>*)p->ev.frame_pose.p;
-    CTBA_CUDA(p, cudaMemsetAsync(sd->Sp.p, 0, (size_t)F * (T + 1) * 36 * sizeof(double), st));
-    CTBA_CUDA(p, cudaMemsetAsync(sd->Sb.p, 0, (size_t)F * 42 * sizeof(double), st));
-    CTBA_CUDA(p, cudaMemsetAsync(sd->rp.p, 0, (size_t)F * 6 * sizeof(double), st));
-    k_landmark_schur<N><<<cdiv((size_t)L * 32, 128), 128, 0, st>>>(G, S.glb, fps, S.lm, L, sd->d_lm_obs_begin.p, sd->d_lm_obs.p, p->d_o_frame.p,
-                                                                   p->ev.Jl.p, (const double2*)p->ev.r_reproj.p, p->ev.f_w.p, M, sd->V0.p, sd->gl.p,
-                                                                   sd->jscale_lm.p, radius, T, gm, sd->Sp.p, sd->Sb.p, sd->rp.p, Hw, rhs_acc + n_pad);
-    k_pose_to_knots<N><<<cdiv((size_t)F * (T + 1) * 32, 128), 128, 0, st>>>(fps, F, T, p->d_f_s.p, sd->d_node_of_knot.p, sd->Sp.p, sd->Sb.p, sd->rp.p,
-                                                                            gm, Hw, rhs_acc);
-    p->launches += 2;
+    bool any_g = false;
+    for (int c = 0; c < 7; ++c) any_g |= gm.a[c] != 0;
+    const int nlb = cdiv(L, 128);
+    k_lm_prepare<N><<<nlb, 128, 0, st>>>(G, S.glb, fps, S.lm, L, sd->d_lm_obs_begin.p, sd->d_lm_obs.p, p->d_o_frame.p, p->ev.Jl.p,
+                                         (const double2*)p->ev.r_reproj.p, p->ev.f_w.p, M, sd->V0.p, sd->gl.p, sd->jscale_lm.p, radius, gm, any_g,
+                                         sd->Vi.p, sd->vig.p, sd->ViYg.p, sd->lm_corner_partial.p);
+    if (any_g) { k_corner_reduce<<<1, 64, 0, st>>>(nlb, sd->lm_corner_partial.p, Hw, rhs_acc + n_pad); p->launches++; }
+    k_obs_yz<N><<<cdiv(M, 128), 128, 0, st>>>(G, S.glb, fps, S.lm, M, p->d_o_frame.p, p->d_o_lm.p, p->ev.Jl.p, (const double2*)p->ev.r_reproj.p,
+                                              p->ev.f_w.p, sd->Vi.p, sd->Yo.p, sd->Zo.p);
+    k_frame_schur<<<F, kFsThreads, 0, st>>>(F, T, p->d_f_obs_begin.p, p->d_o_lm.p, p->d_o_frame.p, sd->d_o_pos.p, sd->d_lm_obs_begin.p,
+                                            sd->d_lm_obs.p, sd->Yo.p, sd->Zo.p, sd->vig.p, sd->ViYg.p, any_g, sd->Sp.p, sd->Sb.p, sd->rp.p);
+    k_knot_schur<N><<<cdiv((size_t)sd->K * (sd->KD + 1) * 32, 128), 128, 0, st>>>(fps, sd->K, sd->KD, T, p->d_f_s.p, sd->d_kf_begin.p,
+                                                                                   sd->d_kf_list.p, sd->d_node_of_knot.p, sd->Sp.p, Hw);
+    k_knot_border<N><<<cdiv((size_t)6 * sd->K, 128), 128, 0, st>>>(fps, sd->K, p->d_f_s.p, sd->d_kf_begin.p, sd->d_kf_list.p,
+                                                                    sd->d_node_of_knot.p, sd->Sb.p, sd->rp.p, gm, any_g, Hw, rhs_acc);
+    p->launches += 4;
   }
   k_set_rhs<<<cdiv(n_pad + kBorder, 256), 256, 0, st>>>(Hw, sd->grad.p, rhs_acc, gm);
   p->launches++;

@@ -43,10 +43,12 @@ __device__ __forceinline__ void add_sym(const BandLayout& B, int i, int j, doubl
 
 struct SolverData {
   // ---- structure ----
-  int K = 0, Kb = 0, nodes = 0, hbn = 0, L = 0, F = 0, T = 0;
+  int K = 0, Kb = 0, nodes = 0, hbn = 0, L = 0, F = 0, T = 0, KD = 0;   // KD: largest knot distance coupled through a landmark
   bool has_bias = false;
   std::vector<int32_t> node_of_knot, node_of_bias;
   DBuf<int32_t> d_node_of_knot, d_node_of_bias, d_lm_obs_begin, d_lm_obs;
+  DBuf<int32_t> d_o_pos, d_kf_begin, d_kf_list;   // observation -> slot in its landmark's list; knot -> frames (CSR)
+  DBuf<double> Vi, vig, ViYg, Yo, Zo, lm_corner_partial;   // Schur gather scratch (ctba_assemble.cu)
   DBuf<uint8_t> d_touch_knot, d_touch_bias, d_touch_lm;  // bit0 rot/acc, bit1 pos/gyr
   int gactive[GT_SIZE] = {0};
   BandLayout H0{}, Hw{};
