@@ -430,13 +430,18 @@ constexpr int kFsThreads = 256;
 __global__ void __launch_bounds__(kFsThreads) k_frame_schur(int F, int T, const int32_t* __restrict__ obs_begin, const int32_t* __restrict__ o_lm,
                                                             const int32_t* __restrict__ o_frame, const int32_t* __restrict__ o_pos,
                                                             const int32_t* __restrict__ lm_obs_begin, const int32_t* __restrict__ lm_obs,
-                                                            const double* __restrict__ Yall, const double* __restrict__ Zall,
+                                                            const int32_t* __restrict__ lm_frame, const double* __restrict__ Yall,
+                                                            const double* __restrict__ Zall,
                                                             const double* __restrict__ vig_all, const double* __restrict__ ViYg_all, bool any_g,
                                                             double* __restrict__ Sp, double* __restrict__ Sb, double* __restrict__ rp) {
   __shared__ double red[kFsThreads / 32][48];
+  extern __shared__ double sY[];   // the frame's Y blocks: n x 18
   const int f = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b0 = obs_begin[f], n = obs_begin[f + 1] - b0;
+  for (int e = threadIdx.x; e < 9 * n; e += kFsThreads)
+    reinterpret_cast<double2*>(sY)[e] = reinterpret_cast<const double2*>(Yall + 18 * (size_t)b0)[e];
+  __syncthreads();
   // ---- pose right-hand side and pose x globals block: threads over the frame's observations ----
   {
     double acc[48];
@@ -444,7 +449,7 @@ __global__ void __launch_bounds__(kFsThreads) k_frame_schur(int F, int T, const 
     for (int e = 0; e < 48; ++e) acc[e] = 0.0;
     for (int i = threadIdx.x; i < n; i += kFsThreads) {
       const int a = b0 + i, l = o_lm[a];
-      const double* Y = Yall + 18 * (size_t)a;
+      const double* Y = sY + 18 * i;
       const double v0 = vig_all[3 * (size_t)l], v1 = vig_all[3 * (size_t)l + 1], v2 = vig_all[3 * (size_t)l + 2];
       double y[18];
 #pragma unroll
@@ -492,17 +497,19 @@ __global__ void __launch_bounds__(kFsThreads) k_frame_schur(int F, int T, const 
         const int a = b0 + i, l = o_lm[a];
         const int lend = lm_obs_begin[l + 1];
         int pos = o_pos[a];                       // position of a in the landmark's (frame-ordered) observation list
+        // tracks are mostly gap-free: try the slot df entries ahead first, fall back to a scan from a's own slot
+        if (df > 0 && pos + df < lend && lm_frame[pos + df] == f2 && lm_frame[pos + df - 1] < f2) pos += df;
         bool loaded = false;
         double y[18];
         for (; pos < lend; ++pos) {
-          const int b = lm_obs[pos];
-          const int fb = o_frame[b];
+          const int fb = lm_frame[pos];
           if (fb > f2) break;
           if (fb < f2) continue;
+          const int b = lm_obs[pos];
           if (!loaded) {
-            const double2* Y = reinterpret_cast<const double2*>(Yall + 18 * (size_t)a);
+            const double* Y = sY + 18 * i;
 #pragma unroll
-            for (int e = 0; e < 9; ++e) { const double2 v = Y[e]; y[2 * e] = v.x; y[2 * e + 1] = v.y; }
+            for (int e = 0; e < 18; ++e) y[e] = Y[e];
             loaded = true;
           }
           const double2* Zp = reinterpret_cast<const double2*>(Zall + 18 * (size_t)b);
@@ -971,8 +978,11 @@ int assemble_structure(ctba_problem* p) {
     std::vector<int32_t> cur(lob.begin(), lob.end() - 1);
     for (int o = 0; o < M; ++o) lobs[cur[p->o_lm[o]]++] = o;
   }
-  std::vector<int32_t> opos(std::max(M, 1), 0);
-  for (int l = 0; l < L; ++l) for (int i = lob[l]; i < lob[l + 1]; ++i) opos[lobs[i]] = i;
+  std::vector<int32_t> opos(std::max(M, 1), 0), lmf(std::max(M, 1), 0);
+  for (int l = 0; l < L; ++l) for (int i = lob[l]; i < lob[l + 1]; ++i) { opos[lobs[i]] = i; lmf[i] = p->o_frame[lobs[i]]; }
+  sd->max_frame_obs = 1;
+  for (int f = 0; f < F; ++f) sd->max_frame_obs = std::max(sd->max_frame_obs, (int)(p->f_obs_begin[f + 1] - p->f_obs_begin[f]));
+  if ((size_t)sd->max_frame_obs * 18 * sizeof(double) > 200 * 1024) { p->err = "assemble_structure: more than 1422 valid observations in one frame"; return CTBA_E_ARG; }
   int T = 0, KD = N - 1;
   for (int l = 0; l < L; ++l) {
     if (lob[l + 1] == lob[l]) continue;
@@ -1036,6 +1046,7 @@ int assemble_structure(ctba_problem* p) {
   cudaStream_t st = p->stream;
   CTBA_CUDA(p, sd->d_node_of_knot.upload(sd->node_of_knot, st)); CTBA_CUDA(p, sd->d_node_of_bias.upload(sd->node_of_bias, st));
   CTBA_CUDA(p, sd->d_lm_obs_begin.upload(lob, st)); CTBA_CUDA(p, sd->d_lm_obs.upload(lobs, st));
+  CTBA_CUDA(p, sd->d_lm_frame.upload(lmf, st));
   CTBA_CUDA(p, sd->d_o_pos.upload(opos, st)); CTBA_CUDA(p, sd->d_kf_begin.upload(kfb, st)); CTBA_CUDA(p, sd->d_kf_list.upload(kfl, st));
   CTBA_CUDA(p, sd->Vi.resize(6 * (size_t)std::max(L, 1))); CTBA_CUDA(p, sd->vig.resize(3 * (size_t)std::max(L, 1)));
   CTBA_CUDA(p, sd->ViYg.resize(21 * (size_t)std::max(L, 1)));
@@ -1142,8 +1153,10 @@ static int assemble_schur_T(ctba_problem* p, double radius) {
     if (any_g) { k_corner_reduce<<<1, 64, 0, st>>>(nlb, sd->lm_corner_partial.p, Hw, rhs_acc + n_pad); p->launches++; }
     k_obs_yz<N><<<cdiv(M, 128), 128, 0, st>>>(G, S.glb, fps, S.lm, M, p->d_o_frame.p, p->d_o_lm.p, p->ev.Jl.p, (const double2*)p->ev.r_reproj.p,
                                               p->ev.f_w.p, sd->Vi.p, sd->Yo.p, sd->Zo.p);
-    k_frame_schur<<<F, kFsThreads, 0, st>>>(F, T, p->d_f_obs_begin.p, p->d_o_lm.p, p->d_o_frame.p, sd->d_o_pos.p, sd->d_lm_obs_begin.p,
-                                            sd->d_lm_obs.p, sd->Yo.p, sd->Zo.p, sd->vig.p, sd->ViYg.p, any_g, sd->Sp.p, sd->Sb.p, sd->rp.p);
+    const size_t fs_smem = (size_t)sd->max_frame_obs * 18 * sizeof(double);
+    if (fs_smem > 48 * 1024) CTBA_CUDA(p, cudaFuncSetAttribute(k_frame_schur, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs_smem));
+    k_frame_schur<<<F, kFsThreads, fs_smem, st>>>(F, T, p->d_f_obs_begin.p, p->d_o_lm.p, p->d_o_frame.p, sd->d_o_pos.p, sd->d_lm_obs_begin.p,
+                                            sd->d_lm_obs.p, sd->d_lm_frame.p, sd->Yo.p, sd->Zo.p, sd->vig.p, sd->ViYg.p, any_g, sd->Sp.p, sd->Sb.p, sd->rp.p);
     k_knot_schur<N><<<cdiv((size_t)sd->K * (sd->KD + 1) * 32, 128), 128, 0, st>>>(fps, sd->K, sd->KD, T, p->d_f_s.p, sd->d_kf_begin.p,
                                                                                    sd->d_kf_list.p, sd->d_node_of_knot.p, sd->Sp.p, Hw);
     k_knot_border<N><<<cdiv((size_t)6 * sd->K, 128), 128, 0, st>>>(fps, sd->K, p->d_f_s.p, sd->d_kf_begin.p, sd->d_kf_list.p,

@@ -47,6 +47,8 @@ struct SolverData {
   bool has_bias = false;
   std::vector<int32_t> node_of_knot, node_of_bias;
   DBuf<int32_t> d_node_of_knot, d_node_of_bias, d_lm_obs_begin, d_lm_obs;
+  DBuf<int32_t> d_lm_frame;   // frame of every entry of the landmark observation lists
+  int max_frame_obs = 1;
   DBuf<int32_t> d_o_pos, d_kf_begin, d_kf_list;   // observation -> slot in its landmark's list; knot -> frames (CSR)
   DBuf<double> Vi, vig, ViYg, Yo, Zo, lm_corner_partial;   // Schur gather scratch (ctba_assemble.cu)
   DBuf<uint8_t> d_touch_knot, d_touch_bias, d_touch_lm;  // bit0 rot/acc, bit1 pos/gyr
