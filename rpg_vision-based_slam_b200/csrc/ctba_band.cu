@@ -9,6 +9,8 @@
 //   k_corner_partial / k_corner_solve   Schur complement of the band onto the <= 15 global parameters, 15x15 solve
 //   k_back_rhs + k_band_backsolve       backward substitution  L^T x = y - Lb^T z
 #include <cooperative_groups.h>
+#include <algorithm>
+#include <cmath>
 #include "ctba_solver.h"
 
 namespace ctba {
@@ -172,6 +174,45 @@ __device__ __forceinline__ void potrf_trsm32_cta(double* sD, double* sX, double*
   if (warp == 1) solve_x_block(kNB - 8);
 }
 
+// ---- time partitions ---------------------------------------------------------------------------------------------------------
+// The factorisation is sequential along the band, so the block columns are cut into P "interiors" I_0 .. I_{P-1} separated by P-1
+// "separators" S_q of nbw block columns each (S_q lies between I_q and I_{q+1}; an interior is at least nbw columns wide, so separators
+// do not couple directly).  All interiors are eliminated CONCURRENTLY (one block column of every interior per launch).  Interior p >= 1
+// sees its left separator S_{p-1} as extra ("fat") border rows: the coupling fills in along the whole interior exactly like the rows of
+// the global parameters do.  What remains is a small block-tridiagonal interface system in the separators (+ globals), solved by the same
+// code with P = 1.  Sequential block steps: max|I_p| + (P-1) nbw instead of nbc.  This is also the multi-GPU decomposition (partition
+// per rank, interface system all-gathered).
+//
+// Border storage of partition p ("FB"): row-major, R = 32*(nrb-1) + 16 rows (nrb-1 = nbw row blocks of S_{p-1} for p >= 1, none for
+// p = 0; the last 16 rows are the 15 globals + right-hand side), ld = 32 * ncols doubles, ncols = |I_p| + (nbw columns of S_p if p < P-1).
+constexpr int kMaxParts = 32;
+struct BandPart {
+  int c0;        // first block column of the interior
+  int nI;        // interior block columns
+  int nrb;       // border row blocks (the last one has 16 rows)
+  int ncols;     // block columns covered by fb: nI (+ nbw for the right separator)
+  int ld;        // 32 * ncols
+  double* fb;    // border rows of this partition
+};
+struct BandParts { int P; BandPart part[kMaxParts]; };
+
+// task counts of partition q at step t (shared by host and device)
+__host__ __device__ inline void part_tasks(const BandLayout& B, const BandPart& q, int t, int* n_panel, int* m_upd, int* k_lo) {
+  const int j = q.c0 + t;
+  const bool has_panel = t < q.nI;
+  const int rows = has_panel ? (B.nbw < B.nbc - 1 - j ? B.nbw : B.nbc - 1 - j) : 0;
+  *n_panel = has_panel ? 1 + rows + q.nrb : 0;
+  *k_lo = has_panel ? j + 1 : j;
+  int k_hi = j - 1 + B.nbw; if (k_hi > B.nbc - 1) k_hi = B.nbc - 1;
+  int m = (t >= 1 && t <= q.nI) ? k_hi - *k_lo + 1 : 0;
+  *m_upd = m > 0 ? m : 0;
+}
+__host__ __device__ inline int part_task_total(const BandLayout& B, const BandPart& q, int t) {
+  int np, m, kl;
+  part_tasks(B, q, t, &np, &m, &kl);
+  return np + m * (m + 1) / 2 + m * q.nrb;
+}
+
 #ifdef CTBA_BAND_TIMING
 __device__ long long g_band_clk[8];
 #define BAND_CLK(k) do { if (j == 100 && b == 1 && tid == 0) g_band_clk[k] = clock64(); } while (0)
@@ -179,43 +220,59 @@ __device__ long long g_band_clk[8];
 #define BAND_CLK(k) do {} while (0)
 #endif
 
-// One launch per block column j (right-looking with a one-column look-ahead):
-//   panel CTAs  [0, rows+2)      : apply column j-1's update to THEIR block of column j (and to the diagonal block, redundantly),
-//                                  factor the diagonal block, triangular-solve their block, store it.  CTA 0 = diagonal (also stores
-//                                  L_jj^-1 for the backward substitution), CTA rows+1 = the 16 border rows (15 globals + right-hand side).
-//   update CTAs [rows+2, ...)    : remaining trailing update of column j-1:  T(i,k) -= L(i,j-1) L(k,j-1)^T  for j+1 <= k <= i <= j-1+nbw,
-//                                  and the border rows of those block columns.
-// Pre-condition of launch j: columns < j final, every trailing block carries the updates of columns <= j-2.
-__global__ void __launch_bounds__(kStepThreads) k_band_step(BandLayout B, int j, double* __restrict__ dinv, int32_t* __restrict__ flag, int pdl) {
+// One launch per step t: every partition p advances to its block column j = c0_p + t (right-looking with a one-column look-ahead):
+//   panel CTAs   : apply column j-1's update to THEIR block of column j (and to the diagonal block, redundantly), factor the diagonal block,
+//                  triangular-solve their block, store it.  Task 0 = diagonal (also stores L_jj^-1 for the backward substitution),
+//                  tasks 1..rows = sub-diagonal blocks, then one task per border row block.
+//   update CTAs  : remaining trailing update of column j-1:  T(i,k) -= L(i,j-1) L(k,j-1)^T  for k_lo <= k <= i <= j-1+nbw, and the border
+//                  row blocks of those block columns.  k_lo = j+1 while the partition still has a panel (the panel CTAs cover column j),
+//                  k_lo = j in the partition's final flush step t = |I_p|.
+// Pre-condition of step t: columns < j of the interior final, every trailing block carries the updates of columns <= j-2.
+__global__ void __launch_bounds__(kStepThreads) k_band_step(BandLayout B, const __grid_constant__ BandParts PS, int t, double* __restrict__ dinv,
+                                                            int32_t* __restrict__ flag, int pdl) {
   __shared__ double sD[kNB * kLd];
   __shared__ double sX[kNB * kLd];
   __shared__ double sRinv[kNB];
-  // programmatic dependent launch (pdl != 0): column j+1's grid may become resident early (pdl 1: now; pdl 2: once this CTA has staged its
-  // operands); it waits here until column j-1's grid has completed and flushed.  Without the launch attribute both are no-ops.
+  // programmatic dependent launch (pdl != 0): the next step's grid may become resident early (pdl 1: now; pdl 2: once this CTA has staged its
+  // operands); it waits here until the previous step's grid has completed and flushed.  Without the launch attribute both are no-ops.
   if (pdl == 1) asm volatile("griddepcontrol.launch_dependents;");
   if (pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nb1 = B.nbw + 1;
-  const int rows = min(B.nbw, B.nbc - 1 - j);
-  const int b = blockIdx.x;
-  const bool prev = j > 0 && B.nbw >= 1;
+  // ---- which partition, which task ----
+  int b = blockIdx.x, pi = 0, n_panel = 0, m = 0, k_lo = 0;
+  for (; pi < PS.P; ++pi) {
+    part_tasks(B, PS.part[pi], t, &n_panel, &m, &k_lo);
+    const int tot = n_panel + m * (m + 1) / 2 + m * PS.part[pi].nrb;
+    if (b < tot) break;
+    b -= tot;
+  }
+  if (pi >= PS.P) return;
+  const BandPart& Q = PS.part[pi];
+  const int j = Q.c0 + t;
+  const bool prev = t > 0 && B.nbw >= 1;
   const double* Lprev = B.band + ((size_t)max(j - 1, 0) * nb1) * 1024;  // column j-1: block (j-1+o, j-1) at offset o
-  const double* Bprev = B.border + (size_t)max(j - 1, 0) * kNB;
-  if (b < rows + 2) {
+  const int lcol = j - Q.c0;                                            // column of fb
+  if (b < n_panel) {
     // ---------------- panel ----------------
+    const int rows = n_panel - 1 - Q.nrb;
     double* Ajj = B.band + ((size_t)j * nb1) * 1024;
-    const bool is_border = (b == rows + 1);
     BAND_CLK(0);
+    int rb = -1, nrows = kNB;
+    double* Fb = nullptr;
     if (b == 0) {
       panel_stage(sD, sX, Ajj, Lprev + 1024, prev, false, nullptr, 0, nullptr, 0, 0, false, warp, lane);
       // identity right-hand side: X L^T = I gives X = L_jj^-T, whose transpose L_jj^-1 is kept for the backward substitution
       for (int e = tid; e < kNB * kNB; e += kStepThreads) sX[(e >> 5) * kLd + (e & 31)] = ((e >> 5) == (e & 31)) ? 1.0 : 0.0;
-    } else if (!is_border) {
+    } else if (b <= rows) {
       const bool have_prev = prev && (b + 1 <= B.nbw);   // block (j+b, j-1) lies inside the band
       panel_stage(sD, sX, Ajj, Lprev + 1024, prev, true, Ajj + (size_t)b * 1024, kNB, Lprev + (size_t)min(b + 1, B.nbw) * 1024, kNB, kNB, have_prev,
                   warp, lane);
     } else {
-      panel_stage(sD, sX, Ajj, Lprev + 1024, prev, true, B.border + (size_t)j * kNB, B.n_pad, Bprev, B.n_pad, kBorder, prev, warp, lane);
+      rb = b - rows - 1;
+      nrows = (rb == Q.nrb - 1) ? kBorder : kNB;
+      Fb = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)lcol * kNB;
+      panel_stage(sD, sX, Ajj, Lprev + 1024, prev, true, Fb, Q.ld, Fb - kNB, Q.ld, nrows, prev, warp, lane);
     }
     __syncthreads();
     if (pdl == 2) asm volatile("griddepcontrol.launch_dependents;");
@@ -230,27 +287,26 @@ __global__ void __launch_bounds__(kStepThreads) k_band_step(BandLayout B, int j,
         Ajj[e] = sD[r * kLd + c];
         dinv[(size_t)j * 1024 + e] = sX[c * kLd + r];   // (L^-1)[r][c] = X[c][r]
       }
-    } else if (!is_border) {
+    } else if (b <= rows) {
       double* Lij = Ajj + (size_t)b * 1024;
       for (int e = tid; e < kNB * kNB; e += kStepThreads) Lij[e] = sX[(e >> 5) * kLd + (e & 31)];
       BAND_CLK(4);
     } else {
-      for (int e = tid; e < kBorder * kNB; e += kStepThreads) { const int r = e >> 5, c = e & 31; B.border[(size_t)r * B.n_pad + j * kNB + c] = sX[r * kLd + c]; }
+      for (int e = tid; e < nrows * kNB; e += kStepThreads) { const int r = e >> 5, c = e & 31; Fb[(size_t)r * Q.ld + c] = sX[r * kLd + c]; }
     }
     return;
   }
-  // ---------------- trailing update of column j-1 (only launched for j >= 1) ----------------
+  // ---------------- trailing update of column j-1 ----------------
   if (pdl == 2) asm volatile("griddepcontrol.launch_dependents;");
-  const int m = min(B.nbw - 1, B.nbc - 1 - j);   // rows j+1 .. j+m carry a block in column j-1
-  int u = b - (rows + 2);
+  int u = b - n_panel;
   const int ntri = m * (m + 1) / 2;
-  const int g = lane >> 2, t = lane & 3;
+  const int g = lane >> 2, tq = lane & 3;
   if (u < ntri) {
     int a = (int)((sqrtf(8.0f * u + 1.0f) - 1.0f) * 0.5f);
     while ((a + 1) * (a + 2) / 2 <= u) ++a;
     while (a * (a + 1) / 2 > u) --a;
     const int c = u - a * (a + 1) / 2;          // 0 <= c <= a < m
-    const int i = j + 1 + a, k = j + 1 + c;
+    const int i = k_lo + a, k = k_lo + c;
     const double* Li = Lprev + (size_t)(i - (j - 1)) * 1024;
     const double* Lk = Lprev + (size_t)(k - (j - 1)) * 1024;
     double* T = B.band + ((size_t)k * nb1 + (i - k)) * 1024;
@@ -260,23 +316,186 @@ __global__ void __launch_bounds__(kStepThreads) k_band_step(BandLayout B, int j,
       const int tc = 2 * (warp & 1) + h;
       double c0 = 0.0, c1 = 0.0;
       tile_abt(Li, kNB, Lk, kNB, tr, tc, lane, c0, c1);
-      double2* dst = reinterpret_cast<double2*>(T + (size_t)(8 * tr + g) * kNB + 8 * tc + 2 * t);
+      double2* dst = reinterpret_cast<double2*>(T + (size_t)(8 * tr + g) * kNB + 8 * tc + 2 * tq);
       double2 v = *dst; v.x -= c0; v.y -= c1; *dst = v;
     }
     return;
   }
   u -= ntri;
-  if (u < m) {   // border rows of block column k
-    const int k = j + 1 + u;
+  if (u < m * Q.nrb) {   // border row block rb of block column k
+    const int k = k_lo + u / Q.nrb, rb = u % Q.nrb;
+    const int nrows = (rb == Q.nrb - 1) ? kBorder : kNB;
     const double* Lk = Lprev + (size_t)(k - (j - 1)) * 1024;
-    const int tr = warp >> 2, tc = warp & 3;     // 2 x 4 tiles of the 16 x 32 border block
-    double c0 = 0.0, c1 = 0.0;
-    tile_abt(Bprev, B.n_pad, Lk, kNB, tr, tc, lane, c0, c1);
-    double2* dst = reinterpret_cast<double2*>(B.border + (size_t)(8 * tr + g) * B.n_pad + (size_t)k * kNB + 8 * tc + 2 * t);
-    double2 v = *dst; v.x -= c0; v.y -= c1; *dst = v;
+    const double* Fprev = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)(lcol - 1) * kNB;
+    double* Fk = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)(k - Q.c0) * kNB;
+    const int tr = warp >> 1;
+    if (8 * tr < nrows) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int tc = 2 * (warp & 1) + h;
+        double c0 = 0.0, c1 = 0.0;
+        tile_abt(Fprev, Q.ld, Lk, kNB, tr, tc, lane, c0, c1);
+        double2* dst = reinterpret_cast<double2*>(Fk + (size_t)(8 * tr + g) * Q.ld + 8 * tc + 2 * tq);
+        double2 v = *dst; v.x -= c0; v.y -= c1; *dst = v;
+      }
+    }
   }
 }
 
+// ---- partition border initialisation -------------------------------------------------------------------------------------------
+// fb_p = [ coupling of the left separator S_{p-1} to the partition's columns (transposed band blocks, zero beyond the band) ; global rows ]
+__global__ void __launch_bounds__(256) k_fb_init(BandLayout B, const __grid_constant__ BandParts PS) {
+  int blk = blockIdx.x, pi = 0;
+  for (; pi < PS.P; ++pi) {
+    const int nb = PS.part[pi].nrb * PS.part[pi].ncols;
+    if (blk < nb) break;
+    blk -= nb;
+  }
+  if (pi >= PS.P) return;
+  const BandPart& Q = PS.part[pi];
+  const int rb = blk / Q.ncols, col = blk % Q.ncols;
+  double* dst = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)col * kNB;
+  const int i = Q.c0 + col;
+  if (rb == Q.nrb - 1) {   // 15 globals + right-hand side (the 16 pad rows below are never read as data)
+    for (int e = threadIdx.x; e < kNB * kNB; e += 256) {
+      const int r = e >> 5, c = e & 31;
+      dst[(size_t)r * Q.ld + c] = r < kBorder ? B.border[(size_t)r * B.n_pad + (size_t)i * kNB + c] : 0.0;
+    }
+    return;
+  }
+  const int k = Q.c0 - B.nbw + rb;          // block column of the left separator that owns this row block
+  const bool inband = (i - k) <= B.nbw;
+  const double* T = B.band + ((size_t)k * (B.nbw + 1) + (inband ? i - k : 0)) * 1024;   // block (i, k)
+  for (int e = threadIdx.x; e < kNB * kNB; e += 256) {
+    const int r = e >> 5, c = e & 31;       // fb[r][c] = A[(k,r),(i,c)] = T(i,k)[c][r]
+    dst[(size_t)r * Q.ld + c] = inband ? T[c * kNB + r] : 0.0;
+  }
+}
+
+// ---- Gram matrices of the factored borders:  G_p = W_p W_p^T over the interior columns (lower 32x32 tiles, split over column chunks) ----
+constexpr int kGramChunk = 16;
+struct GramPlan { int P; int tile0[kMaxParts + 1]; int nsplit[kMaxParts]; int task0[kMaxParts + 1]; };   // tiles / tasks prefix sums
+__global__ void __launch_bounds__(kStepThreads) k_gram_partial(const __grid_constant__ BandParts PS, const __grid_constant__ GramPlan GP,
+                                                               double* __restrict__ scratch /* [task][1024] */) {
+  int task = blockIdx.x, pi = 0;
+  while (pi + 1 < GP.P && task >= GP.task0[pi + 1]) ++pi;
+  task -= GP.task0[pi];
+  const BandPart& Q = PS.part[pi];
+  const int ntile = GP.tile0[pi + 1] - GP.tile0[pi];
+  const int tile = task % ntile, ks = task / ntile;
+  int ta = (int)((sqrtf(8.0f * tile + 1.0f) - 1.0f) * 0.5f);
+  while ((ta + 1) * (ta + 2) / 2 <= tile) ++ta;
+  while (ta * (ta + 1) / 2 > tile) --ta;
+  const int tb = tile - ta * (ta + 1) / 2;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tr = warp >> 1, g = lane >> 2, tq = lane & 3;
+  const int rows_a = (ta == Q.nrb - 1) ? kBorder : kNB, rows_b = (tb == Q.nrb - 1) ? kBorder : kNB;
+  double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+  const int col0 = ks * kGramChunk, col1 = min(col0 + kGramChunk, Q.nI);
+  const double* Fa = Q.fb + (size_t)ta * kNB * Q.ld;
+  const double* Fb = Q.fb + (size_t)tb * kNB * Q.ld;
+  if (8 * tr < rows_a) {
+    for (int col = col0; col < col1; ++col) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int tc = 2 * (warp & 1) + h;
+        if (8 * tc < rows_b) tile_abt(Fa + (size_t)col * kNB, Q.ld, Fb + (size_t)col * kNB, Q.ld, tr, tc, lane, acc[h][0], acc[h][1]);
+      }
+    }
+  }
+  double* out = scratch + ((size_t)blockIdx.x << 10);
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int tc = 2 * (warp & 1) + h;
+    *reinterpret_cast<double2*>(out + (8 * tr + g) * kNB + 8 * tc + 2 * tq) = make_double2(acc[h][0], acc[h][1]);
+  }
+}
+// G_p tile = sum of its column-chunk partials in fixed order (deterministic); G_p is stored row-major with ld = 32 * nrb
+__global__ void __launch_bounds__(256) k_gram_reduce(const __grid_constant__ BandParts PS, const __grid_constant__ GramPlan GP,
+                                                     const double* __restrict__ scratch, double* __restrict__ gram /* concatenated G_p */,
+                                                     const size_t* __restrict__ gram_off) {
+  int t = blockIdx.x, pi = 0;
+  while (pi + 1 < GP.P && t >= GP.tile0[pi + 1]) ++pi;
+  const int tile = t - GP.tile0[pi];
+  const int ntile = GP.tile0[pi + 1] - GP.tile0[pi];
+  int ta = (int)((sqrtf(8.0f * tile + 1.0f) - 1.0f) * 0.5f);
+  while ((ta + 1) * (ta + 2) / 2 <= tile) ++ta;
+  while (ta * (ta + 1) / 2 > tile) --ta;
+  const int tb = tile - ta * (ta + 1) / 2;
+  const int ldg = kNB * PS.part[pi].nrb;
+  double* G = gram + gram_off[pi];
+  for (int e = threadIdx.x; e < kNB * kNB; e += 256) {
+    double s = 0.0;
+    for (int ks = 0; ks < GP.nsplit[pi]; ++ks) s += scratch[((size_t)(GP.task0[pi] + ks * ntile + tile) << 10) + e];
+    G[(size_t)(ta * kNB + (e >> 5)) * ldg + tb * kNB + (e & 31)] = s;
+  }
+}
+
+// ---- interface system in the separators -------------------------------------------------------------------------------------------
+// B2: block columns = the separator columns in time order (nbw per separator), half bandwidth 2 nbw - 1 blocks (dense block tridiagonal).
+struct IfaceArgs { const double* gram; size_t gram_off[kMaxParts]; };
+__global__ void __launch_bounds__(256) k_iface_assemble(BandLayout B, BandLayout B2, const __grid_constant__ BandParts PS, const __grid_constant__ IfaceArgs IA) {
+  const int nb1_2 = B2.nbw + 1;
+  const int nblk = B2.nbc * nb1_2;
+  const int blk = blockIdx.x;
+  const int nbw = B.nbw;
+  if (blk < nblk) {
+    const int K2 = blk / nb1_2, off = blk % nb1_2, I2 = K2 + off;
+    double* dst = B2.band + ((size_t)blk << 10);
+    if (I2 >= B2.nbc) { for (int e = threadIdx.x; e < 1024; e += 256) dst[e] = 0.0; return; }
+    const int qi = I2 / nbw, a = I2 % nbw, qk = K2 / nbw, c = K2 % nbw;
+    if (qi == qk) {
+      const int s = PS.part[qk + 1].c0 - nbw;                         // first block column of separator qk
+      const double* T = B.band + ((size_t)(s + c) * (nbw + 1) + (a - c)) * 1024;
+      const double* G = IA.gram + IA.gram_off[qk + 1];
+      const int ldg = kNB * PS.part[qk + 1].nrb;
+      for (int e = threadIdx.x; e < 1024; e += 256) dst[e] = T[e] - G[(size_t)(a * kNB + (e >> 5)) * ldg + c * kNB + (e & 31)];
+    } else if (qi == qk + 1) {
+      const BandPart& Q = PS.part[qi];                                 // the interior between the two separators
+      const double* F = Q.fb + (size_t)c * kNB * Q.ld + (size_t)(Q.nI + a) * kNB;   // rows of S_qk (block c), columns of S_qi (block a)
+      for (int e = threadIdx.x; e < 1024; e += 256) dst[e] = F[(size_t)(e & 31) * Q.ld + (e >> 5)];
+    } else {
+      for (int e = threadIdx.x; e < 1024; e += 256) dst[e] = 0.0;
+    }
+    return;
+  }
+  const int bb = blk - nblk;
+  if (bb < B2.nbc) {   // global rows over separator column K2
+    const int K2 = bb, qk = K2 / nbw, c = K2 % nbw;
+    const BandPart& Q = PS.part[qk];                                   // left neighbour: carries the global rows over S_qk's columns
+    const double* F = Q.fb + (size_t)(Q.nrb - 1) * kNB * Q.ld + (size_t)(Q.nI + c) * kNB;
+    const double* G = IA.gram + IA.gram_off[qk + 1];
+    const int ldg = kNB * PS.part[qk + 1].nrb;
+    for (int e = threadIdx.x; e < kBorder * kNB; e += 256) {
+      const int g = e >> 5, cc = e & 31;
+      B2.border[(size_t)g * B2.n_pad + (size_t)K2 * kNB + cc] = F[(size_t)g * Q.ld + cc] - G[(size_t)(nbw * kNB + g) * ldg + c * kNB + cc];
+    }
+    return;
+  }
+  // corner
+  for (int e = threadIdx.x; e < kBorder * kBorder; e += 256) {
+    const int a = e / kBorder, b = e % kBorder;
+    double v = B.corner[e];
+    for (int p = 0; p < PS.P; ++p) {
+      const int ldg = kNB * PS.part[p].nrb, o = (PS.part[p].nrb - 1) * kNB;
+      v -= IA.gram[IA.gram_off[p] + (size_t)(o + (a > b ? a : b)) * ldg + o + (a > b ? b : a)];
+    }
+    B2.corner[e] = v;
+  }
+}
+// interface solution -> separator columns of the full solution vector (+ globals)
+__global__ void k_iface_scatter(BandLayout B, BandLayout B2, const __grid_constant__ BandParts PS, const double* __restrict__ delta2, double* __restrict__ delta) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < B2.n_pad) {
+    const int K2 = i >> 5, q = K2 / B.nbw, c = K2 % B.nbw;
+    const int s = PS.part[q + 1].c0 - B.nbw;
+    delta[(size_t)(s + c) * kNB + (i & 31)] = delta2[i];
+  } else if (i < B2.n_pad + kBorder) {
+    delta[B.n_pad + (i - B2.n_pad)] = delta2[i];
+  }
+}
+
+// ---- dense border system of a single-partition solve ---------------------------------------------------------------------------
 // partial[blk][a*16+b] = sum over the block's 256 columns of Lb[a][c] Lb[b][c]
 __global__ void __launch_bounds__(256) k_corner_partial(BandLayout B, double* __restrict__ partial) {
   __shared__ double s[kBorder][257];
@@ -325,27 +544,42 @@ __global__ void k_corner_solve(BandLayout B, int nblk, const double* __restrict_
   delta[B.n_pad + kRhsRow] = 0.0;
 }
 
-// t = y - Lb^T z  (y = forward-substituted right-hand side = border row 15) into delta[0, n_pad)
-__global__ void k_back_rhs(BandLayout B, double* __restrict__ delta) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= B.n_pad) return;
-  double t = B.border[(size_t)kRhsRow * B.n_pad + c];
+// t = y - W^T [x_S ; z] for the interior columns of every partition (y = forward-substituted right-hand side = last border row),
+// x_S = solution on the partition's left separator, z = globals.  Writes delta[interior columns].
+__global__ void __launch_bounds__(256) k_back_rhs(BandLayout B, const __grid_constant__ BandParts PS, double* __restrict__ delta) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= B.n_pad) return;
+  const int jb = col >> 5;
+  int pi = -1;
+  for (int q = 0; q < PS.P; ++q) if (jb >= PS.part[q].c0 && jb < PS.part[q].c0 + PS.part[q].nI) pi = q;
+  if (pi < 0) return;   // separator column: solved by the interface system
+  const BandPart& Q = PS.part[pi];
+  const double* F = Q.fb + (size_t)(jb - Q.c0) * kNB + (col & 31);
+  const int rs = (Q.nrb - 1) * kNB;                 // separator rows
+  double t = F[(size_t)(rs + kRhsRow) * Q.ld];
+  const double* z = delta + B.n_pad;
 #pragma unroll
-  for (int g = 0; g < GT_SIZE; ++g) t -= B.border[(size_t)g * B.n_pad + c] * delta[B.n_pad + g];
-  delta[c] = t;
+  for (int g = 0; g < GT_SIZE; ++g) t -= F[(size_t)(rs + g) * Q.ld] * z[g];
+  const double* xs = delta + (size_t)(Q.c0 - B.nbw) * kNB;   // only dereferenced when rs > 0 (partition >= 1)
+  double t2 = 0.0;
+  for (int r = 0; r < rs; r += 2) { t -= F[(size_t)r * Q.ld] * xs[r]; t2 += F[(size_t)(r + 1) * Q.ld] * xs[r + 1]; }
+  delta[col] = t - t2;
 }
 
-// x = L^-T t, block columns from last to first, by ONE thread-block cluster of kBackCtas CTAs (a single SM cannot stream the factor
-// fast enough: every step reads nbw+1 blocks of 8 KB).  Sub-diagonal offset o (1..nbw) belongs to CTA (o-1) % kBackCtas, warp 1 + (o-1) / kBackCtas:
+// x = L^-T t on the interior of every partition, block columns from last to first; partition p is handled by ONE thread-block cluster of
+// kBackCtas CTAs (a single SM cannot stream the factor fast enough: every step reads nbw+1 blocks of 8 KB).  Sub-diagonal offset o (1..nbw)
+// belongs to CTA (o-1) % kBackCtas, warp 1 + (o-1) / kBackCtas:
 //   warp w>=1 : p_o = L(i+o, i)^T x_{i+o}     (block rows streamed with coalesced loads, the next column prefetched into registers)
 //   warp 0    : sums its CTA's p_o, writes the partial into every CTA's exchange buffer through distributed shared memory;
 //               after ONE cluster barrier every CTA redundantly forms  x_i = L_ii^-T (t_i - sum of partials)  and keeps its own ring of x blocks.
-// The exchange buffer is double-buffered by step parity.  delta[0, n_pad) holds t on entry and x on exit.
+// The ring starts with the (already known) solution on the partition's right separator.  delta holds t on entry and x on exit.
 constexpr int kBackCtas = 8;
-__global__ void __launch_bounds__(160) k_band_backsolve(BandLayout B, const double* __restrict__ dinv, double* __restrict__ delta) {
+__global__ void __launch_bounds__(288) k_band_backsolve(BandLayout B, const __grid_constant__ BandParts PS, const double* __restrict__ dinv,
+                                                        double* __restrict__ delta) {
   extern __shared__ double sh[];
   cg::cluster_group cluster = cg::this_cluster();
   const int rank = (int)cluster.block_rank();
+  const BandPart& Q = PS.part[blockIdx.x / kBackCtas];
   const int nb1 = B.nbw + 1;
   const int nwarps = blockDim.x >> 5;
   double* xs = sh;                               // nb1 * 32      ring of x blocks
@@ -354,15 +588,20 @@ __global__ void __launch_bounds__(160) k_band_backsolve(BandLayout B, const doub
   double* ts = exch + 2 * kBackCtas * kNB;       // 32
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int off = (warp - 1) * kBackCtas + rank + 1;   // this warp's sub-diagonal offset (warp >= 1)
+  const int first = Q.c0, last = Q.c0 + Q.nI - 1;
   auto src = [&](int i) -> const double* {
-    if (i < 0) return nullptr;
+    if (i < first) return nullptr;
     if (warp == 0) return dinv + (size_t)i * 1024 + lane;                                   // (L_ii^-1)[c][lane]
     if (off <= B.nbw && i + off < B.nbc) return B.band + ((size_t)i * nb1 + off) * 1024 + lane;   // L(i+off, i)[r][lane]
     return nullptr;
   };
+  for (int e = threadIdx.x; e < B.nbw * kNB; e += blockDim.x) {   // solution on the right separator (columns last+1 .. last+nbw)
+    const int col = last + 1 + (e >> 5);
+    if (col < B.nbc) xs[(col % nb1) * kNB + (e & 31)] = delta[(size_t)col * kNB + (e & 31)];
+  }
   double cur[kNB], nxt[kNB];
   {
-    const double* s0 = src(B.nbc - 1);
+    const double* s0 = src(last);
 #pragma unroll
     for (int r = 0; r < kNB; ++r) cur[r] = s0 ? s0[r * kNB] : 0.0;
   }
@@ -372,12 +611,12 @@ __global__ void __launch_bounds__(160) k_band_backsolve(BandLayout B, const doub
     for (int r = 0; r < kNB; r += 4) { p0 = fma(cur[r], v[r], p0); p1 = fma(cur[r + 1], v[r + 1], p1); p2 = fma(cur[r + 2], v[r + 2], p2); p3 = fma(cur[r + 3], v[r + 3], p3); }
     return (p0 + p1) + (p2 + p3);
   };
-  double t_cur = (warp == 0) ? delta[(size_t)(B.nbc - 1) * kNB + lane] : 0.0;
-  cluster.sync();   // every CTA of the cluster is running before the first remote store
-  for (int i = B.nbc - 1; i >= 0; --i) {
+  double t_cur = (warp == 0 && last >= first) ? delta[(size_t)last * kNB + lane] : 0.0;
+  cluster.sync();   // every CTA of the cluster is running before the first remote store; also orders the ring initialisation
+  for (int i = last; i >= first; --i) {
     const double* g = src(i);
     const double* gn = src(i - 1);
-    const double t_nxt = (warp == 0 && i > 0) ? delta[(size_t)(i - 1) * kNB + lane] : 0.0;
+    const double t_nxt = (warp == 0 && i > first) ? delta[(size_t)(i - 1) * kNB + lane] : 0.0;
 #pragma unroll
     for (int r = 0; r < kNB; ++r) nxt[r] = gn ? gn[r * kNB] : 0.0;
     if (warp > 0) part[warp * kNB + lane] = g ? dot32(xs + ((i + off) % nb1) * kNB) : 0.0;
@@ -408,38 +647,160 @@ __global__ void __launch_bounds__(160) k_band_backsolve(BandLayout B, const doub
   cluster.sync();   // no CTA exits while a peer may still address its shared memory
 }
 
-static int band_enqueue(ctba_problem* p, cudaStream_t st) {
+// ================================================== host side =====================================================
+struct BandPlan {
+  // key
+  int nbc = -1, nbw = -1, req = -2; const double* band_ptr = nullptr; const double* border_ptr = nullptr;
+  int P = 1, max_steps = 0;
+  BandParts PS{};           // partitions of the full system (P == 1: one partition whose border is Hw.border itself)
+  BandParts PS2{};          // the interface system as a single partition
+  BandLayout B2{};
+  GramPlan GP{};
+  IfaceArgs IA{};
+  int gram_tasks = 0, gram_tiles = 0;
+  DBuf<double> fb, gram, gram_scratch, band2, border2, corner2, delta2, dinv2, cpart, cpart2, dinv;
+  DBuf<int32_t> dummy;
+  size_t* d_gram_off = nullptr;
+  ~BandPlan() {
+    DBuf<double>* dd[] = {&fb, &gram, &gram_scratch, &band2, &border2, &corner2, &delta2, &dinv2, &cpart, &cpart2, &dinv};
+    for (auto* d : dd) d->release();
+    if (d_gram_off) cudaFree(d_gram_off);
+  }
+};
+
+static int choose_partitions(int nbc, int nbw, int requested) {
+  if (nbw < 1 || 2 * nbw > 63) return 1;
+  int P = requested > 0 ? requested : (int)lround(std::sqrt((double)nbc / (1.2 * nbw)));
+  P = std::max(1, std::min(P, kMaxParts));
+  while (P > 1 && (nbc - (P - 1) * nbw) / P < std::max(nbw, 2)) --P;
+  return P;
+}
+
+static int plan_build(ctba_problem* p, BandPlan& pl, const BandLayout& B) {
+  pl.nbc = B.nbc; pl.nbw = B.nbw; pl.req = p->band_partitions; pl.band_ptr = B.band; pl.border_ptr = B.border;
+  pl.P = choose_partitions(B.nbc, B.nbw, p->band_partitions);
+  CTBA_CUDA(p, pl.dinv.resize((size_t)B.nbc * 1024));
+  CTBA_CUDA(p, pl.cpart.resize((size_t)cdiv(B.n_pad, 256) * 256));
+  pl.PS = BandParts{};
+  if (pl.P == 1) {
+    pl.PS.P = 1;
+    pl.PS.part[0] = BandPart{0, B.nbc, 1, B.nbc, B.n_pad, B.border};
+    pl.max_steps = B.nbc;
+    return CTBA_OK;
+  }
+  const int P = pl.P, nbw = B.nbw;
+  const int interior = B.nbc - (P - 1) * nbw;
+  size_t fb_total = 0, gram_total = 0;
+  std::vector<size_t> fb_off(P), g_off(P);
+  int c = 0, maxI = 0;
+  pl.PS.P = P;
+  for (int q = 0; q < P; ++q) {
+    const int nI = interior / P + (q < interior % P ? 1 : 0);
+    BandPart& Q = pl.PS.part[q];
+    Q.c0 = c; Q.nI = nI; Q.nrb = (q == 0 ? 1 : nbw + 1); Q.ncols = nI + (q < P - 1 ? nbw : 0); Q.ld = kNB * Q.ncols; Q.fb = nullptr;
+    fb_off[q] = fb_total; fb_total += (size_t)Q.nrb * kNB * Q.ld;
+    g_off[q] = gram_total; gram_total += (size_t)(Q.nrb * kNB) * (Q.nrb * kNB);
+    c += nI + nbw;
+    maxI = std::max(maxI, nI);
+  }
+  pl.max_steps = maxI + 1;   // + the flush step that applies the last interior column's update to the right separator
+  CTBA_CUDA(p, pl.fb.resize(fb_total)); CTBA_CUDA(p, pl.gram.resize(gram_total));
+  pl.GP = GramPlan{}; pl.GP.P = P;
+  int tiles = 0, tasks = 0;
+  for (int q = 0; q < P; ++q) {
+    BandPart& Q = pl.PS.part[q];
+    Q.fb = pl.fb.p + fb_off[q];
+    pl.IA.gram_off[q] = g_off[q];
+    const int nt = Q.nrb * (Q.nrb + 1) / 2, ns = (Q.nI + kGramChunk - 1) / kGramChunk;
+    pl.GP.tile0[q] = tiles; pl.GP.task0[q] = tasks; pl.GP.nsplit[q] = ns;
+    tiles += nt; tasks += nt * ns;
+  }
+  pl.GP.tile0[P] = tiles; pl.GP.task0[P] = tasks;
+  pl.gram_tiles = tiles; pl.gram_tasks = tasks;
+  pl.IA.gram = pl.gram.p;
+  CTBA_CUDA(p, pl.gram_scratch.resize((size_t)tasks * 1024));
+  if (!pl.d_gram_off) CTBA_CUDA(p, cudaMalloc((void**)&pl.d_gram_off, kMaxParts * sizeof(size_t)));
+  CTBA_CUDA(p, cudaMemcpy(pl.d_gram_off, g_off.data(), P * sizeof(size_t), cudaMemcpyHostToDevice));
+  // interface system
+  BandLayout& B2 = pl.B2;
+  B2.nbc = (P - 1) * nbw; B2.n_pad = B2.nbc * kNB; B2.n_band = B2.n_pad; B2.nbw = std::min(2 * nbw - 1, B2.nbc - 1);
+  CTBA_CUDA(p, pl.band2.resize(B2.band_elems())); CTBA_CUDA(p, pl.border2.resize((size_t)kBorder * B2.n_pad)); CTBA_CUDA(p, pl.corner2.resize(kBorder * kBorder));
+  CTBA_CUDA(p, pl.delta2.resize(B2.n_pad + kBorder)); CTBA_CUDA(p, pl.dinv2.resize((size_t)B2.nbc * 1024));
+  CTBA_CUDA(p, pl.cpart2.resize((size_t)cdiv(B2.n_pad, 256) * 256));
+  B2.band = pl.band2.p; B2.border = pl.border2.p; B2.corner = pl.corner2.p;
+  pl.PS2 = BandParts{}; pl.PS2.P = 1;
+  pl.PS2.part[0] = BandPart{0, B2.nbc, 1, B2.nbc, B2.n_pad, B2.border};
+  return CTBA_OK;
+}
+
+static int enqueue_steps(ctba_problem* p, cudaStream_t st, const BandLayout& B, const BandParts& PS, int nsteps, double* dinv, int64_t* nl) {
   SolverData* sd = p->solver;
-  BandLayout& B = sd->Hw;
-  CTBA_CUDA(p, cudaMemsetAsync(sd->flag.p, 0, 4 * sizeof(int32_t), st));
-  for (int j = 0; j < B.nbc; ++j) {
-    const int rows = std::min(B.nbw, B.nbc - 1 - j);
-    int grid = rows + 2;
-    if (j > 0) { const int m = std::min(B.nbw - 1, B.nbc - 1 - j); if (m > 0) grid += m * (m + 1) / 2 + m; }
+  for (int t = 0; t < nsteps; ++t) {
+    int grid = 0;
+    for (int q = 0; q < PS.P; ++q) grid += part_task_total(B, PS.part[q], t);
+    if (grid == 0) continue;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kStepThreads); cfg.dynamicSmemBytes = 0; cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
-    const int pdl = (j > 0) ? p->band_pdl : 0;   // column 0 follows non-kernel work: plain stream order
+    const int pdl = (t > 0) ? p->band_pdl : 0;   // step 0 follows non-step work: plain stream order
     cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
-    CTBA_CUDA(p, cudaLaunchKernelEx(&cfg, k_band_step, B, j, sd->dinv.p, sd->flag.p, pdl));
+    CTBA_CUDA(p, cudaLaunchKernelEx(&cfg, k_band_step, B, PS, t, dinv, sd->flag.p, pdl));
+    ++*nl;
   }
+  return CTBA_OK;
+}
+
+static int enqueue_backsolve(ctba_problem* p, cudaStream_t st, const BandLayout& B, const BandParts& PS, const double* dinv, double* delta, int64_t* nl) {
+  k_back_rhs<<<cdiv(B.n_pad, 256), 256, 0, st>>>(B, PS, delta);
+  const int nb1 = B.nbw + 1;
+  const int nwarps = 1 + std::max(1, (B.nbw + kBackCtas - 1) / kBackCtas);   // <= 9 for nbw <= 63
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(kBackCtas * PS.P); cfg.blockDim = dim3(32 * nwarps); cfg.stream = st;
+  cfg.dynamicSmemBytes = (size_t)(nb1 + nwarps + 2 * kBackCtas + 1) * kNB * sizeof(double);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kBackCtas; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  CTBA_CUDA(p, cudaLaunchKernelEx(&cfg, k_band_backsolve, B, PS, dinv, delta));
+  *nl += 2;
+  return CTBA_OK;
+}
+
+// factor + solve of a system that is ONE partition (the whole system when P == 1, the interface system otherwise)
+static int enqueue_single(ctba_problem* p, cudaStream_t st, const BandLayout& B, const BandParts& PS1, double* dinv, double* delta, double* cpart, int64_t* nl) {
+  SolverData* sd = p->solver;
+  int rc = enqueue_steps(p, st, B, PS1, B.nbc, dinv, nl); if (rc) return rc;
   const int nblk = cdiv(B.n_pad, 256);
-  k_corner_partial<<<nblk, 256, 0, st>>>(B, sd->corner_partial.p);
-  k_corner_solve<<<1, 256, 0, st>>>(B, nblk, sd->corner_partial.p, sd->delta.p, sd->flag.p);
-  k_back_rhs<<<cdiv(B.n_pad, 256), 256, 0, st>>>(B, sd->delta.p);
-  {
-    const int nb1 = B.nbw + 1;
-    const int nwarps = 1 + std::max(1, (B.nbw + kBackCtas - 1) / kBackCtas);   // <= 5 for nbw <= 31
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(kBackCtas); cfg.blockDim = dim3(32 * nwarps); cfg.stream = st;
-    cfg.dynamicSmemBytes = (size_t)(nb1 + nwarps + 2 * kBackCtas + 1) * kNB * sizeof(double);
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = kBackCtas; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    CTBA_CUDA(p, cudaLaunchKernelEx(&cfg, k_band_backsolve, B, (const double*)sd->dinv.p, sd->delta.p));
+  k_corner_partial<<<nblk, 256, 0, st>>>(B, cpart);
+  k_corner_solve<<<1, 256, 0, st>>>(B, nblk, cpart, delta, sd->flag.p);
+  *nl += 2;
+  return enqueue_backsolve(p, st, B, PS1, dinv, delta, nl);
+}
+
+static int band_enqueue(ctba_problem* p, cudaStream_t st, BandPlan& pl, int64_t* nl) {
+  SolverData* sd = p->solver;
+  BandLayout& B = sd->Hw;
+  CTBA_CUDA(p, cudaMemsetAsync(sd->flag.p, 0, 4 * sizeof(int32_t), st));
+  int rc;
+  if (pl.P == 1) {
+    rc = enqueue_single(p, st, B, pl.PS, pl.dinv.p, sd->delta.p, pl.cpart.p, nl); if (rc) return rc;
+  } else {
+    int nblk = 0;
+    for (int q = 0; q < pl.P; ++q) nblk += pl.PS.part[q].nrb * pl.PS.part[q].ncols;
+    k_fb_init<<<nblk, 256, 0, st>>>(B, pl.PS);
+    ++*nl;
+    rc = enqueue_steps(p, st, B, pl.PS, pl.max_steps, pl.dinv.p, nl); if (rc) return rc;
+    k_gram_partial<<<pl.gram_tasks, kStepThreads, 0, st>>>(pl.PS, pl.GP, pl.gram_scratch.p);
+    k_gram_reduce<<<pl.gram_tiles, 256, 0, st>>>(pl.PS, pl.GP, pl.gram_scratch.p, pl.gram.p, pl.d_gram_off);
+    const BandLayout& B2 = pl.B2;
+    k_iface_assemble<<<B2.nbc * (B2.nbw + 1) + B2.nbc + 1, 256, 0, st>>>(B, B2, pl.PS, pl.IA);
+    *nl += 3;
+    rc = enqueue_single(p, st, B2, pl.PS2, pl.dinv2.p, pl.delta2.p, pl.cpart2.p, nl); if (rc) return rc;
+    k_iface_scatter<<<cdiv(B2.n_pad + kBorder, 256), 256, 0, st>>>(B, B2, pl.PS, pl.delta2.p, sd->delta.p);
+    ++*nl;
+    rc = enqueue_backsolve(p, st, B, pl.PS, pl.dinv.p, sd->delta.p, nl); if (rc) return rc;
   }
   CTBA_CUDA(p, cudaGetLastError());
   return CTBA_OK;
@@ -448,25 +809,32 @@ static int band_enqueue(ctba_problem* p, cudaStream_t st) {
 void band_graph_release(SolverData* sd) {
   if (sd->band_graph_exec) { cudaGraphExecDestroy((cudaGraphExec_t)sd->band_graph_exec); sd->band_graph_exec = nullptr; }
 }
+void band_plan_release(SolverData* sd) {
+  band_graph_release(sd);
+  if (sd->band_plan) { delete (BandPlan*)sd->band_plan; sd->band_plan = nullptr; }
+}
 
 // Factor + solve.  The launch sequence depends only on the band structure and the buffer addresses, so it is captured once into a
-// CUDA graph (cheaper kernel-to-kernel hand-over than 400+ stream launches) and replayed every LM iteration.
+// CUDA graph (cheaper kernel-to-kernel hand-over than hundreds of stream launches) and replayed every LM iteration.
 int band_factor_solve(ctba_problem* p) {
   SolverData* sd = p->solver;
   cudaStream_t st = p->stream;
   BandLayout& B = sd->Hw;
-  if (B.nbw + 1 > 32) { p->err = "band_factor_solve: band wider than 31 blocks of 32 scalars"; return CTBA_E_ARG; }
-  const bool fresh = sd->dinv.n < (size_t)B.nbc * 1024 || sd->corner_partial.n < (size_t)cdiv(B.n_pad, 256) * 256;
-  CTBA_CUDA(p, sd->dinv.resize((size_t)B.nbc * 1024));
-  CTBA_CUDA(p, sd->corner_partial.resize((size_t)cdiv(B.n_pad, 256) * 256));
-  p->launches += B.nbc + 4;
-  if (!p->band_graph) return band_enqueue(p, st);
+  if (B.nbw + 1 > 64) { p->err = "band_factor_solve: band wider than 63 blocks of 32 scalars"; return CTBA_E_ARG; }
+  if (!sd->band_plan) sd->band_plan = new BandPlan();
+  BandPlan& pl = *(BandPlan*)sd->band_plan;
+  if (pl.nbc != B.nbc || pl.nbw != B.nbw || pl.req != p->band_partitions || pl.band_ptr != B.band || pl.border_ptr != B.border) {
+    band_graph_release(sd);
+    const int rc = plan_build(p, pl, B); if (rc) return rc;
+  }
+  int64_t nl = 0;
+  if (!p->band_graph) { const int rc = band_enqueue(p, st, pl, &nl); p->launches += nl; sd->band_launches = nl; return rc; }
   const int key = p->band_pdl;
-  if (fresh || sd->band_graph_key != key) band_graph_release(sd);
+  if (sd->band_graph_key != key) band_graph_release(sd);
   if (!sd->band_graph_exec) {
     cudaGraph_t graph = nullptr;
     CTBA_CUDA(p, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-    const int rc = band_enqueue(p, st);
+    const int rc = band_enqueue(p, st, pl, &nl);
     const cudaError_t e = cudaStreamEndCapture(st, &graph);
     if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
     CTBA_CUDA(p, e);
@@ -474,8 +842,9 @@ int band_factor_solve(ctba_problem* p) {
     const cudaError_t ei = cudaGraphInstantiate(&exec, graph, 0);
     cudaGraphDestroy(graph);
     CTBA_CUDA(p, ei);
-    sd->band_graph_exec = exec; sd->band_graph_key = key;
+    sd->band_graph_exec = exec; sd->band_graph_key = key; sd->band_launches = nl;
   }
+  p->launches += sd->band_launches;
   CTBA_CUDA(p, cudaGraphLaunch((cudaGraphExec_t)sd->band_graph_exec, st));
   return CTBA_OK;
 }

@@ -78,6 +78,7 @@ struct ctba_problem {
   double cauchy_a = 3.0;
   bool bench_no_termination = false;
   int band_pdl = 2;        // programmatic dependent launch between the block-column kernels (0 off, 1 trigger at entry, 2 after staging)
+  int band_partitions = 0; // time partitions of the band factorisation: 0 = automatic, k = force k (1 = plain sequential)
   bool band_graph = true;  // replay the factor+solve launch sequence as a CUDA graph
 
   // ---- host work items ----

@@ -19,9 +19,9 @@ static inline int cdiv(size_t a, int b) { return (int)((a + b - 1) / b); }
 
 void solver_free(SolverData* sd) {
   if (!sd) return;
-  band_graph_release(sd);
+  band_plan_release(sd);
   DBuf<double>* dd[] = {&sd->band0, &sd->bandw, &sd->border0, &sd->borderw, &sd->corner0, &sd->cornerw, &sd->grad, &sd->V0, &sd->gl, &sd->Sp, &sd->Sb,
-                        &sd->rp, &sd->dinv, &sd->corner_partial, &sd->Vi, &sd->vig, &sd->ViYg, &sd->Yo, &sd->Zo, &sd->lm_corner_partial, &sd->jscale, &sd->jscale_lm, &sd->delta, &sd->delta_lm, &sd->dpose, &sd->scal, &sd->cand.knot_q, &sd->cand.knot_p,
+                        &sd->rp, &sd->Vi, &sd->vig, &sd->ViYg, &sd->Yo, &sd->Zo, &sd->lm_corner_partial, &sd->jscale, &sd->jscale_lm, &sd->delta, &sd->delta_lm, &sd->dpose, &sd->scal, &sd->cand.knot_q, &sd->cand.knot_p,
                         &sd->cand.bias_a, &sd->cand.bias_g, &sd->cand.lm, &sd->cand.glb};
   for (auto* d : dd) d->release();
   DBuf<int32_t>* di[] = {&sd->d_node_of_knot, &sd->d_node_of_bias, &sd->d_lm_obs_begin, &sd->d_lm_obs, &sd->d_o_pos, &sd->d_lm_frame, &sd->d_kf_begin, &sd->d_kf_list, &sd->flag};

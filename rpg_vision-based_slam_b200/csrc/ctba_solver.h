@@ -61,10 +61,10 @@ struct SolverData {
   DBuf<double> jscale, jscale_lm;   // Jacobi scaling (fixed per Solve): n_pad+16, 3L
   DBuf<double> delta, delta_lm;     // step: n_pad+16, 3L
   DBuf<double> dpose;               // per frame 6: pose-space step
-  DBuf<double> corner_partial;      // k_corner_partial scratch
+  void* band_plan = nullptr;        // BandPlan (ctba_band.cu): time partitions, interface system, scratch
+  int64_t band_launches = 0;        // kernels in one factor+solve
   void* band_graph_exec = nullptr;  // cudaGraphExec_t of the factor+solve launch sequence (band_factor_solve)
   int band_graph_key = -1;
-  DBuf<double> dinv;                // nbc x 32x32: L_jj^-1 of every diagonal block (backward substitution)
   DBuf<double> scal;                // small scalar outputs (see SC_* in ctba_solve.cu)
   DBuf<int32_t> flag;               // numeric failure flag
   DeviceState cand;
@@ -80,6 +80,7 @@ int backsub_and_candidate(ctba_problem* p, const StatePtrs& S, const StatePtrs& 
 int step_scalars(ctba_problem* p, const StatePtrs& S, const StatePtrs& C, double radius);
 int band_factor_solve(ctba_problem* p);                          // ctba_band.cu
 void band_graph_release(SolverData* sd);
+void band_plan_release(SolverData* sd);
 
 enum { SC_MODEL = 0, SC_STEP2 = 1, SC_XNORM2 = 2, SC_GMAX = 3, SC_COUNT = 8 };
 
