@@ -213,6 +213,7 @@ __host__ __device__ inline int part_task_total(const BandLayout& B, const BandPa
   return np + m * (m + 1) / 2 + m * q.nrb;
 }
 
+
 #ifdef CTBA_BAND_TIMING
 __device__ long long g_band_clk[8];
 #define BAND_CLK(k) do { if (j == 100 && b == 1 && tid == 0) g_band_clk[k] = clock64(); } while (0)
@@ -220,32 +221,28 @@ __device__ long long g_band_clk[8];
 #define BAND_CLK(k) do {} while (0)
 #endif
 
-// One launch per step t: every partition p advances to its block column j = c0_p + t (right-looking with a one-column look-ahead):
-//   panel CTAs   : apply column j-1's update to THEIR block of column j (and to the diagonal block, redundantly), factor the diagonal block,
-//                  triangular-solve their block, store it.  Task 0 = diagonal (also stores L_jj^-1 for the backward substitution),
-//                  tasks 1..rows = sub-diagonal blocks, then one task per border row block.
-//   update CTAs  : remaining trailing update of column j-1:  T(i,k) -= L(i,j-1) L(k,j-1)^T  for k_lo <= k <= i <= j-1+nbw, and the border
-//                  row blocks of those block columns.  k_lo = j+1 while the partition still has a panel (the panel CTAs cover column j),
-//                  k_lo = j in the partition's final flush step t = |I_p|.
-// Pre-condition of step t: columns < j of the interior final, every trailing block carries the updates of columns <= j-2.
-__global__ void __launch_bounds__(kStepThreads) k_band_step(BandLayout B, const __grid_constant__ BandParts PS, int t, double* __restrict__ dinv,
-                                                            int32_t* __restrict__ flag, int pdl) {
+// Two launches per step t (they run concurrently, on two streams / two graph branches): every partition p advances to its block column
+// j = c0_p + t (right-looking with a one-column look-ahead):
+//   k_band_panel  : apply column j-1's update to the CTA's OWN block of column j (and to the diagonal block, redundantly), factor the diagonal
+//                   block, triangular-solve the block, store it.  Task 0 = diagonal (also stores L_jj^-1 for the backward substitution),
+//                   tasks 1..rows = sub-diagonal blocks, then one task per border row block.  This is the critical path.
+//   k_band_update : remaining trailing update of column j-1:  T(i,k) -= L(i,j-1) L(k,j-1)^T  for k_lo <= k <= i <= j-1+nbw, and the border
+//                   row blocks of those block columns.  k_lo = j+1 while the partition still has a panel (the panel CTAs cover column j),
+//                   k_lo = j in the partition's final flush step t = |I_p|.  Small register footprint, so that many CTAs are resident.
+// Both depend on BOTH kernels of step t-1.  Pre-condition of step t: columns < j of the interior final, every trailing block carries the
+// updates of columns <= j-2.
+__global__ void __launch_bounds__(kStepThreads) k_band_panel(BandLayout B, const __grid_constant__ BandParts PS, int t, double* __restrict__ dinv,
+                                                             int32_t* __restrict__ flag) {
   __shared__ double sD[kNB * kLd];
   __shared__ double sX[kNB * kLd];
   __shared__ double sRinv[kNB];
-  // programmatic dependent launch (pdl != 0): the next step's grid may become resident early (pdl 1: now; pdl 2: once this CTA has staged its
-  // operands); it waits here until the previous step's grid has completed and flushed.  Without the launch attribute both are no-ops.
-  if (pdl == 1) asm volatile("griddepcontrol.launch_dependents;");
-  if (pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nb1 = B.nbw + 1;
-  // ---- which partition, which task ----
   int b = blockIdx.x, pi = 0, n_panel = 0, m = 0, k_lo = 0;
   for (; pi < PS.P; ++pi) {
     part_tasks(B, PS.part[pi], t, &n_panel, &m, &k_lo);
-    const int tot = n_panel + m * (m + 1) / 2 + m * PS.part[pi].nrb;
-    if (b < tot) break;
-    b -= tot;
+    if (b < n_panel) break;
+    b -= n_panel;
   }
   if (pi >= PS.P) return;
   const BandPart& Q = PS.part[pi];
@@ -253,92 +250,88 @@ __global__ void __launch_bounds__(kStepThreads) k_band_step(BandLayout B, const 
   const bool prev = t > 0 && B.nbw >= 1;
   const double* Lprev = B.band + ((size_t)max(j - 1, 0) * nb1) * 1024;  // column j-1: block (j-1+o, j-1) at offset o
   const int lcol = j - Q.c0;                                            // column of fb
-  if (b < n_panel) {
-    // ---------------- panel ----------------
-    const int rows = n_panel - 1 - Q.nrb;
-    double* Ajj = B.band + ((size_t)j * nb1) * 1024;
-    BAND_CLK(0);
-    int rb = -1, nrows = kNB;
-    double* Fb = nullptr;
-    if (b == 0) {
-      panel_stage(sD, sX, Ajj, Lprev + 1024, prev, false, nullptr, 0, nullptr, 0, 0, false, warp, lane);
-      // identity right-hand side: X L^T = I gives X = L_jj^-T, whose transpose L_jj^-1 is kept for the backward substitution
-      for (int e = tid; e < kNB * kNB; e += kStepThreads) sX[(e >> 5) * kLd + (e & 31)] = ((e >> 5) == (e & 31)) ? 1.0 : 0.0;
-    } else if (b <= rows) {
-      const bool have_prev = prev && (b + 1 <= B.nbw);   // block (j+b, j-1) lies inside the band
-      panel_stage(sD, sX, Ajj, Lprev + 1024, prev, true, Ajj + (size_t)b * 1024, kNB, Lprev + (size_t)min(b + 1, B.nbw) * 1024, kNB, kNB, have_prev,
-                  warp, lane);
-    } else {
-      rb = b - rows - 1;
-      nrows = (rb == Q.nrb - 1) ? kBorder : kNB;
-      Fb = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)lcol * kNB;
-      panel_stage(sD, sX, Ajj, Lprev + 1024, prev, true, Fb, Q.ld, Fb - kNB, Q.ld, nrows, prev, warp, lane);
-    }
-    __syncthreads();
-    if (pdl == 2) asm volatile("griddepcontrol.launch_dependents;");
-    BAND_CLK(1);
-    potrf_trsm32_cta(sD, sX, sRinv, warp, lane, flag);
-    BAND_CLK(2);
-    __syncthreads();
-    BAND_CLK(3);
-    if (b == 0) {
-      for (int e = tid; e < kNB * kNB; e += kStepThreads) {
-        const int r = e >> 5, c = e & 31;
-        Ajj[e] = sD[r * kLd + c];
-        dinv[(size_t)j * 1024 + e] = sX[c * kLd + r];   // (L^-1)[r][c] = X[c][r]
-      }
-    } else if (b <= rows) {
-      double* Lij = Ajj + (size_t)b * 1024;
-      for (int e = tid; e < kNB * kNB; e += kStepThreads) Lij[e] = sX[(e >> 5) * kLd + (e & 31)];
-      BAND_CLK(4);
-    } else {
-      for (int e = tid; e < nrows * kNB; e += kStepThreads) { const int r = e >> 5, c = e & 31; Fb[(size_t)r * Q.ld + c] = sX[r * kLd + c]; }
-    }
-    return;
+  const int rows = n_panel - 1 - Q.nrb;
+  double* Ajj = B.band + ((size_t)j * nb1) * 1024;
+  BAND_CLK(0);
+  int rb = -1, nrows = kNB;
+  double* Fb = nullptr;
+  if (b == 0) {
+    panel_stage(sD, sX, Ajj, Lprev + 1024, prev, false, nullptr, 0, nullptr, 0, 0, false, warp, lane);
+    // identity right-hand side: X L^T = I gives X = L_jj^-T, whose transpose L_jj^-1 is kept for the backward substitution
+    for (int e = tid; e < kNB * kNB; e += kStepThreads) sX[(e >> 5) * kLd + (e & 31)] = ((e >> 5) == (e & 31)) ? 1.0 : 0.0;
+  } else if (b <= rows) {
+    const bool have_prev = prev && (b + 1 <= B.nbw);   // block (j+b, j-1) lies inside the band
+    panel_stage(sD, sX, Ajj, Lprev + 1024, prev, true, Ajj + (size_t)b * 1024, kNB, Lprev + (size_t)min(b + 1, B.nbw) * 1024, kNB, kNB, have_prev,
+                warp, lane);
+  } else {
+    rb = b - rows - 1;
+    nrows = (rb == Q.nrb - 1) ? kBorder : kNB;
+    Fb = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)lcol * kNB;
+    panel_stage(sD, sX, Ajj, Lprev + 1024, prev, true, Fb, Q.ld, Fb - kNB, Q.ld, nrows, prev, warp, lane);
   }
-  // ---------------- trailing update of column j-1 ----------------
-  if (pdl == 2) asm volatile("griddepcontrol.launch_dependents;");
-  int u = b - n_panel;
+  __syncthreads();
+  BAND_CLK(1);
+  potrf_trsm32_cta(sD, sX, sRinv, warp, lane, flag);
+  BAND_CLK(2);
+  __syncthreads();
+  BAND_CLK(3);
+  if (b == 0) {
+    for (int e = tid; e < kNB * kNB; e += kStepThreads) {
+      const int r = e >> 5, c = e & 31;
+      Ajj[e] = sD[r * kLd + c];
+      dinv[(size_t)j * 1024 + e] = sX[c * kLd + r];   // (L^-1)[r][c] = X[c][r]
+    }
+  } else if (b <= rows) {
+    double* Lij = Ajj + (size_t)b * 1024;
+    for (int e = tid; e < kNB * kNB; e += kStepThreads) Lij[e] = sX[(e >> 5) * kLd + (e & 31)];
+    BAND_CLK(4);
+  } else {
+    for (int e = tid; e < nrows * kNB; e += kStepThreads) { const int r = e >> 5, c = e & 31; Fb[(size_t)r * Q.ld + c] = sX[r * kLd + c]; }
+  }
+}
+
+__global__ void __launch_bounds__(kStepThreads, 4) k_band_update(BandLayout B, const __grid_constant__ BandParts PS, int t) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nb1 = B.nbw + 1;
+  int u = blockIdx.x, pi = 0, n_panel = 0, m = 0, k_lo = 0;
+  for (; pi < PS.P; ++pi) {
+    part_tasks(B, PS.part[pi], t, &n_panel, &m, &k_lo);
+    const int nu = m * (m + 1) / 2 + m * PS.part[pi].nrb;
+    if (u < nu) break;
+    u -= nu;
+  }
+  if (pi >= PS.P) return;
+  const BandPart& Q = PS.part[pi];
+  const int j = Q.c0 + t;
+  const double* Lprev = B.band + ((size_t)(j - 1) * nb1) * 1024;  // column j-1: block (j-1+o, j-1) at offset o
   const int ntri = m * (m + 1) / 2;
-  const int g = lane >> 2, tq = lane & 3;
+  const int g = lane >> 2, tq = lane & 3, tr = warp >> 1;
+  const double* A; const double* Lk; double* T; int lda, ldt, nrows = kNB;
   if (u < ntri) {
     int a = (int)((sqrtf(8.0f * u + 1.0f) - 1.0f) * 0.5f);
     while ((a + 1) * (a + 2) / 2 <= u) ++a;
     while (a * (a + 1) / 2 > u) --a;
     const int c = u - a * (a + 1) / 2;          // 0 <= c <= a < m
     const int i = k_lo + a, k = k_lo + c;
-    const double* Li = Lprev + (size_t)(i - (j - 1)) * 1024;
-    const double* Lk = Lprev + (size_t)(k - (j - 1)) * 1024;
-    double* T = B.band + ((size_t)k * nb1 + (i - k)) * 1024;
-    const int tr = warp >> 1;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int tc = 2 * (warp & 1) + h;
-      double c0 = 0.0, c1 = 0.0;
-      tile_abt(Li, kNB, Lk, kNB, tr, tc, lane, c0, c1);
-      double2* dst = reinterpret_cast<double2*>(T + (size_t)(8 * tr + g) * kNB + 8 * tc + 2 * tq);
-      double2 v = *dst; v.x -= c0; v.y -= c1; *dst = v;
-    }
-    return;
-  }
-  u -= ntri;
-  if (u < m * Q.nrb) {   // border row block rb of block column k
+    A = Lprev + (size_t)(i - (j - 1)) * 1024; lda = kNB;
+    Lk = Lprev + (size_t)(k - (j - 1)) * 1024;
+    T = B.band + ((size_t)k * nb1 + (i - k)) * 1024; ldt = kNB;
+  } else {                                      // border row block rb of block column k
+    u -= ntri;
     const int k = k_lo + u / Q.nrb, rb = u % Q.nrb;
-    const int nrows = (rb == Q.nrb - 1) ? kBorder : kNB;
-    const double* Lk = Lprev + (size_t)(k - (j - 1)) * 1024;
-    const double* Fprev = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)(lcol - 1) * kNB;
-    double* Fk = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)(k - Q.c0) * kNB;
-    const int tr = warp >> 1;
-    if (8 * tr < nrows) {
+    nrows = (rb == Q.nrb - 1) ? kBorder : kNB;
+    Lk = Lprev + (size_t)(k - (j - 1)) * 1024;
+    A = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)(j - 1 - Q.c0) * kNB; lda = Q.ld;
+    T = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)(k - Q.c0) * kNB; ldt = Q.ld;
+  }
+  if (8 * tr >= nrows) return;   // warp-uniform
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int tc = 2 * (warp & 1) + h;
-        double c0 = 0.0, c1 = 0.0;
-        tile_abt(Fprev, Q.ld, Lk, kNB, tr, tc, lane, c0, c1);
-        double2* dst = reinterpret_cast<double2*>(Fk + (size_t)(8 * tr + g) * Q.ld + 8 * tc + 2 * tq);
-        double2 v = *dst; v.x -= c0; v.y -= c1; *dst = v;
-      }
-    }
+  for (int h = 0; h < 2; ++h) {
+    const int tc = 2 * (warp & 1) + h;
+    double c0 = 0.0, c1 = 0.0;
+    tile_abt(A, lda, Lk, kNB, tr, tc, lane, c0, c1);
+    double2* dst = reinterpret_cast<double2*>(T + (size_t)(8 * tr + g) * ldt + 8 * tc + 2 * tq);
+    double2 v = *dst; v.x -= c0; v.y -= c1; *dst = v;
   }
 }
 
@@ -733,22 +726,30 @@ static int plan_build(ctba_problem* p, BandPlan& pl, const BandLayout& B) {
   return CTBA_OK;
 }
 
+// Step launches on two streams (inside a capture: two graph branches): the panel kernel on `st`, the update kernel on the side stream.
+// Each kernel of step t waits for both kernels of step t-1.
 static int enqueue_steps(ctba_problem* p, cudaStream_t st, const BandLayout& B, const BandParts& PS, int nsteps, double* dinv, int64_t* nl) {
   SolverData* sd = p->solver;
+  cudaStream_t s2 = (cudaStream_t)sd->band_stream2;
+  cudaEvent_t evA = (cudaEvent_t)sd->band_evA, evB = (cudaEvent_t)sd->band_evB;
+  CTBA_CUDA(p, cudaEventRecord(evA, st));
+  CTBA_CUDA(p, cudaStreamWaitEvent(s2, evA, 0));       // fork
   for (int t = 0; t < nsteps; ++t) {
-    int grid = 0;
-    for (int q = 0; q < PS.P; ++q) grid += part_task_total(B, PS.part[q], t);
-    if (grid == 0) continue;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kStepThreads); cfg.dynamicSmemBytes = 0; cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    const int pdl = (t > 0) ? p->band_pdl : 0;   // step 0 follows non-step work: plain stream order
-    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
-    CTBA_CUDA(p, cudaLaunchKernelEx(&cfg, k_band_step, B, PS, t, dinv, sd->flag.p, pdl));
-    ++*nl;
+    int gp = 0, gu = 0;
+    for (int q = 0; q < PS.P; ++q) {
+      int np, m, kl;
+      part_tasks(B, PS.part[q], t, &np, &m, &kl);
+      gp += np; gu += m * (m + 1) / 2 + m * PS.part[q].nrb;
+    }
+    if (gp == 0 && gu == 0) continue;
+    if (t > 0) { CTBA_CUDA(p, cudaStreamWaitEvent(st, evB, 0)); CTBA_CUDA(p, cudaStreamWaitEvent(s2, evA, 0)); }
+    if (gp) { k_band_panel<<<gp, kStepThreads, 0, st>>>(B, PS, t, dinv, sd->flag.p); ++*nl; }
+    if (gu) { k_band_update<<<gu, kStepThreads, 0, s2>>>(B, PS, t); ++*nl; }
+    CTBA_CUDA(p, cudaEventRecord(evA, st));
+    CTBA_CUDA(p, cudaEventRecord(evB, s2));
   }
+  CTBA_CUDA(p, cudaStreamWaitEvent(st, evB, 0));       // join
+  CTBA_CUDA(p, cudaGetLastError());
   return CTBA_OK;
 }
 
@@ -812,6 +813,10 @@ void band_graph_release(SolverData* sd) {
 void band_plan_release(SolverData* sd) {
   band_graph_release(sd);
   if (sd->band_plan) { delete (BandPlan*)sd->band_plan; sd->band_plan = nullptr; }
+  if (sd->band_stream2) {
+    cudaStreamDestroy((cudaStream_t)sd->band_stream2); cudaEventDestroy((cudaEvent_t)sd->band_evA); cudaEventDestroy((cudaEvent_t)sd->band_evB);
+    sd->band_stream2 = nullptr;
+  }
 }
 
 // Factor + solve.  The launch sequence depends only on the band structure and the buffer addresses, so it is captured once into a
@@ -822,6 +827,13 @@ int band_factor_solve(ctba_problem* p) {
   BandLayout& B = sd->Hw;
   if (B.nbw + 1 > 64) { p->err = "band_factor_solve: band wider than 63 blocks of 32 scalars"; return CTBA_E_ARG; }
   if (!sd->band_plan) sd->band_plan = new BandPlan();
+  if (!sd->band_stream2) {
+    cudaStream_t s2; cudaEvent_t ea, eb;
+    CTBA_CUDA(p, cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking));
+    CTBA_CUDA(p, cudaEventCreateWithFlags(&ea, cudaEventDisableTiming));
+    CTBA_CUDA(p, cudaEventCreateWithFlags(&eb, cudaEventDisableTiming));
+    sd->band_stream2 = s2; sd->band_evA = ea; sd->band_evB = eb;
+  }
   BandPlan& pl = *(BandPlan*)sd->band_plan;
   if (pl.nbc != B.nbc || pl.nbw != B.nbw || pl.req != p->band_partitions || pl.band_ptr != B.band || pl.border_ptr != B.border) {
     band_graph_release(sd);
