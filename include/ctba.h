@@ -34,7 +34,8 @@ enum {
 enum { CTBA_REPROJ = 0, CTBA_ACCEL = 1, CTBA_GYRO = 2, CTBA_GP = 3, CTBA_BIAS = 4, CTBA_GRAVITY = 5 };
 
 /* BSplineSO3R3<N>::BSplineSO3R3(time_interval_ns, start_time_ns)      bspline_so3r3.h:75-117
- * order N in {4,6}; `device` = CUDA ordinal. */
+ * order N in {4,6}; `device` = CUDA ordinal (-1: planning-only handle — host problem assembly and ctba_shard_plan work,
+ * every compute entry point returns CTBA_E_CUDA). */
 int ctba_create(int order, int64_t dt_ns, int64_t start_t_ns, int device, ctba_problem** out);
 int ctba_destroy(ctba_problem* p);
 const char* ctba_last_error(const ctba_problem* p);
@@ -142,6 +143,26 @@ int ctba_transfer_bytes(ctba_problem* p, int64_t* bytes2);
 /* Device-only benchmarking hooks (inputs already resident): run `reps` passes of the residual+Jacobian
  * kernels (which != 0) or of a full LM iteration, return the kernel launch count. */
 int ctba_bench_evaluate(ctba_problem* p, int reps, int64_t* launches);
+
+/* ---- multi-GPU: ONE problem sharded by time segment over the GPUs of a node --------------------------------
+ * The reference has no counterpart (Ceres runs `num_threads` CPU threads, bspline_so3r3.h:1773).  Every rank (one process per GPU)
+ * makes the SAME calls as a single-GPU caller, with the COMPLETE problem, plus one ctba_comm_init_*; the first ctba_solve /
+ * ctba_evaluate / ctba_cost then keeps only the rank's units (landmarks with all their observations, IMU / GP / bias samples whose
+ * first control point lies in the rank's time segment) and runs the LM loop with five small collectives per iteration.  After
+ * ctba_solve every rank holds the whole optimised state (ctba_get_* as usual).  On a sharded handle ctba_counts / ctba_evaluate
+ * describe the rank's shard; ctba_cost and the summary of ctba_solve describe the whole problem. */
+/* rank 0: 128-byte NCCL unique id, to be broadcast to the other ranks by the caller's own means */
+int ctba_comm_unique_id(char* out128);
+int ctba_comm_init_nccl(ctba_problem* p, int world, int rank, const char* id128);
+/* In-process group for testing on ONE device: `world` handles of one process, each driven by its own host thread (calls that
+ * evaluate or solve are collective: every handle's thread must make them). */
+int ctba_comm_init_local(ctba_problem** handles, int world);
+/* Host-only shard plan of the problem currently held by `p` (works on a planning handle created with device = -1):
+ *   plan[0..15] = P, nbc, nbw, q_lo, q_hi, bc_lo, bc_hi, own_lo, own_hi, F, f_first, f_cost_begin, nodes, hbn, T, KD
+ *   plan[16+2q], plan[17+2q] = first block column and width of the interior of partition q   (plan: 16 + 64 entries)
+ *   *_owner (optional) = owning rank of every landmark / IMU sample / GP sample / bias block */
+int ctba_shard_plan(ctba_problem* p, int world, int rank, int64_t* plan, int32_t* lm_owner, int32_t* imu_owner, int32_t* gp_owner,
+                    int32_t* bias_owner);
 
 #ifdef __cplusplus
 }

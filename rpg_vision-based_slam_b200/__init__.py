@@ -27,6 +27,7 @@ EXPORTS = [
     "ctba_set_camera", "ctba_set_globals", "ctba_set_corrections", "ctba_get_globals", "ctba_set_flags", "ctba_add_frames", "ctba_add_imu",
     "ctba_add_gp", "ctba_add_bias_cost", "ctba_add_gravity_norm", "ctba_counts", "ctba_evaluate", "ctba_cost", "ctba_solve",
     "ctba_relinearize_time_offsets", "ctba_bench_evaluate", "ctba_set_option", "ctba_invalidate_device", "ctba_transfer_bytes",
+    "ctba_comm_unique_id", "ctba_comm_init_nccl", "ctba_comm_init_local", "ctba_shard_plan",
 ]
 
 
@@ -242,6 +243,39 @@ class BSplineSO3R3:
         b = np.zeros(2, dtype=np.int64)
         self._chk(self.L.ctba_transfer_bytes(self.h, _p(b)))
         return int(b[0]), int(b[1])
+
+    # ---- multi-GPU: one problem sharded by time segment (ctba.h, "multi-GPU") ----
+    @staticmethod
+    def commUniqueId():
+        buf = C.create_string_buffer(128)
+        rc = lib().ctba_comm_unique_id(buf)
+        if rc != 0:
+            raise CtbaError(f"ctba_comm_unique_id failed with code {rc} (libnccl.so.2 missing?)")
+        return bytes(buf.raw)
+
+    def initCommNccl(self, world, rank, unique_id):
+        assert len(unique_id) == 128
+        self._chk(self.L.ctba_comm_init_nccl(self.h, int(world), int(rank), C.c_char_p(unique_id)))
+
+    @staticmethod
+    def initCommLocal(problems):
+        arr = (C.c_void_p * len(problems))(*[p.h for p in problems])
+        problems[0]._chk(problems[0].L.ctba_comm_init_local(arr, len(problems)))
+
+    def shardPlan(self, world, rank):
+        c = self.counts()
+        plan = np.zeros(80, dtype=np.int64)
+        lm = np.zeros(max(self._nlm, 1), dtype=np.int32)
+        imu = np.zeros(max(c["accel"], 1), dtype=np.int32)
+        gp = np.zeros(max(c["gp"], 1), dtype=np.int32)
+        bias = np.zeros(max(c["bias"], 1), dtype=np.int32)
+        self._chk(self.L.ctba_shard_plan(self.h, int(world), int(rank), _p(plan), _p(lm), _p(imu), _p(gp), _p(bias)))
+        keys = ["P", "nbc", "nbw", "q_lo", "q_hi", "bc_lo", "bc_hi", "own_lo", "own_hi", "F", "f_first", "f_cost_begin", "nodes", "hbn", "T", "KD"]
+        d = {k: int(v) for k, v in zip(keys, plan[:16])}
+        d["c0"] = [int(plan[16 + 2 * q]) for q in range(d["P"])]
+        d["nI"] = [int(plan[17 + 2 * q]) for q in range(d["P"])]
+        d.update(lm_owner=lm[:self._nlm], imu_owner=imu[:c["accel"]], gp_owner=gp[:c["gp"]], bias_owner=bias[:c["bias"]])
+        return d
 
     def benchEvaluate(self, reps):
         n = C.c_int64(0)

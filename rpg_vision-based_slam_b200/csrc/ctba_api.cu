@@ -3,13 +3,15 @@
 // /root/reference/include/spline/bspline_so3r3.h:355-369, 523-1046, 1807-1875 (cited per function in ctba.h).
 #include <cmath>
 #include <cstring>
-#include "ctba_internal.h"
+#include "ctba_solver.h"
 
 using namespace ctba;
 
 namespace ctba {
 
 int sync_to_device(ctba_problem* p) {
+  if (p->device < 0) { p->err = "planning-only handle (device -1): no compute entry points"; return CTBA_E_CUDA; }
+  if (p->comm && p->comm->world > 1 && !p->sharded) { const int rc = shard_build(p); if (rc) return rc; }
   cudaStream_t st = p->stream;
   if (p->meas_dirty) {
     CTBA_CUDA(p, p->d_f_s.upload(p->f_s, st)); CTBA_CUDA(p, p->d_f_u.upload(p->f_u, st)); CTBA_CUDA(p, p->d_f_inv_std.upload(p->f_inv_std, st));
@@ -43,7 +45,7 @@ int sync_to_device(ctba_problem* p) {
 }
 
 int download_state(ctba_problem* p) {
-  if (!p->host_state_stale) return CTBA_OK;
+  if (!p->host_state_stale || p->device < 0) return CTBA_OK;
   cudaStream_t st = p->stream;
   auto dl = [&](std::vector<double>& h, const DBuf<double>& d) -> cudaError_t {
     if (h.empty()) return cudaSuccess;
@@ -70,22 +72,29 @@ int ctba_create(int order, int64_t dt_ns, int64_t start_t_ns, int device, ctba_p
   *out = nullptr;
   if ((order != 4 && order != 6) || dt_ns <= 0) return CTBA_E_ARG;
   int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) return CTBA_E_CUDA;
-  if (cudaSetDevice(device) != cudaSuccess) return CTBA_E_CUDA;
+  // device == -1: planning-only handle (host problem assembly + ctba_shard_plan; every compute entry point returns CTBA_E_CUDA)
+  if (device != -1 && (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev)) return CTBA_E_CUDA;
+  if (device != -1 && cudaSetDevice(device) != cudaSuccess) return CTBA_E_CUDA;
   ctba_problem* p = new ctba_problem();
   p->N = order; p->dt_ns = dt_ns; p->start_t_ns = start_t_ns; p->device = device;
   p->dt_s = dt_ns * 1e-9;
   p->inv_dt = 1e9 / dt_ns;
-  if (cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking) != cudaSuccess) { delete p; return CTBA_E_CUDA; }
-  p->own_stream = true;
+  if (device != -1) {
+    if (cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking) != cudaSuccess) { delete p; return CTBA_E_CUDA; }
+    p->own_stream = true;
+  }
   *out = p;
   return CTBA_OK;
 }
 
 int ctba_destroy(ctba_problem* p) {
   CHECK_P(p);
-  cudaSetDevice(p->device);
+  if (p->device < 0) { delete p->shard; delete p->gstruct; delete p; return CTBA_OK; }
+  if (p->device >= 0) cudaSetDevice(p->device);
   cudaStreamSynchronize(p->stream);
+  if (p->comm && p->comm_owned) delete p->comm;
+  delete p->shard; delete p->gstruct;
+  p->d_fsq_glob.release(); p->d_gather.release(); p->d_stage.release();
   if (p->solver) solver_free(p->solver);
   DBuf<double>* dd[] = {&p->dstate.knot_q, &p->dstate.knot_p, &p->dstate.bias_a, &p->dstate.bias_g, &p->dstate.lm, &p->dstate.glb,
                         &p->d_f_u, &p->d_f_inv_std, &p->d_o_uv, &p->d_i_st_s, &p->d_i_k, &p->d_i_ub, &p->d_i_inv_a, &p->d_i_inv_g, &p->d_i_acc,
@@ -133,7 +142,7 @@ int ctba_set_knots(ctba_problem* p, int n, const double* q, const double* pos) {
 int ctba_num_knots(const ctba_problem* p) { return p ? (int)p->numKnots() : CTBA_E_ARG; }
 int ctba_get_knots(ctba_problem* p, double* q, double* pos) {
   CHECK_P(p);
-  cudaSetDevice(p->device);
+  if (p->device >= 0) cudaSetDevice(p->device);
   int rc = download_state(p); if (rc) return rc;
   if (q) std::memcpy(q, p->knot_q.data(), p->knot_q.size() * sizeof(double));
   if (pos) std::memcpy(pos, p->knot_p.data(), p->knot_p.size() * sizeof(double));
@@ -158,7 +167,7 @@ int ctba_num_bias_knots(const ctba_problem* p) { return p ? (int)p->numBiasKnots
 int ctba_set_biases(ctba_problem* p, const double* a, const double* g) {
   CHECK_P(p);
   if (!a || !g) return CTBA_E_ARG;
-  cudaSetDevice(p->device);
+  if (p->device >= 0) cudaSetDevice(p->device);
   int rc = download_state(p); if (rc) return rc;
   std::memcpy(p->bias_a.data(), a, p->bias_a.size() * sizeof(double)); std::memcpy(p->bias_g.data(), g, p->bias_g.size() * sizeof(double));
   p->state_dirty = true;
@@ -166,7 +175,7 @@ int ctba_set_biases(ctba_problem* p, const double* a, const double* g) {
 }
 int ctba_get_biases(ctba_problem* p, double* a, double* g) {
   CHECK_P(p);
-  cudaSetDevice(p->device);
+  if (p->device >= 0) cudaSetDevice(p->device);
   int rc = download_state(p); if (rc) return rc;
   if (a) std::memcpy(a, p->bias_a.data(), p->bias_a.size() * sizeof(double));
   if (g) std::memcpy(g, p->bias_g.data(), p->bias_g.size() * sizeof(double));
@@ -177,7 +186,7 @@ int ctba_set_landmarks(ctba_problem* p, int n, const double* xyz) {
   CHECK_P(p);
   if (n < 0 || !xyz) return fail(p, CTBA_E_ARG, "set_landmarks: bad arguments");
   for (int32_t l : p->o_lm) if (l >= n) return fail(p, CTBA_E_ARG, "set_landmarks: existing observations reference a landmark beyond n");
-  cudaSetDevice(p->device);
+  if (p->device >= 0) cudaSetDevice(p->device);
   int rc = download_state(p); if (rc) return rc;
   if ((size_t)n * 3 != p->lm.size()) p->struct_dirty = true;
   p->lm.assign(xyz, xyz + 3 * (size_t)n);
@@ -186,7 +195,7 @@ int ctba_set_landmarks(ctba_problem* p, int n, const double* xyz) {
 }
 int ctba_get_landmarks(ctba_problem* p, double* xyz) {
   CHECK_P(p);
-  cudaSetDevice(p->device);
+  if (p->device >= 0) cudaSetDevice(p->device);
   int rc = download_state(p); if (rc) return rc;
   if (xyz) std::memcpy(xyz, p->lm.data(), p->lm.size() * sizeof(double));
   return CTBA_OK;
@@ -207,7 +216,7 @@ int ctba_set_camera(ctba_problem* p, int model, const double* intr, const double
 int ctba_set_globals(ctba_problem* p, double scale, const double* p_bp, const double* g, double t_s_gp_s) {
   CHECK_P(p);
   if (!p_bp || !g) return CTBA_E_ARG;
-  cudaSetDevice(p->device);
+  if (p->device >= 0) cudaSetDevice(p->device);
   int rc = download_state(p); if (rc) return rc;
   p->scale = scale;
   for (int i = 0; i < 3; ++i) { p->glb[GLB_PBP + i] = p_bp[i]; p->glb[GLB_G + i] = g[i]; }
@@ -218,7 +227,7 @@ int ctba_set_globals(ctba_problem* p, double scale, const double* p_bp, const do
 int ctba_set_corrections(ctba_problem* p, const double* c) {
   CHECK_P(p);
   if (!c) return CTBA_E_ARG;
-  cudaSetDevice(p->device);
+  if (p->device >= 0) cudaSetDevice(p->device);
   int rc = download_state(p); if (rc) return rc;
   p->glb[GLB_SCALE_CORR] = c[0];
   for (int i = 0; i < 4; ++i) p->glb[GLB_RBC_CORR + i] = c[1 + i];
@@ -230,7 +239,7 @@ int ctba_set_corrections(ctba_problem* p, const double* c) {
 int ctba_get_globals(ctba_problem* p, double* o) {
   CHECK_P(p);
   if (!o) return CTBA_E_ARG;
-  cudaSetDevice(p->device);
+  if (p->device >= 0) cudaSetDevice(p->device);
   int rc = download_state(p); if (rc) return rc;
   o[0] = p->glb[GLB_SCALE_CORR];
   for (int i = 0; i < 4; ++i) o[1 + i] = p->glb[GLB_RBC_CORR + i];
@@ -382,6 +391,7 @@ int ctba_counts(ctba_problem* p, int64_t* c) {
 int ctba_evaluate(ctba_problem* p, int kind, double* r_out, double* j_out) {
   CHECK_P(p);
   if (kind < 0 || kind > 5) return fail(p, CTBA_E_ARG, "evaluate: unknown residual kind");
+  if (p->device < 0) return fail(p, CTBA_E_CUDA, "planning-only handle (device -1): no compute entry points");
   CTBA_CUDA(p, cudaSetDevice(p->device));
   int rc = sync_to_device(p); if (rc) return rc;
   const StatePtrs S = p->dstate.ptrs();
@@ -419,18 +429,21 @@ int ctba_evaluate(ctba_problem* p, int kind, double* r_out, double* j_out) {
 int ctba_cost(ctba_problem* p, double* cost7) {
   CHECK_P(p);
   if (!cost7) return CTBA_E_ARG;
+  if (p->device < 0) return fail(p, CTBA_E_CUDA, "planning-only handle (device -1): no compute entry points");
   CTBA_CUDA(p, cudaSetDevice(p->device));
   int rc = sync_to_device(p); if (rc) return rc;
   rc = launch_evaluate(p, p->ev, p->dstate.ptrs(), false); if (rc) return rc;
   rc = launch_cost(p, p->ev); if (rc) return rc;
-  CTBA_CUDA(p, cudaMemcpyAsync(cost7, p->ev.cost.p, 7 * sizeof(double), cudaMemcpyDeviceToHost, p->stream));
-  CTBA_CUDA(p, cudaStreamSynchronize(p->stream));
+  double c8[8];
+  rc = shard_reduce_cost(p, p->ev, c8); if (rc) return rc;   // sharded handles: the cost terms of the whole problem
+  for (int i = 0; i < 7; ++i) cost7[i] = c8[i];
   return CTBA_OK;
 }
 
 int ctba_solve(ctba_problem* p, int max_num_iterations, ctba_summary* summary) {
   CHECK_P(p);
   if (max_num_iterations < 0 || !summary) return fail(p, CTBA_E_ARG, "solve: bad arguments");
+  if (p->device < 0) return fail(p, CTBA_E_CUDA, "planning-only handle (device -1): no compute entry points");
   CTBA_CUDA(p, cudaSetDevice(p->device));
   int rc = sync_to_device(p); if (rc) return rc;
   return solver_solve(p, max_num_iterations, summary);
@@ -438,7 +451,7 @@ int ctba_solve(ctba_problem* p, int max_num_iterations, ctba_summary* summary) {
 
 int ctba_relinearize_time_offsets(ctba_problem* p) {
   CHECK_P(p);
-  cudaSetDevice(p->device);
+  if (p->device >= 0) cudaSetDevice(p->device);
   int rc = download_state(p); if (rc) return rc;
   // :1807-1811, :1853-1857 — bookkeeping only: the work items keep the st_s, k captured when they were added
   p->t_offset_cam_imu_s += p->glb[GLB_T_CAM_IMU_CORR]; p->glb[GLB_T_CAM_IMU_CORR] = 0.0;
@@ -460,7 +473,7 @@ int ctba_set_option(ctba_problem* p, const char* name, double value) {
 
 int ctba_invalidate_device(ctba_problem* p) {
   CHECK_P(p);
-  cudaSetDevice(p->device);
+  if (p->device >= 0) cudaSetDevice(p->device);
   int rc = download_state(p); if (rc) return rc;
   p->meas_dirty = true; p->state_dirty = true;
   return CTBA_OK;
@@ -482,11 +495,60 @@ int ctba_transfer_bytes(ctba_problem* p, int64_t* b) {
 
 int ctba_bench_evaluate(ctba_problem* p, int reps, int64_t* launches) {
   CHECK_P(p);
+  if (p->device < 0) return fail(p, CTBA_E_CUDA, "planning-only handle (device -1): no compute entry points");
   CTBA_CUDA(p, cudaSetDevice(p->device));
   int rc = sync_to_device(p); if (rc) return rc;
   const int64_t l0 = p->launches;
   for (int i = 0; i < reps; ++i) { rc = launch_evaluate(p, p->ev, p->dstate.ptrs(), true); if (rc) return rc; }
   if (launches) *launches = p->launches - l0;
+  return CTBA_OK;
+}
+
+// ---- multi-GPU: time-segment sharding (ctba_shard.h) ----
+int ctba_comm_unique_id(char* out128) {
+  if (!out128) return CTBA_E_ARG;
+  char err[256];
+  return nccl_unique_id(out128, err, sizeof(err)) ? CTBA_E_NCCL : CTBA_OK;
+}
+
+int ctba_comm_init_nccl(ctba_problem* p, int world, int rank, const char* id128) {
+  CHECK_P(p);
+  if (world < 1 || rank < 0 || rank >= world || !id128) return fail(p, CTBA_E_ARG, "comm_init_nccl: bad arguments");
+  if (p->comm || p->sharded) return fail(p, CTBA_E_STATE, "comm_init: the handle already has a communicator");
+  char err[256] = "";
+  Comm* c = make_nccl_comm(world, rank, id128, p->device, err, sizeof(err));
+  if (!c) { p->err = err; return CTBA_E_NCCL; }
+  p->comm = c; p->comm_owned = true; p->struct_dirty = true;
+  return CTBA_OK;
+}
+
+int ctba_comm_init_local(ctba_problem** handles, int world) {
+  if (!handles || world < 1) return CTBA_E_ARG;
+  for (int r = 0; r < world; ++r) {
+    if (!handles[r]) return CTBA_E_ARG;
+    if (handles[r]->comm || handles[r]->sharded) return fail(handles[r], CTBA_E_STATE, "comm_init: the handle already has a communicator");
+    if (handles[r]->device != handles[0]->device || handles[r]->device < 0) return fail(handles[r], CTBA_E_ARG, "comm_init_local: all handles must live on one device");
+  }
+  std::vector<Comm*> cs;
+  if (!make_local_comms(world, &cs)) return fail(handles[0], CTBA_E_ARG, "comm_init_local: world size not supported");
+  for (int r = 0; r < world; ++r) { handles[r]->comm = cs[r]; handles[r]->comm_owned = true; handles[r]->struct_dirty = true; }
+  return CTBA_OK;
+}
+
+int ctba_shard_plan(ctba_problem* p, int world, int rank, int64_t* plan, int32_t* lm_owner, int32_t* imu_owner, int32_t* gp_owner, int32_t* bias_owner) {
+  CHECK_P(p);
+  if (world < 1 || rank < 0 || rank >= world || !plan) return fail(p, CTBA_E_ARG, "shard_plan: bad arguments");
+  if (p->sharded) return fail(p, CTBA_E_STATE, "shard_plan: the handle already holds one shard only");
+  ShardInfo sh; GlobalStructure gs; HostStructure hs;
+  if (shard_plan(p, world, rank, &sh, &gs, &hs)) return fail(p, CTBA_E_ARG, "shard_plan: the reduced system is too short to cut into one time partition per rank");
+  const int64_t v[16] = {sh.layout.P, sh.nbc, sh.nbw, sh.q_lo, sh.q_hi, sh.bc_lo, sh.bc_hi, sh.own_lo, sh.own_hi, sh.F_global, sh.f_first, sh.f_cost_begin,
+                         hs.nodes, hs.hbn, hs.T, hs.KD};
+  for (int i = 0; i < 16; ++i) plan[i] = v[i];
+  for (int q = 0; q < sh.layout.P && q < 32; ++q) { plan[16 + 2 * q] = sh.layout.c0[q]; plan[17 + 2 * q] = sh.layout.nI[q]; }
+  if (lm_owner) for (size_t l = 0; l < p->lm.size() / 3; ++l) lm_owner[l] = sh.lm_owner[l];
+  if (imu_owner) for (size_t i = 0; i < p->i_s.size(); ++i) imu_owner[i] = sh.imu_owner[i];
+  if (gp_owner) for (size_t i = 0; i < p->g_s.size(); ++i) gp_owner[i] = sh.gp_owner[i];
+  if (bias_owner) for (size_t i = 0; i < p->b_s0.size(); ++i) bias_owner[i] = sh.bias_owner[i];
   return CTBA_OK;
 }
 

@@ -660,19 +660,23 @@ __global__ void k_knot_border(const FramePose<N>* __restrict__ fps, int K, const
 }
 
 // ---- Jacobi scaling (iteration 0 of each Solve): 1 / (1 + sqrt(diag J^T J)) ---------------------------------------
-__global__ void k_jscale(BandLayout H, int n_band, const double* __restrict__ V0, int L, GMask gm, double* __restrict__ jscale,
+// [gradient | diag(J^T J)] of this handle's normal equations, packed for the all-reduce of the sharded solve
+__global__ void k_pack_tot(BandLayout H, int n_band, int col_lo, int col_hi, GMask gm, const double* __restrict__ grad, double* __restrict__ tot) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n = H.n_pad + kBorder;
+  if (i >= n) return;
+  tot[i] = grad[i];
+  double d = 0.0;
+  if (i < n_band) d = (i >= col_lo && i < col_hi) ? H.band[band_addr(H, i, i)] : 0.0;   // outside the handle's column range the band is never initialised
+  else if (i >= H.n_pad && i < H.n_pad + GT_SIZE) { const int t = i - H.n_pad; d = gm.a[t] ? H.corner[t * kBorder + t] : 0.0; }
+  tot[n + i] = d;
+}
+
+__global__ void k_jscale(int n_pad, const double* __restrict__ diag /* n_pad + 16 */, const double* __restrict__ V0, int L, double* __restrict__ jscale,
                          double* __restrict__ jscale_lm) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < H.n_pad) {
-    double d = i < n_band ? H.band[band_addr(H, i, i)] : 0.0;
-    jscale[i] = 1.0 / (1.0 + sqrt(fmax(d, 0.0)));
-  } else if (i < H.n_pad + GT_SIZE) {
-    const int t = i - H.n_pad;
-    double d = gm.a[t] ? H.corner[t * kBorder + t] : 0.0;
-    jscale[i] = 1.0 / (1.0 + sqrt(fmax(d, 0.0)));
-  } else if (i < H.n_pad + kBorder) {
-    jscale[i] = 1.0;
-  }
+  if (i < n_pad + GT_SIZE) jscale[i] = 1.0 / (1.0 + sqrt(fmax(diag[i], 0.0)));
+  else if (i < n_pad + kBorder) jscale[i] = 1.0;
   const int j = i;
   if (j < 3 * L) {
     const int di[3] = {0, 3, 5};
@@ -682,29 +686,31 @@ __global__ void k_jscale(BandLayout H, int n_band, const double* __restrict__ V0
 
 // Hw = H0 + LM diagonal (in unscaled space: clamp(H_jj s_j^2, 1e-6, 1e32) / (radius s_j^2)); padding rows get identity;
 // inactive globals get identity; rhs row of the border = -grad (band part) ; corner rhs column = -grad (global part)
-__global__ void k_add_damping(BandLayout H0, BandLayout Hw, int n_band, const double* __restrict__ jscale, const double* __restrict__ grad,
-                              double radius, GMask gm, double* __restrict__ dvec /* n_pad+16: D^2 */) {
+__global__ void k_add_damping(BandLayout H0, BandLayout Hw, int n_band, const double* __restrict__ jscale, const double* __restrict__ diag,
+                              double radius, GMask gm, int own_lo, int own_hi, bool is_root, double* __restrict__ dvec /* n_pad+16: D^2 */) {
+  // diag = diagonal of the WHOLE problem's J^T J; a sharded handle adds the damping only to the columns it owns (H0 holds its partial sums)
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < Hw.n_pad) {
+    const bool own = i >= own_lo && i < own_hi;
     const size_t ad = band_addr(Hw, i, i);
     if (i < n_band) {
-      const double sc = jscale[i], d0 = H0.band[ad];
-      const double dd = fmin(fmax(d0 * sc * sc, 1e-6), 1e32) / (radius * sc * sc);
-      Hw.band[ad] = d0 + dd;   // k_pose_to_knots adds on top atomically afterwards? no: damping is applied LAST (see host order)
+      const double sc = jscale[i];
+      const double dd = fmin(fmax(diag[i] * sc * sc, 1e-6), 1e32) / (radius * sc * sc);
+      if (own) Hw.band[ad] = H0.band[ad] + dd;
       dvec[i] = dd;
     } else {
-      Hw.band[ad] = 1.0;
+      if (own) Hw.band[ad] = 1.0;
       dvec[i] = 0.0;
     }
   } else if (i < Hw.n_pad + GT_SIZE) {
     const int t = i - Hw.n_pad;
     if (gm.a[t]) {
-      const double sc = jscale[i], d0 = H0.corner[t * kBorder + t];
-      const double dd = fmin(fmax(d0 * sc * sc, 1e-6), 1e32) / (radius * sc * sc);
-      atomicAdd(Hw.corner + t * kBorder + t, dd);
+      const double sc = jscale[i];
+      const double dd = fmin(fmax(diag[i] * sc * sc, 1e-6), 1e32) / (radius * sc * sc);
+      if (is_root) atomicAdd(Hw.corner + t * kBorder + t, dd);
       dvec[i] = dd;
     } else {
-      Hw.corner[t * kBorder + t] = 1.0;
+      Hw.corner[t * kBorder + t] = is_root ? 1.0 : 0.0;
       dvec[i] = 0.0;
     }
   }
@@ -843,13 +849,14 @@ __global__ void __launch_bounds__(256) k_step_scalars(int K, int Kb, int L, cons
                                                       const double* __restrict__ delta, const double* __restrict__ delta_lm,
                                                       const double* __restrict__ dvec, const double* __restrict__ dvec_lm,
                                                       const double* __restrict__ grad, const double* __restrict__ gl, StatePtrs S, StatePtrs C,
-                                                      bool have_step, double* __restrict__ partial) {
+                                                      bool have_step, int own_lo, int own_hi, bool is_root, double* __restrict__ partial) {
   __shared__ double sh[4][256];
   double model = 0, step2 = 0, xn2 = 0, gmx = 0;
   const int total = K + Kb + L + 1;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     if (i < K) {
       const int nd = 6 * node_of_knot[i];
+      if (nd < own_lo || nd >= own_hi) continue;   // sharded: a node is counted by the rank owning its first column
       const uint8_t tm = touch_knot[i];
       if (have_step) for (int c = 0; c < 6; ++c) model += delta[nd + c] * (dvec[nd + c] * delta[nd + c] - grad[nd + c]);
       if (tm & 1) {
@@ -867,6 +874,7 @@ __global__ void __launch_bounds__(256) k_step_scalars(int K, int Kb, int L, cons
       }
     } else if (i < K + Kb) {
       const int j = i - K, nd = 6 * node_of_bias[j];
+      if (nd < own_lo || nd >= own_hi) continue;
       const uint8_t tm = touch_bias[j];
       if (have_step) for (int c = 0; c < 6; ++c) model += delta[nd + c] * (dvec[nd + c] * delta[nd + c] - grad[nd + c]);
       for (int c = 0; c < 3; ++c) {
@@ -885,7 +893,7 @@ __global__ void __launch_bounds__(256) k_step_scalars(int K, int Kb, int L, cons
           double d = C.lm[3 * (size_t)l + c] - x; step2 += d * d;
         }
       }
-    } else {
+    } else if (is_root) {
       // globals
       const double* dg = delta + n_pad;
       const double* gg = grad + n_pad;
@@ -932,58 +940,59 @@ __global__ void k_step_scalars_final(int nblocks, const double* __restrict__ par
 // ================================================== host side =====================================================
 static GMask make_gmask(const SolverData* sd) { GMask g; for (int i = 0; i < GT_SIZE; ++i) g.a[i] = sd->gactive[i]; return g; }
 
-int assemble_structure(ctba_problem* p) {
-  if (!p->solver) p->solver = new SolverData();
-  SolverData* sd = p->solver;
-  band_graph_release(sd);   // the captured launch sequence refers to the old structure / buffers
+// Host analysis of the problem structure (no device work): node order, half bandwidth, touch masks, landmark / knot CSR lists.
+void analyse_structure(const ctba_problem* p, const GlobalStructure* gs, HostStructure* hs) {
   const int N = p->N;
   const int K = (int)p->numKnots(), F = (int)p->numFrames(), M = (int)p->numObs(), L = (int)(p->lm.size() / 3);
-  const bool has_imu = !p->i_s.empty() || !p->b_s0.empty();
+  const bool has_imu = gs ? gs->has_imu : (!p->i_s.empty() || !p->b_s0.empty());
   const int Kb = has_imu ? (int)p->numBiasKnots() : 0;
-  sd->K = K; sd->Kb = Kb; sd->L = L; sd->F = F; sd->has_bias = Kb > 0;
+  hs->K = K; hs->Kb = Kb; hs->L = L; hs->F = F; hs->M = M; hs->has_imu = has_imu;
   // ---- node ordering: knots and bias knots merged by time (knot k at k*dt, bias knot j at j*dt_bias; ties: knot first)
-  sd->node_of_knot.assign(K, 0); sd->node_of_bias.assign(std::max(Kb, 1), 0);
+  hs->node_of_knot.assign(K, 0); hs->node_of_bias.assign(std::max(Kb, 1), 0);
   {
     int ik = 0, ib = 0, node = 0;
     while (ik < K || ib < Kb) {
       const bool take_knot = ib >= Kb || (ik < K && (int64_t)ik * p->dt_ns <= (int64_t)ib * p->dt_ns_bias);
-      if (take_knot) sd->node_of_knot[ik++] = node++; else sd->node_of_bias[ib++] = node++;
+      if (take_knot) hs->node_of_knot[ik++] = node++; else hs->node_of_bias[ib++] = node++;
     }
-    sd->nodes = node;
+    hs->nodes = node;
   }
+  const std::vector<int32_t>&nk = hs->node_of_knot, &nb = hs->node_of_bias;
   // ---- half bandwidth in nodes over every coupling group
   int hbn = N - 1;
   auto span = [&](int lo, int hi) { hbn = std::max(hbn, hi - lo); };
-  std::vector<uint8_t> tk(std::max(K, 1), 0), tb(std::max(Kb, 1), 0), tl(std::max(L, 1), 0);
+  std::vector<uint8_t>&tk = hs->tk, &tb = hs->tb, &tl = hs->tl;
+  tk.assign(std::max(K, 1), 0); tb.assign(std::max(Kb, 1), 0); tl.assign(std::max(L, 1), 0);
   for (size_t i = 0; i < p->i_s.size(); ++i) {
     const int s = p->i_s[i], sb = p->i_sb[i];
-    const int lo = std::min(sd->node_of_knot[s], sd->node_of_bias[sb]), hi = std::max(sd->node_of_knot[s + N - 1], sd->node_of_bias[sb + 3]);
+    const int lo = std::min(nk[s], nb[sb]), hi = std::max(nk[s + N - 1], nb[sb + 3]);
     span(lo, hi);
     for (int j = 0; j < N; ++j) tk[s + j] |= 3;
     for (int j = 0; j < 4; ++j) tb[sb + j] |= 3;
     // the reference registers N_ bias blocks per IMU residual (bspline_so3r3.h:585-588): blocks 4..N-1 are in the problem too
     for (int j = 4; j < N; ++j) tb[sb + j] |= 3;
   }
-  for (size_t i = 0; i < p->g_s.size(); ++i) { const int s = p->g_s[i]; span(sd->node_of_knot[s], sd->node_of_knot[s + N - 1]); for (int j = 0; j < N; ++j) tk[s + j] |= 3; }
+  for (size_t i = 0; i < p->g_s.size(); ++i) { const int s = p->g_s[i]; span(nk[s], nk[s + N - 1]); for (int j = 0; j < N; ++j) tk[s + j] |= 3; }
   for (size_t i = 0; i < p->b_s0.size(); ++i) {
     const int a = p->b_s0[i], b = p->b_s1[i];
-    span(sd->node_of_bias[std::min(a, b)], sd->node_of_bias[std::max(a, b) + 3]);
+    span(nb[std::min(a, b)], nb[std::max(a, b) + 3]);
     for (int j = 0; j < 4; ++j) { tb[a + j] |= (p->b_which[i] ? 2 : 1); tb[b + j] |= (p->b_which[i] ? 2 : 1); }
   }
   // landmark -> observation CSR (observations of a landmark in frame order, as they are stored)
-  std::vector<int32_t> lob(L + 1, 0), lobs(M);
+  std::vector<int32_t>&lob = hs->lob, &lobs = hs->lobs;
+  lob.assign(L + 1, 0); lobs.assign(M, 0);
   for (int o = 0; o < M; ++o) lob[p->o_lm[o] + 1]++;
   for (int l = 0; l < L; ++l) lob[l + 1] += lob[l];
   {
     std::vector<int32_t> cur(lob.begin(), lob.end() - 1);
     for (int o = 0; o < M; ++o) lobs[cur[p->o_lm[o]]++] = o;
   }
-  std::vector<int32_t> opos(std::max(M, 1), 0), lmf(std::max(M, 1), 0);
-  for (int l = 0; l < L; ++l) for (int i = lob[l]; i < lob[l + 1]; ++i) { opos[lobs[i]] = i; lmf[i] = p->o_frame[lobs[i]]; }
-  sd->max_frame_obs = 1;
-  for (int f = 0; f < F; ++f) sd->max_frame_obs = std::max(sd->max_frame_obs, (int)(p->f_obs_begin[f + 1] - p->f_obs_begin[f]));
-  if ((size_t)sd->max_frame_obs * 18 * sizeof(double) > 200 * 1024) { p->err = "assemble_structure: more than 1422 valid observations in one frame"; return CTBA_E_ARG; }
+  hs->opos.assign(std::max(M, 1), 0); hs->lmf.assign(std::max(M, 1), 0);
+  for (int l = 0; l < L; ++l) for (int i = lob[l]; i < lob[l + 1]; ++i) { hs->opos[lobs[i]] = i; hs->lmf[i] = p->o_frame[lobs[i]]; }
+  hs->max_frame_obs = 1;
+  for (int f = 0; f < F; ++f) hs->max_frame_obs = std::max(hs->max_frame_obs, (int)(p->f_obs_begin[f + 1] - p->f_obs_begin[f]));
   int T = 0, KD = N - 1;
+  hs->lm_smin.assign(std::max(L, 1), -1);
   for (int l = 0; l < L; ++l) {
     if (lob[l + 1] == lob[l]) continue;
     tl[l] = 1;
@@ -993,16 +1002,18 @@ int assemble_structure(ctba_problem* p) {
       fmin = std::min(fmin, f); fmax_ = std::max(fmax_, f);
       smin = std::min(smin, (int)p->f_s[f]); smax = std::max(smax, (int)p->f_s[f]);
     }
+    hs->lm_smin[l] = smin;
     T = std::max(T, fmax_ - fmin);
     KD = std::max(KD, smax + N - 1 - smin);
-    span(sd->node_of_knot[smin], sd->node_of_knot[smax + N - 1]);
+    span(nk[smin], nk[smax + N - 1]);
   }
-  for (int f = 0; f < F; ++f) { const int s = p->f_s[f]; span(sd->node_of_knot[s], sd->node_of_knot[s + N - 1]); for (int j = 0; j < N; ++j) tk[s + j] |= 3; }
+  for (int f = 0; f < F; ++f) { const int s = p->f_s[f]; span(nk[s], nk[s + N - 1]); for (int j = 0; j < N; ++j) tk[s + j] |= 3; }
   // every SO3 knot carries a local parameterisation in the reference and is therefore part of the program (:378-399)
   for (int k = 0; k < K; ++k) tk[k] |= 1;
-  sd->T = T; sd->hbn = hbn; sd->KD = KD;
+  hs->T = T; hs->hbn = hbn; hs->KD = KD;
   // knot -> frames whose window contains it (CSR), for the gather kernels
-  std::vector<int32_t> kfb(K + 1, 0), kfl((size_t)std::max(F, 1) * N);
+  std::vector<int32_t>&kfb = hs->kfb, &kfl = hs->kfl;
+  kfb.assign(K + 1, 0); kfl.assign((size_t)std::max(F, 1) * N, 0);
   for (int f = 0; f < F; ++f) for (int j = 0; j < N; ++j) kfb[p->f_s[f] + j + 1]++;
   for (int k = 0; k < K; ++k) kfb[k + 1] += kfb[k];
   {
@@ -1010,23 +1021,43 @@ int assemble_structure(ctba_problem* p) {
     for (int f = 0; f < F; ++f) for (int j = 0; j < N; ++j) kfl[cur[p->f_s[f] + j]++] = f;
   }
   // ---- which globals are free (constness set inside add*Measurement)
-  const bool anyF = F > 0, anyI = !p->i_s.empty(), anyG = !p->g_s.empty();
-  for (int i = 0; i < GT_SIZE; ++i) sd->gactive[i] = 0;
-  sd->gactive[GT_SCALE] = p->optimize_scale && (anyF || anyG);
+  const bool anyF = gs ? gs->any_frames : F > 0, anyI = gs ? gs->any_imu : !p->i_s.empty(), anyG = gs ? gs->any_gp : !p->g_s.empty();
+  const bool grav = gs ? gs->gravity_norm : p->gravity_norm;
+  for (int i = 0; i < GT_SIZE; ++i) hs->gactive[i] = 0;
+  hs->gactive[GT_SCALE] = p->optimize_scale && (anyF || anyG);
   for (int c = 0; c < 3; ++c) {
-    sd->gactive[GT_RBC + c] = p->optimize_camimu_extrinsics && anyF;
-    sd->gactive[GT_PBC + c] = p->optimize_camimu_extrinsics && anyF;
-    sd->gactive[GT_PBP + c] = p->optimize_p_bp && anyG;
-    sd->gactive[GT_G + c] = (anyI && p->optimize_gravity) || (!anyI && p->gravity_norm);
+    hs->gactive[GT_RBC + c] = p->optimize_camimu_extrinsics && anyF;
+    hs->gactive[GT_PBC + c] = p->optimize_camimu_extrinsics && anyF;
+    hs->gactive[GT_PBP + c] = p->optimize_p_bp && anyG;
+    hs->gactive[GT_G + c] = (anyI && p->optimize_gravity) || (!anyI && grav);
   }
-  sd->gactive[GT_T_CAM_IMU] = p->optimize_camimu_extrinsics && anyI;
-  sd->gactive[GT_T_GP] = p->optimize_t_offset_s_gs && anyG;
+  hs->gactive[GT_T_CAM_IMU] = p->optimize_camimu_extrinsics && anyI;
+  hs->gactive[GT_T_GP] = p->optimize_t_offset_s_gs && anyG;
+  if (gs) { hs->hbn = gs->hbn; hs->tk = gs->tk; hs->tb = gs->tb; }   // sharded: band width and touched unknowns of the WHOLE problem
+  hs->n_band = 6 * hs->nodes;
+  hs->n_pad = ((hs->n_band + kNB - 1) / kNB) * kNB;
+  const int bw = 6 * hs->hbn + 5;
+  hs->nbw = std::min((bw + 2 * kNB - 2) / kNB, std::max(hs->n_pad / kNB - 1, 0));
+}
 
-  const int n_band = 6 * sd->nodes;
-  const int n_pad = ((n_band + kNB - 1) / kNB) * kNB;
-  const int bw = 6 * hbn + 5;
-  const int nbw = std::min((bw + 2 * kNB - 2) / kNB, std::max(n_pad / kNB - 1, 0));
+int assemble_structure(ctba_problem* p) {
+  if (!p->solver) p->solver = new SolverData();
+  SolverData* sd = p->solver;
+  band_graph_release(sd);   // the captured launch sequence refers to the old structure / buffers
+  HostStructure hs;
+  analyse_structure(p, p->gstruct, &hs);
+  const int K = hs.K, Kb = hs.Kb, F = hs.F, M = hs.M, L = hs.L, T = hs.T;
+  sd->K = K; sd->Kb = Kb; sd->L = L; sd->F = F; sd->has_bias = Kb > 0; sd->nodes = hs.nodes;
+  sd->node_of_knot = hs.node_of_knot; sd->node_of_bias = hs.node_of_bias;
+  sd->max_frame_obs = hs.max_frame_obs;
+  if ((size_t)sd->max_frame_obs * 18 * sizeof(double) > 200 * 1024) { p->err = "assemble_structure: more than 1422 valid observations in one frame"; return CTBA_E_ARG; }
+  sd->T = T; sd->hbn = hs.hbn; sd->KD = hs.KD;
+  for (int i = 0; i < GT_SIZE; ++i) sd->gactive[i] = hs.gactive[i];
+  const int n_band = hs.n_band, n_pad = hs.n_pad, nbw = hs.nbw;
   BandLayout B{n_band, n_pad, n_pad / kNB, nbw, nullptr, nullptr, nullptr};
+  // column range of the band this handle ever touches (sharded: left separator .. right separator of the rank's partitions)
+  sd->bc_lo = 0; sd->bc_hi = B.nbc; sd->own_lo = 0; sd->own_hi = n_pad; sd->is_root = true;
+  if (p->sharded) { sd->bc_lo = p->shard->bc_lo; sd->bc_hi = p->shard->bc_hi; sd->own_lo = p->shard->own_lo; sd->own_hi = p->shard->own_hi; sd->is_root = p->shard->rank == 0; }
   const size_t be = B.band_elems();
   CTBA_CUDA(p, sd->band0.resize(be)); CTBA_CUDA(p, sd->bandw.resize(be));
   CTBA_CUDA(p, sd->border0.resize((size_t)kBorder * n_pad)); CTBA_CUDA(p, sd->borderw.resize((size_t)kBorder * n_pad));
@@ -1034,6 +1065,7 @@ int assemble_structure(ctba_problem* p) {
   sd->H0 = B; sd->H0.band = sd->band0.p; sd->H0.border = sd->border0.p; sd->H0.corner = sd->corner0.p;
   sd->Hw = B; sd->Hw.band = sd->bandw.p; sd->Hw.border = sd->borderw.p; sd->Hw.corner = sd->cornerw.p;
   CTBA_CUDA(p, sd->grad.resize(n_pad + kBorder)); CTBA_CUDA(p, sd->delta.resize(n_pad + kBorder));
+  CTBA_CUDA(p, sd->tot.resize(2 * (size_t)(n_pad + kBorder)));     // [gradient | diag(J^T J)] of the whole problem
   CTBA_CUDA(p, sd->jscale.resize(2 * (size_t)(n_pad + kBorder)));  // second half: D^2 vector
   CTBA_CUDA(p, sd->V0.resize(6 * (size_t)std::max(L, 1))); CTBA_CUDA(p, sd->gl.resize(3 * (size_t)std::max(L, 1)));
   CTBA_CUDA(p, sd->jscale_lm.resize(6 * (size_t)std::max(L, 1)));  // second half: D^2 of landmarks
@@ -1044,15 +1076,16 @@ int assemble_structure(ctba_problem* p) {
   CTBA_CUDA(p, sd->scal.resize(SC_COUNT + 4 * 256));
   CTBA_CUDA(p, sd->flag.resize(4));
   cudaStream_t st = p->stream;
+  CTBA_CUDA(p, cudaMemsetAsync(sd->delta.p, 0, (n_pad + kBorder) * sizeof(double), st));
   CTBA_CUDA(p, sd->d_node_of_knot.upload(sd->node_of_knot, st)); CTBA_CUDA(p, sd->d_node_of_bias.upload(sd->node_of_bias, st));
-  CTBA_CUDA(p, sd->d_lm_obs_begin.upload(lob, st)); CTBA_CUDA(p, sd->d_lm_obs.upload(lobs, st));
-  CTBA_CUDA(p, sd->d_lm_frame.upload(lmf, st));
-  CTBA_CUDA(p, sd->d_o_pos.upload(opos, st)); CTBA_CUDA(p, sd->d_kf_begin.upload(kfb, st)); CTBA_CUDA(p, sd->d_kf_list.upload(kfl, st));
+  CTBA_CUDA(p, sd->d_lm_obs_begin.upload(hs.lob, st)); CTBA_CUDA(p, sd->d_lm_obs.upload(hs.lobs, st));
+  CTBA_CUDA(p, sd->d_lm_frame.upload(hs.lmf, st));
+  CTBA_CUDA(p, sd->d_o_pos.upload(hs.opos, st)); CTBA_CUDA(p, sd->d_kf_begin.upload(hs.kfb, st)); CTBA_CUDA(p, sd->d_kf_list.upload(hs.kfl, st));
   CTBA_CUDA(p, sd->Vi.resize(6 * (size_t)std::max(L, 1))); CTBA_CUDA(p, sd->vig.resize(3 * (size_t)std::max(L, 1)));
   CTBA_CUDA(p, sd->ViYg.resize(21 * (size_t)std::max(L, 1)));
   CTBA_CUDA(p, sd->Yo.resize(18 * (size_t)std::max(M, 1))); CTBA_CUDA(p, sd->Zo.resize(18 * (size_t)std::max(M, 1)));
   CTBA_CUDA(p, sd->lm_corner_partial.resize((size_t)cdiv(std::max(L, 1), 128) * 35));
-  CTBA_CUDA(p, sd->d_touch_knot.upload(tk, st)); CTBA_CUDA(p, sd->d_touch_bias.upload(tb, st)); CTBA_CUDA(p, sd->d_touch_lm.upload(tl, st));
+  CTBA_CUDA(p, sd->d_touch_knot.upload(hs.tk, st)); CTBA_CUDA(p, sd->d_touch_bias.upload(hs.tb, st)); CTBA_CUDA(p, sd->d_touch_lm.upload(hs.tl, st));
   // candidate state buffers
   CTBA_CUDA(p, sd->cand.knot_q.resize(p->dstate.knot_q.n)); CTBA_CUDA(p, sd->cand.knot_p.resize(p->dstate.knot_p.n));
   CTBA_CUDA(p, sd->cand.bias_a.resize(p->dstate.bias_a.n)); CTBA_CUDA(p, sd->cand.bias_g.resize(p->dstate.bias_g.n));
@@ -1070,7 +1103,8 @@ static int assemble_direct_T(ctba_problem* p) {
   const GMask gm = make_gmask(sd);
   const int F = sd->F, M = (int)p->numObs(), L = sd->L;
   BandLayout& H = sd->H0;
-  CTBA_CUDA(p, cudaMemsetAsync(H.band, 0, H.band_elems() * sizeof(double), st));
+  const size_t col_elems = (size_t)(H.nbw + 1) * kNB * kNB;   // one block column of the band
+  CTBA_CUDA(p, cudaMemsetAsync(H.band + sd->bc_lo * col_elems, 0, (size_t)(sd->bc_hi - sd->bc_lo) * col_elems * sizeof(double), st));
   CTBA_CUDA(p, cudaMemsetAsync(H.border, 0, (size_t)kBorder * H.n_pad * sizeof(double), st));
   CTBA_CUDA(p, cudaMemsetAsync(H.corner, 0, kBorder * kBorder * sizeof(double), st));
   CTBA_CUDA(p, cudaMemsetAsync(sd->grad.p, 0, (H.n_pad + kBorder) * sizeof(double), st));
@@ -1109,7 +1143,10 @@ static int assemble_direct_T(ctba_problem* p) {
                                             sd->d_node_of_bias.p, gm, H, sd->grad.p);
     p->launches++;
   }
+  k_pack_tot<<<cdiv(H.n_pad + kBorder, 256), 256, 0, st>>>(H, H.n_band, kNB * sd->bc_lo, kNB * sd->bc_hi, gm, sd->grad.p, sd->tot.p);
+  p->launches++;
   CTBA_CUDA(p, cudaGetLastError());
+  if (p->sharded && p->comm->allreduce_sum(sd->tot.p, 2 * (size_t)(H.n_pad + kBorder), st)) { p->err = p->comm->error(); return CTBA_E_NCCL; }
   return CTBA_OK;
 }
 int assemble_direct(ctba_problem* p) { return p->N == 4 ? assemble_direct_T<4>(p) : assemble_direct_T<6>(p); }
@@ -1117,7 +1154,7 @@ int assemble_direct(ctba_problem* p) { return p->N == 4 ? assemble_direct_T<4>(p
 int compute_jscale(ctba_problem* p) {
   SolverData* sd = p->solver;
   const int n = std::max(sd->H0.n_pad + kBorder, 3 * sd->L);
-  k_jscale<<<cdiv(n, 256), 256, 0, p->stream>>>(sd->H0, sd->H0.n_band, sd->V0.p, sd->L, make_gmask(sd), sd->jscale.p, sd->jscale_lm.p);
+  k_jscale<<<cdiv(n, 256), 256, 0, p->stream>>>(sd->H0.n_pad, sd->tot.p + (sd->H0.n_pad + kBorder), sd->V0.p, sd->L, sd->jscale.p, sd->jscale_lm.p);
   p->launches++;
   CTBA_CUDA(p, cudaGetLastError());
   return CTBA_OK;
@@ -1132,14 +1169,17 @@ static int assemble_schur_T(ctba_problem* p, double radius) {
   const int F = sd->F, M = (int)p->numObs(), L = sd->L, T = sd->T;
   BandLayout &H0 = sd->H0, &Hw = sd->Hw;
   const int n_pad = Hw.n_pad;
-  CTBA_CUDA(p, cudaMemcpyAsync(Hw.band, H0.band, H0.band_elems() * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  const size_t col_elems = (size_t)(H0.nbw + 1) * kNB * kNB;
+  CTBA_CUDA(p, cudaMemcpyAsync(Hw.band + sd->bc_lo * col_elems, H0.band + sd->bc_lo * col_elems, (size_t)(sd->bc_hi - sd->bc_lo) * col_elems * sizeof(double),
+                               cudaMemcpyDeviceToDevice, st));
   CTBA_CUDA(p, cudaMemcpyAsync(Hw.border, H0.border, (size_t)kBorder * n_pad * sizeof(double), cudaMemcpyDeviceToDevice, st));
   CTBA_CUDA(p, cudaMemcpyAsync(Hw.corner, H0.corner, kBorder * kBorder * sizeof(double), cudaMemcpyDeviceToDevice, st));
   double* dvec = sd->jscale.p + (n_pad + kBorder);
   double* rhs_acc = sd->rp.p + (size_t)std::max(F, 1) * 6;  // n_pad + 16 accumulator of Schur right-hand-side corrections
   CTBA_CUDA(p, cudaMemsetAsync(rhs_acc, 0, (n_pad + kBorder) * sizeof(double), st));
   // LM diagonal first (it reads the undamped diagonal of H0), Schur terms are then added atomically on top
-  k_add_damping<<<cdiv(n_pad + kBorder, 256), 256, 0, st>>>(H0, Hw, H0.n_band, sd->jscale.p, sd->grad.p, radius, gm, dvec);
+  k_add_damping<<<cdiv(n_pad + kBorder, 256), 256, 0, st>>>(H0, Hw, H0.n_band, sd->jscale.p, sd->tot.p + (n_pad + kBorder), radius, gm, sd->own_lo, sd->own_hi,
+                                                            sd->is_root, dvec);
   p->launches++;
   const StatePtrs S = p->dstate.ptrs();
   if (F > 0 && L > 0) {
@@ -1214,8 +1254,8 @@ int step_scalars(ctba_problem* p, const StatePtrs& S, const StatePtrs& C, double
   const int total = sd->K + sd->Kb + L + 1;
   const int nb = std::min(256, cdiv(total, 256));
   k_step_scalars<<<nb, 256, 0, p->stream>>>(sd->K, sd->Kb, L, sd->d_node_of_knot.p, sd->d_node_of_bias.p, sd->d_touch_knot.p, sd->d_touch_bias.p,
-                                            sd->d_touch_lm.p, make_gmask(sd), n_pad, sd->delta.p, sd->delta_lm.p, dvec, dvec_lm, sd->grad.p, sd->gl.p, S, C,
-                                            radius > 0, sd->scal.p + SC_COUNT);
+                                            sd->d_touch_lm.p, make_gmask(sd), n_pad, sd->delta.p, sd->delta_lm.p, dvec, dvec_lm, sd->tot.p, sd->gl.p, S, C,
+                                            radius > 0, sd->own_lo, sd->own_hi, sd->is_root, sd->scal.p + SC_COUNT);
   k_step_scalars_final<<<1, 32, 0, p->stream>>>(nb, sd->scal.p + SC_COUNT, sd->scal.p);
   p->launches += 2;
   CTBA_CUDA(p, cudaGetLastError());

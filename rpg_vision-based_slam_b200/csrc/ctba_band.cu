@@ -11,6 +11,7 @@
 #include <cooperative_groups.h>
 #include <algorithm>
 #include <cmath>
+#include <initializer_list>
 #include "ctba_solver.h"
 
 namespace ctba {
@@ -426,24 +427,35 @@ __global__ void __launch_bounds__(256) k_gram_reduce(const __grid_constant__ Ban
 
 // ---- interface system in the separators -------------------------------------------------------------------------------------------
 // B2: block columns = the separator columns in time order (nbw per separator), half bandwidth 2 nbw - 1 blocks (dense block tridiagonal).
-struct IfaceArgs { const double* gram; size_t gram_off[kMaxParts]; };
-__global__ void __launch_bounds__(256) k_iface_assemble(BandLayout B, BandLayout B2, const __grid_constant__ BandParts PS, const __grid_constant__ IfaceArgs IA) {
+// Sharded solves (ctba_shard.h): every rank assembles only the terms it holds — the raw + right-looking-updated separator blocks of its
+// own band copy (zero outside its column range), the Gram matrices and couplings of its own partitions [q_lo, q_hi) — and the interface
+// system is the SUM over ranks (one all-reduce).  q_lo = 0, q_hi = P is the single-GPU case.
+struct IfaceArgs { const double* gram; size_t gram_off[kMaxParts]; int q_lo, q_hi; double* extra; };
+__global__ void __launch_bounds__(256) k_iface_assemble(BandLayout B, BandLayout B2, const __grid_constant__ BandParts PS, const __grid_constant__ IfaceArgs IA,
+                                                        const int32_t* __restrict__ flag) {
   const int nb1_2 = B2.nbw + 1;
   const int nblk = B2.nbc * nb1_2;
   const int blk = blockIdx.x;
   const int nbw = B.nbw;
+  auto local = [&](int q) { return q >= IA.q_lo && q < IA.q_hi; };
   if (blk < nblk) {
     const int K2 = blk / nb1_2, off = blk % nb1_2, I2 = K2 + off;
     double* dst = B2.band + ((size_t)blk << 10);
     if (I2 >= B2.nbc) { for (int e = threadIdx.x; e < 1024; e += 256) dst[e] = 0.0; return; }
     const int qi = I2 / nbw, a = I2 % nbw, qk = K2 / nbw, c = K2 % nbw;
     if (qi == qk) {
+      const bool adjacent = qk >= IA.q_lo - 1 && qk <= IA.q_hi - 1;      // separator qk borders one of this rank's partitions
+      const bool have_g = local(qk + 1);
       const int s = PS.part[qk + 1].c0 - nbw;                         // first block column of separator qk
       const double* T = B.band + ((size_t)(s + c) * (nbw + 1) + (a - c)) * 1024;
       const double* G = IA.gram + IA.gram_off[qk + 1];
       const int ldg = kNB * PS.part[qk + 1].nrb;
-      for (int e = threadIdx.x; e < 1024; e += 256) dst[e] = T[e] - G[(size_t)(a * kNB + (e >> 5)) * ldg + c * kNB + (e & 31)];
-    } else if (qi == qk + 1) {
+      for (int e = threadIdx.x; e < 1024; e += 256) {
+        double v = adjacent ? T[e] : 0.0;
+        if (have_g) v -= G[(size_t)(a * kNB + (e >> 5)) * ldg + c * kNB + (e & 31)];
+        dst[e] = v;
+      }
+    } else if (qi == qk + 1 && local(qi)) {
       const BandPart& Q = PS.part[qi];                                 // the interior between the two separators
       const double* F = Q.fb + (size_t)c * kNB * Q.ld + (size_t)(Q.nI + a) * kNB;   // rows of S_qk (block c), columns of S_qi (block a)
       for (int e = threadIdx.x; e < 1024; e += 256) dst[e] = F[(size_t)(e & 31) * Q.ld + (e >> 5)];
@@ -456,12 +468,17 @@ __global__ void __launch_bounds__(256) k_iface_assemble(BandLayout B, BandLayout
   if (bb < B2.nbc) {   // global rows over separator column K2
     const int K2 = bb, qk = K2 / nbw, c = K2 % nbw;
     const BandPart& Q = PS.part[qk];                                   // left neighbour: carries the global rows over S_qk's columns
-    const double* F = Q.fb + (size_t)(Q.nrb - 1) * kNB * Q.ld + (size_t)(Q.nI + c) * kNB;
+    const bool have_f = local(qk), raw = !have_f && qk == IA.q_lo - 1, have_g = local(qk + 1);
+    const double* F = have_f ? Q.fb + (size_t)(Q.nrb - 1) * kNB * Q.ld + (size_t)(Q.nI + c) * kNB : nullptr;
+    const int s = PS.part[qk + 1].c0 - nbw;
+    const double* Rw = B.border + (size_t)(s + c) * kNB;               // this rank's own contributions to those columns (left partition elsewhere)
     const double* G = IA.gram + IA.gram_off[qk + 1];
     const int ldg = kNB * PS.part[qk + 1].nrb;
     for (int e = threadIdx.x; e < kBorder * kNB; e += 256) {
       const int g = e >> 5, cc = e & 31;
-      B2.border[(size_t)g * B2.n_pad + (size_t)K2 * kNB + cc] = F[(size_t)g * Q.ld + cc] - G[(size_t)(nbw * kNB + g) * ldg + c * kNB + cc];
+      double v = have_f ? F[(size_t)g * Q.ld + cc] : (raw ? Rw[(size_t)g * B.n_pad + cc] : 0.0);
+      if (have_g) v -= G[(size_t)(nbw * kNB + g) * ldg + c * kNB + cc];
+      B2.border[(size_t)g * B2.n_pad + (size_t)K2 * kNB + cc] = v;
     }
     return;
   }
@@ -469,12 +486,16 @@ __global__ void __launch_bounds__(256) k_iface_assemble(BandLayout B, BandLayout
   for (int e = threadIdx.x; e < kBorder * kBorder; e += 256) {
     const int a = e / kBorder, b = e % kBorder;
     double v = B.corner[e];
-    for (int p = 0; p < PS.P; ++p) {
+    for (int p = IA.q_lo; p < IA.q_hi; ++p) {
       const int ldg = kNB * PS.part[p].nrb, o = (PS.part[p].nrb - 1) * kNB;
       v -= IA.gram[IA.gram_off[p] + (size_t)(o + (a > b ? a : b)) * ldg + o + (a > b ? b : a)];
     }
     B2.corner[e] = v;
   }
+  if (threadIdx.x < 32) IA.extra[threadIdx.x] = threadIdx.x == 0 ? (double)(flag[0] != 0) : 0.0;   // a failed interior anywhere fails the solve everywhere
+}
+__global__ void k_flag_from_sum(const double* __restrict__ extra, int32_t* __restrict__ flag) {
+  if (threadIdx.x == 0 && blockIdx.x == 0 && extra[0] != 0.0) atomicExch(flag, 1);
 }
 // interface solution -> separator columns of the full solution vector (+ globals)
 __global__ void k_iface_scatter(BandLayout B, BandLayout B2, const __grid_constant__ BandParts PS, const double* __restrict__ delta2, double* __restrict__ delta) {
@@ -645,82 +666,116 @@ struct BandPlan {
   // key
   int nbc = -1, nbw = -1, req = -2; const double* band_ptr = nullptr; const double* border_ptr = nullptr;
   int P = 1, max_steps = 0;
-  BandParts PS{};           // partitions of the full system (P == 1: one partition whose border is Hw.border itself)
+  BandParts PS{};           // every partition of the full system (P == 1: one partition whose border is Hw.border itself)
+  BandParts PSloc{};        // the partitions this handle factors (all of them unless the problem is sharded over ranks)
   BandParts PS2{};          // the interface system as a single partition
   BandLayout B2{};
   GramPlan GP{};
   IfaceArgs IA{};
   int gram_tasks = 0, gram_tiles = 0;
-  DBuf<double> fb, gram, gram_scratch, band2, border2, corner2, delta2, dinv2, cpart, cpart2, dinv;
-  DBuf<int32_t> dummy;
+  size_t iface_elems = 0;
+  DBuf<double> fb, gram, gram_scratch, iface /* band2 | border2 | corner2 | extra */, delta2, dinv2, cpart, cpart2, dinv;
   size_t* d_gram_off = nullptr;
   ~BandPlan() {
-    DBuf<double>* dd[] = {&fb, &gram, &gram_scratch, &band2, &border2, &corner2, &delta2, &dinv2, &cpart, &cpart2, &dinv};
+    DBuf<double>* dd[] = {&fb, &gram, &gram_scratch, &iface, &delta2, &dinv2, &cpart, &cpart2, &dinv};
     for (auto* d : dd) d->release();
     if (d_gram_off) cudaFree(d_gram_off);
   }
 };
 
-static int choose_partitions(int nbc, int nbw, int requested) {
-  if (nbw < 1 || 2 * nbw > 63) return 1;
-  int P = requested > 0 ? requested : (int)lround(std::sqrt((double)nbc / (1.2 * nbw)));
-  P = std::max(1, std::min(P, kMaxParts));
-  while (P > 1 && (nbc - (P - 1) * nbw) / P < std::max(nbw, 2)) --P;
-  return P;
+int band_partition_layout(int nbc, int nbw, int requested, int world, PartLayout* out) {
+  int P = 1;
+  const auto fits = [&](int q) { return (nbc - (q - 1) * nbw) / q >= std::max(nbw, 2); };
+  if (!(nbw < 1 || 2 * nbw > 63)) {
+    P = requested > 0 ? requested : (int)lround(std::sqrt((double)nbc / (1.2 * nbw)));
+    P = std::max(1, std::min(P, kMaxParts));
+    if (world > 1) {
+      P = std::max(world, (P / world) * world);
+      while (P > world && !fits(P)) P -= world;
+    } else {
+      while (P > 1 && !fits(P)) --P;
+    }
+  }
+  if (world > 1 && (P < world || P > kMaxParts || nbw < 1 || 2 * nbw > 63 || !fits(P))) return -1;
+  out->P = P; out->c0.assign(P, 0); out->nI.assign(P, nbc);
+  if (P == 1) return 0;
+  const int interior = nbc - (P - 1) * nbw;
+  int c = 0;
+  for (int q = 0; q < P; ++q) {
+    out->c0[q] = c; out->nI[q] = interior / P + (q < interior % P ? 1 : 0);
+    c += out->nI[q] + nbw;
+  }
+  return 0;
 }
 
 static int plan_build(ctba_problem* p, BandPlan& pl, const BandLayout& B) {
   pl.nbc = B.nbc; pl.nbw = B.nbw; pl.req = p->band_partitions; pl.band_ptr = B.band; pl.border_ptr = B.border;
-  pl.P = choose_partitions(B.nbc, B.nbw, p->band_partitions);
+  PartLayout lay;
+  int q_lo = 0, q_hi = 1;
+  if (p->sharded) {
+    lay = p->shard->layout; q_lo = p->shard->q_lo; q_hi = p->shard->q_hi;
+    if (p->shard->nbc != B.nbc || p->shard->nbw != B.nbw) { p->err = "band plan: structure differs from the sharding plan"; return CTBA_E_STATE; }
+  } else {
+    band_partition_layout(B.nbc, B.nbw, p->band_partitions, 1, &lay);
+    q_hi = lay.P;
+  }
+  pl.P = lay.P;
   CTBA_CUDA(p, pl.dinv.resize((size_t)B.nbc * 1024));
   CTBA_CUDA(p, pl.cpart.resize((size_t)cdiv(B.n_pad, 256) * 256));
   pl.PS = BandParts{};
   if (pl.P == 1) {
     pl.PS.P = 1;
     pl.PS.part[0] = BandPart{0, B.nbc, 1, B.nbc, B.n_pad, B.border};
+    pl.PSloc = pl.PS;
     pl.max_steps = B.nbc;
     return CTBA_OK;
   }
   const int P = pl.P, nbw = B.nbw;
-  const int interior = B.nbc - (P - 1) * nbw;
   size_t fb_total = 0, gram_total = 0;
-  std::vector<size_t> fb_off(P), g_off(P);
-  int c = 0, maxI = 0;
+  std::vector<size_t> fb_off(P, 0), g_off(P, 0), g_off_loc;
+  int maxI = 0;
   pl.PS.P = P;
   for (int q = 0; q < P; ++q) {
-    const int nI = interior / P + (q < interior % P ? 1 : 0);
+    const int nI = lay.nI[q];
     BandPart& Q = pl.PS.part[q];
-    Q.c0 = c; Q.nI = nI; Q.nrb = (q == 0 ? 1 : nbw + 1); Q.ncols = nI + (q < P - 1 ? nbw : 0); Q.ld = kNB * Q.ncols; Q.fb = nullptr;
+    Q.c0 = lay.c0[q]; Q.nI = nI; Q.nrb = (q == 0 ? 1 : nbw + 1); Q.ncols = nI + (q < P - 1 ? nbw : 0); Q.ld = kNB * Q.ncols; Q.fb = nullptr;
+    if (q < q_lo || q >= q_hi) continue;
     fb_off[q] = fb_total; fb_total += (size_t)Q.nrb * kNB * Q.ld;
     g_off[q] = gram_total; gram_total += (size_t)(Q.nrb * kNB) * (Q.nrb * kNB);
-    c += nI + nbw;
+    g_off_loc.push_back(g_off[q]);
     maxI = std::max(maxI, nI);
   }
   pl.max_steps = maxI + 1;   // + the flush step that applies the last interior column's update to the right separator
   CTBA_CUDA(p, pl.fb.resize(fb_total)); CTBA_CUDA(p, pl.gram.resize(gram_total));
-  pl.GP = GramPlan{}; pl.GP.P = P;
+  pl.GP = GramPlan{}; pl.GP.P = q_hi - q_lo;
+  pl.PSloc = BandParts{}; pl.PSloc.P = q_hi - q_lo;
+  pl.IA = IfaceArgs{};
   int tiles = 0, tasks = 0;
-  for (int q = 0; q < P; ++q) {
+  for (int q = q_lo; q < q_hi; ++q) {
     BandPart& Q = pl.PS.part[q];
     Q.fb = pl.fb.p + fb_off[q];
+    pl.PSloc.part[q - q_lo] = Q;
     pl.IA.gram_off[q] = g_off[q];
     const int nt = Q.nrb * (Q.nrb + 1) / 2, ns = (Q.nI + kGramChunk - 1) / kGramChunk;
-    pl.GP.tile0[q] = tiles; pl.GP.task0[q] = tasks; pl.GP.nsplit[q] = ns;
+    pl.GP.tile0[q - q_lo] = tiles; pl.GP.task0[q - q_lo] = tasks; pl.GP.nsplit[q - q_lo] = ns;
     tiles += nt; tasks += nt * ns;
   }
-  pl.GP.tile0[P] = tiles; pl.GP.task0[P] = tasks;
+  pl.GP.tile0[q_hi - q_lo] = tiles; pl.GP.task0[q_hi - q_lo] = tasks;
   pl.gram_tiles = tiles; pl.gram_tasks = tasks;
-  pl.IA.gram = pl.gram.p;
+  pl.IA.gram = pl.gram.p; pl.IA.q_lo = q_lo; pl.IA.q_hi = q_hi;
   CTBA_CUDA(p, pl.gram_scratch.resize((size_t)tasks * 1024));
   if (!pl.d_gram_off) CTBA_CUDA(p, cudaMalloc((void**)&pl.d_gram_off, kMaxParts * sizeof(size_t)));
-  CTBA_CUDA(p, cudaMemcpy(pl.d_gram_off, g_off.data(), P * sizeof(size_t), cudaMemcpyHostToDevice));
-  // interface system
+  CTBA_CUDA(p, cudaMemcpy(pl.d_gram_off, g_off_loc.data(), g_off_loc.size() * sizeof(size_t), cudaMemcpyHostToDevice));
+  // interface system: band2 | border2 | corner2 | extra in ONE buffer (a sharded solve sums it over the ranks with a single all-reduce)
   BandLayout& B2 = pl.B2;
   B2.nbc = (P - 1) * nbw; B2.n_pad = B2.nbc * kNB; B2.n_band = B2.n_pad; B2.nbw = std::min(2 * nbw - 1, B2.nbc - 1);
-  CTBA_CUDA(p, pl.band2.resize(B2.band_elems())); CTBA_CUDA(p, pl.border2.resize((size_t)kBorder * B2.n_pad)); CTBA_CUDA(p, pl.corner2.resize(kBorder * kBorder));
+  const size_t e_band = B2.band_elems(), e_border = (size_t)kBorder * B2.n_pad;
+  pl.iface_elems = e_band + e_border + kBorder * kBorder + 32;
+  CTBA_CUDA(p, pl.iface.resize(pl.iface_elems));
   CTBA_CUDA(p, pl.delta2.resize(B2.n_pad + kBorder)); CTBA_CUDA(p, pl.dinv2.resize((size_t)B2.nbc * 1024));
   CTBA_CUDA(p, pl.cpart2.resize((size_t)cdiv(B2.n_pad, 256) * 256));
-  B2.band = pl.band2.p; B2.border = pl.border2.p; B2.corner = pl.corner2.p;
+  B2.band = pl.iface.p; B2.border = pl.iface.p + e_band; B2.corner = B2.border + e_border;
+  pl.IA.extra = B2.corner + kBorder * kBorder;
   pl.PS2 = BandParts{}; pl.PS2.P = 1;
   pl.PS2.part[0] = BandPart{0, B2.nbc, 1, B2.nbc, B2.n_pad, B2.border};
   return CTBA_OK;
@@ -780,35 +835,43 @@ static int enqueue_single(ctba_problem* p, cudaStream_t st, const BandLayout& B,
   return enqueue_backsolve(p, st, B, PS1, dinv, delta, nl);
 }
 
-static int band_enqueue(ctba_problem* p, cudaStream_t st, BandPlan& pl, int64_t* nl) {
+// phase 0: the whole solve (one handle holds every partition); phases 1 / 2: the two halves of a sharded solve — interiors + this rank's
+// terms of the interface system | (all-reduce of the interface system in between) | interface solve (replicated) + interior back-substitution
+static int band_enqueue(ctba_problem* p, cudaStream_t st, BandPlan& pl, int phase, int64_t* nl) {
   SolverData* sd = p->solver;
   BandLayout& B = sd->Hw;
-  CTBA_CUDA(p, cudaMemsetAsync(sd->flag.p, 0, 4 * sizeof(int32_t), st));
   int rc;
+  if (phase <= 1) CTBA_CUDA(p, cudaMemsetAsync(sd->flag.p, 0, 4 * sizeof(int32_t), st));
   if (pl.P == 1) {
     rc = enqueue_single(p, st, B, pl.PS, pl.dinv.p, sd->delta.p, pl.cpart.p, nl); if (rc) return rc;
   } else {
-    int nblk = 0;
-    for (int q = 0; q < pl.P; ++q) nblk += pl.PS.part[q].nrb * pl.PS.part[q].ncols;
-    k_fb_init<<<nblk, 256, 0, st>>>(B, pl.PS);
-    ++*nl;
-    rc = enqueue_steps(p, st, B, pl.PS, pl.max_steps, pl.dinv.p, nl); if (rc) return rc;
-    k_gram_partial<<<pl.gram_tasks, kStepThreads, 0, st>>>(pl.PS, pl.GP, pl.gram_scratch.p);
-    k_gram_reduce<<<pl.gram_tiles, 256, 0, st>>>(pl.PS, pl.GP, pl.gram_scratch.p, pl.gram.p, pl.d_gram_off);
     const BandLayout& B2 = pl.B2;
-    k_iface_assemble<<<B2.nbc * (B2.nbw + 1) + B2.nbc + 1, 256, 0, st>>>(B, B2, pl.PS, pl.IA);
-    *nl += 3;
-    rc = enqueue_single(p, st, B2, pl.PS2, pl.dinv2.p, pl.delta2.p, pl.cpart2.p, nl); if (rc) return rc;
-    k_iface_scatter<<<cdiv(B2.n_pad + kBorder, 256), 256, 0, st>>>(B, B2, pl.PS, pl.delta2.p, sd->delta.p);
-    ++*nl;
-    rc = enqueue_backsolve(p, st, B, pl.PS, pl.dinv.p, sd->delta.p, nl); if (rc) return rc;
+    if (phase <= 1) {
+      int nblk = 0;
+      for (int q = 0; q < pl.PSloc.P; ++q) nblk += pl.PSloc.part[q].nrb * pl.PSloc.part[q].ncols;
+      k_fb_init<<<nblk, 256, 0, st>>>(B, pl.PSloc);
+      ++*nl;
+      rc = enqueue_steps(p, st, B, pl.PSloc, pl.max_steps, pl.dinv.p, nl); if (rc) return rc;
+      k_gram_partial<<<pl.gram_tasks, kStepThreads, 0, st>>>(pl.PSloc, pl.GP, pl.gram_scratch.p);
+      k_gram_reduce<<<pl.gram_tiles, 256, 0, st>>>(pl.PSloc, pl.GP, pl.gram_scratch.p, pl.gram.p, pl.d_gram_off);
+      k_iface_assemble<<<B2.nbc * (B2.nbw + 1) + B2.nbc + 1, 256, 0, st>>>(B, B2, pl.PS, pl.IA, sd->flag.p);
+      *nl += 3;
+    }
+    if (phase == 0 || phase == 2) {
+      if (phase == 2) { k_flag_from_sum<<<1, 32, 0, st>>>(pl.IA.extra, sd->flag.p); ++*nl; }
+      rc = enqueue_single(p, st, B2, pl.PS2, pl.dinv2.p, pl.delta2.p, pl.cpart2.p, nl); if (rc) return rc;
+      k_iface_scatter<<<cdiv(B2.n_pad + kBorder, 256), 256, 0, st>>>(B, B2, pl.PS, pl.delta2.p, sd->delta.p);
+      ++*nl;
+      rc = enqueue_backsolve(p, st, B, pl.PSloc, pl.dinv.p, sd->delta.p, nl); if (rc) return rc;
+    }
   }
   CTBA_CUDA(p, cudaGetLastError());
   return CTBA_OK;
 }
 
 void band_graph_release(SolverData* sd) {
-  if (sd->band_graph_exec) { cudaGraphExecDestroy((cudaGraphExec_t)sd->band_graph_exec); sd->band_graph_exec = nullptr; }
+  for (void** g : {&sd->band_graph_exec, &sd->band_graph_exec1, &sd->band_graph_exec2})
+    if (*g) { cudaGraphExecDestroy((cudaGraphExec_t)*g); *g = nullptr; }
 }
 void band_plan_release(SolverData* sd) {
   band_graph_release(sd);
@@ -839,26 +902,36 @@ int band_factor_solve(ctba_problem* p) {
     band_graph_release(sd);
     const int rc = plan_build(p, pl, B); if (rc) return rc;
   }
-  int64_t nl = 0;
-  if (!p->band_graph) { const int rc = band_enqueue(p, st, pl, &nl); p->launches += nl; sd->band_launches = nl; return rc; }
+  // run one phase: eagerly, or as a CUDA graph captured on first use
+  auto run_phase = [&](int phase, void** exec_slot, int64_t* launches_slot) -> int {
+    int64_t nl = 0;
+    if (!p->band_graph) { const int rc = band_enqueue(p, st, pl, phase, &nl); p->launches += nl; *launches_slot = nl; return rc; }
+    if (!*exec_slot) {
+      cudaGraph_t graph = nullptr;
+      CTBA_CUDA(p, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+      const int rc = band_enqueue(p, st, pl, phase, &nl);
+      const cudaError_t e = cudaStreamEndCapture(st, &graph);
+      if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+      CTBA_CUDA(p, e);
+      cudaGraphExec_t exec = nullptr;
+      const cudaError_t ei = cudaGraphInstantiate(&exec, graph, 0);
+      cudaGraphDestroy(graph);
+      CTBA_CUDA(p, ei);
+      *exec_slot = exec; *launches_slot = nl;
+    }
+    p->launches += *launches_slot;
+    CTBA_CUDA(p, cudaGraphLaunch((cudaGraphExec_t)*exec_slot, st));
+    return CTBA_OK;
+  };
   const int key = p->band_pdl;
   if (sd->band_graph_key != key) band_graph_release(sd);
-  if (!sd->band_graph_exec) {
-    cudaGraph_t graph = nullptr;
-    CTBA_CUDA(p, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-    const int rc = band_enqueue(p, st, pl, &nl);
-    const cudaError_t e = cudaStreamEndCapture(st, &graph);
-    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
-    CTBA_CUDA(p, e);
-    cudaGraphExec_t exec = nullptr;
-    const cudaError_t ei = cudaGraphInstantiate(&exec, graph, 0);
-    cudaGraphDestroy(graph);
-    CTBA_CUDA(p, ei);
-    sd->band_graph_exec = exec; sd->band_graph_key = key; sd->band_launches = nl;
-  }
-  p->launches += sd->band_launches;
-  CTBA_CUDA(p, cudaGraphLaunch((cudaGraphExec_t)sd->band_graph_exec, st));
-  return CTBA_OK;
+  sd->band_graph_key = key;
+  if (!p->sharded) return run_phase(0, &sd->band_graph_exec, &sd->band_launches);
+  int rc = run_phase(1, &sd->band_graph_exec1, &sd->band_launches1); if (rc) return rc;
+  if (p->comm->allreduce_sum(pl.iface.p, pl.iface_elems, st)) { p->err = p->comm->error(); return CTBA_E_NCCL; }
+  rc = run_phase(2, &sd->band_graph_exec2, &sd->band_launches2);
+  sd->band_launches = sd->band_launches1 + sd->band_launches2;
+  return rc;
 }
 
 }  // namespace ctba

@@ -71,6 +71,31 @@ __global__ void k_frame_robust(int F, const int32_t* __restrict__ obs_begin, con
   }
 }
 
+// Sharded problems: a frame in the overlap of two time segments has observations on two ranks, and CauchyLoss acts on the whole
+// frame block (bspline_so3r3.h:1032).  k_frame_sq writes this rank's partial |r_frame|^2 at the frame's GLOBAL index, the array is
+// all-reduced, k_frame_weight turns the total into the corrector weight; the cost of a shared frame is counted by the lowest rank.
+__global__ void k_frame_sq(int F, const int32_t* __restrict__ obs_begin, const double2* __restrict__ r, int f_first, double* __restrict__ fsq_glob) {
+  int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= F) return;
+  const int b = obs_begin[warp], e = obs_begin[warp + 1];
+  double s = 0.0;
+  for (int i = b + lane; i < e; i += 32) { double2 v = r[i]; s += v.x * v.x + v.y * v.y; }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) fsq_glob[f_first + warp] = s;
+}
+__global__ void k_frame_weight(int F, int f_first, int f_cost_begin, const double* __restrict__ fsq_glob, double cauchy_a, double* __restrict__ f_sq,
+                               double* __restrict__ f_w, double* __restrict__ f_cost) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= F) return;
+  const double s = fsq_glob[f_first + f];
+  const double bb = cauchy_a * cauchy_a;
+  const double sum = 1.0 + s / bb;
+  f_sq[f] = s;
+  f_w[f] = sqrt(1.0 / sum);
+  f_cost[f] = f >= f_cost_begin ? 0.5 * bb * log(sum) : 0.0;
+}
+
 template <int N, bool JAC>
 __global__ void __launch_bounds__(64) k_imu(const __grid_constant__ Globals G, StatePtrs S, int n, const int32_t* __restrict__ i_s,
                                             const int32_t* __restrict__ i_sb, const double* __restrict__ st_s, const double* __restrict__ kk,
@@ -226,9 +251,22 @@ static int launch_evaluate_T(ctba_problem* p, EvalBuffers& ev, const StatePtrs& 
       k_reproj<N, false><<<cdiv(M, 256), 256, 0, st>>>(G, fp, S.lm, M, p->d_o_frame.p, p->d_o_lm.p, (const double2*)p->d_o_uv.p,
                                                         p->d_f_inv_std.p, (double2*)ev.r_reproj.p, nullptr);
     }
-    k_frame_robust<<<cdiv((size_t)F * 32, 256), 256, 0, st>>>(F, p->d_f_obs_begin.p, (const double2*)ev.r_reproj.p, p->cauchy_a, ev.f_sq.p,
-                                                             ev.f_w.p, ev.f_cost.p);
-    p->launches += 3;
+    if (!p->sharded) {
+      k_frame_robust<<<cdiv((size_t)F * 32, 256), 256, 0, st>>>(F, p->d_f_obs_begin.p, (const double2*)ev.r_reproj.p, p->cauchy_a, ev.f_sq.p,
+                                                               ev.f_w.p, ev.f_cost.p);
+      p->launches += 3;
+    }
+  }
+  if (p->sharded && p->shard->F_global > 0) {   // collective: every rank takes part, with or without local frames
+    const ShardInfo& sh = *p->shard;
+    CTBA_CUDA(p, p->d_fsq_glob.resize(sh.F_global));
+    CTBA_CUDA(p, cudaMemsetAsync(p->d_fsq_glob.p, 0, sh.F_global * sizeof(double), st));
+    if (F > 0) k_frame_sq<<<cdiv((size_t)F * 32, 256), 256, 0, st>>>(F, p->d_f_obs_begin.p, (const double2*)ev.r_reproj.p, sh.f_first, p->d_fsq_glob.p);
+    if (p->comm->allreduce_sum(p->d_fsq_glob.p, sh.F_global, st)) { p->err = p->comm->error(); return CTBA_E_NCCL; }
+    if (F > 0) {
+      k_frame_weight<<<cdiv(F, 256), 256, 0, st>>>(F, sh.f_first, sh.f_cost_begin, p->d_fsq_glob.p, p->cauchy_a, ev.f_sq.p, ev.f_w.p, ev.f_cost.p);
+      p->launches += 4;
+    }
   }
   if (nI > 0) {
     CTBA_CUDA(p, ev.r_acc.resize(3 * (size_t)nI)); CTBA_CUDA(p, ev.r_gyr.resize(3 * (size_t)nI));

@@ -7,6 +7,7 @@
 #include <vector>
 #include "../../include/ctba.h"
 #include "ctba_terms.h"
+#include "ctba_shard.h"
 
 namespace ctba {
 
@@ -105,6 +106,16 @@ struct ctba_problem {
   ctba::SolverData* solver = nullptr;
   int64_t launches = 0;  // kernels launched by this handle (bench bookkeeping)
 
+  // ---- multi-GPU: time-segment sharding (ctba_shard.h) ----
+  ctba::Comm* comm = nullptr;            // set by ctba_comm_init_*; world > 1 => the next solve shards the problem
+  bool comm_owned = true;
+  bool sharded = false;                  // the host work items above hold only this rank's units
+  ctba::ShardInfo* shard = nullptr;
+  ctba::GlobalStructure* gstruct = nullptr;
+  ctba::DBuf<double> d_fsq_glob;         // per GLOBAL frame: squared reprojection norm (all-reduced)
+  ctba::DBuf<double> d_gather;           // all-gather landing zone: world * 8 doubles
+  ctba::DBuf<double> d_stage;            // masked state for the final re-assembly
+
   size_t numKnots() const { return knot_q.size() / 4; }
   size_t numBiasKnots() const { return bias_a.size() / 3; }
   size_t numFrames() const { return f_s.size(); }
@@ -122,6 +133,9 @@ int expand_reproj_dense(ctba_problem* p, const StatePtrs& S, double* d_out);  //
 void solver_free(SolverData* s);
 int solver_solve(ctba_problem* p, int max_iters, ctba_summary* out);
 int solver_num_unknowns(ctba_problem* p);
+int shard_build(ctba_problem* p);                    // ctba_shard.cu: filter the host work items to this rank's units
+int shard_reduce_cost(ctba_problem* p, EvalBuffers& ev, double* host_cost8);   // cost terms of all ranks, summed in rank order
+int shard_gather_state(ctba_problem* p);             // owners' knots / biases / landmarks -> every rank
 }  // namespace ctba
 
 #define CTBA_CUDA(p, call)                                                                                   \

@@ -11,6 +11,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <vector>
 #include "ctba_solver.h"
 
 namespace ctba {
@@ -20,11 +21,11 @@ static inline int cdiv(size_t a, int b) { return (int)((a + b - 1) / b); }
 void solver_free(SolverData* sd) {
   if (!sd) return;
   band_plan_release(sd);
-  DBuf<double>* dd[] = {&sd->band0, &sd->bandw, &sd->border0, &sd->borderw, &sd->corner0, &sd->cornerw, &sd->grad, &sd->V0, &sd->gl, &sd->Sp, &sd->Sb,
+  DBuf<double>* dd[] = {&sd->band0, &sd->bandw, &sd->border0, &sd->borderw, &sd->corner0, &sd->cornerw, &sd->grad, &sd->tot, &sd->V0, &sd->gl, &sd->Sp, &sd->Sb,
                         &sd->rp, &sd->Vi, &sd->vig, &sd->ViYg, &sd->Yo, &sd->Zo, &sd->lm_corner_partial, &sd->jscale, &sd->jscale_lm, &sd->delta, &sd->delta_lm, &sd->dpose, &sd->scal, &sd->cand.knot_q, &sd->cand.knot_p,
                         &sd->cand.bias_a, &sd->cand.bias_g, &sd->cand.lm, &sd->cand.glb};
   for (auto* d : dd) d->release();
-  DBuf<int32_t>* di[] = {&sd->d_node_of_knot, &sd->d_node_of_bias, &sd->d_lm_obs_begin, &sd->d_lm_obs, &sd->d_o_pos, &sd->d_lm_frame, &sd->d_kf_begin, &sd->d_kf_list, &sd->flag};
+  DBuf<int32_t>* di[] = {&sd->d_node_of_knot, &sd->d_node_of_bias, &sd->d_lm_obs_begin, &sd->d_lm_obs, &sd->d_o_pos, &sd->d_lm_frame, &sd->d_kf_begin, &sd->d_kf_list, &sd->flag, &sd->d_lm_owner};
   for (auto* d : di) d->release();
   sd->d_touch_knot.release(); sd->d_touch_bias.release(); sd->d_touch_lm.release();
   delete sd;
@@ -72,7 +73,7 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
     EvTimer t(st, &out->time_eval_s);
     int r = launch_evaluate(p, ev, S, jac); if (r) return r;
     r = launch_cost(p, ev); if (r) return r;
-    CTBA_CUDA(p, cudaMemcpyAsync(host_cost, ev.cost.p, 7 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    r = shard_reduce_cost(p, ev, host_cost); if (r) return r;   // single GPU: plain read-back of the 7 cost terms
     t.stop();
     *cost = host_cost[6];
     return CTBA_OK;
@@ -85,8 +86,23 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
   };
   auto scalars = [&](const StatePtrs& S, const StatePtrs& C, double radius) -> int {
     int r = step_scalars(p, S, C, radius); if (r) return r;
-    CTBA_CUDA(p, cudaMemcpyAsync(host_sc, sd->scal.p, SC_COUNT * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (!p->sharded) {
+      CTBA_CUDA(p, cudaMemcpyAsync(host_sc, sd->scal.p, SC_COUNT * sizeof(double), cudaMemcpyDeviceToHost, st));
+      CTBA_CUDA(p, cudaStreamSynchronize(st));
+      return CTBA_OK;
+    }
+    // sharded: every rank holds the sums over the nodes / landmarks it owns; combined in rank order so that all ranks take the same decisions
+    const int W = p->comm->world;
+    CTBA_CUDA(p, p->d_gather.resize((size_t)W * SC_COUNT));
+    if (p->comm->allgather(sd->scal.p, p->d_gather.p, SC_COUNT, st)) { p->err = p->comm->error(); return CTBA_E_NCCL; }
+    std::vector<double> h((size_t)W * SC_COUNT);
+    CTBA_CUDA(p, cudaMemcpyAsync(h.data(), p->d_gather.p, h.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
     CTBA_CUDA(p, cudaStreamSynchronize(st));
+    for (int c = 0; c < SC_COUNT; ++c) host_sc[c] = 0.0;
+    for (int rk = 0; rk < W; ++rk) {
+      host_sc[SC_MODEL] += h[(size_t)rk * SC_COUNT + SC_MODEL]; host_sc[SC_STEP2] += h[(size_t)rk * SC_COUNT + SC_STEP2];
+      host_sc[SC_XNORM2] += h[(size_t)rk * SC_COUNT + SC_XNORM2]; host_sc[SC_GMAX] = std::max(host_sc[SC_GMAX], h[(size_t)rk * SC_COUNT + SC_GMAX]);
+    }
     return CTBA_OK;
   };
 
@@ -173,6 +189,7 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
     }
   }
 done:
+  rc = shard_gather_state(p); if (rc) return rc;   // sharded: the owners' knots / biases / landmarks reach every rank
   out->final_cost = x_cost;
   out->num_iterations = nit;
   out->kernel_launches = p->launches - launches0;

@@ -41,6 +41,16 @@ __device__ __forceinline__ void add_sym(const BandLayout& B, int i, int j, doubl
   else atomicAdd(B.corner + (r - B.n_pad) * kBorder + (c - B.n_pad), v);
 }
 
+// host analysis of the problem structure (assemble_structure; also used on the whole problem before sharding)
+struct HostStructure {
+  int K = 0, Kb = 0, L = 0, F = 0, M = 0, nodes = 0, hbn = 0, T = 0, KD = 0, max_frame_obs = 1, n_band = 0, n_pad = 0, nbw = 0;
+  bool has_imu = false;
+  std::vector<int32_t> node_of_knot, node_of_bias, lob, lobs, opos, lmf, kfb, kfl, lm_smin;
+  std::vector<uint8_t> tk, tb, tl;
+  int gactive[GT_SIZE] = {0};
+};
+void analyse_structure(const ctba_problem* p, const GlobalStructure* gs, HostStructure* hs);
+
 struct SolverData {
   // ---- structure ----
   int K = 0, Kb = 0, nodes = 0, hbn = 0, L = 0, F = 0, T = 0, KD = 0;   // KD: largest knot distance coupled through a landmark
@@ -48,6 +58,7 @@ struct SolverData {
   std::vector<int32_t> node_of_knot, node_of_bias;
   DBuf<int32_t> d_node_of_knot, d_node_of_bias, d_lm_obs_begin, d_lm_obs;
   DBuf<int32_t> d_lm_frame;   // frame of every entry of the landmark observation lists
+  DBuf<int32_t> d_lm_owner;   // sharded: owning rank of every landmark
   int max_frame_obs = 1;
   DBuf<int32_t> d_o_pos, d_kf_begin, d_kf_list;   // observation -> slot in its landmark's list; knot -> frames (CSR)
   DBuf<double> Vi, vig, ViYg, Yo, Zo, lm_corner_partial;   // Schur gather scratch (ctba_assemble.cu)
@@ -55,7 +66,11 @@ struct SolverData {
   int gactive[GT_SIZE] = {0};
   BandLayout H0{}, Hw{};
   DBuf<double> band0, bandw, border0, borderw, corner0, cornerw;
-  DBuf<double> grad;          // n_pad + 16 : J^T r of the band + global unknowns (no Schur)
+  DBuf<double> grad;          // n_pad + 16 : J^T r of the band + global unknowns (no Schur); sharded: this rank's partial sum
+  DBuf<double> tot;           // [gradient | diag(J^T J)] (n_pad + 16 each) of the WHOLE problem (sharded: all-reduced)
+  int bc_lo = 0, bc_hi = 0;   // block columns this handle's partial system touches
+  int own_lo = 0, own_hi = 0; // scalar columns it owns (damping, step scalars)
+  bool is_root = true;        // owns the global parameters
   DBuf<double> V0, gl;        // per landmark: 6 (xx xy xz yy yz zz), 3
   DBuf<double> Sp, Sb, rp;    // pose-space Schur blocks: F*(T+1)*36, F*42, F*6
   DBuf<double> jscale, jscale_lm;   // Jacobi scaling (fixed per Solve): n_pad+16, 3L
@@ -65,6 +80,8 @@ struct SolverData {
   void* band_plan = nullptr;        // BandPlan (ctba_band.cu): time partitions, interface system, scratch
   int64_t band_launches = 0;        // kernels in one factor+solve
   void* band_graph_exec = nullptr;  // cudaGraphExec_t of the factor+solve launch sequence (band_factor_solve)
+  void* band_graph_exec1 = nullptr; void* band_graph_exec2 = nullptr;   // sharded: the halves before / after the interface all-reduce
+  int64_t band_launches1 = 0, band_launches2 = 0;
   int band_graph_key = -1;
   DBuf<double> scal;                // small scalar outputs (see SC_* in ctba_solve.cu)
   DBuf<int32_t> flag;               // numeric failure flag

@@ -1,0 +1,99 @@
+"""Multi-GPU path on ONE device: the time-segment-sharded LM solve (ctba_shard.h) with the in-process communicator — `world` handles,
+one host thread each, the same kernels and the same exchange points as the NCCL path — against the unsharded solve of the same problem.
+north_star tolerances: per-iteration cost 1e-8 relative, final cost 1e-6, trajectory 1 mm / 0.01 deg."""
+import threading
+
+import numpy as np
+import pytest
+from scipy.spatial.transform import Rotation as Rot
+
+pytestmark = pytest.mark.gpu
+
+
+def _sharded(pkg, sc, world, fn, **kw):
+    hs = [pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=0) for _ in range(world)]
+    for h in hs:
+        pkg.load_scene(h, sc, **kw)
+    pkg.BSplineSO3R3.initCommLocal(hs)
+    out, err = [None] * world, [None] * world
+
+    def run(r):
+        try:
+            out[r] = fn(hs[r])
+        except Exception as e:  # noqa: BLE001
+            err[r] = e
+    th = [threading.Thread(target=run, args=(r,), daemon=True) for r in range(world)]
+    [t.start() for t in th]
+    [t.join(300) for t in th]
+    assert not any(t.is_alive() for t in th), "sharded call hung"
+    for e in err:
+        if e is not None:
+            raise e
+    return hs, out
+
+
+def _compare(pkg, sc, world, iters, **kw):
+    ref = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=0)
+    pkg.load_scene(ref, sc, **kw)
+    c_ref = ref.cost()
+    s_ref = ref.optimize(iters)
+    hs, costs = _sharded(pkg, sc, world, lambda h: h.cost(), **kw)
+    for c in costs:                                               # ctba_cost of a sharded handle = the whole problem's cost terms
+        np.testing.assert_allclose(c, c_ref, rtol=1e-12, atol=1e-9)
+    assert sum(h.counts()["obs"] for h in hs) == ref.counts()["obs"]
+    assert sum(h.counts()["accel"] for h in hs) == ref.counts()["accel"]
+    outs = [None] * world
+
+    def solve(h):
+        return h.optimize(iters)
+    th = [threading.Thread(target=lambda r=r: outs.__setitem__(r, solve(hs[r])), daemon=True) for r in range(world)]
+    [t.start() for t in th]
+    [t.join(600) for t in th]
+    assert all(o is not None for o in outs)
+    ig = s_ref["iterations"]
+    qr, pr = ref.getKnots()
+    for r, (h, s) in enumerate(zip(hs, outs)):
+        it = s["iterations"]
+        assert it.shape == ig.shape and s["termination_type"] == s_ref["termination_type"], (r, it.shape, ig.shape)
+        assert (it[:, 6] == ig[:, 6]).all()                        # same accept / reject sequence on every rank
+        np.testing.assert_allclose(it[:, 0], ig[:, 0], rtol=1e-8)   # per-iteration cost
+        np.testing.assert_allclose(it[:, 5], ig[:, 5], rtol=1e-6)   # trust-region radius
+        np.testing.assert_allclose(it[1:, 3], ig[1:, 3], rtol=1e-5, atol=1e-12)
+        assert abs(s["final_cost"] - s_ref["final_cost"]) <= 1e-6 * s_ref["final_cost"]
+        q, p = h.getKnots()                                        # every rank ends with the whole optimised state
+        assert np.abs(p - pr).max() < 1e-3
+        assert np.rad2deg((Rot.from_quat(q).inv() * Rot.from_quat(qr)).magnitude().max()) < 0.01
+        np.testing.assert_allclose(h.get3DPoints(), ref.get3DPoints(), atol=1e-3)
+        np.testing.assert_allclose(h.getGlobals(), ref.getGlobals(), atol=1e-5)
+        a, g = h.getBiases(); ar, gr = ref.getBiases()
+        if ar.size:
+            np.testing.assert_allclose(a, ar, atol=1e-5); np.testing.assert_allclose(g, gr, atol=1e-6)
+    for h in hs[1:]:                                               # ranks hold bitwise the same state
+        assert (h.getKnots()[1] == hs[0].getKnots()[1]).all() and (h.get3DPoints() == hs[0].get3DPoints()).all()
+    return s_ref, outs
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_gvi_matches_unsharded(pkg, scene, world):
+    """vision + IMU + bias spline + GP + gravity norm, every global free, outliers that trip the gate / the Cauchy loss."""
+    sc = scene.make_scene(order=6, duration_s=30.0 * world, n_landmarks=600 * world, track_len=12, imu_hz=100, gp_hz=10, dt_s_bias=0.5,
+                          flags=(True, True, True, True, True), gravity_norm=True, outlier_frac=0.02, seed=11)
+    s_ref, _ = _compare(pkg, sc, world, 8)
+    assert s_ref["num_successful_steps"] >= 4
+
+
+def test_sharded_gv_cubic_two_partitions_per_rank(pkg, scene):
+    """vision + GP, cubic spline, fisheye camera; 2 ranks x 2 partitions each."""
+    sc = scene.make_scene(order=4, duration_s=80.0, n_landmarks=1600, track_len=10, imu_hz=0, gp_hz=10, cam="fpv", seed=5,
+                          flags=(True, True, False, True, True))
+    ref = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=-1)
+    pkg.load_scene(ref, sc)
+    assert ref.shardPlan(2, 0)["P"] >= 2
+    _compare(pkg, sc, 2, 6)
+
+
+def test_sharded_vi_no_gp(pkg, scene):
+    """vision + IMU only (gauge left to the LM damping), 2 ranks."""
+    sc = scene.make_scene(order=6, duration_s=60.0, n_landmarks=1200, track_len=10, imu_hz=100, gp_hz=0, dt_s_bias=0.5, seed=77,
+                          flags=(False, True, True, True, True), gravity_norm=True)
+    _compare(pkg, sc, 2, 6)
