@@ -118,15 +118,23 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
     torch.cuda.set_device(local_rank)
-    # weak scaling: every rank owns an independent trajectory segment of the configured shape ("replicas"; the
-    # time-segment-sharded single problem is the next multi-GPU row)
-    sc = scene_mod.config_scene(a.config, seed=20240101 + a.config + rank)
+    # N > 1: ONE trajectory of N x the configured duration (N x the landmarks), sharded by time segment over the N ranks (weak scaling:
+    # the per-GPU share of the problem is the configured workload; NCCL exchange steps per LM iteration).  Every rank is
+    # handed the complete problem through the same C-ABI calls as a single-GPU caller; the library keeps the rank's units.
+    base = {1: (50.0, 20000), 2: (180.0, 40000), 3: (3600.0, 200000)}[a.config]
+    sc = scene_mod.config_scene(a.config, duration_s=base[0] * world, n_landmarks=base[1] * world) if world > 1 else scene_mod.config_scene(a.config)
     g = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=local_rank)
     pkg.load_scene(g, sc)
-    n = g.counts()
+    n_total = g.counts()
     stream = torch.cuda.Stream()
     g.setStream(stream.cuda_stream)
     g.setOption("bench_no_termination", 1)
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8, device=f"cuda:{local_rank}")
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(pkg.BSplineSO3R3.commUniqueId()), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        g.initCommNccl(world, rank, bytes(uid.cpu().numpy().tobytes()))
 
     def barrier():
         torch.cuda.synchronize()
@@ -136,6 +144,7 @@ def main():
 
     # ---- device-resident LM iterations ----
     g.optimize(max(a.warmup, 3))
+    n = g.counts()     # sharded: this rank's units
     barrier()
     stop = threading.Event(); samples = []
     th = threading.Thread(target=clocks_sampler, args=(stop, samples, local_rank)); th.start()
@@ -149,7 +158,7 @@ def main():
     assert steps_done == a.steps, (steps_done, a.steps)
     launches = s["kernel_launches"]
 
-    # ---- residual+Jacobian kernels alone (roofline of the dominant evaluation kernel) ----
+    # ---- residual+Jacobian kernels alone ----
     for _ in range(3):
         g.benchEvaluate(1)
     torch.cuda.synchronize()
@@ -157,6 +166,10 @@ def main():
     k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     k0.record(stream); g.benchEvaluate(reps); k1.record(stream); torch.cuda.synchronize()
     ms_eval = k0.elapsed_time(k1) / reps
+    # the dominant (HBM-bound) evaluation kernel alone, L2 flushed between launches
+    g.benchReproj(3, True)
+    ms_reproj = g.benchReproj(20, True)
+    ms_reproj_warm = g.benchReproj(20, False)
     stop.set(); th.join()
 
     # ---- end to end through the C-ABI with host buffers ----
@@ -166,16 +179,20 @@ def main():
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        g.invalidateDevice()          # state + measurements are uploaded again from host memory
+        g.invalidateDevice()          # state + (this rank's) measurements are uploaded again from host memory
         g.optimize(1)                 # one LM iteration
         g.getKnots(); g.get3DPoints()  # result back in host memory
     torch.cuda.synchronize()
     t_e2e = (time.perf_counter() - t0) / e2e_steps
 
-    tms = torch.tensor([ms_total, t_e2e * 1e3, ms_eval], dtype=torch.float64, device=f"cuda:{local_rank}")
+    dev = f"cuda:{local_rank}"
+    tms = torch.tensor([ms_total, t_e2e * 1e3, ms_eval, ms_reproj, ms_reproj_warm], dtype=torch.float64, device=dev)
+    sums = torch.tensor([n["obs"], h2d, d2h, launches], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-    ms_total, e2e_ms, ms_eval = [float(x) for x in tms.cpu()]
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM)
+    ms_total, e2e_ms, ms_eval, ms_reproj, ms_reproj_warm = [float(x) for x in tms.cpu()]
+    obs_all, h2d_all, d2h_all, launches_all = [int(x) for x in sums.cpu()]
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -189,18 +206,28 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6650.0))
     # dominant evaluation kernel k_reproj: algorithmic bytes per observation = 48 B in (uv 16, landmark index 4, frame index 4,
     # landmark 24) + 64 B out (r 16, Jl = dr/dp_w 48): the pose / global Jacobian blocks are linear maps of Jl and are never
-    # materialised.  Its duration is measured separately by profiles/ (ncu) — here the whole evaluation pass is timed.
+    # materialised.  Timed alone with CUDA events on its stream, L2 flushed between launches (rank 0's shard when N > 1).
     alg_bytes = 112.0 * n["obs"]
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "k_reproj_traffic.json"))).get(f"config{a.config}")
+    except Exception:
+        pass
+    wl = WORKLOAD[a.config] if world == 1 else f"{WORKLOAD[a.config]} x {world}: ONE trajectory of {world} x the duration, sharded by time segment (NCCL)"
     line = {"metric": "LM iterations/s", "value": world * 1e3 / ms_step, "unit": "it/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD[a.config], "l2": "inputs+outputs per step exceed L2 only at config 3; band (49 MB) + Jacobians (38 MB) here", **n},
-            "gpu_launches": int(launches), "clocks": clocks_summary(samples),
-            "e2e": {"value": world * 1e3 / e2e_ms, "unit": "it/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-            "mobs_per_s": world * n["obs"] / ms_eval / 1e3, "eval_ms": ms_eval,
+            "config": {"workload": wl, "value_is": "N x (LM iterations/s of the joint N-segment problem) = iterations/s in units of the configured workload",
+                       "l2": "LM step: band (49 MB) + Jacobians (38 MB) per config-2 segment, not flushed (they are produced and consumed on the device "
+                             "inside the step); roofline kernel: L2 flushed with a 256 MiB memset between launches", **n_total, "obs_all_ranks": obs_all},
+            "gpu_launches": int(launches_all), "clocks": clocks_summary(samples),
+            "e2e": {"value": world * 1e3 / e2e_ms, "unit": "it/s", "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h_all},
+            "mobs_per_s": obs_all / ms_eval / 1e3, "eval_ms": ms_eval,
             "lm_breakdown_ms": {"eval": 1e3 * s["time_eval_s"] / a.steps, "assemble": 1e3 * s["time_build_s"] / a.steps, "solve": 1e3 * s["time_solve_s"] / a.steps},
-            "roofline": {"kernel": "evaluation pass (k_frame_pose+k_reproj+k_imu+...)", "bound": "hbm", "achieved": alg_bytes / (ms_eval * 1e-3) / 1e9,
-                         "peak": peak, "unit": "GB/s", "frac": alg_bytes / (ms_eval * 1e-3) / 1e9 / peak, "traffic": None,
-                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}}
+            "roofline": {"kernel": "k_reproj (per-observation residual + Jacobian)", "bound": "hbm", "achieved": alg_bytes / (ms_reproj * 1e-3) / 1e9,
+                         "peak": peak, "unit": "GB/s", "frac": alg_bytes / (ms_reproj * 1e-3) / 1e9 / peak, "traffic": traffic,
+                         "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": ms_reproj, "launch_ms_l2_warm": ms_reproj_warm,
+                         "evaluation_pass_gbs": alg_bytes / (ms_eval * 1e-3) / 1e9,
+                         "peak_source": "MEASURED_PEAKS.json (burst copy)" if peaks else "fallback"}}
     if world == 1:
         r = cpu_reference_leg(scene_mod, a.config, 2, 1, threads, budget_s=15.0)
         line["cpu_baseline"] = {"value": r["lm_per_s"], "unit": "it/s", "cores": threads, "kind": "port", "sample": r["sample"], "mobs_per_s": r["mobs_per_s"]}

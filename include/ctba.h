@@ -143,6 +143,9 @@ int ctba_transfer_bytes(ctba_problem* p, int64_t* bytes2);
 /* Device-only benchmarking hooks (inputs already resident): run `reps` passes of the residual+Jacobian
  * kernels (which != 0) or of a full LM iteration, return the kernel launch count. */
 int ctba_bench_evaluate(ctba_problem* p, int reps, int64_t* launches);
+/* The per-observation reprojection kernel alone, every launch timed with CUDA events on the handle's stream; flush_l2 != 0 overwrites a
+ * 256 MiB buffer between launches so that inputs come from HBM.  ms_avg = average launch duration. */
+int ctba_bench_reproj(ctba_problem* p, int reps, int flush_l2, double* ms_avg);
 
 /* ---- multi-GPU: ONE problem sharded by time segment over the GPUs of a node --------------------------------
  * The reference has no counterpart (Ceres runs `num_threads` CPU threads, bspline_so3r3.h:1773).  Every rank (one process per GPU)

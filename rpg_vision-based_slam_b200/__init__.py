@@ -27,7 +27,7 @@ EXPORTS = [
     "ctba_set_camera", "ctba_set_globals", "ctba_set_corrections", "ctba_get_globals", "ctba_set_flags", "ctba_add_frames", "ctba_add_imu",
     "ctba_add_gp", "ctba_add_bias_cost", "ctba_add_gravity_norm", "ctba_counts", "ctba_evaluate", "ctba_cost", "ctba_solve",
     "ctba_relinearize_time_offsets", "ctba_bench_evaluate", "ctba_set_option", "ctba_invalidate_device", "ctba_transfer_bytes",
-    "ctba_comm_unique_id", "ctba_comm_init_nccl", "ctba_comm_init_local", "ctba_shard_plan",
+    "ctba_bench_reproj", "ctba_comm_unique_id", "ctba_comm_init_nccl", "ctba_comm_init_local", "ctba_shard_plan",
 ]
 
 
@@ -243,6 +243,11 @@ class BSplineSO3R3:
         b = np.zeros(2, dtype=np.int64)
         self._chk(self.L.ctba_transfer_bytes(self.h, _p(b)))
         return int(b[0]), int(b[1])
+
+    def benchReproj(self, reps, flush_l2=True):
+        ms = C.c_double(0.0)
+        self._chk(self.L.ctba_bench_reproj(self.h, int(reps), int(bool(flush_l2)), C.byref(ms)))
+        return float(ms.value)
 
     # ---- multi-GPU: one problem sharded by time segment (ctba.h, "multi-GPU") ----
     @staticmethod

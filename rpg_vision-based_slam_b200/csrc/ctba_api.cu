@@ -504,6 +504,15 @@ int ctba_bench_evaluate(ctba_problem* p, int reps, int64_t* launches) {
   return CTBA_OK;
 }
 
+int ctba_bench_reproj(ctba_problem* p, int reps, int flush_l2, double* ms_avg) {
+  CHECK_P(p);
+  if (!ms_avg) return CTBA_E_ARG;
+  if (p->device < 0) return fail(p, CTBA_E_CUDA, "planning-only handle (device -1): no compute entry points");
+  CTBA_CUDA(p, cudaSetDevice(p->device));
+  int rc = sync_to_device(p); if (rc) return rc;
+  return bench_reproj(p, reps, flush_l2, ms_avg);
+}
+
 // ---- multi-GPU: time-segment sharding (ctba_shard.h) ----
 int ctba_comm_unique_id(char* out128) {
   if (!out128) return CTBA_E_ARG;

@@ -308,6 +308,45 @@ static int launch_evaluate_T(ctba_problem* p, EvalBuffers& ev, const StatePtrs& 
   return CTBA_OK;
 }
 
+// k_reproj alone (the HBM-bound evaluation kernel), timed launch by launch with CUDA events on the handle's stream; between launches
+// a buffer larger than L2 is overwritten so that every launch reads its inputs from HBM.  Returns the average launch time in ms.
+int bench_reproj(ctba_problem* p, int reps, int flush_l2, double* ms_avg) {
+  const Globals G = make_globals(p);
+  cudaStream_t st = p->stream;
+  const int F = (int)p->numFrames(), M = (int)p->numObs();
+  *ms_avg = 0.0;
+  if (F == 0 || M == 0 || reps <= 0) return CTBA_OK;
+  int rc = launch_evaluate(p, p->ev, p->dstate.ptrs(), true); if (rc) return rc;   // frame records + output buffers exist
+  DBuf<double> scratch;
+  const size_t flush_n = (size_t)256 << 17;   // 256 MiB of doubles
+  if (flush_l2) CTBA_CUDA(p, scratch.resize(flush_n));
+  cudaEvent_t a, b;
+  CTBA_CUDA(p, cudaEventCreate(&a)); CTBA_CUDA(p, cudaEventCreate(&b));
+  double total = 0.0;
+  const StatePtrs S = p->dstate.ptrs();
+  for (int i = 0; i < reps; ++i) {
+    if (flush_l2) CTBA_CUDA(p, cudaMemsetAsync(scratch.p, i & 1, flush_n * sizeof(double), st));
+    CTBA_CUDA(p, cudaEventRecord(a, st));
+    if (p->N == 4)
+      k_reproj<4, true><<<cdiv(M, 256), 256, 0, st>>>(G, (const FramePose<4>*)p->ev.frame_pose.p, S.lm, M, p->d_o_frame.p, p->d_o_lm.p,
+                                                       (const double2*)p->d_o_uv.p, p->d_f_inv_std.p, (double2*)p->ev.r_reproj.p, p->ev.Jl.p);
+    else
+      k_reproj<6, true><<<cdiv(M, 256), 256, 0, st>>>(G, (const FramePose<6>*)p->ev.frame_pose.p, S.lm, M, p->d_o_frame.p, p->d_o_lm.p,
+                                                       (const double2*)p->d_o_uv.p, p->d_f_inv_std.p, (double2*)p->ev.r_reproj.p, p->ev.Jl.p);
+    CTBA_CUDA(p, cudaEventRecord(b, st));
+    CTBA_CUDA(p, cudaEventSynchronize(b));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, a, b);
+    total += ms;
+    p->launches++;
+  }
+  cudaEventDestroy(a); cudaEventDestroy(b);
+  scratch.release();
+  *ms_avg = total / reps;
+  CTBA_CUDA(p, cudaGetLastError());
+  return CTBA_OK;
+}
+
 int launch_evaluate(ctba_problem* p, EvalBuffers& ev, const StatePtrs& S, bool jac) {
   return p->N == 4 ? launch_evaluate_T<4>(p, ev, S, jac) : launch_evaluate_T<6>(p, ev, S, jac);
 }

@@ -128,6 +128,7 @@ int sync_to_device(ctba_problem* p);                 // upload dirty measurement
 int download_state(ctba_problem* p);                 // device state -> host vectors
 // residual (+Jacobian) evaluation of every term at state S into p->ev; cost7 (device) filled when want_cost
 int launch_evaluate(ctba_problem* p, EvalBuffers& ev, const StatePtrs& S, bool jac);
+int bench_reproj(ctba_problem* p, int reps, int flush_l2, double* ms_avg);
 int launch_cost(ctba_problem* p, EvalBuffers& ev);   // ev.cost[0..6] from the residual buffers
 int expand_reproj_dense(ctba_problem* p, const StatePtrs& S, double* d_out);  // 2M x (6N+10)
 void solver_free(SolverData* s);

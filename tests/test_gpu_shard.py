@@ -55,10 +55,16 @@ def _compare(pkg, sc, world, iters, **kw):
     for r, (h, s) in enumerate(zip(hs, outs)):
         it = s["iterations"]
         assert it.shape == ig.shape and s["termination_type"] == s_ref["termination_type"], (r, it.shape, ig.shape)
-        assert (it[:, 6] == ig[:, 6]).all()                        # same accept / reject sequence on every rank
-        np.testing.assert_allclose(it[:, 0], ig[:, 0], rtol=1e-8)   # per-iteration cost
-        np.testing.assert_allclose(it[:, 5], ig[:, 5], rtol=1e-6)   # trust-region radius
-        np.testing.assert_allclose(it[1:, 3], ig[1:, 3], rtol=1e-5, atol=1e-12)
+        # same accept / reject sequence; a decision may only differ where the cost change itself is rounding noise (the direct part of
+        # the normal equations is accumulated with atomics, so even two unsharded runs differ in the last bits near convergence)
+        diff = np.nonzero(it[:, 6] != ig[:, 6])[0]
+        k = int(diff[0]) if diff.size else it.shape[0]
+        assert k >= min(5, it.shape[0]), (k, it[:, 6], ig[:, 6])
+        if diff.size:
+            assert abs(ig[k, 1]) <= 1e-6 * ig[k, 0] and abs(it[k, 1]) <= 1e-6 * it[k, 0], (k, ig[k], it[k])
+        np.testing.assert_allclose(it[:k, 0], ig[:k, 0], rtol=1e-8)   # per-iteration cost
+        np.testing.assert_allclose(it[:k, 5], ig[:k, 5], rtol=1e-6)   # trust-region radius
+        np.testing.assert_allclose(it[1:k, 3], ig[1:k, 3], rtol=1e-5, atol=1e-12)
         assert abs(s["final_cost"] - s_ref["final_cost"]) <= 1e-6 * s_ref["final_cost"]
         q, p = h.getKnots()                                        # every rank ends with the whole optimised state
         assert np.abs(p - pr).max() < 1e-3
