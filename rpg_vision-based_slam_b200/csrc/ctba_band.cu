@@ -277,9 +277,11 @@ __global__ void __launch_bounds__(kStepThreads) k_band_panel(BandLayout B, const
   __syncthreads();
   BAND_CLK(3);
   if (b == 0) {
+    // The diagonal block is NOT written back: every other CTA of this launch stages the un-factored A_jj from the same address, and a CTA
+    // that is scheduled late (busy GPU, many partitions) would otherwise read L_jj instead.  Nothing downstream needs L_jj itself — the
+    // substitutions use L_jj^-1.
     for (int e = tid; e < kNB * kNB; e += kStepThreads) {
       const int r = e >> 5, c = e & 31;
-      Ajj[e] = sD[r * kLd + c];
       dinv[(size_t)j * 1024 + e] = sX[c * kLd + r];   // (L^-1)[r][c] = X[c][r]
     }
   } else if (b <= rows) {

@@ -11,6 +11,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <vector>
 #include "ctba_solver.h"
 
@@ -148,6 +149,7 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
       if (!std::isfinite(model_cost_change) || !std::isfinite(step_norm)) ok = false;
     }
     if (!ok || model_cost_change <= 0.0) {
+      if (getenv("CTBA_DEBUG")) fprintf(stderr, "[ctba %p] iter %d invalid step: flag %d %d model %.6g step %.6g radius %.3g\n", (void*)p, iter, host_flag[0], host_flag[1], model_cost_change, step_norm, radius);
       ++invalid;
       radius /= decrease_factor; decrease_factor *= 2.0;
       out->num_unsuccessful_steps++;
