@@ -64,7 +64,7 @@ def cpu_reference_leg(scene_mod, cfg, steps, warmup, threads, budget_s=20.0):
     pkg = importlib.import_module(PKG)
     slice_s = 3.0
     dens = scene_mod.config_scene(cfg, duration_s=slice_s, n_landmarks=1)  # cheap call to read rates
-    full = {1: (50.0, 20000), 2: (180.0, 40000), 3: (3600.0, 200000)}[cfg]
+    full = {1: (50.0, 20000), 2: (180.0, 40000), 3: (3600.0, 270000)}[cfg]
     sc = scene_mod.config_scene(cfg, duration_s=slice_s, n_landmarks=max(int(full[1] * slice_s / full[0]), 50))
     o = OracleSpline(sc["order"], sc["dt_ns"], sc["start_t_ns"])
     pkg.load_scene(o, sc)
@@ -121,7 +121,7 @@ def main():
     # N > 1: ONE trajectory of N x the configured duration (N x the landmarks), sharded by time segment over the N ranks (weak scaling:
     # the per-GPU share of the problem is the configured workload; NCCL exchange steps per LM iteration).  Every rank is
     # handed the complete problem through the same C-ABI calls as a single-GPU caller; the library keeps the rank's units.
-    base = {1: (50.0, 20000), 2: (180.0, 40000), 3: (3600.0, 200000)}[a.config]
+    base = {1: (50.0, 20000), 2: (180.0, 40000), 3: (3600.0, 270000)}[a.config]
     sc = scene_mod.config_scene(a.config, duration_s=base[0] * world, n_landmarks=base[1] * world) if world > 1 else scene_mod.config_scene(a.config)
     g = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=local_rank)
     pkg.load_scene(g, sc)

@@ -619,6 +619,47 @@ __global__ void __launch_bounds__(128) k_knot_schur(const FramePose<N>* __restri
   }
 }
 
+// Same gather with one THREAD per (knot, dk): for sparse frame rates (fewer than ~4 frames per knot, e.g. the 2.8 Hz flight of config 3) a
+// warp per task leaves 29 of 32 lanes idle and spends its time in the 36 x 5 reduction shuffles.
+template <int N>
+__global__ void __launch_bounds__(128) k_knot_schur_thread(const FramePose<N>* __restrict__ fps, int K, int KD, int T, const int32_t* __restrict__ f_s,
+                                                           const int32_t* __restrict__ kf_begin, const int32_t* __restrict__ kf_list,
+                                                           const int32_t* __restrict__ node_of_knot, const double* __restrict__ Sp, BandLayout Hw) {
+  const size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= (size_t)K * (KD + 1)) return;
+  const int kr = (int)(w / (KD + 1)), dk = (int)(w % (KD + 1));
+  const int kc = kr - dk;
+  if (kc < 0) return;
+  const int rb = kf_begin[kr], nr = kf_begin[kr + 1] - rb;
+  const int cb = kf_begin[kc], nc = kf_begin[kc + 1] - cb;
+  if (nr == 0 || nc == 0) return;
+  double C[36];
+#pragma unroll
+  for (int e = 0; e < 36; ++e) C[e] = 0.0;
+  bool any = false;
+  for (int a = 0; a < nr; ++a) {
+    const int f = kf_list[rb + a];
+    for (int b = 0; b < nc; ++b) {
+      const int f2 = kf_list[cb + b];
+      const int d = f2 - f;
+      if (d > T || -d > T) continue;
+      const double2* S2 = reinterpret_cast<const double2*>(Sp + ((size_t)(d >= 0 ? f : f2) * (T + 1) + (d >= 0 ? d : -d)) * 36);
+      double Sl[36];
+#pragma unroll
+      for (int e = 0; e < 18; ++e) { const double2 v = S2[e]; Sl[2 * e] = v.x; Sl[2 * e + 1] = v.y; }
+      chain_block_acc<N>(fps[f], kr - f_s[f], fps[f2], kc - f_s[f2], Sl, d < 0, C);
+      any = true;
+    }
+  }
+  if (!any) return;
+  const int r0 = 6 * node_of_knot[kr], c0 = 6 * node_of_knot[kc];
+#pragma unroll
+  for (int e = 0; e < 36; ++e) {
+    const int a = e / 6, c = e % 6;
+    if (dk > 0 || c <= a) Hw.band[band_addr(Hw, r0 + a, c0 + c)] += C[e];
+  }
+}
+
 // border rows (pose x globals mapped to knot dofs) and the Schur right-hand-side correction, thread per (knot, dof)
 template <int N>
 __global__ void k_knot_border(const FramePose<N>* __restrict__ fps, int K, const int32_t* __restrict__ f_s, const int32_t* __restrict__ kf_begin,
@@ -1052,6 +1093,11 @@ int assemble_structure(ctba_problem* p) {
   sd->max_frame_obs = hs.max_frame_obs;
   if ((size_t)sd->max_frame_obs * 18 * sizeof(double) > 200 * 1024) { p->err = "assemble_structure: more than 1422 valid observations in one frame"; return CTBA_E_ARG; }
   sd->T = T; sd->hbn = hs.hbn; sd->KD = hs.KD;
+  {
+    int covered = 0;
+    for (int k = 0; k < K; ++k) covered += hs.kfb[k + 1] > hs.kfb[k];
+    sd->frames_per_knot = covered ? (double)F * p->N / covered : 0.0;
+  }
   for (int i = 0; i < GT_SIZE; ++i) sd->gactive[i] = hs.gactive[i];
   const int n_band = hs.n_band, n_pad = hs.n_pad, nbw = hs.nbw;
   BandLayout B{n_band, n_pad, n_pad / kNB, nbw, nullptr, nullptr, nullptr};
@@ -1197,8 +1243,14 @@ static int assemble_schur_T(ctba_problem* p, double radius) {
     if (fs_smem > 48 * 1024) CTBA_CUDA(p, cudaFuncSetAttribute(k_frame_schur, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs_smem));
     k_frame_schur<<<F, kFsThreads, fs_smem, st>>>(F, T, p->d_f_obs_begin.p, p->d_o_lm.p, p->d_o_frame.p, sd->d_o_pos.p, sd->d_lm_obs_begin.p,
                                             sd->d_lm_obs.p, sd->d_lm_frame.p, sd->Yo.p, sd->Zo.p, sd->vig.p, sd->ViYg.p, any_g, sd->Sp.p, sd->Sb.p, sd->rp.p);
-    k_knot_schur<N><<<cdiv((size_t)sd->K * (sd->KD + 1) * 32, 128), 128, 0, st>>>(fps, sd->K, sd->KD, T, p->d_f_s.p, sd->d_kf_begin.p,
-                                                                                   sd->d_kf_list.p, sd->d_node_of_knot.p, sd->Sp.p, Hw);
+    // frames per knot = F N / K; a task pairs the frames of two knots
+    const double fpk = sd->frames_per_knot;
+    if (fpk * fpk < 16.0)
+      k_knot_schur_thread<N><<<cdiv((size_t)sd->K * (sd->KD + 1), 128), 128, 0, st>>>(fps, sd->K, sd->KD, T, p->d_f_s.p, sd->d_kf_begin.p,
+                                                                                       sd->d_kf_list.p, sd->d_node_of_knot.p, sd->Sp.p, Hw);
+    else
+      k_knot_schur<N><<<cdiv((size_t)sd->K * (sd->KD + 1) * 32, 128), 128, 0, st>>>(fps, sd->K, sd->KD, T, p->d_f_s.p, sd->d_kf_begin.p,
+                                                                                     sd->d_kf_list.p, sd->d_node_of_knot.p, sd->Sp.p, Hw);
     k_knot_border<N><<<cdiv((size_t)6 * sd->K, 128), 128, 0, st>>>(fps, sd->K, p->d_f_s.p, sd->d_kf_begin.p, sd->d_kf_list.p,
                                                                     sd->d_node_of_knot.p, sd->Sb.p, sd->rp.p, gm, any_g, Hw, rhs_acc);
     p->launches += 4;

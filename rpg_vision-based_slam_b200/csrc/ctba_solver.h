@@ -60,6 +60,7 @@ struct SolverData {
   DBuf<int32_t> d_lm_frame;   // frame of every entry of the landmark observation lists
   DBuf<int32_t> d_lm_owner;   // sharded: owning rank of every landmark
   int max_frame_obs = 1;
+  double frames_per_knot = 0.0;   // average number of frames whose window contains a knot (over the knots that have any)
   DBuf<int32_t> d_o_pos, d_kf_begin, d_kf_list;   // observation -> slot in its landmark's list; knot -> frames (CSR)
   DBuf<double> Vi, vig, ViYg, Yo, Zo, lm_corner_partial;   // Schur gather scratch (ctba_assemble.cu)
   DBuf<uint8_t> d_touch_knot, d_touch_bias, d_touch_lm;  // bit0 rot/acc, bit1 pos/gyr

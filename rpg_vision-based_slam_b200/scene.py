@@ -211,8 +211,8 @@ def config_scene(cfg, **over):
     elif cfg == 2:  # optimize_vi_continuous_time, EuRoC MH_01-shaped: 180 s, 20 Hz camera, 200 Hz IMU, ~40k landmarks, ~600k obs
         kw = dict(order=6, dt_s=0.1, duration_s=180.0, cam_hz=20.0, imu_hz=200.0, gp_hz=0.0, n_landmarks=40000, track_len=17, cam="euroc",
                   seed=20240103, flags=(False, True, True, True, True), gravity_norm=True)
-    elif cfg == 3:  # optimize_gv_continuous_time: 1 h, 10k frames, 200k landmarks, 5M obs, GP 10 Hz
-        kw = dict(order=6, dt_s=0.1, duration_s=3600.0, cam_hz=10000.0 / 3600.0, imu_hz=0.0, gp_hz=10.0, n_landmarks=200000, track_len=28,
+    elif cfg == 3:  # optimize_gv_continuous_time: 1 h, 10k frames, 5M obs (500 per frame), GP 10 Hz; 270k landmarks of 28 frames each, of which ~18.5 project inside the image
+        kw = dict(order=6, dt_s=0.1, duration_s=3600.0, cam_hz=10000.0 / 3600.0, imu_hz=0.0, gp_hz=10.0, n_landmarks=270000, track_len=28,
                   cam="euroc", seed=20240104, flags=(False, True, False, True, True))
     else:
         raise ValueError(cfg)

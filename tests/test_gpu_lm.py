@@ -63,6 +63,14 @@ def test_lm_gv_cubic(pkg, scene, oracle):
     _check(gpu, cpu, sg, so)
 
 
+def test_lm_sparse_frame_rate(pkg, scene, oracle):
+    """3 Hz camera on 0.1 s knots (the config-3 regime: fewer than two frames per knot -> thread-per-task Schur expansion)."""
+    sc = scene.make_scene(order=6, duration_s=8.0, cam_hz=3.0, n_landmarks=120, track_len=6, imu_hz=0, gp_hz=10, seed=13,
+                          flags=(False, True, False, True, True))
+    gpu, cpu, sg, so = _run(pkg, oracle, sc, 6)
+    _check(gpu, cpu, sg, so)
+
+
 def test_lm_fixed_globals_and_first_call(pkg, scene, oracle):
     """optimize(1) as the drivers' first call (always NO_CONVERGENCE), then a second Solve re-derives the Jacobi scaling;
     globals constant."""

@@ -103,3 +103,27 @@ def test_sharded_vi_no_gp(pkg, scene):
     sc = scene.make_scene(order=6, duration_s=60.0, n_landmarks=1200, track_len=10, imu_hz=100, gp_hz=0, dt_s_bias=0.5, seed=77,
                           flags=(False, True, True, True, True), gravity_norm=True)
     _compare(pkg, sc, 2, 6)
+
+
+def test_concurrent_independent_handles_are_deterministic(pkg, scene):
+    """Three unsharded solves of the same problem running concurrently on one device (one host thread each) must take the same path as a
+    solve that has the GPU to itself: regression test for CTAs of one launch that communicated through in-place overwrites."""
+    sc = scene.make_scene(order=6, duration_s=90.0, n_landmarks=1800, track_len=12, imu_hz=100, gp_hz=10, dt_s_bias=0.5,
+                          flags=(True, True, True, True, True), gravity_norm=True, outlier_frac=0.02, seed=11)
+    ref = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=0)
+    pkg.load_scene(ref, sc)
+    s_ref = ref.optimize(6)
+    for _ in range(3):
+        hs = [pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=0) for _ in range(3)]
+        for h in hs:
+            pkg.load_scene(h, sc)
+        outs = [None] * 3
+        th = [threading.Thread(target=lambda r=r: outs.__setitem__(r, hs[r].optimize(6)), daemon=True) for r in range(3)]
+        [t.start() for t in th]
+        [t.join(300) for t in th]
+        for o in outs:
+            assert o is not None
+            assert (o["iterations"][:, 6] == s_ref["iterations"][:, 6]).all()
+            np.testing.assert_allclose(o["iterations"][:, 0], s_ref["iterations"][:, 0], rtol=1e-8)
+        for h in hs:
+            h.close()
