@@ -186,7 +186,7 @@ __device__ __forceinline__ void potrf_trsm32_cta(double* sD, double* sX, double*
 //
 // Border storage of partition p ("FB"): row-major, R = 32*(nrb-1) + 16 rows (nrb-1 = nbw row blocks of S_{p-1} for p >= 1, none for
 // p = 0; the last 16 rows are the 15 globals + right-hand side), ld = 32 * ncols doubles, ncols = |I_p| + (nbw columns of S_p if p < P-1).
-constexpr int kMaxParts = 32;
+constexpr int kMaxParts = 64;
 struct BandPart {
   int c0;        // first block column of the interior
   int nI;        // interior block columns
@@ -195,16 +195,19 @@ struct BandPart {
   int ld;        // 32 * ncols
   double* fb;    // border rows of this partition
 };
-struct BandParts { int P; BandPart part[kMaxParts]; };
+struct BandParts { int P; int sepw; BandPart part[kMaxParts]; };   // sepw: block columns per separator (nbw at level 0)
 
 // task counts of partition q at step t (shared by host and device)
 __host__ __device__ inline void part_tasks(const BandLayout& B, const BandPart& q, int t, int* n_panel, int* m_upd, int* k_lo) {
   const int j = q.c0 + t;
   const bool has_panel = t < q.nI;
-  const int rows = has_panel ? (B.nbw < B.nbc - 1 - j ? B.nbw : B.nbc - 1 - j) : 0;
+  // a partition never reaches past its right separator: at level 0 that is the band reach anyway, at the interface levels (band 2 sepw - 1,
+  // interiors one separator wide) the blocks beyond are structurally zero AND belong to a partition that is being factored concurrently
+  const int last = q.c0 + q.ncols - 1 < B.nbc - 1 ? q.c0 + q.ncols - 1 : B.nbc - 1;
+  const int rows = has_panel ? (B.nbw < last - j ? B.nbw : last - j) : 0;
   *n_panel = has_panel ? 1 + rows + q.nrb : 0;
   *k_lo = has_panel ? j + 1 : j;
-  int k_hi = j - 1 + B.nbw; if (k_hi > B.nbc - 1) k_hi = B.nbc - 1;
+  int k_hi = j - 1 + B.nbw; if (k_hi > last) k_hi = last;
   int m = (t >= 1 && t <= q.nI) ? k_hi - *k_lo + 1 : 0;
   *m_upd = m > 0 ? m : 0;
 }
@@ -359,7 +362,7 @@ __global__ void __launch_bounds__(256) k_fb_init(BandLayout B, const __grid_cons
     }
     return;
   }
-  const int k = Q.c0 - B.nbw + rb;          // block column of the left separator that owns this row block
+  const int k = Q.c0 - (Q.nrb - 1) + rb;    // block column of the left separator that owns this row block
   const bool inband = (i - k) <= B.nbw;
   const double* T = B.band + ((size_t)k * (B.nbw + 1) + (inband ? i - k : 0)) * 1024;   // block (i, k)
   for (int e = threadIdx.x; e < kNB * kNB; e += 256) {
@@ -438,7 +441,7 @@ __global__ void __launch_bounds__(256) k_iface_assemble(BandLayout B, BandLayout
   const int nb1_2 = B2.nbw + 1;
   const int nblk = B2.nbc * nb1_2;
   const int blk = blockIdx.x;
-  const int nbw = B.nbw;
+  const int nbw = PS.sepw;      // separator width (== B.nbw at level 0; the band stride of B is B.nbw + 1)
   auto local = [&](int q) { return q >= IA.q_lo && q < IA.q_hi; };
   if (blk < nblk) {
     const int K2 = blk / nb1_2, off = blk % nb1_2, I2 = K2 + off;
@@ -449,7 +452,7 @@ __global__ void __launch_bounds__(256) k_iface_assemble(BandLayout B, BandLayout
       const bool adjacent = qk >= IA.q_lo - 1 && qk <= IA.q_hi - 1;      // separator qk borders one of this rank's partitions
       const bool have_g = local(qk + 1);
       const int s = PS.part[qk + 1].c0 - nbw;                         // first block column of separator qk
-      const double* T = B.band + ((size_t)(s + c) * (nbw + 1) + (a - c)) * 1024;
+      const double* T = B.band + ((size_t)(s + c) * (B.nbw + 1) + (a - c)) * 1024;
       const double* G = IA.gram + IA.gram_off[qk + 1];
       const int ldg = kNB * PS.part[qk + 1].nrb;
       for (int e = threadIdx.x; e < 1024; e += 256) {
@@ -503,8 +506,8 @@ __global__ void k_flag_from_sum(const double* __restrict__ extra, int32_t* __res
 __global__ void k_iface_scatter(BandLayout B, BandLayout B2, const __grid_constant__ BandParts PS, const double* __restrict__ delta2, double* __restrict__ delta) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < B2.n_pad) {
-    const int K2 = i >> 5, q = K2 / B.nbw, c = K2 % B.nbw;
-    const int s = PS.part[q + 1].c0 - B.nbw;
+    const int K2 = i >> 5, q = K2 / PS.sepw, c = K2 % PS.sepw;
+    const int s = PS.part[q + 1].c0 - PS.sepw;
     delta[(size_t)(s + c) * kNB + (i & 31)] = delta2[i];
   } else if (i < B2.n_pad + kBorder) {
     delta[B.n_pad + (i - B2.n_pad)] = delta2[i];
@@ -576,7 +579,7 @@ __global__ void __launch_bounds__(256) k_back_rhs(BandLayout B, const __grid_con
   const double* z = delta + B.n_pad;
 #pragma unroll
   for (int g = 0; g < GT_SIZE; ++g) t -= F[(size_t)(rs + g) * Q.ld] * z[g];
-  const double* xs = delta + (size_t)(Q.c0 - B.nbw) * kNB;   // only dereferenced when rs > 0 (partition >= 1)
+  const double* xs = delta + (size_t)(Q.c0 - (Q.nrb - 1)) * kNB;   // left separator; only dereferenced when rs > 0 (partition >= 1)
   double t2 = 0.0;
   for (int r = 0; r < rs; r += 2) { t -= F[(size_t)r * Q.ld] * xs[r]; t2 += F[(size_t)(r + 1) * Q.ld] * xs[r + 1]; }
   delta[col] = t - t2;
@@ -608,7 +611,7 @@ __global__ void __launch_bounds__(288) k_band_backsolve(BandLayout B, const __gr
   auto src = [&](int i) -> const double* {
     if (i < first) return nullptr;
     if (warp == 0) return dinv + (size_t)i * 1024 + lane;                                   // (L_ii^-1)[c][lane]
-    if (off <= B.nbw && i + off < B.nbc) return B.band + ((size_t)i * nb1 + off) * 1024 + lane;   // L(i+off, i)[r][lane]
+    if (off <= B.nbw && i + off < B.nbc && i + off < Q.c0 + Q.ncols) return B.band + ((size_t)i * nb1 + off) * 1024 + lane;   // L(i+off, i)[r][lane]
     return nullptr;
   };
   for (int e = threadIdx.x; e < B.nbw * kNB; e += blockDim.x) {   // solution on the right separator (columns last+1 .. last+nbw)
@@ -664,41 +667,69 @@ __global__ void __launch_bounds__(288) k_band_backsolve(BandLayout B, const __gr
 }
 
 // ================================================== host side =====================================================
-struct BandPlan {
-  // key
-  int nbc = -1, nbw = -1, req = -2; const double* band_ptr = nullptr; const double* border_ptr = nullptr;
+// One level of the nested solve.  Level 0 is the reduced system itself (Hw); level l + 1 is the interface system of level l (its separators:
+// block tridiagonal with sepw-wide dense blocks, stored as a band of half width 2 sepw - 1).  Every level with P > 1 eliminates its
+// interiors concurrently, one block column per launch; at the interface levels an interior is ONE separator block of the level below
+// (odd-even reduction), so the sequential depth is  max|I_q| + sepw * ceil(log2 P0)  block steps instead of  max|I_q| + (P0 - 1) sepw.
+struct BandLevel {
+  BandLayout B{};           // the system of this level
   int P = 1, max_steps = 0;
-  BandParts PS{};           // every partition of the full system (P == 1: one partition whose border is Hw.border itself)
-  BandParts PSloc{};        // the partitions this handle factors (all of them unless the problem is sharded over ranks)
-  BandParts PS2{};          // the interface system as a single partition
-  BandLayout B2{};
+  BandParts PS{};           // every partition of this level (P == 1: one partition whose border is B.border itself)
+  BandParts PSloc{};        // the partitions this handle factors (all of them, except at level 0 of a problem sharded over ranks)
   GramPlan GP{};
   IfaceArgs IA{};
   int gram_tasks = 0, gram_tiles = 0;
-  size_t iface_elems = 0;
-  DBuf<double> fb, gram, gram_scratch, iface /* band2 | border2 | corner2 | extra */, delta2, dinv2, cpart, cpart2, dinv;
+  size_t sys_elems = 0;     // next level's band | border | corner | extra, ONE buffer (a sharded solve all-reduces level 0's)
+  DBuf<double> fb, gram, gram_scratch, sys, delta_own, dinv, cpart;
+  double* delta = nullptr;  // solution of this level (level 0: the solver's delta; otherwise delta_own)
   size_t* d_gram_off = nullptr;
-  ~BandPlan() {
-    DBuf<double>* dd[] = {&fb, &gram, &gram_scratch, &iface, &delta2, &dinv2, &cpart, &cpart2, &dinv};
+  ~BandLevel() {
+    DBuf<double>* dd[] = {&fb, &gram, &gram_scratch, &sys, &delta_own, &dinv, &cpart};
     for (auto* d : dd) d->release();
     if (d_gram_off) cudaFree(d_gram_off);
   }
 };
+struct BandPlan {
+  // key
+  int nbc = -1, nbw = -1, req = -2; const double* band_ptr = nullptr; const double* border_ptr = nullptr;
+  std::vector<BandLevel*> lv;
+  void clear() { for (auto* l : lv) delete l; lv.clear(); }
+  ~BandPlan() { clear(); }
+};
 
-int band_partition_layout(int nbc, int nbw, int requested, int world, PartLayout* out) {
+// sequential block steps of the nested solve with P partitions at level 0
+static int nested_depth(int nbc, int nbw, int P) {
+  if (P <= 1) return nbc;
+  int d = (nbc - (P - 1) * nbw + P - 1) / P + 1, m = P - 1;   // largest interior + its flush step
+  while (m > 2) { d += nbw + 1; m = (m + 1) / 2 - 1; }          // one separator block per interface level
+  return d + m * nbw;                                           // last level: one partition of m blocks
+}
+
+int band_partition_layout(int nbc, int nbw, int requested, int world, int nested, PartLayout* out) {
   int P = 1;
-  const auto fits = [&](int q) { return (nbc - (q - 1) * nbw) / q >= std::max(nbw, 2); };
-  if (!(nbw < 1 || 2 * nbw > 63)) {
-    P = requested > 0 ? requested : (int)lround(std::sqrt((double)nbc / (1.2 * nbw)));
-    P = std::max(1, std::min(P, kMaxParts));
-    if (world > 1) {
-      P = std::max(world, (P / world) * world);
+  const auto fits = [&](int q) { return q >= 1 && q <= kMaxParts && (nbc - (q - 1) * nbw) / q >= std::max(nbw, 2); };
+  const bool can_split = !(nbw < 1 || 2 * nbw > 63);
+  if (can_split) {
+    if (requested > 0) {
+      P = std::max(1, std::min(requested, kMaxParts));
+      if (world > 1) P = std::max(world, (P / world) * world);
       while (P > world && !fits(P)) P -= world;
-    } else {
-      while (P > 1 && !fits(P)) --P;
+    } else if (!nested) {   // flat interface system: balance interior length against the sequential interface solve
+      P = (int)lround(std::sqrt((double)nbc / (1.2 * nbw)));
+      P = std::max(1, std::min(P, kMaxParts));
+      if (world > 1) P = std::max(world, (P / world) * world);
+      while (P > (world > 1 ? world : 1) && !fits(P)) P -= (world > 1 ? world : 1);
+    } else {   // nested interface levels: the P that minimises the sequential depth (ties: fewer partitions)
+      int best = nested_depth(nbc, nbw, 1);
+      for (int q = world > 1 ? world : 2; q <= kMaxParts; q += (world > 1 ? world : 1)) {
+        if (!fits(q)) break;
+        const int d = nested_depth(nbc, nbw, q);
+        if (d < best || (world > 1 && P < world)) { best = d; P = q; }
+      }
     }
   }
-  if (world > 1 && (P < world || P > kMaxParts || nbw < 1 || 2 * nbw > 63 || !fits(P))) return -1;
+  if (world > 1 && (P < world || !can_split || !fits(P))) return -1;
+  if (world == 1 && P > 1 && !fits(P)) P = 1;
   out->P = P; out->c0.assign(P, 0); out->nI.assign(P, nbc);
   if (P == 1) return 0;
   const int interior = nbc - (P - 1) * nbw;
@@ -710,76 +741,109 @@ int band_partition_layout(int nbc, int nbw, int requested, int world, PartLayout
   return 0;
 }
 
-static int plan_build(ctba_problem* p, BandPlan& pl, const BandLayout& B) {
-  pl.nbc = B.nbc; pl.nbw = B.nbw; pl.req = p->band_partitions; pl.band_ptr = B.band; pl.border_ptr = B.border;
-  PartLayout lay;
-  int q_lo = 0, q_hi = 1;
-  if (p->sharded) {
-    lay = p->shard->layout; q_lo = p->shard->q_lo; q_hi = p->shard->q_hi;
-    if (p->shard->nbc != B.nbc || p->shard->nbw != B.nbw) { p->err = "band plan: structure differs from the sharding plan"; return CTBA_E_STATE; }
-  } else {
-    band_partition_layout(B.nbc, B.nbw, p->band_partitions, 1, &lay);
-    q_hi = lay.P;
+// partitions of an interface level: m separator blocks of sepw columns; blocks 0, 2, 4, ... are interiors, 1, 3, 5, ... separators;
+// the last interior absorbs a trailing block so that the level ends with an interior
+static void interface_layout(int m, int sepw, PartLayout* out) {
+  const int P = m <= 2 ? 1 : (m + 1) / 2;
+  out->P = P; out->c0.assign(P, 0); out->nI.assign(P, m * sepw);
+  if (P == 1) return;
+  for (int q = 0; q < P; ++q) {
+    out->c0[q] = 2 * q * sepw;
+    out->nI[q] = (q == P - 1) ? (m - 2 * q) * sepw : sepw;
   }
-  pl.P = lay.P;
-  CTBA_CUDA(p, pl.dinv.resize((size_t)B.nbc * 1024));
-  CTBA_CUDA(p, pl.cpart.resize((size_t)cdiv(B.n_pad, 256) * 256));
-  pl.PS = BandParts{};
-  if (pl.P == 1) {
-    pl.PS.P = 1;
-    pl.PS.part[0] = BandPart{0, B.nbc, 1, B.nbc, B.n_pad, B.border};
-    pl.PSloc = pl.PS;
-    pl.max_steps = B.nbc;
+}
+
+// builds level `li` (its system BL.B must be set) and, when it has more than one partition, allocates the next level's system
+static int level_build(ctba_problem* p, BandPlan& pl, int li, const PartLayout& lay, int sepw, int q_lo, int q_hi) {
+  BandLevel& L = *pl.lv[li];
+  const BandLayout& B = L.B;
+  L.P = lay.P;
+  CTBA_CUDA(p, L.dinv.resize((size_t)B.nbc * 1024));
+  CTBA_CUDA(p, L.cpart.resize((size_t)cdiv(B.n_pad, 256) * 256));
+  L.PS = BandParts{};
+  if (L.P == 1) {
+    L.PS.P = 1; L.PS.sepw = 0;
+    L.PS.part[0] = BandPart{0, B.nbc, 1, B.nbc, B.n_pad, B.border};
+    L.PSloc = L.PS;
+    L.max_steps = B.nbc;
     return CTBA_OK;
   }
-  const int P = pl.P, nbw = B.nbw;
+  const int P = L.P;
   size_t fb_total = 0, gram_total = 0;
   std::vector<size_t> fb_off(P, 0), g_off(P, 0), g_off_loc;
   int maxI = 0;
-  pl.PS.P = P;
+  L.PS.P = P; L.PS.sepw = sepw;
   for (int q = 0; q < P; ++q) {
     const int nI = lay.nI[q];
-    BandPart& Q = pl.PS.part[q];
-    Q.c0 = lay.c0[q]; Q.nI = nI; Q.nrb = (q == 0 ? 1 : nbw + 1); Q.ncols = nI + (q < P - 1 ? nbw : 0); Q.ld = kNB * Q.ncols; Q.fb = nullptr;
+    BandPart& Q = L.PS.part[q];
+    Q.c0 = lay.c0[q]; Q.nI = nI; Q.nrb = (q == 0 ? 1 : sepw + 1); Q.ncols = nI + (q < P - 1 ? sepw : 0); Q.ld = kNB * Q.ncols; Q.fb = nullptr;
     if (q < q_lo || q >= q_hi) continue;
     fb_off[q] = fb_total; fb_total += (size_t)Q.nrb * kNB * Q.ld;
     g_off[q] = gram_total; gram_total += (size_t)(Q.nrb * kNB) * (Q.nrb * kNB);
     g_off_loc.push_back(g_off[q]);
     maxI = std::max(maxI, nI);
   }
-  pl.max_steps = maxI + 1;   // + the flush step that applies the last interior column's update to the right separator
-  CTBA_CUDA(p, pl.fb.resize(fb_total)); CTBA_CUDA(p, pl.gram.resize(gram_total));
-  pl.GP = GramPlan{}; pl.GP.P = q_hi - q_lo;
-  pl.PSloc = BandParts{}; pl.PSloc.P = q_hi - q_lo;
-  pl.IA = IfaceArgs{};
+  L.max_steps = maxI + 1;   // + the flush step that applies the last interior column's update to the right separator
+  CTBA_CUDA(p, L.fb.resize(fb_total)); CTBA_CUDA(p, L.gram.resize(gram_total));
+  L.GP = GramPlan{}; L.GP.P = q_hi - q_lo;
+  L.PSloc = BandParts{}; L.PSloc.P = q_hi - q_lo; L.PSloc.sepw = sepw;
+  L.IA = IfaceArgs{};
   int tiles = 0, tasks = 0;
   for (int q = q_lo; q < q_hi; ++q) {
-    BandPart& Q = pl.PS.part[q];
-    Q.fb = pl.fb.p + fb_off[q];
-    pl.PSloc.part[q - q_lo] = Q;
-    pl.IA.gram_off[q] = g_off[q];
+    BandPart& Q = L.PS.part[q];
+    Q.fb = L.fb.p + fb_off[q];
+    L.PSloc.part[q - q_lo] = Q;
+    L.IA.gram_off[q] = g_off[q];
     const int nt = Q.nrb * (Q.nrb + 1) / 2, ns = (Q.nI + kGramChunk - 1) / kGramChunk;
-    pl.GP.tile0[q - q_lo] = tiles; pl.GP.task0[q - q_lo] = tasks; pl.GP.nsplit[q - q_lo] = ns;
+    L.GP.tile0[q - q_lo] = tiles; L.GP.task0[q - q_lo] = tasks; L.GP.nsplit[q - q_lo] = ns;
     tiles += nt; tasks += nt * ns;
   }
-  pl.GP.tile0[q_hi - q_lo] = tiles; pl.GP.task0[q_hi - q_lo] = tasks;
-  pl.gram_tiles = tiles; pl.gram_tasks = tasks;
-  pl.IA.gram = pl.gram.p; pl.IA.q_lo = q_lo; pl.IA.q_hi = q_hi;
-  CTBA_CUDA(p, pl.gram_scratch.resize((size_t)tasks * 1024));
-  if (!pl.d_gram_off) CTBA_CUDA(p, cudaMalloc((void**)&pl.d_gram_off, kMaxParts * sizeof(size_t)));
-  CTBA_CUDA(p, cudaMemcpy(pl.d_gram_off, g_off_loc.data(), g_off_loc.size() * sizeof(size_t), cudaMemcpyHostToDevice));
-  // interface system: band2 | border2 | corner2 | extra in ONE buffer (a sharded solve sums it over the ranks with a single all-reduce)
-  BandLayout& B2 = pl.B2;
-  B2.nbc = (P - 1) * nbw; B2.n_pad = B2.nbc * kNB; B2.n_band = B2.n_pad; B2.nbw = std::min(2 * nbw - 1, B2.nbc - 1);
+  L.GP.tile0[q_hi - q_lo] = tiles; L.GP.task0[q_hi - q_lo] = tasks;
+  L.gram_tiles = tiles; L.gram_tasks = tasks;
+  L.IA.gram = L.gram.p; L.IA.q_lo = q_lo; L.IA.q_hi = q_hi;
+  CTBA_CUDA(p, L.gram_scratch.resize((size_t)tasks * 1024));
+  if (!L.d_gram_off) CTBA_CUDA(p, cudaMalloc((void**)&L.d_gram_off, kMaxParts * sizeof(size_t)));
+  CTBA_CUDA(p, cudaMemcpy(L.d_gram_off, g_off_loc.data(), g_off_loc.size() * sizeof(size_t), cudaMemcpyHostToDevice));
+  // the next level: band | border | corner | extra in ONE buffer
+  BandLayout B2{};
+  B2.nbc = (P - 1) * sepw; B2.n_pad = B2.nbc * kNB; B2.n_band = B2.n_pad; B2.nbw = std::min(2 * sepw - 1, B2.nbc - 1);
   const size_t e_band = B2.band_elems(), e_border = (size_t)kBorder * B2.n_pad;
-  pl.iface_elems = e_band + e_border + kBorder * kBorder + 32;
-  CTBA_CUDA(p, pl.iface.resize(pl.iface_elems));
-  CTBA_CUDA(p, pl.delta2.resize(B2.n_pad + kBorder)); CTBA_CUDA(p, pl.dinv2.resize((size_t)B2.nbc * 1024));
-  CTBA_CUDA(p, pl.cpart2.resize((size_t)cdiv(B2.n_pad, 256) * 256));
-  B2.band = pl.iface.p; B2.border = pl.iface.p + e_band; B2.corner = B2.border + e_border;
-  pl.IA.extra = B2.corner + kBorder * kBorder;
-  pl.PS2 = BandParts{}; pl.PS2.P = 1;
-  pl.PS2.part[0] = BandPart{0, B2.nbc, 1, B2.nbc, B2.n_pad, B2.border};
+  L.sys_elems = e_band + e_border + kBorder * kBorder + 32;
+  CTBA_CUDA(p, L.sys.resize(L.sys_elems));
+  B2.band = L.sys.p; B2.border = L.sys.p + e_band; B2.corner = B2.border + e_border;
+  L.IA.extra = B2.corner + kBorder * kBorder;
+  BandLevel* N = new BandLevel();
+  N->B = B2;
+  CTBA_CUDA(p, N->delta_own.resize(B2.n_pad + kBorder));
+  CTBA_CUDA(p, cudaMemset(N->delta_own.p, 0, (B2.n_pad + kBorder) * sizeof(double)));
+  N->delta = N->delta_own.p;
+  pl.lv.push_back(N);
+  return CTBA_OK;
+}
+
+static int plan_build(ctba_problem* p, BandPlan& pl, const BandLayout& B) {
+  pl.clear();
+  pl.nbc = B.nbc; pl.nbw = B.nbw; pl.req = p->band_partitions + 1000 * p->band_nested; pl.band_ptr = B.band; pl.border_ptr = B.border;
+  PartLayout lay;
+  int q_lo = 0, q_hi = 1;
+  if (p->sharded) {
+    lay = p->shard->layout; q_lo = p->shard->q_lo; q_hi = p->shard->q_hi;
+    if (p->shard->nbc != B.nbc || p->shard->nbw != B.nbw) { p->err = "band plan: structure differs from the sharding plan"; return CTBA_E_STATE; }
+  } else {
+    band_partition_layout(B.nbc, B.nbw, p->band_partitions, 1, p->band_nested, &lay);
+    q_hi = lay.P;
+  }
+  BandLevel* L0 = new BandLevel();
+  L0->B = B; L0->delta = p->solver->delta.p;
+  pl.lv.push_back(L0);
+  int rc = level_build(p, pl, 0, lay, B.nbw, q_lo, q_hi); if (rc) return rc;
+  const int sepw = B.nbw;
+  for (size_t li = 1; li < pl.lv.size(); ++li) {   // level_build appends the next level while the current one still has partitions
+    PartLayout l2;
+    interface_layout(pl.lv[li]->B.nbc / sepw, sepw, &l2);
+    if (p->band_nested == 0) { l2.P = 1; l2.c0.assign(1, 0); l2.nI.assign(1, pl.lv[li]->B.nbc); }   // flat: the interface system as one partition
+    rc = level_build(p, pl, (int)li, l2, sepw, 0, l2.P); if (rc) return rc;
+  }
   return CTBA_OK;
 }
 
@@ -837,35 +901,43 @@ static int enqueue_single(ctba_problem* p, cudaStream_t st, const BandLayout& B,
   return enqueue_backsolve(p, st, B, PS1, dinv, delta, nl);
 }
 
-// phase 0: the whole solve (one handle holds every partition); phases 1 / 2: the two halves of a sharded solve — interiors + this rank's
-// terms of the interface system | (all-reduce of the interface system in between) | interface solve (replicated) + interior back-substitution
+// phase 0: the whole solve (one handle holds every partition); phases 1 / 2: the two halves of a sharded solve — level-0 interiors + this
+// rank's terms of the level-1 system | (all-reduce of that system in between) | remaining levels (replicated) + all back-substitutions
 static int band_enqueue(ctba_problem* p, cudaStream_t st, BandPlan& pl, int phase, int64_t* nl) {
   SolverData* sd = p->solver;
-  BandLayout& B = sd->Hw;
   int rc;
   if (phase <= 1) CTBA_CUDA(p, cudaMemsetAsync(sd->flag.p, 0, 4 * sizeof(int32_t), st));
-  if (pl.P == 1) {
-    rc = enqueue_single(p, st, B, pl.PS, pl.dinv.p, sd->delta.p, pl.cpart.p, nl); if (rc) return rc;
-  } else {
-    const BandLayout& B2 = pl.B2;
-    if (phase <= 1) {
-      int nblk = 0;
-      for (int q = 0; q < pl.PSloc.P; ++q) nblk += pl.PSloc.part[q].nrb * pl.PSloc.part[q].ncols;
-      k_fb_init<<<nblk, 256, 0, st>>>(B, pl.PSloc);
-      ++*nl;
-      rc = enqueue_steps(p, st, B, pl.PSloc, pl.max_steps, pl.dinv.p, nl); if (rc) return rc;
-      k_gram_partial<<<pl.gram_tasks, kStepThreads, 0, st>>>(pl.PSloc, pl.GP, pl.gram_scratch.p);
-      k_gram_reduce<<<pl.gram_tiles, 256, 0, st>>>(pl.PSloc, pl.GP, pl.gram_scratch.p, pl.gram.p, pl.d_gram_off);
-      k_iface_assemble<<<B2.nbc * (B2.nbw + 1) + B2.nbc + 1, 256, 0, st>>>(B, B2, pl.PS, pl.IA, sd->flag.p);
-      *nl += 3;
-    }
-    if (phase == 0 || phase == 2) {
-      if (phase == 2) { k_flag_from_sum<<<1, 32, 0, st>>>(pl.IA.extra, sd->flag.p); ++*nl; }
-      rc = enqueue_single(p, st, B2, pl.PS2, pl.dinv2.p, pl.delta2.p, pl.cpart2.p, nl); if (rc) return rc;
-      k_iface_scatter<<<cdiv(B2.n_pad + kBorder, 256), 256, 0, st>>>(B, B2, pl.PS, pl.delta2.p, sd->delta.p);
-      ++*nl;
-      rc = enqueue_backsolve(p, st, B, pl.PSloc, pl.dinv.p, sd->delta.p, nl); if (rc) return rc;
-    }
+  const int nlev = (int)pl.lv.size();
+  // ---- downward: eliminate the interiors of every level that has partitions, assemble the next level
+  for (int li = (phase == 2 ? 1 : 0); li < nlev - 1; ++li) {
+    BandLevel& L = *pl.lv[li];
+    const BandLayout& B2 = pl.lv[li + 1]->B;
+    if (phase == 2 && li == 1) { k_flag_from_sum<<<1, 32, 0, st>>>(pl.lv[0]->IA.extra, sd->flag.p); ++*nl; }
+    int nblk = 0;
+    for (int q = 0; q < L.PSloc.P; ++q) nblk += L.PSloc.part[q].nrb * L.PSloc.part[q].ncols;
+    k_fb_init<<<nblk, 256, 0, st>>>(L.B, L.PSloc);
+    ++*nl;
+    rc = enqueue_steps(p, st, L.B, L.PSloc, L.max_steps, L.dinv.p, nl); if (rc) return rc;
+    k_gram_partial<<<L.gram_tasks, kStepThreads, 0, st>>>(L.PSloc, L.GP, L.gram_scratch.p);
+    k_gram_reduce<<<L.gram_tiles, 256, 0, st>>>(L.PSloc, L.GP, L.gram_scratch.p, L.gram.p, L.d_gram_off);
+    k_iface_assemble<<<B2.nbc * (B2.nbw + 1) + B2.nbc + 1, 256, 0, st>>>(L.B, B2, L.PS, L.IA, sd->flag.p);
+    *nl += 3;
+    if (phase == 1) break;   // the level-1 system is summed over the ranks before anything else happens
+  }
+  if (phase == 1) { CTBA_CUDA(p, cudaGetLastError()); return CTBA_OK; }
+  if (phase == 2 && nlev == 2) { k_flag_from_sum<<<1, 32, 0, st>>>(pl.lv[0]->IA.extra, sd->flag.p); ++*nl; }
+  // ---- last level: one partition, factor + solve
+  {
+    BandLevel& L = *pl.lv[nlev - 1];
+    rc = enqueue_single(p, st, L.B, L.PS, L.dinv.p, L.delta, L.cpart.p, nl); if (rc) return rc;
+  }
+  // ---- upward: separator solutions -> level below, interior back-substitution
+  for (int li = nlev - 2; li >= 0; --li) {
+    BandLevel& L = *pl.lv[li];
+    const BandLayout& B2 = pl.lv[li + 1]->B;
+    k_iface_scatter<<<cdiv(B2.n_pad + kBorder, 256), 256, 0, st>>>(L.B, B2, L.PS, pl.lv[li + 1]->delta, L.delta);
+    ++*nl;
+    rc = enqueue_backsolve(p, st, L.B, L.PSloc, L.dinv.p, L.delta, nl); if (rc) return rc;
   }
   CTBA_CUDA(p, cudaGetLastError());
   return CTBA_OK;
@@ -900,7 +972,7 @@ int band_factor_solve(ctba_problem* p) {
     sd->band_stream2 = s2; sd->band_evA = ea; sd->band_evB = eb;
   }
   BandPlan& pl = *(BandPlan*)sd->band_plan;
-  if (pl.nbc != B.nbc || pl.nbw != B.nbw || pl.req != p->band_partitions || pl.band_ptr != B.band || pl.border_ptr != B.border) {
+  if (pl.nbc != B.nbc || pl.nbw != B.nbw || pl.req != p->band_partitions + 1000 * p->band_nested || pl.band_ptr != B.band || pl.border_ptr != B.border) {
     band_graph_release(sd);
     const int rc = plan_build(p, pl, B); if (rc) return rc;
   }
@@ -925,12 +997,12 @@ int band_factor_solve(ctba_problem* p) {
     CTBA_CUDA(p, cudaGraphLaunch((cudaGraphExec_t)*exec_slot, st));
     return CTBA_OK;
   };
-  const int key = p->band_pdl;
+  const int key = p->band_pdl + 16 * p->band_nested;
   if (sd->band_graph_key != key) band_graph_release(sd);
   sd->band_graph_key = key;
   if (!p->sharded) return run_phase(0, &sd->band_graph_exec, &sd->band_launches);
   int rc = run_phase(1, &sd->band_graph_exec1, &sd->band_launches1); if (rc) return rc;
-  if (p->comm->allreduce_sum(pl.iface.p, pl.iface_elems, st)) { p->err = p->comm->error(); return CTBA_E_NCCL; }
+  if (p->comm->allreduce_sum(pl.lv[0]->sys.p, pl.lv[0]->sys_elems, st)) { p->err = p->comm->error(); return CTBA_E_NCCL; }
   rc = run_phase(2, &sd->band_graph_exec2, &sd->band_launches2);
   sd->band_launches = sd->band_launches1 + sd->band_launches2;
   return rc;

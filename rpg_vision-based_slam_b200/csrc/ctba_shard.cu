@@ -185,7 +185,7 @@ int shard_plan(const ctba_problem* p, int world, int rank, ShardInfo* sh, Global
   gs->gravity_norm = p->gravity_norm; gs->hbn = hs.hbn; gs->tk = hs.tk; gs->tb = hs.tb;
   sh->world = world; sh->rank = rank;
   sh->nbc = hs.n_pad / kNB; sh->nbw = hs.nbw;
-  if (band_partition_layout(sh->nbc, sh->nbw, p->band_partitions, world, &sh->layout)) return -1;
+  if (band_partition_layout(sh->nbc, sh->nbw, p->band_partitions, world, p->band_nested, &sh->layout)) return -1;
   const int per = sh->layout.P / world;
   sh->q_lo = rank * per; sh->q_hi = (rank + 1) * per;
   sh->bc_lo = sh->layout.sep_start(sh->q_lo - 1);

@@ -37,7 +37,7 @@ struct PartLayout {
   int sep_start(int q) const { return q < 0 ? 0 : c0[q] + nI[q]; }   // first block column of S_q (q = P-1: end of the band)
 };
 // requested: 0 = automatic; world > 1: P is a multiple of world.  Returns 0, or -1 when the band is too short for `world` partitions.
-int band_partition_layout(int nbc, int nbw, int requested, int world, PartLayout* out);
+int band_partition_layout(int nbc, int nbw, int requested, int world, int nested, PartLayout* out);
 
 struct ShardInfo {
   int world = 1, rank = 0;

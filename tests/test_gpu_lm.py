@@ -63,6 +63,20 @@ def test_lm_gv_cubic(pkg, scene, oracle):
     _check(gpu, cpu, sg, so)
 
 
+def test_lm_nested_interface_levels(pkg, scene, oracle):
+    """The same LM parity with the band solver's nested interface reduction (odd-even over the separators, 3 levels here) and with a
+    forced flat 5-partition plan: the linear solve is exact either way."""
+    sc = scene.make_scene(order=4, duration_s=20.0, n_landmarks=420, track_len=6, imu_hz=0, gp_hz=10, seed=29, flags=(True, True, False, True, True))
+    for opts in ({"band_nested": 1}, {"band_nested": 0, "band_partitions": 5}, {"band_nested": 1, "band_partitions": 6}):
+        gpu = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=0)
+        cpu = oracle.OracleSpline(sc["order"], sc["dt_ns"], sc["start_t_ns"])
+        pkg.load_scene(gpu, sc); pkg.load_scene(cpu, sc)
+        for k, v in opts.items():
+            gpu.setOption(k, v)
+        sg, so = gpu.optimize(5), cpu.optimize(5, 8)
+        _check(gpu, cpu, sg, so)
+
+
 def test_lm_sparse_frame_rate(pkg, scene, oracle):
     """3 Hz camera on 0.1 s knots (the config-3 regime: fewer than two frames per knot -> thread-per-task Schur expansion)."""
     sc = scene.make_scene(order=6, duration_s=8.0, cam_hz=3.0, n_landmarks=120, track_len=6, imu_hz=0, gp_hz=10, seed=13,
