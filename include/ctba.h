@@ -128,6 +128,20 @@ typedef struct ctba_summary {
  * (ctba_get_* to read).  Non-convergence is reported in the summary, not as an error. */
 int ctba_solve(ctba_problem* p, int max_num_iterations, ctba_summary* summary);
 
+/* computeValidReprojections(frames): the grid-based choice of the reprojections that enter the problem        bspline_so3r3.h:406-521
+ * (per-frame feature grid of Frame::addPoint2D / setGrid, sensor/camera.h:155-184).  Input = every 2-D point that has a 3-D point,
+ * frame-major CSR pt_begin[F+1] in Frame::points2D order (each landmark at most once per frame, camera.h:372-380).  Output:
+ * valid[M] = Point2D::is_reproj_valid, n_valid[F] = Frame::n_valid_reprojections.  Evaluated at the handle's CURRENT knots, scale and
+ * camera extrinsics (the drivers call it once, before the first Solve).  Sequential over frames, on the host, like the reference.
+ * The caller then passes the valid points to ctba_add_frames. */
+int ctba_compute_valid_reprojections(ctba_problem* p, int F, const int64_t* t_ns, const int32_t* pt_begin, const double* uv /*2M*/,
+                                     const int32_t* lm_index /*M*/, int width, int height, int cell_size_px, uint8_t* valid /*M*/,
+                                     int32_t* n_valid /*F*/);
+/* evaluateReprojectionErrors / evaluateAccelErrors / evaluateGyroErrors / evaluateGlobalPosErrors               bspline_so3r3.h:1229-1579
+ * norm of every measurement's residual with unit weight (inv_std = 1), in the order the measurements were added;
+ * kind = CTBA_REPROJ | CTBA_ACCEL | CTBA_GYRO | CTBA_GP.  Returns the number of errors written (errors may be NULL to query it). */
+int ctba_evaluate_errors(ctba_problem* p, int kind, double* errors);
+
 /* relinearizeSplineImuTimeOffset + relinearizeSplineGlobSensTimeOffset   bspline_so3r3.h:1807-1811, 1853-1857 */
 int ctba_relinearize_time_offsets(ctba_problem* p);
 

@@ -7,6 +7,7 @@
 #include <cstdint>
 #include <cstring>
 #include "lm.h"
+#include "select.h"
 
 using namespace oracle;
 
@@ -233,6 +234,24 @@ int orc_sample(void* h, int64_t s, double u, double* out19) {
   if (p->N == 4) run(std::integral_constant<int, 4>()); else if (p->N == 5) run(std::integral_constant<int, 5>()); else run(std::integral_constant<int, 6>());
   double o[19] = {R.x, R.y, R.z, R.w, pos.x, pos.y, pos.z, w.x, w.y, w.z, wd.x, wd.y, wd.z, vel.x, vel.y, vel.z, acc.x, acc.y, acc.z};
   std::memcpy(out19, o, sizeof(o));
+  return 0;
+}
+
+// computeValidReprojections (select.h): frames as CSR over the 2-D points that have a 3-D point
+int orc_compute_valid_reprojections(void* h, int F, const int64_t* t_ns, const int32_t* pt_begin, const double* uv, const int32_t* lm_index,
+                                    int width, int height, int cell_size_px, uint8_t* valid, int32_t* n_valid) {
+  auto* p = (SplineProblem*)h;
+  std::vector<orc_select::Frame> frames(F);
+  for (int f = 0; f < F; ++f) {
+    frames[f].time_ns = t_ns[f];
+    frames[f].setGrid(width, height, cell_size_px);
+    for (int q = pt_begin[f]; q < pt_begin[f + 1]; ++q) frames[f].addPoint2D(uv[2 * q], uv[2 * q + 1], (uint64_t)lm_index[q]);
+  }
+  orc_select::computeValidReprojections(*p, frames);
+  for (int f = 0; f < F; ++f) {
+    n_valid[f] = frames[f].n_valid_reprojections;
+    for (int q = pt_begin[f]; q < pt_begin[f + 1]; ++q) valid[q] = frames[f].points2D[q - pt_begin[f]].is_reproj_valid ? 1 : 0;
+  }
   return 0;
 }
 

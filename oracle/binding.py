@@ -20,7 +20,7 @@ i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("api.cpp", "lm.h", "problem.h", "functors.h", "ref_math.h", "jet.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("api.cpp", "lm.h", "problem.h", "functors.h", "ref_math.h", "jet.h", "select.h")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "liboracle.so"], stdout=subprocess.DEVNULL)
     return so
@@ -179,6 +179,18 @@ class OracleSpline:
         n = int(s[5])
         return dict(termination_type=int(s[0]), initial_cost=s[1], final_cost=s[2], num_successful_steps=int(s[3]),
                     num_unsuccessful_steps=int(s[4]), iterations=log[:min(n, cap)].copy())
+
+    def computeValidReprojections(self, t_ns, pt_begin, uv, lm_index, width, height, cell_size_px):
+        t = np.ascontiguousarray(t_ns, dtype=np.int64)
+        pb = np.ascontiguousarray(pt_begin, dtype=np.int32)
+        u = _d(uv)
+        li = np.ascontiguousarray(lm_index, dtype=np.int32)
+        valid = np.zeros(max(li.size, 1), dtype=np.uint8)
+        nv = np.zeros(max(t.size, 1), dtype=np.int32)
+        lib().orc_compute_valid_reprojections(self.h, int(t.size), t.ctypes.data_as(C.c_void_p), pb.ctypes.data_as(C.c_void_p),
+                                              u.ctypes.data_as(C.c_void_p), li.ctypes.data_as(C.c_void_p), int(width), int(height),
+                                              int(cell_size_px), valid.ctypes.data_as(C.c_void_p), nv.ctypes.data_as(C.c_void_p))
+        return valid[:li.size].astype(bool), nv[:t.size]
 
     def timeEvaluate(self, num_threads, reps=1, frame_limit=0):
         obs = C.c_int64(0)

@@ -27,7 +27,7 @@ EXPORTS = [
     "ctba_set_camera", "ctba_set_globals", "ctba_set_corrections", "ctba_get_globals", "ctba_set_flags", "ctba_add_frames", "ctba_add_imu",
     "ctba_add_gp", "ctba_add_bias_cost", "ctba_add_gravity_norm", "ctba_counts", "ctba_evaluate", "ctba_cost", "ctba_solve",
     "ctba_relinearize_time_offsets", "ctba_bench_evaluate", "ctba_set_option", "ctba_invalidate_device", "ctba_transfer_bytes",
-    "ctba_bench_reproj", "ctba_comm_unique_id", "ctba_comm_init_nccl", "ctba_comm_init_local", "ctba_shard_plan",
+    "ctba_bench_reproj", "ctba_compute_valid_reprojections", "ctba_evaluate_errors", "ctba_comm_unique_id", "ctba_comm_init_nccl", "ctba_comm_init_local", "ctba_shard_plan",
 ]
 
 
@@ -243,6 +243,23 @@ class BSplineSO3R3:
         b = np.zeros(2, dtype=np.int64)
         self._chk(self.L.ctba_transfer_bytes(self.h, _p(b)))
         return int(b[0]), int(b[1])
+
+    def computeValidReprojections(self, t_ns, pt_begin, uv, lm_index, width, height, cell_size_px):
+        t = np.ascontiguousarray(t_ns, dtype=np.int64)
+        pb = np.ascontiguousarray(pt_begin, dtype=np.int32)
+        u = _d(uv)
+        li = np.ascontiguousarray(lm_index, dtype=np.int32)
+        valid = np.zeros(max(li.size, 1), dtype=np.uint8)
+        nv = np.zeros(max(t.size, 1), dtype=np.int32)
+        self._chk(self.L.ctba_compute_valid_reprojections(self.h, int(t.size), _p(t), _p(pb), _p(u), _p(li), int(width), int(height),
+                                                          int(cell_size_px), _p(valid), _p(nv)))
+        return valid[:li.size].astype(bool), nv[:t.size]
+
+    def evaluateErrors(self, kind):
+        n = self._chk(self.L.ctba_evaluate_errors(self.h, int(kind), None))
+        e = np.zeros(max(n, 1))
+        self._chk(self.L.ctba_evaluate_errors(self.h, int(kind), _p(e)))
+        return e[:n]
 
     def benchReproj(self, reps, flush_l2=True):
         ms = C.c_double(0.0)
