@@ -541,6 +541,220 @@ __global__ void __launch_bounds__(kFsThreads) k_frame_schur(int F, int T, const 
   }
 }
 
+// ---- compact gather (default): per observation only A_o = w^2 Jl^T Jl (6 doubles) is stored.  With X_o[:, pose] = [hat(d) | -I],
+// d = p_w - p_wb(f):   Y_a^T Z_b = [H_a^T ; -I] M [H_b | -I],  M = A_a Vi A_b  (3x3),  d_b = d_a + p_wb(f) - p_wb(f2)  (same landmark),
+// so a partner observation costs 48 B of gathered L2 traffic instead of the 144 B of its Z block, and the frame's own data is
+// 15 doubles per observation (A, d, Vi) in shared memory.
+__global__ void k_obs_a(int M, const int32_t* __restrict__ o_frame, const double* __restrict__ Jl, const double2* __restrict__ r,
+                        const double* __restrict__ f_w, double* __restrict__ Ao) {
+  const int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= M) return;
+  double A[6], b[3];
+  obs_Ab(Jl, r, f_w, M, o, o_frame[o], A, b);
+  double2* dst = reinterpret_cast<double2*>(Ao + 6 * (size_t)o);
+  dst[0] = make_double2(A[0], A[1]); dst[1] = make_double2(A[2], A[3]); dst[2] = make_double2(A[4], A[5]);
+}
+
+__device__ __forceinline__ void sym_mul_sym(const double S[6], const double B[6], double W[9]) {   // W = S * B, both symmetric (xx xy xz yy yz zz)
+  const double s[9] = {S[0], S[1], S[2], S[1], S[3], S[4], S[2], S[4], S[5]};
+  const double b[9] = {B[0], B[1], B[2], B[1], B[3], B[4], B[2], B[4], B[5]};
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) W[3 * i + j] = s[3 * i] * b[j] + s[3 * i + 1] * b[3 + j] + s[3 * i + 2] * b[6 + j];
+}
+
+// one (own observation, partner observation) product accumulated into the 6 x 6 pose block:
+//   acc += [H_a^T ; -I] (A_a Vi A_b) [H_b | -I]        with  H^T n = n x d,   (row of M) H = (row of M) x d
+__device__ __forceinline__ void schur_pair(const double Aa[6], const double Vi[6], const double Ab[6], double dax, double day, double daz,
+                                           double dbx, double dby, double dbz, double acc[36]) {
+  double W[9], Mm[9];
+  sym_mul_sym(Vi, Ab, W);
+  {
+    const double s[9] = {Aa[0], Aa[1], Aa[2], Aa[1], Aa[3], Aa[4], Aa[2], Aa[4], Aa[5]};
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) Mm[3 * r + c] = s[3 * r] * W[c] + s[3 * r + 1] * W[3 + c] + s[3 * r + 2] * W[6 + c];
+  }
+  double Nn[18];   // [M H_b | M]
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const double m0 = Mm[3 * r], m1 = Mm[3 * r + 1], m2 = Mm[3 * r + 2];
+    Nn[6 * r] = m1 * dbz - m2 * dby; Nn[6 * r + 1] = m2 * dbx - m0 * dbz; Nn[6 * r + 2] = m0 * dby - m1 * dbx;
+    Nn[6 * r + 3] = m0; Nn[6 * r + 4] = m1; Nn[6 * r + 5] = m2;
+  }
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    const double n0 = Nn[c], n1 = Nn[6 + c], n2 = Nn[12 + c];
+    if (c < 3) {
+      acc[c] += n1 * daz - n2 * day; acc[6 + c] += n2 * dax - n0 * daz; acc[12 + c] += n0 * day - n1 * dax;
+      acc[18 + c] -= n0; acc[24 + c] -= n1; acc[30 + c] -= n2;
+    } else {
+      acc[c] -= n1 * daz - n2 * day; acc[6 + c] -= n2 * dax - n0 * daz; acc[12 + c] -= n0 * day - n1 * dax;
+      acc[18 + c] += n0; acc[24 + c] += n1; acc[30 + c] += n2;
+    }
+  }
+}
+
+// CTA per frame.  Shared memory (structure of arrays over the frame's observations): A (6), d (3), Vi (6), {slot in the landmark's list, end
+// of the list (negative: the list has two observations in one frame)}, frame of the landmark's last observation.
+constexpr int kFcThreads = 128;
+constexpr int kFcRows = 17;
+template <int N>
+__global__ void __launch_bounds__(kFcThreads, 3) k_frame_schur_c(int F, int T, const FramePose<N>* __restrict__ fps, const double* __restrict__ lm,
+                                                                 const int32_t* __restrict__ obs_begin, const int32_t* __restrict__ o_lm,
+                                                                 const int32_t* __restrict__ o_pos, const int32_t* __restrict__ o_end,
+                                                                 const int32_t* __restrict__ lm_obs, const int32_t* __restrict__ lm_frame,
+                                                                 const double* __restrict__ Ao, const double* __restrict__ Vi_all,
+                                                                 const double* __restrict__ vig_all, const double* __restrict__ ViYg_all, bool any_g,
+                                                                 int n_pad, double* __restrict__ Sp, double* __restrict__ Sb, double* __restrict__ rp) {
+  __shared__ double red[kFcThreads / 32][48];
+  extern __shared__ double sO[];
+  const int f = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b0 = obs_begin[f], n = obs_begin[f + 1] - b0;
+  const double px = fps[f].p_wb[0], py = fps[f].p_wb[1], pz = fps[f].p_wb[2];
+  int2* sPE = reinterpret_cast<int2*>(sO + 15 * (size_t)n_pad);
+  int* sLast = reinterpret_cast<int*>(sO + 16 * (size_t)n_pad);
+  for (int i = threadIdx.x; i < n; i += kFcThreads) {
+    const int a = b0 + i, l = o_lm[a];
+    const double2* Ap = reinterpret_cast<const double2*>(Ao + 6 * (size_t)a);
+    const double2* Vp = reinterpret_cast<const double2*>(Vi_all + 6 * (size_t)l);
+    const double2 a0 = Ap[0], a1 = Ap[1], a2 = Ap[2], v0 = Vp[0], v1 = Vp[1], v2 = Vp[2];
+    const int e = o_end[a];
+    sO[i] = a0.x; sO[n_pad + i] = a0.y; sO[2 * n_pad + i] = a1.x; sO[3 * n_pad + i] = a1.y; sO[4 * n_pad + i] = a2.x; sO[5 * n_pad + i] = a2.y;
+    sO[6 * n_pad + i] = lm[3 * (size_t)l] - px; sO[7 * n_pad + i] = lm[3 * (size_t)l + 1] - py; sO[8 * n_pad + i] = lm[3 * (size_t)l + 2] - pz;
+    sO[9 * n_pad + i] = v0.x; sO[10 * n_pad + i] = v0.y; sO[11 * n_pad + i] = v1.x; sO[12 * n_pad + i] = v1.y; sO[13 * n_pad + i] = v2.x; sO[14 * n_pad + i] = v2.y;
+    sPE[i] = make_int2(o_pos[a], e);
+    sLast[i] = lm_frame[(e < 0 ? -e : e) - 1];
+  }
+  __syncthreads();
+  // ---- pose right-hand side and pose x globals block:  Y_a^T v = [ (A v) x d ; -(A v) ]
+  {
+    double acc[48];
+#pragma unroll
+    for (int e = 0; e < 48; ++e) acc[e] = 0.0;
+    for (int i = threadIdx.x; i < n; i += kFcThreads) {
+      const int l = o_lm[b0 + i];
+      const double A[6] = {sO[i], sO[n_pad + i], sO[2 * n_pad + i], sO[3 * n_pad + i], sO[4 * n_pad + i], sO[5 * n_pad + i]};
+      const double dx = sO[6 * n_pad + i], dy = sO[7 * n_pad + i], dz = sO[8 * n_pad + i];
+      auto apply = [&](const double v[3], double out[6]) {
+        double w[3];
+        symmul3(A, v, w);
+        out[0] = w[1] * dz - w[2] * dy; out[1] = w[2] * dx - w[0] * dz; out[2] = w[0] * dy - w[1] * dx;
+        out[3] = -w[0]; out[4] = -w[1]; out[5] = -w[2];
+      };
+      const double v[3] = {vig_all[3 * (size_t)l], vig_all[3 * (size_t)l + 1], vig_all[3 * (size_t)l + 2]};
+      double o6[6];
+      apply(v, o6);
+#pragma unroll
+      for (int m = 0; m < 6; ++m) acc[m] -= o6[m];
+      if (any_g) {
+        const double* W = ViYg_all + 21 * (size_t)l;
+#pragma unroll
+        for (int g = 0; g < 7; ++g) {
+          const double vg[3] = {W[g], W[7 + g], W[14 + g]};
+          apply(vg, o6);
+#pragma unroll
+          for (int m = 0; m < 6; ++m) acc[6 + 7 * m + g] -= o6[m];
+        }
+      }
+    }
+    const int nv = any_g ? 48 : 6;
+#pragma unroll
+    for (int e = 0; e < 48; ++e) {
+      if (e < nv) {
+        double v = acc[e];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) red[warp][e] = v;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < nv) {
+      double v = 0.0;
+#pragma unroll
+      for (int w = 0; w < kFcThreads / 32; ++w) v += red[w][threadIdx.x];
+      if (threadIdx.x < 6) rp[6 * (size_t)f + threadIdx.x] = v;
+      else Sb[42 * (size_t)f + (threadIdx.x - 6)] = v;
+    }
+    if (!any_g && threadIdx.x < 42) Sb[42 * (size_t)f + threadIdx.x] = 0.0;
+  }
+  // ---- pose-space blocks: warp per frame distance; a lane looks the partner of two observations up at once (independent loads) ----
+  for (int df = warp; df <= T; df += kFcThreads / 32) {
+    const int f2 = f + df;
+    double acc[36];
+#pragma unroll
+    for (int e = 0; e < 36; ++e) acc[e] = 0.0;
+    if (f2 < F) {
+      const double ex = px - fps[f2].p_wb[0], ey = py - fps[f2].p_wb[1], ez = pz - fps[f2].p_wb[2];   // d_b = d_a + e
+      auto own = [&](int i, double Aa[6], double Vi[6], double d[3]) {
+#pragma unroll
+        for (int c = 0; c < 6; ++c) { Aa[c] = sO[c * n_pad + i]; Vi[c] = sO[(9 + c) * n_pad + i]; }
+        d[0] = sO[6 * n_pad + i]; d[1] = sO[7 * n_pad + i]; d[2] = sO[8 * n_pad + i];
+      };
+      // general search (gaps in the track, or two observations of the landmark in one frame)
+      auto slow = [&](int i, int pos, int lend) {
+        double Aa[6], Vi[6], d[3];
+        own(i, Aa, Vi, d);
+        const int a = b0 + i;
+        for (; pos < lend; ++pos) {
+          const int fb = lm_frame[pos];
+          if (fb > f2) break;
+          if (fb < f2) continue;
+          const int b = lm_obs[pos];
+          const double2* Ap = reinterpret_cast<const double2*>(Ao + 6 * (size_t)b);
+          const double2 a0 = Ap[0], a1 = Ap[1], a2 = Ap[2];
+          const double Ab[6] = {a0.x, a0.y, a1.x, a1.y, a2.x, a2.y};
+          schur_pair(Aa, Vi, Ab, d[0], d[1], d[2], d[0] + ex, d[1] + ey, d[2] + ez, acc);
+          if (b != a && df == 0) schur_pair(Ab, Vi, Aa, d[0], d[1], d[2], d[0], d[1], d[2], acc);   // same frame, same landmark: the transposed product too
+        }
+      };
+      for (int i0 = lane; i0 < n; i0 += 64) {
+        int bsel[2] = {-1, -1};
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int i = i0 + 32 * u;
+          if (i >= n) continue;
+          const int2 pe = sPE[i];
+          if (pe.y < 0) { slow(i, pe.x, -pe.y); continue; }
+          if (f2 > sLast[i]) continue;
+          const int j = min(pe.x + df, pe.y - 1);
+          const int fj = lm_frame[j], bj = lm_obs[j];
+          if (fj == f2) bsel[u] = bj;              // strictly increasing frames: the only partner
+          else slow(i, pe.x + 1, j);               // a gap in the track: the partner, if any, sits before slot j
+        }
+        double Ab[2][6];
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+          if (bsel[u] >= 0) {
+            const double2* Ap = reinterpret_cast<const double2*>(Ao + 6 * (size_t)bsel[u]);
+            const double2 a0 = Ap[0], a1 = Ap[1], a2 = Ap[2];
+            Ab[u][0] = a0.x; Ab[u][1] = a0.y; Ab[u][2] = a1.x; Ab[u][3] = a1.y; Ab[u][4] = a2.x; Ab[u][5] = a2.y;
+          }
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+          if (bsel[u] >= 0) {
+            double Aa[6], Vi[6], d[3];
+            own(i0 + 32 * u, Aa, Vi, d);
+            schur_pair(Aa, Vi, Ab[u], d[0], d[1], d[2], d[0] + ex, d[1] + ey, d[2] + ez, acc);
+          }
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < 36; ++e) {
+      double v = acc[e];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      acc[e] = v;
+    }
+    double* dst = Sp + ((size_t)f * (T + 1) + df) * 36;
+#pragma unroll
+    for (int e = 0; e < 36; ++e) if (lane == e % 32 && (e < 32 || lane < 4)) dst[e] = -acc[e];
+  }
+}
+
 // D_f[k]^T S D_f'[k'] for one frame pair; i / i2 = local knot indices inside the two windows
 template <int N>
 __device__ __forceinline__ void chain_block_acc(const FramePose<N>& fa, int i, const FramePose<N>& fb, int i2, const double* S /*36, [m][n]*/, bool transpose,
@@ -1030,6 +1244,13 @@ void analyse_structure(const ctba_problem* p, const GlobalStructure* gs, HostStr
   }
   hs->opos.assign(std::max(M, 1), 0); hs->lmf.assign(std::max(M, 1), 0);
   for (int l = 0; l < L; ++l) for (int i = lob[l]; i < lob[l + 1]; ++i) { hs->opos[lobs[i]] = i; hs->lmf[i] = p->o_frame[lobs[i]]; }
+  // end of the landmark's list per observation; negative when the landmark is seen twice in one frame (k_frame_schur_c's general search)
+  hs->oend.assign(std::max(M, 1), 1);
+  for (int l = 0; l < L; ++l) {
+    bool strictly = true;
+    for (int i = lob[l] + 1; i < lob[l + 1]; ++i) strictly = strictly && hs->lmf[i] > hs->lmf[i - 1];
+    for (int i = lob[l]; i < lob[l + 1]; ++i) hs->oend[lobs[i]] = strictly ? lob[l + 1] : -lob[l + 1];
+  }
   hs->max_frame_obs = 1;
   for (int f = 0; f < F; ++f) hs->max_frame_obs = std::max(hs->max_frame_obs, (int)(p->f_obs_begin[f + 1] - p->f_obs_begin[f]));
   int T = 0, KD = N - 1;
@@ -1126,7 +1347,7 @@ int assemble_structure(ctba_problem* p) {
   CTBA_CUDA(p, sd->d_node_of_knot.upload(sd->node_of_knot, st)); CTBA_CUDA(p, sd->d_node_of_bias.upload(sd->node_of_bias, st));
   CTBA_CUDA(p, sd->d_lm_obs_begin.upload(hs.lob, st)); CTBA_CUDA(p, sd->d_lm_obs.upload(hs.lobs, st));
   CTBA_CUDA(p, sd->d_lm_frame.upload(hs.lmf, st));
-  CTBA_CUDA(p, sd->d_o_pos.upload(hs.opos, st)); CTBA_CUDA(p, sd->d_kf_begin.upload(hs.kfb, st)); CTBA_CUDA(p, sd->d_kf_list.upload(hs.kfl, st));
+  CTBA_CUDA(p, sd->d_o_pos.upload(hs.opos, st)); CTBA_CUDA(p, sd->d_o_end.upload(hs.oend, st)); CTBA_CUDA(p, sd->d_kf_begin.upload(hs.kfb, st)); CTBA_CUDA(p, sd->d_kf_list.upload(hs.kfl, st));
   CTBA_CUDA(p, sd->Vi.resize(6 * (size_t)std::max(L, 1))); CTBA_CUDA(p, sd->vig.resize(3 * (size_t)std::max(L, 1)));
   CTBA_CUDA(p, sd->ViYg.resize(21 * (size_t)std::max(L, 1)));
   CTBA_CUDA(p, sd->Yo.resize(18 * (size_t)std::max(M, 1))); CTBA_CUDA(p, sd->Zo.resize(18 * (size_t)std::max(M, 1)));
@@ -1237,12 +1458,22 @@ static int assemble_schur_T(ctba_problem* p, double radius) {
                                          (const double2*)p->ev.r_reproj.p, p->ev.f_w.p, M, sd->V0.p, sd->gl.p, sd->jscale_lm.p, radius, gm, any_g,
                                          sd->Vi.p, sd->vig.p, sd->ViYg.p, sd->lm_corner_partial.p);
     if (any_g) { k_corner_reduce<<<1, 64, 0, st>>>(nlb, sd->lm_corner_partial.p, Hw, rhs_acc + n_pad); p->launches++; }
-    k_obs_yz<N><<<cdiv(M, 128), 128, 0, st>>>(G, S.glb, fps, S.lm, M, p->d_o_frame.p, p->d_o_lm.p, p->ev.Jl.p, (const double2*)p->ev.r_reproj.p,
-                                              p->ev.f_w.p, sd->Vi.p, sd->Yo.p, sd->Zo.p);
-    const size_t fs_smem = (size_t)sd->max_frame_obs * 18 * sizeof(double);
-    if (fs_smem > 48 * 1024) CTBA_CUDA(p, cudaFuncSetAttribute(k_frame_schur, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs_smem));
-    k_frame_schur<<<F, kFsThreads, fs_smem, st>>>(F, T, p->d_f_obs_begin.p, p->d_o_lm.p, p->d_o_frame.p, sd->d_o_pos.p, sd->d_lm_obs_begin.p,
-                                            sd->d_lm_obs.p, sd->d_lm_frame.p, sd->Yo.p, sd->Zo.p, sd->vig.p, sd->ViYg.p, any_g, sd->Sp.p, sd->Sb.p, sd->rp.p);
+    if (p->schur_compact) {
+      k_obs_a<<<cdiv(M, 256), 256, 0, st>>>(M, p->d_o_frame.p, p->ev.Jl.p, (const double2*)p->ev.r_reproj.p, p->ev.f_w.p, sd->Yo.p);
+      const int n_pad = (sd->max_frame_obs + 1) & ~1;
+      const size_t fs_smem = (size_t)n_pad * kFcRows * sizeof(double);
+      if (fs_smem > 48 * 1024) CTBA_CUDA(p, cudaFuncSetAttribute(k_frame_schur_c<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs_smem));
+      k_frame_schur_c<N><<<F, kFcThreads, fs_smem, st>>>(F, T, fps, S.lm, p->d_f_obs_begin.p, p->d_o_lm.p, sd->d_o_pos.p, sd->d_o_end.p, sd->d_lm_obs.p,
+                                                         sd->d_lm_frame.p, sd->Yo.p, sd->Vi.p, sd->vig.p, sd->ViYg.p, any_g, n_pad, sd->Sp.p, sd->Sb.p,
+                                                         sd->rp.p);
+    } else {
+      k_obs_yz<N><<<cdiv(M, 128), 128, 0, st>>>(G, S.glb, fps, S.lm, M, p->d_o_frame.p, p->d_o_lm.p, p->ev.Jl.p, (const double2*)p->ev.r_reproj.p,
+                                                p->ev.f_w.p, sd->Vi.p, sd->Yo.p, sd->Zo.p);
+      const size_t fs_smem = (size_t)sd->max_frame_obs * 18 * sizeof(double);
+      if (fs_smem > 48 * 1024) CTBA_CUDA(p, cudaFuncSetAttribute(k_frame_schur, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs_smem));
+      k_frame_schur<<<F, kFsThreads, fs_smem, st>>>(F, T, p->d_f_obs_begin.p, p->d_o_lm.p, p->d_o_frame.p, sd->d_o_pos.p, sd->d_lm_obs_begin.p,
+                                              sd->d_lm_obs.p, sd->d_lm_frame.p, sd->Yo.p, sd->Zo.p, sd->vig.p, sd->ViYg.p, any_g, sd->Sp.p, sd->Sb.p, sd->rp.p);
+    }
     // frames per knot = F N / K; a task pairs the frames of two knots
     const double fpk = sd->frames_per_knot;
     if (fpk * fpk < 16.0)
