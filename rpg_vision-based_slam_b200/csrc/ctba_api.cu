@@ -27,14 +27,16 @@ int sync_to_device(ctba_problem* p) {
     p->meas_dirty = false;
   }
   if (p->state_dirty) {
-    // padded copies so that 12-element bias window reads never leave the allocation even with zero bias knots
-    std::vector<double> ba = p->bias_a, bg = p->bias_g;
-    if (ba.size() < 12) { ba.resize(12, 0.0); bg.resize(12, 0.0); }
+    // zero padding so that 12-element bias window reads never leave the allocation even with zero bias knots
+    auto up_padded = [&](DBuf<double>& d, const HVec<double>& h, size_t min_n) -> cudaError_t {
+      cudaError_t e = d.resize(std::max(h.size(), min_n));
+      if (e == cudaSuccess && h.size() < min_n) e = cudaMemsetAsync(d.p, 0, min_n * sizeof(double), st);
+      if (e == cudaSuccess && !h.empty()) e = cudaMemcpyAsync(d.p, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice, st);
+      return e;
+    };
     CTBA_CUDA(p, p->dstate.knot_q.upload(p->knot_q, st)); CTBA_CUDA(p, p->dstate.knot_p.upload(p->knot_p, st));
-    CTBA_CUDA(p, p->dstate.bias_a.upload(ba, st)); CTBA_CUDA(p, p->dstate.bias_g.upload(bg, st));
-    std::vector<double> lm = p->lm;
-    if (lm.empty()) lm.resize(3, 0.0);
-    CTBA_CUDA(p, p->dstate.lm.upload(lm, st));
+    CTBA_CUDA(p, up_padded(p->dstate.bias_a, p->bias_a, 12)); CTBA_CUDA(p, up_padded(p->dstate.bias_g, p->bias_g, 12));
+    CTBA_CUDA(p, up_padded(p->dstate.lm, p->lm, 3));
     std::vector<double> g(p->glb, p->glb + GLB_STATE_SIZE);
     CTBA_CUDA(p, p->dstate.glb.upload(g, st));
     CTBA_CUDA(p, cudaStreamSynchronize(st));  // the staging vectors above are temporaries
@@ -47,7 +49,7 @@ int sync_to_device(ctba_problem* p) {
 int download_state(ctba_problem* p) {
   if (!p->host_state_stale || p->device < 0) return CTBA_OK;
   cudaStream_t st = p->stream;
-  auto dl = [&](std::vector<double>& h, const DBuf<double>& d) -> cudaError_t {
+  auto dl = [&](HVec<double>& h, const DBuf<double>& d) -> cudaError_t {
     if (h.empty()) return cudaSuccess;
     return cudaMemcpyAsync(h.data(), d.p, h.size() * sizeof(double), cudaMemcpyDeviceToHost, st);
   };
@@ -64,6 +66,35 @@ int download_state(ctba_problem* p) {
 
 #define CHECK_P(p) do { if (!(p)) return CTBA_E_ARG; } while (0)
 static int fail(ctba_problem* p, int code, const char* msg) { p->err = msg; return code; }
+
+namespace ctba {
+namespace {
+constexpr size_t kPinMin = 64 * 1024, kHdr = 64;
+constexpr uint64_t kMagicPinned = 0x50494e4e45444d45ull, kMagicPlain = 0x504c41494e4d454dull;
+bool can_pin() {
+  static const bool ok = [] { int n = 0; return cudaGetDeviceCount(&n) == cudaSuccess && n > 0; }();
+  return ok;
+}
+}  // namespace
+void* host_alloc(size_t bytes) {
+  char* base = nullptr;
+  bool pinned = false;
+  if (bytes >= kPinMin && can_pin()) {
+    void* q = nullptr;
+    if (cudaHostAlloc(&q, bytes + kHdr, cudaHostAllocPortable) == cudaSuccess) { base = static_cast<char*>(q); pinned = true; }
+    else cudaGetLastError();
+  }
+  if (!base) base = static_cast<char*>(std::malloc(bytes + kHdr));
+  if (!base) throw std::bad_alloc();
+  *reinterpret_cast<uint64_t*>(base) = pinned ? kMagicPinned : kMagicPlain;
+  return base + kHdr;
+}
+void host_free(void* p) {
+  if (!p) return;
+  char* base = static_cast<char*>(p) - kHdr;
+  if (*reinterpret_cast<uint64_t*>(base) == kMagicPinned) cudaFreeHost(base); else std::free(base);
+}
+}  // namespace ctba
 
 extern "C" {
 

@@ -11,6 +11,23 @@
 
 namespace ctba {
 
+// Host arrays that are uploaded on every solve live in page-locked memory once they are large enough to matter (>= 64 KiB), so that the
+// host -> device copies run at the link rate instead of through the driver's staging buffers.  Without a CUDA device (planning-only
+// handles on a CPU box) the allocator is plain malloc.
+void* host_alloc(size_t bytes);
+void host_free(void* p);
+template <class T>
+struct HostAlloc {
+  using value_type = T;
+  HostAlloc() = default;
+  template <class U> HostAlloc(const HostAlloc<U>&) {}
+  T* allocate(size_t n) { return static_cast<T*>(host_alloc(n * sizeof(T))); }
+  void deallocate(T* p, size_t) { host_free(p); }
+  template <class U> bool operator==(const HostAlloc<U>&) const { return true; }
+  template <class U> bool operator!=(const HostAlloc<U>&) const { return false; }
+};
+template <class T> using HVec = std::vector<T, HostAlloc<T>>;
+
 template <class T>
 struct DBuf {
   T* p = nullptr;
@@ -24,7 +41,8 @@ struct DBuf {
     if (e == cudaSuccess) n = m;
     return e;
   }
-  cudaError_t upload(const std::vector<T>& h, cudaStream_t s) {
+  template <class A>
+  cudaError_t upload(const std::vector<T, A>& h, cudaStream_t s) {
     cudaError_t e = resize(h.size());
     if (e != cudaSuccess || h.empty()) return e;
     return cudaMemcpyAsync(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, s);
@@ -67,7 +85,7 @@ struct ctba_problem {
   std::string err;
 
   // ---- host state (bspline_so3r3.h:1936-1973) ----
-  std::vector<double> knot_q, knot_p, bias_a, bias_g, lm;
+  ctba::HVec<double> knot_q, knot_p, bias_a, bias_g, lm;
   double glb[ctba::GLB_STATE_SIZE] = {0, 0, 0, 0, 1, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   double scale = 0, t_offset_cam_imu_s = 0, cam_t_offset_cam_imu = 0, t_s_gp_s = 0, t_s_gp_init_s = 0;
   int64_t dt_ns_bias = 1000000000;
@@ -85,16 +103,16 @@ struct ctba_problem {
   bool band_graph = true;  // replay the factor+solve launch sequence as a CUDA graph
 
   // ---- host work items ----
-  std::vector<int32_t> f_s, f_obs_begin{0};
-  std::vector<double> f_u, f_inv_std;
-  std::vector<double> o_uv;
-  std::vector<int32_t> o_lm, o_frame;
-  std::vector<int32_t> i_s, i_sb;
-  std::vector<double> i_st_s, i_k, i_ub, i_inv_a, i_inv_g, i_acc, i_gyr;
-  std::vector<int32_t> g_s;
-  std::vector<double> g_st_s, g_k, g_inv_std, g_meas;
-  std::vector<int32_t> b_s0, b_s1, b_which;
-  std::vector<double> b_u0, b_u1, b_inv_std;
+  ctba::HVec<int32_t> f_s, f_obs_begin{0};
+  ctba::HVec<double> f_u, f_inv_std;
+  ctba::HVec<double> o_uv;
+  ctba::HVec<int32_t> o_lm, o_frame;
+  ctba::HVec<int32_t> i_s, i_sb;
+  ctba::HVec<double> i_st_s, i_k, i_ub, i_inv_a, i_inv_g, i_acc, i_gyr;
+  ctba::HVec<int32_t> g_s;
+  ctba::HVec<double> g_st_s, g_k, g_inv_std, g_meas;
+  ctba::HVec<int32_t> b_s0, b_s1, b_which;
+  ctba::HVec<double> b_u0, b_u1, b_inv_std;
   bool gravity_norm = false;
 
   // ---- device ----

@@ -217,8 +217,8 @@ int shard_plan(const ctba_problem* p, int world, int rank, ShardInfo* sh, Global
   return 0;
 }
 
-template <class T>
-static void keep(std::vector<T>& v, const std::vector<char>& mask, int width = 1) {
+template <class T, class A>
+static void keep(std::vector<T, A>& v, const std::vector<char>& mask, int width = 1) {
   size_t w = 0;
   for (size_t i = 0; i < mask.size(); ++i)
     if (mask[i]) { for (int c = 0; c < width; ++c) v[w * width + c] = v[i * width + c]; ++w; }
@@ -245,8 +245,13 @@ int shard_build(ctba_problem* p) {
     std::vector<char> ko(M, 0);
     for (int o = 0; o < M; ++o)
       if (sh.lm_owner[p->o_lm[o]] == rank) { ko[o] = 1; f_lo = std::min(f_lo, (int)p->o_frame[o]); f_hi = std::max(f_hi, (int)p->o_frame[o]); }
-    std::vector<int32_t> fs, fob{0}, olm, ofr;
-    std::vector<double> fu, fis, ouv;
+    HVec<int32_t> fs, fob{0}, olm, ofr;
+    HVec<double> fu, fis, ouv;
+    {
+      size_t nk = 0;
+      for (int o = 0; o < M; ++o) nk += ko[o];
+      olm.reserve(nk); ofr.reserve(nk); ouv.reserve(2 * nk);   // page-locked storage: allocate once
+    }
     for (int f = (f_hi >= 0 ? f_lo : 0); f <= f_hi && f < F; ++f) {
       fs.push_back(p->f_s[f]); fu.push_back(p->f_u[f]); fis.push_back(p->f_inv_std[f]);
       for (int o = p->f_obs_begin[f]; o < p->f_obs_begin[f + 1]; ++o) {
