@@ -8,6 +8,7 @@
 //                     runs on the FP64 tensor pipe (mma.sync m8n8k4 f64 -> DMMA)
 //   k_corner_partial / k_corner_solve   Schur complement of the band onto the <= 15 global parameters, 15x15 solve
 //   k_back_rhs + k_band_backsolve       backward substitution  L^T x = y - Lb^T z
+#include <cstdlib>
 #include <cooperative_groups.h>
 #include <algorithm>
 #include <cmath>
@@ -24,16 +25,22 @@ static inline int cdiv(size_t a, int b) { return (int)((a + b - 1) / b); }
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
+// Operand fragments for K = 32: lane (g, t) holds row g, columns 8t .. 8t+7 — 64 contiguous bytes, two 256-bit loads — and k-step ks
+// multiplies column 8t + ks.  A and B use the same column permutation, so the sum over k is complete; compared with the natural
+// layout (column 4 ks + t: eight 8-byte loads per lane, each touching 8 cache lines per warp) the L1 sees a quarter of the requests,
+// and L1 request throughput is what bounds these kernels (ncu: l1tex 87-99 % busy before the change).
+__device__ __forceinline__ void load_frag8(const double* __restrict__ p, double v[8]) {
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3]) : "l"(p));
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[4]), "=d"(v[5]), "=d"(v[6]), "=d"(v[7]) : "l"(p + 4));
+}
 // One 8x8 tile of  P = A * Bm^T  over K = 32:  A rows [8*tr, 8*tr+8) (row stride lda), Bm rows [8*tc, 8*tc+8) (row stride ldb).
-// Operands are read straight from global memory / L2: per k-step a warp touches 8 rows x one 32 B sector; every sector is used once.
+// Operands are read straight from global memory / L2.
 __device__ __forceinline__ void tile_abt(const double* __restrict__ A, int lda, const double* __restrict__ Bm, int ldb, int tr, int tc, int lane,
                                          double& c0, double& c1) {
   const int g = lane >> 2, t = lane & 3;
-  const double* pa = A + (size_t)(8 * tr + g) * lda + t;
-  const double* pb = Bm + (size_t)(8 * tc + g) * ldb + t;
   double a[8], b[8];
-#pragma unroll
-  for (int ks = 0; ks < 8; ++ks) { a[ks] = pa[4 * ks]; b[ks] = pb[4 * ks]; }
+  load_frag8(A + (size_t)(8 * tr + g) * lda + 8 * t, a);
+  load_frag8(Bm + (size_t)(8 * tc + g) * ldb + 8 * t, b);
 #pragma unroll
   for (int ks = 0; ks < 8; ++ks) dmma884(c0, c1, a[ks], b[ks]);
 }
@@ -55,20 +62,11 @@ __device__ __forceinline__ void panel_stage(double* sD, double* sX, const double
   sub_x = sub_x && live_x;
   double ad[8], ax[8], b0[8], b1[8];
   if (sub_d || sub_x) {
-    const double* pb0 = Ld + (size_t)(8 * tc0 + g) * kNB + t;
-#pragma unroll
-    for (int ks = 0; ks < 8; ++ks) { b0[ks] = pb0[4 * ks]; b1[ks] = pb0[8 * kNB + 4 * ks]; }
+    const double* pb0 = Ld + (size_t)(8 * tc0 + g) * kNB + 8 * t;
+    load_frag8(pb0, b0); load_frag8(pb0 + 8 * kNB, b1);
   }
-  if (sub_d) {
-    const double* pa = Ld + (size_t)r * kNB + t;
-#pragma unroll
-    for (int ks = 0; ks < 8; ++ks) ad[ks] = pa[4 * ks];
-  }
-  if (sub_x) {
-    const double* pa = Ax + (size_t)r * ldax + t;
-#pragma unroll
-    for (int ks = 0; ks < 8; ++ks) ax[ks] = pa[4 * ks];
-  }
+  if (sub_d) load_frag8(Ld + (size_t)r * kNB + 8 * t, ad);
+  if (sub_x) load_frag8(Ax + (size_t)r * ldax + 8 * t, ax);
   const int c = 8 * tc0 + 2 * t;
   double2 d0 = *reinterpret_cast<const double2*>(Cd + (size_t)r * kNB + c);
   double2 d1 = *reinterpret_cast<const double2*>(Cd + (size_t)r * kNB + c + 8);
@@ -331,14 +329,25 @@ __global__ void __launch_bounds__(kStepThreads, 4) k_band_update(BandLayout B, c
     T = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)(k - Q.c0) * kNB; ldt = Q.ld;
   }
   if (8 * tr >= nrows) return;   // warp-uniform
+  // every operand of the warp's two tiles (A rows, both L_k row groups, both target tiles) is requested before the first DMMA: one L2
+  // round trip per CTA instead of four dependent ones (the compiler cannot hoist the second tile's loads above the first tile's store)
+  const int tc0 = 2 * (warp & 1);
+  const double* pb = Lk + (size_t)(8 * tc0 + g) * kNB + 8 * tq;
+  double2* dst0 = reinterpret_cast<double2*>(T + (size_t)(8 * tr + g) * ldt + 8 * tc0 + 2 * tq);
+  double2* dst1 = dst0 + 4;
+  double a[8], b0[8], b1[8];
+  load_frag8(A + (size_t)(8 * tr + g) * lda + 8 * tq, a);
+  load_frag8(pb, b0); load_frag8(pb + 8 * kNB, b1);
+  double2 v0 = *dst0, v1 = *dst1;
+  // two accumulator chains per tile (even / odd k-steps): the DMMA latency chain is 4 deep instead of 8
+  double p0 = 0.0, p1 = 0.0, q0 = 0.0, q1 = 0.0, r0 = 0.0, r1 = 0.0, s0 = 0.0, s1 = 0.0;
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    const int tc = 2 * (warp & 1) + h;
-    double c0 = 0.0, c1 = 0.0;
-    tile_abt(A, lda, Lk, kNB, tr, tc, lane, c0, c1);
-    double2* dst = reinterpret_cast<double2*>(T + (size_t)(8 * tr + g) * ldt + 8 * tc + 2 * tq);
-    double2 v = *dst; v.x -= c0; v.y -= c1; *dst = v;
+  for (int ks = 0; ks < 8; ks += 2) {
+    dmma884(p0, p1, a[ks], b0[ks]); dmma884(r0, r1, a[ks], b1[ks]);
+    dmma884(q0, q1, a[ks + 1], b0[ks + 1]); dmma884(s0, s1, a[ks + 1], b1[ks + 1]);
   }
+  v0.x -= p0 + q0; v0.y -= p1 + q1; v1.x -= r0 + s0; v1.y -= r1 + s1;
+  *dst0 = v0; *dst1 = v1;
 }
 
 // ---- partition border initialisation -------------------------------------------------------------------------------------------
@@ -864,8 +873,9 @@ static int enqueue_steps(ctba_problem* p, cudaStream_t st, const BandLayout& B, 
     }
     if (gp == 0 && gu == 0) continue;
     if (t > 0) { CTBA_CUDA(p, cudaStreamWaitEvent(st, evB, 0)); CTBA_CUDA(p, cudaStreamWaitEvent(s2, evA, 0)); }
-    if (gp) { k_band_panel<<<gp, kStepThreads, 0, st>>>(B, PS, t, dinv, sd->flag.p); ++*nl; }
-    if (gu) { k_band_update<<<gu, kStepThreads, 0, s2>>>(B, PS, t); ++*nl; }
+    static const int skip = std::getenv("CTBA_BAND_SKIP") ? std::atoi(std::getenv("CTBA_BAND_SKIP")) : 0;   // timing experiments only (wrong factors)
+    if (gp && skip != 2) { k_band_panel<<<gp, kStepThreads, 0, st>>>(B, PS, t, dinv, sd->flag.p); ++*nl; }
+    if (gu && skip != 1) { k_band_update<<<gu, kStepThreads, 0, s2>>>(B, PS, t); ++*nl; }
     CTBA_CUDA(p, cudaEventRecord(evA, st));
     CTBA_CUDA(p, cudaEventRecord(evB, s2));
   }
