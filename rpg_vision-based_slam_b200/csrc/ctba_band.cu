@@ -538,60 +538,74 @@ __global__ void __launch_bounds__(256) k_corner_partial(BandLayout B, double* __
   for (int c = 0; c < 256; ++c) v += s[a][c] * s[b][c];
   partial[(size_t)blockIdx.x * 256 + threadIdx.x] = v;
 }
-// G' = G - Lb Lb^T ; c' = c - Lb y ; z = G'^-1 c'   (15x15, one thread) ; delta[n_pad + t] = z[t]
-__global__ void k_corner_solve(BandLayout B, int nblk, const double* __restrict__ partial, double* __restrict__ delta, int32_t* __restrict__ flag) {
-  __shared__ double Msum[256];
+// G' = G - Lb Lb^T ; c' = c - Lb y ; z = G'^-1 c'   (15x15 in shared memory, 256 threads: right-looking Cholesky, the right-hand side
+// rides along as a 16th row, then a serial 15-step back substitution) ; delta[n_pad + t] = z[t]
+__global__ void __launch_bounds__(256) k_corner_solve(BandLayout B, int nblk, const double* __restrict__ partial, double* __restrict__ delta,
+                                                      int32_t* __restrict__ flag) {
+  __shared__ double M[16][17];
+  const int a = threadIdx.x >> 4, b = threadIdx.x & 15;
   {
     double v = 0.0;
     for (int k = 0; k < nblk; ++k) v += partial[(size_t)k * 256 + threadIdx.x];
-    Msum[threadIdx.x] = v;
+    // rows 0..14: G' (lower part used), row 15 = kRhsRow: c'
+    M[a][b] = (b <= a || a == kRhsRow) ? B.corner[a * kBorder + b] - v : 0.0;
   }
   __syncthreads();
-  if (threadIdx.x != 0) return;
   const int n = GT_SIZE;
-  double Gm[GT_SIZE][GT_SIZE], c[GT_SIZE];
-  for (int a = 0; a < n; ++a) {
-    for (int b = 0; b <= a; ++b) { Gm[a][b] = B.corner[a * kBorder + b] - Msum[a * 16 + b]; Gm[b][a] = Gm[a][b]; }
-    c[a] = B.corner[kRhsRow * kBorder + a] - Msum[kRhsRow * 16 + a];
-  }
   for (int j = 0; j < n; ++j) {
-    double d = Gm[j][j];
-    for (int k = 0; k < j; ++k) d -= Gm[j][k] * Gm[j][k];
-    if (!(d > 0.0) || !isfinite(d)) { atomicExch(flag, 2); d = 1.0; }
-    d = sqrt(d);
-    Gm[j][j] = d;
-    for (int i = j + 1; i < n; ++i) {
-      double s = Gm[i][j];
-      for (int k = 0; k < j; ++k) s -= Gm[i][k] * Gm[j][k];
-      Gm[i][j] = s / d;
-    }
+    double d = M[j][j];
+    const bool bad = !(d > 0.0) || !isfinite(d);
+    if (bad) { if (threadIdx.x == 0) atomicExch(flag, 2); d = 1.0; }
+    const double rinv = 1.0 / sqrt(d);
+    const double la = (a > j) ? M[a][j] * rinv : 0.0, lb = (b > j && b < n) ? M[b][j] * rinv : 0.0;
+    __syncthreads();
+    if (a > j && b > j && b <= a && b < n) M[a][b] -= la * lb;      // trailing update (the right-hand-side row a = 15 included)
+    if (b == j) M[a][j] = (a > j) ? la : (a == j ? sqrt(d) : M[a][j]);
+    __syncthreads();
   }
-  for (int i = 0; i < n; ++i) { double s = c[i]; for (int k = 0; k < i; ++k) s -= Gm[i][k] * c[k]; c[i] = s / Gm[i][i]; }
-  for (int i = n - 1; i >= 0; --i) { double s = c[i]; for (int k = i + 1; k < n; ++k) s -= Gm[k][i] * c[k]; c[i] = s / Gm[i][i]; }
-  for (int i = 0; i < n; ++i) delta[B.n_pad + i] = c[i];
-  delta[B.n_pad + kRhsRow] = 0.0;
+  // row 15 now holds y^T = (L^-1 c')^T ; back substitution L^T z = y
+  if (threadIdx.x == 0) {
+    double z[GT_SIZE];
+#pragma unroll
+    for (int i = n - 1; i >= 0; --i) {
+      double sacc = M[kRhsRow][i];
+#pragma unroll
+      for (int k = i + 1; k < n; ++k) sacc -= M[k][i] * z[k];
+      z[i] = sacc / M[i][i];
+    }
+#pragma unroll
+    for (int i = 0; i < n; ++i) delta[B.n_pad + i] = z[i];
+    delta[B.n_pad + kRhsRow] = 0.0;
+  }
 }
 
 // t = y - W^T [x_S ; z] for the interior columns of every partition (y = forward-substituted right-hand side = last border row),
 // x_S = solution on the partition's left separator, z = globals.  Writes delta[interior columns].
 __global__ void __launch_bounds__(256) k_back_rhs(BandLayout B, const __grid_constant__ BandParts PS, double* __restrict__ delta) {
-  const int col = blockIdx.x * blockDim.x + threadIdx.x;
-  if (col >= B.n_pad) return;
-  const int jb = col >> 5;
+  __shared__ double red[8][kNB];
+  const int jb = blockIdx.x, lane = threadIdx.x & 31, grp = threadIdx.x >> 5;   // CTA per block column, warp = row group
   int pi = -1;
   for (int q = 0; q < PS.P; ++q) if (jb >= PS.part[q].c0 && jb < PS.part[q].c0 + PS.part[q].nI) pi = q;
   if (pi < 0) return;   // separator column: solved by the interface system
   const BandPart& Q = PS.part[pi];
-  const double* F = Q.fb + (size_t)(jb - Q.c0) * kNB + (col & 31);
+  const double* F = Q.fb + (size_t)(jb - Q.c0) * kNB + lane;
   const int rs = (Q.nrb - 1) * kNB;                 // separator rows
-  double t = F[(size_t)(rs + kRhsRow) * Q.ld];
   const double* z = delta + B.n_pad;
-#pragma unroll
-  for (int g = 0; g < GT_SIZE; ++g) t -= F[(size_t)(rs + g) * Q.ld] * z[g];
   const double* xs = delta + (size_t)(Q.c0 - (Q.nrb - 1)) * kNB;   // left separator; only dereferenced when rs > 0 (partition >= 1)
-  double t2 = 0.0;
-  for (int r = 0; r < rs; r += 2) { t -= F[(size_t)r * Q.ld] * xs[r]; t2 += F[(size_t)(r + 1) * Q.ld] * xs[r + 1]; }
-  delta[col] = t - t2;
+  double t0 = 0.0, t1 = 0.0;
+  for (int r = grp; r < rs; r += 16) {
+    t0 = fma(F[(size_t)r * Q.ld], xs[r], t0);
+    if (r + 8 < rs) t1 = fma(F[(size_t)(r + 8) * Q.ld], xs[r + 8], t1);
+  }
+  for (int g = grp; g < GT_SIZE; g += 8) t0 = fma(F[(size_t)(rs + g) * Q.ld], z[g], t0);
+  red[grp][lane] = t0 + t1;
+  __syncthreads();
+  if (grp == 0) {
+    double t = F[(size_t)(rs + kRhsRow) * Q.ld];
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t -= red[w][lane];
+    delta[(size_t)jb * kNB + lane] = t;
+  }
 }
 
 // x = L^-T t on the interior of every partition, block columns from last to first; partition p is handled by ONE thread-block cluster of
@@ -885,7 +899,7 @@ static int enqueue_steps(ctba_problem* p, cudaStream_t st, const BandLayout& B, 
 }
 
 static int enqueue_backsolve(ctba_problem* p, cudaStream_t st, const BandLayout& B, const BandParts& PS, const double* dinv, double* delta, int64_t* nl) {
-  k_back_rhs<<<cdiv(B.n_pad, 256), 256, 0, st>>>(B, PS, delta);
+  k_back_rhs<<<B.nbc, 256, 0, st>>>(B, PS, delta);
   const int nb1 = B.nbw + 1;
   const int nwarps = 1 + std::max(1, (B.nbw + kBackCtas - 1) / kBackCtas);   // <= 9 for nbw <= 63
   cudaLaunchConfig_t cfg = {};
