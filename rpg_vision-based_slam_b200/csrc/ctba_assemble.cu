@@ -270,6 +270,87 @@ __global__ void __launch_bounds__(128) k_rows_accumulate(int kind, int n, int wi
   }
 }
 
+// Same accumulation for the sample kinds that arrive at a high rate (1 accel, 2 gyro, 3 global position): consecutive samples inside one knot
+// interval (and one bias-knot interval) address the SAME unknowns, so a CTA sums J^T J and J^T r over such a run of samples in registers
+// and issues one atomic per entry and run instead of one per entry and sample (200 Hz IMU, 0.1 s knots: 20 x fewer atomics).
+constexpr int kSegThreads = 128, kSegBatch = 8, kSegMaxPairs = 11;   // 52 * 53 / 2 = 1378 pairs <= 128 * 11
+template <int N>
+__global__ void __launch_bounds__(kSegThreads) k_rows_accumulate_seg(int kind, int nseg, const int32_t* __restrict__ seg_begin, int width,
+                                                                     const double* __restrict__ J, const double* __restrict__ r,
+                                                                     const int32_t* __restrict__ i_s, const int32_t* __restrict__ i_sb,
+                                                                     const int32_t* __restrict__ node_of_knot,
+                                                                     const int32_t* __restrict__ node_of_bias, GMask gm, BandLayout H,
+                                                                     double* __restrict__ grad) {
+  __shared__ double sJ[kSegBatch][3 * 64];
+  __shared__ double sR[kSegBatch][3];
+  __shared__ int sI[64];
+  const int seg = blockIdx.x, tid = threadIdx.x;
+  if (seg >= nseg) return;
+  const int i0 = seg_begin[seg], i1 = seg_begin[seg + 1];
+  for (int c = tid; c < width; c += kSegThreads) {
+    int idx = -1;
+    if (kind == 1) {  // [3N rot | 3N pos | 12 acc-bias | 3 g | 1 t]
+      if (c < 3 * N) idx = 6 * node_of_knot[i_s[i0] + c / 3] + c % 3;
+      else if (c < 6 * N) idx = 6 * node_of_knot[i_s[i0] + (c - 3 * N) / 3] + 3 + c % 3;
+      else if (c < 6 * N + 12) idx = 6 * node_of_bias[i_sb[i0] + (c - 6 * N) / 3] + (c - 6 * N) % 3;
+      else if (c < 6 * N + 15) idx = gm.a[GT_G] ? H.n_pad + GT_G + (c - 6 * N - 12) : -1;
+      else idx = gm.a[GT_T_CAM_IMU] ? H.n_pad + GT_T_CAM_IMU : -1;
+    } else if (kind == 2) {  // [3N rot | 12 gyro-bias | 1 t]
+      if (c < 3 * N) idx = 6 * node_of_knot[i_s[i0] + c / 3] + c % 3;
+      else if (c < 3 * N + 12) idx = 6 * node_of_bias[i_sb[i0] + (c - 3 * N) / 3] + 3 + (c - 3 * N) % 3;
+      else idx = gm.a[GT_T_CAM_IMU] ? H.n_pad + GT_T_CAM_IMU : -1;
+    } else {  // [3N rot | 3N pos | p_bp 3 | t 1 | scale 1]
+      if (c < 3 * N) idx = 6 * node_of_knot[i_s[i0] + c / 3] + c % 3;
+      else if (c < 6 * N) idx = 6 * node_of_knot[i_s[i0] + (c - 3 * N) / 3] + 3 + c % 3;
+      else if (c < 6 * N + 3) idx = gm.a[GT_PBP] ? H.n_pad + GT_PBP + (c - 6 * N) : -1;
+      else if (c == 6 * N + 3) idx = gm.a[GT_T_GP] ? H.n_pad + GT_T_GP : -1;
+      else idx = gm.a[GT_SCALE] ? H.n_pad + GT_SCALE : -1;
+    }
+    sI[c] = idx;
+  }
+  const int npairs = width * (width + 1) / 2;
+  int pa[kSegMaxPairs], pc[kSegMaxPairs];
+  double acc[kSegMaxPairs];
+#pragma unroll
+  for (int q = 0; q < kSegMaxPairs; ++q) {
+    const int e = tid + q * kSegThreads;
+    int a = 0, c = 0;
+    if (e < npairs) {
+      a = (int)((sqrt(8.0 * e + 1.0) - 1.0) * 0.5);
+      while ((a + 1) * (a + 2) / 2 <= e) ++a;
+      while (a * (a + 1) / 2 > e) --a;
+      c = e - a * (a + 1) / 2;
+    }
+    pa[q] = a; pc[q] = c; acc[q] = 0.0;
+  }
+  double gacc = 0.0;
+  for (int b0 = i0; b0 < i1; b0 += kSegBatch) {
+    const int nb = min(kSegBatch, i1 - b0);
+    __syncthreads();
+    for (int e = tid; e < nb * 3 * width; e += kSegThreads) {
+      const int smp = e / (3 * width), rem = e - smp * 3 * width;
+      sJ[smp][(rem / width) * 64 + rem % width] = J[(size_t)(b0 + smp) * 3 * width + rem];
+    }
+    if (tid < nb * 3) sR[tid / 3][tid % 3] = r[(size_t)b0 * 3 + tid];
+    __syncthreads();
+    for (int smp = 0; smp < nb; ++smp) {
+      const double* j0 = sJ[smp];
+#pragma unroll
+      for (int q = 0; q < kSegMaxPairs; ++q)
+        acc[q] += j0[pa[q]] * j0[pc[q]] + j0[64 + pa[q]] * j0[64 + pc[q]] + j0[128 + pa[q]] * j0[128 + pc[q]];
+      if (tid < width) gacc += j0[tid] * sR[smp][0] + j0[64 + tid] * sR[smp][1] + j0[128 + tid] * sR[smp][2];
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < kSegMaxPairs; ++q) {
+    if (tid + q * kSegThreads >= npairs) continue;
+    const int ia = sI[pa[q]], ic = sI[pc[q]];
+    if (ia < 0 || ic < 0 || acc[q] == 0.0) continue;
+    add_sym(H, ia, ic, acc[q]);
+  }
+  if (tid < width && sI[tid] >= 0 && gacc != 0.0) atomicAdd(grad + sI[tid], gacc);
+}
+
 // ---- Schur complement of the landmarks, gather formulation (no atomics, bitwise reproducible) ------------------------------------
 //   k_lm_prepare   thread per landmark : damped V_l, Vi = V_l^-1, vig = Vi g_l; with free reprojection globals also Yg_l = sum_o A_o Xg_o,
 //                                        ViYg_l, and per-block partials of the global x global corner / right-hand side
@@ -1233,6 +1314,15 @@ void analyse_structure(const ctba_problem* p, const GlobalStructure* gs, HostStr
     span(nb[std::min(a, b)], nb[std::max(a, b) + 3]);
     for (int j = 0; j < 4; ++j) { tb[a + j] |= (p->b_which[i] ? 2 : 1); tb[b + j] |= (p->b_which[i] ? 2 : 1); }
   }
+  // runs of consecutive samples that address the same unknowns (k_rows_accumulate_seg)
+  hs->imu_seg.assign(1, 0);
+  for (size_t i = 1; i < p->i_s.size(); ++i)
+    if (p->i_s[i] != p->i_s[i - 1] || p->i_sb[i] != p->i_sb[i - 1]) hs->imu_seg.push_back((int32_t)i);
+  if (!p->i_s.empty()) hs->imu_seg.push_back((int32_t)p->i_s.size());
+  hs->gp_seg.assign(1, 0);
+  for (size_t i = 1; i < p->g_s.size(); ++i)
+    if (p->g_s[i] != p->g_s[i - 1]) hs->gp_seg.push_back((int32_t)i);
+  if (!p->g_s.empty()) hs->gp_seg.push_back((int32_t)p->g_s.size());
   // landmark -> observation CSR (observations of a landmark in frame order, as they are stored)
   std::vector<int32_t>&lob = hs->lob, &lobs = hs->lobs;
   lob.assign(L + 1, 0); lobs.assign(M, 0);
@@ -1347,7 +1437,9 @@ int assemble_structure(ctba_problem* p) {
   CTBA_CUDA(p, sd->d_node_of_knot.upload(sd->node_of_knot, st)); CTBA_CUDA(p, sd->d_node_of_bias.upload(sd->node_of_bias, st));
   CTBA_CUDA(p, sd->d_lm_obs_begin.upload(hs.lob, st)); CTBA_CUDA(p, sd->d_lm_obs.upload(hs.lobs, st));
   CTBA_CUDA(p, sd->d_lm_frame.upload(hs.lmf, st));
-  CTBA_CUDA(p, sd->d_o_pos.upload(hs.opos, st)); CTBA_CUDA(p, sd->d_o_end.upload(hs.oend, st)); CTBA_CUDA(p, sd->d_kf_begin.upload(hs.kfb, st)); CTBA_CUDA(p, sd->d_kf_list.upload(hs.kfl, st));
+  CTBA_CUDA(p, sd->d_o_pos.upload(hs.opos, st)); CTBA_CUDA(p, sd->d_o_end.upload(hs.oend, st));
+  CTBA_CUDA(p, sd->d_imu_seg.upload(hs.imu_seg, st)); CTBA_CUDA(p, sd->d_gp_seg.upload(hs.gp_seg, st));
+  sd->n_imu_seg = (int)hs.imu_seg.size() - 1; sd->n_gp_seg = (int)hs.gp_seg.size() - 1; CTBA_CUDA(p, sd->d_kf_begin.upload(hs.kfb, st)); CTBA_CUDA(p, sd->d_kf_list.upload(hs.kfl, st));
   CTBA_CUDA(p, sd->Vi.resize(6 * (size_t)std::max(L, 1))); CTBA_CUDA(p, sd->vig.resize(3 * (size_t)std::max(L, 1)));
   CTBA_CUDA(p, sd->ViYg.resize(21 * (size_t)std::max(L, 1)));
   CTBA_CUDA(p, sd->Yo.resize(18 * (size_t)std::max(M, 1))); CTBA_CUDA(p, sd->Zo.resize(18 * (size_t)std::max(M, 1)));
@@ -1389,15 +1481,15 @@ static int assemble_direct_T(ctba_problem* p) {
   }
   const int nI = (int)p->i_s.size(), nG = (int)p->g_s.size(), nB = (int)p->b_s0.size();
   if (nI > 0) {
-    k_rows_accumulate<N><<<cdiv(nI, 4), 128, 0, st>>>(1, nI, 6 * N + 16, p->ev.J_acc.p, p->ev.r_acc.p, p->d_i_s.p, p->d_i_sb.p, nullptr, nullptr,
-                                                      sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
-    k_rows_accumulate<N><<<cdiv(nI, 4), 128, 0, st>>>(2, nI, 3 * N + 13, p->ev.J_gyr.p, p->ev.r_gyr.p, p->d_i_s.p, p->d_i_sb.p, nullptr, nullptr,
-                                                      sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
+    k_rows_accumulate_seg<N><<<sd->n_imu_seg, kSegThreads, 0, st>>>(1, sd->n_imu_seg, sd->d_imu_seg.p, 6 * N + 16, p->ev.J_acc.p, p->ev.r_acc.p,
+                                                                    p->d_i_s.p, p->d_i_sb.p, sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
+    k_rows_accumulate_seg<N><<<sd->n_imu_seg, kSegThreads, 0, st>>>(2, sd->n_imu_seg, sd->d_imu_seg.p, 3 * N + 13, p->ev.J_gyr.p, p->ev.r_gyr.p,
+                                                                    p->d_i_s.p, p->d_i_sb.p, sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
     p->launches += 2;
   }
   if (nG > 0) {
-    k_rows_accumulate<N><<<cdiv(nG, 4), 128, 0, st>>>(3, nG, 6 * N + 5, p->ev.J_gp.p, p->ev.r_gp.p, p->d_g_s.p, nullptr, nullptr, nullptr,
-                                                      sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
+    k_rows_accumulate_seg<N><<<sd->n_gp_seg, kSegThreads, 0, st>>>(3, sd->n_gp_seg, sd->d_gp_seg.p, 6 * N + 5, p->ev.J_gp.p, p->ev.r_gp.p, p->d_g_s.p,
+                                                                   nullptr, sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
     p->launches++;
   }
   if (nB > 0) {
