@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(128) k_rows_accumulate(int kind, int n, int wi
 // Same accumulation for the sample kinds that arrive at a high rate (1 accel, 2 gyro, 3 global position): consecutive samples inside one knot
 // interval (and one bias-knot interval) address the SAME unknowns, so a CTA sums J^T J and J^T r over such a run of samples in registers
 // and issues one atomic per entry and run instead of one per entry and sample (200 Hz IMU, 0.1 s knots: 20 x fewer atomics).
-constexpr int kSegThreads = 128, kSegBatch = 8, kSegMaxPairs = 11;   // 52 * 53 / 2 = 1378 pairs <= 128 * 11
+constexpr int kSegThreads = 128, kSegBatch = 8;   // widest row: 6 N + 16 = 52 columns = 13 blocks of 4 -> 91 block pairs <= 128 threads
 template <int N>
 __global__ void __launch_bounds__(kSegThreads) k_rows_accumulate_seg(int kind, int nseg, const int32_t* __restrict__ seg_begin, int width,
                                                                      const double* __restrict__ J, const double* __restrict__ r,
@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(kSegThreads) k_rows_accumulate_seg(int kind, i
                                                                      const int32_t* __restrict__ node_of_knot,
                                                                      const int32_t* __restrict__ node_of_bias, GMask gm, BandLayout H,
                                                                      double* __restrict__ grad) {
-  __shared__ double sJ[kSegBatch][3 * 64];
+  __shared__ __align__(32) double sJ[kSegBatch][3 * 64];
   __shared__ double sR[kSegBatch][3];
   __shared__ int sI[64];
   const int seg = blockIdx.x, tid = threadIdx.x;
@@ -308,45 +308,56 @@ __global__ void __launch_bounds__(kSegThreads) k_rows_accumulate_seg(int kind, i
     }
     sI[c] = idx;
   }
-  const int npairs = width * (width + 1) / 2;
-  int pa[kSegMaxPairs], pc[kSegMaxPairs];
-  double acc[kSegMaxPairs];
-#pragma unroll
-  for (int q = 0; q < kSegMaxPairs; ++q) {
-    const int e = tid + q * kSegThreads;
-    int a = 0, c = 0;
-    if (e < npairs) {
-      a = (int)((sqrt(8.0 * e + 1.0) - 1.0) * 0.5);
-      while ((a + 1) * (a + 2) / 2 <= e) ++a;
-      while (a * (a + 1) / 2 > e) --a;
-      c = e - a * (a + 1) / 2;
-    }
-    pa[q] = a; pc[q] = c; acc[q] = 0.0;
+  // thread = one 4 x 4 block (ba >= bc) of J^T J: 8 shared-memory loads per 16 FMAs and residual row
+  const int wpad = (width + 3) & ~3, nblk = wpad >> 2, nblocks = nblk * (nblk + 1) / 2;
+  for (int c = width + tid; c < wpad; c += kSegThreads) sI[c] = -1;
+  int ba = 0, bc = 0;
+  if (tid < nblocks) {
+    ba = (int)((sqrtf(8.0f * tid + 1.0f) - 1.0f) * 0.5f);
+    while ((ba + 1) * (ba + 2) / 2 <= tid) ++ba;
+    while (ba * (ba + 1) / 2 > tid) --ba;
+    bc = tid - ba * (ba + 1) / 2;
   }
+  double acc[16];
+#pragma unroll
+  for (int q = 0; q < 16; ++q) acc[q] = 0.0;
   double gacc = 0.0;
   for (int b0 = i0; b0 < i1; b0 += kSegBatch) {
     const int nb = min(kSegBatch, i1 - b0);
     __syncthreads();
-    for (int e = tid; e < nb * 3 * width; e += kSegThreads) {
-      const int smp = e / (3 * width), rem = e - smp * 3 * width;
-      sJ[smp][(rem / width) * 64 + rem % width] = J[(size_t)(b0 + smp) * 3 * width + rem];
+    for (int e = tid; e < nb * 3 * wpad; e += kSegThreads) {
+      const int smp = e / (3 * wpad), rem = e - smp * 3 * wpad, rr = rem / wpad, c = rem - rr * wpad;
+      sJ[smp][rr * 64 + c] = c < width ? J[((size_t)(b0 + smp) * 3 + rr) * width + c] : 0.0;
     }
     if (tid < nb * 3) sR[tid / 3][tid % 3] = r[(size_t)b0 * 3 + tid];
     __syncthreads();
     for (int smp = 0; smp < nb; ++smp) {
       const double* j0 = sJ[smp];
+      if (tid < nblocks) {
 #pragma unroll
-      for (int q = 0; q < kSegMaxPairs; ++q)
-        acc[q] += j0[pa[q]] * j0[pc[q]] + j0[64 + pa[q]] * j0[64 + pc[q]] + j0[128 + pa[q]] * j0[128 + pc[q]];
+        for (int rr = 0; rr < 3; ++rr) {
+          const double4 va = *reinterpret_cast<const double4*>(j0 + rr * 64 + 4 * ba);
+          const double4 vc = *reinterpret_cast<const double4*>(j0 + rr * 64 + 4 * bc);
+          const double xa[4] = {va.x, va.y, va.z, va.w}, xc[4] = {vc.x, vc.y, vc.z, vc.w};
+#pragma unroll
+          for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+            for (int ic = 0; ic < 4; ++ic) acc[4 * ia + ic] = fma(xa[ia], xc[ic], acc[4 * ia + ic]);
+        }
+      }
       if (tid < width) gacc += j0[tid] * sR[smp][0] + j0[64 + tid] * sR[smp][1] + j0[128 + tid] * sR[smp][2];
     }
   }
+  if (tid < nblocks) {
 #pragma unroll
-  for (int q = 0; q < kSegMaxPairs; ++q) {
-    if (tid + q * kSegThreads >= npairs) continue;
-    const int ia = sI[pa[q]], ic = sI[pc[q]];
-    if (ia < 0 || ic < 0 || acc[q] == 0.0) continue;
-    add_sym(H, ia, ic, acc[q]);
+    for (int ia = 0; ia < 4; ++ia)
+#pragma unroll
+      for (int ic = 0; ic < 4; ++ic) {
+        if (ba == bc && ic > ia) continue;
+        const int ua = sI[4 * ba + ia], uc = sI[4 * bc + ic];
+        if (ua < 0 || uc < 0 || acc[4 * ia + ic] == 0.0) continue;
+        add_sym(H, ua, uc, acc[4 * ia + ic]);
+      }
   }
   if (tid < width && sI[tid] >= 0 && gacc != 0.0) atomicAdd(grad + sI[tid], gacc);
 }
