@@ -141,6 +141,16 @@ int ctba_compute_valid_reprojections(ctba_problem* p, int F, const int64_t* t_ns
  * norm of every measurement's residual with unit weight (inv_std = 1), in the order the measurements were added;
  * kind = CTBA_REPROJ | CTBA_ACCEL | CTBA_GYRO | CTBA_GP.  Returns the number of errors written (errors may be NULL to query it). */
 int ctba_evaluate_errors(ctba_problem* p, int kind, double* errors);
+/* getPose / getAccel / getGyro / getAccelBias / getGyroBias at n timestamps, evaluated on the device at the CURRENT state
+ *                                                                       bspline_so3r3.h:221-264, 122-174, 176-213, 266-295, 297-327
+ * — the loops of traceSpline / traceAccBiasSpline / traceGyroBiasSpline (include/util/save.h:99-153) and of the drivers' predicted-IMU
+ * dumps (src/optimize_continuous_time.cpp:88-130) as one call.  out: 7 doubles per pose in the trace file order tx ty tz qx qy qz qw,
+ * 3 doubles otherwise.  GYRO_WORLD applies R_wb^-1 to the body rate exactly like the reference (:203-207); the bias getters evaluate
+ * the bias knots with the order-N helper (:285-292).  A time before the spline start or a window beyond the last knot is where the
+ * reference asserts: CTBA_E_ARG, nothing written. */
+enum { CTBA_SAMPLE_POSE = 0, CTBA_SAMPLE_ACCEL_BODY = 1, CTBA_SAMPLE_ACCEL_WORLD = 2, CTBA_SAMPLE_GYRO_BODY = 3, CTBA_SAMPLE_GYRO_WORLD = 4,
+       CTBA_SAMPLE_ACCEL_BIAS = 5, CTBA_SAMPLE_GYRO_BIAS = 6 };
+int ctba_sample(ctba_problem* p, int what, int64_t n, const int64_t* t_ns, double* out);
 
 /* relinearizeSplineImuTimeOffset + relinearizeSplineGlobSensTimeOffset   bspline_so3r3.h:1807-1811, 1853-1857 */
 int ctba_relinearize_time_offsets(ctba_problem* p);

@@ -8,6 +8,7 @@
 #include <cstring>
 #include "lm.h"
 #include "select.h"
+#include "sample.h"
 
 using namespace oracle;
 
@@ -236,6 +237,9 @@ int orc_sample(void* h, int64_t s, double u, double* out19) {
   std::memcpy(out19, o, sizeof(o));
   return 0;
 }
+
+// getPose / getAccel / getGyro / get*Bias at timestamps (sample.h)
+int orc_sample_at(void* h, int what, int64_t n, const int64_t* t_ns, double* out) { return orc_getters::sample(*(SplineProblem*)h, what, n, t_ns, out); }
 
 // computeValidReprojections (select.h): frames as CSR over the 2-D points that have a 3-D point
 int orc_compute_valid_reprojections(void* h, int F, const int64_t* t_ns, const int32_t* pt_begin, const double* uv, const int32_t* lm_index,

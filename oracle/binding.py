@@ -197,6 +197,14 @@ class OracleSpline:
         t = self.L.orc_time_evaluate(self.h, int(num_threads), int(reps), int(frame_limit), C.byref(obs))
         return float(t), int(obs.value)
 
+    def sampleAt(self, what, t_ns):
+        t = np.ascontiguousarray(t_ns, dtype=np.int64)
+        out = np.zeros((t.size, 7 if what == 0 else 3))
+        rc = self.L.orc_sample_at(self.h, int(what), C.c_int64(t.size), t.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p))
+        if rc:
+            raise ValueError("sample time outside the spline")
+        return out
+
     def sample(self, s, u):
         o = np.zeros(19)
         self.L.orc_sample(self.h, C.c_int64(int(s)), C.c_double(u), o.ctypes.data_as(C.c_void_p))

@@ -20,6 +20,8 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libctba.so")
 _LIB = None
 
 CTBA_REPROJ, CTBA_ACCEL, CTBA_GYRO, CTBA_GP, CTBA_BIAS, CTBA_GRAVITY = range(6)
+(CTBA_SAMPLE_POSE, CTBA_SAMPLE_ACCEL_BODY, CTBA_SAMPLE_ACCEL_WORLD, CTBA_SAMPLE_GYRO_BODY, CTBA_SAMPLE_GYRO_WORLD, CTBA_SAMPLE_ACCEL_BIAS,
+ CTBA_SAMPLE_GYRO_BIAS) = range(7)
 
 EXPORTS = [
     "ctba_create", "ctba_destroy", "ctba_last_error", "ctba_set_stream", "ctba_set_knots", "ctba_num_knots", "ctba_get_knots",
@@ -27,7 +29,7 @@ EXPORTS = [
     "ctba_set_camera", "ctba_set_globals", "ctba_set_corrections", "ctba_get_globals", "ctba_set_flags", "ctba_add_frames", "ctba_add_imu",
     "ctba_add_gp", "ctba_add_bias_cost", "ctba_add_gravity_norm", "ctba_counts", "ctba_evaluate", "ctba_cost", "ctba_solve",
     "ctba_relinearize_time_offsets", "ctba_bench_evaluate", "ctba_set_option", "ctba_invalidate_device", "ctba_transfer_bytes",
-    "ctba_bench_reproj", "ctba_compute_valid_reprojections", "ctba_evaluate_errors", "ctba_comm_unique_id", "ctba_comm_init_nccl", "ctba_comm_init_local", "ctba_shard_plan",
+    "ctba_bench_reproj", "ctba_compute_valid_reprojections", "ctba_evaluate_errors", "ctba_sample", "ctba_comm_unique_id", "ctba_comm_init_nccl", "ctba_comm_init_local", "ctba_shard_plan",
 ]
 
 
@@ -81,6 +83,7 @@ class BSplineSO3R3:
             self.h = None
             raise CtbaError(f"ctba_create failed with code {rc} (no CUDA device or bad arguments); there is no CPU fallback")
         self._nlm = 0
+        self.dt_ns, self.start_t_ns, self.dt_ns_bias = int(dt_ns), int(start_t_ns), None
 
     def close(self):
         if getattr(self, "h", None):
@@ -260,6 +263,22 @@ class BSplineSO3R3:
         e = np.zeros(max(n, 1))
         self._chk(self.L.ctba_evaluate_errors(self.h, int(kind), _p(e)))
         return e[:n]
+
+    def sampleAt(self, what, t_ns):
+        """getPose / getAccel / getGyro / get*Bias at many timestamps (bspline_so3r3.h:122-327; traceSpline, save.h:99-153)"""
+        t = np.ascontiguousarray(t_ns, dtype=np.int64)
+        out = np.zeros((t.size, 7 if what == CTBA_SAMPLE_POSE else 3))
+        self._chk(self.L.ctba_sample(self.h, int(what), C.c_int64(t.size), _p(t), _p(out)))
+        return out
+
+    def getEndTns(self):
+        """bspline_so3r3.h:1862-1867 (1 ms before the end of the last window)"""
+        return (self.numKnots() - self.N + 1) * self.dt_ns + self.start_t_ns - 1000000
+
+    def traceSpline(self, dt_ns, t_end_ns=None):
+        """traceSpline (save.h:99-121): rows 'timestamp_s tx ty tz qx qy qz qw' from getStartTns() to getEndTns() (exclusive)"""
+        t = np.arange(self.start_t_ns, int(self.getEndTns() if t_end_ns is None else t_end_ns), int(dt_ns), dtype=np.int64)
+        return np.concatenate([(t * 1e-9)[:, None], self.sampleAt(CTBA_SAMPLE_POSE, t)], axis=1)
 
     def benchReproj(self, reps, flush_l2=True):
         ms = C.c_double(0.0)

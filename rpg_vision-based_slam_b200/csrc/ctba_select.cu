@@ -2,6 +2,8 @@
 //   ctba_compute_valid_reprojections   BSplineSO3R3::computeValidReprojections   include/spline/bspline_so3r3.h:406-521
 //                                      (+ the per-frame feature grid of Frame::addPoint2D / setGrid, include/sensor/camera.h:155-184)
 //   ctba_evaluate_errors               evaluate{Accel,Gyro,GlobalPos,Reprojection}Errors   bspline_so3r3.h:1229-1579
+//   ctba_sample                        getPose / getAccel / getGyro / get*Bias at many timestamps   bspline_so3r3.h:122-327
+//                                      (the loops of traceSpline & co., include/util/save.h:99-153), thread per timestamp
 // The selection is sequential from frame to frame (the grid of frame k-1 seeds frame k), so it stays on the host like in the
 // reference; it is written over flat arrays (CSR frames, one stamp array for the landmark -> point lookup instead of std::find).
 #include <cmath>
@@ -33,6 +35,57 @@ __global__ void k_error_norms(int n, int nres, const double* __restrict__ r, con
   for (int c = 0; c < nres; ++c) { const double v = r[(size_t)i * nres + c]; s += v * v; }
   const double w = inv_std[idx ? idx[i] : i];
   out[i] = sqrt(s) / w;   // the reference evaluates the functor with inv_std = 1
+}
+
+// thread per timestamp; (window, u) from the int64 nanosecond arithmetic of the reference getters
+template <int N>
+__global__ void k_sample(const __grid_constant__ Globals G, StatePtrs S, int what, int64_t n, const int64_t* __restrict__ t_ns, int64_t start_t_ns,
+                         int64_t dt_ns, int64_t dt_ns_bias, double* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int64_t st_ns = t_ns[i] - start_t_ns;
+  if (what == CTBA_SAMPLE_ACCEL_BIAS || what == CTBA_SAMPLE_GYRO_BIAS) {
+    const int64_t s = st_ns / dt_ns_bias;
+    const double u = double(st_ns % dt_ns_bias) / double(dt_ns_bias);
+    const double* b = (what == CTBA_SAMPLE_ACCEL_BIAS ? S.bias_a : S.bias_g) + 3 * s;
+    double c[N];
+    spline_coeffs<N>(G.tb.blend, G.tb.base, 0, 1.0, u, c);     // order N on the bias knots, like the reference getter
+    double v[3] = {0, 0, 0};
+    for (int j = 0; j < N; ++j) for (int k = 0; k < 3; ++k) v[k] += c[j] * b[3 * j + k];
+    for (int k = 0; k < 3; ++k) out[3 * i + k] = v[k];
+    return;
+  }
+  const int64_t s = st_ns / dt_ns;
+  const double u = double(st_ns % dt_ns) / double(dt_ns);
+  const double* kq = S.knot_q + 4 * s;
+  const double* kp = S.knot_p + 3 * s;
+  auto r3 = [&](int D, double sc) {
+    double c[N];
+    spline_coeffs<N>(G.tb.blend, G.tb.base, D, sc, u, c);
+    v3 a{0, 0, 0};
+    for (int j = 0; j < N; ++j) { a.x += c[j] * kp[3 * j]; a.y += c[j] * kp[3 * j + 1]; a.z += c[j] * kp[3 * j + 2]; }
+    return a;
+  };
+  if (what == CTBA_SAMPLE_POSE) {
+    So3SplineResult<N> sr;
+    so3_spline_eval<N, false, false, false>(G.tb, kq, u, G.inv_dt, &sr);
+    const v3 t = r3(0, 1.0);
+    double* o = out + 7 * i;
+    o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = sr.q.x; o[4] = sr.q.y; o[5] = sr.q.z; o[6] = sr.q.w;
+  } else if (what == CTBA_SAMPLE_ACCEL_BODY || what == CTBA_SAMPLE_ACCEL_WORLD) {
+    So3SplineResult<N> sr;
+    so3_spline_eval<N, false, false, false>(G.tb, kq, u, G.inv_dt, &sr);
+    v3 a = r3(2, G.inv_dt * G.inv_dt);
+    a.x += S.glb[GLB_G]; a.y += S.glb[GLB_G + 1]; a.z += S.glb[GLB_G + 2];
+    if (what == CTBA_SAMPLE_ACCEL_BODY) a = quat_act(quat_inv(sr.q), a);
+    out[3 * i] = a.x; out[3 * i + 1] = a.y; out[3 * i + 2] = a.z;
+  } else {
+    So3SplineResult<N> sr;
+    so3_spline_eval<N, true, false, false>(G.tb, kq, u, G.inv_dt, &sr);
+    v3 w = sr.w;
+    if (what == CTBA_SAMPLE_GYRO_WORLD) w = quat_act(quat_inv(sr.q), w);   // sic (bspline_so3r3.h:203-207)
+    out[3 * i] = w.x; out[3 * i + 1] = w.y; out[3 * i + 2] = w.z;
+  }
 }
 
 }  // namespace
@@ -146,6 +199,42 @@ int ctba_evaluate_errors(ctba_problem* p, int kind, double* errors) {
   out.release();
   if (e != cudaSuccess) { p->err = cudaGetErrorString(e); return CTBA_E_CUDA; }
   return n;
+}
+
+int ctba_sample(ctba_problem* p, int what, int64_t n, const int64_t* t_ns, double* out) {
+  if (!p) return CTBA_E_ARG;
+  if (what < CTBA_SAMPLE_POSE || what > CTBA_SAMPLE_GYRO_BIAS || n < 0 || (n > 0 && (!t_ns || !out))) { p->err = "sample: bad arguments"; return CTBA_E_ARG; }
+  if (p->device < 0) { p->err = "planning-only handle (device -1): no compute entry points"; return CTBA_E_CUDA; }
+  if (n == 0) return CTBA_OK;
+  const bool bias = what == CTBA_SAMPLE_ACCEL_BIAS || what == CTBA_SAMPLE_GYRO_BIAS;
+  const int64_t dt = bias ? p->dt_ns_bias : p->dt_ns;
+  const size_t nk = bias ? p->numBiasKnots() : p->numKnots();
+  for (int64_t i = 0; i < n; ++i) {                        // the reference getters assert on these (bspline_so3r3.h:126-136, 225-235, 271-280)
+    const int64_t st_ns = t_ns[i] - p->start_t_ns;
+    if (st_ns < 0 || (size_t)(st_ns / dt + p->N) > nk) { p->err = "sample: time outside the spline"; return CTBA_E_ARG; }
+  }
+  CTBA_CUDA(p, cudaSetDevice(p->device));
+  int rc = sync_to_device(p); if (rc) return rc;
+  cudaStream_t st = p->stream;
+  const int w = what == CTBA_SAMPLE_POSE ? 7 : 3;
+  DBuf<double> d_out;
+  DBuf<int64_t> d_t;
+  CTBA_CUDA(p, d_out.resize((size_t)n * w));
+  CTBA_CUDA(p, d_t.resize((size_t)n));
+  cudaError_t e = cudaMemcpyAsync(d_t.p, t_ns, (size_t)n * sizeof(int64_t), cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) {
+    const Globals G = make_globals(p);
+    const int grid = (int)((n + 127) / 128);
+    if (p->N == 4) k_sample<4><<<grid, 128, 0, st>>>(G, p->dstate.ptrs(), what, n, d_t.p, p->start_t_ns, p->dt_ns, p->dt_ns_bias, d_out.p);
+    else k_sample<6><<<grid, 128, 0, st>>>(G, p->dstate.ptrs(), what, n, d_t.p, p->start_t_ns, p->dt_ns, p->dt_ns_bias, d_out.p);
+    p->launches++;
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out.p, (size_t)n * w * sizeof(double), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  d_out.release(); d_t.release();
+  if (e != cudaSuccess) { p->err = cudaGetErrorString(e); return CTBA_E_CUDA; }
+  return CTBA_OK;
 }
 
 }  // extern "C"
