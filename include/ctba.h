@@ -31,7 +31,7 @@ enum {
 };
 
 /* residual kinds (ctba_evaluate) */
-enum { CTBA_REPROJ = 0, CTBA_ACCEL = 1, CTBA_GYRO = 2, CTBA_GP = 3, CTBA_BIAS = 4, CTBA_GRAVITY = 5 };
+enum { CTBA_REPROJ = 0, CTBA_ACCEL = 1, CTBA_GYRO = 2, CTBA_GP = 3, CTBA_BIAS = 4, CTBA_GRAVITY = 5, CTBA_PRIOR = 6 };
 
 /* BSplineSO3R3<N>::BSplineSO3R3(time_interval_ns, start_time_ns)      bspline_so3r3.h:75-117
  * order N in {4,6}; `device` = CUDA ordinal (-1: planning-only handle — host problem assembly and ctba_shard_plan work,
@@ -85,6 +85,14 @@ int ctba_add_imu(ctba_problem* p, int n, const int64_t* t_ns, const double* acc 
                  double acc_noise_density, double gyro_noise_density);
 /* addGlobalPosMeasurement for n samples                                  bspline_so3r3.h:880-958 */
 int ctba_add_gp(ctba_problem* p, int n, const int64_t* t_ns, const double* pos /*3n*/, double noise);
+/* addPositionMeasurement / addOrientationMeasurement for n samples (the spline-fitting tools: src/fit_spline_to_colmap.cpp:182-192,
+ * fit_spline_to_gp_measurements)                                         bspline_so3r3.h:1048-1085, 1087-1123
+ * residuals: PositionCostFunctor (optimization/continuous_time/position_cost_functor.h:39-53)  r = (p(u) - meas) / noise,
+ *            OrientationCostFunctor (orientation_cost_functor.h:39-57)   r = 2 vec(R(u) meas^-1) / noise;  quaternions as x y z w.
+ * Returns the number of samples accepted (same skip rules as the reference).  Problems with pose priors run on one GPU. */
+int ctba_add_position_measurements(ctba_problem* p, int n, const int64_t* t_ns, const double* pos /*3n*/, double noise);
+int ctba_add_orientation_measurements(ctba_problem* p, int n, const int64_t* t_ns, const double* quat_xyzw /*4n*/, double noise);
+int ctba_num_priors(const ctba_problem* p);
 /* addImuBiasCost(bias_err_freq_hz, bias_err_dt_s); random walks from ImuCalibration   bspline_so3r3.h:706-792 */
 int ctba_add_bias_cost(ctba_problem* p, double freq_hz, double dt_s, double acc_random_walk, double gyro_random_walk);
 /* addGravityNormError()                                                  bspline_so3r3.h:1213-1227 */
@@ -101,11 +109,14 @@ int ctba_counts(ctba_problem* p, int64_t* counts);
  *   CTBA_GP      per sample      3 x (6N+5) : [3N rot | 3N pos | p_bp 3 | t_s_gp_corr | scale_corr]
  *   CTBA_BIAS    per block       3 x 24     : [4 knots @s0 | 4 knots @s1]
  *   CTBA_GRAVITY                 1 x 3
+ *   CTBA_PRIOR                   3 x 3N   (position prior: the position knots; orientation prior: the right tangents of the rotation knots)
  * residuals / jacobians may be NULL.  Returns the number of residuals written (>=0) or an error.
  * Also serves evaluate*Errors (bspline_so3r3.h:1229-1579). */
 int ctba_evaluate(ctba_problem* p, int kind, double* residuals, double* jacobians);
 /* cost[7]: 1/2 sum rho(|r|^2) per kind (Cauchy on reprojection frames), cost[6] = total */
 int ctba_cost(ctba_problem* p, double* cost7);
+/* the same with cost[7] = the pose priors (position + orientation measurements; included in the total cost[6]) */
+int ctba_cost_terms(ctba_problem* p, double* cost8);
 
 typedef struct ctba_iteration {
   double cost, cost_change, gradient_max_norm, step_norm, tr_ratio, tr_radius;
@@ -139,7 +150,7 @@ int ctba_compute_valid_reprojections(ctba_problem* p, int F, const int64_t* t_ns
                                      int32_t* n_valid /*F*/);
 /* evaluateReprojectionErrors / evaluateAccelErrors / evaluateGyroErrors / evaluateGlobalPosErrors               bspline_so3r3.h:1229-1579
  * norm of every measurement's residual with unit weight (inv_std = 1), in the order the measurements were added;
- * kind = CTBA_REPROJ | CTBA_ACCEL | CTBA_GYRO | CTBA_GP.  Returns the number of errors written (errors may be NULL to query it). */
+ * kind = CTBA_REPROJ | CTBA_ACCEL | CTBA_GYRO | CTBA_GP | CTBA_PRIOR (evaluatePositionErrors / evaluateOrientationErrors, :1581-1680).  Returns the number of errors written (errors may be NULL to query it). */
 int ctba_evaluate_errors(ctba_problem* p, int kind, double* errors);
 /* getPose / getAccel / getGyro / getAccelBias / getGyroBias at n timestamps, evaluated on the device at the CURRENT state
  *                                                                       bspline_so3r3.h:221-264, 122-174, 176-213, 266-295, 297-327

@@ -87,6 +87,8 @@ int orc_add_imu(void* h, int n, const int64_t* t_ns, const double* acc, const do
   return ((SplineProblem*)h)->addImu(n, t_ns, acc, gyr, acc_nd, gyr_nd);
 }
 int orc_add_gp(void* h, int n, const int64_t* t_ns, const double* pos, double noise) { return ((SplineProblem*)h)->addGp(n, t_ns, pos, noise); }
+int orc_add_priors(void* h, int which, int n, const int64_t* t_ns, const double* meas, double noise) { return ((SplineProblem*)h)->addPriors(which, n, t_ns, meas, noise); }
+int orc_num_priors(void* h) { return (int)((SplineProblem*)h)->priors.size(); }
 int orc_add_bias_cost(void* h, double freq_hz, double dt_s, double acc_rw, double gyr_rw) { return ((SplineProblem*)h)->addBiasCost(freq_hz, dt_s, acc_rw, gyr_rw); }
 int orc_add_gravity_norm(void* h) { auto* p = (SplineProblem*)h; p->gravity_norm = true; p->built = false; return 0; }
 int orc_relinearize(void* h) { ((SplineProblem*)h)->relinearize(); return 0; }
@@ -153,12 +155,12 @@ int orc_evaluate(void* h, int kind, double* r_out, double* j_out, double* aux) {
 // cost[k] = 1/2 sum over blocks of kind k of rho(||r||^2); cost[6] = total
 int orc_cost(void* h, double* cost) {
   auto* p = (SplineProblem*)h; p->build();
-  for (int k = 0; k < 7; ++k) cost[k] = 0;
+  for (int k = 0; k < 8; ++k) cost[k] = 0;     // cost[7] = pose priors (block kind 6)
   for (const auto& b : p->mp.blocks) {
     EvalBlockOut o; p->mp.evalBlock(b, false, &o);
     double c = 0.5 * o.sq_norm;
     if (b.cauchy_a > 0) { double rho[3]; cauchy(b.cauchy_a, o.sq_norm, rho); c = 0.5 * rho[0]; }
-    cost[b.kind] += c; cost[6] += c;
+    cost[b.kind == 6 ? 7 : b.kind] += c; cost[6] += c;
   }
   return 0;
 }

@@ -155,11 +155,11 @@ class OracleSpline:
 
     def jac_width(self, kind):
         N = self.N
-        return [6 * N + 10, 6 * N + 16, 3 * N + 13, 6 * N + 5, 24, 3][kind]
+        return [6 * N + 10, 6 * N + 16, 3 * N + 13, 6 * N + 5, 24, 3, 3 * N][kind]
 
     def evaluate(self, kind, jac=True):
         c = self.counts()
-        nres = [2 * c["obs"], 3 * c["accel"], 3 * c["gyro"], 3 * c["gp"], 3 * c["bias"], c["gravity"]][kind]
+        nres = [2 * c["obs"], 3 * c["accel"], 3 * c["gyro"], 3 * c["gp"], 3 * c["bias"], c["gravity"], 3 * self.numPriors()][kind]
         r = np.zeros(nres)
         J = np.zeros((nres, self.jac_width(kind))) if jac else None
         aux = np.zeros(1)
@@ -167,9 +167,23 @@ class OracleSpline:
         return r, J, float(aux[0])
 
     def cost(self):
-        o = np.zeros(7)
+        return self.costTerms()[:7]
+
+    def costTerms(self):
+        o = np.zeros(8)
         self.L.orc_cost(self.h, o.ctypes.data_as(C.c_void_p))
         return o
+
+    def addPositionMeasurements(self, t_ns, pos, noise):
+        t = np.ascontiguousarray(t_ns, dtype=np.int64); m = np.ascontiguousarray(pos, dtype=np.float64)
+        return self.L.orc_add_priors(self.h, 0, len(t), t.ctypes.data_as(C.c_void_p), m.ctypes.data_as(C.c_void_p), C.c_double(noise))
+
+    def addOrientationMeasurements(self, t_ns, quat_xyzw, noise):
+        t = np.ascontiguousarray(t_ns, dtype=np.int64); m = np.ascontiguousarray(quat_xyzw, dtype=np.float64)
+        return self.L.orc_add_priors(self.h, 1, len(t), t.ctypes.data_as(C.c_void_p), m.ctypes.data_as(C.c_void_p), C.c_double(noise))
+
+    def numPriors(self):
+        return self.L.orc_num_priors(self.h)
 
     def optimize(self, max_num_iterations, num_threads=1):
         s = np.zeros(6)

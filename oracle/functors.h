@@ -171,6 +171,40 @@ struct GlobalPositionSensorCostFunctor {
   }
 };
 
+// position_cost_functor.h:24-57
+template <int N>
+struct PositionCostFunctor {
+  double meas[3];
+  double u, inv_dt, inv_std;
+  template <class T>
+  bool operator()(T const* const* sKnots, T* r) const {
+    V3<T> p;
+    SplineHelper<N>::template evaluate<T, 0, double>(sKnots, u, inv_dt, &p);
+    r[0] = inv_std * (p.x - meas[0]);
+    r[1] = inv_std * (p.y - meas[1]);
+    r[2] = inv_std * (p.z - meas[2]);
+    return true;
+  }
+};
+
+// orientation_cost_functor.h:24-61:  dr = r * measurement.inverse();  residuals = inv_std * 2 dr.unit_quaternion().vec()
+template <int N>
+struct OrientationCostFunctor {
+  double meas[4];   // x y z w
+  double u, inv_dt, inv_std;
+  template <class T>
+  bool operator()(T const* const* sKnots, T* r) const {
+    SO3<T> rot;
+    SplineHelper<N>::template evaluate_lie<T, double>(sKnots, u, inv_dt, &rot);
+    SO3<T> mi = SO3<T>{T(meas[0]), T(meas[1]), T(meas[2]), T(meas[3])}.inverse();
+    SO3<T> dr = rot * mi;
+    r[0] = inv_std * (2.0 * dr.x);
+    r[1] = inv_std * (2.0 * dr.y);
+    r[2] = inv_std * (2.0 * dr.z);
+    return true;
+  }
+};
+
 struct GravityNormCostFunctor {
   double g_norm = 9.80665;
   double weight = 1e6;

@@ -137,6 +137,7 @@ struct FrameMeas {
 };
 struct ImuMeas { int64_t s; double st_s, k; int64_t s_bias; double u_bias; double meas[3]; double inv_std; };
 struct GpMeas { int64_t s; double st_s, k; double meas[3]; double inv_std; };
+struct PriorMeas { int64_t s; double u; int which; double meas[4]; double inv_std; };   // which: 0 position, 1 orientation
 struct BiasMeas { int64_t s0, s1; double u0, u1, inv_std; int which; /*0 acc 1 gyro*/ };
 
 struct SplineProblem {
@@ -161,6 +162,7 @@ struct SplineProblem {
   std::vector<FrameMeas> frames;
   std::vector<ImuMeas> accel, gyro;
   std::vector<GpMeas> gp;
+  std::vector<PriorMeas> priors;
   std::vector<BiasMeas> bias;
   bool gravity_norm = false;
 
@@ -285,6 +287,24 @@ struct SplineProblem {
     return added;
   }
 
+  // addPositionMeasurement :1048-1085 / addOrientationMeasurement :1087-1123
+  int addPriors(int which, int n, const int64_t* t_ns, const double* meas, double noise) {
+    int added = 0;
+    const int w = which ? 4 : 3;
+    for (int i = 0; i < n; ++i) {
+      int64_t st_ns = (t_ns[i] - start_t_ns);
+      if (st_ns < 0) continue;
+      int64_t s = st_ns / dt_ns;
+      double u = double(st_ns % dt_ns) / double(dt_ns);
+      if (size_t(s + N) > numKnots()) continue;
+      PriorMeas m; m.s = s; m.u = u; m.which = which; m.inv_std = 1.0 / noise;
+      for (int c = 0; c < 4; ++c) m.meas[c] = c < w ? meas[(size_t)w * i + c] : 0.0;
+      priors.push_back(m); ++added;
+    }
+    built = false;
+    return added;
+  }
+
   // Wire everything into the MiniProblem in the reference driver's order
   // (src/optimize_continuous_time.cpp:497, 526, 567-601): gravity norm, SO3 parameterisations,
   // GP, accel+gyro interleaved, frames, bias cost.
@@ -301,6 +321,20 @@ struct SplineProblem {
     }
     for (size_t i = 0; i < K; ++i) mp.AddParameterBlock(&so3[4 * i], 4, true);
     mp.AddParameterBlock(R_bc_corr, 4, true);
+    for (size_t i = 0; i < priors.size(); ++i) {   // fit_spline_to_colmap.cpp:182-192: after the parameterisations
+      const PriorMeas& m = priors[i];
+      ResidualBlock b; b.kind = 6; b.index = (int)i; b.nres = 3; b.cauchy_a = 0;
+      if (m.which == 0) {
+        for (int j = 0; j < NN; ++j) b.pb.push_back(mp.AddParameterBlock(&r3[3 * (m.s + j)], 3));
+        PositionCostFunctor<NN> f{{m.meas[0], m.meas[1], m.meas[2]}, m.u, inv_dt, m.inv_std};
+        b.eval = [f](const std::vector<const double*>& p, const std::vector<int>& sz, double* r, double* j) { dynamic_autodiff(f, p, sz, 3, r, j); };
+      } else {
+        for (int j = 0; j < NN; ++j) b.pb.push_back(mp.AddParameterBlock(&so3[4 * (m.s + j)], 4, true));
+        OrientationCostFunctor<NN> f{{m.meas[0], m.meas[1], m.meas[2], m.meas[3]}, m.u, inv_dt, m.inv_std};
+        b.eval = [f](const std::vector<const double*>& p, const std::vector<int>& sz, double* r, double* j) { dynamic_autodiff(f, p, sz, 3, r, j); };
+      }
+      mp.blocks.push_back(std::move(b));
+    }
     for (size_t i = 0; i < gp.size(); ++i) {
       const GpMeas& m = gp[i];
       ResidualBlock b; b.kind = 3; b.index = (int)i; b.nres = 3; b.cauchy_a = 0;

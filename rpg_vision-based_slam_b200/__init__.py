@@ -19,7 +19,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "libctba.so")
 _LIB = None
 
-CTBA_REPROJ, CTBA_ACCEL, CTBA_GYRO, CTBA_GP, CTBA_BIAS, CTBA_GRAVITY = range(6)
+CTBA_REPROJ, CTBA_ACCEL, CTBA_GYRO, CTBA_GP, CTBA_BIAS, CTBA_GRAVITY, CTBA_PRIOR = range(7)
 (CTBA_SAMPLE_POSE, CTBA_SAMPLE_ACCEL_BODY, CTBA_SAMPLE_ACCEL_WORLD, CTBA_SAMPLE_GYRO_BODY, CTBA_SAMPLE_GYRO_WORLD, CTBA_SAMPLE_ACCEL_BIAS,
  CTBA_SAMPLE_GYRO_BIAS) = range(7)
 
@@ -27,7 +27,7 @@ EXPORTS = [
     "ctba_create", "ctba_destroy", "ctba_last_error", "ctba_set_stream", "ctba_set_knots", "ctba_num_knots", "ctba_get_knots",
     "ctba_initialize_biases", "ctba_num_bias_knots", "ctba_set_biases", "ctba_get_biases", "ctba_set_landmarks", "ctba_get_landmarks",
     "ctba_set_camera", "ctba_set_globals", "ctba_set_corrections", "ctba_get_globals", "ctba_set_flags", "ctba_add_frames", "ctba_add_imu",
-    "ctba_add_gp", "ctba_add_bias_cost", "ctba_add_gravity_norm", "ctba_counts", "ctba_evaluate", "ctba_cost", "ctba_solve",
+    "ctba_add_gp", "ctba_add_position_measurements", "ctba_add_orientation_measurements", "ctba_num_priors", "ctba_cost_terms", "ctba_add_bias_cost", "ctba_add_gravity_norm", "ctba_counts", "ctba_evaluate", "ctba_cost", "ctba_solve",
     "ctba_relinearize_time_offsets", "ctba_bench_evaluate", "ctba_set_option", "ctba_invalidate_device", "ctba_transfer_bytes",
     "ctba_bench_reproj", "ctba_compute_valid_reprojections", "ctba_evaluate_errors", "ctba_sample", "ctba_comm_unique_id", "ctba_comm_init_nccl", "ctba_comm_init_local", "ctba_shard_plan",
 ]
@@ -188,6 +188,21 @@ class BSplineSO3R3:
         x = _d(pos)
         return self._chk(self.L.ctba_add_gp(self.h, int(t.size), _p(t), _p(x), C.c_double(noise)))
 
+    def addPositionMeasurements(self, t_ns, pos, noise):
+        """addPositionMeasurement per sample (bspline_so3r3.h:1048-1085)"""
+        t = np.ascontiguousarray(t_ns, dtype=np.int64)
+        x = _d(pos)
+        return self._chk(self.L.ctba_add_position_measurements(self.h, int(t.size), _p(t), _p(x), C.c_double(noise)))
+
+    def addOrientationMeasurements(self, t_ns, quat_xyzw, noise):
+        """addOrientationMeasurement per sample (bspline_so3r3.h:1087-1123)"""
+        t = np.ascontiguousarray(t_ns, dtype=np.int64)
+        x = _d(quat_xyzw)
+        return self._chk(self.L.ctba_add_orientation_measurements(self.h, int(t.size), _p(t), _p(x), C.c_double(noise)))
+
+    def numPriors(self):
+        return self.L.ctba_num_priors(self.h)
+
     def addImuBiasCost(self, freq_hz, dt_s, acc_rw, gyr_rw):
         return self._chk(self.L.ctba_add_bias_cost(self.h, C.c_double(freq_hz), C.c_double(dt_s), C.c_double(acc_rw), C.c_double(gyr_rw)))
 
@@ -202,11 +217,11 @@ class BSplineSO3R3:
     # ---- evaluation / solve ----
     def jac_width(self, kind):
         N = self.N
-        return [6 * N + 10, 6 * N + 16, 3 * N + 13, 6 * N + 5, 24, 3][kind]
+        return [6 * N + 10, 6 * N + 16, 3 * N + 13, 6 * N + 5, 24, 3, 3 * N][kind]
 
     def evaluate(self, kind, jac=True):
         c = self.counts()
-        nres = [2 * c["obs"], 3 * c["accel"], 3 * c["gyro"], 3 * c["gp"], 3 * c["bias"], c["gravity"]][kind]
+        nres = [2 * c["obs"], 3 * c["accel"], 3 * c["gyro"], 3 * c["gp"], 3 * c["bias"], c["gravity"], 3 * self.numPriors()][kind]
         r = np.zeros(nres)
         J = np.zeros((nres, self.jac_width(kind))) if jac else None
         n = self._chk(self.L.ctba_evaluate(self.h, int(kind), _p(r), _p(J) if jac else None))
@@ -216,6 +231,12 @@ class BSplineSO3R3:
     def cost(self):
         o = np.zeros(7)
         self._chk(self.L.ctba_cost(self.h, _p(o)))
+        return o
+
+    def costTerms(self):
+        """cost() plus [7] = the pose priors (position / orientation measurements)"""
+        o = np.zeros(8)
+        self._chk(self.L.ctba_cost_terms(self.h, _p(o)))
         return o
 
     def optimize(self, max_num_iterations):

@@ -24,6 +24,8 @@ int sync_to_device(ctba_problem* p) {
     CTBA_CUDA(p, p->d_g_inv_std.upload(p->g_inv_std, st)); CTBA_CUDA(p, p->d_g_meas.upload(p->g_meas, st));
     CTBA_CUDA(p, p->d_b_s0.upload(p->b_s0, st)); CTBA_CUDA(p, p->d_b_s1.upload(p->b_s1, st)); CTBA_CUDA(p, p->d_b_which.upload(p->b_which, st));
     CTBA_CUDA(p, p->d_b_u0.upload(p->b_u0, st)); CTBA_CUDA(p, p->d_b_u1.upload(p->b_u1, st)); CTBA_CUDA(p, p->d_b_inv_std.upload(p->b_inv_std, st));
+    CTBA_CUDA(p, p->d_q_s.upload(p->q_s, st)); CTBA_CUDA(p, p->d_q_which.upload(p->q_which, st)); CTBA_CUDA(p, p->d_q_u.upload(p->q_u, st));
+    CTBA_CUDA(p, p->d_q_inv_std.upload(p->q_inv_std, st)); CTBA_CUDA(p, p->d_q_meas.upload(p->q_meas, st));
     p->meas_dirty = false;
   }
   if (p->state_dirty) {
@@ -378,6 +380,36 @@ int ctba_add_gp(ctba_problem* p, int n, const int64_t* t_ns, const double* pos, 
   return added;
 }
 
+// addPositionMeasurement (bspline_so3r3.h:1048-1085) / addOrientationMeasurement (:1087-1123): same window arithmetic and skip rules
+static int add_priors(ctba_problem* p, int which, int n, const int64_t* t_ns, const double* meas, double noise) {
+  const int N = p->N, w = which ? 4 : 3;
+  int added = 0;
+  for (int i = 0; i < n; ++i) {
+    const int64_t st_ns = t_ns[i] - p->start_t_ns;
+    if (st_ns < 0) continue;
+    const int64_t s = st_ns / p->dt_ns;
+    const double u = double(st_ns % p->dt_ns) / double(p->dt_ns);
+    if (size_t(s + N) > p->numKnots()) continue;
+    p->q_s.push_back((int32_t)s); p->q_which.push_back(which); p->q_u.push_back(u); p->q_inv_std.push_back(1.0 / noise);
+    for (int c = 0; c < 4; ++c) p->q_meas.push_back(c < w ? meas[(size_t)w * i + c] : 0.0);
+    ++added;
+  }
+  p->meas_dirty = true; p->struct_dirty = true;
+  return added;
+}
+int ctba_add_position_measurements(ctba_problem* p, int n, const int64_t* t_ns, const double* pos, double noise) {
+  CHECK_P(p);
+  if (n < 0 || !t_ns || !pos || !(noise > 0)) return fail(p, CTBA_E_ARG, "add_position_measurements: bad arguments");
+  return add_priors(p, 0, n, t_ns, pos, noise);
+}
+int ctba_add_orientation_measurements(ctba_problem* p, int n, const int64_t* t_ns, const double* quat_xyzw, double noise) {
+  CHECK_P(p);
+  if (n < 0 || !t_ns || !quat_xyzw || !(noise > 0)) return fail(p, CTBA_E_ARG, "add_orientation_measurements: bad arguments");
+  return add_priors(p, 1, n, t_ns, quat_xyzw, noise);
+}
+
+int ctba_num_priors(const ctba_problem* p) { return p ? (int)p->q_s.size() : CTBA_E_ARG; }
+
 int ctba_add_bias_cost(ctba_problem* p, double freq_hz, double bias_err_dt_s, double acc_rw, double gyr_rw) {
   CHECK_P(p);
   if (!(freq_hz > 0) || !(acc_rw > 0) || !(gyr_rw > 0)) return fail(p, CTBA_E_ARG, "add_bias_cost: bad arguments");
@@ -421,7 +453,7 @@ int ctba_counts(ctba_problem* p, int64_t* c) {
 
 int ctba_evaluate(ctba_problem* p, int kind, double* r_out, double* j_out) {
   CHECK_P(p);
-  if (kind < 0 || kind > 5) return fail(p, CTBA_E_ARG, "evaluate: unknown residual kind");
+  if (kind < 0 || kind > CTBA_PRIOR) return fail(p, CTBA_E_ARG, "evaluate: unknown residual kind");
   if (p->device < 0) return fail(p, CTBA_E_CUDA, "planning-only handle (device -1): no compute entry points");
   CTBA_CUDA(p, cudaSetDevice(p->device));
   int rc = sync_to_device(p); if (rc) return rc;
@@ -447,6 +479,7 @@ int ctba_evaluate(ctba_problem* p, int kind, double* r_out, double* j_out) {
     case CTBA_GP: nres = 3 * p->g_s.size(); width = 6 * N + 5; d_r = p->ev.r_gp.p; d_J = p->ev.J_gp.p; break;
     case CTBA_BIAS: nres = 3 * p->b_s0.size(); width = 24; d_r = p->ev.r_bias.p; d_J = p->ev.J_bias.p; break;
     case CTBA_GRAVITY: nres = p->gravity_norm ? 1 : 0; width = 3; d_r = p->ev.r_grav.p; d_J = p->ev.J_grav.p; break;
+    case CTBA_PRIOR: nres = 3 * p->q_s.size(); width = 3 * N; d_r = p->ev.r_prior.p; d_J = p->ev.J_prior.p; break;
   }
   cudaError_t e = cudaSuccess;
   if (nres && r_out) e = cudaMemcpyAsync(r_out, d_r, nres * sizeof(double), cudaMemcpyDeviceToHost, st);
@@ -468,6 +501,16 @@ int ctba_cost(ctba_problem* p, double* cost7) {
   double c8[8];
   rc = shard_reduce_cost(p, p->ev, c8); if (rc) return rc;   // sharded handles: the cost terms of the whole problem
   for (int i = 0; i < 7; ++i) cost7[i] = c8[i];
+  return CTBA_OK;
+}
+
+int ctba_cost_terms(ctba_problem* p, double* cost8) {
+  double c7[7];
+  int rc = ctba_cost(p, c7); if (rc) return rc;
+  if (!cost8) return CTBA_E_ARG;
+  double c8[8];
+  rc = shard_reduce_cost(p, p->ev, c8); if (rc) return rc;
+  for (int i = 0; i < 8; ++i) cost8[i] = c8[i];
   return CTBA_OK;
 }
 
@@ -516,7 +559,7 @@ int ctba_transfer_bytes(ctba_problem* p, int64_t* b) {
   CHECK_P(p);
   if (!b) return CTBA_E_ARG;
   const int64_t state = (int64_t)(p->knot_q.size() + p->knot_p.size() + p->bias_a.size() + p->bias_g.size() + p->lm.size() + GLB_STATE_SIZE) * 8;
-  int64_t meas = 0;
+  int64_t meas = (int64_t)(p->q_s.size() + p->q_which.size()) * 4 + (int64_t)(p->q_u.size() + p->q_inv_std.size() + p->q_meas.size()) * 8;
   meas += (int64_t)(p->f_s.size() + p->f_obs_begin.size() + p->o_lm.size() + p->o_frame.size() + p->i_s.size() + p->i_sb.size() + p->g_s.size() +
                     p->b_s0.size() + p->b_s1.size() + p->b_which.size()) * 4;
   meas += (int64_t)(p->f_u.size() + p->f_inv_std.size() + p->o_uv.size() + p->i_st_s.size() + p->i_k.size() + p->i_ub.size() + p->i_inv_a.size() +

@@ -299,12 +299,14 @@ __global__ void __launch_bounds__(kSegThreads) k_rows_accumulate_seg(int kind, i
       if (c < 3 * N) idx = 6 * node_of_knot[i_s[i0] + c / 3] + c % 3;
       else if (c < 3 * N + 12) idx = 6 * node_of_bias[i_sb[i0] + (c - 3 * N) / 3] + 3 + (c - 3 * N) % 3;
       else idx = gm.a[GT_T_CAM_IMU] ? H.n_pad + GT_T_CAM_IMU : -1;
-    } else {  // [3N rot | 3N pos | p_bp 3 | t 1 | scale 1]
+    } else if (kind == 3) {  // [3N rot | 3N pos | p_bp 3 | t 1 | scale 1]
       if (c < 3 * N) idx = 6 * node_of_knot[i_s[i0] + c / 3] + c % 3;
       else if (c < 6 * N) idx = 6 * node_of_knot[i_s[i0] + (c - 3 * N) / 3] + 3 + c % 3;
       else if (c < 6 * N + 3) idx = gm.a[GT_PBP] ? H.n_pad + GT_PBP + (c - 6 * N) : -1;
       else if (c == 6 * N + 3) idx = gm.a[GT_T_GP] ? H.n_pad + GT_T_GP : -1;
       else idx = gm.a[GT_SCALE] ? H.n_pad + GT_SCALE : -1;
+    } else {  // pose prior: 3N columns over the position knots (i_sb = 0) or the rotation knots (i_sb = 1)
+      idx = 6 * node_of_knot[i_s[i0] + c / 3] + (i_sb[i0] ? 0 : 3) + c % 3;
     }
     sI[c] = idx;
   }
@@ -1325,7 +1327,16 @@ void analyse_structure(const ctba_problem* p, const GlobalStructure* gs, HostStr
     span(nb[std::min(a, b)], nb[std::max(a, b) + 3]);
     for (int j = 0; j < 4; ++j) { tb[a + j] |= (p->b_which[i] ? 2 : 1); tb[b + j] |= (p->b_which[i] ? 2 : 1); }
   }
+  for (size_t i = 0; i < p->q_s.size(); ++i) {
+    const int s = p->q_s[i];
+    span(nk[s], nk[s + N - 1]);
+    for (int j = 0; j < N; ++j) tk[s + j] |= (p->q_which[i] ? 1 : 2);
+  }
   // runs of consecutive samples that address the same unknowns (k_rows_accumulate_seg)
+  hs->prior_seg.assign(1, 0);
+  for (size_t i = 1; i < p->q_s.size(); ++i)
+    if (p->q_s[i] != p->q_s[i - 1] || p->q_which[i] != p->q_which[i - 1]) hs->prior_seg.push_back((int32_t)i);
+  if (!p->q_s.empty()) hs->prior_seg.push_back((int32_t)p->q_s.size());
   hs->imu_seg.assign(1, 0);
   for (size_t i = 1; i < p->i_s.size(); ++i)
     if (p->i_s[i] != p->i_s[i - 1] || p->i_sb[i] != p->i_sb[i - 1]) hs->imu_seg.push_back((int32_t)i);
@@ -1450,7 +1461,8 @@ int assemble_structure(ctba_problem* p) {
   CTBA_CUDA(p, sd->d_lm_frame.upload(hs.lmf, st));
   CTBA_CUDA(p, sd->d_o_pos.upload(hs.opos, st)); CTBA_CUDA(p, sd->d_o_end.upload(hs.oend, st));
   CTBA_CUDA(p, sd->d_imu_seg.upload(hs.imu_seg, st)); CTBA_CUDA(p, sd->d_gp_seg.upload(hs.gp_seg, st));
-  sd->n_imu_seg = (int)hs.imu_seg.size() - 1; sd->n_gp_seg = (int)hs.gp_seg.size() - 1; CTBA_CUDA(p, sd->d_kf_begin.upload(hs.kfb, st)); CTBA_CUDA(p, sd->d_kf_list.upload(hs.kfl, st));
+  CTBA_CUDA(p, sd->d_prior_seg.upload(hs.prior_seg, st));
+  sd->n_imu_seg = (int)hs.imu_seg.size() - 1; sd->n_gp_seg = (int)hs.gp_seg.size() - 1; sd->n_prior_seg = (int)hs.prior_seg.size() - 1; CTBA_CUDA(p, sd->d_kf_begin.upload(hs.kfb, st)); CTBA_CUDA(p, sd->d_kf_list.upload(hs.kfl, st));
   CTBA_CUDA(p, sd->Vi.resize(6 * (size_t)std::max(L, 1))); CTBA_CUDA(p, sd->vig.resize(3 * (size_t)std::max(L, 1)));
   CTBA_CUDA(p, sd->ViYg.resize(21 * (size_t)std::max(L, 1)));
   CTBA_CUDA(p, sd->Yo.resize(18 * (size_t)std::max(M, 1))); CTBA_CUDA(p, sd->Zo.resize(18 * (size_t)std::max(M, 1)));
@@ -1501,6 +1513,11 @@ static int assemble_direct_T(ctba_problem* p) {
   if (nG > 0) {
     k_rows_accumulate_seg<N><<<sd->n_gp_seg, kSegThreads, 0, st>>>(3, sd->n_gp_seg, sd->d_gp_seg.p, 6 * N + 5, p->ev.J_gp.p, p->ev.r_gp.p, p->d_g_s.p,
                                                                    nullptr, sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
+    p->launches++;
+  }
+  if (!p->q_s.empty()) {
+    k_rows_accumulate_seg<N><<<sd->n_prior_seg, kSegThreads, 0, st>>>(6, sd->n_prior_seg, sd->d_prior_seg.p, 3 * N, p->ev.J_prior.p, p->ev.r_prior.p,
+                                                                      p->d_q_s.p, p->d_q_which.p, sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
     p->launches++;
   }
   if (nB > 0) {

@@ -143,6 +143,26 @@ __global__ void __launch_bounds__(64) k_gp(const __grid_constant__ Globals G, St
   for (int c = 0; c < 3; ++c) r[3 * (size_t)i + c] = rr[c];
 }
 
+template <int N, bool JAC>
+__global__ void __launch_bounds__(64) k_prior(const __grid_constant__ Globals G, StatePtrs S, int n, const int32_t* __restrict__ q_s,
+                                              const int32_t* __restrict__ q_which, const double* __restrict__ q_u,
+                                              const double* __restrict__ meas, const double* __restrict__ inv_std, double* __restrict__ r,
+                                              double* __restrict__ J) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int s = q_s[i];
+  double kq[4 * N], kp[3 * N];
+#pragma unroll
+  for (int e = 0; e < 4 * N; ++e) kq[e] = S.knot_q[4 * (size_t)s + e];
+#pragma unroll
+  for (int e = 0; e < 3 * N; ++e) kp[e] = S.knot_p[3 * (size_t)s + e];
+  const double m[4] = {meas[4 * (size_t)i], meas[4 * (size_t)i + 1], meas[4 * (size_t)i + 2], meas[4 * (size_t)i + 3]};
+  double rr[3];
+  prior_eval<N, JAC>(G, kq, kp, q_which[i], q_u[i], m, inv_std[i], rr, JAC ? J + (size_t)i * 9 * N : nullptr);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) r[3 * (size_t)i + c] = rr[c];
+}
+
 template <bool JAC>
 __global__ void k_bias(const __grid_constant__ Globals G, StatePtrs S, int n, const int32_t* __restrict__ s0, const int32_t* __restrict__ s1,
                        const int32_t* __restrict__ which, const double* __restrict__ u0, const double* __restrict__ u1,
@@ -181,11 +201,12 @@ __global__ void __launch_bounds__(kRedThreads) k_partial_sum(const double* __res
   }
   if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
 }
-// cost[k] = factor * sum(partial[k*kRedBlocks ..]) for k<6 ; cost[6] = total
+// cost[k] = factor * sum(partial[k*kRedBlocks ..]) for k<6 and k = 7 (pose priors) ; cost[6] = total
 __global__ void __launch_bounds__(kRedThreads) k_final_cost(const double* __restrict__ partial, double* __restrict__ cost) {
   __shared__ double sh[kRedThreads];
-  __shared__ double tot[6];
-  for (int k = 0; k < 6; ++k) {
+  __shared__ double tot[8];
+  for (int k = 0; k < 8; ++k) {
+    if (k == 6) continue;
     sh[threadIdx.x] = partial[k * kRedBlocks + threadIdx.x];
     __syncthreads();
     for (int o = kRedThreads / 2; o > 0; o >>= 1) {
@@ -198,7 +219,8 @@ __global__ void __launch_bounds__(kRedThreads) k_final_cost(const double* __rest
   if (threadIdx.x == 0) {
     double t = 0;
     for (int k = 0; k < 6; ++k) { cost[k] = tot[k]; t += tot[k]; }
-    cost[6] = t;
+    cost[7] = tot[7];
+    cost[6] = t + tot[7];
   }
 }
 
@@ -299,6 +321,16 @@ static int launch_evaluate_T(ctba_problem* p, EvalBuffers& ev, const StatePtrs& 
                                                     ev.r_bias.p, nullptr);
     p->launches += 1;
   }
+  const int nQ = (int)p->q_s.size();
+  if (nQ > 0) {
+    CTBA_CUDA(p, ev.r_prior.resize(3 * (size_t)nQ));
+    if (jac) CTBA_CUDA(p, ev.J_prior.resize((size_t)nQ * 9 * N));
+    if (jac)
+      k_prior<N, true><<<cdiv(nQ, 64), 64, 0, st>>>(G, S, nQ, p->d_q_s.p, p->d_q_which.p, p->d_q_u.p, p->d_q_meas.p, p->d_q_inv_std.p, ev.r_prior.p, ev.J_prior.p);
+    else
+      k_prior<N, false><<<cdiv(nQ, 64), 64, 0, st>>>(G, S, nQ, p->d_q_s.p, p->d_q_which.p, p->d_q_u.p, p->d_q_meas.p, p->d_q_inv_std.p, ev.r_prior.p, nullptr);
+    p->launches += 1;
+  }
   if (p->gravity_norm) {
     CTBA_CUDA(p, ev.r_grav.resize(1)); CTBA_CUDA(p, ev.J_grav.resize(3));
     k_gravity<<<1, 32, 0, st>>>(S, ev.r_grav.p, jac ? ev.J_grav.p : nullptr);
@@ -353,9 +385,9 @@ int launch_evaluate(ctba_problem* p, EvalBuffers& ev, const StatePtrs& S, bool j
 
 int launch_cost(ctba_problem* p, EvalBuffers& ev) {
   cudaStream_t st = p->stream;
-  CTBA_CUDA(p, ev.partial.resize(6 * kRedBlocks));
+  CTBA_CUDA(p, ev.partial.resize(8 * kRedBlocks));
   CTBA_CUDA(p, ev.cost.resize(8));
-  CTBA_CUDA(p, cudaMemsetAsync(ev.partial.p, 0, 6 * kRedBlocks * sizeof(double), st));
+  CTBA_CUDA(p, cudaMemsetAsync(ev.partial.p, 0, 8 * kRedBlocks * sizeof(double), st));
   const size_t F = p->numFrames(), nI = p->i_s.size(), nG = p->g_s.size(), nB = p->b_s0.size();
   if (F) { k_partial_sum<<<kRedBlocks, kRedThreads, 0, st>>>(ev.f_cost.p, F, false, ev.partial.p + 0 * kRedBlocks); p->launches++; }
   if (nI) {
@@ -366,6 +398,7 @@ int launch_cost(ctba_problem* p, EvalBuffers& ev) {
   if (nG) { k_partial_sum<<<kRedBlocks, kRedThreads, 0, st>>>(ev.r_gp.p, 3 * nG, true, ev.partial.p + 3 * kRedBlocks); p->launches++; }
   if (nB) { k_partial_sum<<<kRedBlocks, kRedThreads, 0, st>>>(ev.r_bias.p, 3 * nB, true, ev.partial.p + 4 * kRedBlocks); p->launches++; }
   if (p->gravity_norm) { k_partial_sum<<<kRedBlocks, kRedThreads, 0, st>>>(ev.r_grav.p, 1, true, ev.partial.p + 5 * kRedBlocks); p->launches++; }
+  if (!p->q_s.empty()) { k_partial_sum<<<kRedBlocks, kRedThreads, 0, st>>>(ev.r_prior.p, 3 * p->q_s.size(), true, ev.partial.p + 7 * kRedBlocks); p->launches++; }
   k_final_cost<<<1, kRedThreads, 0, st>>>(ev.partial.p, ev.cost.p);
   p->launches++;
   CTBA_CUDA(p, cudaGetLastError());

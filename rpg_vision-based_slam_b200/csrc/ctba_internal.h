@@ -66,7 +66,7 @@ struct EvalBuffers {
   DBuf<double> Jl;                // 6M   planar: Jl[c*M + i]
   DBuf<double> f_sq, f_w, f_cost; // per frame: |r|^2, sqrt(rho'), 1/2 rho
   DBuf<double> r_acc, r_gyr, J_acc, J_gyr;
-  DBuf<double> r_gp, J_gp, r_bias, J_bias, r_grav, J_grav;
+  DBuf<double> r_gp, J_gp, r_bias, J_bias, r_grav, J_grav, r_prior, J_prior;
   DBuf<double> partial;           // reduction scratch
   DBuf<double> cost;              // 8 doubles
 };
@@ -113,12 +113,16 @@ struct ctba_problem {
   ctba::HVec<double> g_st_s, g_k, g_inv_std, g_meas;
   ctba::HVec<int32_t> b_s0, b_s1, b_which;
   ctba::HVec<double> b_u0, b_u1, b_inv_std;
+  ctba::HVec<int32_t> q_s, q_which;             // pose priors (addPositionMeasurement / addOrientationMeasurement): window, 0 position | 1 orientation
+  ctba::HVec<double> q_u, q_inv_std, q_meas;    // u, 1 / noise, measurement (4 per prior: x y z - | qx qy qz qw)
   bool gravity_norm = false;
 
   // ---- device ----
   bool meas_dirty = true, state_dirty = true, host_state_stale = false, struct_dirty = true;
   ctba::DeviceState dstate;
   ctba::DBuf<int32_t> d_f_s, d_f_obs_begin, d_o_lm, d_o_frame, d_i_s, d_i_sb, d_g_s, d_b_s0, d_b_s1, d_b_which;
+  ctba::DBuf<int32_t> d_q_s, d_q_which;
+  ctba::DBuf<double> d_q_u, d_q_inv_std, d_q_meas;
   ctba::DBuf<double> d_f_u, d_f_inv_std, d_o_uv, d_i_st_s, d_i_k, d_i_ub, d_i_inv_a, d_i_inv_g, d_i_acc, d_i_gyr, d_g_st_s, d_g_k,
       d_g_inv_std, d_g_meas, d_b_u0, d_b_u1, d_b_inv_std;
   ctba::EvalBuffers ev;      // evaluation at the current state (Jacobians used by the assembly kernels)

@@ -174,7 +174,7 @@ int ctba_compute_valid_reprojections(ctba_problem* p, int F, const int64_t* t_ns
 
 int ctba_evaluate_errors(ctba_problem* p, int kind, double* errors) {
   if (!p) return CTBA_E_ARG;
-  if (kind < CTBA_REPROJ || kind > CTBA_GP) { p->err = "evaluate_errors: kind must be reprojection, accel, gyro or global position"; return CTBA_E_ARG; }
+  if ((kind < CTBA_REPROJ || kind > CTBA_GP) && kind != CTBA_PRIOR) { p->err = "evaluate_errors: kind must be reprojection, accel, gyro, global position or pose prior"; return CTBA_E_ARG; }
   if (p->device < 0) { p->err = "planning-only handle (device -1): no compute entry points"; return CTBA_E_CUDA; }
   CTBA_CUDA(p, cudaSetDevice(p->device));
   int rc = sync_to_device(p); if (rc) return rc;
@@ -187,6 +187,7 @@ int ctba_evaluate_errors(ctba_problem* p, int kind, double* errors) {
     case CTBA_REPROJ: n = (int)p->numObs(); nres = 2; r = p->ev.r_reproj.p; w = p->d_f_inv_std.p; idx = p->d_o_frame.p; break;
     case CTBA_ACCEL: n = (int)p->i_s.size(); r = p->ev.r_acc.p; w = p->d_i_inv_a.p; break;
     case CTBA_GYRO: n = (int)p->i_s.size(); r = p->ev.r_gyr.p; w = p->d_i_inv_g.p; break;
+    case CTBA_PRIOR: n = (int)p->q_s.size(); r = p->ev.r_prior.p; w = p->d_q_inv_std.p; break;   // evaluatePositionErrors / evaluateOrientationErrors :1581-1680
     default: n = (int)p->g_s.size(); r = p->ev.r_gp.p; w = p->d_g_inv_std.p; break;
   }
   if (n == 0 || !errors) return n;

@@ -228,6 +228,7 @@ static void keep(std::vector<T, A>& v, const std::vector<char>& mask, int width 
 int shard_build(ctba_problem* p) {
   if (!p->comm || p->comm->world <= 1 || p->sharded) return CTBA_OK;
   const int world = p->comm->world, rank = p->comm->rank;
+  if (!p->q_s.empty()) { p->err = "shard: pose priors (spline-fitting problems) are solved on one GPU"; return CTBA_E_ARG; }
   if (!p->shard) p->shard = new ShardInfo();
   if (!p->gstruct) p->gstruct = new GlobalStructure();
   ShardInfo& sh = *p->shard;
@@ -293,7 +294,7 @@ int shard_build(ctba_problem* p) {
 int shard_reduce_cost(ctba_problem* p, EvalBuffers& ev, double* host_cost8) {
   cudaStream_t st = p->stream;
   if (!p->sharded) {
-    CTBA_CUDA(p, cudaMemcpyAsync(host_cost8, ev.cost.p, 7 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CTBA_CUDA(p, cudaMemcpyAsync(host_cost8, ev.cost.p, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
     CTBA_CUDA(p, cudaStreamSynchronize(st));
     return CTBA_OK;
   }
@@ -303,7 +304,7 @@ int shard_reduce_cost(ctba_problem* p, EvalBuffers& ev, double* host_cost8) {
   std::vector<double> h((size_t)W * 8);
   CTBA_CUDA(p, cudaMemcpyAsync(h.data(), p->d_gather.p, h.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
   CTBA_CUDA(p, cudaStreamSynchronize(st));
-  for (int c = 0; c < 7; ++c) { double s = 0.0; for (int r = 0; r < W; ++r) s += h[(size_t)r * 8 + c]; host_cost8[c] = s; }
+  for (int c = 0; c < 8; ++c) { double s = 0.0; for (int r = 0; r < W; ++r) s += h[(size_t)r * 8 + c]; host_cost8[c] = s; }
   return CTBA_OK;
 }
 

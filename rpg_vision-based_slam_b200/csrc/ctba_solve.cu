@@ -26,7 +26,7 @@ void solver_free(SolverData* sd) {
                         &sd->rp, &sd->Vi, &sd->vig, &sd->ViYg, &sd->Yo, &sd->Zo, &sd->lm_corner_partial, &sd->jscale, &sd->jscale_lm, &sd->delta, &sd->delta_lm, &sd->dpose, &sd->scal, &sd->cand.knot_q, &sd->cand.knot_p,
                         &sd->cand.bias_a, &sd->cand.bias_g, &sd->cand.lm, &sd->cand.glb};
   for (auto* d : dd) d->release();
-  DBuf<int32_t>* di[] = {&sd->d_node_of_knot, &sd->d_node_of_bias, &sd->d_lm_obs_begin, &sd->d_lm_obs, &sd->d_o_pos, &sd->d_o_end, &sd->d_imu_seg, &sd->d_gp_seg, &sd->d_lm_frame, &sd->d_kf_begin, &sd->d_kf_list, &sd->flag, &sd->d_lm_owner};
+  DBuf<int32_t>* di[] = {&sd->d_node_of_knot, &sd->d_node_of_bias, &sd->d_lm_obs_begin, &sd->d_lm_obs, &sd->d_o_pos, &sd->d_o_end, &sd->d_imu_seg, &sd->d_gp_seg, &sd->d_prior_seg, &sd->d_lm_frame, &sd->d_kf_begin, &sd->d_kf_list, &sd->flag, &sd->d_lm_owner};
   for (auto* d : di) d->release();
   sd->d_touch_knot.release(); sd->d_touch_bias.release(); sd->d_touch_lm.release();
   delete sd;

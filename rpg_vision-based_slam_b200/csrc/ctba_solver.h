@@ -45,7 +45,7 @@ __device__ __forceinline__ void add_sym(const BandLayout& B, int i, int j, doubl
 struct HostStructure {
   int K = 0, Kb = 0, L = 0, F = 0, M = 0, nodes = 0, hbn = 0, T = 0, KD = 0, max_frame_obs = 1, n_band = 0, n_pad = 0, nbw = 0;
   bool has_imu = false;
-  std::vector<int32_t> node_of_knot, node_of_bias, lob, lobs, opos, oend, imu_seg, gp_seg, lmf, kfb, kfl, lm_smin;
+  std::vector<int32_t> node_of_knot, node_of_bias, lob, lobs, opos, oend, imu_seg, gp_seg, prior_seg, lmf, kfb, kfl, lm_smin;
   std::vector<uint8_t> tk, tb, tl;
   int gactive[GT_SIZE] = {0};
 };
@@ -61,8 +61,8 @@ struct SolverData {
   DBuf<int32_t> d_lm_owner;   // sharded: owning rank of every landmark
   int max_frame_obs = 1;
   double frames_per_knot = 0.0;   // average number of frames whose window contains a knot (over the knots that have any)
-  DBuf<int32_t> d_imu_seg, d_gp_seg;   // runs of samples with the same unknowns (CSR offsets)
-  int n_imu_seg = 0, n_gp_seg = 0;
+  DBuf<int32_t> d_imu_seg, d_gp_seg, d_prior_seg;   // runs of samples with the same unknowns (CSR offsets)
+  int n_imu_seg = 0, n_gp_seg = 0, n_prior_seg = 0;
   DBuf<int32_t> d_o_pos, d_o_end, d_kf_begin, d_kf_list;   // observation -> slot in its landmark's list; knot -> frames (CSR)
   DBuf<double> Vi, vig, ViYg, Yo, Zo, lm_corner_partial;   // Schur gather scratch (ctba_assemble.cu)
   DBuf<uint8_t> d_touch_knot, d_touch_bias, d_touch_lm;  // bit0 rot/acc, bit1 pos/gyr

@@ -281,6 +281,63 @@ CTBA_HD void gp_sample_eval(const Globals& G, const double* glb, const double* k
   }
 }
 
+// Pose priors of the spline-fitting tools.  which = 0: PositionCostFunctor (position_cost_functor.h:39-53), r = inv_std (p(u) - meas),
+// J 3 x 3N over the position knots;  which = 1: OrientationCostFunctor (orientation_cost_functor.h:39-57),
+// r = inv_std * 2 vec(R(u) * meas^-1), J 3 x 3N over the right tangents of the rotation knots.
+template <int N, bool JAC>
+CTBA_HD void prior_eval(const Globals& G, const double* knot_q, const double* knot_p, int which, double u, const double* meas /*4*/,
+                        double inv_std, double* r, double* J) {
+  constexpr int W = 3 * N;
+  if (which == 0) {
+    double c[N];
+    spline_coeffs<N>(G.tb.blend, G.tb.base, 0, 1.0, u, c);
+    v3 p{0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < N; ++i) { p.x += c[i] * knot_p[3 * i]; p.y += c[i] * knot_p[3 * i + 1]; p.z += c[i] * knot_p[3 * i + 2]; }
+    r[0] = inv_std * (p.x - meas[0]); r[1] = inv_std * (p.y - meas[1]); r[2] = inv_std * (p.z - meas[2]);
+    if (JAC) {
+#pragma unroll
+      for (int i = 0; i < N; ++i)
+#pragma unroll
+        for (int rr = 0; rr < 3; ++rr)
+#pragma unroll
+          for (int cc = 0; cc < 3; ++cc) J[rr * W + 3 * i + cc] = (rr == cc) ? inv_std * c[i] : 0.0;
+    }
+    return;
+  }
+  So3SplineResult<N> sr;
+  so3_spline_eval<N, false, false, JAC>(G.tb, knot_q, u, G.inv_dt, &sr);
+  const quat mi = quat_inv(quat{meas[0], meas[1], meas[2], meas[3]});
+  const quat dr = quat_mul(sr.q, mi);
+  r[0] = inv_std * 2.0 * dr.x; r[1] = inv_std * 2.0 * dr.y; r[2] = inv_std * 2.0 * dr.z;
+  if (JAC) {
+    // d[2 vec(q (e/2, 1) m^-1)]/de = vec(q (e_k, 0) m^-1): plain Hamilton products (a unit-norm product stays unit to first order)
+    auto ham = [](quat a, quat b) {
+      quat o;
+      o.w = a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z;
+      o.x = a.w * b.x + a.x * b.w + a.y * b.z - a.z * b.y;
+      o.y = a.w * b.y + a.y * b.w + a.z * b.x - a.x * b.z;
+      o.z = a.w * b.z + a.z * b.w + a.x * b.y - a.y * b.x;
+      return o;
+    };
+    m3 Je;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const quat e{k == 0 ? 1.0 : 0.0, k == 1 ? 1.0 : 0.0, k == 2 ? 1.0 : 0.0, 0.0};
+      const quat o = ham(ham(sr.q, e), mi);
+      Je.a[k] = o.x; Je.a[3 + k] = o.y; Je.a[6 + k] = o.z;
+    }
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      const m3 Ji = mul(Je, sr.dR[i]);
+#pragma unroll
+      for (int rr = 0; rr < 3; ++rr)
+#pragma unroll
+        for (int cc = 0; cc < 3; ++cc) J[rr * W + 3 * i + cc] = inv_std * Ji.a[3 * rr + cc];
+    }
+  }
+}
+
 // Bias smoothness. J layout 3 x 24: [4 knots at s0 | 4 knots at s1]
 template <bool JAC>
 CTBA_HD void bias_cost_eval(const Globals& G, const double* b0 /*12*/, const double* b1 /*12*/, double u0, double u1, double inv_std, double* r,
