@@ -63,6 +63,21 @@ def test_lm_gv_cubic(pkg, scene, oracle):
     _check(gpu, cpu, sg, so)
 
 
+def test_lm_gi_no_frames(pkg, scene, oracle):
+    """optimize_gi_continuous_time-shaped (src/optimize_gi_continuous_time.cpp:303-431): global positions + IMU + bias cost, NO vision;
+    p_bp, gravity and the spline / global-sensor time offset free; one iteration, relinearise, then the rest (outer / inner loop)."""
+    sc = scene.make_scene(order=6, duration_s=4.0, n_landmarks=20, track_len=4, imu_hz=100, gp_hz=10, dt_s_bias=0.25, seed=41,
+                          flags=(False, True, True, True, True), gravity_norm=True)
+    gpu = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=0)
+    cpu = oracle.OracleSpline(sc["order"], sc["dt_ns"], sc["start_t_ns"])
+    pkg.load_scene(gpu, sc, with_frames=False); pkg.load_scene(cpu, sc, with_frames=False)
+    assert gpu.counts()["frames"] == 0 and gpu.counts()["gp"] > 0 and gpu.counts()["accel"] > 0
+    for h in (gpu, cpu):
+        h.optimize(1); h.relinearize()
+    sg = gpu.optimize(8); so = cpu.optimize(8, 8)
+    _check(gpu, cpu, sg, so)
+
+
 def test_lm_nested_interface_levels(pkg, scene, oracle):
     """The same LM parity with the band solver's nested interface reduction (odd-even over the separators, 3 levels here) and with a
     forced flat 5-partition plan: the linear solve is exact either way."""
