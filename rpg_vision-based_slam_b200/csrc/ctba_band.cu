@@ -382,41 +382,73 @@ __global__ void __launch_bounds__(256) k_fb_init(BandLayout B, const __grid_cons
 
 // ---- Gram matrices of the factored borders:  G_p = W_p W_p^T over the interior columns (lower 32x32 tiles, split over column chunks) ----
 constexpr int kGramChunk = 16;
-struct GramPlan { int P; int tile0[kMaxParts + 1]; int nsplit[kMaxParts]; int task0[kMaxParts + 1]; };   // tiles / tasks prefix sums
-__global__ void __launch_bounds__(kStepThreads) k_gram_partial(const __grid_constant__ BandParts PS, const __grid_constant__ GramPlan GP,
-                                                               double* __restrict__ scratch /* [task][1024] */) {
+struct GramPlan { int P; int tile0[kMaxParts + 1]; int nsplit[kMaxParts]; int task0[kMaxParts + 1]; int stask0[kMaxParts + 1]; };   // tiles / tasks / super-tile tasks prefix sums
+// CTA = a 64 x 64 super-tile (2 x 2 tiles of 32 x 32, lower triangle of super-tiles) over one column chunk; warp (wr, wc) owns rows
+// 16 wr .. +16 and columns 32 wc .. +32 of it: 2 x 4 tiles of 8 x 8, so one pair of A fragments and two pairs of B fragments feed 32 DMMAs
+// (the 32 x 32 version loaded three fragments per 16).  The partials land in the same [task][1024] scratch layout (task = chunk * ntile
+// + 32-tile), so the reduction kernel is unchanged.
+__global__ void __launch_bounds__(kStepThreads, 2) k_gram_partial(const __grid_constant__ BandParts PS, const __grid_constant__ GramPlan GP,
+                                                                  double* __restrict__ scratch /* [task][1024] */) {
   int task = blockIdx.x, pi = 0;
-  while (pi + 1 < GP.P && task >= GP.task0[pi + 1]) ++pi;
-  task -= GP.task0[pi];
+  while (pi + 1 < GP.P && task >= GP.stask0[pi + 1]) ++pi;
+  task -= GP.stask0[pi];
   const BandPart& Q = PS.part[pi];
   const int ntile = GP.tile0[pi + 1] - GP.tile0[pi];
-  const int tile = task % ntile, ks = task / ntile;
-  int ta = (int)((sqrtf(8.0f * tile + 1.0f) - 1.0f) * 0.5f);
-  while ((ta + 1) * (ta + 2) / 2 <= tile) ++ta;
-  while (ta * (ta + 1) / 2 > tile) --ta;
-  const int tb = tile - ta * (ta + 1) / 2;
+  const int nst = (Q.nrb + 1) >> 1, nsuper = nst * (nst + 1) / 2;
+  const int sup = task % nsuper, ks = task / nsuper;
+  int sa = (int)((sqrtf(8.0f * sup + 1.0f) - 1.0f) * 0.5f);
+  while ((sa + 1) * (sa + 2) / 2 <= sup) ++sa;
+  while (sa * (sa + 1) / 2 > sup) --sa;
+  const int sb = sup - sa * (sa + 1) / 2;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tr = warp >> 1, g = lane >> 2, tq = lane & 3;
-  const int rows_a = (ta == Q.nrb - 1) ? kBorder : kNB, rows_b = (tb == Q.nrb - 1) ? kBorder : kNB;
-  double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
-  const int col0 = ks * kGramChunk, col1 = min(col0 + kGramChunk, Q.nI);
-  const double* Fa = Q.fb + (size_t)ta * kNB * Q.ld;
-  const double* Fb = Q.fb + (size_t)tb * kNB * Q.ld;
-  if (8 * tr < rows_a) {
-    for (int col = col0; col < col1; ++col) {
+  const int wr = warp >> 1, wc = warp & 1, g = lane >> 2, tq = lane & 3;
+  const int R = kNB * (Q.nrb - 1) + kBorder, Rpad = kNB * Q.nrb;
+  const int row0 = 64 * sa + 16 * wr, col0 = 64 * sb + 32 * wc;
+  if (row0 >= Rpad || col0 >= Rpad) return;                       // no 32-tile here (odd number of row blocks)
+  if ((row0 >> 5) < (col0 >> 5)) return;                          // the upper 32-tile of a diagonal super-tile
+  double acc[2][4][2];
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int tc = 2 * (warp & 1) + h;
-        if (8 * tc < rows_b) tile_abt(Fa + (size_t)col * kNB, Q.ld, Fb + (size_t)col * kNB, Q.ld, tr, tc, lane, acc[h][0], acc[h][1]);
-      }
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int h = 0; h < 4; ++h) acc[i][h][0] = acc[i][h][1] = 0.0;
+  const int col_first = ks * kGramChunk, col_last = min(col_first + kGramChunk, Q.nI);
+  const bool va0 = row0 < R, va1 = row0 + 8 < R;
+  const bool vb0 = col0 < R, vb1 = col0 + 8 < R, vb2 = col0 + 16 < R, vb3 = col0 + 24 < R;
+  const double* Fa = Q.fb + (size_t)(row0 + g) * Q.ld + 8 * tq;
+  const double* Fb = Q.fb + (size_t)(col0 + g) * Q.ld + 8 * tq;
+  const size_t r8 = (size_t)8 * Q.ld;
+  for (int col = col_first; col < col_last; ++col) {
+    const size_t co = (size_t)col * kNB;
+    double a0[8], a1[8], b0[8], b1[8];
+    if (va0) load_frag8(Fa + co, a0);
+    if (va1) load_frag8(Fa + r8 + co, a1);
+    if (vb0) load_frag8(Fb + co, b0);
+    if (vb1) load_frag8(Fb + r8 + co, b1);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (va0 && vb0) dmma884(acc[0][0][0], acc[0][0][1], a0[k], b0[k]);
+      if (va0 && vb1) dmma884(acc[0][1][0], acc[0][1][1], a0[k], b1[k]);
+      if (va1 && vb0) dmma884(acc[1][0][0], acc[1][0][1], a1[k], b0[k]);
+      if (va1 && vb1) dmma884(acc[1][1][0], acc[1][1][1], a1[k], b1[k]);
+    }
+    if (vb2) load_frag8(Fb + 2 * r8 + co, b0);
+    if (vb3) load_frag8(Fb + 3 * r8 + co, b1);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (va0 && vb2) dmma884(acc[0][2][0], acc[0][2][1], a0[k], b0[k]);
+      if (va0 && vb3) dmma884(acc[0][3][0], acc[0][3][1], a0[k], b1[k]);
+      if (va1 && vb2) dmma884(acc[1][2][0], acc[1][2][1], a1[k], b0[k]);
+      if (va1 && vb3) dmma884(acc[1][3][0], acc[1][3][1], a1[k], b1[k]);
     }
   }
-  double* out = scratch + ((size_t)blockIdx.x << 10);
+  // rows / columns past R inside an existing 32-tile are written as zeros (the reduction reads whole tiles)
+  const int ta = row0 >> 5, tb = col0 >> 5;
+  double* out = scratch + ((size_t)(GP.task0[pi] + ks * ntile + ta * (ta + 1) / 2 + tb) << 10);
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    const int tc = 2 * (warp & 1) + h;
-    *reinterpret_cast<double2*>(out + (8 * tr + g) * kNB + 8 * tc + 2 * tq) = make_double2(acc[h][0], acc[h][1]);
-  }
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int h = 0; h < 4; ++h)
+      *reinterpret_cast<double2*>(out + ((row0 & 31) + 8 * i + g) * kNB + 8 * h + 2 * tq) = make_double2(acc[i][h][0], acc[i][h][1]);
 }
 // G_p tile = sum of its column-chunk partials in fixed order (deterministic); G_p is stored row-major with ld = 32 * nrb
 __global__ void __launch_bounds__(256) k_gram_reduce(const __grid_constant__ BandParts PS, const __grid_constant__ GramPlan GP,
@@ -701,7 +733,7 @@ struct BandLevel {
   BandParts PSloc{};        // the partitions this handle factors (all of them, except at level 0 of a problem sharded over ranks)
   GramPlan GP{};
   IfaceArgs IA{};
-  int gram_tasks = 0, gram_tiles = 0;
+  int gram_tasks = 0, gram_tiles = 0, gram_stasks = 0;
   size_t sys_elems = 0;     // next level's band | border | corner | extra, ONE buffer (a sharded solve all-reduces level 0's)
   DBuf<double> fb, gram, gram_scratch, sys, delta_own, dinv, cpart;
   double* delta = nullptr;  // solution of this level (level 0: the solver's delta; otherwise delta_own)
@@ -811,18 +843,19 @@ static int level_build(ctba_problem* p, BandPlan& pl, int li, const PartLayout& 
   L.GP = GramPlan{}; L.GP.P = q_hi - q_lo;
   L.PSloc = BandParts{}; L.PSloc.P = q_hi - q_lo; L.PSloc.sepw = sepw;
   L.IA = IfaceArgs{};
-  int tiles = 0, tasks = 0;
+  int tiles = 0, tasks = 0, stasks = 0;
   for (int q = q_lo; q < q_hi; ++q) {
     BandPart& Q = L.PS.part[q];
     Q.fb = L.fb.p + fb_off[q];
     L.PSloc.part[q - q_lo] = Q;
     L.IA.gram_off[q] = g_off[q];
     const int nt = Q.nrb * (Q.nrb + 1) / 2, ns = (Q.nI + kGramChunk - 1) / kGramChunk;
-    L.GP.tile0[q - q_lo] = tiles; L.GP.task0[q - q_lo] = tasks; L.GP.nsplit[q - q_lo] = ns;
-    tiles += nt; tasks += nt * ns;
+    L.GP.tile0[q - q_lo] = tiles; L.GP.task0[q - q_lo] = tasks; L.GP.nsplit[q - q_lo] = ns; L.GP.stask0[q - q_lo] = stasks;
+    const int nst = (Q.nrb + 1) / 2;
+    tiles += nt; tasks += nt * ns; stasks += nst * (nst + 1) / 2 * ns;
   }
-  L.GP.tile0[q_hi - q_lo] = tiles; L.GP.task0[q_hi - q_lo] = tasks;
-  L.gram_tiles = tiles; L.gram_tasks = tasks;
+  L.GP.tile0[q_hi - q_lo] = tiles; L.GP.task0[q_hi - q_lo] = tasks; L.GP.stask0[q_hi - q_lo] = stasks;
+  L.gram_tiles = tiles; L.gram_tasks = tasks; L.gram_stasks = stasks;
   L.IA.gram = L.gram.p; L.IA.q_lo = q_lo; L.IA.q_hi = q_hi;
   CTBA_CUDA(p, L.gram_scratch.resize((size_t)tasks * 1024));
   if (!L.d_gram_off) CTBA_CUDA(p, cudaMalloc((void**)&L.d_gram_off, kMaxParts * sizeof(size_t)));
@@ -942,7 +975,7 @@ static int band_enqueue(ctba_problem* p, cudaStream_t st, BandPlan& pl, int phas
     k_fb_init<<<nblk, 256, 0, st>>>(L.B, L.PSloc);
     ++*nl;
     rc = enqueue_steps(p, st, L.B, L.PSloc, L.max_steps, L.dinv.p, nl); if (rc) return rc;
-    k_gram_partial<<<L.gram_tasks, kStepThreads, 0, st>>>(L.PSloc, L.GP, L.gram_scratch.p);
+    k_gram_partial<<<L.gram_stasks, kStepThreads, 0, st>>>(L.PSloc, L.GP, L.gram_scratch.p);
     k_gram_reduce<<<L.gram_tiles, 256, 0, st>>>(L.PSloc, L.GP, L.gram_scratch.p, L.gram.p, L.d_gram_off);
     k_iface_assemble<<<B2.nbc * (B2.nbw + 1) + B2.nbc + 1, 256, 0, st>>>(L.B, B2, L.PS, L.IA, sd->flag.p);
     *nl += 3;
