@@ -209,10 +209,17 @@ __host__ __device__ inline void part_tasks(const BandLayout& B, const BandPart& 
   int m = (t >= 1 && t <= q.nI) ? k_hi - *k_lo + 1 : 0;
   *m_upd = m > 0 ? m : 0;
 }
+// update tasks of one partition at one step: 64 x 64 super-tiles (2 x 2 blocks) over the lower triangle of the m trailing block columns
+// and over (border row blocks) x (trailing block columns)
+__host__ __device__ inline int part_update_tasks(int m, int nrb) {
+  const int ms = (m + 1) >> 1, nrs = (nrb + 1) >> 1;
+  return m > 0 ? ms * (ms + 1) / 2 + ms * nrs : 0;
+}
+
 __host__ __device__ inline int part_task_total(const BandLayout& B, const BandPart& q, int t) {
   int np, m, kl;
   part_tasks(B, q, t, &np, &m, &kl);
-  return np + m * (m + 1) / 2 + m * q.nrb;
+  return np + part_update_tasks(m, q.nrb);
 }
 
 
@@ -294,13 +301,16 @@ __global__ void __launch_bounds__(kStepThreads) k_band_panel(BandLayout B, const
   }
 }
 
-__global__ void __launch_bounds__(kStepThreads, 4) k_band_update(BandLayout B, const __grid_constant__ BandParts PS, int t) {
+// CTA = one super-tile; warp (wr, wc) owns rows 16 (wr & 1) .. +16 of row block (wr >> 1) and the 32 columns of column block wc of it:
+// 2 x 4 DMMA tiles from two A fragments and four B fragments (the one-block-per-CTA version loaded three fragments per two tiles), all
+// operand and target loads issued before the first DMMA.
+__global__ void __launch_bounds__(kStepThreads, 2) k_band_update(BandLayout B, const __grid_constant__ BandParts PS, int t) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nb1 = B.nbw + 1;
   int u = blockIdx.x, pi = 0, n_panel = 0, m = 0, k_lo = 0;
   for (; pi < PS.P; ++pi) {
     part_tasks(B, PS.part[pi], t, &n_panel, &m, &k_lo);
-    const int nu = m * (m + 1) / 2 + m * PS.part[pi].nrb;
+    const int nu = part_update_tasks(m, PS.part[pi].nrb);
     if (u < nu) break;
     u -= nu;
   }
@@ -308,46 +318,60 @@ __global__ void __launch_bounds__(kStepThreads, 4) k_band_update(BandLayout B, c
   const BandPart& Q = PS.part[pi];
   const int j = Q.c0 + t;
   const double* Lprev = B.band + ((size_t)(j - 1) * nb1) * 1024;  // column j-1: block (j-1+o, j-1) at offset o
-  const int ntri = m * (m + 1) / 2;
-  const int g = lane >> 2, tq = lane & 3, tr = warp >> 1;
-  const double* A; const double* Lk; double* T; int lda, ldt, nrows = kNB;
+  const int ms = (m + 1) >> 1, ntri = ms * (ms + 1) / 2;
+  const int g = lane >> 2, tq = lane & 3, wr = warp >> 1, wc = warp & 1;
+  const int half = wr & 1;                        // which 16 rows of the row block
+  const double* A; const double* Lk; double* T; int lda, ldt;
   if (u < ntri) {
-    int a = (int)((sqrtf(8.0f * u + 1.0f) - 1.0f) * 0.5f);
-    while ((a + 1) * (a + 2) / 2 <= u) ++a;
-    while (a * (a + 1) / 2 > u) --a;
-    const int c = u - a * (a + 1) / 2;          // 0 <= c <= a < m
+    int sa = (int)((sqrtf(8.0f * u + 1.0f) - 1.0f) * 0.5f);
+    while ((sa + 1) * (sa + 2) / 2 <= u) ++sa;
+    while (sa * (sa + 1) / 2 > u) --sa;
+    const int sb = u - sa * (sa + 1) / 2;
+    const int a = 2 * sa + (wr >> 1), c = 2 * sb + wc;          // block row / column inside the trailing window, 0 <= c, a < m
+    if (a >= m || c >= m || c > a) return;                      // warp-uniform: outside the window or above the diagonal
     const int i = k_lo + a, k = k_lo + c;
     A = Lprev + (size_t)(i - (j - 1)) * 1024; lda = kNB;
     Lk = Lprev + (size_t)(k - (j - 1)) * 1024;
     T = B.band + ((size_t)k * nb1 + (i - k)) * 1024; ldt = kNB;
-  } else {                                      // border row block rb of block column k
+  } else {                                        // border row blocks (2 per task) x block columns (2 per task)
     u -= ntri;
-    const int k = k_lo + u / Q.nrb, rb = u % Q.nrb;
-    nrows = (rb == Q.nrb - 1) ? kBorder : kNB;
+    const int rs = u / ms, cs = u - rs * ms;
+    const int rb = 2 * rs + (wr >> 1), c = 2 * cs + wc;
+    if (rb >= Q.nrb || c >= m) return;
+    if (rb == Q.nrb - 1 && half * 16 >= kBorder) return;        // the last row block has 16 rows
+    const int k = k_lo + c;
     Lk = Lprev + (size_t)(k - (j - 1)) * 1024;
     A = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)(j - 1 - Q.c0) * kNB; lda = Q.ld;
     T = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)(k - Q.c0) * kNB; ldt = Q.ld;
   }
-  if (8 * tr >= nrows) return;   // warp-uniform
-  // every operand of the warp's two tiles (A rows, both L_k row groups, both target tiles) is requested before the first DMMA: one L2
-  // round trip per CTA instead of four dependent ones (the compiler cannot hoist the second tile's loads above the first tile's store)
-  const int tc0 = 2 * (warp & 1);
-  const double* pb = Lk + (size_t)(8 * tc0 + g) * kNB + 8 * tq;
-  double2* dst0 = reinterpret_cast<double2*>(T + (size_t)(8 * tr + g) * ldt + 8 * tc0 + 2 * tq);
-  double2* dst1 = dst0 + 4;
-  double a[8], b0[8], b1[8];
-  load_frag8(A + (size_t)(8 * tr + g) * lda + 8 * tq, a);
-  load_frag8(pb, b0); load_frag8(pb + 8 * kNB, b1);
-  double2 v0 = *dst0, v1 = *dst1;
-  // two accumulator chains per tile (even / odd k-steps): the DMMA latency chain is 4 deep instead of 8
-  double p0 = 0.0, p1 = 0.0, q0 = 0.0, q1 = 0.0, r0 = 0.0, r1 = 0.0, s0 = 0.0, s1 = 0.0;
+  const int r0 = 16 * half + g;
+  double a0[8], a1[8], b0[8], b1[8], b2[8], b3[8];
+  load_frag8(A + (size_t)r0 * lda + 8 * tq, a0);
+  load_frag8(A + (size_t)(r0 + 8) * lda + 8 * tq, a1);
+  const double* pb = Lk + (size_t)g * kNB + 8 * tq;
+  load_frag8(pb, b0); load_frag8(pb + 8 * kNB, b1); load_frag8(pb + 16 * kNB, b2); load_frag8(pb + 24 * kNB, b3);
+  double2* d0 = reinterpret_cast<double2*>(T + (size_t)r0 * ldt + 2 * tq);
+  double2* d1 = reinterpret_cast<double2*>(T + (size_t)(r0 + 8) * ldt + 2 * tq);
+  double2 v[2][4];
 #pragma unroll
-  for (int ks = 0; ks < 8; ks += 2) {
-    dmma884(p0, p1, a[ks], b0[ks]); dmma884(r0, r1, a[ks], b1[ks]);
-    dmma884(q0, q1, a[ks + 1], b0[ks + 1]); dmma884(s0, s1, a[ks + 1], b1[ks + 1]);
+  for (int h = 0; h < 4; ++h) { v[0][h] = d0[4 * h]; v[1][h] = d1[4 * h]; }
+  double acc[2][4][2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int h = 0; h < 4; ++h) acc[i][h][0] = acc[i][h][1] = 0.0;
+#pragma unroll
+  for (int ks = 0; ks < 8; ++ks) {
+    dmma884(acc[0][0][0], acc[0][0][1], a0[ks], b0[ks]); dmma884(acc[1][0][0], acc[1][0][1], a1[ks], b0[ks]);
+    dmma884(acc[0][1][0], acc[0][1][1], a0[ks], b1[ks]); dmma884(acc[1][1][0], acc[1][1][1], a1[ks], b1[ks]);
+    dmma884(acc[0][2][0], acc[0][2][1], a0[ks], b2[ks]); dmma884(acc[1][2][0], acc[1][2][1], a1[ks], b2[ks]);
+    dmma884(acc[0][3][0], acc[0][3][1], a0[ks], b3[ks]); dmma884(acc[1][3][0], acc[1][3][1], a1[ks], b3[ks]);
   }
-  v0.x -= p0 + q0; v0.y -= p1 + q1; v1.x -= r0 + s0; v1.y -= r1 + s1;
-  *dst0 = v0; *dst1 = v1;
+#pragma unroll
+  for (int h = 0; h < 4; ++h) {
+    v[0][h].x -= acc[0][h][0]; v[0][h].y -= acc[0][h][1]; v[1][h].x -= acc[1][h][0]; v[1][h].y -= acc[1][h][1];
+    d0[4 * h] = v[0][h]; d1[4 * h] = v[1][h];
+  }
 }
 
 // ---- partition border initialisation -------------------------------------------------------------------------------------------
@@ -916,7 +940,7 @@ static int enqueue_steps(ctba_problem* p, cudaStream_t st, const BandLayout& B, 
     for (int q = 0; q < PS.P; ++q) {
       int np, m, kl;
       part_tasks(B, PS.part[q], t, &np, &m, &kl);
-      gp += np; gu += m * (m + 1) / 2 + m * PS.part[q].nrb;
+      gp += np; gu += part_update_tasks(m, PS.part[q].nrb);
     }
     if (gp == 0 && gu == 0) continue;
     if (t > 0) { CTBA_CUDA(p, cudaStreamWaitEvent(st, evB, 0)); CTBA_CUDA(p, cudaStreamWaitEvent(s2, evA, 0)); }
