@@ -795,6 +795,10 @@ int band_partition_layout(int nbc, int nbw, int requested, int world, int nested
       while (P > world && !fits(P)) P -= world;
     } else if (!nested) {   // flat interface system: balance interior length against the sequential interface solve
       P = (int)lround(std::sqrt((double)nbc / (1.2 * nbw)));
+      // wide bands are throughput-bound, not latency-bound: one partition-step is ~8 ns * nbw^2 of DMMA work against a ~8.5 us
+      // launch-chain floor, and beyond ~2.5x that many concurrent partitions more partitions only add interface steps
+      // (measured on config 3, nbw = 20: P = 17 -> 34.5 ms, P = 6..8 -> 31 ms)
+      if (world == 1) P = std::min(P, std::max(2, (int)lround(2650.0 / ((double)nbw * nbw))));
       P = std::max(1, std::min(P, kMaxParts));
       if (world > 1) P = std::max(world, (P / world) * world);
       while (P > (world > 1 ? world : 1) && !fits(P)) P -= (world > 1 ? world : 1);
