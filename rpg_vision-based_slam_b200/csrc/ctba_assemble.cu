@@ -660,6 +660,8 @@ __device__ __forceinline__ void sym_mul_sym(const double S[6], const double B[6]
 
 // one (own observation, partner observation) product accumulated into the 6 x 6 pose block:
 //   acc += [H_a^T ; -I] (A_a Vi A_b) [H_b | -I]        with  H^T n = n x d,   (row of M) H = (row of M) x d
+__device__ __forceinline__ void schur_pair_m(const double Mm[9], double dax, double day, double daz, double dbx, double dby, double dbz,
+                                             double acc[36]);
 __device__ __forceinline__ void schur_pair(const double Aa[6], const double Vi[6], const double Ab[6], double dax, double day, double daz,
                                            double dbx, double dby, double dbz, double acc[36]) {
   double W[9], Mm[9];
@@ -671,6 +673,21 @@ __device__ __forceinline__ void schur_pair(const double Aa[6], const double Vi[6
 #pragma unroll
       for (int c = 0; c < 3; ++c) Mm[3 * r + c] = s[3 * r] * W[c] + s[3 * r + 1] * W[3 + c] + s[3 * r + 2] * W[6 + c];
   }
+  schur_pair_m(Mm, dax, day, daz, dbx, dby, dbz, acc);
+}
+// the common case: C_a = A_a Vi (3 x 3, precomputed once per own observation) so that M = C_a A_b costs one 3 x 3 product per partner
+__device__ __forceinline__ void schur_pair_c(const double Ca[9], const double Ab[6], double dax, double day, double daz, double dbx, double dby,
+                                             double dbz, double acc[36]) {
+  const double b[9] = {Ab[0], Ab[1], Ab[2], Ab[1], Ab[3], Ab[4], Ab[2], Ab[4], Ab[5]};
+  double Mm[9];
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int c = 0; c < 3; ++c) Mm[3 * r + c] = Ca[3 * r] * b[c] + Ca[3 * r + 1] * b[3 + c] + Ca[3 * r + 2] * b[6 + c];
+  schur_pair_m(Mm, dax, day, daz, dbx, dby, dbz, acc);
+}
+__device__ __forceinline__ void schur_pair_m(const double Mm[9], double dax, double day, double daz, double dbx, double dby, double dbz,
+                                             double acc[36]) {
   double Nn[18];   // [M H_b | M]
 #pragma unroll
   for (int r = 0; r < 3; ++r) {
@@ -691,10 +708,10 @@ __device__ __forceinline__ void schur_pair(const double Aa[6], const double Vi[6
   }
 }
 
-// CTA per frame.  Shared memory (structure of arrays over the frame's observations): A (6), d (3), Vi (6), {slot in the landmark's list, end
-// of the list (negative: the list has two observations in one frame)}, frame of the landmark's last observation.
+// CTA per frame.  Shared memory (structure of arrays over the frame's observations): C = A Vi (9), d (3), {slot in the landmark's list,
+// end of the list (negative: the list has two observations in one frame)}, frame of the landmark's last observation.
 constexpr int kFcThreads = 128;
-constexpr int kFcRows = 17;
+constexpr int kFcRows = 14;
 template <int N>
 __global__ void __launch_bounds__(kFcThreads, 3) k_frame_schur_c(int F, int T, const FramePose<N>* __restrict__ fps, const double* __restrict__ lm,
                                                                  const int32_t* __restrict__ obs_begin, const int32_t* __restrict__ o_lm,
@@ -709,17 +726,22 @@ __global__ void __launch_bounds__(kFcThreads, 3) k_frame_schur_c(int F, int T, c
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b0 = obs_begin[f], n = obs_begin[f + 1] - b0;
   const double px = fps[f].p_wb[0], py = fps[f].p_wb[1], pz = fps[f].p_wb[2];
-  int2* sPE = reinterpret_cast<int2*>(sO + 15 * (size_t)n_pad);
-  int* sLast = reinterpret_cast<int*>(sO + 16 * (size_t)n_pad);
+  int2* sPE = reinterpret_cast<int2*>(sO + 12 * (size_t)n_pad);
+  int* sLast = reinterpret_cast<int*>(sO + 13 * (size_t)n_pad);
   for (int i = threadIdx.x; i < n; i += kFcThreads) {
     const int a = b0 + i, l = o_lm[a];
     const double2* Ap = reinterpret_cast<const double2*>(Ao + 6 * (size_t)a);
     const double2* Vp = reinterpret_cast<const double2*>(Vi_all + 6 * (size_t)l);
     const double2 a0 = Ap[0], a1 = Ap[1], a2 = Ap[2], v0 = Vp[0], v1 = Vp[1], v2 = Vp[2];
     const int e = o_end[a];
-    sO[i] = a0.x; sO[n_pad + i] = a0.y; sO[2 * n_pad + i] = a1.x; sO[3 * n_pad + i] = a1.y; sO[4 * n_pad + i] = a2.x; sO[5 * n_pad + i] = a2.y;
-    sO[6 * n_pad + i] = lm[3 * (size_t)l] - px; sO[7 * n_pad + i] = lm[3 * (size_t)l + 1] - py; sO[8 * n_pad + i] = lm[3 * (size_t)l + 2] - pz;
-    sO[9 * n_pad + i] = v0.x; sO[10 * n_pad + i] = v0.y; sO[11 * n_pad + i] = v1.x; sO[12 * n_pad + i] = v1.y; sO[13 * n_pad + i] = v2.x; sO[14 * n_pad + i] = v2.y;
+    {
+      const double A6[6] = {a0.x, a0.y, a1.x, a1.y, a2.x, a2.y}, V6[6] = {v0.x, v0.y, v1.x, v1.y, v2.x, v2.y};
+      double C9[9];
+      sym_mul_sym(A6, V6, C9);
+#pragma unroll
+      for (int c = 0; c < 9; ++c) sO[c * n_pad + i] = C9[c];
+    }
+    sO[9 * n_pad + i] = lm[3 * (size_t)l] - px; sO[10 * n_pad + i] = lm[3 * (size_t)l + 1] - py; sO[11 * n_pad + i] = lm[3 * (size_t)l + 2] - pz;
     sPE[i] = make_int2(o_pos[a], e);
     sLast[i] = lm_frame[(e < 0 ? -e : e) - 1];
   }
@@ -731,8 +753,10 @@ __global__ void __launch_bounds__(kFcThreads, 3) k_frame_schur_c(int F, int T, c
     for (int e = 0; e < 48; ++e) acc[e] = 0.0;
     for (int i = threadIdx.x; i < n; i += kFcThreads) {
       const int l = o_lm[b0 + i];
-      const double A[6] = {sO[i], sO[n_pad + i], sO[2 * n_pad + i], sO[3 * n_pad + i], sO[4 * n_pad + i], sO[5 * n_pad + i]};
-      const double dx = sO[6 * n_pad + i], dy = sO[7 * n_pad + i], dz = sO[8 * n_pad + i];
+      const double2* Ap = reinterpret_cast<const double2*>(Ao + 6 * (size_t)(b0 + i));
+      const double2 q0 = Ap[0], q1 = Ap[1], q2 = Ap[2];
+      const double A[6] = {q0.x, q0.y, q1.x, q1.y, q2.x, q2.y};
+      const double dx = sO[9 * n_pad + i], dy = sO[10 * n_pad + i], dz = sO[11 * n_pad + i];
       auto apply = [&](const double v[3], double out[6]) {
         double w[3];
         symmul3(A, v, w);
@@ -783,16 +807,21 @@ __global__ void __launch_bounds__(kFcThreads, 3) k_frame_schur_c(int F, int T, c
     for (int e = 0; e < 36; ++e) acc[e] = 0.0;
     if (f2 < F) {
       const double ex = px - fps[f2].p_wb[0], ey = py - fps[f2].p_wb[1], ez = pz - fps[f2].p_wb[2];   // d_b = d_a + e
-      auto own = [&](int i, double Aa[6], double Vi[6], double d[3]) {
+      auto own = [&](int i, double Ca[9], double d[3]) {
 #pragma unroll
-        for (int c = 0; c < 6; ++c) { Aa[c] = sO[c * n_pad + i]; Vi[c] = sO[(9 + c) * n_pad + i]; }
-        d[0] = sO[6 * n_pad + i]; d[1] = sO[7 * n_pad + i]; d[2] = sO[8 * n_pad + i];
+        for (int c = 0; c < 9; ++c) Ca[c] = sO[c * n_pad + i];
+        d[0] = sO[9 * n_pad + i]; d[1] = sO[10 * n_pad + i]; d[2] = sO[11 * n_pad + i];
       };
       // general search (gaps in the track, or two observations of the landmark in one frame)
       auto slow = [&](int i, int pos, int lend) {
-        double Aa[6], Vi[6], d[3];
-        own(i, Aa, Vi, d);
         const int a = b0 + i;
+        double Aa[6], Vi[6];
+        const double d[3] = {sO[9 * n_pad + i], sO[10 * n_pad + i], sO[11 * n_pad + i]};
+        {
+          const int l = o_lm[a];
+#pragma unroll
+          for (int c = 0; c < 6; ++c) { Aa[c] = Ao[6 * (size_t)a + c]; Vi[c] = Vi_all[6 * (size_t)l + c]; }
+        }
         for (; pos < lend; ++pos) {
           const int fb = lm_frame[pos];
           if (fb > f2) break;
@@ -830,9 +859,9 @@ __global__ void __launch_bounds__(kFcThreads, 3) k_frame_schur_c(int F, int T, c
 #pragma unroll
         for (int u = 0; u < 2; ++u)
           if (bsel[u] >= 0) {
-            double Aa[6], Vi[6], d[3];
-            own(i0 + 32 * u, Aa, Vi, d);
-            schur_pair(Aa, Vi, Ab[u], d[0], d[1], d[2], d[0] + ex, d[1] + ey, d[2] + ez, acc);
+            double Ca[9], d[3];
+            own(i0 + 32 * u, Ca, d);
+            schur_pair_c(Ca, Ab[u], d[0], d[1], d[2], d[0] + ex, d[1] + ey, d[2] + ez, acc);
           }
       }
     }
