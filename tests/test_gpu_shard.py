@@ -127,3 +127,10 @@ def test_concurrent_independent_handles_are_deterministic(pkg, scene):
             np.testing.assert_allclose(o["iterations"][:, 0], s_ref["iterations"][:, 0], rtol=1e-8)
         for h in hs:
             h.close()
+
+
+def test_full_size_config2_sharded_over_two_ranks(pkg, scene):
+    """BASELINE configs[1] at full size (678 k observations, IMU + bias spline): the sharded pipeline (world 2, in-process communicator)
+    against the unsharded solve — same comparison as above, at the size the bench runs."""
+    sc = scene.config_scene(2)
+    _compare(pkg, sc, 2, 4)
