@@ -98,6 +98,16 @@ void host_free(void* p) {
 }
 }  // namespace ctba
 
+namespace ctba {
+// planar [entry][sample] -> row-major [sample][entry] for ctba_evaluate's documented layout
+__global__ void k_planar_to_rows(int n, int per, const double* __restrict__ in, double* __restrict__ out) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (size_t)n * per) return;
+  const size_t i = t / per, e = t % per;
+  out[t] = in[e * n + i];
+}
+}  // namespace ctba
+
 extern "C" {
 
 int ctba_create(int order, int64_t dt_ns, int64_t start_t_ns, int device, ctba_problem** out) {
@@ -474,8 +484,19 @@ int ctba_evaluate(ctba_problem* p, int kind, double* r_out, double* j_out) {
       }
       break;
     }
-    case CTBA_ACCEL: nres = 3 * p->i_s.size(); width = 6 * N + 16; d_r = p->ev.r_acc.p; d_J = p->ev.J_acc.p; break;
-    case CTBA_GYRO: nres = 3 * p->i_s.size(); width = 3 * N + 13; d_r = p->ev.r_gyr.p; d_J = p->ev.J_gyr.p; break;
+    case CTBA_ACCEL:
+    case CTBA_GYRO: {
+      const bool acc = kind == CTBA_ACCEL;
+      nres = 3 * p->i_s.size(); width = acc ? 6 * N + 16 : 3 * N + 13; d_r = acc ? p->ev.r_acc.p : p->ev.r_gyr.p;
+      if (j_out && nres) {     // the IMU Jacobians are stored planar on the device
+        CTBA_CUDA(p, dense.resize(nres * width));
+        const int n = (int)p->i_s.size(), per = 3 * (int)width;
+        k_planar_to_rows<<<(unsigned)(((size_t)n * per + 255) / 256), 256, 0, st>>>(n, per, acc ? p->ev.J_acc.p : p->ev.J_gyr.p, dense.p);
+        p->launches++;
+        d_J = dense.p;
+      }
+      break;
+    }
     case CTBA_GP: nres = 3 * p->g_s.size(); width = 6 * N + 5; d_r = p->ev.r_gp.p; d_J = p->ev.J_gp.p; break;
     case CTBA_BIAS: nres = 3 * p->b_s0.size(); width = 24; d_r = p->ev.r_bias.p; d_J = p->ev.J_bias.p; break;
     case CTBA_GRAVITY: nres = p->gravity_norm ? 1 : 0; width = 3; d_r = p->ev.r_grav.p; d_J = p->ev.J_grav.p; break;

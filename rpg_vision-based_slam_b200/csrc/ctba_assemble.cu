@@ -275,7 +275,7 @@ __global__ void __launch_bounds__(128) k_rows_accumulate(int kind, int n, int wi
 // and issues one atomic per entry and run instead of one per entry and sample (200 Hz IMU, 0.1 s knots: 20 x fewer atomics).
 constexpr int kSegThreads = 128, kSegBatch = 8;   // widest row: 6 N + 16 = 52 columns = 13 blocks of 4 -> 91 block pairs <= 128 threads
 template <int N>
-__global__ void __launch_bounds__(kSegThreads) k_rows_accumulate_seg(int kind, int nseg, const int32_t* __restrict__ seg_begin, int width,
+__global__ void __launch_bounds__(kSegThreads) k_rows_accumulate_seg(int kind, int nseg, const int32_t* __restrict__ seg_begin, int width, int planar_n,
                                                                      const double* __restrict__ J, const double* __restrict__ r,
                                                                      const int32_t* __restrict__ i_s, const int32_t* __restrict__ i_sb,
                                                                      const int32_t* __restrict__ node_of_knot,
@@ -327,9 +327,16 @@ __global__ void __launch_bounds__(kSegThreads) k_rows_accumulate_seg(int kind, i
   for (int b0 = i0; b0 < i1; b0 += kSegBatch) {
     const int nb = min(kSegBatch, i1 - b0);
     __syncthreads();
-    for (int e = tid; e < nb * 3 * wpad; e += kSegThreads) {
-      const int smp = e / (3 * wpad), rem = e - smp * 3 * wpad, rr = rem / wpad, c = rem - rr * wpad;
-      sJ[smp][rr * 64 + c] = c < width ? J[((size_t)(b0 + smp) * 3 + rr) * width + c] : 0.0;
+    if (planar_n > 0) {   // J[entry][sample] with planar_n samples (the IMU kernels' layout): sample index fastest, 64-byte pieces per entry
+      for (int e = tid; e < nb * 3 * wpad; e += kSegThreads) {
+        const int smp = e % nb, rc = e / nb, rr = rc / wpad, c = rc - rr * wpad;
+        sJ[smp][rr * 64 + c] = c < width ? J[(size_t)(rr * width + c) * planar_n + (b0 + smp)] : 0.0;
+      }
+    } else {
+      for (int e = tid; e < nb * 3 * wpad; e += kSegThreads) {
+        const int smp = e / (3 * wpad), rem = e - smp * 3 * wpad, rr = rem / wpad, c = rem - rr * wpad;
+        sJ[smp][rr * 64 + c] = c < width ? J[((size_t)(b0 + smp) * 3 + rr) * width + c] : 0.0;
+      }
     }
     if (tid < nb * 3) sR[tid / 3][tid % 3] = r[(size_t)b0 * 3 + tid];
     __syncthreads();
@@ -1567,19 +1574,19 @@ static int assemble_direct_T(ctba_problem* p) {
   }
   const int nI = (int)p->i_s.size(), nG = (int)p->g_s.size(), nB = (int)p->b_s0.size();
   if (nI > 0) {
-    k_rows_accumulate_seg<N><<<sd->n_imu_seg, kSegThreads, 0, st>>>(1, sd->n_imu_seg, sd->d_imu_seg.p, 6 * N + 16, p->ev.J_acc.p, p->ev.r_acc.p,
+    k_rows_accumulate_seg<N><<<sd->n_imu_seg, kSegThreads, 0, st>>>(1, sd->n_imu_seg, sd->d_imu_seg.p, 6 * N + 16, nI, p->ev.J_acc.p, p->ev.r_acc.p,
                                                                     p->d_i_s.p, p->d_i_sb.p, sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
-    k_rows_accumulate_seg<N><<<sd->n_imu_seg, kSegThreads, 0, st>>>(2, sd->n_imu_seg, sd->d_imu_seg.p, 3 * N + 13, p->ev.J_gyr.p, p->ev.r_gyr.p,
+    k_rows_accumulate_seg<N><<<sd->n_imu_seg, kSegThreads, 0, st>>>(2, sd->n_imu_seg, sd->d_imu_seg.p, 3 * N + 13, nI, p->ev.J_gyr.p, p->ev.r_gyr.p,
                                                                     p->d_i_s.p, p->d_i_sb.p, sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
     p->launches += 2;
   }
   if (nG > 0) {
-    k_rows_accumulate_seg<N><<<sd->n_gp_seg, kSegThreads, 0, st>>>(3, sd->n_gp_seg, sd->d_gp_seg.p, 6 * N + 5, p->ev.J_gp.p, p->ev.r_gp.p, p->d_g_s.p,
+    k_rows_accumulate_seg<N><<<sd->n_gp_seg, kSegThreads, 0, st>>>(3, sd->n_gp_seg, sd->d_gp_seg.p, 6 * N + 5, 0, p->ev.J_gp.p, p->ev.r_gp.p, p->d_g_s.p,
                                                                    nullptr, sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
     p->launches++;
   }
   if (!p->q_s.empty()) {
-    k_rows_accumulate_seg<N><<<sd->n_prior_seg, kSegThreads, 0, st>>>(6, sd->n_prior_seg, sd->d_prior_seg.p, 3 * N, p->ev.J_prior.p, p->ev.r_prior.p,
+    k_rows_accumulate_seg<N><<<sd->n_prior_seg, kSegThreads, 0, st>>>(6, sd->n_prior_seg, sd->d_prior_seg.p, 3 * N, 0, p->ev.J_prior.p, p->ev.r_prior.p,
                                                                       p->d_q_s.p, p->d_q_which.p, sd->d_node_of_knot.p, sd->d_node_of_bias.p, gm, H, sd->grad.p);
     p->launches++;
   }

@@ -116,9 +116,12 @@ __global__ void __launch_bounds__(64) k_imu(const __grid_constant__ Globals G, S
   const double gm[3] = {gyr[3 * (size_t)i], gyr[3 * (size_t)i + 1], gyr[3 * (size_t)i + 2]};
   double ra[3], rg[3];
   constexpr int WA = 6 * N + 16, WG = 3 * N + 13;
-  double* Ja = JAC ? J_a + (size_t)i * 3 * WA : nullptr;
-  double* Jg = JAC ? J_g + (size_t)i * 3 * WG : nullptr;
-  imu_sample_eval<N, JAC>(G, S.glb, kq, kp, ba, bg, st_s[i], kk[i], ub[i], am, gm, inv_a[i], inv_g[i], ra, rg, Ja, Jg);
+  // planar Jacobians J[entry][sample]: the 32 samples of a warp store 256 contiguous bytes per entry (row-major per sample made every
+  // lane write its own 1.2 KB region: 8-byte stores into 32 different sectors per instruction, 110 MB of DRAM writes for 72 MB of data)
+  double* Ja = JAC ? J_a + i : nullptr;
+  double* Jg = JAC ? J_g + i : nullptr;
+  (void)WA; (void)WG;
+  imu_sample_eval<N, JAC>(G, S.glb, kq, kp, ba, bg, st_s[i], kk[i], ub[i], am, gm, inv_a[i], inv_g[i], ra, rg, Ja, Jg, (size_t)n);
 #pragma unroll
   for (int c = 0; c < 3; ++c) { r_a[3 * (size_t)i + c] = ra[c]; r_g[3 * (size_t)i + c] = rg[c]; }
 }

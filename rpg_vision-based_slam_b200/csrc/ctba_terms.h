@@ -153,7 +153,8 @@ CTBA_HD void reproj_expand(const Globals& G, const double* glb, const FramePose<
 template <int N, bool JAC>
 CTBA_HD void imu_sample_eval(const Globals& G, const double* glb, const double* knot_q, const double* knot_p, const double* bias_a /*12*/,
                              const double* bias_g /*12*/, double st_s, double k, double u_bias, const double* acc_meas, const double* gyr_meas,
-                             double inv_std_a, double inv_std_g, double* r_a, double* r_g, double* J_a, double* J_g) {
+                             double inv_std_a, double inv_std_g, double* r_a, double* r_g, double* J_a, double* J_g, size_t ld = 1) {
+  // ld: distance between consecutive Jacobian entries of this sample (1: row-major per sample; n: planar [entry][sample], coalesced stores)
   const double t_corr = glb[GLB_T_CAM_IMU_CORR];
   const double st_corr = st_s - t_corr;
   const double u = (st_corr - k * G.dt_s) / G.dt_s;
@@ -200,9 +201,9 @@ CTBA_HD void imu_sample_eval(const Globals& G, const double* glb, const double* 
       for (int rr = 0; rr < 3; ++rr)
 #pragma unroll
         for (int cc = 0; cc < 3; ++cc) {
-          J_g[rr * WG + 3 * i + cc] = inv_std_g * sr.dW[i].a[3 * rr + cc];
-          J_a[rr * WA + 3 * i + cc] = inv_std_a * Ja.a[3 * rr + cc];
-          J_a[rr * WA + 3 * N + 3 * i + cc] = inv_std_a * c2[i] * Rt.a[3 * rr + cc];
+          J_g[(rr * WG + 3 * i + cc) * ld] = inv_std_g * sr.dW[i].a[3 * rr + cc];
+          J_a[(rr * WA + 3 * i + cc) * ld] = inv_std_a * Ja.a[3 * rr + cc];
+          J_a[(rr * WA + 3 * N + 3 * i + cc) * ld] = inv_std_a * c2[i] * Rt.a[3 * rr + cc];
         }
     }
 #pragma unroll
@@ -211,17 +212,17 @@ CTBA_HD void imu_sample_eval(const Globals& G, const double* glb, const double* 
       for (int rr = 0; rr < 3; ++rr)
 #pragma unroll
         for (int cc = 0; cc < 3; ++cc) {
-          J_g[rr * WG + 3 * N + 3 * i + cc] = (rr == cc) ? inv_std_g * cb[i] : 0.0;
-          J_a[rr * WA + 6 * N + 3 * i + cc] = (rr == cc) ? inv_std_a * cb[i] : 0.0;
+          J_g[(rr * WG + 3 * N + 3 * i + cc) * ld] = (rr == cc) ? inv_std_g * cb[i] : 0.0;
+          J_a[(rr * WA + 6 * N + 3 * i + cc) * ld] = (rr == cc) ? inv_std_a * cb[i] : 0.0;
         }
     const double wd[3] = {sr.wd.x, sr.wd.y, sr.wd.z};
     const double da[3] = {dadt.x, dadt.y, dadt.z};
 #pragma unroll
     for (int rr = 0; rr < 3; ++rr) {
 #pragma unroll
-      for (int cc = 0; cc < 3; ++cc) J_a[rr * WA + 6 * N + 12 + cc] = inv_std_a * Rt.a[3 * rr + cc];
-      J_g[rr * WG + 3 * N + 12] = -inv_std_g * wd[rr];
-      J_a[rr * WA + 6 * N + 15] = -inv_std_a * da[rr];
+      for (int cc = 0; cc < 3; ++cc) J_a[(rr * WA + 6 * N + 12 + cc) * ld] = inv_std_a * Rt.a[3 * rr + cc];
+      J_g[(rr * WG + 3 * N + 12) * ld] = -inv_std_g * wd[rr];
+      J_a[(rr * WA + 6 * N + 15) * ld] = -inv_std_a * da[rr];
     }
   }
 }
