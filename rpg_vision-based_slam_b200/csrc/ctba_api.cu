@@ -561,6 +561,7 @@ int ctba_set_option(ctba_problem* p, const char* name, double value) {
   if (!std::strcmp(name, "bench_no_termination")) { p->bench_no_termination = value != 0.0; return CTBA_OK; }
   if (!std::strcmp(name, "band_pdl")) { p->band_pdl = (int)value; return CTBA_OK; }
   if (!std::strcmp(name, "band_partitions")) { p->band_partitions = (int)value; return CTBA_OK; }
+  if (!std::strcmp(name, "schur_two_stage")) { p->schur_two_stage = value != 0.0; return CTBA_OK; }
   if (!std::strcmp(name, "schur_compact")) { p->schur_compact = value != 0.0; return CTBA_OK; }
   if (!std::strcmp(name, "band_nested")) { p->band_nested = value != 0.0; return CTBA_OK; }
   if (!std::strcmp(name, "band_graph")) { p->band_graph = value != 0.0; return CTBA_OK; }

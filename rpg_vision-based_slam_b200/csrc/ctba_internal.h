@@ -99,6 +99,7 @@ struct ctba_problem {
   int band_pdl = 2;        // programmatic dependent launch between the block-column kernels (0 off, 1 trigger at entry, 2 after staging)
   int band_partitions = 0; // time partitions of the band factorisation: 0 = automatic, k = force k (1 = plain sequential)
   int band_nested = 0;     // 1: interface systems are reduced recursively (odd-even over the separators); 0: one flat interface system
+  bool schur_two_stage = true;   // knot-space expansion of the Schur blocks through U(f, kc) (false: one pass over all frame pairs per knot pair)
   bool schur_compact = true;   // landmark Schur gather from the 6-double A blocks (false: from the 18-double Y / Z blocks)
   bool band_graph = true;  // replay the factor+solve launch sequence as a CUDA graph
 

@@ -76,6 +76,7 @@ struct SolverData {
   bool is_root = true;        // owns the global parameters
   DBuf<double> V0, gl;        // per landmark: 6 (xx xy xz yy yz zz), 3
   DBuf<double> Sp, Sb, rp;    // pose-space Schur blocks: F*(T+1)*36, F*42, F*6
+  DBuf<double> Uk;            // half-expanded blocks U(f, kc) = sum_f2 S(f, f2) D_f2[kc]: F*(KD+N)*36 (dense frame rates only)
   DBuf<double> jscale, jscale_lm;   // Jacobi scaling (fixed per Solve): n_pad+16, 3L
   DBuf<double> delta, delta_lm;     // step: n_pad+16, 3L
   DBuf<double> dpose;               // per frame 6: pose-space step
