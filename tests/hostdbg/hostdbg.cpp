@@ -54,4 +54,11 @@ int dbg_gp(int N, const double* cfg, const double* glb, const double* kq, const 
   else return -1;
   return 0;
 }
+int dbg_prior(int N, const double* cfg, const double* kq, const double* kp, int which, double u, const double* meas4, double is, double* r, double* J) {
+  Globals G = make_globals(N, cfg);
+  if (N == 4) prior_eval<4, true>(G, kq, kp, which, u, meas4, is, r, J);
+  else if (N == 6) prior_eval<6, true>(G, kq, kp, which, u, meas4, is, r, J);
+  else return -1;
+  return 0;
+}
 }

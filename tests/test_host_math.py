@@ -87,3 +87,31 @@ def test_terms_vs_oracle(oracle, scene, hostdbg, N, model, small):
         rp = np.zeros(3); Jp = np.zeros((3, 6 * N + 5))
         hostdbg.dbg_gp(N, P(S["cfg"]), P(S["glb"]), P(q), P(p), C.c_double(int(0.23 * S["dt_ns"]) * 1e-9), C.c_double(0.0), P(gpz), C.c_double(10.0), P(rp), P(Jp))
         assert relerr(rp, rp_o) < TOL and relerr(Jp, Jp_o) < TOL
+
+
+@pytest.mark.parametrize("N", [4, 6])
+@pytest.mark.parametrize("small", [False, True])
+def test_pose_prior_terms_vs_oracle(oracle, scene, hostdbg, N, small):
+    """prior_eval (ctba_terms.h; PositionCostFunctor / OrientationCostFunctor) compiled for the host against the oracle's Jet autodiff,
+    including a measurement that coincides with the spline (zero residual) and one half a turn away."""
+    rng = np.random.default_rng(900 + N + (3 if small else 0))
+    S = _setup(oracle, scene, N, 4, rng, small)
+    q, p = S["q"], S["p"]
+    for u in (0.0, 0.41, 0.999999):
+        t_ns = np.array([int(round(u * S["dt_ns"]))], dtype=np.int64)
+        uu = float(t_ns[0] % S["dt_ns"]) / float(S["dt_ns"])
+        smp = S["o"].sample(0, uu)
+        for k, dq in enumerate(([0.0, 0.0, 0.0, 1.0], Rot.from_rotvec(rng.normal(size=3) * 0.3).as_quat(), Rot.from_rotvec([0.0, 3.0, 0.5]).as_quat())):
+            meas_q = (Rot.from_quat(smp[:4]) * Rot.from_quat(dq)).as_quat()
+            meas_p = smp[4:7] + (0.0 if k == 0 else rng.normal(size=3) * 0.2)
+            o2 = oracle.OracleSpline(N, S["dt_ns"], 0)
+            o2.setKnots(q, p)
+            assert o2.addPositionMeasurements(t_ns, meas_p[None, :], 0.05) == 1
+            assert o2.addOrientationMeasurements(t_ns, meas_q[None, :], 0.02) == 1
+            r_o, J_o, _ = o2.evaluate(6)
+            for which, meas4, inv_std, sl in ((0, np.r_[meas_p, 0.0], 20.0, slice(0, 3)), (1, meas_q, 50.0, slice(3, 6))):
+                r_d = np.zeros(3); J_d = np.zeros((3, 3 * N))
+                assert hostdbg.dbg_prior(N, P(S["cfg"]), P(q), P(p), which, C.c_double(uu), P(np.ascontiguousarray(meas4, dtype=np.float64)),
+                                         C.c_double(inv_std), P(r_d), P(J_d)) == 0
+                np.testing.assert_allclose(r_d, r_o[sl], rtol=1e-10, atol=1e-11)
+                np.testing.assert_allclose(J_d, J_o[sl], rtol=1e-10, atol=1e-10)
