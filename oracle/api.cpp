@@ -89,6 +89,26 @@ int orc_add_imu(void* h, int n, const int64_t* t_ns, const double* acc, const do
 int orc_add_gp(void* h, int n, const int64_t* t_ns, const double* pos, double noise) { return ((SplineProblem*)h)->addGp(n, t_ns, pos, noise); }
 int orc_add_priors(void* h, int which, int n, const int64_t* t_ns, const double* meas, double noise) { return ((SplineProblem*)h)->addPriors(which, n, t_ns, meas, noise); }
 int orc_num_priors(void* h) { return (int)((SplineProblem*)h)->priors.size(); }
+// world alignment of a frozen spline (align_spline_to_global_frame.cpp:153-226)
+int orc_add_align(void* h, int n, const int64_t* t_ns, const double* pos, double noise) { return ((SplineProblem*)h)->addAlign(n, t_ns, pos, noise); }
+int orc_num_align(void* h) { return (int)((SplineProblem*)h)->align.size(); }
+int orc_set_alignment(void* h, const double* T_wg, const double* corr) {   // setWorldColmapTransformation :1825 (+ the corrections, for tests)
+  auto* p = (SplineProblem*)h;
+  for (int i = 0; i < 7; ++i) p->T_wg[i] = T_wg[i];
+  if (corr) { for (int i = 0; i < 4; ++i) p->R_wg_corr[i] = corr[i]; for (int i = 0; i < 3; ++i) p->p_wg_corr[i] = corr[4 + i]; }
+  p->built = false; return 0;
+}
+// T (7): getWorldColmapTransformation :1827-1834 = (R(T_wg) R_corr, t(T_wg) + p_corr);  corr (7): getWorldColmapTransformationCorr :1836-1840
+int orc_get_alignment(void* h, double* T, double* corr) {
+  auto* p = (SplineProblem*)h;
+  SO3<double> q0{p->T_wg[0], p->T_wg[1], p->T_wg[2], p->T_wg[3]}, qc{p->R_wg_corr[0], p->R_wg_corr[1], p->R_wg_corr[2], p->R_wg_corr[3]};
+  SO3<double> q = q0 * qc;
+  T[0] = q.x; T[1] = q.y; T[2] = q.z; T[3] = q.w;
+  for (int i = 0; i < 3; ++i) T[4 + i] = p->T_wg[4 + i] + p->p_wg_corr[i];
+  for (int i = 0; i < 4; ++i) corr[i] = p->R_wg_corr[i];
+  for (int i = 0; i < 3; ++i) corr[4 + i] = p->p_wg_corr[i];
+  return 0;
+}
 int orc_add_bias_cost(void* h, double freq_hz, double dt_s, double acc_rw, double gyr_rw) { return ((SplineProblem*)h)->addBiasCost(freq_hz, dt_s, acc_rw, gyr_rw); }
 int orc_add_gravity_norm(void* h) { auto* p = (SplineProblem*)h; p->gravity_norm = true; p->built = false; return 0; }
 int orc_relinearize(void* h) { ((SplineProblem*)h)->relinearize(); return 0; }

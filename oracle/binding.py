@@ -155,11 +155,11 @@ class OracleSpline:
 
     def jac_width(self, kind):
         N = self.N
-        return [6 * N + 10, 6 * N + 16, 3 * N + 13, 6 * N + 5, 24, 3, 3 * N][kind]
+        return [6 * N + 10, 6 * N + 16, 3 * N + 13, 6 * N + 5, 24, 3, 3 * N, 6 * N + 11][kind]   # 7: world alignment, all blocks of the functor (knots first)
 
     def evaluate(self, kind, jac=True):
         c = self.counts()
-        nres = [2 * c["obs"], 3 * c["accel"], 3 * c["gyro"], 3 * c["gp"], 3 * c["bias"], c["gravity"], 3 * self.numPriors()][kind]
+        nres = [2 * c["obs"], 3 * c["accel"], 3 * c["gyro"], 3 * c["gp"], 3 * c["bias"], c["gravity"], 3 * self.numPriors(), 3 * self.numAlignmentMeasurements()][kind]
         r = np.zeros(nres)
         J = np.zeros((nres, self.jac_width(kind))) if jac else None
         aux = np.zeros(1)
@@ -184,6 +184,23 @@ class OracleSpline:
 
     def numPriors(self):
         return self.L.orc_num_priors(self.h)
+
+    # ---- alignment of a frozen spline to the world frame (align_spline_to_global_frame.cpp) ----
+    def setWorldColmapTransformation(self, T_wg, corr=None):
+        T = _d(T_wg); c = _d(corr) if corr is not None else None
+        self.L.orc_set_alignment(self.h, T.ctypes.data_as(C.c_void_p), c.ctypes.data_as(C.c_void_p) if c is not None else None)
+
+    def addWorldColmapAlignmentMeasurements(self, t_ns, pos, noise):
+        t = np.ascontiguousarray(t_ns, dtype=np.int64); m = _d(pos)
+        return self.L.orc_add_align(self.h, len(t), t.ctypes.data_as(C.c_void_p), m.ctypes.data_as(C.c_void_p), C.c_double(noise))
+
+    def numAlignmentMeasurements(self):
+        return self.L.orc_num_align(self.h)
+
+    def getWorldColmapTransformation(self):
+        T = np.zeros(7); c = np.zeros(7)
+        self.L.orc_get_alignment(self.h, T.ctypes.data_as(C.c_void_p), c.ctypes.data_as(C.c_void_p))
+        return T, c
 
     def optimize(self, max_num_iterations, num_threads=1):
         s = np.zeros(6)

@@ -9,6 +9,7 @@
 //   BiasCostFunctor<4>                  include/optimization/continuous_time/imu_cost_functor.h:351-369
 //   GlobalPositionSensorCostFunctor<N>  include/optimization/continuous_time/global_position_cost_functor.h:45-73
 //   GravityNormCostFunctor              include/optimization/gravity_norm_cost_functor.h:26-39
+//   GlobalPositionSensorWithAlignmentCorrectionCostFunctor<N>   global_position_cost_functor.h:82-150
 // Parameter-block order inside each functor is the order wired by bspline_so3r3.h
 // (:596-610, :685-694, :928-939, :1007-1028, :771-788, :1222-1224).
 #pragma once
@@ -164,6 +165,45 @@ struct GlobalPositionSensorCostFunctor {
     M3<T> sR;
     for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) sR.m[i][j] = s * Rwb.m[i][j];
     V3<T> p_w_p = mul(sR, p_b_p) + p_w_b;
+    r[0] = inv_std * (p_w_p.x - meas[0]);
+    r[1] = inv_std * (p_w_p.y - meas[1]);
+    r[2] = inv_std * (p_w_p.z - meas[2]);
+    return true;
+  }
+};
+
+// global_position_cost_functor.h:82-150 — parameter blocks: N rotation knots, N position knots, t_corr, scale_corr, R_w_g_corr, p_w_g_corr, p_b_p
+// (bspline_so3r3.h:1151-1188).  Eigen evaluates `s * R_w_g * p_g_b` and `s * R_w_b * p_b_p` left to right: the matrix is scaled first.
+template <int N>
+struct GlobalPositionSensorWithAlignmentCorrectionCostFunctor {
+  double meas[3];
+  double q_wg[4], p_wg0[3];   // T_w_g
+  double scale, st_s, k, dt_s, inv_dt, inv_std;
+  template <class T>
+  bool operator()(T const* const* sKnots, T* r) const {
+    T t_corr_s = sKnots[2 * N][0];
+    T st_corr_s = st_s - t_corr_s;
+    T u = (st_corr_s - k * dt_s) / dt_s;
+    SO3<T> R_g_b;
+    SplineHelper<N>::template evaluate_lie<T, T>(sKnots, u, inv_dt, &R_g_b);
+    V3<T> p_g_b;
+    SplineHelper<N>::template evaluate<T, 0, T>(sKnots + N, u, inv_dt, &p_g_b);
+    T scale_corr = sKnots[2 * N + 1][0];
+    T s = scale + scale_corr;
+    SO3<T> R_w_g_corr = SO3<T>::fromRaw(sKnots[2 * N + 2]);
+    V3<T> p_w_g_corr{sKnots[2 * N + 3][0], sKnots[2 * N + 3][1], sKnots[2 * N + 3][2]};
+    V3<T> p_b_p{sKnots[2 * N + 4][0], sKnots[2 * N + 4][1], sKnots[2 * N + 4][2]};
+    SO3<double> q0{q_wg[0], q_wg[1], q_wg[2], q_wg[3]};
+    M3<double> R0d = q0.matrix();
+    M3<T> R0;
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) R0.m[i][j] = T(R0d.m[i][j]);
+    M3<T> R_w_g = mul(R0, R_w_g_corr.matrix());
+    V3<T> p_w_g{T(p_wg0[0]) + p_w_g_corr.x, T(p_wg0[1]) + p_w_g_corr.y, T(p_wg0[2]) + p_w_g_corr.z};
+    M3<T> R_w_b = mul(R_w_g, R_g_b.matrix());
+    M3<T> sRwg, sRwb;
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) { sRwg.m[i][j] = s * R_w_g.m[i][j]; sRwb.m[i][j] = s * R_w_b.m[i][j]; }
+    V3<T> p_w_b = mul(sRwg, p_g_b) + p_w_g;
+    V3<T> p_w_p = mul(sRwb, p_b_p) + p_w_b;
     r[0] = inv_std * (p_w_p.x - meas[0]);
     r[1] = inv_std * (p_w_p.y - meas[1]);
     r[2] = inv_std * (p_w_p.z - meas[2]);

@@ -31,7 +31,7 @@ struct ParamBlock {
 };
 
 struct ResidualBlock {
-  int kind;   // 0 reproj frame, 1 accel, 2 gyro, 3 gp, 4 bias, 5 gravity
+  int kind;   // 0 reproj frame, 1 accel, 2 gyro, 3 gp, 4 bias, 5 gravity, 6 pose prior, 7 world alignment
   int index;  // index inside its kind
   int nres;
   double cauchy_a;  // 0 => no loss
@@ -163,6 +163,10 @@ struct SplineProblem {
   std::vector<ImuMeas> accel, gyro;
   std::vector<GpMeas> gp;
   std::vector<PriorMeas> priors;
+  std::vector<GpMeas> align;              // addWorldColmapAlignmentMeasurement
+  double T_wg[7] = {0, 0, 0, 1, 0, 0, 0};   // T_w_g_ (q x y z w | p), :1968
+  double R_wg_corr[4] = {0, 0, 0, 1}, p_wg_corr[3] = {0, 0, 0};
+  double align_cauchy_a = 0.10;           // :1189
   std::vector<BiasMeas> bias;
   bool gravity_norm = false;
 
@@ -305,6 +309,25 @@ struct SplineProblem {
     return added;
   }
 
+  // addWorldColmapAlignmentMeasurement :1121-1211 (same window arithmetic as addGlobalPosMeasurement)
+  int addAlign(int n, const int64_t* t_ns, const double* pos, double noise) {
+    int added = 0;
+    for (int i = 0; i < n; ++i) {
+      int64_t t_s_gp_init_ns = static_cast<int64_t>(t_s_gp_s * 1e9);
+      int64_t st_ns = (t_ns[i] - start_t_ns - t_s_gp_init_ns);
+      double st_s = st_ns * 1e-9;
+      if (st_ns < 0) continue;
+      int64_t s = st_ns / dt_ns;
+      int k_int = (int)(st_ns / dt_ns);
+      if (size_t(s + N) > numKnots()) continue;
+      GpMeas m; m.s = s; m.st_s = st_s; m.k = (double)k_int; m.inv_std = 1.0 / noise;
+      for (int c = 0; c < 3; ++c) m.meas[c] = pos[3 * i + c];
+      align.push_back(m); ++added;
+    }
+    built = false;
+    return added;
+  }
+
   // Wire everything into the MiniProblem in the reference driver's order
   // (src/optimize_continuous_time.cpp:497, 526, 567-601): gravity norm, SO3 parameterisations,
   // GP, accel+gyro interleaved, frames, bias cost.
@@ -334,6 +357,25 @@ struct SplineProblem {
         b.eval = [f](const std::vector<const double*>& p, const std::vector<int>& sz, double* r, double* j) { dynamic_autodiff(f, p, sz, 3, r, j); };
       }
       mp.blocks.push_back(std::move(b));
+    }
+    if (!align.empty()) mp.AddParameterBlock(R_wg_corr, 4, true);   // addRotationLocalParametrization (align_spline_to_global_frame.cpp:194)
+    for (size_t i = 0; i < align.size(); ++i) {
+      const GpMeas& m = align[i];
+      ResidualBlock b; b.kind = 7; b.index = (int)i; b.nres = 3; b.cauchy_a = align_cauchy_a;
+      for (int j = 0; j < NN; ++j) b.pb.push_back(mp.AddParameterBlock(&so3[4 * (m.s + j)], 4, true));
+      for (int j = 0; j < NN; ++j) b.pb.push_back(mp.AddParameterBlock(&r3[3 * (m.s + j)], 3));
+      b.pb.push_back(mp.AddParameterBlock(&t_s_gp_corr_s, 1));
+      b.pb.push_back(mp.AddParameterBlock(&scale_corr, 1));
+      b.pb.push_back(mp.AddParameterBlock(R_wg_corr, 4, true));
+      b.pb.push_back(mp.AddParameterBlock(p_wg_corr, 3));
+      b.pb.push_back(mp.AddParameterBlock(p_bp, 3));
+      GlobalPositionSensorWithAlignmentCorrectionCostFunctor<NN> f{{m.meas[0], m.meas[1], m.meas[2]}, {T_wg[0], T_wg[1], T_wg[2], T_wg[3]},
+                                                                   {T_wg[4], T_wg[5], T_wg[6]}, scale, m.st_s, m.k, dt_s, inv_dt, m.inv_std};
+      b.eval = [f](const std::vector<const double*>& p, const std::vector<int>& sz, double* r, double* j) { dynamic_autodiff(f, p, sz, 3, r, j); };
+      mp.blocks.push_back(std::move(b));
+      for (int j = 0; j < NN; ++j) { mp.SetParameterBlockConstant(&so3[4 * (m.s + j)]); mp.SetParameterBlockConstant(&r3[3 * (m.s + j)]); }   // :1191-1199
+      if (!optimize_p_bp) mp.SetParameterBlockConstant(p_bp);
+      if (!optimize_t_offset_s_gs) mp.SetParameterBlockConstant(&t_s_gp_corr_s);
     }
     for (size_t i = 0; i < gp.size(); ++i) {
       const GpMeas& m = gp[i];

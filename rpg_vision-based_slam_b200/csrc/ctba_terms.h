@@ -7,6 +7,8 @@
 //   gp_sample_eval    : GlobalPositionSensorCostFunctor (global_position_cost_functor.h:45-73)
 //   bias_cost_eval    : BiasCostFunctor<4> (imu_cost_functor.h:351-369)
 //   gravity_eval      : GravityNormCostFunctor (gravity_norm_cost_functor.h:26-39)
+//   prior_eval        : PositionCostFunctor / OrientationCostFunctor (position_cost_functor.h, orientation_cost_functor.h)
+//   align_eval        : GlobalPositionSensorWithAlignmentCorrectionCostFunctor (global_position_cost_functor.h:82-150)
 // Tangent conventions: SO(3) blocks use the right perturbation q <- q*exp(delta)
 // (lie_local_parametrization.h:34-41); everything else is Euclidean.
 #pragma once
@@ -335,6 +337,63 @@ CTBA_HD void prior_eval(const Globals& G, const double* knot_q, const double* kn
       for (int rr = 0; rr < 3; ++rr)
 #pragma unroll
         for (int cc = 0; cc < 3; ++cc) J[rr * W + 3 * i + cc] = inv_std * Ji.a[3 * rr + cc];
+    }
+  }
+}
+
+// Alignment of a FROZEN spline (expressed in a gauge frame g, e.g. COLMAP's) to the world frame of the global position sensor:
+// GlobalPositionSensorWithAlignmentCorrectionCostFunctor (global_position_cost_functor.h:82-150) as wired by
+// addWorldColmapAlignmentMeasurement (bspline_so3r3.h:1121-1211: every knot block is set constant).
+//   p_w_p = s R_wg (R_gb(u) p_bp + p_gb(u)) + p_wg,  R_wg = R(T_wg) R_corr,  p_wg = t(T_wg) + p_corr,  s = scale + scale_corr,
+//   u = (st_s - t_corr - k dt) / dt.
+// State x (12): [t_corr | scale_corr | R_corr x y z w | p_corr | p_bp];  tangent (11): [t | scale | R_corr right tangent | p_corr | p_bp].
+// e = p_w_p - meas and J = de/d(tangent) are returned UNWEIGHTED (the caller applies inv_std and the loss).
+enum { AL_T = 0, AL_SCALE = 1, AL_R = 2, AL_P = 6, AL_PBP = 9, AL_STATE = 12 };
+enum { AT_T = 0, AT_SCALE = 1, AT_R = 2, AT_P = 5, AT_PBP = 8, AT_SIZE = 11 };
+template <int N, bool JAC>
+CTBA_HD void align_eval(const Globals& G, const double* T_wg /*q x y z w | p*/, const double* x, const double* knot_q, const double* knot_p,
+                        double st_s, double k, const double* meas, double* e, double* J) {
+  const double st_corr = st_s - x[AL_T];
+  const double u = (st_corr - k * G.dt_s) / G.dt_s;
+  So3SplineResult<N> sr;
+  so3_spline_eval<N, JAC, false, false>(G.tb, knot_q, u, G.inv_dt, &sr);
+  double c[N];
+  spline_coeffs<N>(G.tb.blend, G.tb.base, 0, 1.0, u, c);
+  v3 p{0, 0, 0};
+#pragma unroll
+  for (int i = 0; i < N; ++i) { p.x += c[i] * knot_p[3 * i]; p.y += c[i] * knot_p[3 * i + 1]; p.z += c[i] * knot_p[3 * i + 2]; }
+  const double s = G.scale + x[AL_SCALE];
+  const m3 R0 = quat_matrix(quat{T_wg[0], T_wg[1], T_wg[2], T_wg[3]});
+  const m3 Rc = quat_matrix(quat{x[AL_R], x[AL_R + 1], x[AL_R + 2], x[AL_R + 3]});
+  const m3 Rwg = mul(R0, Rc);
+  const m3 Rgb = quat_matrix(sr.q);
+  const v3 pbp{x[AL_PBP], x[AL_PBP + 1], x[AL_PBP + 2]};
+  const v3 xg = mul(Rgb, pbp) + p;             // antenna in the gauge frame
+  const v3 y = mul(Rwg, xg);
+  e[0] = s * y.x + (T_wg[4] + x[AL_P]) - meas[0];
+  e[1] = s * y.y + (T_wg[5] + x[AL_P + 1]) - meas[1];
+  e[2] = s * y.z + (T_wg[6] + x[AL_P + 2]) - meas[2];
+  if (JAC) {
+    double c1[N];
+    spline_coeffs<N>(G.tb.blend, G.tb.base, 1, G.inv_dt, u, c1);
+    v3 vel{0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < N; ++i) { vel.x += c1[i] * knot_p[3 * i]; vel.y += c1[i] * knot_p[3 * i + 1]; vel.z += c1[i] * knot_p[3 * i + 2]; }
+    const v3 xdot = mul(Rgb, cross(sr.w, pbp)) + vel;   // d xg / d time
+    const v3 dt = mul(Rwg, xdot);
+    const m3 B = mul(Rwg, hat(xg));                     // d(R_wg Exp(d) xg)/dd = -R_wg [xg]x
+    const m3 RR = mul(Rwg, Rgb);
+    const double dt3[3] = {dt.x, dt.y, dt.z}, y3[3] = {y.x, y.y, y.z};
+#pragma unroll
+    for (int rr = 0; rr < 3; ++rr) {
+      J[rr * AT_SIZE + AT_T] = -s * dt3[rr];
+      J[rr * AT_SIZE + AT_SCALE] = y3[rr];
+#pragma unroll
+      for (int cc = 0; cc < 3; ++cc) {
+        J[rr * AT_SIZE + AT_R + cc] = -s * B.a[3 * rr + cc];
+        J[rr * AT_SIZE + AT_P + cc] = (rr == cc) ? 1.0 : 0.0;
+        J[rr * AT_SIZE + AT_PBP + cc] = s * RR.a[3 * rr + cc];
+      }
     }
   }
 }

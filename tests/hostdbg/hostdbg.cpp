@@ -61,4 +61,12 @@ int dbg_prior(int N, const double* cfg, const double* kq, const double* kp, int 
   else return -1;
   return 0;
 }
+int dbg_align(int N, const double* cfg, const double* T_wg, const double* x12, const double* kq, const double* kp, double st_s, double k,
+              const double* meas, double* e, double* J) {
+  Globals G = make_globals(N, cfg);
+  if (N == 4) align_eval<4, true>(G, T_wg, x12, kq, kp, st_s, k, meas, e, J);
+  else if (N == 6) align_eval<6, true>(G, T_wg, x12, kq, kp, st_s, k, meas, e, J);
+  else return -1;
+  return 0;
+}
 }

@@ -115,3 +115,35 @@ def test_pose_prior_terms_vs_oracle(oracle, scene, hostdbg, N, small):
                                          C.c_double(inv_std), P(r_d), P(J_d)) == 0
                 np.testing.assert_allclose(r_d, r_o[sl], rtol=1e-10, atol=1e-11)
                 np.testing.assert_allclose(J_d, J_o[sl], rtol=1e-10, atol=1e-10)
+
+
+@pytest.mark.parametrize("N", [4, 6])
+@pytest.mark.parametrize("small", [False, True])
+def test_world_alignment_term_vs_oracle(oracle, scene, hostdbg, N, small):
+    """align_eval (ctba_terms.h; GlobalPositionSensorWithAlignmentCorrectionCostFunctor over the 11 free tangent directions of the
+    alignment problem) compiled for the host against the oracle's Jet autodiff; the oracle's Jacobian w.r.t. the (constant) knots is ignored."""
+    rng = np.random.default_rng(1300 + N + (3 if small else 0))
+    S = _setup(oracle, scene, N, 4, rng, small)
+    q, p = S["q"], S["p"]
+    T_wg = np.r_[Rot.from_rotvec([0.4, -1.1, 2.0]).as_quat(), [12.0, -7.0, 3.5]]
+    for t_corr, ident in ((0.0, True), (0.004, False), (-0.003, False)):
+        corr = np.r_[[0.0, 0.0, 0.0, 1.0] if ident else Rot.from_rotvec(rng.normal(size=3) * 0.2).as_quat(), rng.normal(size=3) * (0.0 if ident else 0.5)]
+        scale_corr = 0.0 if ident else 0.07
+        o2 = oracle.OracleSpline(N, S["dt_ns"], 0)
+        o2.setKnots(q, p)
+        o2.setGlobals(S["scale"], S["p_bp"], S["g"], 0.0)
+        c10 = np.zeros(10); c10[0] = scale_corr; c10[4] = 1.0; c10[9] = t_corr
+        o2.setCorrections(c10)
+        o2.setWorldColmapTransformation(T_wg, corr)
+        t_ns = np.array([int(0.45 * S["dt_ns"])], dtype=np.int64)
+        meas = rng.normal(size=(1, 3)) * 3.0
+        assert o2.addWorldColmapAlignmentMeasurements(t_ns, meas, 0.25) == 1
+        r_o, J_o, _ = o2.evaluate(7)
+        x12 = np.r_[t_corr, scale_corr, corr[:4], corr[4:], S["p_bp"]]
+        e_d = np.zeros(3); J_d = np.zeros((3, 11))
+        st_s = float(t_ns[0]) * 1e-9
+        assert hostdbg.dbg_align(N, P(S["cfg"]), P(T_wg), P(np.ascontiguousarray(x12)), P(q), P(p), C.c_double(st_s), C.c_double(0.0),
+                                 P(np.ascontiguousarray(meas[0])), P(e_d), P(J_d)) == 0
+        np.testing.assert_allclose(4.0 * e_d, r_o, rtol=1e-10, atol=1e-11)
+        np.testing.assert_allclose(4.0 * J_d, J_o[:, 6 * N:], rtol=1e-10, atol=1e-10)
+        assert np.abs(J_o[:, 6 * N:]).min(axis=0).max() > 0      # every one of the 11 directions is exercised
