@@ -3,6 +3,7 @@
 // checked against the oracle on a GPU-less machine.  Not part of the product library.
 #include <cstring>
 #include "../../rpg_vision-based_slam_b200/csrc/ctba_terms.h"
+#include "../../rpg_vision-based_slam_b200/csrc/ctba_align.h"
 using namespace ctba;
 
 static Globals make_globals(int N, const double* cfg) {
@@ -29,7 +30,48 @@ static void frame_reproj(const Globals& G, const double* glb, const double* kq, 
   }
 }
 
+// Serial host backend of align_lm_loop (ctba_align.h): the same per-sample accumulation and LM step functions as the kernels of
+// ctba_align.cu, summed in measurement order.
+template <int N>
+struct HostAlignBackend {
+  Globals G; const double* T_wg; const double *kq, *kp; int n; const int32_t* s; const double *st_s, *k, *meas, *inv_std;
+  double cauchy_b; unsigned mask;
+  double x[AL_STATE], cand[AL_STATE], sys[2][AS_SIZE], jscale[AT_SIZE]; int cur = 0;
+  int evaluate(bool candidate, double* cost) {
+    double* S = sys[candidate ? 1 - cur : cur];
+    for (int i = 0; i < AS_SIZE; ++i) S[i] = 0.0;
+    for (int i = 0; i < n; ++i)
+      align_sample_accumulate<N>(G, T_wg, candidate ? cand : x, kq + 4 * (size_t)s[i], kp + 3 * (size_t)s[i], st_s[i], k[i], meas + 3 * (size_t)i,
+                                 inv_std[i], cauchy_b, true, S);
+    *cost = S[AS_COST];
+    return 0;
+  }
+  int step(double radius, bool init_jscale, double* sc) { align_lm_step(sys[cur], x, mask, radius, init_jscale, jscale, cand, sc); return 0; }
+  void accept() { std::memcpy(x, cand, sizeof(x)); cur = 1 - cur; }
+};
+template <int N>
+static int align_lm_host(const Globals& G, const double* T_wg, double* x12, unsigned mask, const double* kq, const double* kp, int n, const int32_t* s,
+                         const double* st_s, const double* k, const double* meas, const double* inv_std, double cauchy_a, int max_iters,
+                         ctba_summary* out, double* sys_out) {
+  HostAlignBackend<N> be;
+  be.G = G; be.T_wg = T_wg; be.kq = kq; be.kp = kp; be.n = n; be.s = s; be.st_s = st_s; be.k = k; be.meas = meas; be.inv_std = inv_std;
+  be.cauchy_b = cauchy_a * cauchy_a; be.mask = mask;
+  std::memcpy(be.x, x12, sizeof(be.x));
+  int rc = align_lm_loop(be, max_iters, false, out);
+  std::memcpy(x12, be.x, sizeof(be.x));
+  if (sys_out) std::memcpy(sys_out, be.sys[be.cur], sizeof(double) * AS_SIZE);
+  return rc;
+}
+
 extern "C" {
+int dbg_align_lm(int N, const double* cfg, const double* T_wg, double* x12, unsigned mask, const double* kq, const double* kp, int n, const int32_t* s,
+                 const double* st_s, const double* k, const double* meas, const double* inv_std, double cauchy_a, int max_iters,
+                 ctba_summary* out, double* sys_out) {
+  Globals G = make_globals(N, cfg);
+  if (N == 4) return align_lm_host<4>(G, T_wg, x12, mask, kq, kp, n, s, st_s, k, meas, inv_std, cauchy_a, max_iters, out, sys_out);
+  if (N == 6) return align_lm_host<6>(G, T_wg, x12, mask, kq, kp, n, s, st_s, k, meas, inv_std, cauchy_a, max_iters, out, sys_out);
+  return -1;
+}
 int dbg_frame_reproj(int N, const double* cfg, const double* glb, const double* kq, const double* kp, double u, int n, const double* pw,
                      const double* uv, double inv_std, double* r, double* J) {
   Globals G = make_globals(N, cfg);
