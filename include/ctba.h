@@ -31,7 +31,7 @@ enum {
 };
 
 /* residual kinds (ctba_evaluate) */
-enum { CTBA_REPROJ = 0, CTBA_ACCEL = 1, CTBA_GYRO = 2, CTBA_GP = 3, CTBA_BIAS = 4, CTBA_GRAVITY = 5, CTBA_PRIOR = 6 };
+enum { CTBA_REPROJ = 0, CTBA_ACCEL = 1, CTBA_GYRO = 2, CTBA_GP = 3, CTBA_BIAS = 4, CTBA_GRAVITY = 5, CTBA_PRIOR = 6, CTBA_ALIGN = 7 };
 
 /* BSplineSO3R3<N>::BSplineSO3R3(time_interval_ns, start_time_ns)      bspline_so3r3.h:75-117
  * order N in {4,6}; `device` = CUDA ordinal (-1: planning-only handle — host problem assembly and ctba_shard_plan work,
@@ -93,6 +93,19 @@ int ctba_add_gp(ctba_problem* p, int n, const int64_t* t_ns, const double* pos /
 int ctba_add_position_measurements(ctba_problem* p, int n, const int64_t* t_ns, const double* pos /*3n*/, double noise);
 int ctba_add_orientation_measurements(ctba_problem* p, int n, const int64_t* t_ns, const double* quat_xyzw /*4n*/, double noise);
 int ctba_num_priors(const ctba_problem* p);
+/* ---- align_spline_to_global_frame (src/align_spline_to_global_frame.cpp:153-226): a FROZEN spline expressed in a gauge frame g is aligned
+ * to the world frame of the global position sensor.  Unknowns: scale_corr, R_w_g_corr, p_w_g_corr, and p_bp / t_s_gp_corr when their
+ * optimise flags are set; residual GlobalPositionSensorWithAlignmentCorrectionCostFunctor (global_position_cost_functor.h:82-150),
+ * CauchyLoss(0.10) per measurement.  A handle that holds alignment measurements solves THIS problem in ctba_solve (every knot constant,
+ * bspline_so3r3.h:1191-1199); mixing them with other measurement kinds is CTBA_E_STATE.
+ * setWorldColmapTransformation(T_w_g)                                    bspline_so3r3.h:1825     T = qx qy qz qw tx ty tz;
+ * corr7 = R_w_g_corr | p_w_g_corr (NULL: unchanged; only needed to evaluate at a non-default linearisation point) */
+int ctba_set_world_alignment(ctba_problem* p, const double* T_wg7, const double* corr7);
+/* getWorldColmapTransformation / getWorldColmapTransformationCorr       bspline_so3r3.h:1827-1840  (either pointer may be NULL) */
+int ctba_get_world_alignment(ctba_problem* p, double* T_wg7, double* corr7);
+/* addWorldColmapAlignmentMeasurement for n samples; returns the number accepted   bspline_so3r3.h:1121-1211 */
+int ctba_add_alignment_measurements(ctba_problem* p, int n, const int64_t* t_ns, const double* pos /*3n*/, double noise);
+int ctba_num_alignment_measurements(const ctba_problem* p);
 /* addImuBiasCost(bias_err_freq_hz, bias_err_dt_s); random walks from ImuCalibration   bspline_so3r3.h:706-792 */
 int ctba_add_bias_cost(ctba_problem* p, double freq_hz, double dt_s, double acc_random_walk, double gyro_random_walk);
 /* addGravityNormError()                                                  bspline_so3r3.h:1213-1227 */
@@ -110,6 +123,7 @@ int ctba_counts(ctba_problem* p, int64_t* counts);
  *   CTBA_BIAS    per block       3 x 24     : [4 knots @s0 | 4 knots @s1]
  *   CTBA_GRAVITY                 1 x 3
  *   CTBA_PRIOR                   3 x 3N   (position prior: the position knots; orientation prior: the right tangents of the rotation knots)
+ *   CTBA_ALIGN   per sample      3 x 11     : [t_s_gp_corr | scale_corr | R_w_g_corr 3 | p_w_g_corr 3 | p_bp 3]   (the knots are constant)
  * residuals / jacobians may be NULL.  Returns the number of residuals written (>=0) or an error.
  * Also serves evaluate*Errors (bspline_so3r3.h:1229-1579). */
 int ctba_evaluate(ctba_problem* p, int kind, double* residuals, double* jacobians);
@@ -150,7 +164,8 @@ int ctba_compute_valid_reprojections(ctba_problem* p, int F, const int64_t* t_ns
                                      int32_t* n_valid /*F*/);
 /* evaluateReprojectionErrors / evaluateAccelErrors / evaluateGyroErrors / evaluateGlobalPosErrors               bspline_so3r3.h:1229-1579
  * norm of every measurement's residual with unit weight (inv_std = 1), in the order the measurements were added;
- * kind = CTBA_REPROJ | CTBA_ACCEL | CTBA_GYRO | CTBA_GP | CTBA_PRIOR (evaluatePositionErrors / evaluateOrientationErrors, :1581-1680).  Returns the number of errors written (errors may be NULL to query it). */
+ * kind = CTBA_REPROJ | CTBA_ACCEL | CTBA_GYRO | CTBA_GP | CTBA_PRIOR (evaluatePositionErrors / evaluateOrientationErrors, :1581-1680) |
+ * CTBA_ALIGN (evaluateWorldColmapAlignmentErrors, :1682-1790).  Returns the number of errors written (errors may be NULL to query it). */
 int ctba_evaluate_errors(ctba_problem* p, int kind, double* errors);
 /* getPose / getAccel / getGyro / getAccelBias / getGyroBias at n timestamps, evaluated on the device at the CURRENT state
  *                                                                       bspline_so3r3.h:221-264, 122-174, 176-213, 266-295, 297-327

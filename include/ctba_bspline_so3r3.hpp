@@ -134,6 +134,26 @@ class BSplineSO3R3 {
   // addPositionMeasurement / addOrientationMeasurement (spline fitting)                 :1048-1123
   bool addPositionMeasurement(const Vec3& meas, int64_t time_ns, double noise) { return chk(ctba_add_position_measurements(h_, 1, &time_ns, meas.data(), noise)) == 1; }
   bool addOrientationMeasurement(const Quat& meas, int64_t time_ns, double noise) { return chk(ctba_add_orientation_measurements(h_, 1, &time_ns, meas.data(), noise)) == 1; }
+  // ---- alignment of a frozen spline to the world frame (src/align_spline_to_global_frame.cpp:153-226) --------------------------
+  void setWorldColmapTransformation(const Pose& T) {                                   // :1825
+    const double t[7] = {T.q[0], T.q[1], T.q[2], T.q[3], T.p[0], T.p[1], T.p[2]};
+    chk(ctba_set_world_alignment(h_, t, nullptr));
+  }
+  // addWorldColmapAlignmentMeasurement(meas, time_ns, noise)                           :1121-1211
+  bool addWorldColmapAlignmentMeasurement(const Vec3& meas, int64_t time_ns, double noise) {
+    return chk(ctba_add_alignment_measurements(h_, 1, &time_ns, meas.data(), noise)) == 1;
+  }
+  Pose getWorldColmapTransformation() {                                                // :1827-1834
+    double t[7]; chk(ctba_get_world_alignment(h_, t, nullptr));
+    return Pose{{t[4], t[5], t[6]}, {t[0], t[1], t[2], t[3]}};
+  }
+  Pose getWorldColmapTransformationCorr() {                                            // :1836-1840
+    double c[7]; chk(ctba_get_world_alignment(h_, nullptr, c));
+    return Pose{{c[4], c[5], c[6]}, {c[0], c[1], c[2], c[3]}};
+  }
+  std::vector<double> evaluateWorldColmapAlignmentErrors() { return evaluateErrors(CTBA_ALIGN); }   // :1682-1790
+  double getScaleCorr() { return globals()[0]; }                                        // :1882
+  double getSplineGlobSensTimeOffsetCorr() { return globals()[9]; }                     // :1852
 
   // ---- solve ----------------------------------------------------------------------------------------------------------------
   // loadOptimizationParams(n_max_outer_iters, n_max_inner_iters, n_threads)            :1760-1766 (threads: the GPU decides)

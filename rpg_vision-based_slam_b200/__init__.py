@@ -30,6 +30,7 @@ EXPORTS = [
     "ctba_add_gp", "ctba_add_position_measurements", "ctba_add_orientation_measurements", "ctba_num_priors", "ctba_cost_terms", "ctba_add_bias_cost", "ctba_add_gravity_norm", "ctba_counts", "ctba_evaluate", "ctba_cost", "ctba_solve",
     "ctba_relinearize_time_offsets", "ctba_bench_evaluate", "ctba_set_option", "ctba_invalidate_device", "ctba_transfer_bytes",
     "ctba_bench_reproj", "ctba_compute_valid_reprojections", "ctba_evaluate_errors", "ctba_sample", "ctba_comm_unique_id", "ctba_comm_init_nccl", "ctba_comm_init_local", "ctba_shard_plan",
+    "ctba_set_world_alignment", "ctba_get_world_alignment", "ctba_add_alignment_measurements", "ctba_num_alignment_measurements",
 ]
 
 
@@ -203,6 +204,31 @@ class BSplineSO3R3:
     def numPriors(self):
         return self.L.ctba_num_priors(self.h)
 
+    # ---- alignment of a frozen spline to the world frame (src/align_spline_to_global_frame.cpp:153-226) ----
+    def setWorldColmapTransformation(self, T_wg, corr=None):
+        """setWorldColmapTransformation (bspline_so3r3.h:1825); T_wg = qx qy qz qw tx ty tz"""
+        T = _d(T_wg); c = _d(corr) if corr is not None else None
+        self._chk(self.L.ctba_set_world_alignment(self.h, _p(T), _p(c) if c is not None else None))
+
+    def addWorldColmapAlignmentMeasurements(self, t_ns, pos, noise):
+        """addWorldColmapAlignmentMeasurement per sample (bspline_so3r3.h:1121-1211)"""
+        t = np.ascontiguousarray(t_ns, dtype=np.int64)
+        x = _d(pos)
+        return self._chk(self.L.ctba_add_alignment_measurements(self.h, int(t.size), _p(t), _p(x), C.c_double(noise)))
+
+    def numAlignmentMeasurements(self):
+        return self.L.ctba_num_alignment_measurements(self.h)
+
+    def getWorldColmapTransformation(self):
+        """(getWorldColmapTransformation, getWorldColmapTransformationCorr)  bspline_so3r3.h:1827-1840"""
+        T = np.zeros(7); c = np.zeros(7)
+        self._chk(self.L.ctba_get_world_alignment(self.h, _p(T), _p(c)))
+        return T, c
+
+    def evaluateWorldColmapAlignmentErrors(self):
+        """bspline_so3r3.h:1682-1790: |residual| of every alignment measurement with unit weight"""
+        return self.evaluateErrors(7)
+
     def addImuBiasCost(self, freq_hz, dt_s, acc_rw, gyr_rw):
         return self._chk(self.L.ctba_add_bias_cost(self.h, C.c_double(freq_hz), C.c_double(dt_s), C.c_double(acc_rw), C.c_double(gyr_rw)))
 
@@ -217,11 +243,12 @@ class BSplineSO3R3:
     # ---- evaluation / solve ----
     def jac_width(self, kind):
         N = self.N
-        return [6 * N + 10, 6 * N + 16, 3 * N + 13, 6 * N + 5, 24, 3, 3 * N][kind]
+        return [6 * N + 10, 6 * N + 16, 3 * N + 13, 6 * N + 5, 24, 3, 3 * N, 11][kind]
 
     def evaluate(self, kind, jac=True):
         c = self.counts()
-        nres = [2 * c["obs"], 3 * c["accel"], 3 * c["gyro"], 3 * c["gp"], 3 * c["bias"], c["gravity"], 3 * self.numPriors()][kind]
+        nres = [2 * c["obs"], 3 * c["accel"], 3 * c["gyro"], 3 * c["gp"], 3 * c["bias"], c["gravity"], 3 * self.numPriors(),
+                3 * self.numAlignmentMeasurements()][kind]
         r = np.zeros(nres)
         J = np.zeros((nres, self.jac_width(kind))) if jac else None
         n = self._chk(self.L.ctba_evaluate(self.h, int(kind), _p(r), _p(J) if jac else None))

@@ -139,6 +139,7 @@ int ctba_destroy(ctba_problem* p) {
   delete p->shard; delete p->gstruct;
   p->d_fsq_glob.release(); p->d_gather.release(); p->d_stage.release();
   if (p->solver) solver_free(p->solver);
+  align_free(p->align);
   DBuf<double>* dd[] = {&p->dstate.knot_q, &p->dstate.knot_p, &p->dstate.bias_a, &p->dstate.bias_g, &p->dstate.lm, &p->dstate.glb,
                         &p->d_f_u, &p->d_f_inv_std, &p->d_o_uv, &p->d_i_st_s, &p->d_i_k, &p->d_i_ub, &p->d_i_inv_a, &p->d_i_inv_g, &p->d_i_acc,
                         &p->d_i_gyr, &p->d_g_st_s, &p->d_g_k, &p->d_g_inv_std, &p->d_g_meas, &p->d_b_u0, &p->d_b_u1, &p->d_b_inv_std,
@@ -390,6 +391,49 @@ int ctba_add_gp(ctba_problem* p, int n, const int64_t* t_ns, const double* pos, 
   return added;
 }
 
+// addWorldColmapAlignmentMeasurement (bspline_so3r3.h:1121-1211): the window arithmetic and skip rules of addGlobalPosMeasurement
+int ctba_add_alignment_measurements(ctba_problem* p, int n, const int64_t* t_ns, const double* pos, double noise) {
+  CHECK_P(p);
+  if (n < 0 || !t_ns || !pos || !(noise > 0)) return fail(p, CTBA_E_ARG, "add_alignment_measurements: bad arguments");
+  const int N = p->N;
+  int added = 0;
+  for (int i = 0; i < n; ++i) {
+    int64_t t_s_gp_init_ns = static_cast<int64_t>(p->t_s_gp_s * 1e9);  // :1127
+    int64_t st_ns = (t_ns[i] - p->start_t_ns - t_s_gp_init_ns);
+    double st_s = st_ns * 1e-9;
+    if (st_ns < 0) continue;
+    int64_t s = st_ns / p->dt_ns;
+    int k_int = (int)(st_ns / p->dt_ns);
+    if (size_t(s + N) > p->numKnots()) continue;
+    p->al_s.push_back((int32_t)s); p->al_st_s.push_back(st_s); p->al_k.push_back((double)k_int); p->al_inv_std.push_back(1.0 / noise);
+    for (int c = 0; c < 3; ++c) p->al_meas.push_back(pos[3 * (size_t)i + c]);
+    ++added;
+  }
+  p->align_dirty = true;
+  return added;
+}
+int ctba_num_alignment_measurements(const ctba_problem* p) { return p ? (int)p->al_s.size() : CTBA_E_ARG; }
+
+// setWorldColmapTransformation (:1825); corr7 (tests: a non-identity linearisation point) = R_w_g_corr (xyzw) | p_w_g_corr, NULL keeps it
+int ctba_set_world_alignment(ctba_problem* p, const double* T_wg7, const double* corr7) {
+  CHECK_P(p);
+  if (!T_wg7) return fail(p, CTBA_E_ARG, "set_world_alignment: T_wg is NULL");
+  for (int i = 0; i < 7; ++i) p->T_wg[i] = T_wg7[i];
+  if (corr7) { for (int i = 0; i < 4; ++i) p->R_wg_corr[i] = corr7[i]; for (int i = 0; i < 3; ++i) p->p_wg_corr[i] = corr7[4 + i]; }
+  return CTBA_OK;
+}
+// getWorldColmapTransformation (:1827-1834): (R(T_w_g) R_w_g_corr, t(T_w_g) + p_w_g_corr); getWorldColmapTransformationCorr (:1836-1840)
+int ctba_get_world_alignment(ctba_problem* p, double* T_wg7, double* corr7) {
+  CHECK_P(p);
+  if (T_wg7) {
+    const quat q = quat_mul(quat{p->T_wg[0], p->T_wg[1], p->T_wg[2], p->T_wg[3]}, quat{p->R_wg_corr[0], p->R_wg_corr[1], p->R_wg_corr[2], p->R_wg_corr[3]});
+    T_wg7[0] = q.x; T_wg7[1] = q.y; T_wg7[2] = q.z; T_wg7[3] = q.w;
+    for (int i = 0; i < 3; ++i) T_wg7[4 + i] = p->T_wg[4 + i] + p->p_wg_corr[i];
+  }
+  if (corr7) { for (int i = 0; i < 4; ++i) corr7[i] = p->R_wg_corr[i]; for (int i = 0; i < 3; ++i) corr7[4 + i] = p->p_wg_corr[i]; }
+  return CTBA_OK;
+}
+
 // addPositionMeasurement (bspline_so3r3.h:1048-1085) / addOrientationMeasurement (:1087-1123): same window arithmetic and skip rules
 static int add_priors(ctba_problem* p, int which, int n, const int64_t* t_ns, const double* meas, double noise) {
   const int N = p->N, w = which ? 4 : 3;
@@ -463,9 +507,14 @@ int ctba_counts(ctba_problem* p, int64_t* c) {
 
 int ctba_evaluate(ctba_problem* p, int kind, double* r_out, double* j_out) {
   CHECK_P(p);
-  if (kind < 0 || kind > CTBA_PRIOR) return fail(p, CTBA_E_ARG, "evaluate: unknown residual kind");
+  if (kind < 0 || kind > CTBA_ALIGN) return fail(p, CTBA_E_ARG, "evaluate: unknown residual kind");
   if (p->device < 0) return fail(p, CTBA_E_CUDA, "planning-only handle (device -1): no compute entry points");
   CTBA_CUDA(p, cudaSetDevice(p->device));
+  if (kind == CTBA_ALIGN) {
+    if (p->al_s.empty()) return 0;
+    const int n = align_evaluate(p, r_out, j_out, nullptr);
+    return n < 0 ? n : 3 * n;
+  }
   int rc = sync_to_device(p); if (rc) return rc;
   const StatePtrs S = p->dstate.ptrs();
   rc = launch_evaluate(p, p->ev, S, true); if (rc) return rc;
@@ -540,6 +589,7 @@ int ctba_solve(ctba_problem* p, int max_num_iterations, ctba_summary* summary) {
   if (max_num_iterations < 0 || !summary) return fail(p, CTBA_E_ARG, "solve: bad arguments");
   if (p->device < 0) return fail(p, CTBA_E_CUDA, "planning-only handle (device -1): no compute entry points");
   CTBA_CUDA(p, cudaSetDevice(p->device));
+  if (!p->al_s.empty()) return align_solve(p, max_num_iterations, summary);   // align_spline_to_global_frame: frozen spline, <= 11 unknowns
   int rc = sync_to_device(p); if (rc) return rc;
   return solver_solve(p, max_num_iterations, summary);
 }
@@ -573,7 +623,7 @@ int ctba_invalidate_device(ctba_problem* p) {
   CHECK_P(p);
   if (p->device >= 0) cudaSetDevice(p->device);
   int rc = download_state(p); if (rc) return rc;
-  p->meas_dirty = true; p->state_dirty = true;
+  p->meas_dirty = true; p->state_dirty = true; p->align_dirty = true;
   return CTBA_OK;
 }
 

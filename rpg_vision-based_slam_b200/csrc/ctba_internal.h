@@ -72,6 +72,7 @@ struct EvalBuffers {
 };
 
 struct SolverData;  // ctba_solve.cu
+struct AlignData;   // ctba_align.cu
 
 }  // namespace ctba
 
@@ -117,6 +118,13 @@ struct ctba_problem {
   ctba::HVec<int32_t> q_s, q_which;             // pose priors (addPositionMeasurement / addOrientationMeasurement): window, 0 position | 1 orientation
   ctba::HVec<double> q_u, q_inv_std, q_meas;    // u, 1 / noise, measurement (4 per prior: x y z - | qx qy qz qw)
   bool gravity_norm = false;
+  // world alignment of a frozen spline (addWorldColmapAlignmentMeasurement, bspline_so3r3.h:1121-1211; members :1966-1970)
+  ctba::HVec<int32_t> al_s;
+  ctba::HVec<double> al_st_s, al_k, al_inv_std, al_meas;
+  double T_wg[7] = {0, 0, 0, 1, 0, 0, 0}, R_wg_corr[4] = {0, 0, 0, 1}, p_wg_corr[3] = {0, 0, 0};
+  double align_cauchy_a = 0.10;          // CauchyLoss(0.10), :1189
+  ctba::AlignData* align = nullptr;      // device side (ctba_align.cu)
+  bool align_dirty = true;
 
   // ---- device ----
   bool meas_dirty = true, state_dirty = true, host_state_stale = false, struct_dirty = true;
@@ -159,6 +167,10 @@ int expand_reproj_dense(ctba_problem* p, const StatePtrs& S, double* d_out);  //
 void solver_free(SolverData* s);
 int solver_solve(ctba_problem* p, int max_iters, ctba_summary* out);
 int solver_num_unknowns(ctba_problem* p);
+// ctba_align.cu: the frozen-spline alignment problem (handles that hold alignment measurements)
+int align_solve(ctba_problem* p, int max_iters, ctba_summary* out);
+int align_evaluate(ctba_problem* p, double* r_out, double* j_out, double* err_out);   // 3n residuals (x 1/noise), 3n x 11 Jacobians, n unit-weight norms
+void align_free(AlignData* a);
 int shard_build(ctba_problem* p);                    // ctba_shard.cu: filter the host work items to this rank's units
 int shard_reduce_cost(ctba_problem* p, EvalBuffers& ev, double* host_cost8);   // cost terms of all ranks, summed in rank order
 int shard_gather_state(ctba_problem* p);             // owners' knots / biases / landmarks -> every rank

@@ -174,6 +174,12 @@ int ctba_compute_valid_reprojections(ctba_problem* p, int F, const int64_t* t_ns
 
 int ctba_evaluate_errors(ctba_problem* p, int kind, double* errors) {
   if (!p) return CTBA_E_ARG;
+  if (kind == CTBA_ALIGN) {   // evaluateWorldColmapAlignmentErrors :1682-1790
+    if (p->device < 0) { p->err = "planning-only handle (device -1): no compute entry points"; return CTBA_E_CUDA; }
+    if (p->al_s.empty() || !errors) return (int)p->al_s.size();
+    CTBA_CUDA(p, cudaSetDevice(p->device));
+    return align_evaluate(p, nullptr, nullptr, errors);
+  }
   if ((kind < CTBA_REPROJ || kind > CTBA_GP) && kind != CTBA_PRIOR) { p->err = "evaluate_errors: kind must be reprojection, accel, gyro, global position or pose prior"; return CTBA_E_ARG; }
   if (p->device < 0) { p->err = "planning-only handle (device -1): no compute entry points"; return CTBA_E_CUDA; }
   CTBA_CUDA(p, cudaSetDevice(p->device));

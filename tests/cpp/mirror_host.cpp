@@ -46,6 +46,25 @@ int main() {
   auto c = spline.counts();   // frames, observations, accel, gyro, gp, bias blocks, gravity
   REQUIRE(c[0] == 1 && c[1] == 2 && c[2] == 1 && c[3] == 1 && c[4] == 2);
   REQUIRE(ctba_num_priors(spline.handle()) == 2);
+  // world alignment (align_spline_to_global_frame): transformation composition and the skip rules, on a second handle
+  {
+    Spline al(dt_ns, start_ns, /*device=*/-1);
+    al.initializeFromNumTraj(q, p);
+    al.setWorldColmapTransformation(ctba::Pose{{1, 2, 3}, {0, 0, 0.6, 0.8}});
+    al.setScale(2.0);
+    al.setInitSplineGlobSensTimeOffset(0.05);
+    REQUIRE(!al.addWorldColmapAlignmentMeasurement({0, 0, 0}, start_ns + 49999999, 1.0));   // before start + offset
+    REQUIRE(al.addWorldColmapAlignmentMeasurement({0, 0, 0}, start_ns + 50000000, 1.0));
+    REQUIRE(!al.addWorldColmapAlignmentMeasurement({0, 0, 0}, al.maxTimeNs() + 50000001, 1.0));
+    REQUIRE(ctba_num_alignment_measurements(al.handle()) == 1);
+    ctba::Pose T = al.getWorldColmapTransformation(), Tc = al.getWorldColmapTransformationCorr();
+    REQUIRE(std::fabs(T.q[2] - 0.6) < 1e-15 && std::fabs(T.q[3] - 0.8) < 1e-15 && T.p[1] == 2.0);
+    REQUIRE(Tc.q[3] == 1.0 && Tc.p[0] == 0.0);
+    REQUIRE(al.getScaleCorr() == 0.0 && al.getSplineGlobSensTimeOffsetCorr() == 0.0);
+    bool t2 = false;
+    try { al.optimize(3); } catch (const ctba::Error& e) { t2 = e.code == CTBA_E_CUDA; }
+    REQUIRE(t2);
+  }
   // no device: the compute entry points fail loudly (there is no CPU fallback)
   bool threw = false;
   try { spline.optimize(3); } catch (const ctba::Error& e) { threw = e.code == CTBA_E_CUDA; }

@@ -88,3 +88,62 @@ def test_alignment_lm_host_pieces_vs_oracle(oracle, scene, hostdbg, N, optimize_
     assert abs(case["scale_init"] + g[0] - tr["scale"]) < (5e-3 if optimize_pbp and optimize_t else 3e-2) * tr["scale"]
     if optimize_pbp and optimize_t:
         assert abs(g[9] - tr["t_off"]) < 8e-3
+
+
+def test_alignment_host_logic_on_planning_handle(pkg, oracle, scene):
+    """Host side of the C ABI without a GPU (device -1): skip rules of addWorldColmapAlignmentMeasurement, get/setWorldColmapTransformation
+    composition (bspline_so3r3.h:1827-1840) and the loud failure of the compute entry points."""
+    N = 4
+    case = make_alignment_case(scene, oracle, N, seed=3, duration_s=5.0)
+    g = pkg.BSplineSO3R3(N, case["dt_ns"], case["start_t_ns"], device=-1)
+    o = oracle.OracleSpline(N, case["dt_ns"], case["start_t_ns"])
+    # measurements before the spline start and beyond the last window are skipped by both
+    t_ns = np.r_[case["start_t_ns"] - 5, case["t_ns"], case["start_t_ns"] + int(1e12)].astype(np.int64)
+    z = np.vstack([np.zeros((1, 3)), case["z"], np.zeros((1, 3))])
+    case2 = dict(case, t_ns=t_ns, z=z)
+    n_g = load_alignment(g, case2, True, True)
+    n_o = load_alignment(o, case2, True, True)
+    assert n_g == n_o == len(case["t_ns"]) and g.numAlignmentMeasurements() == n_o
+    corr = np.r_[Rot.from_rotvec([0.1, 0.2, -0.3]).as_quat(), [0.5, -0.25, 1.0]]
+    g.setWorldColmapTransformation(case["T_wg_init"], corr); o.setWorldColmapTransformation(case["T_wg_init"], corr)
+    Tg, cg = g.getWorldColmapTransformation(); To, co = o.getWorldColmapTransformation()
+    np.testing.assert_allclose(Tg, To, rtol=0, atol=1e-15)
+    np.testing.assert_array_equal(cg, co)
+    with pytest.raises(pkg.CtbaError):
+        g.optimize(3)
+    with pytest.raises(pkg.CtbaError):
+        g.evaluate(7)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N", [4, 6])
+@pytest.mark.parametrize("optimize_pbp,optimize_t", [(True, True), (False, False)])
+def test_alignment_gpu_vs_oracle(pkg, oracle, scene, N, optimize_pbp, optimize_t):
+    """The device path through the C ABI: residuals / Jacobians 1e-10, unit-weight errors, LM trace 1e-8, final cost 1e-6, same state."""
+    case = make_alignment_case(scene, oracle, N, seed=60 + N, duration_s=40.0, gp_hz=20.0)
+    g = pkg.BSplineSO3R3(N, case["dt_ns"], case["start_t_ns"], device=0)
+    o = oracle.OracleSpline(N, case["dt_ns"], case["start_t_ns"])
+    assert load_alignment(g, case, optimize_pbp, optimize_t) == load_alignment(o, case, optimize_pbp, optimize_t) == len(case["t_ns"])
+    r_g, J_g = g.evaluate(7)
+    r_o, J_o, _ = o.evaluate(7)
+    np.testing.assert_allclose(r_g, r_o, rtol=1e-10, atol=1e-10 * np.abs(r_o).max())
+    np.testing.assert_allclose(J_g, J_o[:, 6 * N:], rtol=1e-10, atol=1e-10 * np.abs(J_o).max())
+    e_g = g.evaluateWorldColmapAlignmentErrors()
+    np.testing.assert_allclose(e_g, np.linalg.norm(r_o.reshape(-1, 3), axis=1) * case["noise_arg"], rtol=1e-10)
+    sg = g.optimize(30)
+    so = o.optimize(30)
+    lg, lo = sg["iterations"], so["iterations"]
+    assert sg["termination_type"] == so["termination_type"] == 0 and len(lg) == len(lo)
+    np.testing.assert_allclose(lg[:, 0], lo[:, 0], rtol=1e-8)
+    np.testing.assert_array_equal(lg[:, 6], lo[:, 6])
+    assert abs(sg["final_cost"] - so["final_cost"]) <= 1e-6 * so["final_cost"]
+    Tg, cg = g.getWorldColmapTransformation(); To, co = o.getWorldColmapTransformation()
+    np.testing.assert_allclose(Tg, To, atol=1e-8)
+    gg, go = g.getGlobals(), o.getGlobals()
+    np.testing.assert_allclose(gg[[0, 9, 10, 11, 12]], go[[0, 9, 10, 11, 12]], atol=1e-8)
+    # a second solve from the optimum terminates at once with the same cost (state round trip host <-> device)
+    s2 = g.optimize(5)
+    assert abs(s2["initial_cost"] - sg["final_cost"]) <= 1e-9 * sg["final_cost"]
+    # relinearizeSplineGlobSensTimeOffset after the solve (align_spline_to_global_frame.cpp:217)
+    g.relinearize(); o.relinearize()
+    np.testing.assert_allclose(g.getGlobals()[17], o.getGlobals()[17], atol=1e-9)
