@@ -1,0 +1,250 @@
+// ctba_io.hpp — the on-disk formats either side of the solve, dependency-free C++14.
+//
+// Loaders restate the reference's parsing idioms exactly, including "read one record too many, then pop_back" (so a file must end with a
+// newline to give the same count) and "a '#' is only recognised as the first character of a record":
+//   loadGpMeasurements   /root/reference/include/sensor/global_position_sensor.h:43-74     t x y z
+//   loadSplineFromFile   /root/reference/include/spline/spline_common.h:125-163            t tx ty tz qx qy qz qw
+//   loadPose             /root/reference/include/util/load.h:18-49                         3x4 row-major R|t, R re-orthonormalised
+//   loadVector3d / loadScalar                          load.h:52-101
+//   fixRotationMatrix    /root/reference/include/util/utils.h:34-50                        U V^T of the SVD (here: polar iteration, same matrix)
+// Writers: createTrace / tracePose / tracePosition / traceScalar / traceSpline   /root/reference/include/util/save.h:25-39, 99-117, 156-178
+// YAML: the experiment files are flat `key: value` maps (experiments/**/**.yaml); Yaml reads exactly that subset.
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <fstream>
+#include <iomanip>
+#include <iostream>
+#include <limits>
+#include <map>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include "ctba_bspline_so3r3.hpp"
+
+namespace ctba {
+namespace io {
+
+struct GlobalPosMeasurement { double t; Vec3 pos; };
+
+inline void skipComment(std::ifstream& fs) {
+  if (fs.peek() == '#') fs.ignore(std::numeric_limits<std::streamsize>::max(), '\n');
+}
+
+inline bool loadGpMeasurements(const std::string& filename, std::vector<GlobalPosMeasurement>& measurements) {
+  std::ifstream fs(filename.c_str());
+  if (!fs.is_open()) { std::cerr << "Could not open file: " << filename << "\n"; return false; }
+  while (fs.good() && !fs.eof()) {
+    skipComment(fs);
+    double stamp = 0, x = 0, y = 0, z = 0;
+    fs >> stamp >> x >> y >> z;
+    measurements.push_back(GlobalPosMeasurement{stamp, Vec3{{x, y, z}}});
+  }
+  if (!measurements.empty()) measurements.pop_back();   // the loop reads one record past the last line (:69-71)
+  return true;
+}
+
+inline Quat normalized(const Quat& q) {   // Sophus::SO3d(Eigen::Quaterniond) normalises (so3.hpp:481-487)
+  const double n = std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  return Quat{{q[0] / n, q[1] / n, q[2] / n, q[3] / n}};
+}
+
+inline bool loadSplineFromFile(const std::string& filename, std::vector<Quat>& so3_knots, std::vector<Vec3>& r3_knots, std::vector<double>& ts) {
+  std::ifstream fs(filename.c_str());
+  if (!fs.is_open()) { std::cerr << "Could not open file: " << filename << "\n"; return false; }
+  while (fs.good() && !fs.eof()) {
+    skipComment(fs);
+    double stamp = 0, tx = 0, ty = 0, tz = 0, qw = 1, qx = 0, qy = 0, qz = 0;
+    fs >> stamp >> tx >> ty >> tz >> qx >> qy >> qz >> qw;
+    ts.push_back(stamp);
+    so3_knots.push_back(normalized(Quat{{qx, qy, qz, qw}}));
+    r3_knots.push_back(Vec3{{tx, ty, tz}});
+  }
+  if (!ts.empty()) { ts.pop_back(); so3_knots.pop_back(); r3_knots.pop_back(); }   // :154-157
+  return true;
+}
+
+// Nearest rotation to a 3x3 matrix: R (R^T R)^(-1/2) = U V^T of the SVD, by Newton's polar iteration X <- (X + X^-T) / 2
+// (quadratically convergent for the nearly orthogonal matrices of a 9-digit pose file).  det < 0 => the matrix is negated (utils.h:44-47).
+inline void fixRotationMatrix(const double R[9], double R_new[9]) {
+  double X[9];
+  for (int i = 0; i < 9; ++i) X[i] = R[i];
+  for (int it = 0; it < 50; ++it) {
+    const double c00 = X[4] * X[8] - X[5] * X[7], c01 = X[5] * X[6] - X[3] * X[8], c02 = X[3] * X[7] - X[4] * X[6];
+    const double det = X[0] * c00 + X[1] * c01 + X[2] * c02;
+    const double C[9] = {c00, c01, c02,                                                    // cofactor matrix = det * X^-T
+                         X[2] * X[7] - X[1] * X[8], X[0] * X[8] - X[2] * X[6], X[1] * X[6] - X[0] * X[7],
+                         X[1] * X[5] - X[2] * X[4], X[2] * X[3] - X[0] * X[5], X[0] * X[4] - X[1] * X[3]};
+    double diff = 0;
+    for (int i = 0; i < 9; ++i) { const double y = 0.5 * (X[i] + C[i] / det); diff = std::fmax(diff, std::fabs(y - X[i])); X[i] = y; }
+    if (diff < 1e-16) break;
+  }
+  const double det = X[0] * (X[4] * X[8] - X[5] * X[7]) + X[1] * (X[5] * X[6] - X[3] * X[8]) + X[2] * (X[3] * X[7] - X[4] * X[6]);
+  for (int i = 0; i < 9; ++i) R_new[i] = det < 0 ? -X[i] : X[i];
+}
+
+// Eigen::Quaterniond(Matrix3d) (Shepperd's branches, as Eigen's QuaternionBase::operator=(MatrixBase)); x y z w
+inline Quat quatFromMatrix(const double R[9]) {
+  double q[4];   // w x y z
+  const double t = R[0] + R[4] + R[8];
+  if (t > 0.0) {
+    double s = std::sqrt(t + 1.0);
+    q[0] = 0.5 * s; s = 0.5 / s;
+    q[1] = (R[7] - R[5]) * s; q[2] = (R[2] - R[6]) * s; q[3] = (R[3] - R[1]) * s;
+  } else {
+    int i = 0;
+    if (R[4] > R[0]) i = 1;
+    if (R[8] > R[4 * i]) i = 2;
+    const int j = (i + 1) % 3, k = (j + 1) % 3;
+    double s = std::sqrt(R[4 * i] - R[4 * j] - R[4 * k] + 1.0);
+    q[1 + i] = 0.5 * s; s = 0.5 / s;
+    q[0] = (R[3 * k + j] - R[3 * j + k]) * s;
+    q[1 + j] = (R[3 * j + i] + R[3 * i + j]) * s;
+    q[1 + k] = (R[3 * k + i] + R[3 * i + k]) * s;
+  }
+  return normalized(Quat{{q[1], q[2], q[3], q[0]}});
+}
+
+inline void matrixFromQuat(const Quat& q, double R[9]) {   // Eigen::Quaterniond::toRotationMatrix
+  const double tx = 2 * q[0], ty = 2 * q[1], tz = 2 * q[2];
+  const double twx = tx * q[3], twy = ty * q[3], twz = tz * q[3], txx = tx * q[0], txy = ty * q[0], txz = tz * q[0], tyy = ty * q[1], tyz = tz * q[1], tzz = tz * q[2];
+  R[0] = 1 - (tyy + tzz); R[1] = txy - twz; R[2] = txz + twy;
+  R[3] = txy + twz; R[4] = 1 - (txx + tzz); R[5] = tyz - twx;
+  R[6] = txz - twy; R[7] = tyz + twx; R[8] = 1 - (txx + tyy);
+}
+
+inline bool loadPose(const std::string& filename, Pose& pose) {
+  std::ifstream fs(filename.c_str());
+  if (!fs.is_open()) { std::cerr << "Could not open file: " << filename << "\n"; return false; }
+  skipComment(fs);
+  double R[9], t[3];
+  fs >> R[0] >> R[1] >> R[2] >> t[0] >> R[3] >> R[4] >> R[5] >> t[1] >> R[6] >> R[7] >> R[8] >> t[2];
+  double Rn[9];
+  fixRotationMatrix(R, Rn);
+  pose.q = quatFromMatrix(Rn);
+  pose.p = Vec3{{t[0], t[1], t[2]}};
+  return true;
+}
+
+inline bool loadVector3d(const std::string& filename, Vec3& v) {
+  std::ifstream fs(filename.c_str());
+  if (!fs.is_open()) { std::cerr << "Could not open file: " << filename << "\n"; return false; }
+  skipComment(fs);
+  fs >> v[0] >> v[1] >> v[2];
+  return true;
+}
+
+template <typename T>
+bool loadScalar(const std::string& filename, T& scalar) {
+  std::ifstream fs(filename.c_str());
+  if (!fs.is_open()) { std::cerr << "Could not open file: " << filename << "\n"; return false; }
+  skipComment(fs);
+  T s{};
+  fs >> s;
+  scalar = s;
+  return true;
+}
+
+// ---- writers (save.h) ----
+inline void createTrace(const std::string& trace_dir, const std::string& trace_fn, std::ofstream* fs) {
+  const std::string full_fn = trace_dir + "/" + trace_fn;
+  fs->open(full_fn.c_str());
+  if (fs->fail()) throw std::runtime_error("Fail to create trace: " + full_fn);   // the reference aborts (save.h:30-34)
+  std::cout << "Created trace: " << full_fn << "\n";
+}
+inline void traceScalar(double v, std::ofstream& s) { s << v << std::endl; }
+inline void tracePose(const Pose& pose, std::ofstream& s) {
+  double R[9];
+  matrixFromQuat(pose.q, R);
+  s << R[0] << " " << R[1] << " " << R[2] << " " << pose.p[0] << "\n"
+    << R[3] << " " << R[4] << " " << R[5] << " " << pose.p[1] << "\n"
+    << R[6] << " " << R[7] << " " << R[8] << " " << pose.p[2] << "\n"
+    << 0.0 << " " << 0.0 << " " << 0.0 << " " << 1.0 << std::endl;
+}
+inline void tracePosition(const Vec3& pos, std::ofstream& s) {
+  s << "# x y z" << std::endl;
+  s << pos[0] << " " << pos[1] << " " << pos[2] << std::endl;
+}
+// traceSpline (save.h:99-117): one device call for all samples instead of a getPose per line
+template <class Spline>
+void traceSpline(Spline& spline, int64_t dt_ns, std::ofstream& s) {
+  s << "# timestamp tx ty tz qx qy qz qw" << std::endl;
+  for (const auto& r : spline.traceSpline(dt_ns))
+    s << std::setprecision(15) << r[0] << " " << r[1] << " " << r[2] << " " << r[3] << " " << r[4] << " " << r[5] << " " << r[6] << " " << r[7] << std::endl;
+}
+// the tools' saveSpline / savePose / savePosition / saveScalar (src/align_spline_to_global_frame.cpp:40-85, src/fit_spline_to_colmap.cpp)
+template <class Spline>
+void saveSpline(const std::string& trace_dir, Spline& spline) {
+  std::ofstream f; createTrace(trace_dir, "spline.txt", &f); f.precision(9);
+  traceSpline(spline, static_cast<int64_t>((1.0 / 100.0) * 1e9), f);
+}
+inline void savePose(const std::string& trace_dir, const std::string& fn, const Pose& pose) { std::ofstream f; createTrace(trace_dir, fn, &f); f.precision(9); tracePose(pose, f); }
+inline void savePosition(const std::string& trace_dir, const std::string& fn, const Vec3& p) { std::ofstream f; createTrace(trace_dir, fn, &f); f.precision(9); tracePosition(p, f); }
+inline void saveScalar(const std::string& trace_dir, const std::string& fn, double v) { std::ofstream f; createTrace(trace_dir, fn, &f); f.precision(16); traceScalar(v, f); }
+// spline_knots.txt as loadSplineFromFile reads it (the knot time stamps are t0 + i dt)
+template <class Spline>
+void saveSplineKnots(const std::string& trace_dir, const std::string& fn, Spline& spline) {
+  std::ofstream f; createTrace(trace_dir, fn, &f);
+  f << "# timestamp tx ty tz qx qy qz qw" << std::endl;
+  for (size_t i = 0; i < spline.numKnots(); ++i) {
+    const Pose k = spline.getKnot(i);
+    f << std::setprecision(17) << (spline.getStartTns() + (int64_t)i * spline.getDeltaTns()) * 1e-9 << " " << k.p[0] << " " << k.p[1] << " " << k.p[2] << " "
+      << k.q[0] << " " << k.q[1] << " " << k.q[2] << " " << k.q[3] << std::endl;
+  }
+}
+
+// ---- flat YAML (`key: value`, '#' comments, optional quotes) — what YAML::LoadFile + config["k"].as<T>() is used for in the drivers ----
+class Yaml {
+ public:
+  static Yaml LoadFile(const std::string& fn) {
+    std::ifstream fs(fn.c_str());
+    if (!fs.is_open()) throw std::runtime_error("Could not open yaml file: " + fn);
+    Yaml y;
+    std::string line;
+    while (std::getline(fs, line)) {
+      bool in_q = false; char qc = 0; size_t cut = line.size();
+      for (size_t i = 0; i < line.size(); ++i) {
+        const char c = line[i];
+        if (in_q) { if (c == qc) in_q = false; }
+        else if (c == '"' || c == '\'') { in_q = true; qc = c; }
+        else if (c == '#' && (i == 0 || line[i - 1] == ' ' || line[i - 1] == '\t')) { cut = i; break; }
+      }
+      line = line.substr(0, cut);
+      const size_t colon = line.find(':');
+      if (colon == std::string::npos) continue;
+      std::string key = trim(line.substr(0, colon)), val = trim(line.substr(colon + 1));
+      if (val.size() >= 2 && (val.front() == '"' || val.front() == '\'') && val.back() == val.front()) val = val.substr(1, val.size() - 2);
+      if (!key.empty()) y.kv_[key] = val;
+    }
+    return y;
+  }
+  bool has(const std::string& k) const { return kv_.count(k) != 0; }
+  template <class T> T as(const std::string& k) const {
+    auto it = kv_.find(k);
+    if (it == kv_.end()) throw std::runtime_error("yaml: missing key '" + k + "'");   // yaml-cpp throws InvalidNode / BadConversion
+    return conv(it->second, k, static_cast<T*>(nullptr));
+  }
+ private:
+  static std::string trim(const std::string& s) {
+    const size_t a = s.find_first_not_of(" \t\r\n"), b = s.find_last_not_of(" \t\r\n");
+    return a == std::string::npos ? std::string() : s.substr(a, b - a + 1);
+  }
+  static std::string conv(const std::string& v, const std::string&, std::string*) { return v; }
+  static double conv(const std::string& v, const std::string& k, double*) {
+    std::istringstream ss(v); double d; if (!(ss >> d)) throw std::runtime_error("yaml: '" + k + "' is not a number"); return d;
+  }
+  static int conv(const std::string& v, const std::string& k, int*) {
+    std::istringstream ss(v); int d; if (!(ss >> d)) throw std::runtime_error("yaml: '" + k + "' is not an integer"); return d;
+  }
+  static bool conv(const std::string& v, const std::string& k, bool*) {   // yaml-cpp: true/false, yes/no, on/off, y/n in any of three capitalisations
+    std::string l; for (char c : v) l += (char)std::tolower((unsigned char)c);
+    if (l == "true" || l == "yes" || l == "on" || l == "y") return true;
+    if (l == "false" || l == "no" || l == "off" || l == "n") return false;
+    throw std::runtime_error("yaml: '" + k + "' is not a boolean");
+  }
+  std::map<std::string, std::string> kv_;
+};
+
+}  // namespace io
+}  // namespace ctba

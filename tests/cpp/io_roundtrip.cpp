@@ -1,0 +1,34 @@
+// Reads the files tests/test_drivers.py wrote with drivers/ctba_io.hpp and prints what it parsed (one "key v v v" line each);
+// then writes a pose / position / scalar back with the reference's precisions.
+#include <cstdio>
+#include "../../drivers/ctba_io.hpp"
+using namespace ctba;
+using namespace ctba::io;
+int main(int argc, char** argv) {
+  if (argc < 2) return 1;
+  const std::string d = argv[1];
+  std::vector<GlobalPosMeasurement> gp;
+  if (!loadGpMeasurements(d + "/gp.txt", gp)) return 2;
+  std::printf("gp_count %zu\n", gp.size());
+  if (!gp.empty()) std::printf("gp_last %.17g %.17g %.17g %.17g\n", gp.back().t, gp.back().pos[0], gp.back().pos[1], gp.back().pos[2]);
+  std::vector<Quat> kq; std::vector<Vec3> kp; std::vector<double> ts;
+  if (!loadSplineFromFile(d + "/spline_knots.txt", kq, kp, ts)) return 3;
+  std::printf("knot_count %zu\n", ts.size());
+  std::printf("knot1 %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g\n", ts[1], kp[1][0], kp[1][1], kp[1][2], kq[1][0], kq[1][1], kq[1][2], kq[1][3]);
+  Pose T;
+  if (!loadPose(d + "/T.txt", T)) return 4;
+  std::printf("pose %.17g %.17g %.17g %.17g %.17g %.17g %.17g\n", T.q[0], T.q[1], T.q[2], T.q[3], T.p[0], T.p[1], T.p[2]);
+  double sc = 0; Vec3 v{};
+  if (!loadScalar<double>(d + "/scalar.txt", sc) || !loadVector3d(d + "/vec.txt", v)) return 5;
+  std::printf("scalar %.17g\nvec %.17g %.17g %.17g\n", sc, v[0], v[1], v[2]);
+  if (loadScalar<double>(d + "/does_not_exist.txt", sc)) return 6;
+  Yaml y = Yaml::LoadFile(d + "/cfg.yaml");
+  std::printf("yaml %s|%d|%.17g|%d|%d|%d\n", y.as<std::string>("gp_fn").c_str(), y.as<int>("spline_order"), y.as<double>("spline_control_nodes_dt_s"),
+              (int)y.as<bool>("optimize_pBP"), (int)y.as<bool>("optimize_spline_globsens_time_offset"), (int)y.has("nope"));
+  bool threw = false;
+  try { y.as<int>("nope"); } catch (const std::exception&) { threw = true; }
+  if (!threw) return 7;
+  savePose(d, "T_out.txt", T); savePosition(d, "p_out.txt", v); saveScalar(d, "s_out.txt", sc);
+  std::printf("OK\n");
+  return 0;
+}

@@ -1,0 +1,155 @@
+"""drivers/: the file formats either side of the solve and the align_spline_to_global_frame tool re-hosted on the C ABI.
+CPU: loaders / writers / flat YAML of drivers/ctba_io.hpp against files written here (including the reference's "one record too many, then
+pop_back" idiom and the re-orthonormalisation of pose files); the tool builds with -Wall -Werror and stops loudly without a GPU.
+GPU: the tool end to end on a synthetic dataset, result files against the oracle's solve of the same problem."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+from scipy.spatial.transform import Rotation as Rot
+
+from align_case import load_alignment, make_alignment_case
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIBDIR = os.path.join(ROOT, "rpg_vision-based_slam_b200", "csrc")
+
+
+def _gxx(src, exe, pkg):
+    pkg.lib()
+    subprocess.check_call(["g++", "-std=c++14", "-O1", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), src, "-L", LIBDIR, "-lctba",
+                           "-Wl,-rpath," + LIBDIR, "-o", exe])
+    return exe
+
+
+def _write_pose(fn, q_xyzw, p, digits=9):
+    R = Rot.from_quat(q_xyzw).as_matrix()
+    with open(fn, "w") as f:
+        for r in range(3):
+            f.write(" ".join(f"{v:.{digits}g}" for v in list(R[r]) + [p[r]]) + "\n")
+        f.write("0 0 0 1\n")
+
+
+def _write_dataset(d, case, order, optimize_pbp, optimize_t):
+    dt_ms = int(case["dt_ns"] * 1e-9 * 1000)
+    sub = f"order_{order}/dt_{dt_ms}_ms"
+    os.makedirs(os.path.join(d, "fitted", sub)); os.makedirs(os.path.join(d, "align", sub))
+    with open(os.path.join(d, "fitted", sub, "spline_knots.txt"), "w") as f:
+        f.write("# timestamp tx ty tz qx qy qz qw\n")
+        for i, (q, p) in enumerate(zip(case["q"], case["p"])):
+            t = (case["start_t_ns"] + i * case["dt_ns"]) * 1e-9
+            f.write(" ".join(f"{v:.17g}" for v in [t, *p, *q]) + "\n")
+    with open(os.path.join(d, "gp.txt"), "w") as f:
+        f.write("# timestamp x y z\n")
+        for t, z in zip(case["t_ns"], case["z"]):
+            f.write(" ".join(f"{v:.17g}" for v in [t * 1e-9, *z]) + "\n")
+    _write_pose(os.path.join(d, "align", sub, "T_wg_init.txt"), case["T_wg_init"][:4], case["T_wg_init"][4:], digits=17)
+    with open(os.path.join(d, "align", sub, "scale_init.txt"), "w") as f:
+        f.write(f"{case['scale_init']:.17g}\n")
+    yml = os.path.join(d, "cfg.yaml")
+    with open(yml, "w") as f:
+        f.write(f"""dataset: Custom
+
+## Files
+gp_fn: "{d}/gp.txt"   # measurements
+colmap_spline_dir: "{d}/fitted"
+spline_global_ref_alignment_dir: '{d}/align'
+
+## Parameters
+spline_order: {order}
+spline_control_nodes_dt_s: {case['dt_ns'] * 1e-9} # [s]
+init_t_offset_cam_gp: {case['t_off_init']}
+optimize_pBP: {'true' if optimize_pbp else 'false'} # pBP = body - antenna
+optimize_spline_globsens_time_offset: {'True' if optimize_t else 'False'}
+n_max_iters: 30
+n_threads: 4
+""")
+    return yml, os.path.join(d, "align", sub)
+
+
+def test_io_formats_roundtrip(pkg, tmp_path):
+    d = str(tmp_path)
+    rng = np.random.default_rng(5)
+    gp = np.c_[100.0 + 0.1 * np.arange(7), rng.normal(size=(7, 3))]
+    with open(os.path.join(d, "gp.txt"), "w") as f:
+        f.write("# t x y z\n")
+        for r in gp: f.write(" ".join(f"{v:.17g}" for v in r) + "\n")
+    q = Rot.from_rotvec(rng.normal(size=(5, 3))).as_quat(); p = rng.normal(size=(5, 3))
+    with open(os.path.join(d, "spline_knots.txt"), "w") as f:
+        f.write("# timestamp tx ty tz qx qy qz qw\n")
+        for i in range(5): f.write(" ".join(f"{v:.17g}" for v in [50.0 + 0.1 * i, *p[i], *(2.0 * q[i])]) + "\n")     # un-normalised on purpose
+    qT = Rot.from_rotvec([2.9, 0.4, -0.6]).as_quat()       # trace < 0: the other branch of the matrix -> quaternion conversion
+    _write_pose(os.path.join(d, "T.txt"), qT, [1.5, -2.5, 3.5], digits=6)   # 6 digits: visibly non-orthogonal before the fix
+    open(os.path.join(d, "scalar.txt"), "w").write("# scale\n2.25\n")
+    open(os.path.join(d, "vec.txt"), "w").write("0.5 -0.25 0.125\n")
+    open(os.path.join(d, "cfg.yaml"), "w").write('gp_fn: "/a b/c#d.txt"  # comment\nspline_order: 6\nspline_control_nodes_dt_s: 0.1 # [s]\n'
+                                                 "optimize_pBP: false\noptimize_spline_globsens_time_offset: True\n")
+    exe = _gxx(os.path.join(ROOT, "tests", "cpp", "io_roundtrip.cpp"), str(tmp_path / "io_roundtrip"), pkg)
+    out = subprocess.run([exe, d], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 0 and out.stdout.strip().endswith("OK"), out.stdout + out.stderr
+    kv = {l.split(" ", 1)[0]: l.split(" ", 1)[1] for l in out.stdout.splitlines() if " " in l and not l.startswith("Created")}
+    assert int(kv["gp_count"]) == 7 and int(kv["knot_count"]) == 5
+    np.testing.assert_array_equal(np.array(kv["gp_last"].split(), dtype=float), gp[-1])
+    k1 = np.array(kv["knot1"].split(), dtype=float)
+    np.testing.assert_array_equal(k1[:4], [50.1, *p[1]])
+    np.testing.assert_allclose(k1[4:], q[1], atol=1e-15)                       # normalised like Sophus::SO3d(Quaterniond)
+    pose = np.array(kv["pose"].split(), dtype=float)
+    assert abs(np.linalg.norm(pose[:4]) - 1.0) < 1e-15
+    assert (Rot.from_quat(pose[:4]).inv() * Rot.from_quat(qT)).magnitude() < 1e-5
+    # the re-orthonormalised rotation is the polar factor U V^T of what was in the file (fixRotationMatrix, utils.h:34-50)
+    M = np.loadtxt(os.path.join(d, "T.txt"))[:3, :3]
+    U, _, Vt = np.linalg.svd(M)
+    np.testing.assert_allclose(Rot.from_quat(pose[:4]).as_matrix(), U @ Vt, atol=1e-14)
+    np.testing.assert_array_equal(pose[4:], [1.5, -2.5, 3.5])
+    assert float(kv["scalar"]) == 2.25 and kv["vec"].split() == ["0.5", "-0.25", "0.125"]
+    assert kv["yaml"] == "/a b/c#d.txt|6|0.10000000000000001|0|1|0"
+    # writers: 3x4 + "0 0 0 1" with 9 significant digits, "# x y z" header, 16-digit scalars (save.h:156-178)
+    T_out = np.loadtxt(os.path.join(d, "T_out.txt"))
+    assert T_out.shape == (4, 4) and list(T_out[3]) == [0, 0, 0, 1]
+    np.testing.assert_allclose(T_out[:3, :3], Rot.from_quat(pose[:4]).as_matrix(), atol=5e-9)
+    assert open(os.path.join(d, "p_out.txt")).read() == "# x y z\n0.5 -0.25 0.125\n"
+    assert open(os.path.join(d, "s_out.txt")).read() == "2.25\n"
+
+
+def test_align_tool_builds_and_fails_loudly_without_gpu(pkg, oracle, scene, tmp_path):
+    import torch
+    exe = _gxx(os.path.join(ROOT, "drivers", "align_spline_to_global_frame.cpp"), str(tmp_path / "align_tool"), pkg)
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    case = make_alignment_case(scene, oracle, 6, seed=11, duration_s=5.0)
+    yml, _ = _write_dataset(str(tmp_path), case, 6, True, True)
+    out = subprocess.run([exe, yml], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 3 and "no CPU fallback" in out.stderr, out.stdout + out.stderr
+    assert "Loaded %d leica measurements" % len(case["t_ns"]) in out.stdout and "Loaded %d spline knots" % len(case["q"]) in out.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("order,optimize_pbp,optimize_t", [(6, True, True), (4, False, False)])
+def test_align_tool_end_to_end_on_gpu(pkg, oracle, scene, tmp_path, order, optimize_pbp, optimize_t):
+    exe = _gxx(os.path.join(ROOT, "drivers", "align_spline_to_global_frame.cpp"), str(tmp_path / "align_tool"), pkg)
+    case = make_alignment_case(scene, oracle, order, seed=21 + order, duration_s=30.0)
+    yml, res = _write_dataset(str(tmp_path), case, order, optimize_pbp, optimize_t)
+    out = subprocess.run([exe, yml], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    # the oracle on the same problem, loaded the way the tool loads it (pose file with 17 digits: the same T_wg_init up to rounding)
+    o = oracle.OracleSpline(order, case["dt_ns"], case["start_t_ns"])
+    load_alignment(o, case, optimize_pbp, optimize_t)
+    so = o.optimize(30)
+    assert so["termination_type"] == 0
+    T_o, _ = o.getWorldColmapTransformation()
+    o.relinearize()
+    g = o.getGlobals()
+    T_wg = np.loadtxt(os.path.join(res, "T_wg.txt"))
+    np.testing.assert_allclose(T_wg[:3, :3], Rot.from_quat(T_o[:4]).as_matrix(), atol=2e-8)      # 9 significant digits in the file
+    np.testing.assert_allclose(T_wg[:3, 3], T_o[4:], rtol=2e-8, atol=1e-7)
+    assert abs(float(open(os.path.join(res, "scale.txt")).read()) - (g[18] + g[0])) < 1e-8
+    assert abs(float(open(os.path.join(res, "spline_globalsensor_time_offset.txt")).read()) - g[17]) < 1e-9
+    np.testing.assert_allclose(np.loadtxt(os.path.join(res, "p_bp.txt")), g[10:13], atol=1e-7)
+    # spline.txt: the frozen spline sampled at 100 Hz like traceSpline (save.h:99-117)
+    tr = np.loadtxt(os.path.join(res, "spline.txt"))
+    end_ns = (len(case["q"]) - order + 1) * case["dt_ns"] + case["start_t_ns"] - 1_000_000
+    t_ns = np.arange(case["start_t_ns"], end_ns, 10_000_000, dtype=np.int64)
+    assert tr.shape == (len(t_ns), 8)
+    ref = o.sampleAt(0, t_ns)
+    np.testing.assert_allclose(tr[:, 1:], ref, atol=1e-12)
+    assert f"Number of errors: {len(case['t_ns'])}" in out.stdout
