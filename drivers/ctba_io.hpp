@@ -114,6 +114,58 @@ inline void matrixFromQuat(const Quat& q, double R[9]) {   // Eigen::Quaterniond
   R[6] = txz - twy; R[7] = tyz + twx; R[8] = 1 - (txx + tyy);
 }
 
+// ---- Sophus::SO3d group operations on x y z w quaternions, as the tools use them on the host (so3.hpp:229-231, 247-290, 325-339, 583-619) ----
+inline Quat quatMul(const Quat& a, const Quat& b) {   // SO3 product (normalising, so3.hpp:325-339)
+  return normalized(Quat{{a[3] * b[0] + a[0] * b[3] + a[1] * b[2] - a[2] * b[1], a[3] * b[1] + a[1] * b[3] + a[2] * b[0] - a[0] * b[2],
+                          a[3] * b[2] + a[2] * b[3] + a[0] * b[1] - a[1] * b[0], a[3] * b[3] - a[0] * b[0] - a[1] * b[1] - a[2] * b[2]}});
+}
+inline Quat quatInverse(const Quat& q) { return Quat{{-q[0], -q[1], -q[2], q[3]}}; }
+inline Quat so3Exp(const Vec3& om) {
+  const double t2 = om[0] * om[0] + om[1] * om[1] + om[2] * om[2];
+  double imag, real;
+  if (t2 < 1e-20) { const double t4 = t2 * t2; imag = 0.5 - t2 / 48.0 + t4 / 3840.0; real = 1.0 - t2 / 8.0 + t4 / 384.0; }
+  else { const double t = std::sqrt(t2), h = 0.5 * t; imag = std::sin(h) / t; real = std::cos(h); }
+  return Quat{{imag * om[0], imag * om[1], imag * om[2], real}};
+}
+inline Vec3 so3Log(const Quat& q) {
+  const double n2 = q[0] * q[0] + q[1] * q[1] + q[2] * q[2], w = q[3];
+  double f;
+  if (n2 < 1e-20) f = 2.0 / w - (2.0 / 3.0) * n2 / (w * w * w);
+  else { const double n = std::sqrt(n2); f = std::fabs(w) < 1e-10 ? (w > 0 ? M_PI : -M_PI) / n : 2.0 * std::atan(n / w) / n; }
+  return Vec3{{f * q[0], f * q[1], f * q[2]}};
+}
+// Sophus::interpolate (interpolate.hpp:27-34): a * exp(p * log(a^-1 b))
+inline Quat so3Interpolate(const Quat& a, const Quat& b, double p) {
+  const Vec3 l = so3Log(quatMul(quatInverse(a), b));
+  return quatMul(a, so3Exp(Vec3{{p * l[0], p * l[1], p * l[2]}}));
+}
+
+// loadTrajectoryFromFile (util/trajectory_utils.h:17-55): the same 8 columns and idiom as loadSplineFromFile
+inline bool loadTrajectoryFromFile(const std::string& filename, std::vector<Quat>& ori, std::vector<Vec3>& pos, std::vector<double>& ts) {
+  return loadSplineFromFile(filename, ori, pos, ts);
+}
+
+// linearInterpolation (util/trajectory_utils.h:96-143), including its stop rule: samples at or after ts.back() are never produced and the
+// size check then fails (the reference aborts; here: std::runtime_error)
+inline void linearInterpolation(const std::vector<Vec3>& pos, const std::vector<Quat>& ori, const std::vector<double>& ts,
+                                const std::vector<double>& interpolated_ts, std::vector<Vec3>& interpolated_pos, std::vector<Quat>& interpolated_ori) {
+  size_t it_i = 0, t_i = 0;
+  const size_t n = interpolated_ts.size(), m = ts.size() - 1;
+  while (n > 0 && ts.size() >= 2) {
+    if (interpolated_ts[it_i] >= ts[t_i] && interpolated_ts[it_i] < ts[t_i + 1]) {
+      const double dt = (interpolated_ts[it_i] - ts[t_i]) / (ts[t_i + 1] - ts[t_i]);
+      const Vec3 &p1 = pos[t_i], &p2 = pos[t_i + 1];
+      interpolated_pos.push_back(Vec3{{p1[0] + dt * (p2[0] - p1[0]), p1[1] + dt * (p2[1] - p1[1]), p1[2] + dt * (p2[2] - p1[2])}});
+      interpolated_ori.push_back(so3Interpolate(ori[t_i], ori[t_i + 1], dt));
+      if (++it_i == n) break;
+    } else {
+      if (++t_i == m) break;
+    }
+  }
+  if (interpolated_pos.size() != n)
+    throw std::runtime_error("interpolated_pos.size() (= " + std::to_string(interpolated_pos.size()) + ") != interpolated_ts.size() (= " + std::to_string(n) + ")");
+}
+
 inline bool loadPose(const std::string& filename, Pose& pose) {
   std::ifstream fs(filename.c_str());
   if (!fs.is_open()) { std::cerr << "Could not open file: " << filename << "\n"; return false; }
@@ -182,13 +234,23 @@ void saveSpline(const std::string& trace_dir, Spline& spline) {
 inline void savePose(const std::string& trace_dir, const std::string& fn, const Pose& pose) { std::ofstream f; createTrace(trace_dir, fn, &f); f.precision(9); tracePose(pose, f); }
 inline void savePosition(const std::string& trace_dir, const std::string& fn, const Vec3& p) { std::ofstream f; createTrace(trace_dir, fn, &f); f.precision(9); tracePosition(p, f); }
 inline void saveScalar(const std::string& trace_dir, const std::string& fn, double v) { std::ofstream f; createTrace(trace_dir, fn, &f); f.precision(16); traceScalar(v, f); }
+// traceSplineKnots (save.h:81-96) / saveSplineKnots of fit_spline_to_colmap.cpp:35-44: knot i with the caller's time stamp ts[i], 15 digits
+template <class Spline>
+void saveSplineKnots(const std::string& trace_dir, Spline& spline, const std::vector<double>& ts) {
+  std::ofstream f; createTrace(trace_dir, "spline_knots.txt", &f); f.precision(15);
+  f << "# timestamp tx ty tz qx qy qz qw" << std::endl;
+  for (size_t i = 0; i < spline.numKnots(); ++i) {
+    const Pose k = spline.getKnot((int)i);
+    f << std::setprecision(15) << ts.at(i) << " " << k.p[0] << " " << k.p[1] << " " << k.p[2] << " " << k.q[0] << " " << k.q[1] << " " << k.q[2] << " " << k.q[3] << std::endl;
+  }
+}
 // spline_knots.txt as loadSplineFromFile reads it (the knot time stamps are t0 + i dt)
 template <class Spline>
 void saveSplineKnots(const std::string& trace_dir, const std::string& fn, Spline& spline) {
   std::ofstream f; createTrace(trace_dir, fn, &f);
   f << "# timestamp tx ty tz qx qy qz qw" << std::endl;
   for (size_t i = 0; i < spline.numKnots(); ++i) {
-    const Pose k = spline.getKnot(i);
+    const Pose k = spline.getKnot((int)i);
     f << std::setprecision(17) << (spline.getStartTns() + (int64_t)i * spline.getDeltaTns()) * 1e-9 << " " << k.p[0] << " " << k.p[1] << " " << k.p[2] << " "
       << k.q[0] << " " << k.q[1] << " " << k.q[2] << " " << k.q[3] << std::endl;
   }

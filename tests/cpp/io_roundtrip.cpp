@@ -29,6 +29,21 @@ int main(int argc, char** argv) {
   try { y.as<int>("nope"); } catch (const std::exception&) { threw = true; }
   if (!threw) return 7;
   savePose(d, "T_out.txt", T); savePosition(d, "p_out.txt", v); saveScalar(d, "s_out.txt", sc);
+  // linearInterpolation (trajectory_utils.h:96-143) of a trajectory file at the times of interp_ts.txt (one per line)
+  std::vector<Quat> tq; std::vector<Vec3> tp; std::vector<double> tt;
+  if (loadTrajectoryFromFile(d + "/traj.txt", tq, tp, tt)) {
+    std::vector<double> its; std::ifstream f((d + "/interp_ts.txt").c_str()); double t;
+    while (f >> t) its.push_back(t);
+    std::vector<Quat> oq; std::vector<Vec3> op;
+    linearInterpolation(tp, tq, tt, its, op, oq);
+    for (size_t i = 0; i < its.size(); ++i)
+      std::printf("interp%zu %.17g %.17g %.17g %.17g %.17g %.17g %.17g\n", i, op[i][0], op[i][1], op[i][2], oq[i][0], oq[i][1], oq[i][2], oq[i][3]);
+    its.push_back(tt.back());            // a sample AT the last stamp is never produced: the reference's size assert fires
+    bool thr = false;
+    std::vector<Quat> oq2; std::vector<Vec3> op2;
+    try { linearInterpolation(tp, tq, tt, its, op2, oq2); } catch (const std::runtime_error&) { thr = true; }
+    if (!thr) return 8;
+  }
   std::printf("OK\n");
   return 0;
 }

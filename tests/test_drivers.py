@@ -67,6 +67,33 @@ n_threads: 4
     return yml, os.path.join(d, "align", sub)
 
 
+def _colmap_track(rng, duration_s, hz, t0=1000.0):
+    """COLMAP body estimates: t tx ty tz qx qy qz qw at the camera rate, a smooth track with a little noise"""
+    t = t0 + np.arange(int(duration_s * hz) + 1) / hz
+    p = np.c_[2.0 * np.cos(0.5 * t), 2.0 * np.sin(0.5 * t), 0.3 * np.sin(0.9 * t)] + rng.normal(size=(len(t), 3)) * 0.002
+    q = (Rot.from_rotvec(np.c_[0.2 * np.sin(0.7 * t), 0.1 * np.cos(0.4 * t), 0.5 * t]) * Rot.from_rotvec(rng.normal(size=(len(t), 3)) * 0.001)).as_quat()
+    return t, q, p
+
+
+def _write_traj(fn, t, q, p):
+    with open(fn, "w") as f:
+        f.write("# timestamp tx ty tz qx qy qz qw\n")
+        for i in range(len(t)):
+            f.write(" ".join(f"{v:.17g}" for v in [t[i], *p[i], *q[i]]) + "\n")
+
+
+def _interp(t, q, p, its):
+    """linearInterpolation (util/trajectory_utils.h:96-143) + Sophus::interpolate (interpolate.hpp:27-34), restated with scipy"""
+    op, oq = [], []
+    for x in its:
+        i = int(np.searchsorted(t, x, side="right")) - 1
+        a = (x - t[i]) / (t[i + 1] - t[i])
+        op.append(p[i] + a * (p[i + 1] - p[i]))
+        r1, r2 = Rot.from_quat(q[i]), Rot.from_quat(q[i + 1])
+        oq.append((r1 * Rot.from_rotvec(a * (r1.inv() * r2).as_rotvec())).as_quat())
+    return np.array(op), np.array(oq)
+
+
 def test_io_formats_roundtrip(pkg, tmp_path):
     d = str(tmp_path)
     rng = np.random.default_rng(5)
@@ -84,6 +111,10 @@ def test_io_formats_roundtrip(pkg, tmp_path):
     open(os.path.join(d, "vec.txt"), "w").write("0.5 -0.25 0.125\n")
     open(os.path.join(d, "cfg.yaml"), "w").write('gp_fn: "/a b/c#d.txt"  # comment\nspline_order: 6\nspline_control_nodes_dt_s: 0.1 # [s]\n'
                                                  "optimize_pBP: false\noptimize_spline_globsens_time_offset: True\n")
+    traj_t, traj_q, traj_p = _colmap_track(rng, 2.0, 10.0)
+    _write_traj(os.path.join(d, "traj.txt"), traj_t, traj_q, traj_p)
+    its = np.array([traj_t[0], traj_t[0] + 0.03, traj_t[3], 0.5 * (traj_t[7] + traj_t[8]), traj_t[-1] - 1e-9])
+    np.savetxt(os.path.join(d, "interp_ts.txt"), its, fmt="%.17g")
     exe = _gxx(os.path.join(ROOT, "tests", "cpp", "io_roundtrip.cpp"), str(tmp_path / "io_roundtrip"), pkg)
     out = subprocess.run([exe, d], capture_output=True, text=True, timeout=60)
     assert out.returncode == 0 and out.stdout.strip().endswith("OK"), out.stdout + out.stderr
@@ -103,6 +134,11 @@ def test_io_formats_roundtrip(pkg, tmp_path):
     np.testing.assert_array_equal(pose[4:], [1.5, -2.5, 3.5])
     assert float(kv["scalar"]) == 2.25 and kv["vec"].split() == ["0.5", "-0.25", "0.125"]
     assert kv["yaml"] == "/a b/c#d.txt|6|0.10000000000000001|0|1|0"
+    ip, iq = _interp(traj_t, traj_q, traj_p, its)
+    for i in range(len(its)):
+        v = np.array(kv[f"interp{i}"].split(), dtype=float)
+        np.testing.assert_allclose(v[:3], ip[i], atol=1e-14)
+        assert min(np.abs(v[3:] - iq[i]).max(), np.abs(v[3:] + iq[i]).max()) < 1e-13
     # writers: 3x4 + "0 0 0 1" with 9 significant digits, "# x y z" header, 16-digit scalars (save.h:156-178)
     T_out = np.loadtxt(os.path.join(d, "T_out.txt"))
     assert T_out.shape == (4, 4) and list(T_out[3]) == [0, 0, 0, 1]
@@ -153,3 +189,88 @@ def test_align_tool_end_to_end_on_gpu(pkg, oracle, scene, tmp_path, order, optim
     ref = o.sampleAt(0, t_ns)
     np.testing.assert_allclose(tr[:, 1:], ref, atol=1e-12)
     assert f"Number of errors: {len(case['t_ns'])}" in out.stdout
+
+
+def _write_fit_dataset(d, rng, order, duration_s=8.0, num_errors=150):
+    t, q, p = _colmap_track(rng, duration_s, 20.0)
+    _write_traj(os.path.join(d, "colmap_body_estimates.txt"), t, q, p)
+    yml = os.path.join(d, "fit.yaml")
+    with open(yml, "w") as f:
+        f.write(f"""## Files
+colmap_fn: "{d}/colmap_body_estimates.txt"
+colmap_spline_dir: "{d}/results"
+## Parameters
+start_t: {t[2] - 1e-6:.12f} # time of first image
+end_t: {t[-3] + 1e-6:.12f}
+spline_control_nodes_dt_s: 0.1
+num_errors: {num_errors}
+n_max_iters: 20
+n_threads: 4
+""")
+    return yml, os.path.join(d, "results", "colmap_fitted_spline", f"order_{order}", "dt_100_ms"), (t[2:-2], q[2:-2], p[2:-2])
+
+
+def _fit_pipeline_python(oracle, order, t, q, p, num_errors):
+    """src/fit_spline_to_colmap.cpp:126-190 restated: knots and measurements by linear interpolation, then the oracle's priors"""
+    dt_s = 0.1
+    knots_ts = []
+    x = t[0]
+    while x <= t[-1]:
+        knots_ts.append(x); x += dt_s
+    kp, kq = _interp(t, q, p, knots_ts)
+    dt_meas = (t[-1] - t[0]) / float(num_errors)
+    meas_ts = []
+    x = t[0]
+    while x <= t[-1]:
+        meas_ts.append(x); x += dt_meas
+    mp, mq = _interp(t, q, p, meas_ts)
+    o = oracle.OracleSpline(order, int(dt_s * 1e9), int(t[0] * 1e9))
+    o.setKnots(kq, kp)
+    t_ns = np.array([int(v * 1e9) for v in meas_ts], dtype=np.int64)
+    n_pos = o.addPositionMeasurements(t_ns, mp, 1.0)
+    n_ori = o.addOrientationMeasurements(t_ns, mq, 1.0)
+    return o, np.array(knots_ts), n_pos, n_ori
+
+
+def test_fit_tool_builds_and_fails_loudly_without_gpu(pkg, tmp_path):
+    import torch
+    exe = _gxx(os.path.join(ROOT, "drivers", "fit_spline_to_colmap.cpp"), str(tmp_path / "fit_tool"), pkg)
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    yml, _, _ = _write_fit_dataset(str(tmp_path), np.random.default_rng(2), 6)
+    out = subprocess.run([exe, yml], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 3 and "no CPU fallback" in out.stderr, out.stdout + out.stderr
+    assert "Loaded 161 colmap estimates" in out.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("order", [6, 4])
+def test_fit_tool_end_to_end_on_gpu(pkg, oracle, tmp_path, order):
+    exe = _gxx(os.path.join(ROOT, "drivers", "fit_spline_to_colmap.cpp"), str(tmp_path / "fit_tool"), pkg)
+    num_errors = 150
+    yml, res, (t, q, p) = _write_fit_dataset(str(tmp_path), np.random.default_rng(30 + order), order, num_errors=num_errors)
+    out = subprocess.run([exe, yml, "0", str(order)], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    o, knots_ts, n_pos, n_ori = _fit_pipeline_python(oracle, order, t, q, p, num_errors)
+    assert f"Number of position errors: {n_pos}\n" in out.stdout and f"Number of orientation errors: {n_ori}\n" in out.stdout
+    so = o.optimize(20)
+    kq_o, kp_o = o.getKnots()
+    kn = np.loadtxt(os.path.join(res, "spline_knots.txt"))
+    assert kn.shape == (len(knots_ts), 8)
+    np.testing.assert_allclose(kn[:, 0], knots_ts, rtol=1e-14)
+    # weakly constrained end knots amplify the 1e-8 differences of the LM traces (measured: < 1e-6); the sampled trajectory (what the next
+    # tools consume) is checked far inside the 1 mm / 0.01 deg of north_star
+    np.testing.assert_allclose(kn[:, 1:4], kp_o, atol=1e-5)
+    sgn = np.sign(np.sum(kn[:, 4:] * kq_o, axis=1))[:, None]
+    np.testing.assert_allclose(kn[:, 4:], sgn * kq_o, atol=1e-5)
+    line = [l for l in out.stdout.splitlines() if l.startswith("iterations ")][0]
+    final_cost = float(line.split("->")[1].split(",")[0])
+    assert abs(final_cost - so["final_cost"]) <= 1e-6 * so["final_cost"]
+    tr = np.loadtxt(os.path.join(res, "spline.txt"))
+    end_ns = (len(knots_ts) - order + 1) * 100_000_000 + int(t[0] * 1e9) - 1_000_000
+    t_ns = np.arange(int(t[0] * 1e9), end_ns, 10_000_000, dtype=np.int64)
+    assert tr.shape == (len(t_ns), 8)
+    ref = o.sampleAt(0, t_ns)
+    np.testing.assert_allclose(tr[:, 1:4], ref[:, :3], atol=1e-5)
+    ang = (Rot.from_quat(tr[:, 4:]).inv() * Rot.from_quat(ref[:, 3:])).magnitude()
+    assert ang.max() < np.deg2rad(0.001)
