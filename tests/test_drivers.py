@@ -274,3 +274,52 @@ def test_fit_tool_end_to_end_on_gpu(pkg, oracle, tmp_path, order):
     np.testing.assert_allclose(tr[:, 1:4], ref[:, :3], atol=1e-5)
     ang = (Rot.from_quat(tr[:, 4:]).inv() * Rot.from_quat(ref[:, 3:])).magnitude()
     assert ang.max() < np.deg2rad(0.001)
+
+
+def _write_gpfit_dataset(d, rng, order, num_errors=120):
+    t = 2000.0 + np.arange(160) / 20.0                        # last stamp t0 + 7.95: strictly after the last 0.1 s knot (see the tool's comment)
+    z = np.c_[3.0 * np.cos(0.4 * t), 2.0 * np.sin(0.6 * t), 0.5 * np.sin(0.9 * t)] + rng.normal(size=(len(t), 3)) * 0.01
+    with open(os.path.join(d, "gp.txt"), "w") as f:
+        f.write("# timestamp x y z\n")
+        for i in range(len(t)):
+            f.write(" ".join(f"{v:.17g}" for v in [t[i], *z[i]]) + "\n")
+    yml = os.path.join(d, "gpfit.yaml")
+    with open(yml, "w") as f:
+        f.write(f'gp_fn: "{d}/gp.txt"\nspline_dir: "{d}/results"\nstart_t: {t[0] - 1.0:.6f}\nend_t: {t[-1] + 1.0:.6f}\n'
+                f"spline_control_nodes_dt_s: 0.1\nnum_errors: {num_errors}\nn_max_iters: 20\nn_threads: 4\n")
+    return yml, os.path.join(d, "results", "fit_spline_on_gp_meas", f"order_{order}", "dt_100_ms"), (t, z)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("order", [6, 4])
+def test_gpfit_tool_end_to_end_on_gpu(pkg, oracle, tmp_path, order):
+    """fit_spline_to_gp_measurements: position priors only; the rotation knots are not part of the problem and stay at identity."""
+    exe = _gxx(os.path.join(ROOT, "drivers", "fit_spline_to_gp_measurements.cpp"), str(tmp_path / "gpfit_tool"), pkg)
+    num_errors = 120
+    yml, res, (t, z) = _write_gpfit_dataset(str(tmp_path), np.random.default_rng(70 + order), order, num_errors)
+    out = subprocess.run([exe, yml, "0", str(order)], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    ident = np.tile([0.0, 0.0, 0.0, 1.0], (len(t), 1))
+    knots_ts, x = [], t[0]
+    while x <= t[-1]:
+        knots_ts.append(x); x += 0.1
+    kp, kq = _interp(t, ident, z, knots_ts)
+    dt_meas = (t[-1] - t[0]) / float(num_errors)
+    meas_ts, x = [], t[0]
+    while x <= t[-1]:
+        meas_ts.append(x); x += dt_meas
+    mp, _ = _interp(t, ident, z, meas_ts)
+    o = oracle.OracleSpline(order, 100_000_000, int(t[0] * 1e9))
+    o.setKnots(kq, kp)
+    n_pos = o.addPositionMeasurements(np.array([int(v * 1e9) for v in meas_ts], dtype=np.int64), mp, 1.0)
+    assert f"Number of position errors: {n_pos}\n" in out.stdout
+    so = o.optimize(20)
+    kq_o, kp_o = o.getKnots()
+    kn = np.loadtxt(os.path.join(res, "spline_knots.txt"))
+    assert kn.shape == (len(knots_ts), 8)
+    np.testing.assert_allclose(kn[:, 1:4], kp_o, atol=1e-5)
+    np.testing.assert_array_equal(kn[:, 4:], ident[:len(kn)])
+    line = [l for l in out.stdout.splitlines() if l.startswith("iterations ")][0]
+    assert int(line.split()[1].rstrip(",")) == len(so["iterations"])
+    final_cost = float(line.split("->")[1].split(",")[0])
+    assert abs(final_cost - so["final_cost"]) <= 1e-6 * so["final_cost"]
