@@ -323,3 +323,89 @@ def test_gpfit_tool_end_to_end_on_gpu(pkg, oracle, tmp_path, order):
     assert int(line.split()[1].rstrip(",")) == len(so["iterations"])
     final_cost = float(line.split("->")[1].split(",")[0])
     assert abs(final_cost - so["final_cost"]) <= 1e-6 * so["final_cost"]
+
+
+def _write_colmap_bin(d, cams, images, points):
+    """COLMAP's binary export (reconstruction.cc WriteCamerasBinary / WriteImagesBinary / WritePoints3DBinary)"""
+    import struct
+    with open(os.path.join(d, "cameras.bin"), "wb") as f:
+        f.write(struct.pack("<Q", len(cams)))
+        for c in cams:
+            f.write(struct.pack("<IiQQ", c["id"], c["model"], c["w"], c["h"]))
+            f.write(struct.pack(f"<{len(c['params'])}d", *c["params"]))
+    with open(os.path.join(d, "images.bin"), "wb") as f:
+        f.write(struct.pack("<Q", len(images)))
+        for im in images:
+            f.write(struct.pack("<I4d3dI", im["id"], *im["qwxyz"], *im["t"], im["cam"]))
+            f.write(im["name"].encode() + b"\0")
+            f.write(struct.pack("<Q", len(im["pts"])))
+            for (x, y, pid) in im["pts"]:
+                f.write(struct.pack("<ddQ", x, y, pid))
+    with open(os.path.join(d, "points3D.bin"), "wb") as f:
+        f.write(struct.pack("<Q", len(points)))
+        for pt in points:
+            f.write(struct.pack("<Q3d3Bd", pt["id"], *pt["xyz"], 10, 20, 30, pt["err"]))
+            f.write(struct.pack("<Q", len(pt["track"])))
+            for (im_id, p2) in pt["track"]:
+                f.write(struct.pack("<II", im_id, p2))
+
+
+def _kept_points(pts):
+    """the selection rules of readImagesAndPoints3DBinary (sensor/camera.h:340-385), restated"""
+    INVALID = 2 ** 64 - 1
+    xs, ys, seen, kept = {}, {}, [], []
+    for j, (x, y, pid) in enumerate(pts):
+        if pid == INVALID: continue
+        if x in xs and y in ys and xs[x] == ys[y]: continue
+        if pid in seen: continue
+        kept.append((j, x, y, pid)); seen.append(pid)
+        xs[x] = j; ys[y] = j
+    return kept
+
+
+def test_colmap_binary_ingest(tmp_path):
+    d = str(tmp_path)
+    rng = np.random.default_rng(9)
+    INVALID = 2 ** 64 - 1
+    # OPENCV_FISHEYE (8 parameters) is read exactly; OPENCV (model 4, 8 parameters) is read as fx fy cx cy + 8 doubles, i.e. four past its
+    # record (the reference's quirk, SURVEY A7) — harmless only for the last camera of the file, which is where it is put here
+    cams = [dict(id=1, model=5, w=640, h=480, params=[278.6, 278.5, 319.5, 241.2, -0.013, 0.02, -0.01, 0.003]),
+            dict(id=2, model=4, w=752, h=480, params=[458.6, 457.3, 367.2, 248.4, -0.28, 0.07, 1.9e-4, 1.8e-5])]
+    points = [dict(id=int(i), xyz=rng.normal(size=3) * 4, err=float(rng.random()), track=[(1, 0), (2, 3)]) for i in (7, 3, 900000000000, 12, 5)]
+    points.append(dict(id=3, xyz=[9.0, 9.0, 9.0], err=1.0, track=[(3, 1)]))          # repeated id: the first record wins
+    images = []
+    for k in range(3):
+        pts = [(float(x), float(y), int(pid)) for x, y, pid in zip(rng.uniform(0, 700, 9), rng.uniform(0, 470, 9), [7, INVALID, 3, 12, INVALID, 5, 900000000000, 44, 7])]
+        pts.insert(4, (pts[0][0], pts[0][1], 3 if k else 99))    # exact duplicate of point 0 (note 1), whatever its 3-D id
+        pts.insert(6, (pts[2][0], 123.25, 12))                   # same x as an earlier point, different y: kept unless its 3-D id was seen
+        q = Rot.from_rotvec(rng.normal(size=3)).as_quat() * 1.7  # un-normalised on disk
+        images.append(dict(id=k + 1, qwxyz=[q[3], q[0], q[1], q[2]], t=list(rng.normal(size=3)), cam=1 + k % 2, name=f"cam0/{1000 + k}.png", pts=pts))
+    _write_colmap_bin(d, cams, images, points)
+    exe = str(tmp_path / "colmap_ingest")
+    subprocess.check_call(["g++", "-std=c++14", "-O1", "-Wall", "-Werror", os.path.join(ROOT, "tests", "cpp", "colmap_ingest.cpp"), "-o", exe])
+    out = subprocess.run([exe, d], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 0 and out.stdout.strip().endswith("OK"), out.stdout + out.stderr
+    L = [l.split() for l in out.stdout.splitlines()]
+    cam_l = [l for l in L if l[0] == "cam"]
+    assert [int(cam_l[0][1]), int(cam_l[0][2]), int(cam_l[0][9])] == [1, 5, 4] and [int(cam_l[1][1]), int(cam_l[1][2]), int(cam_l[1][9])] == [2, 4, 8]
+    for c in range(2):
+        assert [int(cam_l[c][3]), int(cam_l[c][4])] == [cams[c]["w"], cams[c]["h"]]
+        np.testing.assert_array_equal(np.array(cam_l[c][5:9], dtype=float), cams[c]["params"][:4])
+        np.testing.assert_array_equal(np.array(cam_l[c][10:14], dtype=float), cams[c]["params"][4:8])
+    fr_l = [l for l in L if l[0] == "frame"]; pt_l = [l for l in L if l[0] == "pt"]; lm_l = [l for l in L if l[0] == "lm"]
+    assert len(fr_l) == 3
+    ids = [p["id"] for p in points[:5]]
+    for k, im in enumerate(images):
+        assert int(fr_l[k][1]) == k and fr_l[k][3] == im["name"]
+        q = np.array(fr_l[k][4:8], dtype=float)
+        qn = np.array(im["qwxyz"])[[1, 2, 3, 0]]; qn = qn / np.linalg.norm(qn)
+        np.testing.assert_allclose(q, qn, atol=1e-16)
+        np.testing.assert_array_equal(np.array(fr_l[k][8:11], dtype=float), im["t"])
+        kept = _kept_points(im["pts"])
+        got = [(int(l[2]), float(l[3]), float(l[4]), int(l[5]), int(l[6])) for l in pt_l if int(l[1]) == k]
+        assert int(fr_l[k][11]) == len(kept) == len(got)
+        for (j, x, y, pid), g in zip(kept, got):
+            assert g[:4] == (j, x, y, pid) and g[4] == (ids.index(pid) if pid in ids else -1)
+    assert [int(l[2]) for l in lm_l] == ids
+    np.testing.assert_array_equal(np.array(lm_l[1][3:6], dtype=float), points[1]["xyz"])     # id 3: the first record
+    assert all(int(l[7]) == 2 for l in lm_l)
