@@ -10,6 +10,7 @@
 // Writers: createTrace / tracePose / tracePosition / traceScalar / traceSpline   /root/reference/include/util/save.h:25-39, 99-117, 156-178
 // YAML: the experiment files are flat `key: value` maps (experiments/**/**.yaml); Yaml reads exactly that subset.
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <fstream>
@@ -164,6 +165,88 @@ inline void linearInterpolation(const std::vector<Vec3>& pos, const std::vector<
   }
   if (interpolated_pos.size() != n)
     throw std::runtime_error("interpolated_pos.size() (= " + std::to_string(interpolated_pos.size()) + ") != interpolated_ts.size() (= " + std::to_string(n) + ")");
+}
+
+// ---- rigid transforms on Pose (Sophus::SE3d as far as the drivers use it) ----
+inline Vec3 rotate(const Quat& q, const Vec3& v) { double R[9]; matrixFromQuat(q, R); return Vec3{{R[0] * v[0] + R[1] * v[1] + R[2] * v[2], R[3] * v[0] + R[4] * v[1] + R[5] * v[2], R[6] * v[0] + R[7] * v[1] + R[8] * v[2]}}; }
+inline Pose poseInverse(const Pose& T) { const Quat qi = quatInverse(T.q); const Vec3 t = rotate(qi, T.p); return Pose{{-t[0], -t[1], -t[2]}, qi}; }
+
+// loadFrameTimes (util/colmap_utils.h:14-42): first column of colmap_cam_estimates.txt
+inline bool loadFrameTimes(const std::string& filename, std::vector<double>& timestamps) {
+  std::vector<Quat> q; std::vector<Vec3> p;
+  return loadSplineFromFile(filename, q, p, timestamps);
+}
+
+// SimpleCamImuCalib + loadEuRoCSimpleCamImuCalib (util/load_calibration.h:20-60, 166-201): the EuRoC-format calibration YAML
+// (datasets/EuRoC/calib/*/calib.yaml: cameras: [- camera: {...}, T_B_C: {...}], imu_params: {...}), read with a reader for that layout.
+// The UZH-FPV (Kalibr camchain) variant, loadUZHFPVSimpleCamImuCalib, is not built.
+struct SimpleCamImuCalib {
+  int idx_ = 0;
+  std::string camera_model_, distortion_model_;
+  double resolution_[2] = {0, 0}, distortion_coeffs_[4] = {0, 0, 0, 0}, intrinsics_[4] = {0, 0, 0, 0};
+  Pose T_cam_imu_{{{0, 0, 0}}, {{0, 0, 0, 1}}};
+  double timeshift_cam_imu_ = 0, imu_rate_ = 0, acc_noise_density_ = 0, acc_random_walk_ = 0, gyro_noise_density_ = 0, gyro_random_walk_ = 0;
+};
+namespace detail {
+inline std::string valueAfter(const std::string& seg, const std::string& key, size_t from = 0) {   // "key: value" -> value (to end of line / comment)
+  const size_t k = seg.find(key, from);
+  if (k == std::string::npos) throw std::runtime_error("calibration yaml: missing '" + key + "'");
+  size_t e = seg.find('\n', k);
+  std::string v = seg.substr(k + key.size(), (e == std::string::npos ? seg.size() : e) - k - key.size());
+  const size_t h = v.find('#'); if (h != std::string::npos) v = v.substr(0, h);
+  const size_t a = v.find_first_not_of(" \t\r\"'"), b = v.find_last_not_of(" \t\r\"'");
+  return a == std::string::npos ? std::string() : v.substr(a, b - a + 1);
+}
+inline std::vector<double> dataAfter(const std::string& seg, const std::string& section) {       // section: ... data: [a, b, ...] (may span lines)
+  const size_t k = seg.find(section);
+  if (k == std::string::npos) throw std::runtime_error("calibration yaml: missing '" + section + "'");
+  const size_t d = seg.find("data:", k), lb = seg.find('[', d), rb = seg.find(']', lb);
+  if (d == std::string::npos || lb == std::string::npos || rb == std::string::npos) throw std::runtime_error("calibration yaml: no data list after '" + section + "'");
+  std::string body = seg.substr(lb + 1, rb - lb - 1);
+  for (char& c : body) if (c == ',') c = ' ';
+  std::istringstream ss(body); std::vector<double> out; double v;
+  while (ss >> v) out.push_back(v);
+  return out;
+}
+}  // namespace detail
+inline bool loadEuRoCSimpleCamImuCalib(const std::string& calib_fn, int cam_id, SimpleCamImuCalib& calib) {
+  std::ifstream fs(calib_fn.c_str());
+  if (!fs.is_open()) throw std::runtime_error("Could not open yaml file: " + calib_fn);   // YAML::LoadFile throws BadFile
+  std::vector<std::string> lines; std::string line;
+  while (std::getline(fs, line)) lines.push_back(line);
+  auto top_level = [](const std::string& l) { return !l.empty() && l[0] != ' ' && l[0] != '\t' && l[0] != '#' && l[0] != '-'; };
+  std::vector<size_t> cams;
+  size_t imu_line = lines.size();
+  for (size_t i = 0; i < lines.size(); ++i) {
+    const size_t a = lines[i].find_first_not_of(" \t");
+    if (a != std::string::npos && lines[i].compare(a, 9, "- camera:") == 0) cams.push_back(i);
+    if (lines[i].compare(0, 11, "imu_params:") == 0) imu_line = i;
+  }
+  if (cam_id < 0 || (size_t)cam_id >= cams.size() || imu_line == lines.size()) throw std::runtime_error("calibration yaml: camera " + std::to_string(cam_id) + " or imu_params not found");
+  auto segment = [&](size_t b, bool stop_at_camera) {
+    std::string seg;
+    for (size_t i = b; i < lines.size(); ++i) {
+      if (i > b && (top_level(lines[i]) || (stop_at_camera && std::find(cams.begin(), cams.end(), i) != cams.end()))) break;
+      seg += lines[i]; seg += '\n';
+    }
+    return seg;
+  };
+  const std::string cam = segment(cams[(size_t)cam_id], true), imu = segment(imu_line, false);
+  calib.idx_ = cam_id;
+  calib.camera_model_ = detail::valueAfter(cam, " type:");
+  calib.resolution_[0] = std::stod(detail::valueAfter(cam, "image_width:")); calib.resolution_[1] = std::stod(detail::valueAfter(cam, "image_height:"));
+  calib.distortion_model_ = detail::valueAfter(cam, " type:", cam.find("distortion:"));
+  const std::vector<double> dc = detail::dataAfter(cam, "distortion:"), in = detail::dataAfter(cam, "intrinsics:"), T = detail::dataAfter(cam, "T_B_C:");
+  if (dc.size() < 4 || in.size() < 4 || T.size() < 16) throw std::runtime_error("calibration yaml: short data list");
+  for (int i = 0; i < 4; ++i) { calib.distortion_coeffs_[i] = dc[i]; calib.intrinsics_[i] = in[i]; }
+  const double R[9] = {T[0], T[1], T[2], T[4], T[5], T[6], T[8], T[9], T[10]};           // the list is row-major (Matrix4d(data).transpose(), :189-190)
+  Pose T_imu_cam{{{T[3], T[7], T[11]}}, quatFromMatrix(R)};
+  calib.T_cam_imu_ = poseInverse(T_imu_cam);
+  calib.timeshift_cam_imu_ = -1.0 * std::stod(detail::valueAfter(imu, "delay_imu_cam:"));
+  calib.imu_rate_ = std::stod(detail::valueAfter(imu, "imu_rate:"));
+  calib.acc_noise_density_ = std::stod(detail::valueAfter(imu, "sigma_acc_c:")); calib.acc_random_walk_ = std::stod(detail::valueAfter(imu, "sigma_acc_bias_c:"));
+  calib.gyro_noise_density_ = std::stod(detail::valueAfter(imu, "sigma_omega_c:")); calib.gyro_random_walk_ = std::stod(detail::valueAfter(imu, "sigma_omega_bias_c:"));
+  return true;
 }
 
 inline bool loadPose(const std::string& filename, Pose& pose) {

@@ -409,3 +409,144 @@ def test_colmap_binary_ingest(tmp_path):
     assert [int(l[2]) for l in lm_l] == ids
     np.testing.assert_array_equal(np.array(lm_l[1][3:6], dtype=float), points[1]["xyz"])     # id 3: the first record
     assert all(int(l[7]) == 2 for l in lm_l)
+
+
+def _t_of(t_ns):
+    """what static_cast<int64_t>(t * 1e9) gives for a stamp written with 17 digits"""
+    return int(float(f"{t_ns * 1e-9:.17g}") * 1e9)
+
+
+def _write_gv_dataset(d, sc, order, T_wg_q, T_wg_p, flags):
+    """A scene of scene.make_scene as the files optimize_gv_continuous_time reads."""
+    R_wg = Rot.from_quat(T_wg_q)
+    dt_ms = int(sc["dt_ns"] * 1e-9 * 1000)
+    sub = f"order_{order}/dt_{dt_ms}_ms"
+    for k in ("fitted", "align"): os.makedirs(os.path.join(d, k, sub))
+    os.makedirs(os.path.join(d, "colmap"))
+    kq_g = (R_wg.inv() * Rot.from_quat(sc["knot_q"])).as_quat(); kp_g = R_wg.inv().apply(sc["knot_p"] - T_wg_p) / sc["scale"]
+    lm_g = R_wg.inv().apply(sc["landmarks"] - T_wg_p) / sc["scale"]
+    with open(os.path.join(d, "fitted", sub, "spline_knots.txt"), "w") as f:
+        f.write("# timestamp tx ty tz qx qy qz qw\n")
+        for i in range(len(kq_g)):
+            f.write(" ".join(f"{v:.17g}" for v in [(sc["start_t_ns"] + i * sc["dt_ns"]) * 1e-9, *kp_g[i], *kq_g[i]]) + "\n")
+    _write_pose(os.path.join(d, "align", sub, "T_wg_init.txt"), T_wg_q, T_wg_p, digits=17)
+    open(os.path.join(d, "align", sub, "scale_init.txt"), "w").write(f"{sc['scale']:.17g}\n")
+    open(os.path.join(d, "align", sub, "p_bp.txt"), "w").write("# x y z\n" + " ".join(f"{v:.17g}" for v in sc["p_bp"]) + "\n")
+    with open(os.path.join(d, "gp.txt"), "w") as f:
+        f.write("# timestamp x y z\n")
+        for t, z in zip(sc["gp_t_ns"], sc["gp_pos"]):
+            f.write(" ".join(f"{v:.17g}" for v in [t * 1e-9, *z]) + "\n")
+    F = len(sc["frame_t_ns"])
+    with open(os.path.join(d, "colmap", "colmap_cam_estimates.txt"), "w") as f:
+        f.write("# timestamp tx ty tz qx qy qz qw\n")
+        for t in sc["frame_t_ns"]:
+            f.write(f"{t * 1e-9:.17g} 0 0 0 0 0 0 1\n")
+    ids = [10 + 3 * i for i in range(len(lm_g))]
+    cams = [dict(id=1, model=sc["cam_model"], w=sc["width"], h=sc["height"], params=list(sc["intr"]) + list(sc["dist"]))]
+    images = []
+    for f_ in range(F):
+        b, e = sc["obs_begin"][f_], sc["obs_begin"][f_ + 1]
+        pts = [(float(sc["uv"][q, 0]), float(sc["uv"][q, 1]), ids[sc["lm_index"][q]]) for q in range(b, e)]
+        pts.insert(0, (5.0, 5.0, 2 ** 64 - 1))                      # a 2-D point without a 3-D point
+        images.append(dict(id=f_ + 1, qwxyz=[1.0, 0, 0, 0], t=[0.0, 0, 0], cam=1, name=f"{f_}.png", pts=pts))
+    points = [dict(id=ids[i], xyz=list(lm_g[i]), err=0.5, track=[]) for i in range(len(lm_g))]
+    _write_colmap_bin(os.path.join(d, "colmap"), cams, images, points)
+    R_bc = Rot.from_quat(sc["q_bc"]).as_matrix()
+    rows = [list(R_bc[r]) + [sc["p_bc"][r]] for r in range(3)] + [[0.0, 0.0, 0.0, 1.0]]
+    with open(os.path.join(d, "calib.yaml"), "w") as f:
+        f.write("label: \"synthetic\"\ncameras:\n- camera:\n    label: cam0\n    image_height: %d\n    image_width: %d\n    type: pinhole\n" % (sc["height"], sc["width"]))
+        f.write("    intrinsics:\n      cols: 1\n      rows: 4\n      data: [%s]\n" % ", ".join(f"{v:.17g}" for v in sc["intr"]))
+        f.write("    distortion:\n      type: radial-tangential\n      parameters:\n        cols: 1\n        rows: 4\n        data: [%s,\n    %s]\n"
+                % (", ".join(f"{v:.17g}" for v in sc["dist"][:3]), f"{sc['dist'][3]:.17g}"))
+        f.write("  T_B_C:\n    cols: 4\n    rows: 4\n    data: [%s]\n" % ",\n           ".join(", ".join(f"{v:.17g}" for v in r) for r in rows))
+        f.write("\nimu_params:\n  delay_imu_cam: %.17g\n  sigma_omega_c: 0.05\n  sigma_acc_c: 0.1\n  sigma_omega_bias_c: 4.0e-05\n  sigma_acc_bias_c: 0.002\n  imu_rate: 200\n"
+                % (-sc["t_offset_cam_imu"]))
+    yml = os.path.join(d, "gv.yaml")
+    with open(yml, "w") as f:
+        f.write(f"""dataset: Custom
+cam_id: 0
+camimu_calib_fn: "{d}/calib.yaml"
+gp_fn: "{d}/gp.txt"
+colmap_dir: "{d}/colmap/"
+colmap_spline_dir: "{d}/fitted"
+spline_global_ref_alignment_dir: "{d}/align"
+full_batch_optimization_dir: "{d}/full_batch"
+spline_control_nodes_dt_s: {sc['dt_ns'] * 1e-9}
+sampling_spline_rate: 50.0
+grid_cell_size: 30
+gp_std: {sc['gp_std']}
+sigma_reproj_px: {sc['sigma_reproj_px']}
+optimize_scale: {'true' if flags[0] else 'false'}
+optimize_pBP: {'true' if flags[1] else 'false'}
+optimize_spline_globsens_time_offset: {'true' if flags[4] else 'false'}
+n_max_outer_iters: 3
+n_max_inner_iters: 4
+n_threads: 4
+""")
+    return yml, os.path.join(d, "full_batch", "continuous_time", sub), (kq_g, kp_g, lm_g)
+
+
+def _gv_scene(scene, order):
+    flags = (True, True, False, True, True)     # the driver leaves optimize_camimu_extrinsics at the constructor default (true)
+    return scene.make_scene(order=order, duration_s=3.0, n_landmarks=160, track_len=9, imu_hz=0, gp_hz=10, flags=flags, seed=77 + order), flags
+
+
+def test_gv_driver_builds_and_fails_loudly_without_gpu(pkg, scene, tmp_path):
+    import torch
+    exe = _gxx(os.path.join(ROOT, "drivers", "optimize_gv_continuous_time.cpp"), str(tmp_path / "gv"), pkg)
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    sc, flags = _gv_scene(scene, 6)
+    yml, _, _ = _write_gv_dataset(str(tmp_path), sc, 6, Rot.from_rotvec([0.2, -0.4, 1.0]).as_quat(), np.array([3.0, -2.0, 1.0]), flags)
+    out = subprocess.run([exe, yml], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 3 and "no CPU fallback" in out.stderr, out.stdout + out.stderr
+    # everything up to the construction of the spline ran: calibration, measurements, COLMAP export, knots
+    assert f"Loaded {len(sc['gp_t_ns'])} global measurements" in out.stdout and f"Loaded: {len(sc['frame_t_ns'])} images" in out.stdout
+    assert f"Loaded: {len(sc['landmarks'])} 3D points" in out.stdout and f"Loaded {len(sc['knot_q'])} initial spline knots" in out.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("order", [6, 4])
+def test_gv_driver_end_to_end_on_gpu(pkg, oracle, scene, tmp_path, order):
+    exe = _gxx(os.path.join(ROOT, "drivers", "optimize_gv_continuous_time.cpp"), str(tmp_path / "gv"), pkg)
+    sc, flags = _gv_scene(scene, order)
+    T_q, T_p = Rot.from_rotvec([0.2, -0.4, 1.0]).as_quat(), np.array([3.0, -2.0, 1.0])
+    yml, res, (kq_g, kp_g, lm_g) = _write_gv_dataset(str(tmp_path), sc, order, T_q, T_p, flags)
+    out = subprocess.run([exe, yml, "0", str(order)], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    # the oracle through the same steps (src/optimize_gv_continuous_time.cpp:320-511)
+    R_wg = Rot.from_quat(T_q)
+    o = oracle.OracleSpline(order, sc["dt_ns"], sc["start_t_ns"])
+    o.setCamera(sc["cam_model"], sc["intr"], sc["dist"], sc["q_bc"], sc["p_bc"], sc["t_offset_cam_imu"])
+    o.setKnots((R_wg * Rot.from_quat(kq_g)).as_quat(), sc["scale"] * R_wg.apply(kp_g) + T_p)
+    o.setGlobals(sc["scale"], sc["p_bp"], np.zeros(3), 0.0)
+    o.setFlags(*flags)
+    o.set3DPoints(sc["scale"] * R_wg.apply(lm_g) + T_p)
+    t_fr = np.array([_t_of(t) for t in sc["frame_t_ns"]], dtype=np.int64)
+    valid, _ = o.computeValidReprojections(t_fr, sc["obs_begin"], sc["uv"], sc["lm_index"], sc["width"], sc["height"], 30)
+    o.addGp(np.array([_t_of(t) for t in sc["gp_t_ns"]], dtype=np.int64), sc["gp_pos"], sc["gp_std"])
+    ob = np.r_[0, np.cumsum([valid[sc["obs_begin"][f]:sc["obs_begin"][f + 1]].sum() for f in range(len(t_fr))])].astype(np.int32)
+    o.addFrames(t_fr, ob, sc["uv"][valid], sc["lm_index"][valid], sc["sigma_reproj_px"])
+    assert f"valid reprojections: {int(valid.sum())}\n" in out.stdout
+    s = o.optimize(1); o.relinearize()
+    costs = [s["final_cost"]]
+    for _ in range(3):
+        s = o.optimize(4); o.relinearize(); costs.append(s["final_cost"])
+        if s["termination_type"] == 0: break
+    got = [float(l.split("->")[1].split(",")[0]) for l in out.stdout.splitlines() if l.startswith("solve ")]
+    assert len(got) == len(costs)
+    np.testing.assert_allclose(got, costs, rtol=1e-6)
+    g = o.getGlobals()
+    assert abs(float(open(os.path.join(res, "scale.txt")).read()) - (g[18] + g[0])) < 1e-7
+    assert abs(float(open(os.path.join(res, "spline_globalsensor_time_offset.txt")).read()) - g[17]) < 1e-7
+    np.testing.assert_allclose(np.loadtxt(os.path.join(res, "p_bp.txt")), g[10:13], atol=1e-6)
+    np.testing.assert_allclose(np.loadtxt(os.path.join(res, "points3D.txt")), o.get3DPoints(), atol=1e-5)
+    tr = np.loadtxt(os.path.join(res, "spline.txt"))
+    end_ns = (len(sc["knot_q"]) - order + 1) * sc["dt_ns"] + sc["start_t_ns"] - 1_000_000
+    t_ns = np.arange(sc["start_t_ns"], end_ns, 20_000_000, dtype=np.int64)
+    assert tr.shape == (len(t_ns), 8)
+    ref = o.sampleAt(0, t_ns)
+    np.testing.assert_allclose(tr[:, 1:4], ref[:, :3], atol=1e-5)                     # north_star: 1 mm / 0.01 deg
+    assert (Rot.from_quat(tr[:, 4:]).inv() * Rot.from_quat(ref[:, 3:])).magnitude().max() < np.deg2rad(0.001)
+    for fn in ("initial_spline.txt", "initial_points3D.txt", "initial_scale.txt", "initial_p_bp.txt", "gravity.txt", "initial_reprojection_errors.txt"):
+        assert os.path.exists(os.path.join(res, fn))
