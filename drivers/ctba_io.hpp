@@ -46,6 +46,21 @@ inline bool loadGpMeasurements(const std::string& filename, std::vector<GlobalPo
   return true;
 }
 
+// loadImuMeasurementsFromFile (sensor/imu.h:355-388): id t wx wy wz ax ay az
+struct ImuMeasurement { double t; Vec3 lin_acc, ang_vel; };
+inline bool loadImuMeasurementsFromFile(const std::string& filename, std::vector<ImuMeasurement>& measurements) {
+  std::ifstream fs(filename.c_str());
+  if (!fs.is_open()) { std::cerr << "Could not open imu file: " << filename << "\n"; return false; }
+  while (fs.good() && !fs.eof()) {
+    skipComment(fs);
+    size_t imu_id = 0; double stamp = 0, wx = 0, wy = 0, wz = 0, ax = 0, ay = 0, az = 0;
+    fs >> imu_id >> stamp >> wx >> wy >> wz >> ax >> ay >> az;
+    measurements.push_back(ImuMeasurement{stamp, Vec3{{ax, ay, az}}, Vec3{{wx, wy, wz}}});
+  }
+  if (!measurements.empty()) measurements.pop_back();
+  return true;
+}
+
 inline Quat normalized(const Quat& q) {   // Sophus::SO3d(Eigen::Quaterniond) normalises (so3.hpp:481-487)
   const double n = std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
   return Quat{{q[0] / n, q[1] / n, q[2] / n, q[3] / n}};
@@ -346,7 +361,7 @@ class Yaml {
     std::ifstream fs(fn.c_str());
     if (!fs.is_open()) throw std::runtime_error("Could not open yaml file: " + fn);
     Yaml y;
-    std::string line;
+    std::string line, open_key;
     while (std::getline(fs, line)) {
       bool in_q = false; char qc = 0; size_t cut = line.size();
       for (size_t i = 0; i < line.size(); ++i) {
@@ -356,15 +371,29 @@ class Yaml {
         else if (c == '#' && (i == 0 || line[i - 1] == ' ' || line[i - 1] == '\t')) { cut = i; break; }
       }
       line = line.substr(0, cut);
+      if (!open_key.empty()) {                       // continuation of a flow sequence `key: [a, b,` ... `c]`
+        y.kv_[open_key] += " " + trim(line);
+        if (line.find(']') != std::string::npos) open_key.clear();
+        continue;
+      }
       const size_t colon = line.find(':');
       if (colon == std::string::npos) continue;
       std::string key = trim(line.substr(0, colon)), val = trim(line.substr(colon + 1));
       if (val.size() >= 2 && (val.front() == '"' || val.front() == '\'') && val.back() == val.front()) val = val.substr(1, val.size() - 2);
       if (!key.empty()) y.kv_[key] = val;
+      if (!key.empty() && val.find('[') != std::string::npos && val.find(']') == std::string::npos) open_key = key;
     }
     return y;
   }
   bool has(const std::string& k) const { return kv_.count(k) != 0; }
+  // config["k"].as<std::vector<double>>() for a one-line flow sequence `k: [a, b, c]`
+  std::vector<double> asList(const std::string& k) const {
+    std::string v = as<std::string>(k);
+    for (char& c : v) if (c == '[' || c == ']' || c == ',') c = ' ';
+    std::istringstream ss(v); std::vector<double> out; double d;
+    while (ss >> d) out.push_back(d);
+    return out;
+  }
   template <class T> T as(const std::string& k) const {
     auto it = kv_.find(k);
     if (it == kv_.end()) throw std::runtime_error("yaml: missing key '" + k + "'");   // yaml-cpp throws InvalidNode / BadConversion

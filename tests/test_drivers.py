@@ -550,3 +550,122 @@ def test_gv_driver_end_to_end_on_gpu(pkg, oracle, scene, tmp_path, order):
     assert (Rot.from_quat(tr[:, 4:]).inv() * Rot.from_quat(ref[:, 3:])).magnitude().max() < np.deg2rad(0.001)
     for fn in ("initial_spline.txt", "initial_points3D.txt", "initial_scale.txt", "initial_p_bp.txt", "gravity.txt", "initial_reprojection_errors.txt"):
         assert os.path.exists(os.path.join(res, fn))
+
+
+def _write_vi_dataset(d, sc, order, T_wg_q, T_wg_p, flags):
+    """the gv dataset plus imu.txt and the keys of full_batch_optimization_vi/continuous_time/*.yaml (T_wg inline over several lines)"""
+    _, _, g = _write_gv_dataset(d, sc, order, T_wg_q, T_wg_p, flags)
+    with open(os.path.join(d, "imu.txt"), "w") as f:
+        f.write("# id timestamp wx wy wz ax ay az\n")
+        for i, (t, w, a) in enumerate(zip(sc["imu_t_ns"], sc["imu_gyr"], sc["imu_acc"])):
+            f.write(f"{i} " + " ".join(f"{v:.17g}" for v in [t * 1e-9, *w, *a]) + "\n")
+    R = Rot.from_quat(T_wg_q).as_matrix()
+    rows = [", ".join(f"{v:.17g}" for v in list(R[r]) + [T_wg_p[r]]) for r in range(3)] + ["0.0, 0.0, 0.0, 1.0"]
+    dt_ms = int(sc["dt_ns"] * 1e-9 * 1000)
+    yml = os.path.join(d, "vi.yaml")
+    with open(yml, "w") as f:
+        f.write(f"""dataset: Custom
+cam_id: 0
+camimu_calib_fn: "{d}/calib.yaml"
+imu_fn: "{d}/imu.txt"
+colmap_dir: "{d}/colmap/"
+colmap_spline_dir: "{d}/fitted"
+full_batch_optimization_dir: "{d}/full_batch_vi"
+spline_control_nodes_dt_s: {sc['dt_ns'] * 1e-9}
+bias_spline_control_nodes_dt_s: {sc['dt_s_bias']}
+init_acc_bias: [0.0, 0.0, 0.0]
+init_gyro_bias: [0.0, 0.0, 0.0]
+sampling_spline_rate: 50.0
+grid_cell_size: 30
+sigma_reproj_px: {sc['sigma_reproj_px']}
+sigma_acc_c: {sc['sigma_acc_c']}
+sigma_acc_bias_c: {sc['sigma_acc_bias_c']}
+sigma_omega_c: {sc['sigma_omega_c']}
+sigma_omega_bias_c: {sc['sigma_omega_bias_c']}
+bias_err_freq_hz: {sc['bias_err_freq_hz']}
+bias_err_dt_s: {sc['bias_err_dt_s']}
+initial_scale: {sc['scale']}
+T_wg: [{rows[0]},
+       {rows[1]},
+       {rows[2]},
+       {rows[3]}]
+optimize_scale: {'true' if flags[0] else 'false'}
+optimize_gravity: {'true' if flags[2] else 'false'}
+optimize_camimu_extrinsics: {'true' if flags[3] else 'false'}
+n_max_outer_iters: 2
+n_max_inner_iters: 4
+n_threads: 4
+""")
+    return yml, os.path.join(d, "full_batch_vi", "continuous_time", f"order_{order}", f"dt_{dt_ms}_ms"), g
+
+
+def _vi_scene(scene, order):
+    flags = (False, True, True, True, True)
+    sc = scene.make_scene(order=order, duration_s=3.0, n_landmarks=160, track_len=9, imu_hz=200, gp_hz=0, dt_s_bias=0.25, flags=flags, seed=99 + order)
+    return sc, flags
+
+
+def test_vi_driver_builds_and_fails_loudly_without_gpu(pkg, scene, tmp_path):
+    import torch
+    exe = _gxx(os.path.join(ROOT, "drivers", "optimize_vi_continuous_time.cpp"), str(tmp_path / "vi"), pkg)
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    sc, flags = _vi_scene(scene, 6)
+    yml, _, _ = _write_vi_dataset(str(tmp_path), sc, 6, Rot.from_rotvec([0.2, -0.4, 1.0]).as_quat(), np.array([3.0, -2.0, 1.0]), flags)
+    out = subprocess.run([exe, yml], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 3 and "no CPU fallback" in out.stderr, out.stdout + out.stderr
+    assert f"Loaded {len(sc['imu_t_ns'])} imu measurements" in out.stdout and f"Loaded {len(sc['knot_q'])} initial spline knots" in out.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("order", [6, 4])
+def test_vi_driver_end_to_end_on_gpu(pkg, oracle, scene, tmp_path, order):
+    exe = _gxx(os.path.join(ROOT, "drivers", "optimize_vi_continuous_time.cpp"), str(tmp_path / "vi"), pkg)
+    sc, flags = _vi_scene(scene, order)
+    T_q, T_p = Rot.from_rotvec([0.2, -0.4, 1.0]).as_quat(), np.array([3.0, -2.0, 1.0])
+    yml, res, (kq_g, kp_g, lm_g) = _write_vi_dataset(str(tmp_path), sc, order, T_q, T_p, flags)
+    out = subprocess.run([exe, yml, "0", str(order)], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    R_wg = Rot.from_quat(T_q)
+    o = oracle.OracleSpline(order, sc["dt_ns"], sc["start_t_ns"])
+    o.setCamera(sc["cam_model"], sc["intr"], sc["dist"], sc["q_bc"], sc["p_bc"], sc["t_offset_cam_imu"])
+    o.setKnots((R_wg * Rot.from_quat(kq_g)).as_quat(), sc["scale"] * R_wg.apply(kp_g) + T_p)
+    o.setGlobals(sc["scale"], np.zeros(3), np.array([0.0, 0.0, 9.80665]), 0.0)
+    o.setFlags(*flags)
+    o.set3DPoints(sc["scale"] * R_wg.apply(lm_g) + T_p)
+    o.addGravityNormError()
+    o.initializeBiases(sc["dt_s_bias"], np.zeros(3), np.zeros(3))
+    t_fr = np.array([_t_of(t) for t in sc["frame_t_ns"]], dtype=np.int64)
+    valid, _ = o.computeValidReprojections(t_fr, sc["obs_begin"], sc["uv"], sc["lm_index"], sc["width"], sc["height"], 30)
+    n_imu = o.addImu(np.array([_t_of(t) for t in sc["imu_t_ns"]], dtype=np.int64), sc["imu_acc"], sc["imu_gyr"], sc["sigma_acc_c"], sc["sigma_omega_c"])
+    ob = np.r_[0, np.cumsum([valid[sc["obs_begin"][f]:sc["obs_begin"][f + 1]].sum() for f in range(len(t_fr))])].astype(np.int32)
+    o.addFrames(t_fr, ob, sc["uv"][valid], sc["lm_index"][valid], sc["sigma_reproj_px"])
+    o.addImuBiasCost(sc["bias_err_freq_hz"], sc["bias_err_dt_s"], sc["sigma_acc_bias_c"], sc["sigma_omega_bias_c"])
+    assert f"IMU samples in the problem: {n_imu} of" in out.stdout and f"valid reprojections: {int(valid.sum())}\n" in out.stdout
+    s = o.optimize(1); o.relinearize()
+    costs = [s["final_cost"]]
+    for _ in range(2):
+        s = o.optimize(4); o.relinearize(); costs.append(s["final_cost"])
+        if s["termination_type"] == 0: break
+    got = [float(l.split("->")[1].split(",")[0]) for l in out.stdout.splitlines() if l.startswith("solve ")]
+    assert len(got) == len(costs)
+    np.testing.assert_allclose(got, costs, rtol=1e-6)
+    g = o.getGlobals()
+    assert abs(float(open(os.path.join(res, "cam_imu_time_offset.txt")).read()) - g[16]) < 1e-7
+    np.testing.assert_allclose(np.loadtxt(os.path.join(res, "gravity.txt")), g[13:16], atol=1e-6)
+    T_bc = np.loadtxt(os.path.join(res, "T_bc.txt"))
+    R_o = (Rot.from_quat(sc["q_bc"]) * Rot.from_quat(g[1:5])).as_matrix(); p_o = sc["p_bc"] + Rot.from_quat(sc["q_bc"]).apply(g[5:8])
+    np.testing.assert_allclose(T_bc[:3, :3], R_o, atol=1e-6); np.testing.assert_allclose(T_bc[:3, 3], p_o, atol=1e-6)
+    tr = np.loadtxt(os.path.join(res, "spline.txt"))
+    end_ns = (len(sc["knot_q"]) - order + 1) * sc["dt_ns"] + sc["start_t_ns"] - 1_000_000
+    t_ns = np.arange(sc["start_t_ns"], end_ns, 20_000_000, dtype=np.int64)
+    assert tr.shape == (len(t_ns), 8)
+    ref = o.sampleAt(0, t_ns)
+    np.testing.assert_allclose(tr[:, 1:4], ref[:, :3], atol=1e-5)
+    assert (Rot.from_quat(tr[:, 4:]).inv() * Rot.from_quat(ref[:, 3:])).magnitude().max() < np.deg2rad(0.001)
+    ab = np.loadtxt(os.path.join(res, "acc_bias_spline.txt"))
+    np.testing.assert_allclose(ab[:, 1:], o.sampleAt(5, (ab[:, 0] * 1e9).round().astype(np.int64)), atol=1e-6)
+    pim = np.loadtxt(os.path.join(res, "predicted_imu.txt"))
+    assert pim.shape[1] == 7 and len(pim) > 0.8 * n_imu
+    for fn in ("initial_spline.txt", "initial_predicted_imu.txt", "gyro_bias_spline.txt", "acc_errors.txt", "gyro_errors.txt", "reprojection_errors.txt", "points3D.txt", "scale.txt"):
+        assert os.path.exists(os.path.join(res, fn))
