@@ -669,3 +669,37 @@ def test_vi_driver_end_to_end_on_gpu(pkg, oracle, scene, tmp_path, order):
     assert pim.shape[1] == 7 and len(pim) > 0.8 * n_imu
     for fn in ("initial_spline.txt", "initial_predicted_imu.txt", "gyro_bias_spline.txt", "acc_errors.txt", "gyro_errors.txt", "reprojection_errors.txt", "points3D.txt", "scale.txt"):
         assert os.path.exists(os.path.join(res, fn))
+
+
+def _write_ct_dataset(d, sc, order, T_wg_q, T_wg_p, flags, t_gp_init):
+    """gv + vi datasets and the alignment results optimize_continuous_time starts from (T_wg.txt, scale.txt, spline_globalsensor_time_offset.txt)"""
+    _, _, g = _write_vi_dataset(d, sc, order, T_wg_q, T_wg_p, flags)
+    dt_ms = int(sc["dt_ns"] * 1e-9 * 1000)
+    al = os.path.join(d, "align", f"order_{order}", f"dt_{dt_ms}_ms")
+    _write_pose(os.path.join(al, "T_wg.txt"), T_wg_q, T_wg_p, digits=17)
+    open(os.path.join(al, "scale.txt"), "w").write(f"{sc['scale']:.17g}\n")
+    open(os.path.join(al, "spline_globalsensor_time_offset.txt"), "w").write(f"{t_gp_init:.17g}\n")
+    vi = open(os.path.join(d, "vi.yaml")).read().replace("full_batch_vi", "full_batch_ct")
+    yml = os.path.join(d, "ct.yaml")
+    with open(yml, "w") as f:
+        f.write(vi + f'gp_fn: "{d}/gp.txt"\nspline_global_ref_alignment_dir: "{d}/align"\ngp_std: {sc["gp_std"]}\n'
+                f"optimize_pBP: {'true' if flags[1] else 'false'}\noptimize_spline_globsens_time_offset: {'true' if flags[4] else 'false'}\n")
+    return yml, os.path.join(d, "full_batch_ct", "continuous_time", f"order_{order}", f"dt_{dt_ms}_ms"), g
+
+
+def _ct_scene(scene, order):
+    flags = (False, True, True, True, True)
+    return scene.make_scene(order=order, duration_s=3.0, n_landmarks=160, track_len=9, imu_hz=200, gp_hz=10, dt_s_bias=0.25, flags=flags, seed=55 + order), flags
+
+
+def test_ct_driver_builds_and_fails_loudly_without_gpu(pkg, scene, tmp_path):
+    import torch
+    exe = _gxx(os.path.join(ROOT, "drivers", "optimize_continuous_time.cpp"), str(tmp_path / "ct"), pkg)
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    sc, flags = _ct_scene(scene, 6)
+    yml, _, _ = _write_ct_dataset(str(tmp_path), sc, 6, Rot.from_rotvec([0.2, -0.4, 1.0]).as_quat(), np.array([3.0, -2.0, 1.0]), flags, 0.002)
+    out = subprocess.run([exe, yml], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 3 and "no CPU fallback" in out.stderr, out.stdout + out.stderr
+    assert f"Loaded {len(sc['imu_t_ns'])} imu measurements" in out.stdout and f"Loaded {len(sc['gp_t_ns'])} global measurements" in out.stdout
+    assert f"Loaded {len(sc['knot_q'])} initial spline knots" in out.stdout and "Loaded scale: 1" in out.stdout
