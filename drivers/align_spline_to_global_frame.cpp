@@ -77,7 +77,7 @@ static int run(const Yaml& config, int device) {
   // The reference evaluates the final errors after the relinearisation and re-derives every st from the folded offset (:1692-1695); the
   // library's work items keep the st of add time, so the equivalent state is the one before t_corr is folded away.
   std::vector<double> errors = spline_gb.evaluateWorldColmapAlignmentErrors();
-  spline_gb.relinearizeSplineImuTimeOffset();                                   // both offsets (relinearizeSplineGlobSensTimeOffset, :217)
+  spline_gb.relinearizeSplineGlobSensTimeOffset();                              // :217
   std::cout << "Number of errors: " << errors.size() << "\nFinal error mean: " << meanOf(errors) << "\n\n";
 
   std::cout << "Optimized colmap - global reference scale: " << spline_gb.getScale() << "\nScale correction was: " << spline_gb.getScaleCorr() << "\n\n";

@@ -232,16 +232,16 @@ static int run(const Yaml& config, int device) {
   spline_wb.loadOptimizationParams(n_max_outer_iters, n_max_inner_iters, config.as<int>("n_threads"));
   std::cout << "\n\nOptimizing ...\n\n";
   Summary summary = spline_wb.optimize(1);
-  spline_wb.relinearizeSplineImuTimeOffset();
+  spline_wb.relinearizeSplineGlobSensTimeOffset(); spline_wb.relinearizeSplineImuTimeOffset();
   std::printf("solve 0: iterations %zu, cost %.12g -> %.12g\n", summary.iterations.size(), summary.initial_cost, summary.final_cost);
   for (int i = 0; i < n_max_outer_iters; i++) {
     summary = spline_wb.optimize(n_max_inner_iters);
-    spline_wb.relinearizeSplineImuTimeOffset();
+    spline_wb.relinearizeSplineGlobSensTimeOffset(); spline_wb.relinearizeSplineImuTimeOffset();
     std::printf("solve %d: iterations %zu, cost %.12g -> %.12g, termination %d\n", i + 1, summary.iterations.size(), summary.initial_cost, summary.final_cost, summary.termination_type);
     if (summary.termination_type == 0) { std::cout << "\n===== Solver converged =====\n\nnumber of outer iterations = " << i + 1 << "\n"; break; }
     if (i == n_max_outer_iters - 1) std::cout << "\n\n===== Solver did not converge =====\n\n";
   }
-  spline_wb.relinearizeSplineImuTimeOffset();
+  spline_wb.relinearizeSplineGlobSensTimeOffset(); spline_wb.relinearizeSplineImuTimeOffset();
 
   std::cout << "+-+-+-+-+- Final Errors +-+-+-+-+-\n\n";
   e_acc = spline_wb.evaluateErrors(CTBA_ACCEL); e_gyr = spline_wb.evaluateErrors(CTBA_GYRO); e_rep = spline_wb.evaluateErrors(CTBA_REPROJ);

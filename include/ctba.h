@@ -178,7 +178,8 @@ enum { CTBA_SAMPLE_POSE = 0, CTBA_SAMPLE_ACCEL_BODY = 1, CTBA_SAMPLE_ACCEL_WORLD
        CTBA_SAMPLE_ACCEL_BIAS = 5, CTBA_SAMPLE_GYRO_BIAS = 6 };
 int ctba_sample(ctba_problem* p, int what, int64_t n, const int64_t* t_ns, double* out);
 
-/* relinearizeSplineImuTimeOffset + relinearizeSplineGlobSensTimeOffset   bspline_so3r3.h:1807-1811, 1853-1857 */
+/* relinearizeSplineImuTimeOffset + relinearizeSplineGlobSensTimeOffset   bspline_so3r3.h:1807-1811, 1853-1857
+ * (option "relinearize_mask": 1 = only the spline-imu offset, 2 = only the spline / global-sensor offset, 3 = both, the default) */
 int ctba_relinearize_time_offsets(ctba_problem* p);
 
 /* Options: "bench_no_termination" (1 = ctba_solve runs exactly max_num_iterations LM iterations, convergence tests

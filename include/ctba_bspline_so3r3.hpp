@@ -172,8 +172,8 @@ class BSplineSO3R3 {
     knots_fresh_ = false;
     return s;
   }
-  void relinearizeSplineImuTimeOffset() { chk(ctba_relinearize_time_offsets(h_)); }     // :1807-1811 (+ :1853-1857, both offsets)
-  void relinearizeSplineGlobSensTimeOffset() {}                                        // done by the call above
+  void relinearizeSplineImuTimeOffset() { relinearize(1); }                             // :1807-1811
+  void relinearizeSplineGlobSensTimeOffset() { relinearize(2); }                        // :1853-1857
 
   // ---- results --------------------------------------------------------------------------------------------------------------
   Pose getPose(int64_t time_ns) {                                                      // :221-264
@@ -213,6 +213,11 @@ class BSplineSO3R3 {
   int chk(int rc) const {
     if (rc < 0) throw Error(rc, std::string(ctba_last_error(h_)));
     return rc;
+  }
+  void relinearize(int mask) {
+    chk(ctba_set_option(h_, "relinearize_mask", mask));
+    chk(ctba_relinearize_time_offsets(h_));
+    chk(ctba_set_option(h_, "relinearize_mask", 3));
   }
   void pushGlobals() { chk(ctba_set_globals(h_, scale_, p_bp_.data(), g_.data(), t_s_gp_s_)); }
   void pushFlags() { chk(ctba_set_flags(h_, opt_[0], opt_[1], opt_[2], opt_[3], opt_[4])); }

@@ -599,8 +599,8 @@ int ctba_relinearize_time_offsets(ctba_problem* p) {
   if (p->device >= 0) cudaSetDevice(p->device);
   int rc = download_state(p); if (rc) return rc;
   // :1807-1811, :1853-1857 — bookkeeping only: the work items keep the st_s, k captured when they were added
-  p->t_offset_cam_imu_s += p->glb[GLB_T_CAM_IMU_CORR]; p->glb[GLB_T_CAM_IMU_CORR] = 0.0;
-  p->t_s_gp_s += p->glb[GLB_T_GP_CORR]; p->glb[GLB_T_GP_CORR] = 0.0;
+  if (p->relinearize_mask & 1) { p->t_offset_cam_imu_s += p->glb[GLB_T_CAM_IMU_CORR]; p->glb[GLB_T_CAM_IMU_CORR] = 0.0; }   // relinearizeSplineImuTimeOffset
+  if (p->relinearize_mask & 2) { p->t_s_gp_s += p->glb[GLB_T_GP_CORR]; p->glb[GLB_T_GP_CORR] = 0.0; }                        // relinearizeSplineGlobSensTimeOffset
   p->state_dirty = true;
   return CTBA_OK;
 }
@@ -609,6 +609,7 @@ int ctba_set_option(ctba_problem* p, const char* name, double value) {
   CHECK_P(p);
   if (!name) return CTBA_E_ARG;
   if (!std::strcmp(name, "bench_no_termination")) { p->bench_no_termination = value != 0.0; return CTBA_OK; }
+  if (!std::strcmp(name, "relinearize_mask")) { p->relinearize_mask = (int)value & 3; return CTBA_OK; }
   if (!std::strcmp(name, "band_pdl")) { p->band_pdl = (int)value; return CTBA_OK; }
   if (!std::strcmp(name, "band_partitions")) { p->band_partitions = (int)value; return CTBA_OK; }
   if (!std::strcmp(name, "schur_two_stage")) { p->schur_two_stage = value != 0.0; return CTBA_OK; }

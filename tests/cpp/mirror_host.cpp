@@ -65,6 +65,21 @@ int main() {
     try { al.optimize(3); } catch (const ctba::Error& e) { t2 = e.code == CTBA_E_CUDA; }
     REQUIRE(t2);
   }
+  // relinearizeSplineImuTimeOffset / relinearizeSplineGlobSensTimeOffset fold their own offset only (:1807-1811, :1853-1857)
+  {
+    Spline rl(dt_ns, start_ns, /*device=*/-1);
+    rl.initializeFromNumTraj(q, p);
+    rl.setInitSplineGlobSensTimeOffset(0.5);
+    const double corr[10] = {0, 0, 0, 0, 1, 0, 0, 0, 0.01, 0.02};   // t_offset_cam_imu_corr = 0.01, t_s_gp_corr = 0.02
+    REQUIRE(ctba_set_corrections(rl.handle(), corr) == CTBA_OK);
+    rl.relinearizeSplineImuTimeOffset();
+    REQUIRE(std::fabs(rl.getSplineImuTimeOffset() - 0.01) < 1e-15 && rl.getSplineGlobSensTimeOffset() == 0.5 && rl.getSplineGlobSensTimeOffsetCorr() == 0.02);
+    rl.relinearizeSplineGlobSensTimeOffset();
+    REQUIRE(std::fabs(rl.getSplineGlobSensTimeOffset() - 0.52) < 1e-15 && rl.getSplineGlobSensTimeOffsetCorr() == 0.0);
+    REQUIRE(ctba_set_corrections(rl.handle(), corr) == CTBA_OK);
+    REQUIRE(ctba_relinearize_time_offsets(rl.handle()) == CTBA_OK);   // the plain C call still folds both
+    REQUIRE(std::fabs(rl.getSplineImuTimeOffset() - 0.02) < 1e-15 && std::fabs(rl.getSplineGlobSensTimeOffset() - 0.54) < 1e-15);
+  }
   // no device: the compute entry points fail loudly (there is no CPU fallback)
   bool threw = false;
   try { spline.optimize(3); } catch (const ctba::Error& e) { threw = e.code == CTBA_E_CUDA; }

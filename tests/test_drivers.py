@@ -761,3 +761,28 @@ def _ct_oracle(oracle, sc, flags, order, T_q, T_p, kq_g, kp_g, lm_g, t_gp_init):
         s = o.optimize(4); o.relinearize(); costs.append(s["final_cost"])
         if s["termination_type"] == 0: break
     return o, costs
+
+
+def test_gi_driver_builds_and_fails_loudly_without_gpu(pkg, scene, tmp_path):
+    """optimize_gi_continuous_time (GP + IMU, no vision; the library shape is covered on the GPU by test_lm_gi_no_frames).  The tool's own
+    end-to-end GPU run was not made this round (GPU budget spent): only the build, the parsing and the loud failure are checked here."""
+    import torch
+    exe = _gxx(os.path.join(ROOT, "drivers", "optimize_gi_continuous_time.cpp"), str(tmp_path / "gi"), pkg)
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    sc, flags = _ct_scene(scene, 6)
+    d = str(tmp_path)
+    _write_ct_dataset(d, sc, 6, Rot.from_quat([0, 0, 0, 1.0]).as_quat(), np.zeros(3), flags, 0.0)
+    os.makedirs(os.path.join(d, "gpfit", "order_6", "dt_100_ms"))
+    os.replace(os.path.join(d, "fitted", "order_6", "dt_100_ms", "spline_knots.txt"), os.path.join(d, "gpfit", "order_6", "dt_100_ms", "spline_knots.txt"))
+    yml = os.path.join(d, "gi.yaml")
+    with open(yml, "w") as f:
+        f.write(f'dataset: EuRoC\nimu_fn: "{d}/imu.txt"\ngp_fn: "{d}/gp.txt"\nspline_dir: "{d}/gpfit"\nfull_batch_optimization_dir: "{d}/full_batch_gi"\n'
+                f"spline_control_nodes_dt_s: 0.1\nsampling_spline_rate: 50.0\nbias_spline_control_nodes_dt_s: {sc['dt_s_bias']}\ninit_acc_bias: [0.0, 0.0, 0.0]\n"
+                f"init_gyro_bias: [0.0, 0.0, 0.0]\nsigma_acc_c: 0.1\nsigma_acc_bias_c: 0.002\nsigma_omega_c: 0.05\nsigma_omega_bias_c: 4.0e-05\n"
+                f"bias_err_freq_hz: {sc['bias_err_freq_hz']}\nbias_err_dt_s: {sc['bias_err_dt_s']}\ngp_std: 0.1\noptimize_gravity: false\noptimize_pBP: true\n"
+                f"optimize_spline_globsens_time_offset: true\nn_max_outer_iters: 2\nn_max_inner_iters: 4\nn_threads: 4\n")
+    out = subprocess.run([exe, yml], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 3 and "no CPU fallback" in out.stderr, out.stdout + out.stderr
+    assert f"Loaded {len(sc['imu_t_ns'])} imu measurements" in out.stdout and f"Loaded {len(sc['gp_t_ns'])} global measurements" in out.stdout
+    assert f"Loaded {len(sc['knot_q'])} initial spline knots" in out.stdout
