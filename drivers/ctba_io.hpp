@@ -420,5 +420,61 @@ class Yaml {
   std::map<std::string, std::string> kv_;
 };
 
+// loadUZHFPVSimpleCamImuCalib (util/load_calibration.h:83-160): Kalibr camchain (cam0 / cam1 maps with flow sequences that may start on
+// the line after the key) + Kalibr imu.yaml
+namespace detail {
+inline std::vector<double> listAfterKey(const std::string& seg, const std::string& key) {
+  const size_t k = seg.find(key);
+  if (k == std::string::npos) throw std::runtime_error("calibration yaml: missing '" + key + "'");
+  const size_t lb = seg.find('[', k), rb = seg.find(']', lb);
+  if (lb == std::string::npos || rb == std::string::npos) throw std::runtime_error("calibration yaml: no list after '" + key + "'");
+  std::string body = seg.substr(lb + 1, rb - lb - 1);
+  for (char& c : body) if (c == ',') c = ' ';
+  std::istringstream ss(body); std::vector<double> out; double v;
+  while (ss >> v) out.push_back(v);
+  return out;
+}
+}  // namespace detail
+inline bool loadUZHFPVSimpleCamImuCalib(const std::string& camimu_calib_fn, const std::string& imu_calib_fn, int cam_id, SimpleCamImuCalib& calib) {
+  if (cam_id != 0 && cam_id != 1) return false;
+  std::ifstream fs(camimu_calib_fn.c_str());
+  if (!fs.is_open()) throw std::runtime_error("Could not open yaml file: " + camimu_calib_fn);
+  const std::string want = cam_id == 0 ? "cam0:" : "cam1:";
+  std::string line, cam; bool in = false;
+  while (std::getline(fs, line)) {
+    const bool top = !line.empty() && line[0] != ' ' && line[0] != '\t' && line[0] != '#' && line[0] != '[';
+    if (top) in = line.compare(0, want.size(), want) == 0;
+    if (in) { cam += line; cam += '\n'; }
+  }
+  if (cam.empty()) throw std::runtime_error("calibration yaml: '" + want + "' not found");
+  calib.idx_ = cam_id;
+  calib.camera_model_ = detail::valueAfter(cam, "camera_model:");
+  calib.distortion_model_ = detail::valueAfter(cam, "distortion_model:");
+  const std::vector<double> dc = detail::listAfterKey(cam, "distortion_coeffs:"), res = detail::listAfterKey(cam, "resolution:"),
+                            in4 = detail::listAfterKey(cam, "intrinsics:"), T = detail::listAfterKey(cam, "T_cam_imu:");
+  if (dc.size() < 4 || res.size() < 2 || in4.size() < 4 || T.size() < 16) throw std::runtime_error("calibration yaml: short list");
+  for (int i = 0; i < 4; ++i) { calib.distortion_coeffs_[i] = dc[i]; calib.intrinsics_[i] = in4[i]; }
+  calib.resolution_[0] = res[0]; calib.resolution_[1] = res[1];
+  calib.timeshift_cam_imu_ = std::stod(detail::valueAfter(cam, "timeshift_cam_imu:"));
+  const double R[9] = {T[0], T[1], T[2], T[4], T[5], T[6], T[8], T[9], T[10]};           // row-major list (Matrix4d(data).transpose(), :115-117)
+  calib.T_cam_imu_ = Pose{{{T[3], T[7], T[11]}}, quatFromMatrix(R)};
+  const Yaml imu = Yaml::LoadFile(imu_calib_fn);
+  calib.imu_rate_ = imu.as<double>("update_rate");
+  calib.acc_noise_density_ = imu.as<double>("accelerometer_noise_density"); calib.acc_random_walk_ = imu.as<double>("accelerometer_random_walk");
+  calib.gyro_noise_density_ = imu.as<double>("gyroscope_noise_density"); calib.gyro_random_walk_ = imu.as<double>("gyroscope_random_walk");
+  return true;
+}
+// the drivers' dataset switch (src/optimize_continuous_time.cpp:288-311, 551-565): calibration format and the key of the GP noise
+inline bool loadCalibForDataset(const Yaml& config, const std::string& dataset, int cam_id, SimpleCamImuCalib& calib) {
+  if (dataset == "UZH_FPV") return loadUZHFPVSimpleCamImuCalib(config.as<std::string>("camimu_calib_fn"), config.as<std::string>("imu_calib_fn"), cam_id, calib);
+  if (dataset == "EuRoC" || dataset == "Custom") return loadEuRoCSimpleCamImuCalib(config.as<std::string>("camimu_calib_fn"), cam_id, calib);
+  throw std::runtime_error("Unknown dataset");
+}
+inline double gpStdForDataset(const Yaml& config, const std::string& dataset) {
+  if (dataset == "UZH_FPV") return config.as<double>("leica_std");
+  if (dataset == "EuRoC" || dataset == "Custom") return config.as<double>("gp_std");
+  throw std::runtime_error("Unknown dataset");
+}
+
 }  // namespace io
 }  // namespace ctba

@@ -3,8 +3,8 @@
 // Same YAML keys (experiments/*/*/full_batch_optimization/continuous_time/*.yaml), same inputs (EuRoC-format calibration YAML, imu.txt, global
 // position measurements, the COLMAP export, the fitted spline_knots.txt, and T_wg.txt / scale.txt / spline_globalsensor_time_offset.txt /
 // p_bp.txt written by align_spline_to_global_frame), the same call order, outer loop (both time offsets re-linearised between solves) and
-// result files.  optimize() runs on the GPU (ctba_solve).  Host-side differences: `dataset: UZH_FPV` (Kalibr calibration, `leica_std`) is
-// not built; points3D.txt rows are in points3D.bin order.
+// result files.  optimize() runs on the GPU (ctba_solve).  Host-side difference: points3D.txt rows are in
+// points3D.bin order.
 //   usage: optimize_continuous_time <config.yaml> [cuda device] [order 4|6]
 #include <cstdio>
 #include <cstdlib>
@@ -37,7 +37,7 @@ static double meanAbove(const std::vector<double>& v, double thr, int* n) { doub
 template <int order>
 static int run(const Yaml& config, int device) {
   const int cam_id = config.as<int>("cam_id");
-  const std::string camimu_calib_fn = config.as<std::string>("camimu_calib_fn"), imu_fn = config.as<std::string>("imu_fn"), gp_fn = config.as<std::string>("gp_fn"), colmap_dir = config.as<std::string>("colmap_dir");
+  const std::string imu_fn = config.as<std::string>("imu_fn"), gp_fn = config.as<std::string>("gp_fn"), colmap_dir = config.as<std::string>("colmap_dir");
   const double spline_knots_dt_s = config.as<double>("spline_control_nodes_dt_s"), sampling_spline_rate_hz = config.as<double>("sampling_spline_rate");
   const int spline_knots_dt_ms = spline_knots_dt_s * 1000;
   const std::string sub = "/order_" + std::to_string(order) + "/dt_" + std::to_string(spline_knots_dt_ms) + "_ms";
@@ -51,8 +51,7 @@ static int run(const Yaml& config, int device) {
   std::cout << "Dataset: " << dataset_fn << "\nresult dir: " << trace_dir << "\n\n";
 
   SimpleCamImuCalib calib;
-  require(dataset_fn == "EuRoC" || dataset_fn == "Custom", dataset_fn == "UZH_FPV" ? "dataset UZH_FPV: the Kalibr calibration loader is not built" : "Unknown dataset");
-  require(loadEuRoCSimpleCamImuCalib(camimu_calib_fn, cam_id, calib), "Camera-Imu calibration could not be loaded");
+  require(loadCalibForDataset(config, dataset_fn, cam_id, calib), "Camera-Imu calibration could not be loaded");   // UZH_FPV: Kalibr camchain + imu.yaml; EuRoC / Custom: EuRoC format
   ImuNoise noise;                                                                   // imu noise from the config file (:307-311)
   noise.acc_noise_density = config.as<double>("sigma_acc_c"); noise.acc_random_walk = config.as<double>("sigma_acc_bias_c");
   noise.gyro_noise_density = config.as<double>("sigma_omega_c"); noise.gyro_random_walk = config.as<double>("sigma_omega_bias_c");
@@ -133,7 +132,7 @@ static int run(const Yaml& config, int device) {
   int rc = ctba_compute_valid_reprojections(spline_wb.handle(), F, frame_t_ns.data(), sc.pt_begin.data(), sc.uv.data(), sc.lm_index.data(), (int)sc.frames[0].w,
                                             (int)sc.frames[0].h, grid_cell_size, valid.data(), n_valid.data());
   if (rc < 0) throw Error(rc, ctba_last_error(spline_wb.handle()));
-  const double gp_meas_std = config.as<double>("gp_std");
+  const double gp_meas_std = gpStdForDataset(config, dataset_fn);
   std::cout << "Sigma global measurements: " << gp_meas_std << " [m]\n\n";
   {
     std::vector<int64_t> t(gp_meas.size()); std::vector<double> z(3 * gp_meas.size());

@@ -5,7 +5,7 @@
 // scale_init.txt / p_bp.txt of the alignment step), the same call order on the spline object, the same outer loop (1 iteration, then up to
 // n_max_outer_iters x n_max_inner_iters with the time offset re-linearised in between) and the same result files.  Everything the
 // reference does inside optimize() runs on the GPU (ctba_solve); computeValidReprojections stays a host pass (ctba_compute_valid_reprojections).
-// Differences, all on the host side: `dataset: UZH_FPV` (Kalibr camchain calibration) is not built; points3D.txt rows are in points3D.bin
+// Difference on the host side: points3D.txt rows are in points3D.bin
 // order (the reference writes its unordered_map's iteration order, save.h:200-208).
 //   usage: optimize_gv_continuous_time <config.yaml> [cuda device] [order 4|6]
 #include <cstdio>
@@ -39,7 +39,7 @@ static double meanAbove(const std::vector<double>& v, double thr, int* n) { doub
 template <int order>
 static int run(const Yaml& config, int device) {
   const int cam_id = config.as<int>("cam_id");
-  const std::string camimu_calib_fn = config.as<std::string>("camimu_calib_fn"), gp_fn = config.as<std::string>("gp_fn"), colmap_dir = config.as<std::string>("colmap_dir");
+  const std::string gp_fn = config.as<std::string>("gp_fn"), colmap_dir = config.as<std::string>("colmap_dir");
   const double spline_knots_dt_s = config.as<double>("spline_control_nodes_dt_s"), sampling_spline_rate_hz = config.as<double>("sampling_spline_rate");
   const int spline_knots_dt_ms = spline_knots_dt_s * 1000;
   const std::string sub = "/order_" + std::to_string(order) + "/dt_" + std::to_string(spline_knots_dt_ms) + "_ms";
@@ -53,8 +53,7 @@ static int run(const Yaml& config, int device) {
   std::cout << "Dataset: " << dataset_fn << "\nresult dir: " << trace_dir << "\n\n";
 
   SimpleCamImuCalib calib;
-  require(dataset_fn == "EuRoC" || dataset_fn == "Custom", dataset_fn == "UZH_FPV" ? "dataset UZH_FPV: the Kalibr calibration loader is not built" : "Unknown dataset");
-  require(loadEuRoCSimpleCamImuCalib(camimu_calib_fn, cam_id, calib), "Camera-Imu calibration could not be loaded");
+  require(loadCalibForDataset(config, dataset_fn, cam_id, calib), "Camera-Imu calibration could not be loaded");   // UZH_FPV: Kalibr camchain + imu.yaml; EuRoC / Custom: EuRoC format
   std::vector<GlobalPosMeasurement> gp_meas;
   require(loadGpMeasurements(gp_fn, gp_meas), "Could not load global measurements.");
   std::cout << "Loaded " << gp_meas.size() << " global measurements.\n\n";
@@ -120,7 +119,7 @@ static int run(const Yaml& config, int device) {
                                             (int)sc.frames[0].h, grid_cell_size, valid.data(), n_valid.data());
   if (rc < 0) throw Error(rc, ctba_last_error(spline_wb.handle()));
 
-  const double gp_meas_std = config.as<double>("gp_std");
+  const double gp_meas_std = gpStdForDataset(config, dataset_fn);
   std::cout << "Sigma global measurements: " << gp_meas_std << " [m]\n\n";
   {
     std::vector<int64_t> t(gp_meas.size()); std::vector<double> z(3 * gp_meas.size());

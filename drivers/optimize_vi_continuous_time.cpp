@@ -3,7 +3,7 @@
 // Same YAML keys (experiments/*/*/full_batch_optimization_vi/continuous_time/*.yaml: T_wg and initial_scale inline, imu noise, bias spline,
 // bias error sampling, gravity / scale / cam-imu extrinsics flags), same inputs (EuRoC-format calibration YAML, imu.txt, the COLMAP
 // export, the fitted spline_knots.txt), the same call order, outer loop and result files.  optimize() runs on the GPU (ctba_solve).
-// Differences, host side only: `dataset: UZH_FPV` (Kalibr calibration) is not built; points3D.txt rows are in points3D.bin order.
+// Difference, host side only: points3D.txt rows are in points3D.bin order.
 //   usage: optimize_vi_continuous_time <config.yaml> [cuda device] [order 4|6]
 #include <cstdio>
 #include <cstdlib>
@@ -36,7 +36,7 @@ static double meanAbove(const std::vector<double>& v, double thr, int* n) { doub
 template <int order>
 static int run(const Yaml& config, int device) {
   const int cam_id = config.as<int>("cam_id");
-  const std::string camimu_calib_fn = config.as<std::string>("camimu_calib_fn"), imu_fn = config.as<std::string>("imu_fn"), colmap_dir = config.as<std::string>("colmap_dir");
+  const std::string imu_fn = config.as<std::string>("imu_fn"), colmap_dir = config.as<std::string>("colmap_dir");
   const double spline_knots_dt_s = config.as<double>("spline_control_nodes_dt_s"), sampling_spline_rate_hz = config.as<double>("sampling_spline_rate");
   const int spline_knots_dt_ms = spline_knots_dt_s * 1000;
   const std::string sub = "/order_" + std::to_string(order) + "/dt_" + std::to_string(spline_knots_dt_ms) + "_ms";
@@ -49,8 +49,7 @@ static int run(const Yaml& config, int device) {
   std::cout << "Dataset: " << dataset_fn << "\nresult dir: " << trace_dir << "\n\n";
 
   SimpleCamImuCalib calib;
-  require(dataset_fn == "EuRoC" || dataset_fn == "Custom", dataset_fn == "UZH_FPV" ? "dataset UZH_FPV: the Kalibr calibration loader is not built" : "Unknown dataset");
-  require(loadEuRoCSimpleCamImuCalib(camimu_calib_fn, cam_id, calib), "Camera-Imu calibration could not be loaded");
+  require(loadCalibForDataset(config, dataset_fn, cam_id, calib), "Camera-Imu calibration could not be loaded");   // UZH_FPV: Kalibr camchain + imu.yaml; EuRoC / Custom: EuRoC format
   ImuNoise noise;                                                                   // imu noise from the config file (:307-311)
   noise.acc_noise_density = config.as<double>("sigma_acc_c"); noise.acc_random_walk = config.as<double>("sigma_acc_bias_c");
   noise.gyro_noise_density = config.as<double>("sigma_omega_c"); noise.gyro_random_walk = config.as<double>("sigma_omega_bias_c");

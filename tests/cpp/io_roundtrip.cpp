@@ -44,6 +44,29 @@ int main(int argc, char** argv) {
     try { linearInterpolation(tp, tq, tt, its, op2, oq2); } catch (const std::runtime_error&) { thr = true; }
     if (!thr) return 8;
   }
+  // calibration files: Kalibr camchain + imu.yaml (UZH-FPV) and the EuRoC layout
+  {
+    std::ifstream probe((d + "/camchain.yaml").c_str());
+    if (probe.is_open()) {
+      for (int cam = 0; cam < 2; ++cam) {
+        SimpleCamImuCalib c;
+        if (!loadUZHFPVSimpleCamImuCalib(d + "/camchain.yaml", d + "/imu.yaml", cam, c)) return 9;
+        const Pose Tbc = poseInverse(c.T_cam_imu_);
+        std::printf("kalibr%d %s|%s %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g\n", cam,
+                    c.camera_model_.c_str(), c.distortion_model_.c_str(), c.intrinsics_[0], c.intrinsics_[1], c.intrinsics_[2], c.intrinsics_[3], c.distortion_coeffs_[0],
+                    c.distortion_coeffs_[1], c.distortion_coeffs_[2], c.distortion_coeffs_[3], c.resolution_[0], c.resolution_[1], c.timeshift_cam_imu_, c.imu_rate_,
+                    c.acc_noise_density_, c.acc_random_walk_, c.gyro_noise_density_, c.gyro_random_walk_, Tbc.q[0], Tbc.q[1], Tbc.q[2], Tbc.q[3], Tbc.p[0], Tbc.p[1], Tbc.p[2]);
+      }
+      SimpleCamImuCalib bad;
+      if (loadUZHFPVSimpleCamImuCalib(d + "/camchain.yaml", d + "/imu.yaml", 2, bad)) return 10;
+      SimpleCamImuCalib e;
+      if (!loadEuRoCSimpleCamImuCalib(d + "/euroc.yaml", 1, e)) return 11;
+      const Pose Tbc = poseInverse(e.T_cam_imu_);
+      std::printf("euroc1 %s|%s %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g\n", e.camera_model_.c_str(), e.distortion_model_.c_str(),
+                  e.intrinsics_[0], e.intrinsics_[3], e.distortion_coeffs_[0], e.distortion_coeffs_[3], e.timeshift_cam_imu_, e.imu_rate_, Tbc.q[0], Tbc.q[1], Tbc.q[2], Tbc.q[3],
+                  Tbc.p[0], Tbc.p[1], Tbc.p[2]);
+    }
+  }
   std::printf("OK\n");
   return 0;
 }

@@ -115,6 +115,25 @@ def test_io_formats_roundtrip(pkg, tmp_path):
     _write_traj(os.path.join(d, "traj.txt"), traj_t, traj_q, traj_p)
     its = np.array([traj_t[0], traj_t[0] + 0.03, traj_t[3], 0.5 * (traj_t[7] + traj_t[8]), traj_t[-1] - 1e-9])
     np.savetxt(os.path.join(d, "interp_ts.txt"), its, fmt="%.17g")
+    # calibration files in the two layouts of the reference's datasets (datasets/UZH_FPV/calib/*/camchain-*.yaml + imu.yaml, datasets/EuRoC/calib/*/calib.yaml)
+    q_ci = [Rot.from_rotvec(rng.normal(size=3)) for _ in range(2)]; p_ci = rng.normal(size=(2, 3)) * 0.05
+    def _rows(R, t): return [list(R.as_matrix()[r]) + [t[r]] for r in range(3)] + [[0.0, 0.0, 0.0, 1.0]]
+    def _flow(rows, sep): return sep.join(", ".join(f"{v:.17g}" for v in r) for r in rows)
+    with open(os.path.join(d, "camchain.yaml"), "w") as f:
+        f.write("cam0:\n  T_cam_imu: [%s]\n  camera_model: pinhole\n  distortion_coeffs: [-0.0137, 0.0207, -0.0127,\n    0.0025]\n  distortion_model: equidistant\n"
+                "  intrinsics: [278.66, 278.48, 319.75, 241.96]\n  resolution: [640, 480]\n  timeshift_cam_imu: -0.016684572091862235\n" % _flow(_rows(q_ci[0], p_ci[0]), ",\n  "))
+        f.write("cam1:\n  T_cam_imu:\n  [%s]\n  camera_model: pinhole\n  distortion_coeffs: [-0.0084, 0.0114, -0.0069,\n    0.0015]\n  distortion_model: equidistant\n"
+                "  intrinsics: [277.61, 277.63, 314.89, 236.04]\n  resolution: [640, 480]\n  timeshift_cam_imu: -0.0165\n" % _flow(_rows(q_ci[1], p_ci[1]), ",\n  "))
+    open(os.path.join(d, "imu.yaml"), "w").write("accelerometer_noise_density: 0.1\naccelerometer_random_walk: 0.002\ngyroscope_noise_density: 0.05\n"
+                                                 "gyroscope_random_walk: 4.0e-05\nrostopic: /snappy_imu\nupdate_rate: 500.0\n")
+    R_bc1 = Rot.from_rotvec([1.2, -1.2, 1.2]); p_bc1 = np.array([-0.0198, 0.0454, 0.0079])
+    with open(os.path.join(d, "euroc.yaml"), "w") as f:
+        f.write('label: "Euroc"\ncameras:\n')
+        for k, (R, t, fx) in enumerate(((Rot.from_rotvec([0.1, 0.2, 0.3]), np.zeros(3), 458.65), (R_bc1, p_bc1, 457.58))):
+            f.write(f"- camera:\n    label: cam{k}\n    image_height: 480\n    image_width: 752\n    type: pinhole\n    intrinsics:\n      cols: 1\n      rows: 4\n"
+                    f"      data: [{fx}, 456.13, 379.99, 255.23]\n    distortion:\n      type: radial-tangential\n      parameters:\n        cols: 1\n        rows: 4\n"
+                    f"        data: [-0.2836, 0.0745, -0.000104,\n    -3.55e-05]\n  T_B_C:\n    cols: 4\n    rows: 4\n    data: [{_flow(_rows(R, t), ',' + chr(10) + '           ')}]\n")
+        f.write("\nimu_params:\n  delay_imu_cam: 0.004\n  sigma_omega_c: 0.05\n  sigma_acc_c: 0.1\n  sigma_omega_bias_c: 4.0e-05\n  sigma_acc_bias_c: 0.002\n  imu_rate: 200\n")
     exe = _gxx(os.path.join(ROOT, "tests", "cpp", "io_roundtrip.cpp"), str(tmp_path / "io_roundtrip"), pkg)
     out = subprocess.run([exe, d], capture_output=True, text=True, timeout=60)
     assert out.returncode == 0 and out.stdout.strip().endswith("OK"), out.stdout + out.stderr
@@ -139,6 +158,22 @@ def test_io_formats_roundtrip(pkg, tmp_path):
         v = np.array(kv[f"interp{i}"].split(), dtype=float)
         np.testing.assert_allclose(v[:3], ip[i], atol=1e-14)
         assert min(np.abs(v[3:] - iq[i]).max(), np.abs(v[3:] + iq[i]).max()) < 1e-13
+    for cam in range(2):
+        head, *vals = kv[f"kalibr{cam}"].split(" ")
+        v = np.array(vals, dtype=float)
+        assert head == "pinhole|equidistant"
+        np.testing.assert_array_equal(v[:4], [[278.66, 278.48, 319.75, 241.96], [277.61, 277.63, 314.89, 236.04]][cam])
+        np.testing.assert_array_equal(v[4:8], [[-0.0137, 0.0207, -0.0127, 0.0025], [-0.0084, 0.0114, -0.0069, 0.0015]][cam])
+        np.testing.assert_array_equal(v[8:16], [640, 480, [-0.016684572091862235, -0.0165][cam], 500.0, 0.1, 0.002, 0.05, 4.0e-05])
+        T_bc = q_ci[cam].inv()                                   # the drivers use T_b_c = T_cam_imu^-1
+        assert (Rot.from_quat(v[16:20]).inv() * T_bc).magnitude() < 1e-14
+        np.testing.assert_allclose(v[20:23], -T_bc.apply(p_ci[cam]), atol=1e-15)
+    head, *vals = kv["euroc1"].split(" ")
+    v = np.array(vals, dtype=float)
+    assert head == "pinhole|radial-tangential"
+    np.testing.assert_array_equal(v[:6], [457.58, 255.23, -0.2836, -3.55e-05, -0.004, 200.0])      # timeshift = -delay_imu_cam
+    assert (Rot.from_quat(v[6:10]).inv() * R_bc1).magnitude() < 1e-14
+    np.testing.assert_allclose(v[10:13], p_bc1, atol=1e-15)
     # writers: 3x4 + "0 0 0 1" with 9 significant digits, "# x y z" header, 16-digit scalars (save.h:156-178)
     T_out = np.loadtxt(os.path.join(d, "T_out.txt"))
     assert T_out.shape == (4, 4) and list(T_out[3]) == [0, 0, 0, 1]
