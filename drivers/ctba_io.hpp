@@ -184,6 +184,7 @@ inline void linearInterpolation(const std::vector<Vec3>& pos, const std::vector<
 
 // ---- rigid transforms on Pose (Sophus::SE3d as far as the drivers use it) ----
 inline Vec3 rotate(const Quat& q, const Vec3& v) { double R[9]; matrixFromQuat(q, R); return Vec3{{R[0] * v[0] + R[1] * v[1] + R[2] * v[2], R[3] * v[0] + R[4] * v[1] + R[5] * v[2], R[6] * v[0] + R[7] * v[1] + R[8] * v[2]}}; }
+inline Pose poseMul(const Pose& A, const Pose& B) { const Vec3 t = rotate(A.q, B.p); return Pose{{{t[0] + A.p[0], t[1] + A.p[1], t[2] + A.p[2]}}, quatMul(A.q, B.q)}; }
 inline Pose poseInverse(const Pose& T) { const Quat qi = quatInverse(T.q); const Vec3 t = rotate(qi, T.p); return Pose{{-t[0], -t[1], -t[2]}, qi}; }
 
 // loadFrameTimes (util/colmap_utils.h:14-42): first column of colmap_cam_estimates.txt

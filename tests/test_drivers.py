@@ -821,3 +821,42 @@ def test_gi_driver_builds_and_fails_loudly_without_gpu(pkg, scene, tmp_path):
     assert out.returncode == 3 and "no CPU fallback" in out.stderr, out.stdout + out.stderr
     assert f"Loaded {len(sc['imu_t_ns'])} imu measurements" in out.stdout and f"Loaded {len(sc['gp_t_ns'])} global measurements" in out.stdout
     assert f"Loaded {len(sc['knot_q'])} initial spline knots" in out.stdout
+
+
+def test_align_colmap_to_imu_tool(pkg, scene, tmp_path):
+    """align_colmap_to_imu is host-only (no solver): the whole tool is checked on the CPU against a numpy restatement of
+    src/align_colmap_to_imu.cpp:51-82, 158-190."""
+    d = str(tmp_path)
+    rng = np.random.default_rng(17)
+    sc, flags = _vi_scene(scene, 6)
+    _write_vi_dataset(d, sc, 6, Rot.from_quat([0, 0, 0, 1.0]).as_quat(), np.zeros(3), flags)        # calib.yaml
+    t_imu = 500.0 + np.arange(60) / 200.0
+    R_true = Rot.from_rotvec([0.3, -0.5, 0.2])
+    acc = R_true.inv().apply(np.array([0.0, 0.0, 9.81])) + rng.normal(size=(60, 3)) * 0.05
+    with open(os.path.join(d, "imu_a.txt"), "w") as f:
+        f.write("# id t wx wy wz ax ay az\n")
+        for i in range(60):
+            f.write(f"{i} {t_imu[i]:.17g} 0 0 0 " + " ".join(f"{v:.17g}" for v in acc[i]) + "\n")
+    q_gc = Rot.from_rotvec(rng.normal(size=(3, 3))).as_quat(); p_gc = rng.normal(size=(3, 3))
+    t_cam = [t_imu[7] + 1e-4, t_imu[20], t_imu[40]]
+    os.makedirs(os.path.join(d, "colmap_a"))
+    _write_traj(os.path.join(d, "colmap_a", "colmap_cam_estimates.txt"), t_cam, q_gc, p_gc)
+    yml = os.path.join(d, "aci.yaml")
+    open(yml, "w").write(f'dataset: Custom\ncam_id: 0\ncamimu_calib_fn: "{d}/calib.yaml"\nimu_fn: "{d}/imu_a.txt"\ncolmap_dir: "{d}/colmap_a/"\nresult_dir: "{d}/aci_out"\n')
+    exe = _gxx(os.path.join(ROOT, "drivers", "align_colmap_to_imu.cpp"), str(tmp_path / "aci"), pkg)
+    out = subprocess.run([exe, yml], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 0, out.stdout + out.stderr
+    # restatement: samples with t >= first image (index 8 on), edges [m0.t, m10.t] -> samples 0..11 of those
+    sel = acc[8:][:12]
+    e = sel.mean(axis=0); e /= np.linalg.norm(e)
+    ax = np.cross([0.0, 0.0, 1.0], e); ax /= np.linalg.norm(ax)
+    R_IB = Rot.from_rotvec(-ax * np.arccos(e[2]))
+    T_IB = np.loadtxt(os.path.join(d, "aci_out", "T_IB.txt"))
+    np.testing.assert_allclose(T_IB[:3, :3], R_IB.as_matrix(), atol=2e-9); np.testing.assert_array_equal(T_IB[:3, 3], 0.0)
+    np.testing.assert_allclose(R_IB.apply(e), [0, 0, 1], atol=1e-12)          # gravity direction ends up on +z
+    R_bc, p_bc = Rot.from_quat(sc["q_bc"]), sc["p_bc"]                         # T_cam_imu = T_b_c^-1
+    R_ci, p_ci = R_bc.inv(), -R_bc.inv().apply(p_bc)
+    R_gb = Rot.from_quat(q_gc[0]) * R_ci; p_gb = Rot.from_quat(q_gc[0]).apply(p_ci) + p_gc[0]
+    R_ig = R_IB * R_gb.inv(); p_ig = -R_ig.apply(p_gb)
+    T_IG = np.loadtxt(os.path.join(d, "aci_out", "T_IG.txt"))
+    np.testing.assert_allclose(T_IG[:3, :3], R_ig.as_matrix(), atol=2e-9); np.testing.assert_allclose(T_IG[:3, 3], p_ig, rtol=2e-8, atol=2e-9)
