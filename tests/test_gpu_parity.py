@@ -1,10 +1,10 @@
 """GPU parity tests proper: the CUDA path through the C-ABI (libctba.so) against the CPU oracle on the
-same seeded inputs.  Tolerances (north_star): residuals/Jacobians 1e-10 relative element-wise (relative
-to the largest entry of the compared array, i.e. with an absolute floor for structural zeros), cost 1e-8."""
+same seeded inputs.  Tolerances (north_star): residuals/Jacobians element-wise |a - b| <= 1e-10 |b| + 1e-12 colscale
+(colscale = the largest magnitude of the oracle's column: conftest.elemerr), cost 1e-8."""
 import numpy as np
 import pytest
 
-from conftest import relerr
+from conftest import elemerr
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-10
@@ -26,8 +26,8 @@ def _compare_all(gpu, cpu):
         r_c, J_c, dropped = cpu.evaluate(kind)
         assert dropped == 0.0
         assert r_g.shape == r_c.shape and J_g.shape == J_c.shape
-        assert relerr(r_g, r_c) < TOL, (kind, relerr(r_g, r_c))
-        assert relerr(J_g, J_c) < TOL, (kind, relerr(J_g, J_c))
+        assert elemerr(r_g, r_c) <= 1.0, (kind, elemerr(r_g, r_c))
+        assert elemerr(J_g, J_c) <= 1.0, (kind, elemerr(J_g, J_c))
     cg, cc = gpu.cost(), cpu.cost()
     for k in range(7):
         assert abs(cg[k] - cc[k]) <= 1e-8 * max(abs(cc[k]), 1e-300) + 1e-300, (k, cg, cc)
