@@ -112,7 +112,7 @@ static int run(const Yaml& config, int device) {
   };
   auto saveBiasSplines = [&]() {                                                    // :63-85, 10 Hz up to getEndTnsBiasSpline (:1870-1875)
     const int64_t dt_ns_bias = static_cast<int64_t>(dt_bias_spline_s * 1e9);
-    const int64_t t_end = ((int64_t)spline_wb.numBiasKnots() - order + 1) * dt_ns_bias + spline_wb.getStartTns() - 1000000;
+    const int64_t t_end = (int64_t)((double)(((int64_t)spline_wb.numBiasKnots() - order + 1) * dt_ns_bias + spline_wb.getStartTns()) - 1e6);   // getEndTnsBiasSpline: through double
     std::vector<int64_t> ts;
     for (int64_t t = spline_wb.getStartTns(); t < t_end; t += 100000000) ts.push_back(t);
     for (int which = 0; which < 2; ++which) {

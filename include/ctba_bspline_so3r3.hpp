@@ -78,7 +78,7 @@ class BSplineSO3R3 {
   int64_t getDeltaTns() const { return dt_ns_; }                                       // :1877
   int64_t minTimeNs() const { return start_t_ns_; }                                    // :1789
   int64_t maxTimeNs() const { return start_t_ns_ + ((int64_t)numKnots() - N + 1) * dt_ns_ - 1; }        // :1784-1787
-  int64_t getEndTns() const { return ((int64_t)numKnots() - N + 1) * dt_ns_ + start_t_ns_ - 1000000; }   // :1862-1867
+  int64_t getEndTns() const { return (int64_t)((double)(((int64_t)numKnots() - N + 1) * dt_ns_ + start_t_ns_) - 1e6); }   // through double, like the reference   // :1862-1867
   Pose getKnot(int i) {                                                                // :215-219
     fetchKnots();
     if (i < 0 || i >= (int)kq_.size()) throw Error(CTBA_E_ARG, "getKnot: index out of range");

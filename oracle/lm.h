@@ -200,7 +200,6 @@ inline SolveSummary solveLM(MiniProblem& mp, int max_num_iterations, int num_thr
   while (true) {
     if (iter >= max_num_iterations) { sum.termination_type = 1; break; }
     if (radius < min_radius) { sum.termination_type = 0; break; }
-    if (invalid > max_consecutive_invalid) { sum.termination_type = 2; break; }
     ++iter;
     // scaled system: Hs = S H S, gs = S g
     std::vector<double> A((size_t)n * n), rhs(n);
@@ -232,7 +231,8 @@ inline SolveSummary solveLM(MiniProblem& mp, int max_num_iterations, int num_thr
       for (int i = 0; i < n; ++i) if (!std::isfinite(delta[i])) ok = false;
     }
     if (!ok || model_cost_change <= 0.0) {
-      ++invalid;
+      // HandleInvalidStep [Ceres, recalled]: the max_num_consecutive_invalid_steps-th invalid step in a row ends the solve with FAILURE
+      if (++invalid >= max_consecutive_invalid) { sum.termination_type = 2; break; }
       radius /= decrease_factor; decrease_factor *= 2.0;
       sum.num_unsuccessful_steps++;
       sum.iterations.push_back({x_cost, 0.0, gmax, 0.0, 0.0, radius, 0});

@@ -193,7 +193,7 @@ struct SplineProblem {
   int64_t getEndTnsBiasSpline() const {
     int a = (int)numBiasKnots() - N + 1;
     int64_t t_end_ns = (int64_t)a * dt_ns_bias + start_t_ns;
-    return t_end_ns - (int64_t)1e6;
+    return (int64_t)((double)t_end_ns - 1e6);   // `t_end_ns - 1e6` is evaluated in double and converted back (:1874)
   }
 
   // :523-624 / :626-702 (window mapping only; the residual blocks are wired in build())

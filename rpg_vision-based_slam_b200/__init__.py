@@ -321,7 +321,7 @@ class BSplineSO3R3:
 
     def getEndTns(self):
         """bspline_so3r3.h:1862-1867 (1 ms before the end of the last window)"""
-        return (self.numKnots() - self.N + 1) * self.dt_ns + self.start_t_ns - 1000000
+        return int(float((self.numKnots() - self.N + 1) * self.dt_ns + self.start_t_ns) - 1e6)   # `t_end_ns - 1e6` goes through double
 
     def traceSpline(self, dt_ns, t_end_ns=None):
         """traceSpline (save.h:99-121): rows 'timestamp_s tx ty tz qx qy qz qw' from getStartTns() to getEndTns() (exclusive)"""

@@ -178,13 +178,12 @@ int align_lm_loop(Backend& be, int max_num_iterations, bool no_termination, ctba
   while (!stop) {
     if (iter >= max_num_iterations) { out->termination_type = 1; break; }
     if (radius < min_radius) { if (no_termination) radius = initial_radius; else { out->termination_type = 0; break; } }
-    if (invalid > max_consecutive_invalid && !no_termination) { out->termination_type = 2; break; }
     ++iter;
     rc = be.step(radius, false, sc); if (rc) return rc;
     const double model_cost_change = sc[AK_MODEL], step_norm = sc[AK_STEP];
     const bool ok = sc[AK_OK] != 0.0 && std::isfinite(model_cost_change) && std::isfinite(step_norm);
     if (!ok || model_cost_change <= 0.0) {
-      ++invalid;
+      if (++invalid >= max_consecutive_invalid && !no_termination) { out->termination_type = 2; break; }   // HandleInvalidStep [Ceres, recalled]
       radius /= decrease_factor; decrease_factor *= 2.0;
       out->num_unsuccessful_steps++;
       log_it(x_cost, 0.0, gmax, 0.0, 0.0, radius, 0);

@@ -148,9 +148,11 @@ int ctba_destroy(ctba_problem* p) {
                         &p->ev.partial, &p->ev.cost,
                         &p->ev_alt.frame_pose, &p->ev_alt.r_reproj, &p->ev_alt.Jl, &p->ev_alt.f_sq, &p->ev_alt.f_w, &p->ev_alt.f_cost, &p->ev_alt.r_acc,
                         &p->ev_alt.r_gyr, &p->ev_alt.J_acc, &p->ev_alt.J_gyr, &p->ev_alt.r_gp, &p->ev_alt.J_gp, &p->ev_alt.r_bias, &p->ev_alt.J_bias,
-                        &p->ev_alt.r_grav, &p->ev_alt.J_grav, &p->ev_alt.partial, &p->ev_alt.cost};
+                        &p->ev_alt.r_grav, &p->ev_alt.J_grav, &p->ev_alt.partial, &p->ev_alt.cost,
+                        &p->ev.r_prior, &p->ev.J_prior, &p->ev_alt.r_prior, &p->ev_alt.J_prior, &p->d_q_u, &p->d_q_inv_std, &p->d_q_meas};
   for (auto* d : dd) d->release();
-  DBuf<int32_t>* di[] = {&p->d_f_s, &p->d_f_obs_begin, &p->d_o_lm, &p->d_o_frame, &p->d_i_s, &p->d_i_sb, &p->d_g_s, &p->d_b_s0, &p->d_b_s1, &p->d_b_which};
+  DBuf<int32_t>* di[] = {&p->d_f_s, &p->d_f_obs_begin, &p->d_o_lm, &p->d_o_frame, &p->d_i_s, &p->d_i_sb, &p->d_g_s, &p->d_b_s0, &p->d_b_s1, &p->d_b_which,
+                         &p->d_q_s, &p->d_q_which};
   for (auto* d : di) d->release();
   if (p->own_stream) cudaStreamDestroy(p->stream);
   delete p;
@@ -175,9 +177,13 @@ int ctba_set_stream(ctba_problem* p, void* s) {
 int ctba_set_knots(ctba_problem* p, int n, const double* q, const double* pos) {
   CHECK_P(p);
   if (n < 0 || !q || !pos) return fail(p, CTBA_E_ARG, "set_knots: bad arguments");
-  if (!p->f_s.empty() || !p->i_s.empty() || !p->g_s.empty()) {
+  if (!p->f_s.empty() || !p->i_s.empty() || !p->g_s.empty() || !p->q_s.empty() || !p->al_s.empty() || !p->b_s0.empty()) {
     if ((size_t)n != p->numKnots()) return fail(p, CTBA_E_STATE, "set_knots: knot count cannot change after measurements were added");
   }
+  // after a solve the device holds the optimised landmarks / biases / globals: bring them to the host before the host copy becomes the
+  // master again (otherwise the next upload would overwrite them with the pre-solve values, or a getter would overwrite the new knots)
+  if (p->device >= 0) cudaSetDevice(p->device);
+  { int rc = download_state(p); if (rc) return rc; }
   if ((size_t)n != p->numKnots()) p->struct_dirty = true;
   p->knot_q.assign(q, q + 4 * (size_t)n); p->knot_p.assign(pos, pos + 3 * (size_t)n);
   p->state_dirty = true;
@@ -197,6 +203,8 @@ int ctba_initialize_biases(ctba_problem* p, double dt_s_bias, const double* a0, 
   CHECK_P(p);
   if (!(dt_s_bias > 0) || !a0 || !g0) return fail(p, CTBA_E_ARG, "initialize_biases: bad arguments");
   if (!p->i_s.empty() || !p->b_s0.empty()) return fail(p, CTBA_E_STATE, "initialize_biases: IMU measurements already added");
+  if (p->device >= 0) cudaSetDevice(p->device);
+  { int rc = download_state(p); if (rc) return rc; }
   p->dt_ns_bias = (int64_t) static_cast<uint64_t>(dt_s_bias / 1e-9);  // :363
   p->inv_dt_bias = 1e9 / p->dt_ns_bias;
   double d = p->dt_s * (double)(p->knot_p.size() / 3);
@@ -333,7 +341,7 @@ int ctba_add_frames(ctba_problem* p, int F, const int64_t* t_ns, const int32_t* 
 static int64_t end_t_ns_bias(const ctba_problem* p) {  // getEndTnsBiasSpline :1870-1875 (N_, not Nb_)
   int a = (int)p->numBiasKnots() - p->N + 1;
   int64_t t_end_ns = (int64_t)a * p->dt_ns_bias + p->start_t_ns;
-  return t_end_ns - (int64_t)1e6;
+  return (int64_t)((double)t_end_ns - 1e6);   // the reference subtracts the double literal 1e6: the result is rounded through double (:1874)
 }
 
 int ctba_add_imu(ctba_problem* p, int n, const int64_t* t_ns, const double* acc, const double* gyr, double acc_nd, double gyr_nd) {

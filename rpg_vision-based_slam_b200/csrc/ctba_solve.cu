@@ -42,10 +42,11 @@ static void swap_state(DeviceState& a, DeviceState& b) {
   std::swap(a.lm, b.lm); std::swap(a.glb, b.glb);
 }
 
-struct EvTimer {
-  cudaEvent_t a, b; cudaStream_t st; double* acc;
+struct EvTimer {   // RAII: the events are released on every path, also on early error returns
+  cudaEvent_t a = nullptr, b = nullptr; cudaStream_t st; double* acc;
   EvTimer(cudaStream_t s, double* t) : st(s), acc(t) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, st); }
-  void stop() { cudaEventRecord(b, st); cudaEventSynchronize(b); float ms = 0; cudaEventElapsedTime(&ms, a, b); *acc += ms * 1e-3; cudaEventDestroy(a); cudaEventDestroy(b); }
+  void stop() { cudaEventRecord(b, st); cudaEventSynchronize(b); float ms = 0; cudaEventElapsedTime(&ms, a, b); *acc += ms * 1e-3; }
+  ~EvTimer() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
 };
 
 int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
@@ -124,7 +125,6 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
   while (true) {
     if (iter >= max_num_iterations) { out->termination_type = 1; break; }
     if (radius < min_radius) { if (p->bench_no_termination) radius = initial_radius; else { out->termination_type = 0; break; } }
-    if (invalid > max_consecutive_invalid && !p->bench_no_termination) { out->termination_type = 2; break; }
     ++iter;
     {
       EvTimer tb(st, &out->time_build_s);
@@ -150,7 +150,8 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
     }
     if (!ok || model_cost_change <= 0.0) {
       if (getenv("CTBA_DEBUG")) fprintf(stderr, "[ctba %p] iter %d invalid step: flag %d %d model %.6g step %.6g radius %.3g\n", (void*)p, iter, host_flag[0], host_flag[1], model_cost_change, step_norm, radius);
-      ++invalid;
+      // HandleInvalidStep [Ceres, recalled]: the max_num_consecutive_invalid_steps-th invalid step in a row ends the solve with FAILURE
+      if (++invalid >= max_consecutive_invalid && !p->bench_no_termination) { out->termination_type = 2; break; }
       radius /= decrease_factor; decrease_factor *= 2.0;
       out->num_unsuccessful_steps++;
       log_it(x_cost, 0.0, gmax, 0.0, 0.0, radius, 0);
