@@ -7,6 +7,7 @@
 #include <cstdint>
 #include <cstring>
 #include "lm.h"
+#include "sparse_lm.h"
 #include "select.h"
 #include "sample.h"
 
@@ -196,6 +197,27 @@ int orc_solve(void* h, int max_iters, int num_threads, double* summary, double* 
     const auto& it = s.iterations[i];
     double* o = iter_log + 7 * i;
     o[0] = it.cost; o[1] = it.cost_change; o[2] = it.gradient_max_norm; o[3] = it.step_norm; o[4] = it.tr_ratio; o[5] = it.tr_radius; o[6] = it.successful;
+  }
+  return 0;
+}
+
+// Sparse LM (sparse_lm.h): the whole problem on `num_threads` host threads.  summary / iter_log as orc_solve; timings (12):
+// [eval_jac_s, eval_res_s, build_s, factor_s, total_s, jac_evals, res_evals, solves, n_band, half_bandwidth, n_globals, n_landmarks]
+int orc_solve_sparse(void* h, int max_iters, int num_threads, int no_termination, double* summary, double* iter_log, int iter_cap, double* timings) {
+  auto* p = (SplineProblem*)h; p->build();
+  SparseTimings tm;
+  SolveSummary s = solveLMSparse(*p, max_iters, num_threads, &tm, no_termination != 0);
+  summary[0] = s.termination_type; summary[1] = s.initial_cost; summary[2] = s.final_cost;
+  summary[3] = s.num_successful_steps; summary[4] = s.num_unsuccessful_steps; summary[5] = (double)s.iterations.size();
+  for (size_t i = 0; i < s.iterations.size() && (int)i < iter_cap; ++i) {
+    const auto& it = s.iterations[i];
+    double* o = iter_log + 7 * i;
+    o[0] = it.cost; o[1] = it.cost_change; o[2] = it.gradient_max_norm; o[3] = it.step_norm; o[4] = it.tr_ratio; o[5] = it.tr_radius; o[6] = it.successful;
+  }
+  if (timings) {
+    const double t[12] = {tm.eval_jac_s, tm.eval_res_s, tm.build_s, tm.factor_s, tm.total_s, (double)tm.jac_evals, (double)tm.res_evals, (double)tm.solves,
+                          (double)tm.n_band, (double)tm.half_bandwidth, (double)tm.n_globals, (double)tm.n_landmarks};
+    std::memcpy(timings, t, sizeof(t));
   }
   return 0;
 }

@@ -20,7 +20,7 @@ i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("api.cpp", "lm.h", "problem.h", "functors.h", "ref_math.h", "jet.h", "select.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("api.cpp", "lm.h", "sparse_lm.h", "problem.h", "functors.h", "ref_math.h", "jet.h", "select.h")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "liboracle.so"], stdout=subprocess.DEVNULL)
     return so
@@ -210,6 +210,20 @@ class OracleSpline:
         n = int(s[5])
         return dict(termination_type=int(s[0]), initial_cost=s[1], final_cost=s[2], num_successful_steps=int(s[3]),
                     num_unsuccessful_steps=int(s[4]), iterations=log[:min(n, cap)].copy())
+
+    def optimizeSparse(self, max_num_iterations, num_threads=1, no_termination=False):
+        """The same LM as optimize() with the sparse exact solve of sparse_lm.h (landmark Schur complement + bordered band Cholesky on
+        host threads): whole BASELINE configs fit.  Adds the phase timings of the run."""
+        s = np.zeros(6)
+        cap = max_num_iterations + 2
+        log = np.zeros((cap, 7))
+        tm = np.zeros(12)
+        self.L.orc_solve_sparse(self.h, int(max_num_iterations), int(num_threads), int(bool(no_termination)), s.ctypes.data_as(C.c_void_p),
+                                log.ctypes.data_as(C.c_void_p), cap, tm.ctypes.data_as(C.c_void_p))
+        n = int(s[5])
+        keys = ["eval_jac_s", "eval_res_s", "build_s", "factor_s", "total_s", "jac_evals", "res_evals", "solves", "n_band", "half_bandwidth", "n_globals", "n_landmarks"]
+        return dict(termination_type=int(s[0]), initial_cost=s[1], final_cost=s[2], num_successful_steps=int(s[3]),
+                    num_unsuccessful_steps=int(s[4]), iterations=log[:min(n, cap)].copy(), timings=dict(zip(keys, [float(v) for v in tm])))
 
     def computeValidReprojections(self, t_ns, pt_begin, uv, lm_index, width, height, cell_size_px):
         t = np.ascontiguousarray(t_ns, dtype=np.int64)
