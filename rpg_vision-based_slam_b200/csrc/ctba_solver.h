@@ -80,7 +80,7 @@ struct SolverData {
   DBuf<double> jscale, jscale_lm;   // Jacobi scaling (fixed per Solve): n_pad+16, 3L
   DBuf<double> delta, delta_lm;     // step: n_pad+16, 3L
   DBuf<double> dpose;               // per frame 6: pose-space step
-  void* band_stream2 = nullptr; void* band_evA = nullptr; void* band_evB = nullptr;   // side stream + events of the step launches
+  void* band_stream2 = nullptr; void* band_stream3 = nullptr; void* band_evA = nullptr; void* band_evB = nullptr; void* band_evC = nullptr;   // side streams + events of the step launches
   void* band_plan = nullptr;        // BandPlan (ctba_band.cu): time partitions, interface system, scratch
   int64_t band_launches = 0;        // kernels in one factor+solve
   void* band_graph_exec = nullptr;  // cudaGraphExec_t of the factor+solve launch sequence (band_factor_solve)
