@@ -1,15 +1,24 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the hot path on synthetic scenes (datasets are not available offline).
 
-metric : LM iterations/s of the full-batch continuous-time bundle adjustment (BASELINE.json `metric`), measured on
-         BASELINE configs[1] (optimize_vi_continuous_time, EuRoC MH_01-shaped: 180 s, 20 Hz camera, 200 Hz IMU,
-         ~40k landmarks, ~600k observations).  One "step" = one trust-region LM iteration over the whole batch
-         (residual+Jacobian evaluation of every term, Schur complement, banded solve, candidate evaluation).
-value  : device-resident rate (state and measurements already in HBM), CUDA events on the launching stream.
-e2e    : the same metric through the C-ABI with HOST buffers: every step re-uploads state + measurements
-         (ctba_invalidate_device), runs ctba_solve(1 iteration) and reads the state back.
-extra  : residual+Jacobian Mobs/s of the evaluation kernels alone, with the roofline of the dominant kernel.
---impl reference : the CPU oracle (restated reference functors, Ceres DynamicAutoDiff schedule) on the host cores.
+metric : LM iterations/s of the full-batch continuous-time bundle adjustment (BASELINE.json `metric`).  Default workload = BASELINE
+         configs[2], the north-star problem (optimize_gv_continuous_time: 1 h, 10k frames, 200k+ landmarks, 5 M observations); it fits one
+         GPU.  N > 1: the SAME problem sharded by time segment over N ranks (strong scaling); `--scaling weak` makes the trajectory N x
+         longer instead.  One "step" = one trust-region LM iteration over the whole batch (residual + Jacobian evaluation of every term,
+         landmark Schur complement, bordered band factorisation, candidate evaluation, accept / reject).
+value  : device-resident rate (state and measurements already in HBM), CUDA events on the solver's stream.  The timed region starts from
+         the scene's initial (perturbed) state; accepted / rejected step counts are printed; if more than 20 % of the timed steps were
+         rejected (the LM has converged inside the region) the region is timed again with every valid candidate accepted, so that each
+         timed iteration does the full work of an accepted step (`timed_mode`).
+e2e    : the same metric through the C-ABI with HOST buffers: every step re-uploads state + measurements (ctba_invalidate_device), runs
+         ctba_solve(1 iteration) and reads the state back.
+also   : N = 1 only — the device-resident rate of configs[0] (G+V+I driver shape) and configs[1] (V+I, EuRoC-shaped).
+roofline      : HBM roofline of k_reproj (the per-observation residual + Jacobian kernel north_star's 60 % target names).
+roofline_band : FP64 tensor-pipe roofline of the band factorisation (the phase that dominates the iteration): algorithmic flops of the
+                block band Cholesky, nbc (nbw+1)(nbw+2)/2 block products of 2*32^3 flop, over the measured solve-phase time and the measured
+                DMMA peak (profiles/fp64_peaks.json).
+--impl reference : the reference's CPU path restated (oracle): Jet evaluation with Ceres' DynamicAutoDiff schedule + sparse exact LM step
+         (landmark Schur complement + band Cholesky) on all host threads, on the WHOLE configured scene, one LM iteration per step.
 """
 import argparse
 import importlib
@@ -25,8 +34,9 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 PKG = "rpg_vision-based_slam_b200"
-WORKLOAD = {1: "configs[0] optimize_continuous_time indoor_forward_3-shaped", 2: "configs[1] optimize_vi_continuous_time EuRoC MH_01-shaped",
+WORKLOAD = {1: "configs[0] optimize_continuous_time indoor_forward_3-shaped (G+V+I)", 2: "configs[1] optimize_vi_continuous_time EuRoC MH_01-shaped",
             3: "configs[2] optimize_gv_continuous_time 1h/10k frames/5M obs"}
+BASE = {1: (50.0, 20000), 2: (180.0, 40000), 3: (3600.0, 270000)}   # duration, landmarks of the configured scene
 
 
 def clocks_sampler(stop, out, dev):
@@ -55,34 +65,92 @@ def clocks_summary(samples):
     return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(samples[0][1]), "reasons": reasons}
 
 
-def cpu_reference_leg(scene_mod, cfg, steps, warmup, threads, budget_s=20.0):
-    """The reference's CPU path restated (oracle): Jacobian evaluation with the Ceres DynamicAutoDiff schedule (stride-4 Jets,
-    one residual block per frame incl. all its landmarks) + a residual-only candidate evaluation = the evaluation work of one
-    LM iteration.  The sparse Cholesky of Ceres is NOT timed (Ceres is absent; the oracle's exact solver is dense), so the
-    reported LM rate is an UPPER bound of the CPU rate.  Bounded sample: a time slice of the same scene."""
+def cpu_reference_leg(scene_mod, cfg, steps, warmup, threads, budget_s):
+    """The reference's CPU path restated (oracle/): ONE LM iteration per step on the WHOLE configured scene — Jacobian evaluation with the
+    Ceres DynamicAutoDiff schedule (stride-4 Jets, one residual block per frame with all its landmarks: what the reference executes),
+    landmark Schur complement + bordered band Cholesky (oracle/sparse_lm.h, an exact sparse step like SPARSE_NORMAL_CHOLESKY, with an
+    elimination order that is favourable to the CPU), candidate evaluation, accept / reject.  Steps beyond the time budget are not run:
+    the line reports the steps that were."""
     from oracle.binding import OracleSpline
     pkg = importlib.import_module(PKG)
-    slice_s = 3.0
-    dens = scene_mod.config_scene(cfg, duration_s=slice_s, n_landmarks=1)  # cheap call to read rates
-    full = {1: (50.0, 20000), 2: (180.0, 40000), 3: (3600.0, 270000)}[cfg]
-    sc = scene_mod.config_scene(cfg, duration_s=slice_s, n_landmarks=max(int(full[1] * slice_s / full[0]), 50))
+    sc = scene_mod.config_scene(cfg)
     o = OracleSpline(sc["order"], sc["dt_ns"], sc["start_t_ns"])
     pkg.load_scene(o, sc)
     c = o.counts()
-    t1, obs = o.timeEvaluate(threads, 1, 0)   # calibrate
-    reps = max(1, min(int(budget_s / max(t1, 1e-3) / max(steps + warmup, 1)), 3))
-    times = []
+    t_begin = time.perf_counter()
+    times, phases, done_w = [], [], 0
     for i in range(warmup + steps):
-        t, obs = o.timeEvaluate(threads, reps, 0)
-        t0 = time.perf_counter(); o.cost(); tc = time.perf_counter() - t0   # candidate (residual-only) evaluation, 1 thread -> scale
-        if i >= warmup:
-            times.append(t / reps + tc / threads)
-    t_iter_sample = float(np.mean(times))
-    frac = slice_s / full[0]
-    return dict(sample=f"{slice_s:.0f} s slice of the scene ({c['frames']} frames, {c['obs']} observations, {c['accel']} IMU samples), "
-                       f"evaluation work of one LM iteration, linear solve excluded (upper bound)",
-                t_iter_sample=t_iter_sample, obs_sample=c["obs"], lm_per_s=frac / t_iter_sample, mobs_per_s=c["obs"] / (t_iter_sample) / 1e6,
-                threads=threads)
+        t0 = time.perf_counter()
+        s = o.optimizeSparse(1, threads, True)
+        dt = time.perf_counter() - t0
+        tm = s["timings"]
+        # a Solve of one iteration evaluates the Jacobian at the start AND after an accepted step; one LM iteration owns one Jacobian
+        # evaluation, one build + factorisation and one candidate evaluation
+        t_iter = tm["eval_jac_s"] / max(tm["jac_evals"], 1) + tm["eval_res_s"] + tm["build_s"] + tm["factor_s"]
+        if i < warmup:
+            done_w += 1
+        else:
+            times.append(t_iter); phases.append(tm)
+        elapsed = time.perf_counter() - t_begin
+        if i + 1 >= warmup + 1 and elapsed + dt > budget_s:   # at least one timed step
+            break
+    t_it = float(np.mean(times))
+    ph = {k: float(np.mean([p[k] / (max(p["jac_evals"], 1) if k == "eval_jac_s" else 1.0) for p in phases])) for k in ("eval_jac_s", "eval_res_s", "build_s", "factor_s")}
+    return dict(sample=f"whole scene ({c['frames']} frames, {c['obs']} observations, {c['accel']} IMU samples, {c['gp']} GP samples): {len(times)} timed LM "
+                       f"iteration(s) after {done_w} warm-up; Jacobians by Jet autodiff with Ceres' schedule, sparse exact step (Schur + band Cholesky)",
+                t_iter=t_it, lm_per_s=1.0 / t_it, mobs_per_s=c["obs"] / ph["eval_jac_s"] / 1e6, threads=threads, steps_done=len(times), warmup_done=done_w,
+                phases_s=ph, half_bandwidth=int(phases[-1]["half_bandwidth"]), n_band=int(phases[-1]["n_band"]))
+
+
+def reset_state(g, sc):
+    """The scene's initial (perturbed) state back into the handle."""
+    g.setKnots(sc["knot_q"], sc["knot_p"])
+    g.set3DPoints(sc["landmarks"])
+    g.setGlobals(sc["scale"], sc["p_bp"], sc["g"], sc["t_s_gp"])
+    c = np.zeros(10); c[4] = 1.0
+    g.setCorrections(c)
+    if sc["imu_t_ns"].size:
+        nb = g.numBiasKnots()
+        g.setBiases(np.tile(sc["init_acc_bias"], (nb, 1)), np.tile(sc["init_gyro_bias"], (nb, 1)))
+
+
+def timed_lm(torch, g, sc, stream, steps, warmup, barrier):
+    """K LM iterations from the initial state, device resident.  Returns (ms_total, summary, mode)."""
+    def run(mode):
+        g.setOption("bench_accept_all", 1 if mode == "accept_all" else 0)
+        reset_state(g, sc)
+        g.optimize(0)                      # uploads the state, evaluates; no iteration
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        s = g.optimize(steps)
+        e1.record(stream)
+        barrier()
+        return e0.elapsed_time(e1), s
+    g.optimize(max(warmup, 3))             # warm-up: structure analysis, graph capture, clocks
+    ms, s = run("lm")
+    mode = "lm"
+    if s["num_unsuccessful_steps"] > 0.2 * steps:
+        ms, s = run("accept_all")
+        mode = "accept_all"
+    g.setOption("bench_accept_all", 0)
+    return ms, s, mode
+
+
+def small_config_rate(torch, pkg, scene_mod, cfg, dev, steps=10):
+    sc = scene_mod.config_scene(cfg)
+    g = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=dev)
+    pkg.load_scene(g, sc)
+    stream = torch.cuda.Stream()
+    g.setStream(stream.cuda_stream)
+    g.setOption("bench_no_termination", 1)
+    ms, s, mode = timed_lm(torch, g, sc, stream, steps, 3, torch.cuda.synchronize)
+    n = g.counts()
+    out = {"workload": WORKLOAD[cfg], "ms_per_step": ms / steps, "lm_it_per_s": 1e3 * steps / ms, "obs": n["obs"], "timed_mode": mode,
+           "accepted": s["num_successful_steps"], "rejected": s["num_unsuccessful_steps"],
+           "lm_breakdown_ms": {"eval": 1e3 * s["time_eval_s"] / steps, "assemble": 1e3 * s["time_build_s"] / steps, "solve": 1e3 * s["time_solve_s"] / steps}}
+    g.close()
+    return out
 
 
 def main():
@@ -91,9 +159,11 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--config", type=int, default=2)
-    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
-                    help="N > 1: weak = ONE trajectory of N x the configured duration; strong = the configured problem itself, sharded over N ranks")
+    ap.add_argument("--config", type=int, default=3)
+    ap.add_argument("--scaling", default="strong", choices=["weak", "strong"],
+                    help="N > 1: strong = the configured problem itself, sharded over N ranks; weak = ONE trajectory of N x the configured duration")
+    ap.add_argument("--cpu-budget-s", type=float, default=None, help="time budget of the CPU leg (reference arm: 240 s; cpu_baseline: 100 s)")
+    ap.add_argument("--no-also", action="store_true", help="skip the configs[0] / configs[1] rates")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -104,11 +174,12 @@ def main():
     if a.impl == "reference":
         if rank != 0:
             return
-        r = cpu_reference_leg(scene_mod, a.config, a.steps, max(a.warmup, 1), threads)
-        line = {"impl": "reference", "metric": "LM iterations/s", "value": r["lm_per_s"], "unit": "it/s", "n_gpus": a.gpus, "steps": a.steps,
-                "warmup": a.warmup, "ms_per_step": 1e3 / r["lm_per_s"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f64", "data": "synthetic", "config": {"workload": WORKLOAD[a.config]},
-                "cpu_baseline": {"value": r["lm_per_s"], "unit": "it/s", "cores": threads, "kind": "port", "sample": r["sample"]},
+        r = cpu_reference_leg(scene_mod, a.config, a.steps, a.warmup, threads, a.cpu_budget_s or 240.0)
+        line = {"impl": "reference", "metric": "LM iterations/s", "value": r["lm_per_s"], "unit": "it/s", "n_gpus": a.gpus, "steps": r["steps_done"],
+                "warmup": r["warmup_done"], "steps_requested": a.steps, "warmup_requested": a.warmup, "ms_per_step": 1e3 * r["t_iter"], "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": {"workload": WORKLOAD[a.config]},
+                "cpu_baseline": {"value": r["lm_per_s"], "unit": "it/s", "cores": threads, "kind": "port", "sample": r["sample"], "phases_s": r["phases_s"],
+                                 "half_bandwidth": r["half_bandwidth"], "band_unknowns": r["n_band"]},
                 "e2e": {"value": r["lm_per_s"], "unit": "it/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "mobs_per_s": r["mobs_per_s"]}
         print(json.dumps(line))
@@ -120,16 +191,15 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
     torch.cuda.set_device(local_rank)
-    # N > 1: ONE trajectory of N x the configured duration (N x the landmarks), sharded by time segment over the N ranks (weak scaling:
-    # the per-GPU share of the problem is the configured workload; NCCL exchange steps per LM iteration).  Every rank is
-    # handed the complete problem through the same C-ABI calls as a single-GPU caller; the library keeps the rank's units.
-    base = {1: (50.0, 20000), 2: (180.0, 40000), 3: (3600.0, 270000)}[a.config]
+    # Every rank is handed the complete problem through the same C-ABI calls as a single-GPU caller; the library keeps the rank's units
+    # (time-segment sharding, NCCL exchange steps per LM iteration: DESIGN.md §7).
     weak = world > 1 and a.scaling == "weak"
     mult = world if weak else 1
-    sc = scene_mod.config_scene(a.config, duration_s=base[0] * world, n_landmarks=base[1] * world) if weak else scene_mod.config_scene(a.config)
+    sc = scene_mod.config_scene(a.config, duration_s=BASE[a.config][0] * world, n_landmarks=BASE[a.config][1] * world) if weak else scene_mod.config_scene(a.config)
     g = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=local_rank)
     pkg.load_scene(g, sc)
     n_total = g.counts()
+    plan1 = g.shardPlan(1, 0)          # structure of the reduced system: block columns, band width
     stream = torch.cuda.Stream()
     g.setStream(stream.cuda_stream)
     g.setOption("bench_no_termination", 1)
@@ -147,20 +217,14 @@ def main():
             torch.cuda.synchronize()
 
     # ---- device-resident LM iterations ----
-    g.optimize(max(a.warmup, 3))
-    n = g.counts()     # sharded: this rank's units
-    barrier()
     stop = threading.Event(); samples = []
     th = threading.Thread(target=clocks_sampler, args=(stop, samples, local_rank)); th.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    s = g.optimize(a.steps)
-    e1.record(stream)
-    barrier()
-    ms_total = e0.elapsed_time(e1)
+    ms_total, s, mode = timed_lm(torch, g, sc, stream, a.steps, a.warmup, barrier)
+    n = g.counts()     # sharded: this rank's units
     steps_done = s["iterations"].shape[0] - 1
     assert steps_done == a.steps, (steps_done, a.steps)
     launches = s["kernel_launches"]
+    trace = s["iterations"][:, 0].copy(); acc_seq = s["iterations"][:, 6].copy()
 
     # ---- residual+Jacobian kernels alone ----
     for _ in range(3):
@@ -179,6 +243,7 @@ def main():
     # ---- end to end through the C-ABI with host buffers ----
     h2d, d2h = g.transferBytes()
     e2e_steps = max(3, min(a.steps, 10))
+    reset_state(g, sc)
     g.invalidateDevice(); g.optimize(1); g.getKnots()
     barrier()
     t0 = time.perf_counter()
@@ -188,6 +253,26 @@ def main():
         g.getKnots(); g.get3DPoints()  # result back in host memory
     torch.cuda.synchronize()
     t_e2e = (time.perf_counter() - t0) / e2e_steps
+
+    # ---- N > 1: the sharded (NCCL) solve against the SAME problem solved unsharded on rank 0, outside every timed region ----
+    parity = None
+    if world > 1:
+        reset_state(g, sc)
+        g.setOption("bench_accept_all", 0)
+        sp = g.optimize(3)
+        if rank == 0:
+            u = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=local_rank)
+            pkg.load_scene(u, sc)
+            u.setOption("bench_no_termination", 1)
+            su = u.optimize(3)
+            a_, b_ = sp["iterations"], su["iterations"]
+            parity = {"iterations": 3, "cost_rel": float(np.max(np.abs(a_[:, 0] - b_[:, 0]) / np.abs(b_[:, 0]))),
+                      "accept_seq_equal": bool((a_[:, 6] == b_[:, 6]).all())}
+            (qs, ps), (qu, pu) = g.getKnots(), u.getKnots()
+            parity["knot_pos_max_abs_m"] = float(np.abs(ps - pu).max())
+            u.close()
+        else:
+            g.getKnots()
 
     dev = f"cuda:{local_rank}"
     tms = torch.tensor([ms_total, t_e2e * 1e3, ms_eval, ms_reproj, ms_reproj_warm], dtype=torch.float64, device=dev)
@@ -202,9 +287,13 @@ def main():
             dist.destroy_process_group()
         return
     ms_step = ms_total / a.steps
-    peaks = {}
+    peaks, fp64 = {}, {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    try:
+        fp64 = json.load(open(os.path.join(ROOT, "profiles", "fp64_peaks.json")))
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
@@ -222,23 +311,44 @@ def main():
         wl += f" x {world}: ONE trajectory of {world} x the duration, sharded by time segment over {world} ranks (NCCL)"
     elif world > 1:
         wl += f", the one problem sharded by time segment over {world} ranks (NCCL)"
+    solve_ms = 1e3 * s["time_solve_s"] / a.steps
+    nbc, nbw = plan1["nbc"], plan1["nbw"]
+    band_flops = float(nbc) * (nbw + 1) * (nbw + 2) / 2.0 * 2.0 * 32 ** 3
+    dmma_peak = float(fp64.get("dmma_tflops", 37.1))
+    bound = "hbm" if (traffic is None or traffic >= 0.5 * alg_bytes) else "l2"   # measured DRAM traffic far below the algorithmic bytes: the data lives in L2
     line = {"metric": "LM iterations/s", "value": mult * 1e3 / ms_step, "unit": "it/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak" if (weak or world == 1) else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": wl, "value_is": "N x (LM iterations/s of the joint N-segment problem) = iterations/s in units of the configured workload",
-                       "l2": "LM step: band (49 MB) + Jacobians (38 MB) per config-2 segment, not flushed (they are produced and consumed on the device "
-                             "inside the step); roofline kernel: L2 flushed with a 256 MiB memset between launches", **n_total, "obs_all_ranks": obs_all},
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": wl, "value_is": "LM iterations/s of the configured problem" + (" x N (weak: N x longer trajectory)" if weak else ""),
+                       "l2": "LM step: the working set (band 2 x 1.2 GB + Jacobians 0.3 GB at configs[2]) is larger than L2, nothing is flushed inside the step; "
+                             "roofline kernel: L2 flushed with a 256 MiB memset between launches", **n_total, "obs_all_ranks": obs_all,
+                       "band_block_columns": nbc, "band_half_width_blocks": nbw},
+            "timed_mode": mode, "accepted": int(s["num_successful_steps"]), "rejected": int(s["num_unsuccessful_steps"]),
             "gpu_launches": int(launches_all), "clocks": clocks_summary(samples),
             "e2e": {"value": mult * 1e3 / e2e_ms, "unit": "it/s", "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h_all},
             "mobs_per_s": obs_all / ms_eval / 1e3, "eval_ms": ms_eval,
-            "lm_breakdown_ms": {"eval": 1e3 * s["time_eval_s"] / a.steps, "assemble": 1e3 * s["time_build_s"] / a.steps, "solve": 1e3 * s["time_solve_s"] / a.steps},
-            "roofline": {"kernel": "k_reproj (per-observation residual + Jacobian)", "bound": "hbm", "achieved": alg_bytes / (ms_reproj * 1e-3) / 1e9,
+            "lm_breakdown_ms": {"eval": 1e3 * s["time_eval_s"] / a.steps, "assemble": 1e3 * s["time_build_s"] / a.steps, "solve": solve_ms},
+            "roofline": {"kernel": "k_reproj (per-observation residual + Jacobian)", "bound": bound, "achieved": alg_bytes / (ms_reproj * 1e-3) / 1e9,
                          "peak": peak, "unit": "GB/s", "frac": alg_bytes / (ms_reproj * 1e-3) / 1e9 / peak, "traffic": traffic,
                          "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": ms_reproj, "launch_ms_l2_warm": ms_reproj_warm,
                          "evaluation_pass_gbs": alg_bytes / (ms_eval * 1e-3) / 1e9,
-                         "peak_source": "MEASURED_PEAKS.json (burst copy)" if peaks else "fallback"}}
+                         "peak_source": "MEASURED_PEAKS.json (burst copy)" if peaks else "fallback"},
+            "roofline_band": {"kernel": "band factorisation + substitutions (k_band_panel / k_band_gather / k_band_border / k_gram_* / k_band_backsolve)",
+                              "bound": "tensor", "achieved": band_flops / (solve_ms * 1e-3) / 1e12, "peak": dmma_peak, "unit": "TFLOP/s",
+                              "frac": band_flops / (solve_ms * 1e-3) / 1e12 / dmma_peak, "traffic": None, "algorithmic_flops": band_flops,
+                              "solve_ms": solve_ms, "note": "FP64 DMMA peak measured by profiles/tools/fp64_peaks.cu (profiles/fp64_peaks.json); algorithmic flops = "
+                              "sequential block band Cholesky, the time partitions' redundant border work is not counted" + (" (N > 1: rank 0's share of the time, whole-problem flops)" if world > 1 else "")}}
+    if parity is not None:
+        line["parity_vs_unsharded"] = parity
+        if parity["cost_rel"] > 1e-8 or not parity["accept_seq_equal"]:
+            print(json.dumps(line))
+            raise SystemExit(f"sharded solve deviates from the unsharded solve: {parity}")
     if world == 1:
-        r = cpu_reference_leg(scene_mod, a.config, 2, 1, threads, budget_s=15.0)
-        line["cpu_baseline"] = {"value": r["lm_per_s"], "unit": "it/s", "cores": threads, "kind": "port", "sample": r["sample"], "mobs_per_s": r["mobs_per_s"]}
+        if not a.no_also:
+            del g
+            line["also"] = {f"cfg{c}": small_config_rate(torch, pkg, scene_mod, c, local_rank) for c in (1, 2) if c != a.config}
+        r = cpu_reference_leg(scene_mod, a.config, 1, 0, threads, a.cpu_budget_s or 100.0)
+        line["cpu_baseline"] = {"value": r["lm_per_s"], "unit": "it/s", "cores": threads, "kind": "port", "sample": r["sample"], "mobs_per_s": r["mobs_per_s"],
+                                "phases_s": r["phases_s"]}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -16,7 +16,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libctba.so")
+LIB_PATH = os.environ.get("CTBA_LIB_PATH") or os.path.join(_HERE, "csrc", "libctba.so")   # the override loads instrumented debug builds (profiles/tools)
 _LIB = None
 
 CTBA_REPROJ, CTBA_ACCEL, CTBA_GYRO, CTBA_GP, CTBA_BIAS, CTBA_GRAVITY, CTBA_PRIOR = range(7)

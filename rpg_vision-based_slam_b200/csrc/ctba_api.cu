@@ -617,8 +617,8 @@ int ctba_set_option(ctba_problem* p, const char* name, double value) {
   CHECK_P(p);
   if (!name) return CTBA_E_ARG;
   if (!std::strcmp(name, "bench_no_termination")) { p->bench_no_termination = value != 0.0; return CTBA_OK; }
+  if (!std::strcmp(name, "bench_accept_all")) { p->bench_accept_all = value != 0.0; return CTBA_OK; }
   if (!std::strcmp(name, "relinearize_mask")) { p->relinearize_mask = (int)value & 3; return CTBA_OK; }
-  if (!std::strcmp(name, "band_pdl")) { p->band_pdl = (int)value; return CTBA_OK; }
   if (!std::strcmp(name, "band_partitions")) { p->band_partitions = (int)value; return CTBA_OK; }
   if (!std::strcmp(name, "schur_two_stage")) { p->schur_two_stage = value != 0.0; return CTBA_OK; }
   if (!std::strcmp(name, "schur_compact")) { p->schur_compact = value != 0.0; return CTBA_OK; }

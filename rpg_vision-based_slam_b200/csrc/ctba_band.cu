@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <cmath>
 #include <initializer_list>
+#include <vector>
 #include "ctba_solver.h"
 
 namespace ctba {
@@ -229,6 +230,18 @@ __host__ __device__ inline int part_gather_tasks(const BandLayout& B, const Band
   return part_gather_targets(q, t, final_pass) * part_gather_slots(B, q, final_pass, defer);
 }
 
+// Debug build only (-DCTBA_BAND_TRACE, profiles/tools/band_trace.py): first CTA start / last CTA end of every step launch in nanoseconds
+// (globaltimer), per kernel kind (0 panel, 1 gather, 2 border chunk) — the timeline of one factorisation as it runs inside the graph.
+#ifdef CTBA_BAND_TRACE
+constexpr int kTraceSteps = 8192;
+__device__ unsigned long long g_band_trace[3][kTraceSteps][2];
+__device__ __forceinline__ unsigned long long trace_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define BAND_TRACE_BEGIN(kind, t) do { if (threadIdx.x == 0 && (t) < kTraceSteps) atomicMin(&g_band_trace[kind][t][0], trace_now()); } while (0)
+#define BAND_TRACE_END(kind, t) do { if (threadIdx.x == 0 && (t) < kTraceSteps) atomicMax(&g_band_trace[kind][t][1], trace_now()); } while (0)
+#else
+#define BAND_TRACE_BEGIN(kind, t) do {} while (0)
+#define BAND_TRACE_END(kind, t) do {} while (0)
+#endif
 #ifdef CTBA_BAND_TIMING
 __device__ long long g_band_clk[8];
 #define BAND_CLK(k) do { if (j == 100 && b == 1 && tid == 0) g_band_clk[k] = clock64(); } while (0)
@@ -259,6 +272,7 @@ __global__ void __launch_bounds__(kStepThreads) k_band_panel(BandLayout B, const
   if (pi >= PS.P) return;
   const BandPart& Q = PS.part[pi];
   const int j = Q.c0 + t;
+  BAND_TRACE_BEGIN(0, t);
   const bool prev = t > 0 && B.nbw >= 1;
   const double* Lprev = B.band + ((size_t)max(j - 1, 0) * nb1) * 1024;  // column j-1: block (j-1+o, j-1) at offset o
   const int lcol = j - Q.c0;                                            // column of fb
@@ -302,6 +316,7 @@ __global__ void __launch_bounds__(kStepThreads) k_band_panel(BandLayout B, const
   } else {
     for (int e = tid; e < nrows * kNB; e += kStepThreads) { const int r = e >> 5, c = e & 31; Fb[(size_t)r * Q.ld + c] = sX[r * kLd + c]; }
   }
+  BAND_TRACE_END(0, t);
 }
 
 // Left-looking trailing update.  The right-looking version (one rank-32 update of the whole trailing window per step) read and wrote every
@@ -347,6 +362,7 @@ __global__ void __launch_bounds__(kGatherThreads) k_band_gather(BandLayout B, co
   const int k_hi = FINAL ? Q.c0 + Q.nI - 1 : c - 2;               // last finished column that is gathered here
   const int last = Q.c0 + Q.ncols - 1 < B.nbc - 1 ? Q.c0 + Q.ncols - 1 : B.nbc - 1;
   const int g = lane >> 2, tq = lane & 3, wr = warp >> 1, wc = warp & 1;
+  if (!FINAL) BAND_TRACE_BEGIN(1, t);
   int k_lo = Q.c0 > c - B.nbw ? Q.c0 : c - B.nbw;
   const double* pa; size_t a_step, a8; double* T; int ldt;
   if (slot < nb1) {                                // band row block i = c + slot
@@ -396,6 +412,7 @@ __global__ void __launch_bounds__(kGatherThreads) k_band_gather(BandLayout B, co
       v.y -= (acc[0][i][h][1] + acc[1][i][h][1]) + (acc[2][i][h][1] + acc[3][i][h][1]);
       *d = v;
     }
+  if (!FINAL) BAND_TRACE_END(1, t);
 }
 
 // ---- deferred border rows:  W = FB L^-T  as a pipeline that trails the band factorisation ------------------------------------------------
@@ -421,6 +438,7 @@ __global__ void __launch_bounds__(kBorderThreads) k_band_border(BandLayout B, co
   const BandPart& Q = PS.part[pi];
   double* F = Q.fb + (size_t)u * kNB * Q.ld;                       // row block u of the partition's border, row stride Q.ld
   const int tend = t1 < Q.nI ? t1 : Q.nI;
+  BAND_TRACE_BEGIN(2, t0);
   for (int t = t0; t < tend; ++t) {
     const int j = Q.c0 + t;
     const int k_lo = Q.c0 > j - B.nbw ? Q.c0 : j - B.nbw;
@@ -479,6 +497,7 @@ __global__ void __launch_bounds__(kBorderThreads) k_band_border(BandLayout B, co
       *reinterpret_cast<double2*>(Fj + (size_t)(8 * warp + g) * Q.ld + 8 * h + 2 * tq) = make_double2(x[h][0][0] + x[h][1][0], x[h][0][1] + x[h][1][1]);
     __syncthreads();   // the block is visible to the whole CTA before the next column reads it back; sP / sL may be overwritten
   }
+  BAND_TRACE_END(2, t0);
 }
 
 // ---- partition border initialisation -------------------------------------------------------------------------------------------
@@ -1224,5 +1243,18 @@ int band_factor_solve(ctba_problem* p) {
 #ifdef CTBA_BAND_TIMING
 extern "C" int ctba_debug_band_clocks(long long* out8) {
   return cudaMemcpyFromSymbol(out8, ctba::g_band_clk, sizeof(long long) * 8) == cudaSuccess ? 0 : -2;
+}
+#endif
+#ifdef CTBA_BAND_TRACE
+// reset != 0: arm the trace (starts = max, ends = 0); otherwise copy it out: 3 x 8192 x 2 unsigned 64-bit nanosecond stamps
+extern "C" int ctba_debug_band_trace(unsigned long long* out, int reset) {
+  const size_t n = (size_t)3 * ctba::kTraceSteps * 2;
+  if (reset) {
+    std::vector<unsigned long long> h(n);
+    for (size_t i = 0; i < n; ++i) h[i] = (i & 1) ? 0ull : ~0ull;
+    return cudaMemcpyToSymbol(ctba::g_band_trace, h.data(), n * sizeof(unsigned long long)) == cudaSuccess ? 0 : -2;
+  }
+  cudaDeviceSynchronize();
+  return cudaMemcpyFromSymbol(out, ctba::g_band_trace, n * sizeof(unsigned long long)) == cudaSuccess ? 0 : -2;
 }
 #endif

@@ -97,8 +97,8 @@ struct ctba_problem {
   double q_bc0[4] = {0, 0, 0, 1}, p_bc0[3] = {0, 0, 0};
   double cauchy_a = 3.0;
   bool bench_no_termination = false;
+  bool bench_accept_all = false;   // timing only: every valid candidate is taken, so that each iteration does the full work of an accepted step
   int relinearize_mask = 3;  // ctba_relinearize_time_offsets folds: bit 0 the spline-imu offset, bit 1 the spline / global-sensor offset
-  int band_pdl = 2;        // programmatic dependent launch between the block-column kernels (0 off, 1 trigger at entry, 2 after staging)
   int band_partitions = 0; // time partitions of the band factorisation: 0 = automatic, k = force k (1 = plain sequential)
   int band_nested = 0;     // 1: interface systems are reduced recursively (odd-even over the separators); 0: one flat interface system
   bool schur_two_stage = true;   // knot-space expansion of the Schur blocks through U(f, kc) (false: one pass over all frame pairs per knot pair)

@@ -172,7 +172,7 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
       log_it(x_cost, cost_change, gmax, step_norm, ratio, radius, 0);
       out->termination_type = 0; break;
     }
-    if (std::isfinite(cand_cost) && ratio > min_relative_decrease) {
+    if (std::isfinite(cand_cost) && (ratio > min_relative_decrease || p->bench_accept_all)) {
       swap_state(p->dstate, sd->cand);
       std::swap(p->ev, p->ev_alt);
       p->host_state_stale = true;
@@ -180,8 +180,8 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
       rc = build_at(); if (rc) return rc;
       rc = scalars(p->dstate.ptrs(), p->dstate.ptrs(), -1.0); if (rc) return rc;
       x_norm = std::sqrt(host_sc[SC_XNORM2]); gmax = host_sc[SC_GMAX];
-      radius = std::min(max_radius, radius / std::max(1.0 / 3.0, 1.0 - std::pow(2.0 * ratio - 1.0, 3)));
-      decrease_factor = 2.0;
+      if (ratio > min_relative_decrease) { radius = std::min(max_radius, radius / std::max(1.0 / 3.0, 1.0 - std::pow(2.0 * ratio - 1.0, 3))); decrease_factor = 2.0; }
+      else { radius /= decrease_factor; decrease_factor *= 2.0; }   // bench_accept_all only
       out->num_successful_steps++;
       log_it(x_cost, cost_change, gmax, step_norm, ratio, radius, 1);
       if (!p->bench_no_termination && gmax <= gradient_tolerance) { out->termination_type = 0; break; }
