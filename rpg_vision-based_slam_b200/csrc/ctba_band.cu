@@ -4,9 +4,9 @@
 // This is the linear solve that Ceres' SPARSE_NORMAL_CHOLESKY performs inside ceres::Solve for the reference
 // (include/spline/bspline_so3r3.h:1771, 1778) — here on the block band that the spline's locality produces.
 //
-//   k_band_panel / k_band_gather   one launch pair per 32-column block, left-looking with a one-column look-ahead; every 32x32x32
+//   k_band_panel / k_band_update   one launch pair per 32-column block, right-looking with a one-column look-ahead; every 32x32x32
 //                     product runs on the FP64 tensor pipe (mma.sync m8n8k4 f64 -> DMMA)
-//   k_band_border     the border rows of a time partition as a trailing triangular solve with many right-hand sides
+//   k_band_border     the border rows of a time partition as a trailing triangular solve with many right-hand sides (left-looking K loop)
 //   k_corner_partial / k_corner_solve   Schur complement of the band onto the <= 15 global parameters, 15x15 solve
 //   k_back_rhs + k_band_backsolve       backward substitution  L^T x = y - Lb^T z
 #include <cstdlib>
@@ -77,23 +77,17 @@ __device__ __forceinline__ void panel_stage(double* sD, double* sX, const double
     x0 = *reinterpret_cast<const double2*>(Cx + (size_t)r * ldcx + c);
     x1 = *reinterpret_cast<const double2*>(Cx + (size_t)r * ldcx + c + 8);
   }
-  // four accumulator sets per tile (k sub-step ks -> set ks & 3): the dependent-issue latency of DMMA is paid twice per tile instead of
-  // eight times (profiles/fp64_peaks.json: dmma_dependent_latency_cycles)
-  double pd[4][2], qd[4][2], px[4][2], qx[4][2];
-#pragma unroll
-  for (int q = 0; q < 4; ++q) pd[q][0] = pd[q][1] = qd[q][0] = qd[q][1] = px[q][0] = px[q][1] = qx[q][0] = qx[q][1] = 0.0;
-#pragma unroll
-  for (int ks = 0; ks < 8; ++ks) {
-    if (sub_d) { dmma884(pd[ks & 3][0], pd[ks & 3][1], ad[ks], b0[ks]); dmma884(qd[ks & 3][0], qd[ks & 3][1], ad[ks], b1[ks]); }
-    if (sub_x) { dmma884(px[ks & 3][0], px[ks & 3][1], ax[ks], b0[ks]); dmma884(qx[ks & 3][0], qx[ks & 3][1], ax[ks], b1[ks]); }
-  }
   if (sub_d) {
-    d0.x -= (pd[0][0] + pd[1][0]) + (pd[2][0] + pd[3][0]); d0.y -= (pd[0][1] + pd[1][1]) + (pd[2][1] + pd[3][1]);
-    d1.x -= (qd[0][0] + qd[1][0]) + (qd[2][0] + qd[3][0]); d1.y -= (qd[0][1] + qd[1][1]) + (qd[2][1] + qd[3][1]);
+    double p0 = 0.0, p1 = 0.0, q0 = 0.0, q1 = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) { dmma884(p0, p1, ad[ks], b0[ks]); dmma884(q0, q1, ad[ks], b1[ks]); }
+    d0.x -= p0; d0.y -= p1; d1.x -= q0; d1.y -= q1;
   }
   if (sub_x) {
-    x0.x -= (px[0][0] + px[1][0]) + (px[2][0] + px[3][0]); x0.y -= (px[0][1] + px[1][1]) + (px[2][1] + px[3][1]);
-    x1.x -= (qx[0][0] + qx[1][0]) + (qx[2][0] + qx[3][0]); x1.y -= (qx[0][1] + qx[1][1]) + (qx[2][1] + qx[3][1]);
+    double p0 = 0.0, p1 = 0.0, q0 = 0.0, q1 = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) { dmma884(p0, p1, ax[ks], b0[ks]); dmma884(q0, q1, ax[ks], b1[ks]); }
+    x0.x -= p0; x0.y -= p1; x1.x -= q0; x1.y -= q1;
   }
   sD[r * kLd + c] = d0.x; sD[r * kLd + c + 1] = d0.y; sD[r * kLd + c + 8] = d1.x; sD[r * kLd + c + 9] = d1.y;
   if (want_x) { sX[r * kLd + c] = x0.x; sX[r * kLd + c + 1] = x0.y; sX[r * kLd + c + 8] = x1.x; sX[r * kLd + c + 9] = x1.y; }
@@ -205,30 +199,28 @@ struct BandPart {
 // steps; they trail the band factorisation as a triangular solve with many right-hand sides (k_band_border).
 struct BandParts { int P; int sepw; int defer; BandPart part[kMaxParts]; };
 
-// panel tasks of partition q at step t (shared by host and device): diagonal block + sub-diagonal blocks inside the band + (unless they
-// are deferred) the border row blocks
-__host__ __device__ inline int part_panel_tasks(const BandLayout& B, const BandPart& q, int t, int defer) {
-  if (t >= q.nI) return 0;
+// task counts of partition q at step t (shared by host and device)
+__host__ __device__ inline void part_tasks(const BandLayout& B, const BandPart& q, int t, int defer, int* n_panel, int* m_upd, int* k_lo) {
   const int j = q.c0 + t;
+  const bool has_panel = t < q.nI;
   // a partition never reaches past its right separator: at level 0 that is the band reach anyway, at the interface levels (band 2 sepw - 1,
   // interiors one separator wide) the blocks beyond are structurally zero AND belong to a partition that is being factored concurrently
   const int last = q.c0 + q.ncols - 1 < B.nbc - 1 ? q.c0 + q.ncols - 1 : B.nbc - 1;
-  const int rows = B.nbw < last - j ? B.nbw : last - j;
-  return 1 + rows + (defer ? 0 : q.nrb);
+  const int rows = has_panel ? (B.nbw < last - j ? B.nbw : last - j) : 0;
+  *n_panel = has_panel ? 1 + rows + (defer ? 0 : q.nrb) : 0;
+  *k_lo = has_panel ? j + 1 : j;
+  int k_hi = j - 1 + B.nbw; if (k_hi > last) k_hi = last;
+  int m = (t >= 1 && t <= q.nI) ? k_hi - *k_lo + 1 : 0;
+  *m_upd = m > 0 ? m : 0;
 }
-// gather tasks (left-looking update, k_band_gather): one CTA per (target block column, row slot); row slots = nbw + 1 band offsets + the border
-// row blocks.  Step mode (final = 0): the ONE target column c0 + t + 1 of the partition (an interior column that is factored at step t + 1).
-// Final mode: the partition's right-separator columns, which gather the whole interior at once after its last panel step.
-__host__ __device__ inline int part_gather_targets(const BandPart& q, int t, int final_pass) {
-  if (final_pass) return q.ncols - q.nI;
-  return (t >= 1 && t + 1 < q.nI) ? 1 : 0;
+// update tasks of one partition at one step: 64 x 64 super-tiles (2 x 2 blocks) over the lower triangle of the m trailing block columns
+// and over (border row blocks) x (trailing block columns)
+__host__ __device__ inline int part_update_tasks(int m, int nrb) {
+  const int ms = (m + 1) >> 1, nrs = (nrb + 1) >> 1;
+  return m > 0 ? ms * (ms + 1) / 2 + ms * nrs : 0;
 }
-__host__ __device__ inline int part_gather_slots(const BandLayout& B, const BandPart& q, int final_pass, int defer) {
-  return B.nbw + 1 + ((defer && !final_pass) ? 0 : q.nrb);   // deferred border rows are final before the separator gather
-}
-__host__ __device__ inline int part_gather_tasks(const BandLayout& B, const BandPart& q, int t, int final_pass, int defer) {
-  return part_gather_targets(q, t, final_pass) * part_gather_slots(B, q, final_pass, defer);
-}
+
+
 
 // Debug build only (-DCTBA_BAND_TRACE, profiles/tools/band_trace.py): first CTA start / last CTA end of every step launch in nanoseconds
 // (globaltimer), per kernel kind (0 panel, 1 gather, 2 border chunk) — the timeline of one factorisation as it runs inside the graph.
@@ -250,12 +242,15 @@ __device__ long long g_band_clk[8];
 #endif
 
 // Two launches per step t (they run concurrently, on two streams / two graph branches): every partition p advances to its block column
-// j = c0_p + t (left-looking with a one-column look-ahead):
-//   k_band_panel  : apply column j-1's term to the CTA's OWN block of column j (and to the diagonal block, redundantly), factor the diagonal
-//                   block, triangular-solve the block, store it.  Task 0 = diagonal (also stores L_jj^-1 for the border pipeline and the
-//                   backward substitution), tasks 1..rows = sub-diagonal blocks, then (not deferred) one task per border row block.
-//   k_band_gather : every other term of the NEXT column:  T(i, j+1) -= sum_{k <= j-1} L(i,k) L(j+1,k)^T.
-// Pre-condition of step t: columns < j of the interior final, column j carries the terms of columns <= j-2.
+// j = c0_p + t (right-looking with a one-column look-ahead):
+//   k_band_panel  : apply column j-1's update to the CTA's OWN block of column j (and to the diagonal block, redundantly), factor the diagonal
+//                   block, triangular-solve the block, store it.  Task 0 = diagonal (also stores L_jj^-1 for the backward substitution),
+//                   tasks 1..rows = sub-diagonal blocks, then one task per border row block.  This is the critical path.
+//   k_band_update : remaining trailing update of column j-1:  T(i,k) -= L(i,j-1) L(k,j-1)^T  for k_lo <= k <= i <= j-1+nbw, and the border
+//                   row blocks of those block columns.  k_lo = j+1 while the partition still has a panel (the panel CTAs cover column j),
+//                   k_lo = j in the partition's final flush step t = |I_p|.  Small register footprint, so that many CTAs are resident.
+// Both depend on BOTH kernels of step t-1.  Pre-condition of step t: columns < j of the interior final, every trailing block carries the
+// updates of columns <= j-2.
 __global__ void __launch_bounds__(kStepThreads) k_band_panel(BandLayout B, const __grid_constant__ BandParts PS, int t, double* __restrict__ dinv,
                                                              int32_t* __restrict__ flag) {
   __shared__ double sD[kNB * kLd];
@@ -263,9 +258,9 @@ __global__ void __launch_bounds__(kStepThreads) k_band_panel(BandLayout B, const
   __shared__ double sRinv[kNB];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nb1 = B.nbw + 1;
-  int b = blockIdx.x, pi = 0, n_panel = 0;
+  int b = blockIdx.x, pi = 0, n_panel = 0, m = 0, k_lo = 0;
   for (; pi < PS.P; ++pi) {
-    n_panel = part_panel_tasks(B, PS.part[pi], t, PS.defer);
+    part_tasks(B, PS.part[pi], t, PS.defer, &n_panel, &m, &k_lo);
     if (b < n_panel) break;
     b -= n_panel;
   }
@@ -319,100 +314,137 @@ __global__ void __launch_bounds__(kStepThreads) k_band_panel(BandLayout B, const
   BAND_TRACE_END(0, t);
 }
 
-// Left-looking trailing update.  The right-looking version (one rank-32 update of the whole trailing window per step) read and wrote every
-// target block once per block column: 16 KB of L2 traffic per 65 kflop, ~14 TFLOP/s at config 3 with the L2 at 5 TB/s.  Here every target
-// block is written ONCE: the CTA gathers  T(i, c) -= sum_k L(i, k) L(c, k)^T  over all finished columns k in registers (K loop, operand
-// fragments straight from L2, double-buffered in registers; profiles/fp64_peaks.json: 31-33 TFLOP/s of the 37.1 TFLOP/s DMMA peak for this
-// loop shape, against 25 TFLOP/s when the blocks are staged through shared memory by cp.async.bulk).
-//   step mode : launched next to the panel kernel of step t (column j = c0 + t); target = column c = j + 1, terms k <= j - 1 (final since step
-//               t - 1).  The panel kernel of step t + 1 applies the one remaining term k = j itself (its look-ahead).
-//   final mode: after the partition's last panel step, the right-separator columns gather every interior column.
-// CTA = (partition, target column, row slot), 4 warps: warp (wr, wc) owns rows 16 wr .. +16 and columns 16 wc .. +16 of the 32 x 32 target.
-constexpr int kGatherThreads = 128;
-struct GFrag { double a0[8], a1[8], b0[8], b1[8]; };
-__device__ __forceinline__ void gather_load(GFrag& f, const double* __restrict__ pa, size_t a8, const double* __restrict__ pb) {
-  load_frag8(pa, f.a0); load_frag8(pa + a8, f.a1);
-  load_frag8(pb, f.b0); load_frag8(pb + 8 * kNB, f.b1);
-}
-// A warp keeps FOUR sets of its 4 accumulator tiles (k sub-step ks accumulates into set ks & 3: 16 independent DMMA chains, 2 dependent
-// DMMAs per tile and k block) and adds the sets once at the end: the dependent-issue latency of DMMA is far above its issue interval.
-__device__ __forceinline__ void gather_mma(double (&acc)[4][2][2][2], const GFrag& f) {
-#pragma unroll
-  for (int ks = 0; ks < 8; ++ks) {
-    double(&a)[2][2][2] = acc[ks & 3];
-    dmma884(a[0][0][0], a[0][0][1], f.a0[ks], f.b0[ks]); dmma884(a[1][0][0], a[1][0][1], f.a1[ks], f.b0[ks]);
-    dmma884(a[0][1][0], a[0][1][1], f.a0[ks], f.b1[ks]); dmma884(a[1][1][0], a[1][1][1], f.a1[ks], f.b1[ks]);
-  }
-}
-template <int FINAL>
-__global__ void __launch_bounds__(kGatherThreads) k_band_gather(BandLayout B, const __grid_constant__ BandParts PS, int t) {
+// CTA = one super-tile; warp (wr, wc) owns rows 16 (wr & 1) .. +16 of row block (wr >> 1) and the 32 columns of column block wc of it:
+// 2 x 4 DMMA tiles from two A fragments and four B fragments (the one-block-per-CTA version loaded three fragments per two tiles), all
+// operand and target loads issued before the first DMMA.
+__global__ void __launch_bounds__(kStepThreads, 2) k_band_update(BandLayout B, const __grid_constant__ BandParts PS, int t) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nb1 = B.nbw + 1;
-  int u = blockIdx.x, pi = 0;
+  int u = blockIdx.x, pi = 0, n_panel = 0, m = 0, k_lo = 0;
   for (; pi < PS.P; ++pi) {
-    const int nu = part_gather_tasks(B, PS.part[pi], t, FINAL, PS.defer);
+    part_tasks(B, PS.part[pi], t, PS.defer, &n_panel, &m, &k_lo);
+    const int nu = part_update_tasks(m, PS.defer ? 0 : PS.part[pi].nrb);
     if (u < nu) break;
     u -= nu;
   }
   if (pi >= PS.P) return;
   const BandPart& Q = PS.part[pi];
-  const int nslot = part_gather_slots(B, Q, FINAL, PS.defer);
-  const int tc = u / nslot, slot = u - tc * nslot;
-  const int c = FINAL ? Q.c0 + Q.nI + tc : Q.c0 + t + 1;          // target block column
-  const int k_hi = FINAL ? Q.c0 + Q.nI - 1 : c - 2;               // last finished column that is gathered here
-  const int last = Q.c0 + Q.ncols - 1 < B.nbc - 1 ? Q.c0 + Q.ncols - 1 : B.nbc - 1;
+  const int j = Q.c0 + t;
+  BAND_TRACE_BEGIN(1, t);
+  const double* Lprev = B.band + ((size_t)(j - 1) * nb1) * 1024;  // column j-1: block (j-1+o, j-1) at offset o
+  const int ms = (m + 1) >> 1, ntri = ms * (ms + 1) / 2;
   const int g = lane >> 2, tq = lane & 3, wr = warp >> 1, wc = warp & 1;
-  if (!FINAL) BAND_TRACE_BEGIN(1, t);
-  int k_lo = Q.c0 > c - B.nbw ? Q.c0 : c - B.nbw;
-  const double* pa; size_t a_step, a8; double* T; int ldt;
-  if (slot < nb1) {                                // band row block i = c + slot
-    const int i = c + slot;
-    if (i > last) return;
-    if (i - B.nbw > k_lo) k_lo = i - B.nbw;
-    if (k_lo > k_hi) return;
-    pa = B.band + ((size_t)k_lo * nb1 + (i - k_lo)) * 1024 + (size_t)(16 * wr + g) * kNB + 8 * tq;   // L(i, k): next k = + (nb1 - 1) blocks
-    a_step = (size_t)(nb1 - 1) * 1024; a8 = 8 * kNB;
-    T = B.band + ((size_t)c * nb1 + slot) * 1024; ldt = kNB;
-  } else {                                         // border row block rb of the partition (last one: 16 rows)
-    const int rb = slot - nb1;
-    if (k_lo > k_hi) return;
-    if (rb == Q.nrb - 1 && 16 * wr >= kBorder) return;
-    double* F = Q.fb + (size_t)rb * kNB * Q.ld;
-    pa = F + (size_t)(16 * wr + g) * Q.ld + (size_t)(k_lo - Q.c0) * kNB + 8 * tq;
-    a_step = kNB; a8 = (size_t)8 * Q.ld;
-    T = F + (size_t)(c - Q.c0) * kNB; ldt = Q.ld;
+  const int half = wr & 1;                        // which 16 rows of the row block
+  const double* A; const double* Lk; double* T; int lda, ldt;
+  if (u < ntri) {
+    int sa = (int)((sqrtf(8.0f * u + 1.0f) - 1.0f) * 0.5f);
+    while ((sa + 1) * (sa + 2) / 2 <= u) ++sa;
+    while (sa * (sa + 1) / 2 > u) --sa;
+    const int sb = u - sa * (sa + 1) / 2;
+    const int a = 2 * sa + (wr >> 1), c = 2 * sb + wc;          // block row / column inside the trailing window, 0 <= c, a < m
+    if (a >= m || c >= m || c > a) return;                      // warp-uniform: outside the window or above the diagonal
+    const int i = k_lo + a, k = k_lo + c;
+    A = Lprev + (size_t)(i - (j - 1)) * 1024; lda = kNB;
+    Lk = Lprev + (size_t)(k - (j - 1)) * 1024;
+    T = B.band + ((size_t)k * nb1 + (i - k)) * 1024; ldt = kNB;
+  } else {                                        // border row blocks (2 per task) x block columns (2 per task)
+    u -= ntri;
+    const int rs = u / ms, cs = u - rs * ms;
+    const int rb = 2 * rs + (wr >> 1), c = 2 * cs + wc;
+    if (rb >= Q.nrb || c >= m) return;
+    if (rb == Q.nrb - 1 && half * 16 >= kBorder) return;        // the last row block has 16 rows
+    const int k = k_lo + c;
+    Lk = Lprev + (size_t)(k - (j - 1)) * 1024;
+    A = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)(j - 1 - Q.c0) * kNB; lda = Q.ld;
+    T = Q.fb + (size_t)rb * kNB * Q.ld + (size_t)(k - Q.c0) * kNB; ldt = Q.ld;
   }
-  const double* pb = B.band + ((size_t)k_lo * nb1 + (c - k_lo)) * 1024 + (size_t)(16 * wc + g) * kNB + 8 * tq;   // L(c, k)
-  const size_t b_step = (size_t)(nb1 - 1) * 1024;
-  double acc[4][2][2][2];
+  const int r0 = 16 * half + g;
+  double a0[8], a1[8], b0[8], b1[8], b2[8], b3[8];
+  load_frag8(A + (size_t)r0 * lda + 8 * tq, a0);
+  load_frag8(A + (size_t)(r0 + 8) * lda + 8 * tq, a1);
+  const double* pb = Lk + (size_t)g * kNB + 8 * tq;
+  load_frag8(pb, b0); load_frag8(pb + 8 * kNB, b1); load_frag8(pb + 16 * kNB, b2); load_frag8(pb + 24 * kNB, b3);
+  double2* d0 = reinterpret_cast<double2*>(T + (size_t)r0 * ldt + 2 * tq);
+  double2* d1 = reinterpret_cast<double2*>(T + (size_t)(r0 + 8) * ldt + 2 * tq);
+  double2 v[2][4];
 #pragma unroll
-  for (int q = 0; q < 4; ++q)
-#pragma unroll
-    for (int i = 0; i < 2; ++i)
-#pragma unroll
-      for (int h = 0; h < 2; ++h) acc[q][i][h][0] = acc[q][i][h][1] = 0.0;
-  GFrag f0, f1;
-  int k = k_lo;
-  gather_load(f0, pa, a8, pb);
-  while (true) {
-    if (k < k_hi) { pa += a_step; pb += b_step; gather_load(f1, pa, a8, pb); }
-    gather_mma(acc, f0);
-    if (++k > k_hi) break;
-    if (k < k_hi) { pa += a_step; pb += b_step; gather_load(f0, pa, a8, pb); }
-    gather_mma(acc, f1);
-    if (++k > k_hi) break;
-  }
+  for (int h = 0; h < 4; ++h) { v[0][h] = d0[4 * h]; v[1][h] = d1[4 * h]; }
+  double acc[2][4][2];
 #pragma unroll
   for (int i = 0; i < 2; ++i)
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      double2* d = reinterpret_cast<double2*>(T + (size_t)(16 * wr + 8 * i + g) * ldt + 16 * wc + 8 * h + 2 * tq);
-      double2 v = *d;
-      v.x -= (acc[0][i][h][0] + acc[1][i][h][0]) + (acc[2][i][h][0] + acc[3][i][h][0]);
-      v.y -= (acc[0][i][h][1] + acc[1][i][h][1]) + (acc[2][i][h][1] + acc[3][i][h][1]);
-      *d = v;
+    for (int h = 0; h < 4; ++h) acc[i][h][0] = acc[i][h][1] = 0.0;
+#pragma unroll
+  for (int ks = 0; ks < 8; ++ks) {
+    dmma884(acc[0][0][0], acc[0][0][1], a0[ks], b0[ks]); dmma884(acc[1][0][0], acc[1][0][1], a1[ks], b0[ks]);
+    dmma884(acc[0][1][0], acc[0][1][1], a0[ks], b1[ks]); dmma884(acc[1][1][0], acc[1][1][1], a1[ks], b1[ks]);
+    dmma884(acc[0][2][0], acc[0][2][1], a0[ks], b2[ks]); dmma884(acc[1][2][0], acc[1][2][1], a1[ks], b2[ks]);
+    dmma884(acc[0][3][0], acc[0][3][1], a0[ks], b3[ks]); dmma884(acc[1][3][0], acc[1][3][1], a1[ks], b3[ks]);
+  }
+#pragma unroll
+  for (int h = 0; h < 4; ++h) {
+    v[0][h].x -= acc[0][h][0]; v[0][h].y -= acc[0][h][1]; v[1][h].x -= acc[1][h][0]; v[1][h].y -= acc[1][h][1];
+    d0[4 * h] = v[0][h]; d1[4 * h] = v[1][h];
+  }
+  BAND_TRACE_END(1, t);
+}
+
+// ---- K loop shared by the border kernels ---------------------------------------------------------------------------------
+// One warp accumulates  acc += sum_k A_k Bm_k^T  for a whole 32 x 32 tile (16 accumulator tiles of 8 x 8 = 16 independent DMMA chains) over
+// the blocks k = 0 .. nk-1 it is given (A_k = pa + k a_step with `a_rs` doubles between rows, Bm_k = pb + k b_step, row-major 32 x 32 with
+// leading dimension 32).  Operand fragments come straight from L2 — profiles/fp64_peaks.json: 31-33 TFLOP/s of the 37.1 TFLOP/s DMMA peak for
+// this loop shape against 25 TFLOP/s when the blocks are staged through shared memory by cp.async.bulk — and a block is consumed in two
+// halves (fragment columns 8 t + 4 half .. + 4: one 256-bit load per 8-row group and operand); the next half is in flight while the current
+// one feeds 64 DMMAs (1024 issue cycles per warp: more than the L2 latency, so one stage of prefetch hides it).
+// (measured: DMMA.8x8x4 issues every ~16 cycles per SM sub-partition with a dependent latency of ~27 cycles, so 2 chains per warp suffice.)
+// COHERENT: the A operand was written by this CTA earlier in the same launch (plain loads instead of the read-only path).
+// rows_a: A rows >= rows_a are not read (taken as zero) — the 16-row border of an unpartitioned system.
+struct KFrag { double a[4][4], b[4][4]; };
+template <bool COHERENT>
+__device__ __forceinline__ void kfrag_load(KFrag& f, const double* pa, size_t a_rs, const double* __restrict__ pb, int half, int rows_a) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if (8 * i < rows_a) {
+      if (COHERENT) asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(f.a[i][0]), "=d"(f.a[i][1]), "=d"(f.a[i][2]), "=d"(f.a[i][3]) : "l"(pa + (size_t)(8 * i) * a_rs + 4 * half) : "memory");
+      else asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(f.a[i][0]), "=d"(f.a[i][1]), "=d"(f.a[i][2]), "=d"(f.a[i][3]) : "l"(pa + (size_t)(8 * i) * a_rs + 4 * half));
+    } else {
+      f.a[i][0] = f.a[i][1] = f.a[i][2] = f.a[i][3] = 0.0;
     }
-  if (!FINAL) BAND_TRACE_END(1, t);
+    asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(f.b[i][0]), "=d"(f.b[i][1]), "=d"(f.b[i][2]), "=d"(f.b[i][3]) : "l"(pb + (size_t)(8 * i) * kNB + 4 * half));
+  }
+}
+__device__ __forceinline__ void kfrag_mma(double (&acc)[4][4][2], const KFrag& f) {
+#pragma unroll
+  for (int ks = 0; ks < 4; ++ks)
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int h = 0; h < 4; ++h) dmma884(acc[i][h][0], acc[i][h][1], f.a[i][ks], f.b[h][ks]);
+}
+// pa / pb point at this lane's fragment origin (row g, column 8 tq) of the first block
+template <bool COHERENT>
+__device__ __forceinline__ void kloop(double (&acc)[4][4][2], const double* pa, size_t a_rs, size_t a_step, const double* __restrict__ pb, size_t b_step,
+                                      int nk, int rows_a) {
+  if (nk <= 0) return;
+  KFrag f0, f1;
+  kfrag_load<COHERENT>(f0, pa, a_rs, pb, 0, rows_a);
+  for (int k = 0; k < nk; ++k) {
+    kfrag_load<COHERENT>(f1, pa, a_rs, pb, 1, rows_a);
+    kfrag_mma(acc, f0);
+    pa += a_step; pb += b_step;
+    if (k + 1 < nk) kfrag_load<COHERENT>(f0, pa, a_rs, pb, 0, rows_a);
+    kfrag_mma(acc, f1);
+  }
+}
+constexpr int kLdS = 36;   // shared-memory leading dimension: (4 g + t) mod 16 distinct -> conflict-free 8-byte fragment reads (col = 4 ks + t)
+__device__ __forceinline__ void acc_to_smem(double* sP, const double (&acc)[4][4][2], int g, int tq) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int h = 0; h < 4; ++h) {
+      double* d = &sP[(8 * i + g) * kLdS + 8 * h + 2 * tq];
+      d[0] = acc[i][h][0]; d[1] = acc[i][h][1];
+    }
 }
 
 // ---- deferred border rows:  W = FB L^-T  as a pipeline that trails the band factorisation ------------------------------------------------
@@ -421,11 +453,9 @@ __global__ void __launch_bounds__(kGatherThreads) k_band_gather(BandLayout B, co
 // (where each border row block cost one more CTA with its own redundant 32 x 32 factorisation on the critical path) and computed by this
 // kernel, launched once per chunk of block steps on its own stream:  CTA = (partition, border row block) walks the chunk's block columns
 //     W(r, j) = ( FB(r, j) - sum_{k = max(c0, j - nbw)}^{j-1} W(r, k) L(j, k)^T ) L_jj^-T
-// in order; every dependency is either final (L, L_jj^-1 from the panel kernel) or the CTA's own earlier output.  4 warps split the k range
-// (warp w: k = k_lo + w, k_lo + w + 4, ...; a 32 x 32 accumulator = 16 independent DMMA chains per warp), the partial sums meet in shared
-// memory, then the product with L_jj^-1 (staged in shared memory while the k loop runs) gives the block.
+// in order; every dependency is either final (L, L_jj^-1 from the panel kernel) or the CTA's own earlier output.  4 warps split the k range,
+// the partial sums meet in shared memory, then the product with L_jj^-1 (staged in shared memory while the k loop runs) gives the block.
 constexpr int kBorderThreads = 128;
-constexpr int kLdS = 36;   // shared-memory leading dimension: (4 g + t) mod 16 distinct -> conflict-free 8-byte fragment reads (col = 4 ks + t)
 __global__ void __launch_bounds__(kBorderThreads) k_band_border(BandLayout B, const __grid_constant__ BandParts PS, int t0, int t1,
                                                                 const double* __restrict__ dinv) {
   __shared__ double sP[4][kNB * kLdS];     // per-warp partial sums; sP[0] becomes the block T = FB - sum
@@ -444,37 +474,15 @@ __global__ void __launch_bounds__(kBorderThreads) k_band_border(BandLayout B, co
     const int k_lo = Q.c0 > j - B.nbw ? Q.c0 : j - B.nbw;
     // L_jj^-1 -> shared memory (overlaps with the k loop; consumed after the barriers below)
     for (int e = threadIdx.x; e < kNB * kNB; e += kBorderThreads) sL[(e >> 5) * kLdS + (e & 31)] = dinv[(size_t)j * 1024 + e];
-    double acc[4][4][2];   // [row group][column group]: 16 independent DMMA chains
+    double acc[4][4][2];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
       for (int h = 0; h < 4; ++h) acc[i][h][0] = acc[i][h][1] = 0.0;
-    for (int k = k_lo + warp; k < j; k += 4) {
-      const double* pa = F + (size_t)g * Q.ld + (size_t)(k - Q.c0) * kNB + 8 * tq;                          // W(r, k): written by this CTA
-      const double* pb = B.band + ((size_t)k * nb1 + (j - k)) * 1024 + (size_t)g * kNB + 8 * tq;            // L(j, k)
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {   // fragment columns 8 tq + 4 half .. + 4: one 256-bit load per row group and operand
-        double a[4][4], b[4][4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a[i][0]), "=d"(a[i][1]), "=d"(a[i][2]), "=d"(a[i][3]) : "l"(pa + (size_t)(8 * i) * Q.ld + 4 * half) : "memory");
-          asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(b[i][0]), "=d"(b[i][1]), "=d"(b[i][2]), "=d"(b[i][3]) : "l"(pb + (size_t)(8 * i) * kNB + 4 * half));
-        }
-#pragma unroll
-        for (int ks = 0; ks < 4; ++ks)
-#pragma unroll
-          for (int i = 0; i < 4; ++i)
-#pragma unroll
-            for (int h = 0; h < 4; ++h) dmma884(acc[i][h][0], acc[i][h][1], a[i][ks], b[h][ks]);
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-      for (int h = 0; h < 4; ++h) {
-        double* d = &sP[warp][(8 * i + g) * kLdS + 8 * h + 2 * tq];
-        d[0] = acc[i][h][0]; d[1] = acc[i][h][1];
-      }
+    const int nk_all = j - k_lo, nk = warp < nk_all ? (nk_all - warp + 3) / 4 : 0;
+    kloop<true>(acc, F + (size_t)g * Q.ld + (size_t)(k_lo + warp - Q.c0) * kNB + 8 * tq, Q.ld, 4 * kNB,
+                B.band + ((size_t)(k_lo + warp) * nb1 + (j - k_lo - warp)) * 1024 + (size_t)g * kNB + 8 * tq, (size_t)4 * (nb1 - 1) * 1024, nk, kNB);
+    acc_to_smem(sP[warp], acc, g, tq);
     __syncthreads();
     double* Fj = F + (size_t)t * kNB;
     for (int e = threadIdx.x; e < kNB * kNB; e += kBorderThreads) {
@@ -498,6 +506,40 @@ __global__ void __launch_bounds__(kBorderThreads) k_band_border(BandLayout B, co
     __syncthreads();   // the block is visible to the whole CTA before the next column reads it back; sP / sL may be overwritten
   }
   BAND_TRACE_END(2, t0);
+}
+
+// Border rows over the right separator of a partition: after the border pipeline has finished the interior,
+//     FB(r, c) -= sum_{k = max(c0, c - nbw)}^{c0 + nI - 1} W(r, k) L(c, k)^T      for every separator column c
+// (the band blocks of the separator columns are updated by k_band_update step by step; the border rows are not part of the steps).
+// CTA = (partition, separator column, border row block); 4 warps split the k range.
+__global__ void __launch_bounds__(kBorderThreads) k_band_border_sep(BandLayout B, const __grid_constant__ BandParts PS) {
+  __shared__ double sP[4][kNB * kLdS];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tq = lane & 3;
+  const int nb1 = B.nbw + 1;
+  int u = blockIdx.x, pi = 0;
+  for (; pi < PS.P; ++pi) { const int nu = (PS.part[pi].ncols - PS.part[pi].nI) * PS.part[pi].nrb; if (u < nu) break; u -= nu; }
+  if (pi >= PS.P) return;
+  const BandPart& Q = PS.part[pi];
+  const int tc = u / Q.nrb, rb = u - tc * Q.nrb;
+  const int c = Q.c0 + Q.nI + tc, k_hi = Q.c0 + Q.nI - 1;
+  const int k_lo = Q.c0 > c - B.nbw ? Q.c0 : c - B.nbw;
+  if (k_lo > k_hi) return;
+  double* F = Q.fb + (size_t)rb * kNB * Q.ld;
+  double acc[4][4][2];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int h = 0; h < 4; ++h) acc[i][h][0] = acc[i][h][1] = 0.0;
+  const int nk_all = k_hi - k_lo + 1, nk = warp < nk_all ? (nk_all - warp + 3) / 4 : 0;
+  kloop<false>(acc, F + (size_t)g * Q.ld + (size_t)(k_lo + warp - Q.c0) * kNB + 8 * tq, Q.ld, 4 * kNB,
+               B.band + ((size_t)(k_lo + warp) * nb1 + (c - k_lo - warp)) * 1024 + (size_t)g * kNB + 8 * tq, (size_t)4 * (nb1 - 1) * 1024, nk, kNB);
+  acc_to_smem(sP[warp], acc, g, tq);
+  __syncthreads();
+  double* T = F + (size_t)(c - Q.c0) * kNB;
+  for (int e = threadIdx.x; e < kNB * kNB; e += kBorderThreads) {
+    const int r = e >> 5, cc = e & 31, o = r * kLdS + cc;
+    T[(size_t)r * Q.ld + cc] -= (sP[0][o] + sP[1][o]) + (sP[2][o] + sP[3][o]);
+  }
 }
 
 // ---- partition border initialisation -------------------------------------------------------------------------------------------
@@ -905,7 +947,7 @@ struct BandPlan {
 // sequential block steps of the nested solve with P partitions at level 0
 static int nested_depth(int nbc, int nbw, int P) {
   if (P <= 1) return nbc;
-  int d = (nbc - (P - 1) * nbw + P - 1) / P + 1, m = P - 1;   // largest interior + the separator gather
+  int d = (nbc - (P - 1) * nbw + P - 1) / P + 1, m = P - 1;   // largest interior + its flush step
   while (m > 2) { d += nbw + 1; m = (m + 1) / 2 - 1; }          // one separator block per interface level
   return d + m * nbw;                                           // last level: one partition of m blocks
 }
@@ -992,7 +1034,7 @@ static int level_build(ctba_problem* p, BandPlan& pl, int li, const PartLayout& 
     g_off_loc.push_back(g_off[q]);
     maxI = std::max(maxI, nI);
   }
-  L.max_steps = maxI;
+  L.max_steps = maxI + 1;   // + the flush step that applies the last interior column's update to the right separator
   CTBA_CUDA(p, L.fb.resize(fb_total)); CTBA_CUDA(p, L.gram.resize(gram_total));
   L.GP = GramPlan{}; L.GP.P = q_hi - q_lo;
   L.PSloc = BandParts{}; L.PSloc.P = q_hi - q_lo; L.PSloc.sepw = sepw; L.PSloc.defer = 1;
@@ -1057,13 +1099,10 @@ static int plan_build(ctba_problem* p, BandPlan& pl, const BandLayout& B) {
   return CTBA_OK;
 }
 
-// Step launches on three streams (inside a capture: three graph branches): the panel kernel of step t on `st`; next to it on the side
-// stream the gather kernel that prepares the NEXT step's block column from the columns that were final before step t; and, on levels with
-// partitions, the border pipeline on a third stream, one launch per chunk of steps.
-//   panel(t)  waits for panel(t-1) (stream order) and gather(t-1)   (its column carries every term but the one it applies itself)
-//   gather(t) waits for panel(t-1)                                  (reads columns <= c0 + t - 1, writes column c0 + t + 1)
-//   border(chunk) waits for the chunk's last panel step and the previous chunk (stream order)
-// After the last panel step and the last border chunk one gather launch fills the right separators of every partition from their interiors.
+// Step launches on three streams (inside a capture: three graph branches): the panel kernel on `st`, the update kernel on a side stream
+// (each kernel of step t waits for both kernels of step t-1) and, on levels with partitions, the border pipeline on a third stream: one
+// launch per chunk of steps, which waits for the chunk's last panel step and for the previous chunk.  After the last step and the last
+// chunk one launch carries the border rows over the right separators.
 constexpr int kBorderChunk = 8;
 static int enqueue_steps(ctba_problem* p, cudaStream_t st, const BandLayout& B, const BandParts& PS, int nsteps, double* dinv, int64_t* nl) {
   SolverData* sd = p->solver;
@@ -1074,18 +1113,24 @@ static int enqueue_steps(ctba_problem* p, cudaStream_t st, const BandLayout& B, 
   CTBA_CUDA(p, cudaStreamWaitEvent(s3, evA, 0));
   CTBA_CUDA(p, cudaEventRecord(evB, s2));              // the joins below are valid even when a side stream gets no work
   CTBA_CUDA(p, cudaEventRecord(evC, s3));
-  int nborder = 0;
-  if (PS.defer) for (int q = 0; q < PS.P; ++q) nborder += PS.part[q].nrb;
+  int nborder = 0, nsep = 0, max_panel = 0;
+  if (PS.defer) for (int q = 0; q < PS.P; ++q) { nborder += PS.part[q].nrb; nsep += (PS.part[q].ncols - PS.part[q].nI) * PS.part[q].nrb; max_panel = std::max(max_panel, PS.part[q].nI); }
   int chunk_begin = 0;
   for (int t = 0; t < nsteps; ++t) {
     int gp = 0, gu = 0;
-    for (int q = 0; q < PS.P; ++q) { gp += part_panel_tasks(B, PS.part[q], t, PS.defer); gu += part_gather_tasks(B, PS.part[q], t, 0, PS.defer); }
-    if (gp || gu) {
-      if (t > 0) { CTBA_CUDA(p, cudaStreamWaitEvent(s2, evA, 0)); CTBA_CUDA(p, cudaStreamWaitEvent(st, evB, 0)); }
-      if (gp) { k_band_panel<<<gp, kStepThreads, 0, st>>>(B, PS, t, dinv, sd->flag.p); ++*nl; CTBA_CUDA(p, cudaEventRecord(evA, st)); }
-      if (gu) { k_band_gather<0><<<gu, kGatherThreads, 0, s2>>>(B, PS, t); ++*nl; CTBA_CUDA(p, cudaEventRecord(evB, s2)); }
+    for (int q = 0; q < PS.P; ++q) {
+      int np, m, kl;
+      part_tasks(B, PS.part[q], t, PS.defer, &np, &m, &kl);
+      gp += np; gu += part_update_tasks(m, PS.defer ? 0 : PS.part[q].nrb);
     }
-    if (nborder && (t + 1 - chunk_begin == kBorderChunk || t + 1 == nsteps)) {
+    if (gp || gu) {
+      if (t > 0) { CTBA_CUDA(p, cudaStreamWaitEvent(st, evB, 0)); CTBA_CUDA(p, cudaStreamWaitEvent(s2, evA, 0)); }
+      if (gp) { k_band_panel<<<gp, kStepThreads, 0, st>>>(B, PS, t, dinv, sd->flag.p); ++*nl; }
+      if (gu) { k_band_update<<<gu, kStepThreads, 0, s2>>>(B, PS, t); ++*nl; }
+      CTBA_CUDA(p, cudaEventRecord(evA, st));
+      CTBA_CUDA(p, cudaEventRecord(evB, s2));
+    }
+    if (nborder && t < max_panel && (t + 1 - chunk_begin == kBorderChunk || t + 1 == max_panel)) {
       CTBA_CUDA(p, cudaStreamWaitEvent(s3, evA, 0));   // evA: the most recent panel step = the chunk's last
       k_band_border<<<nborder, kBorderThreads, 0, s3>>>(B, PS, chunk_begin, t + 1, dinv); ++*nl;
       CTBA_CUDA(p, cudaEventRecord(evC, s3));
@@ -1094,9 +1139,7 @@ static int enqueue_steps(ctba_problem* p, cudaStream_t st, const BandLayout& B, 
   }
   CTBA_CUDA(p, cudaStreamWaitEvent(st, evB, 0));       // join
   CTBA_CUDA(p, cudaStreamWaitEvent(st, evC, 0));
-  int gf = 0;
-  for (int q = 0; q < PS.P; ++q) gf += part_gather_tasks(B, PS.part[q], 0, 1, PS.defer);
-  if (gf) { k_band_gather<1><<<gf, kGatherThreads, 0, st>>>(B, PS, 0); ++*nl; }
+  if (nsep) { k_band_border_sep<<<nsep, kBorderThreads, 0, st>>>(B, PS); ++*nl; }
   CTBA_CUDA(p, cudaGetLastError());
   return CTBA_OK;
 }
