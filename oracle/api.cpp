@@ -113,6 +113,7 @@ int orc_get_alignment(void* h, double* T, double* corr) {
 int orc_add_bias_cost(void* h, double freq_hz, double dt_s, double acc_rw, double gyr_rw) { return ((SplineProblem*)h)->addBiasCost(freq_hz, dt_s, acc_rw, gyr_rw); }
 int orc_add_gravity_norm(void* h) { auto* p = (SplineProblem*)h; p->gravity_norm = true; p->built = false; return 0; }
 int orc_relinearize(void* h) { ((SplineProblem*)h)->relinearize(); return 0; }
+int orc_relinearize_mask(void* h, int mask) { ((SplineProblem*)h)->relinearize(mask); return 0; }
 
 // counts: [frames, obs, accel, gyro, gp, bias, gravity, tangent columns]
 int orc_counts(void* h, int64_t* c) {

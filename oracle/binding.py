@@ -148,6 +148,10 @@ class OracleSpline:
     def relinearize(self):
         self.L.orc_relinearize(self.h)
 
+    def relinearizeMask(self, mask):
+        """bit 0: relinearizeSplineImuTimeOffset only, bit 1: relinearizeSplineGlobSensTimeOffset only"""
+        self.L.orc_relinearize_mask(self.h, int(mask))
+
     def counts(self):
         c = np.zeros(8, dtype=np.int64)
         self.L.orc_counts(self.h, c.ctypes.data_as(C.c_void_p))

@@ -454,9 +454,9 @@ struct SplineProblem {
   }
 
   // :1807-1811, :1853-1857 — bookkeeping only; the residual blocks keep their captured st_s, k
-  void relinearize() {
-    t_offset_cam_imu_s += t_offset_cam_imu_corr_s; t_offset_cam_imu_corr_s = 0.0;
-    t_s_gp_s += t_s_gp_corr_s; t_s_gp_corr_s = 0.0;
+  void relinearize(int mask = 3) {   // bit 0: relinearizeSplineImuTimeOffset, bit 1: relinearizeSplineGlobSensTimeOffset
+    if (mask & 1) { t_offset_cam_imu_s += t_offset_cam_imu_corr_s; t_offset_cam_imu_corr_s = 0.0; }
+    if (mask & 2) { t_s_gp_s += t_s_gp_corr_s; t_s_gp_corr_s = 0.0; }
   }
 };
 

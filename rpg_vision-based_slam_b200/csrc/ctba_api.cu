@@ -344,36 +344,59 @@ static int64_t end_t_ns_bias(const ctba_problem* p) {  // getEndTnsBiasSpline :1
   return (int64_t)((double)t_end_ns - 1e6);   // the reference subtracts the double literal 1e6: the result is rounded through double (:1874)
 }
 
+// window mapping of one IMU sample (bspline_so3r3.h:525-563); false = skipped
+static bool map_imu_sample(const ctba_problem* p, int64_t t_ns, int32_t* s_out, int32_t* sb_out, double* st_s_out, double* k_out, double* ub_out) {
+  const int N = p->N;
+  int64_t t_offset_imu_cam_ns = static_cast<int64_t>(-p->t_offset_cam_imu_s * 1e9);  // :525-526
+  int64_t st_ns = (t_ns + t_offset_imu_cam_ns - p->start_t_ns);
+  double st_s = st_ns * 1e-9;
+  if (st_ns < 0) return false;
+  int64_t s = st_ns / p->dt_ns;
+  int k_int = (int)(st_ns / p->dt_ns);
+  if (size_t(s + N) > p->numKnots()) return false;
+  int64_t st_bias_ns = (t_ns - p->start_t_ns);
+  int64_t s_bias = st_bias_ns / p->dt_ns_bias;
+  double u_bias = double(st_bias_ns % p->dt_ns_bias) / double(p->dt_ns_bias);
+  if (s_bias < 0) { *sb_out = -1; return true; }
+  if (size_t(s_bias + N) > p->numBiasKnots()) {  // :557-563
+    st_bias_ns = end_t_ns_bias(p) - p->start_t_ns;
+    s_bias = st_bias_ns / p->dt_ns_bias;
+    u_bias = double(st_bias_ns % p->dt_ns_bias) / double(p->dt_ns_bias);
+  }
+  *s_out = (int32_t)s; *sb_out = (int32_t)s_bias; *st_s_out = st_s; *k_out = (double)k_int; *ub_out = u_bias;
+  return true;
+}
+// window mapping of one global-position sample (:882-895)
+static bool map_gp_sample(const ctba_problem* p, int64_t t_ns, int32_t* s_out, double* st_s_out, double* k_out) {
+  int64_t t_s_gp_init_ns = static_cast<int64_t>(p->t_s_gp_s * 1e9);  // :882
+  int64_t st_ns = (t_ns - p->start_t_ns - t_s_gp_init_ns);
+  double st_s = st_ns * 1e-9;
+  if (st_ns < 0) return false;
+  int64_t s = st_ns / p->dt_ns;
+  int k_int = (int)(st_ns / p->dt_ns);
+  if (size_t(s + p->N) > p->numKnots()) return false;
+  *s_out = (int32_t)s; *st_s_out = st_s; *k_out = (double)k_int;
+  return true;
+}
+
 int ctba_add_imu(ctba_problem* p, int n, const int64_t* t_ns, const double* acc, const double* gyr, double acc_nd, double gyr_nd) {
   CHECK_P(p);
   if (n < 0 || !t_ns || !acc || !gyr || !(acc_nd > 0) || !(gyr_nd > 0)) return fail(p, CTBA_E_ARG, "add_imu: bad arguments");
   if ((int)p->numBiasKnots() < p->N) return fail(p, CTBA_E_STATE, "add_imu: initialize_biases first (needs >= N bias knots)");
-  const int N = p->N;
   int added = 0;
   for (int i = 0; i < n; ++i) {
-    int64_t t_offset_imu_cam_ns = static_cast<int64_t>(-p->t_offset_cam_imu_s * 1e9);  // :525-526
-    int64_t st_ns = (t_ns[i] + t_offset_imu_cam_ns - p->start_t_ns);
-    double st_s = st_ns * 1e-9;
-    if (st_ns < 0) continue;
-    int64_t s = st_ns / p->dt_ns;
-    int k_int = (int)(st_ns / p->dt_ns);
-    if (size_t(s + N) > p->numKnots()) continue;
-    int64_t st_bias_ns = (t_ns[i] - p->start_t_ns);
-    int64_t s_bias = st_bias_ns / p->dt_ns_bias;
-    double u_bias = double(st_bias_ns % p->dt_ns_bias) / double(p->dt_ns_bias);
-    if (s_bias < 0) return fail(p, CTBA_E_ARG, "add_imu: s_bias < 0 (bspline_so3r3.h:548)");
-    if (size_t(s_bias + N) > p->numBiasKnots()) {  // :557-563
-      st_bias_ns = end_t_ns_bias(p) - p->start_t_ns;
-      s_bias = st_bias_ns / p->dt_ns_bias;
-      u_bias = double(st_bias_ns % p->dt_ns_bias) / double(p->dt_ns_bias);
-      if (s_bias < 0) return fail(p, CTBA_E_ARG, "add_imu: s_bias < 0 after clamp");
-    }
-    p->i_s.push_back((int32_t)s); p->i_sb.push_back((int32_t)s_bias);
-    p->i_st_s.push_back(st_s); p->i_k.push_back((double)k_int); p->i_ub.push_back(u_bias);
+    int32_t s = 0, sb = 0; double st_s = 0, k = 0, ub = 0;
+    p->raw_imu_t.push_back(t_ns[i]);
+    for (int c = 0; c < 3; ++c) { p->raw_imu_acc.push_back(acc[3 * (size_t)i + c]); p->raw_imu_gyr.push_back(gyr[3 * (size_t)i + c]); }
+    if (!map_imu_sample(p, t_ns[i], &s, &sb, &st_s, &k, &ub)) continue;
+    if (sb < 0) return fail(p, CTBA_E_ARG, "add_imu: s_bias < 0 (bspline_so3r3.h:548)");
+    p->i_s.push_back(s); p->i_sb.push_back(sb);
+    p->i_st_s.push_back(st_s); p->i_k.push_back(k); p->i_ub.push_back(ub);
     p->i_inv_a.push_back(1.0 / acc_nd); p->i_inv_g.push_back(1.0 / gyr_nd);
     for (int c = 0; c < 3; ++c) { p->i_acc.push_back(acc[3 * (size_t)i + c]); p->i_gyr.push_back(gyr[3 * (size_t)i + c]); }
     ++added;
   }
+  p->raw_imu_inv_a = 1.0 / acc_nd; p->raw_imu_inv_g = 1.0 / gyr_nd;
   p->meas_dirty = true; p->struct_dirty = true;
   return added;
 }
@@ -381,23 +404,54 @@ int ctba_add_imu(ctba_problem* p, int n, const int64_t* t_ns, const double* acc,
 int ctba_add_gp(ctba_problem* p, int n, const int64_t* t_ns, const double* pos, double noise) {
   CHECK_P(p);
   if (n < 0 || !t_ns || !pos || !(noise > 0)) return fail(p, CTBA_E_ARG, "add_gp: bad arguments");
-  const int N = p->N;
   int added = 0;
   for (int i = 0; i < n; ++i) {
-    int64_t t_s_gp_init_ns = static_cast<int64_t>(p->t_s_gp_s * 1e9);  // :882
-    int64_t st_ns = (t_ns[i] - p->start_t_ns - t_s_gp_init_ns);
-    double st_s = st_ns * 1e-9;
-    if (st_ns < 0) continue;
-    int64_t s = st_ns / p->dt_ns;
-    int k_int = (int)(st_ns / p->dt_ns);
-    if (size_t(s + N) > p->numKnots()) continue;
-    p->g_s.push_back((int32_t)s); p->g_st_s.push_back(st_s); p->g_k.push_back((double)k_int); p->g_inv_std.push_back(1.0 / noise);
+    int32_t s = 0; double st_s = 0, k = 0;
+    p->raw_gp_t.push_back(t_ns[i]);
+    for (int c = 0; c < 3; ++c) p->raw_gp_pos.push_back(pos[3 * (size_t)i + c]);
+    if (!map_gp_sample(p, t_ns[i], &s, &st_s, &k)) continue;
+    p->g_s.push_back(s); p->g_st_s.push_back(st_s); p->g_k.push_back(k); p->g_inv_std.push_back(1.0 / noise);
     for (int c = 0; c < 3; ++c) p->g_meas.push_back(pos[3 * (size_t)i + c]);
     ++added;
   }
+  p->raw_gp_inv = 1.0 / noise;
   p->meas_dirty = true; p->struct_dirty = true;
   return added;
 }
+
+}  // extern "C"
+namespace ctba {
+int remap_measurements_begin(ctba_problem* p, MeasBackup* b) {
+  b->i_s.swap(p->i_s); b->i_sb.swap(p->i_sb); b->g_s.swap(p->g_s);
+  b->i_st_s.swap(p->i_st_s); b->i_k.swap(p->i_k); b->i_ub.swap(p->i_ub); b->i_inv_a.swap(p->i_inv_a); b->i_inv_g.swap(p->i_inv_g);
+  b->i_acc.swap(p->i_acc); b->i_gyr.swap(p->i_gyr); b->g_st_s.swap(p->g_st_s); b->g_k.swap(p->g_k); b->g_inv_std.swap(p->g_inv_std); b->g_meas.swap(p->g_meas);
+  b->active = true;
+  for (size_t i = 0; i < p->raw_imu_t.size(); ++i) {
+    int32_t s = 0, sb = 0; double st_s = 0, k = 0, ub = 0;
+    if (!map_imu_sample(p, p->raw_imu_t[i], &s, &sb, &st_s, &k, &ub) || sb < 0) continue;
+    p->i_s.push_back(s); p->i_sb.push_back(sb); p->i_st_s.push_back(st_s); p->i_k.push_back(k); p->i_ub.push_back(ub);
+    p->i_inv_a.push_back(p->raw_imu_inv_a); p->i_inv_g.push_back(p->raw_imu_inv_g);
+    for (int c = 0; c < 3; ++c) { p->i_acc.push_back(p->raw_imu_acc[3 * i + c]); p->i_gyr.push_back(p->raw_imu_gyr[3 * i + c]); }
+  }
+  for (size_t i = 0; i < p->raw_gp_t.size(); ++i) {
+    int32_t s = 0; double st_s = 0, k = 0;
+    if (!map_gp_sample(p, p->raw_gp_t[i], &s, &st_s, &k)) continue;
+    p->g_s.push_back(s); p->g_st_s.push_back(st_s); p->g_k.push_back(k); p->g_inv_std.push_back(p->raw_gp_inv);
+    for (int c = 0; c < 3; ++c) p->g_meas.push_back(p->raw_gp_pos[3 * i + c]);
+  }
+  p->meas_dirty = true;
+  return CTBA_OK;
+}
+void remap_measurements_end(ctba_problem* p, MeasBackup* b) {
+  if (!b->active) return;
+  b->i_s.swap(p->i_s); b->i_sb.swap(p->i_sb); b->g_s.swap(p->g_s);
+  b->i_st_s.swap(p->i_st_s); b->i_k.swap(p->i_k); b->i_ub.swap(p->i_ub); b->i_inv_a.swap(p->i_inv_a); b->i_inv_g.swap(p->i_inv_g);
+  b->i_acc.swap(p->i_acc); b->i_gyr.swap(p->i_gyr); b->g_st_s.swap(p->g_st_s); b->g_k.swap(p->g_k); b->g_inv_std.swap(p->g_inv_std); b->g_meas.swap(p->g_meas);
+  b->active = false;
+  p->meas_dirty = true;
+}
+}  // namespace ctba
+extern "C" {
 
 // addWorldColmapAlignmentMeasurement (bspline_so3r3.h:1121-1211): the window arithmetic and skip rules of addGlobalPosMeasurement
 int ctba_add_alignment_measurements(ctba_problem* p, int n, const int64_t* t_ns, const double* pos, double noise) {

@@ -114,6 +114,11 @@ struct ctba_problem {
   ctba::HVec<double> i_st_s, i_k, i_ub, i_inv_a, i_inv_g, i_acc, i_gyr;
   ctba::HVec<int32_t> g_s;
   ctba::HVec<double> g_st_s, g_k, g_inv_std, g_meas;
+  // every IMU / global-position measurement the caller passed, skipped ones included: evaluate*Errors re-derives the windows from the CURRENT
+  // (folded) time offsets and re-applies the skip rules, like the reference (bspline_so3r3.h:1239-1256, 1692-1707)
+  std::vector<int64_t> raw_imu_t, raw_gp_t;
+  std::vector<double> raw_imu_acc, raw_imu_gyr, raw_gp_pos;
+  double raw_imu_inv_a = 1.0, raw_imu_inv_g = 1.0, raw_gp_inv = 1.0;
   ctba::HVec<int32_t> b_s0, b_s1, b_which;
   ctba::HVec<double> b_u0, b_u1, b_inv_std;
   ctba::HVec<int32_t> q_s, q_which;             // pose priors (addPositionMeasurement / addOrientationMeasurement): window, 0 position | 1 orientation
@@ -172,6 +177,15 @@ int solver_num_unknowns(ctba_problem* p);
 int align_solve(ctba_problem* p, int max_iters, ctba_summary* out);
 int align_evaluate(ctba_problem* p, double* r_out, double* j_out, double* err_out);   // 3n residuals (x 1/noise), 3n x 11 Jacobians, n unit-weight norms
 void align_free(AlignData* a);
+// evaluate*Errors: swap in IMU / GP work items rebuilt from the raw measurements with the current time offsets (begin), swap the solver's
+// work items back (end).  The solver structure is not touched.
+struct MeasBackup {
+  HVec<int32_t> i_s, i_sb, g_s;
+  HVec<double> i_st_s, i_k, i_ub, i_inv_a, i_inv_g, i_acc, i_gyr, g_st_s, g_k, g_inv_std, g_meas;
+  bool active = false;
+};
+int remap_measurements_begin(ctba_problem* p, MeasBackup* b);
+void remap_measurements_end(ctba_problem* p, MeasBackup* b);
 int shard_build(ctba_problem* p);                    // ctba_shard.cu: filter the host work items to this rank's units
 int shard_reduce_cost(ctba_problem* p, EvalBuffers& ev, double* host_cost8);   // cost terms of all ranks, summed in rank order
 int shard_gather_state(ctba_problem* p);             // owners' knots / biases / landmarks -> every rank

@@ -183,6 +183,13 @@ int ctba_evaluate_errors(ctba_problem* p, int kind, double* errors) {
   if ((kind < CTBA_REPROJ || kind > CTBA_GP) && kind != CTBA_PRIOR) { p->err = "evaluate_errors: kind must be reprojection, accel, gyro, global position or pose prior"; return CTBA_E_ARG; }
   if (p->device < 0) { p->err = "planning-only handle (device -1): no compute entry points"; return CTBA_E_CUDA; }
   CTBA_CUDA(p, cudaSetDevice(p->device));
+  // accel / gyro / global position: the reference re-derives every sample's window from the current (possibly folded) time offsets and
+  // re-applies the skip rules (bspline_so3r3.h:1239-1256, 1346-1363, 1692-1707); the solver's own work items keep the windows they were
+  // added with, so the error pass runs on rebuilt work items and the solver's are swapped back afterwards.
+  MeasBackup backup;
+  const bool remap = (kind == CTBA_ACCEL || kind == CTBA_GYRO || kind == CTBA_GP) && !p->sharded;
+  struct Restore { ctba_problem* p; MeasBackup* b; ~Restore() { remap_measurements_end(p, b); } } restore{p, &backup};
+  if (remap) remap_measurements_begin(p, &backup);
   int rc = sync_to_device(p); if (rc) return rc;
   rc = launch_evaluate(p, p->ev, p->dstate.ptrs(), false); if (rc) return rc;
   cudaStream_t st = p->stream;

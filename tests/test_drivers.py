@@ -799,8 +799,7 @@ def _ct_oracle(oracle, sc, flags, order, T_q, T_p, kq_g, kp_g, lm_g, t_gp_init):
 
 
 def test_gi_driver_builds_and_fails_loudly_without_gpu(pkg, scene, tmp_path):
-    """optimize_gi_continuous_time (GP + IMU, no vision; the library shape is covered on the GPU by test_lm_gi_no_frames).  The tool's own
-    end-to-end GPU run was not made this round (GPU budget spent): only the build, the parsing and the loud failure are checked here."""
+    """optimize_gi_continuous_time without a GPU: the build, the parsing and the loud failure (the end-to-end run is the -m gpu twin below)."""
     import torch
     exe = _gxx(os.path.join(ROOT, "drivers", "optimize_gi_continuous_time.cpp"), str(tmp_path / "gi"), pkg)
     if torch.cuda.is_available():
@@ -821,6 +820,63 @@ def test_gi_driver_builds_and_fails_loudly_without_gpu(pkg, scene, tmp_path):
     assert out.returncode == 3 and "no CPU fallback" in out.stderr, out.stdout + out.stderr
     assert f"Loaded {len(sc['imu_t_ns'])} imu measurements" in out.stdout and f"Loaded {len(sc['gp_t_ns'])} global measurements" in out.stdout
     assert f"Loaded {len(sc['knot_q'])} initial spline knots" in out.stdout
+
+
+def _write_gi_dataset(d, sc):
+    flags = (False, True, False, True, True)
+    _write_ct_dataset(d, sc, 6, Rot.from_quat([0, 0, 0, 1.0]).as_quat(), np.zeros(3), flags, 0.0)
+    sub = os.path.join(d, "gpfit", "order_6", "dt_100_ms")
+    os.makedirs(sub)
+    _write_traj(os.path.join(sub, "spline_knots.txt"), [(sc["start_t_ns"] + i * sc["dt_ns"]) * 1e-9 for i in range(len(sc["knot_q"]))], sc["knot_q"], sc["knot_p"])
+    yml = os.path.join(d, "gi.yaml")
+    with open(yml, "w") as f:
+        f.write(f'dataset: EuRoC\nimu_fn: "{d}/imu.txt"\ngp_fn: "{d}/gp.txt"\nspline_dir: "{d}/gpfit"\nfull_batch_optimization_dir: "{d}/full_batch_gi"\n'
+                f"spline_control_nodes_dt_s: 0.1\nsampling_spline_rate: 50.0\nbias_spline_control_nodes_dt_s: {sc['dt_s_bias']}\ninit_acc_bias: [0.0, 0.0, 0.0]\n"
+                f"init_gyro_bias: [0.0, 0.0, 0.0]\nsigma_acc_c: 0.1\nsigma_acc_bias_c: 0.002\nsigma_omega_c: 0.05\nsigma_omega_bias_c: 4.0e-05\n"
+                f"bias_err_freq_hz: {sc['bias_err_freq_hz']}\nbias_err_dt_s: {sc['bias_err_dt_s']}\ngp_std: 0.1\noptimize_gravity: false\noptimize_pBP: true\n"
+                f"optimize_spline_globsens_time_offset: true\nn_max_outer_iters: 2\nn_max_inner_iters: 4\nn_threads: 4\n")
+    return yml, os.path.join(d, "full_batch_gi", "continuous_time", "order_6", "dt_100_ms")
+
+
+@pytest.mark.gpu
+def test_gi_driver_end_to_end_on_gpu(pkg, oracle, scene, tmp_path):
+    """optimize_gi_continuous_time (src/optimize_gi_continuous_time.cpp:303-431): GP + IMU + bias cost, no vision, scale left at the constructor's
+    0 (so p_bp has no effect — reproduced), only the spline-imu offset re-linearised between the solves.  The tool's solve costs and result
+    files against the oracle taken through the same steps."""
+    exe = _gxx(os.path.join(ROOT, "drivers", "optimize_gi_continuous_time.cpp"), str(tmp_path / "gi"), pkg)
+    sc, _ = _ct_scene(scene, 6)
+    yml, res = _write_gi_dataset(str(tmp_path), sc)
+    out = subprocess.run([exe, yml, "0", "6"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    o = oracle.OracleSpline(6, sc["dt_ns"], sc["start_t_ns"])
+    o.setKnots(sc["knot_q"], sc["knot_p"])
+    o.setGlobals(0.0, np.zeros(3), np.array([0.0, 0.0, 9.80665]), 0.0)
+    o.setFlags(False, True, False, True, True)
+    o.set3DPoints(np.zeros((0, 3)))
+    o.initializeBiases(sc["dt_s_bias"], np.zeros(3), np.zeros(3))
+    o.addGp(np.array([_t_of(t) for t in sc["gp_t_ns"]], dtype=np.int64), sc["gp_pos"], sc["gp_std"])
+    o.addImu(np.array([_t_of(t) for t in sc["imu_t_ns"]], dtype=np.int64), sc["imu_acc"], sc["imu_gyr"], sc["sigma_acc_c"], sc["sigma_omega_c"])
+    o.addImuBiasCost(sc["bias_err_freq_hz"], sc["bias_err_dt_s"], sc["sigma_acc_bias_c"], sc["sigma_omega_bias_c"])
+    s = o.optimize(1); o.relinearizeMask(1)
+    costs = [s["final_cost"]]
+    for _ in range(2):
+        s = o.optimize(4); o.relinearizeMask(1); costs.append(s["final_cost"])
+        if s["termination_type"] == 0: break
+    got = [float(l.split("->")[1].split(",")[0]) for l in out.stdout.splitlines() if l.startswith("solve ")]
+    assert len(got) == len(costs)
+    np.testing.assert_allclose(got, costs, rtol=1e-6)
+    g = o.getGlobals()
+    assert abs(float(open(os.path.join(res, "globalsensor_imu_time_offset.txt")).read()) - g[16]) < 1e-7
+    np.testing.assert_allclose(np.loadtxt(os.path.join(res, "gravity.txt")), g[13:16], atol=1e-6)
+    tr = np.loadtxt(os.path.join(res, "spline.txt"))
+    end_ns = int(float((len(sc["knot_q"]) - 6 + 1) * sc["dt_ns"] + sc["start_t_ns"]) - 1e6)
+    t_ns = np.arange(sc["start_t_ns"], end_ns, 20_000_000, dtype=np.int64)
+    assert tr.shape == (len(t_ns), 8)
+    ref = o.sampleAt(0, t_ns)
+    np.testing.assert_allclose(tr[:, 1:4], ref[:, :3], atol=1e-5)
+    assert (Rot.from_quat(tr[:, 4:]).inv() * Rot.from_quat(ref[:, 3:])).magnitude().max() < np.deg2rad(0.001)
+    for fn in ("acc_errors.txt", "gyro_errors.txt", "global_position_errors.txt", "predicted_imu.txt", "acc_bias_spline.txt", "gyro_bias_spline.txt", "p_bp.txt"):
+        assert os.path.exists(os.path.join(res, fn))
 
 
 def test_align_colmap_to_imu_tool(pkg, scene, tmp_path):

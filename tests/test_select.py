@@ -87,3 +87,31 @@ def test_evaluate_errors_match_unit_weight_residual_norms(pkg, scene, oracle):
         assert e.size == r.shape[0] > 0
         np.testing.assert_allclose(e, np.linalg.norm(r, axis=1) * std, rtol=1e-10, atol=1e-13)
     assert (gpu.evaluateErrors(pkg.CTBA_REPROJ) == 0).any()      # gated observations (|e|^2 > 100 px^2) report 0 like the reference
+
+
+@pytest.mark.gpu
+def test_evaluate_errors_follow_the_folded_time_offsets(pkg, scene, oracle):
+    """evaluate{Accel,Gyro,GlobalPos}Errors re-derive every sample's window from the CURRENT time offsets (bspline_so3r3.h:1239-1256,
+    1346-1363, 1692-1707): after relinearize*TimeOffset folded a non-zero correction, the errors must be those of a problem that is built
+    afresh with the folded offsets (skip rules re-applied) — not those of the work items the solver keeps."""
+    sc = scene.make_scene(order=6, duration_s=4.0, n_landmarks=60, track_len=8, imu_hz=100, gp_hz=20, dt_s_bias=0.25, seed=41,
+                          flags=(False, True, True, True, True))
+    g = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=0)
+    pkg.load_scene(g, sc)
+    corr = np.zeros(10); corr[4] = 1.0; corr[8] = 0.0437; corr[9] = -0.0312     # moves samples across knot boundaries and across the spline's ends
+    g.setCorrections(corr)
+    before = [g.evaluateErrors(k) for k in (1, 2, 3)]
+    g.relinearize()
+    after = [g.evaluateErrors(k) for k in (1, 2, 3)]
+    sc2 = dict(sc); sc2["t_offset_cam_imu"] = sc["t_offset_cam_imu"] + corr[8]; sc2["t_s_gp"] = sc["t_s_gp"] + corr[9]
+    o = oracle.OracleSpline(sc["order"], sc["dt_ns"], sc["start_t_ns"])
+    pkg.load_scene(o, sc2)
+    for k, sigma, e in ((1, sc["sigma_acc_c"], after[0]), (2, sc["sigma_omega_c"], after[1]), (3, sc["gp_std"], after[2])):
+        r, _, _ = o.evaluate(k, jac=False)
+        ref = np.linalg.norm(r.reshape(-1, 3), axis=1) * sigma
+        assert e.shape == ref.shape
+        np.testing.assert_allclose(e, ref, rtol=1e-9, atol=1e-12)
+    # before the fold the correction acts through the functor's u: same physical sampling times, up to the int64 truncation of the fold
+    assert abs(np.median(before[0]) - np.median(after[0])) < 1e-3 * np.median(after[0]) + 1e-9
+    # the solver's own work items are untouched: cost and counts as before the error pass
+    assert g.counts()["accel"] == len(before[0])
