@@ -8,6 +8,7 @@
 // Difference on the host side: points3D.txt rows are in points3D.bin
 // order (the reference writes its unordered_map's iteration order, save.h:200-208).
 //   usage: optimize_gv_continuous_time <config.yaml> [cuda device] [order 4|6]
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <sys/stat.h>
@@ -52,6 +53,13 @@ static int run(const Yaml& config, int device) {
   const std::string dataset_fn = config.as<std::string>("dataset");
   std::cout << "Dataset: " << dataset_fn << "\nresult dir: " << trace_dir << "\n\n";
 
+  // wall-clock phases of the tool ("[timing]" lines): decides whether ingest / selection are worth moving to the device
+  auto t_phase = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    const auto now = std::chrono::steady_clock::now();
+    std::printf("[timing] %s: %.3f s\n", what, std::chrono::duration<double>(now - t_phase).count());
+    t_phase = now;
+  };
   SimpleCamImuCalib calib;
   require(loadCalibForDataset(config, dataset_fn, cam_id, calib), "Camera-Imu calibration could not be loaded");   // UZH_FPV: Kalibr camchain + imu.yaml; EuRoC / Custom: EuRoC format
   std::vector<GlobalPosMeasurement> gp_meas;
@@ -67,6 +75,7 @@ static int run(const Yaml& config, int device) {
   const int grid_cell_size = config.as<int>("grid_cell_size");
   readImagesAndPoints3DBinary(colmap_dir + "images.bin", colmap_dir + "points3D.bin", cameras, sc);
   std::cout << "Loaded: " << sc.frames.size() << " images.\n\nLoaded: " << sc.lm_id.size() << " 3D points.\n\n";
+  lap("calibration + global positions + COLMAP binary ingest (cameras.bin, images.bin, points3D.bin)");
   for (int32_t l : sc.lm_index) require(l >= 0, "images.bin refers to a 3D point that points3D.bin does not hold");
 
   std::vector<Quat> knots_q_gb; std::vector<Vec3> knots_r_gb; std::vector<double> knots_ts;
@@ -110,6 +119,7 @@ static int run(const Yaml& config, int device) {
   spline_wb.addRotationLocalParametrization();
   spline_wb.set3DPoints(points_w);
 
+  lap("spline / alignment files, frame transforms, handle set-up");
   // computeValidReprojections (:392-406) on every kept 2-D point, then the valid ones enter the problem
   const int F = (int)sc.frames.size();
   std::vector<int64_t> frame_t_ns(F);
@@ -118,6 +128,7 @@ static int run(const Yaml& config, int device) {
   int rc = ctba_compute_valid_reprojections(spline_wb.handle(), F, frame_t_ns.data(), sc.pt_begin.data(), sc.uv.data(), sc.lm_index.data(), (int)sc.frames[0].w,
                                             (int)sc.frames[0].h, grid_cell_size, valid.data(), n_valid.data());
   if (rc < 0) throw Error(rc, ctba_last_error(spline_wb.handle()));
+  lap("computeValidReprojections (host, ctba_compute_valid_reprojections)");
 
   const double gp_meas_std = gpStdForDataset(config, dataset_fn);
   std::cout << "Sigma global measurements: " << gp_meas_std << " [m]\n\n";
@@ -141,6 +152,7 @@ static int run(const Yaml& config, int device) {
     std::cout << "Frames in the problem: " << rc << " of " << F << ", valid reprojections: " << lm.size() << "\n\n";
   }
 
+  lap("measurements into the problem (ctba_add_gp, ctba_add_frames: host work items)");
   std::cout << "+-+-+-+-+- Initial Errors +-+-+-+-+-\n\n";
   int n_err = 0;
   std::vector<double> init_gp_errors = spline_wb.evaluateErrors(CTBA_GP), init_reproj_errors = spline_wb.evaluateErrors(CTBA_REPROJ);
@@ -157,6 +169,7 @@ static int run(const Yaml& config, int device) {
 
   const int n_max_outer_iters = config.as<int>("n_max_outer_iters"), n_max_inner_iters = config.as<int>("n_max_inner_iters");
   spline_wb.loadOptimizationParams(n_max_outer_iters, n_max_inner_iters, config.as<int>("n_threads"));
+  lap("initial errors (first upload + evaluation) and initial result files");
   std::cout << "\n\nOptimizing ...\n\n";
   Summary summary = spline_wb.optimize(1);                                          // :485-486
   spline_wb.relinearizeSplineGlobSensTimeOffset();
@@ -169,6 +182,7 @@ static int run(const Yaml& config, int device) {
     if (i == n_max_outer_iters - 1) std::cout << "\n\n===== Solver did not converge =====\n\n";
   }
   spline_wb.relinearizeSplineGlobSensTimeOffset();
+  lap("all solves (structure analysis + LM iterations on the device)");
 
   std::cout << "+-+-+-+-+- Final Errors +-+-+-+-+-\n\n";
   std::vector<double> opti_gp_errors = spline_wb.evaluateErrors(CTBA_GP), opti_reproj_errors = spline_wb.evaluateErrors(CTBA_REPROJ);
