@@ -12,6 +12,13 @@ kw = {}
 if len(sys.argv) > 2:
     kw = dict(duration_s=float(sys.argv[1]), n_landmarks=int(sys.argv[2]))
 t0 = time.time(); sc = scene.config_scene(3, **kw); print(f"scene generated in {time.time() - t0:.1f} s: {len(sc['frame_t_ns'])} frames, {len(sc['uv'])} observations", flush=True)
+# the feature grid of computeValidReprojections asserts that every feature lies inside the image (camera.h:157-168): pixel noise pushes a few
+# synthetic features over the border, they are dropped here like a feature detector would never report them
+inside = (sc["uv"][:, 0] >= 0) & (sc["uv"][:, 0] < sc["width"]) & (sc["uv"][:, 1] >= 0) & (sc["uv"][:, 1] < sc["height"])
+cnt = np.add.reduceat(inside.astype(np.int64), sc["obs_begin"][:-1]) if len(sc["uv"]) else np.zeros(0, np.int64)
+sc["obs_begin"] = np.concatenate([[0], np.cumsum(cnt)]).astype(np.int32)
+sc["uv"] = np.ascontiguousarray(sc["uv"][inside]); sc["lm_index"] = np.ascontiguousarray(sc["lm_index"][inside])
+print(f"{int((~inside).sum())} features outside the image dropped")
 d = tempfile.mkdtemp(prefix="ctba_ingest_")
 t0 = time.time()
 yml, res, _ = T._write_gv_dataset(d, sc, 6, Rot.from_quat([0, 0, 0, 1.0]).as_quat(), np.zeros(3), (False, True, False, True, True))

