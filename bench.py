@@ -35,8 +35,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 PKG = "rpg_vision-based_slam_b200"
 WORKLOAD = {1: "configs[0] optimize_continuous_time indoor_forward_3-shaped (G+V+I)", 2: "configs[1] optimize_vi_continuous_time EuRoC MH_01-shaped",
-            3: "configs[2] optimize_gv_continuous_time 1h/10k frames/5M obs"}
-BASE = {1: (50.0, 20000), 2: (180.0, 40000), 3: (3600.0, 270000)}   # duration, landmarks of the configured scene
+            3: "configs[2] optimize_gv_continuous_time 1h/10k frames/5M obs",
+            5: "configs[4] knot-spacing / spline-order sweep at 2M observations (GV shape, 1440 s)"}
+BASE = {1: (50.0, 20000), 2: (180.0, 40000), 3: (3600.0, 270000), 5: (1440.0, 108000)}   # duration, landmarks of the configured scene
 
 
 def clocks_sampler(stop, out, dev):
@@ -65,6 +66,9 @@ def clocks_summary(samples):
     return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(samples[0][1]), "reasons": reasons}
 
 
+SCENE_OVER = {}   # config 5: {"dt_s": ..., "order": ...}
+
+
 def cpu_reference_leg(scene_mod, cfg, steps, warmup, threads, budget_s):
     """The reference's CPU path restated (oracle/): ONE LM iteration per step on the WHOLE configured scene — Jacobian evaluation with the
     Ceres DynamicAutoDiff schedule (stride-4 Jets, one residual block per frame with all its landmarks: what the reference executes),
@@ -73,7 +77,7 @@ def cpu_reference_leg(scene_mod, cfg, steps, warmup, threads, budget_s):
     the line reports the steps that were."""
     from oracle.binding import OracleSpline
     pkg = importlib.import_module(PKG)
-    sc = scene_mod.config_scene(cfg)
+    sc = scene_mod.config_scene(cfg, **SCENE_OVER)
     o = OracleSpline(sc["order"], sc["dt_ns"], sc["start_t_ns"])
     pkg.load_scene(o, sc)
     c = o.counts()
@@ -164,12 +168,21 @@ def main():
                     help="N > 1: strong = the configured problem itself, sharded over N ranks; weak = ONE trajectory of N x the configured duration")
     ap.add_argument("--cpu-budget-s", type=float, default=None, help="time budget of the CPU leg (reference arm: 240 s; cpu_baseline: 100 s)")
     ap.add_argument("--no-also", action="store_true", help="skip the configs[0] / configs[1] rates")
+    ap.add_argument("--dt", type=float, default=None, help="config 5: knot spacing in seconds (0.02 .. 0.2)")
+    ap.add_argument("--order", type=int, default=None, help="config 5: spline order (4 or 6)")
+    ap.add_argument("--linear-solver", default="cholesky", choices=["cholesky", "pcg"], help="bordered band Cholesky (exact step) or block-Jacobi PCG on the same reduced system")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     scene_mod = importlib.import_module(PKG + ".scene")
     threads = os.cpu_count() or 1
+    if a.dt is not None:
+        SCENE_OVER["dt_s"] = a.dt
+    if a.order is not None:
+        SCENE_OVER["order"] = a.order
+    if SCENE_OVER:
+        WORKLOAD[a.config] += ", " + ", ".join(f"{k} = {v}" for k, v in SCENE_OVER.items())
 
     if a.impl == "reference":
         if rank != 0:
@@ -195,7 +208,8 @@ def main():
     # (time-segment sharding, NCCL exchange steps per LM iteration: DESIGN.md §7).
     weak = world > 1 and a.scaling == "weak"
     mult = world if weak else 1
-    sc = scene_mod.config_scene(a.config, duration_s=BASE[a.config][0] * world, n_landmarks=BASE[a.config][1] * world) if weak else scene_mod.config_scene(a.config)
+    sc = (scene_mod.config_scene(a.config, duration_s=BASE[a.config][0] * world, n_landmarks=BASE[a.config][1] * world, **SCENE_OVER) if weak
+          else scene_mod.config_scene(a.config, **SCENE_OVER))
     g = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=local_rank)
     pkg.load_scene(g, sc)
     n_total = g.counts()
@@ -203,6 +217,8 @@ def main():
     stream = torch.cuda.Stream()
     g.setStream(stream.cuda_stream)
     g.setOption("bench_no_termination", 1)
+    if a.linear_solver == "pcg":
+        g.setOption("linear_solver", 1)
     if world > 1:
         uid = torch.zeros(128, dtype=torch.uint8, device=f"cuda:{local_rank}")
         if rank == 0:
@@ -224,7 +240,7 @@ def main():
     steps_done = s["iterations"].shape[0] - 1
     assert steps_done == a.steps, (steps_done, a.steps)
     launches = s["kernel_launches"]
-    trace = s["iterations"][:, 0].copy(); acc_seq = s["iterations"][:, 6].copy()
+    pcg_stats = (g.getStat("pcg_iterations"), g.getStat("pcg_rel_residual")) if a.linear_solver == "pcg" else None
 
     # ---- residual+Jacobian kernels alone ----
     for _ in range(3):
@@ -337,15 +353,21 @@ def main():
                               "frac": band_flops / (solve_ms * 1e-3) / 1e12 / dmma_peak, "traffic": None, "algorithmic_flops": band_flops,
                               "solve_ms": solve_ms, "note": "FP64 DMMA peak measured by profiles/tools/fp64_peaks.cu (profiles/fp64_peaks.json); algorithmic flops = "
                               "sequential block band Cholesky, the time partitions' redundant border work is not counted" + (" (N > 1: rank 0's share of the time, whole-problem flops)" if world > 1 else "")}}
+    line["config"]["linear_solver"] = a.linear_solver
+    if a.linear_solver == "pcg":
+        line["pcg"] = {"iterations_last_solve": pcg_stats[0], "rel_residual_last_solve": pcg_stats[1]}
     if parity is not None:
         line["parity_vs_unsharded"] = parity
         if parity["cost_rel"] > 1e-8 or not parity["accept_seq_equal"]:
             print(json.dumps(line))
             raise SystemExit(f"sharded solve deviates from the unsharded solve: {parity}")
     if world == 1:
-        if not a.no_also:
+        if not a.no_also and a.config == 3:
             del g
             line["also"] = {f"cfg{c}": small_config_rate(torch, pkg, scene_mod, c, local_rank) for c in (1, 2) if c != a.config}
+        if a.cpu_budget_s is not None and a.cpu_budget_s <= 0:
+            print(json.dumps(line))
+            return
         r = cpu_reference_leg(scene_mod, a.config, 1, 0, threads, a.cpu_budget_s or 100.0)
         line["cpu_baseline"] = {"value": r["lm_per_s"], "unit": "it/s", "cores": threads, "kind": "port", "sample": r["sample"], "mobs_per_s": r["mobs_per_s"],
                                 "phases_s": r["phases_s"]}

@@ -185,6 +185,12 @@ int ctba_relinearize_time_offsets(ctba_problem* p);
 /* Options: "bench_no_termination" (1 = ctba_solve runs exactly max_num_iterations LM iterations, convergence tests
  * disabled; measurement only), "cauchy_a" (CauchyLoss parameter of the reprojection blocks, default 3.0, bspline_so3r3.h:1032). */
 int ctba_set_option(ctba_problem* p, const char* name, double value);
+/* More options: "linear_solver" (0 = bordered band Cholesky, the exact step of the reference's SPARSE_NORMAL_CHOLESKY, bspline_so3r3.h:1771;
+ * 1 = block-Jacobi PCG on the same reduced system, the ITERATIVE_SCHUR-style alternative for bands too wide to factor), "pcg_tol"
+ * (|r| <= tol |b|, default 1e-10), "pcg_max_iters", "band_partitions", "bench_accept_all".
+ * ctba_get_stat: read-only facts about the last solve — "pcg_iterations", "pcg_rel_residual", "band_block_columns",
+ * "band_half_width_blocks", "band_launches". */
+int ctba_get_stat(ctba_problem* p, const char* name, double* value);
 /* Forget the device mirrors: the next evaluate/solve uploads state and measurements from the host copies again
  * (used to time the end-to-end path with host buffers). */
 int ctba_invalidate_device(ctba_problem* p);

@@ -28,7 +28,7 @@ EXPORTS = [
     "ctba_initialize_biases", "ctba_num_bias_knots", "ctba_set_biases", "ctba_get_biases", "ctba_set_landmarks", "ctba_get_landmarks",
     "ctba_set_camera", "ctba_set_globals", "ctba_set_corrections", "ctba_get_globals", "ctba_set_flags", "ctba_add_frames", "ctba_add_imu",
     "ctba_add_gp", "ctba_add_position_measurements", "ctba_add_orientation_measurements", "ctba_num_priors", "ctba_cost_terms", "ctba_add_bias_cost", "ctba_add_gravity_norm", "ctba_counts", "ctba_evaluate", "ctba_cost", "ctba_solve",
-    "ctba_relinearize_time_offsets", "ctba_bench_evaluate", "ctba_set_option", "ctba_invalidate_device", "ctba_transfer_bytes",
+    "ctba_relinearize_time_offsets", "ctba_bench_evaluate", "ctba_set_option", "ctba_get_stat", "ctba_invalidate_device", "ctba_transfer_bytes",
     "ctba_bench_reproj", "ctba_compute_valid_reprojections", "ctba_evaluate_errors", "ctba_sample", "ctba_comm_unique_id", "ctba_comm_init_nccl", "ctba_comm_init_local", "ctba_shard_plan",
     "ctba_set_world_alignment", "ctba_get_world_alignment", "ctba_add_alignment_measurements", "ctba_num_alignment_measurements",
 ]
@@ -286,6 +286,11 @@ class BSplineSO3R3:
 
     def setOption(self, name, value):
         self._chk(self.L.ctba_set_option(self.h, name.encode(), C.c_double(value)))
+
+    def getStat(self, name):
+        v = C.c_double(0.0)
+        self._chk(self.L.ctba_get_stat(self.h, name.encode(), C.byref(v)))
+        return float(v.value)
 
     def invalidateDevice(self):
         self._chk(self.L.ctba_invalidate_device(self.h))

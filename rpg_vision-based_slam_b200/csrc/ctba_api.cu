@@ -671,6 +671,9 @@ int ctba_set_option(ctba_problem* p, const char* name, double value) {
   CHECK_P(p);
   if (!name) return CTBA_E_ARG;
   if (!std::strcmp(name, "bench_no_termination")) { p->bench_no_termination = value != 0.0; return CTBA_OK; }
+  if (!std::strcmp(name, "linear_solver")) { p->linear_solver = value != 0.0 ? 1 : 0; return CTBA_OK; }
+  if (!std::strcmp(name, "pcg_tol")) { if (!(value > 0)) return fail(p, CTBA_E_ARG, "pcg_tol must be > 0"); p->pcg_tol = value; return CTBA_OK; }
+  if (!std::strcmp(name, "pcg_max_iters")) { p->pcg_max_iters = (int)value; return CTBA_OK; }
   if (!std::strcmp(name, "bench_accept_all")) { p->bench_accept_all = value != 0.0; return CTBA_OK; }
   if (!std::strcmp(name, "relinearize_mask")) { p->relinearize_mask = (int)value & 3; return CTBA_OK; }
   if (!std::strcmp(name, "band_partitions")) { p->band_partitions = (int)value; return CTBA_OK; }
@@ -680,6 +683,20 @@ int ctba_set_option(ctba_problem* p, const char* name, double value) {
   if (!std::strcmp(name, "band_graph")) { p->band_graph = value != 0.0; return CTBA_OK; }
   if (!std::strcmp(name, "cauchy_a")) { if (!(value > 0)) return fail(p, CTBA_E_ARG, "cauchy_a must be > 0"); p->cauchy_a = value; return CTBA_OK; }
   return fail(p, CTBA_E_ARG, "set_option: unknown option");
+}
+
+// read-only facts about the last solve / the solver's structure (bench and sweep reports)
+int ctba_get_stat(ctba_problem* p, const char* name, double* value) {
+  CHECK_P(p);
+  if (!name || !value) return CTBA_E_ARG;
+  SolverData* sd = p->solver;
+  if (!sd || !sd->built) return fail(p, CTBA_E_STATE, "get_stat: no solve has run on this handle");
+  if (!std::strcmp(name, "pcg_iterations")) { *value = sd->pcg_iterations; return CTBA_OK; }
+  if (!std::strcmp(name, "pcg_rel_residual")) { *value = sd->pcg_rel_residual; return CTBA_OK; }
+  if (!std::strcmp(name, "band_block_columns")) { *value = sd->Hw.nbc; return CTBA_OK; }
+  if (!std::strcmp(name, "band_half_width_blocks")) { *value = sd->Hw.nbw; return CTBA_OK; }
+  if (!std::strcmp(name, "band_launches")) { *value = (double)sd->band_launches; return CTBA_OK; }
+  return fail(p, CTBA_E_ARG, "get_stat: unknown name");
 }
 
 int ctba_invalidate_device(ctba_problem* p) {

@@ -840,7 +840,8 @@ __global__ void __launch_bounds__(256) k_back_rhs(BandLayout B, const __grid_con
 //               after ONE cluster barrier every CTA redundantly forms  x_i = L_ii^-T (t_i - sum of partials)  and keeps its own ring of x blocks.
 // The ring starts with the (already known) solution on the partition's right separator.  delta holds t on entry and x on exit.
 constexpr int kBackCtas = 8;
-__global__ void __launch_bounds__(288) k_band_backsolve(BandLayout B, const __grid_constant__ BandParts PS, const double* __restrict__ dinv,
+template <int MAXT>   // 288 threads cover bands of up to 64 block diagonals; the 448-thread build (wider bands) spills a little
+__global__ void __launch_bounds__(MAXT) k_band_backsolve(BandLayout B, const __grid_constant__ BandParts PS, const double* __restrict__ dinv,
                                                         double* __restrict__ delta) {
   extern __shared__ double sh[];
   cg::cluster_group cluster = cg::this_cluster();
@@ -1155,7 +1156,8 @@ static int enqueue_backsolve(ctba_problem* p, cudaStream_t st, const BandLayout&
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = kBackCtas; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  CTBA_CUDA(p, cudaLaunchKernelEx(&cfg, k_band_backsolve, B, PS, dinv, delta));
+  if (32 * nwarps <= 288) CTBA_CUDA(p, cudaLaunchKernelEx(&cfg, k_band_backsolve<288>, B, PS, dinv, delta));
+  else CTBA_CUDA(p, cudaLaunchKernelEx(&cfg, k_band_backsolve<448>, B, PS, dinv, delta));
   *nl += 2;
   return CTBA_OK;
 }
@@ -1233,7 +1235,7 @@ int band_factor_solve(ctba_problem* p) {
   SolverData* sd = p->solver;
   cudaStream_t st = p->stream;
   BandLayout& B = sd->Hw;
-  if (B.nbw + 1 > 64) { p->err = "band_factor_solve: band wider than 63 blocks of 32 scalars"; return CTBA_E_ARG; }
+  if (B.nbw > 103) { p->err = "band_factor_solve: band wider than 103 blocks of 32 scalars (use linear_solver = 1)"; return CTBA_E_ARG; }
   if (!sd->band_plan) sd->band_plan = new BandPlan();
   if (!sd->band_stream2) {
     cudaStream_t s2, s3; cudaEvent_t ea, eb, ec;

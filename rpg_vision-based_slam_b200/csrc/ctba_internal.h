@@ -104,6 +104,9 @@ struct ctba_problem {
   bool schur_two_stage = true;   // knot-space expansion of the Schur blocks through U(f, kc) (false: one pass over all frame pairs per knot pair)
   bool schur_compact = true;   // landmark Schur gather from the 6-double A blocks (false: from the 18-double Y / Z blocks)
   bool band_graph = true;  // replay the factor+solve launch sequence as a CUDA graph
+  int linear_solver = 0;   // 0: bordered band Cholesky (exact step); 1: block-Jacobi PCG on the same reduced system (ctba_pcg.cu)
+  double pcg_tol = 1e-10;  // PCG stops at |r| <= pcg_tol |b|
+  int pcg_max_iters = 20000;
 
   // ---- host work items ----
   ctba::HVec<int32_t> f_s, f_obs_begin{0};

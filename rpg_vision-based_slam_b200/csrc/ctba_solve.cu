@@ -22,6 +22,7 @@ static inline int cdiv(size_t a, int b) { return (int)((a + b - 1) / b); }
 void solver_free(SolverData* sd) {
   if (!sd) return;
   band_plan_release(sd);
+  pcg_release(sd);
   DBuf<double>* dd[] = {&sd->band0, &sd->bandw, &sd->border0, &sd->borderw, &sd->corner0, &sd->cornerw, &sd->grad, &sd->tot, &sd->V0, &sd->gl, &sd->Sp, &sd->Uk, &sd->Sb,
                         &sd->rp, &sd->Vi, &sd->vig, &sd->ViYg, &sd->Yo, &sd->Zo, &sd->lm_corner_partial, &sd->jscale, &sd->jscale_lm, &sd->delta, &sd->delta_lm, &sd->dpose, &sd->scal, &sd->cand.knot_q, &sd->cand.knot_p,
                         &sd->cand.bias_a, &sd->cand.bias_g, &sd->cand.lm, &sd->cand.glb};
@@ -134,7 +135,7 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
     }
     {
       EvTimer ts(st, &out->time_solve_s);
-      rc = band_factor_solve(p);
+      rc = p->linear_solver ? band_pcg_solve(p) : band_factor_solve(p);
       if (rc) return rc;
       CTBA_CUDA(p, cudaMemcpyAsync(host_flag, sd->flag.p, sizeof(host_flag), cudaMemcpyDeviceToHost, st));
       ts.stop();

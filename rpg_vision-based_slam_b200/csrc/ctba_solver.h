@@ -82,6 +82,8 @@ struct SolverData {
   DBuf<double> dpose;               // per frame 6: pose-space step
   void* band_stream2 = nullptr; void* band_stream3 = nullptr; void* band_evA = nullptr; void* band_evB = nullptr; void* band_evC = nullptr;   // side streams + events of the step launches
   void* band_plan = nullptr;        // BandPlan (ctba_band.cu): time partitions, interface system, scratch
+  void* pcg = nullptr;              // PcgData (ctba_pcg.cu)
+  int pcg_iterations = 0; double pcg_rel_residual = 0.0;   // of the last PCG solve
   int64_t band_launches = 0;        // kernels in one factor+solve
   void* band_graph_exec = nullptr;  // cudaGraphExec_t of the factor+solve launch sequence (band_factor_solve)
   void* band_graph_exec1 = nullptr; void* band_graph_exec2 = nullptr;   // sharded: the halves before / after the interface all-reduce
@@ -101,6 +103,8 @@ int compute_jscale(ctba_problem* p);
 int backsub_and_candidate(ctba_problem* p, const StatePtrs& S, const StatePtrs& C, double radius);
 int step_scalars(ctba_problem* p, const StatePtrs& S, const StatePtrs& C, double radius);
 int band_factor_solve(ctba_problem* p);                          // ctba_band.cu
+int band_pcg_solve(ctba_problem* p);                             // ctba_pcg.cu (option linear_solver = 1)
+void pcg_release(SolverData* sd);
 void band_graph_release(SolverData* sd);
 void band_plan_release(SolverData* sd);
 

@@ -214,6 +214,9 @@ def config_scene(cfg, **over):
     elif cfg == 3:  # optimize_gv_continuous_time: 1 h, 10k frames, 5M obs (500 per frame), GP 10 Hz; 270k landmarks of 28 frames each, of which ~18.5 project inside the image
         kw = dict(order=6, dt_s=0.1, duration_s=3600.0, cam_hz=10000.0 / 3600.0, imu_hz=0.0, gp_hz=10.0, n_landmarks=270000, track_len=28,
                   cam="euroc", seed=20240104, flags=(False, True, False, True, True))
+    elif cfg == 5:  # knot-spacing / spline-order sweep at a fixed 2 M observations: the configs[2] recipe over 1440 s (4000 frames x 500); pass dt_s, order
+        kw = dict(order=6, dt_s=0.1, duration_s=1440.0, cam_hz=10000.0 / 3600.0, imu_hz=0.0, gp_hz=10.0, n_landmarks=108000, track_len=28,
+                  cam="euroc", seed=20240106, flags=(False, True, False, True, True))
     else:
         raise ValueError(cfg)
     kw.update(over)
