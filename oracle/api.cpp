@@ -8,6 +8,7 @@
 #include <cstring>
 #include "lm.h"
 #include "sparse_lm.h"
+#include "dt_problem.h"
 #include "select.h"
 #include "sample.h"
 
@@ -303,5 +304,144 @@ int orc_compute_valid_reprojections(void* h, int F, const int64_t* t_ns, const i
   }
   return 0;
 }
+
+
+// ======================= discrete-time estimator (dt_problem.h) =======================
+void* orc_dt_create() { return new DtProblem(); }
+void orc_dt_destroy(void* h) { delete (DtProblem*)h; }
+int orc_dt_set_camera(void* h, int model, const double* intr, const double* dist, const double* q_bc, const double* p_bc, double t_off, double w, double hh) {
+  auto* p = (DtProblem*)h;
+  p->camera.cam.model = model; p->camera.cam.fx = intr[0]; p->camera.cam.fy = intr[1]; p->camera.cam.cx = intr[2]; p->camera.cam.cy = intr[3];
+  for (int i = 0; i < 4; ++i) { p->camera.cam.d[i] = dist[i]; p->camera.cam.q_bc[i] = q_bc[i]; }
+  for (int i = 0; i < 3; ++i) p->camera.cam.p_bc[i] = p_bc[i];
+  p->camera.t_offset_cam_imu = t_off; p->camera.w = w; p->camera.h = hh; p->built = false;
+  return 0;
+}
+int orc_dt_set_imu_params(void* h, double gnd, double and_, double grw, double arw, double g_max, double a_max, const double* gW) {
+  auto* p = (DtProblem*)h;
+  p->imu.gyro_noise_density = gnd; p->imu.acc_noise_density = and_; p->imu.gyro_random_walk = grw; p->imu.acc_random_walk = arw; p->imu.g_max = g_max; p->imu.a_max = a_max;
+  for (int i = 0; i < 3; ++i) p->imu.g_W[i] = gW[i];
+  return 0;
+}
+int orc_dt_set_states(void* h, int F, const double* poses, const double* ts_cam) { ((DtProblem*)h)->initializeStates(F, poses, ts_cam); return 0; }
+int orc_dt_init_velocity(void* h) { ((DtProblem*)h)->initializeLinearVelocity(); return 0; }
+int orc_dt_set_speed_bias(void* h, const double* sb) { auto* p = (DtProblem*)h; std::memcpy(p->sb.data(), sb, p->sb.size() * sizeof(double)); return 0; }
+int orc_dt_overwrite_states(void* h, const double* poses, const double* sb) { auto* p = (DtProblem*)h; std::memcpy(p->pose.data(), poses, p->pose.size() * 8); std::memcpy(p->sb.data(), sb, p->sb.size() * 8); return 0; }
+int orc_dt_set_pbp(void* h, const double* v) { auto* p = (DtProblem*)h; for (int i = 0; i < 3; ++i) p->p_bp[i] = v[i]; return 0; }
+int orc_dt_get_states(void* h, double* poses, double* sb) { auto* p = (DtProblem*)h; std::memcpy(poses, p->pose.data(), p->pose.size() * 8); std::memcpy(sb, p->sb.data(), p->sb.size() * 8); return 0; }
+int orc_dt_set_landmarks(void* h, int L, const double* xyz) { auto* p = (DtProblem*)h; p->lm.assign(xyz, xyz + 3 * (size_t)L); p->built = false; return 0; }
+int orc_dt_get_landmarks(void* h, double* xyz) { auto* p = (DtProblem*)h; std::memcpy(xyz, p->lm.data(), p->lm.size() * 8); return 0; }
+int orc_dt_set_globals(void* h, double scale, const double* p_bp, double t_gs_imu) { auto* p = (DtProblem*)h; p->scale = scale; for (int i = 0; i < 3; ++i) p->p_bp[i] = p_bp[i]; p->t_offset_gs_imu = t_gs_imu; p->built = false; return 0; }
+// corr9: scale_corr, R_bc_corr (x y z w), p_bc_corr (3), t_offset_cam_imu_corr ; t_gs_corr separately
+int orc_dt_set_corrections(void* h, const double* c9, double t_gs_corr) {
+  auto* p = (DtProblem*)h;
+  p->scale_corr = c9[0]; for (int i = 0; i < 4; ++i) p->R_bc_corr[i] = c9[1 + i]; for (int i = 0; i < 3; ++i) p->p_bc_corr[i] = c9[5 + i]; p->t_offset_cam_imu_corr = c9[8]; p->t_offset_gs_imu_corr = t_gs_corr;
+  return 0;
+}
+// out13: scale_corr, R_bc_corr(4), p_bc_corr(3), t_offset_cam_imu_corr, t_offset_gs_imu_corr, p_bp(3)
+int orc_dt_get_globals(void* h, double* o) {
+  auto* p = (DtProblem*)h;
+  o[0] = p->scale_corr; for (int i = 0; i < 4; ++i) o[1 + i] = p->R_bc_corr[i]; for (int i = 0; i < 3; ++i) o[5 + i] = p->p_bc_corr[i]; o[8] = p->t_offset_cam_imu_corr; o[9] = p->t_offset_gs_imu_corr;
+  for (int i = 0; i < 3; ++i) o[10 + i] = p->p_bp[i];
+  return 0;
+}
+int orc_dt_set_flags(void* h, int scale, int pbp, int camimu, int tgs) { auto* p = (DtProblem*)h; p->optimize_scale = scale; p->optimize_p_bp = pbp; p->optimize_camimu_extrinsics = camimu; p->optimize_t_offset_gs_imu = tgs; p->built = false; return 0; }
+// valid reprojections only: CSR over frames; vel = Point2D::velocity (estimator.h:293-325)
+int orc_dt_add_frames(void* h, int nF, const int32_t* state_id, const int32_t* obs_begin, const double* uv, const double* vel, const int32_t* lm, double sigma) {
+  auto* p = (DtProblem*)h;
+  for (int f = 0; f < nF; ++f) {
+    DtFrame fr; fr.state_id = state_id[f]; fr.inv_std = 1.0 / sigma;
+    for (int q = obs_begin[f]; q < obs_begin[f + 1]; ++q) { fr.uv.push_back(uv[2 * q]); fr.uv.push_back(uv[2 * q + 1]); fr.vel.push_back(vel[2 * q]); fr.vel.push_back(vel[2 * q + 1]); fr.lm.push_back(lm[q]); }
+    p->frames.push_back(std::move(fr));
+  }
+  p->built = false;
+  return nF;
+}
+int orc_dt_add_imu_factor(void* h, int frame0, int n, const double* t, const double* gyr, const double* acc) {
+  auto* p = (DtProblem*)h;
+  auto f = std::make_shared<DtImuFactor>();
+  f->par = p->imu; f->t0 = p->ts_imu[frame0]; f->t1 = p->ts_imu[frame0 + 1];
+  for (int i = 0; i < n; ++i) { DtImuSample s; s.t = t[i]; for (int c = 0; c < 3; ++c) { s.gyr[c] = gyr[3 * i + c]; s.acc[c] = acc[3 * i + c]; } f->meas.push_back(s); }
+  p->imu_factors.push_back(f); p->imu_frame0.push_back(frame0); p->built = false;
+  return 0;
+}
+int orc_dt_add_gp(void* h, int n, const double* t, const double* pos, const int32_t* frame0, double sigma) {
+  auto* p = (DtProblem*)h;
+  for (int i = 0; i < n; ++i) p->gps.push_back({t[i], {pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]}, frame0[i], 1.0 / sigma});
+  p->built = false;
+  return n;
+}
+int orc_dt_counts(void* h, int64_t* c) {
+  auto* p = (DtProblem*)h; p->build();
+  int64_t obs = 0, nf = 0; for (auto& f : p->frames) { obs += (int64_t)f.lm.size(); nf += !f.lm.empty(); }
+  c[0] = nf; c[1] = obs; c[2] = (int64_t)p->imu_factors.size(); c[3] = (int64_t)p->gps.size(); c[4] = p->mp.num_cols;
+  return 0;
+}
+// raw residuals + LOCAL Jacobians, row-major.  kind 0: per observation 2 x 17 [pose 6 | scale 1 | R_bc 3 | p_bc 3 | t_cam_imu 1 | landmark 3];
+// kind 1: per IMU factor 15 x 30 [pose k 6 | sb k 9 | pose k+1 6 | sb k+1 9]; kind 2: per GP 3 x 17 [pose0 6 | pose1 6 | scale 1 | t 1 | p_bp 3].
+// EVERY call evaluates the IMU factors (their pre-integration cache may be redone: imu_cost_functor.h:693-704).
+int orc_dt_evaluate(void* h, int kind, double* r_out, double* j_out) {
+  auto* p = (DtProblem*)h; p->build();
+  size_t ro = 0, jo = 0;
+  for (const auto& b : p->mp.blocks) {
+    if (b.kind != kind) continue;
+    EvalBlockOut o;
+    p->mp.evalBlock(b, j_out != nullptr, &o);
+    const int nc = o.ncols_local;
+    if (kind == 0) {
+      const int n = b.nres / 2, base = 14;
+      for (int i = 0; i < n; ++i)
+        for (int rr = 0; rr < 2; ++rr) {
+          if (r_out) r_out[ro++] = o.r[2 * i + rr];
+          if (j_out) {
+            const double* row = &o.jl[(size_t)(2 * i + rr) * nc];
+            for (int c = 0; c < base; ++c) j_out[jo++] = row[c];
+            for (int c = 0; c < 3; ++c) j_out[jo++] = row[base + 3 * i + c];
+          }
+        }
+    } else {
+      for (int rr = 0; rr < b.nres; ++rr) {
+        if (r_out) r_out[ro++] = o.r[rr];
+        if (j_out) for (int c = 0; c < nc; ++c) j_out[jo++] = o.jl[(size_t)rr * nc + c];
+      }
+    }
+  }
+  return (int)ro;
+}
+int orc_dt_cost(void* h, double* cost4) {
+  auto* p = (DtProblem*)h; p->build();
+  for (int k = 0; k < 4; ++k) cost4[k] = 0;
+  for (const auto& b : p->mp.blocks) {
+    EvalBlockOut o; p->mp.evalBlock(b, false, &o);
+    double c = 0.5 * o.sq_norm;
+    if (b.cauchy_a > 0) { double rho[3]; cauchy(b.cauchy_a, o.sq_norm, rho); c = 0.5 * rho[0]; }
+    cost4[b.kind] += c; cost4[3] += c;
+  }
+  return 0;
+}
+int orc_dt_solve(void* h, int max_iters, int num_threads, double* summary, double* iter_log, int iter_cap) {
+  auto* p = (DtProblem*)h; p->build();
+  SolveSummary s = solveLM(p->mp, max_iters, num_threads);
+  summary[0] = s.termination_type; summary[1] = s.initial_cost; summary[2] = s.final_cost;
+  summary[3] = s.num_successful_steps; summary[4] = s.num_unsuccessful_steps; summary[5] = (double)s.iterations.size();
+  for (size_t i = 0; i < s.iterations.size() && (int)i < iter_cap; ++i) {
+    const auto& it = s.iterations[i];
+    double* o = iter_log + 7 * i;
+    o[0] = it.cost; o[1] = it.cost_change; o[2] = it.gradient_max_norm; o[3] = it.step_norm; o[4] = it.tr_ratio; o[5] = it.tr_radius; o[6] = it.successful;
+  }
+  return 0;
+}
+// one IMU factor at the current state: weighted residual (15) and the reference's MINIMAL Jacobians (15 x 30, jacobians_minimal)
+int orc_dt_imu_minimal(void* h, int k, double* r15, double* jmin) {
+  auto* p = (DtProblem*)h;
+  const int f0 = p->imu_frame0[k];
+  std::vector<const double*> ptrs = {&p->pose[7 * f0], &p->sb[9 * f0], &p->pose[7 * (f0 + 1)], &p->sb[9 * (f0 + 1)]};
+  double jac[15 * 32];
+  p->imu_factors[k]->evaluate(ptrs, r15, jac, jmin);
+  return 0;
+}
+int orc_dt_imu_redo_count(void* h, int k) { return ((DtProblem*)h)->imu_factors[k]->redo_counter; }
+void orc_se3_plus(const double* T, const double* d, double* out) { se3_plus(T, d, out); }
+void orc_se3_plus_jacobian(const double* T, double* J) { double Jm[7][6]; se3_plus_jacobian(T, Jm); for (int i = 0; i < 7; ++i) for (int j = 0; j < 6; ++j) J[6 * i + j] = Jm[i][j]; }
 
 }  // extern "C"

@@ -20,7 +20,7 @@ i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("api.cpp", "lm.h", "sparse_lm.h", "problem.h", "functors.h", "ref_math.h", "jet.h", "select.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("api.cpp", "lm.h", "sparse_lm.h", "dt_problem.h", "problem.h", "functors.h", "ref_math.h", "jet.h", "select.h")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "liboracle.so"], stdout=subprocess.DEVNULL)
     return so
@@ -258,6 +258,142 @@ class OracleSpline:
         o = np.zeros(19)
         self.L.orc_sample(self.h, C.c_int64(int(s)), C.c_double(u), o.ctypes.data_as(C.c_void_p))
         return o
+
+
+class OracleDiscrete:
+    """CPU restatement of DiscreteTimeEstimator + its three cost terms (oracle/dt_problem.h).  Method names follow
+    include/discrete_time_estimator/estimator.h; poses are Sophus SE3 blocks [qx qy qz qw tx ty tz]."""
+
+    def __init__(self):
+        self.L = lib()
+        self.L.orc_dt_create.restype = C.c_void_p
+        self.h = C.c_void_p(self.L.orc_dt_create())
+        self.F = 0
+        self._nlm = 0
+
+    def __del__(self):
+        try:
+            self.L.orc_dt_destroy(self.h)
+        except Exception:
+            pass
+
+    def setCamera(self, model, intr, dist, q_bc, p_bc, t_offset_cam_imu, width, height):
+        a = [_d(v) for v in (intr, dist, q_bc, p_bc)]
+        self.L.orc_dt_set_camera(self.h, int(model), *[v.ctypes.data_as(C.c_void_p) for v in a], C.c_double(t_offset_cam_imu), C.c_double(width), C.c_double(height))
+
+    def setImu(self, gyro_noise_density, acc_noise_density, gyro_random_walk, acc_random_walk, g_W, g_max=7.8, a_max=150.0):
+        g = _d(g_W)
+        self.L.orc_dt_set_imu_params(self.h, C.c_double(gyro_noise_density), C.c_double(acc_noise_density), C.c_double(gyro_random_walk), C.c_double(acc_random_walk),
+                                     C.c_double(g_max), C.c_double(a_max), g.ctypes.data_as(C.c_void_p))
+
+    def initializeStates(self, poses, cam_ts):
+        P, t = _d(poses), _d(cam_ts)
+        self.F = len(t)
+        self.L.orc_dt_set_states(self.h, self.F, P.ctypes.data_as(C.c_void_p), t.ctypes.data_as(C.c_void_p))
+
+    def initializeLinearVelocity(self):
+        self.L.orc_dt_init_velocity(self.h)
+
+    def initializeStatesKeep(self, poses, sb):
+        """overwrite poses and speed-and-biases of the existing states (measurements and IMU caches stay)"""
+        P, x = _d(poses), _d(sb)
+        assert P.shape == (self.F, 7) and x.shape == (self.F, 9)
+        self.L.orc_dt_overwrite_states(self.h, P.ctypes.data_as(C.c_void_p), x.ctypes.data_as(C.c_void_p))
+
+    def setPbp(self, p_bp):
+        a = _d(p_bp)
+        self.L.orc_dt_set_pbp(self.h, a.ctypes.data_as(C.c_void_p))
+
+    def setSpeedAndBias(self, sb):
+        x = _d(sb)
+        assert x.shape == (self.F, 9)
+        self.L.orc_dt_set_speed_bias(self.h, x.ctypes.data_as(C.c_void_p))
+
+    def getStates(self):
+        P, sb = np.zeros((self.F, 7)), np.zeros((self.F, 9))
+        self.L.orc_dt_get_states(self.h, P.ctypes.data_as(C.c_void_p), sb.ctypes.data_as(C.c_void_p))
+        return P, sb
+
+    def set3DPoints(self, xyz):
+        x = _d(xyz); self._nlm = len(x)
+        self.L.orc_dt_set_landmarks(self.h, len(x), x.ctypes.data_as(C.c_void_p))
+
+    def get3DPoints(self):
+        x = np.zeros((self._nlm, 3))
+        self.L.orc_dt_get_landmarks(self.h, x.ctypes.data_as(C.c_void_p))
+        return x
+
+    def setGlobals(self, scale, p_bp, t_offset_globsens_imu):
+        a = _d(p_bp)
+        self.L.orc_dt_set_globals(self.h, C.c_double(scale), a.ctypes.data_as(C.c_void_p), C.c_double(t_offset_globsens_imu))
+
+    def setCorrections(self, corr9, t_gs_corr=0.0):
+        c = _d(corr9); assert c.size == 9
+        self.L.orc_dt_set_corrections(self.h, c.ctypes.data_as(C.c_void_p), C.c_double(t_gs_corr))
+
+    def getGlobals(self):
+        o = np.zeros(13)
+        self.L.orc_dt_get_globals(self.h, o.ctypes.data_as(C.c_void_p))
+        return o
+
+    def setFlags(self, optimize_scale, optimize_pbp, optimize_camimu_extrinsics, optimize_t_offset_globsens_imu):
+        self.L.orc_dt_set_flags(self.h, int(optimize_scale), int(optimize_pbp), int(optimize_camimu_extrinsics), int(optimize_t_offset_globsens_imu))
+
+    def addFrames(self, state_ids, obs_begin, uv, vel, lm_index, sigma_px):
+        sid = np.ascontiguousarray(state_ids, dtype=np.int32); ob = np.ascontiguousarray(obs_begin, dtype=np.int32)
+        u, v = _d(uv), _d(vel); li = np.ascontiguousarray(lm_index, dtype=np.int32)
+        return self.L.orc_dt_add_frames(self.h, len(sid), sid.ctypes.data_as(C.c_void_p), ob.ctypes.data_as(C.c_void_p), u.ctypes.data_as(C.c_void_p),
+                                        v.ctypes.data_as(C.c_void_p), li.ctypes.data_as(C.c_void_p), C.c_double(sigma_px))
+
+    def addImuMeasurements(self, frame0, t, gyr, acc):
+        t, g, a = _d(t), _d(gyr), _d(acc)
+        self.L.orc_dt_add_imu_factor(self.h, int(frame0), len(t), t.ctypes.data_as(C.c_void_p), g.ctypes.data_as(C.c_void_p), a.ctypes.data_as(C.c_void_p))
+
+    def addGlobalSensMeasurements(self, t, pos, frame0, sigma):
+        t, x = _d(t), _d(pos); f0 = np.ascontiguousarray(frame0, dtype=np.int32)
+        return self.L.orc_dt_add_gp(self.h, len(t), t.ctypes.data_as(C.c_void_p), x.ctypes.data_as(C.c_void_p), f0.ctypes.data_as(C.c_void_p), C.c_double(sigma))
+
+    def counts(self):
+        c = np.zeros(5, dtype=np.int64)
+        self.L.orc_dt_counts(self.h, c.ctypes.data_as(C.c_void_p))
+        return dict(zip(["frames", "obs", "imu", "gp", "cols"], [int(v) for v in c]))
+
+    def evaluate(self, kind, jac=True):
+        c = self.counts()
+        nres, w = [(2 * c["obs"], 17), (15 * c["imu"], 30), (3 * c["gp"], 17)][kind]
+        r = np.zeros(nres); J = np.zeros((nres, w)) if jac else None
+        self.L.orc_dt_evaluate(self.h, int(kind), r.ctypes.data_as(C.c_void_p), J.ctypes.data_as(C.c_void_p) if jac else None)
+        return r, J
+
+    def cost(self):
+        o = np.zeros(4)
+        self.L.orc_dt_cost(self.h, o.ctypes.data_as(C.c_void_p))
+        return o
+
+    def optimize(self, max_num_iterations, num_threads=1):
+        s = np.zeros(6); cap = max_num_iterations + 2; log = np.zeros((cap, 7))
+        self.L.orc_dt_solve(self.h, int(max_num_iterations), int(num_threads), s.ctypes.data_as(C.c_void_p), log.ctypes.data_as(C.c_void_p), cap)
+        n = int(s[5])
+        return dict(termination_type=int(s[0]), initial_cost=s[1], final_cost=s[2], num_successful_steps=int(s[3]), num_unsuccessful_steps=int(s[4]),
+                    iterations=log[:min(n, cap)].copy())
+
+    def imuMinimal(self, k):
+        r = np.zeros(15); J = np.zeros((15, 30))
+        self.L.orc_dt_imu_minimal(self.h, int(k), r.ctypes.data_as(C.c_void_p), J.ctypes.data_as(C.c_void_p))
+        return r, J
+
+    def imuRedoCount(self, k):
+        return self.L.orc_dt_imu_redo_count(self.h, int(k))
+
+
+def se3_plus(T, d):
+    o = np.zeros(7); T = _d(T); d = _d(d)
+    lib().orc_se3_plus(T.ctypes.data_as(C.c_void_p), d.ctypes.data_as(C.c_void_p), o.ctypes.data_as(C.c_void_p)); return o
+
+
+def se3_plus_jacobian(T):
+    J = np.zeros((7, 6)); T = _d(T)
+    lib().orc_se3_plus_jacobian(T.ctypes.data_as(C.c_void_p), J.ctypes.data_as(C.c_void_p)); return J
 
 
 # ---- primitives for known-answer tests ----

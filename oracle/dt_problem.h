@@ -59,6 +59,9 @@ inline void se3_plus_jacobian(const double* T, double J[7][6]) {
   J[6][0] = -c17 + c18; J[6][1] = c20 + c21; J[6][2] = c10 + c11 + c19;
 }
 
+inline void se3_plus_fwd(const double* T, const double* d, double* out) { se3_plus(T, d, out); }
+inline void se3_plus_jacobian_fwd(const double* T, double J[7][6]) { se3_plus_jacobian(T, J); }
+
 struct DtCamera { CameraModel cam; double w = 0, h = 0, t_offset_cam_imu = 0; };
 
 // reprojection_cost_functor.h:36-116 (discrete time).  Parameters: T_WB(7), scale_corr(1), R_BC_corr(4), p_BC_corr(3), t_offset_cam_imu_corr(1),
@@ -352,7 +355,7 @@ struct DtImuFactor {
   }
 
   // :667-856.  jac (may be null): 15 x 32 row-major = [15x7 | 15x9 | 15x7 | 15x9], the blocks the reference hands to Ceres
-  void evaluate(const std::vector<const double*>& p, double* residuals, double* jac) const {
+  void evaluate(const std::vector<const double*>& p, double* residuals, double* jac, double* jac_minimal = nullptr) const {
     using namespace dt_detail;
     const double* T0 = p[0]; const double* sb0 = p[1]; const double* T1p = p[2]; const double* sb1 = p[3];
     const Q4 q0{T0[0], T0[1], T0[2], T0[3]}, q1{T1p[0], T1p[1], T1p[2], T1p[3]};
@@ -404,7 +407,7 @@ struct DtImuFactor {
     for (int a = 0; a < 3; ++a) { double s = 0; for (int k = 0; k < 6; ++k) s += F0[6 + a][9 + k] * Delta_b[k]; error[6 + a] = t3[a] + acc_integral[a] + s; }
     for (int c = 0; c < 6; ++c) error[9 + c] = sb0[3 + c] - sb1[3 + c];
     for (int a = 0; a < 15; ++a) { double s = 0; for (int k = 0; k < 15; ++k) s += sqrt_info[a][k] * error[k]; residuals[a] = s; }
-    if (!jac) return;
+    if (!jac && !jac_minimal) return;
     double SF0[15][15], SF1[15][15];
     for (int a = 0; a < 15; ++a) for (int b = 0; b < 15; ++b) { double s0 = 0, s1 = 0; for (int k = 0; k < 15; ++k) { s0 += sqrt_info[a][k] * F0[k][b]; s1 += sqrt_info[a][k] * F1[k][b]; } SF0[a][b] = s0; SF1[a][b] = s1; }
     auto lift = [&](const double* x, double Jl[6][7]) {   // pose_local_parameterization.h:20-31 (reads x[3..6] as a quaternion: the OKVIS layout)
@@ -415,6 +418,9 @@ struct DtImuFactor {
       qoplus(q_inv, Qp);
       for (int a = 0; a < 3; ++a) for (int b = 0; b < 4; ++b) Jl[3 + a][3 + b] = 2.0 * Qp[a][b];
     };
+    if (jac_minimal)   // jacobians_minimal of the reference (:799-806, 829-836): 15 x 30 = [15x6 | 15x9 | 15x6 | 15x9]
+      for (int a = 0; a < 15; ++a) for (int b = 0; b < 15; ++b) { jac_minimal[(size_t)a * 30 + b] = SF0[a][b]; jac_minimal[(size_t)a * 30 + 15 + b] = SF1[a][b]; }
+    if (!jac) return;
     double L0[6][7], L1[6][7];
     lift(T0, L0); lift(T1p, L1);
     for (int a = 0; a < 15; ++a) {

@@ -44,6 +44,8 @@ inline void plusAll(const MiniProblem& mp, const std::vector<double>& delta, std
       SO3<double> e = SO3<double>::exp(V3<double>{delta[p.col], delta[p.col + 1], delta[p.col + 2]});
       SO3<double> r = q * e;
       o[0] = r.x; o[1] = r.y; o[2] = r.z; o[3] = r.w;
+    } else if (p.se3) {
+      se3_plus_fwd(p.ptr, &delta[p.col], o.data());
     } else {
       for (int k = 0; k < p.gsize; ++k) o[k] = p.ptr[k] + delta[p.col + k];
     }

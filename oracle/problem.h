@@ -21,13 +21,18 @@
 
 namespace oracle {
 
+// SE3 plus / plus-Jacobian on the Sophus layout (defined in dt_problem.h)
+void se3_plus_fwd(const double* T, const double* d, double* out);
+void se3_plus_jacobian_fwd(const double* T, double J[7][6]);
+
 struct ParamBlock {
   double* ptr;
   int gsize;
   bool so3;
   bool constant;
-  int lsize() const { return so3 ? 3 : gsize; }
+  int lsize() const { return so3 ? 3 : (se3 ? 6 : gsize); }
   int col = -1;  // tangent-space column offset among ACTIVE blocks (assigned by finalize)
+  bool se3 = false;   // Sophus SE3 block [q, t] with LieLocalParameterization<SE3d> (discrete-time estimator, dt_problem.h)
 };
 
 struct ResidualBlock {
@@ -62,6 +67,11 @@ struct MiniProblem {
     int id = (int)params.size();
     params.push_back({ptr, gsize, so3, false});
     by_ptr[ptr] = id;
+    return id;
+  }
+  int AddParameterBlockSE3(double* ptr) {
+    const int id = AddParameterBlock(ptr, 7, false);
+    params[id].se3 = true;
     return id;
   }
   void SetParameterBlockConstant(double* ptr) { params[by_ptr.at(ptr)].constant = true; }
@@ -105,6 +115,16 @@ struct MiniProblem {
             for (int c = 0; c < 3; ++c) {
               double s = 0;
               for (int k = 0; k < 4; ++k) s += jg[(size_t)r * gtot + g0 + k] * PJ[k][c];
+              out->jl[(size_t)r * ltot + l0 + c] = s;
+            }
+        } else if (p.se3) {
+          // J_local = J_global (r x 7) * SE3::Dx_this_mul_exp_x_at_0 (7 x 6), se3.hpp:135-204
+          double PJ[7][6];
+          se3_plus_jacobian_fwd(p.ptr, PJ);
+          for (int r = 0; r < b.nres; ++r)
+            for (int c = 0; c < 6; ++c) {
+              double s = 0;
+              for (int k = 0; k < 7; ++k) s += jg[(size_t)r * gtot + g0 + k] * PJ[k][c];
               out->jl[(size_t)r * ltot + l0 + c] = s;
             }
         } else {

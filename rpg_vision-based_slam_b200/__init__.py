@@ -400,3 +400,22 @@ def load_scene(prob, sc, with_imu=True, with_gp=True, with_frames=True, with_bia
     if with_imu and with_bias_cost and sc["imu_t_ns"].size:
         n["bias"] = prob.addImuBiasCost(sc["bias_err_freq_hz"], sc["bias_err_dt_s"], sc["sigma_acc_bias_c"], sc["sigma_omega_bias_c"])
     return n
+
+
+def load_dt_scene(prob, d, with_imu=True, with_gp=True, with_frames=True):
+    """Feed a discrete-time scene (scene.dt_scene_from) into any object with the DiscreteTimeEstimator method set (the CUDA problem or the
+    CPU oracle), in the reference driver's order (src/optimize_discrete_time.cpp:436-570)."""
+    prob.setCamera(d["cam_model"], d["intr"], d["dist"], d["q_bc"], d["p_bc"], d["t_offset_cam_imu"], d["width"], d["height"])
+    prob.setImu(d["gyro_noise_density"], d["acc_noise_density"], d["gyro_random_walk"], d["acc_random_walk"], d["g_W"])
+    prob.initializeStates(d["poses"], d["cam_ts"])
+    prob.initializeLinearVelocity()
+    prob.setGlobals(d["scale"], d["p_bp"], d["t_offset_gs_imu"])
+    prob.setFlags(*d["flags"])
+    prob.set3DPoints(d["landmarks"])
+    if with_imu:
+        for (f0, t, gyr, acc) in d["imu"]:
+            prob.addImuMeasurements(f0, t, gyr, acc)
+    if with_frames and d["uv"].shape[0]:
+        prob.addFrames(d["state_ids"], d["obs_begin"], d["uv"], d["vel"], d["lm_index"], d["sigma_reproj_px"])
+    if with_gp and d["gp_t"].size:
+        prob.addGlobalSensMeasurements(d["gp_t"], d["gp_pos"], d["gp_frame0"], d["gp_std"])

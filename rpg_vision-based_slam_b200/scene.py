@@ -194,7 +194,7 @@ def make_scene(order=6, dt_s=0.1, duration_s=6.0, cam_hz=20.0, imu_hz=200.0, gp_
         order=N, dt_ns=dt_ns, start_t_ns=int(start_t_ns), cam_model=c["cam_model"], intr=c["intr"], dist=c["dist"], q_bc=c["q_bc"], p_bc=p_bc,
         t_offset_cam_imu=c["t_offset_cam_imu"], width=W_, height=H_, scale=scale, p_bp=p_bp, g=G_W.copy(), t_s_gp=t_s_gp, flags=tuple(flags),
         knot_q=np.ascontiguousarray(knot_q), knot_p=np.ascontiguousarray(knot_p), landmarks=np.ascontiguousarray(landmarks),
-        gt_knot_q=gt_q, gt_knot_p=gt_p, gt_landmarks=lm_gt,
+        gt_knot_q=gt_q, gt_knot_p=gt_p, gt_landmarks=lm_gt, gt_frame_q=Rwb_f.as_quat(), gt_frame_p=pwb_f,
         frame_t_ns=frame_t_ns, obs_begin=obs_begin, uv=np.ascontiguousarray(uv), lm_index=li.astype(np.int32), sigma_reproj_px=1.0,
         imu_t_ns=imu_t_ns, imu_acc=np.ascontiguousarray(imu_acc), imu_gyr=np.ascontiguousarray(imu_gyr), sigma_acc_c=0.1, sigma_omega_c=0.05,
         sigma_acc_bias_c=0.002, sigma_omega_bias_c=4.0e-05, dt_s_bias=dt_s_bias, init_acc_bias=np.zeros(3), init_gyro_bias=np.zeros(3),
@@ -221,3 +221,52 @@ def config_scene(cfg, **over):
         raise ValueError(cfg)
     kw.update(over)
     return make_scene(**kw)
+
+
+def dt_scene_from(sc, perturb=(0.02, 0.5), seed=7, gyro_random_walk=4.0e-5, acc_random_walk=2.0e-3):
+    """The discrete-time problem (BASELINE configs[3]: one SE(3) state + [v, b_g, b_a] per frame) over the data of a scene of make_scene,
+    prepared the way src/optimize_discrete_time.cpp:436-570 prepares it: states at the frames (ground truth perturbed), IMU samples per
+    consecutive pair with the edge samples (Imu::getMeasurementsContainingEdges, sensor/imu.h:86-135), feature velocities from the next
+    frame (DiscreteTimeEstimator::computeFeatureVelocity, estimator.h:293-325), global positions with their left-closest state
+    (getLeftClosestStateId, sensor/global_position_sensor.h:82-96).  Every observation of the scene is taken as a valid reprojection."""
+    rng = np.random.default_rng(seed)
+    F = sc["frame_t_ns"].size
+    cam_ts = sc["frame_t_ns"] * 1e-9
+    ts_imu = cam_ts + sc["t_offset_cam_imu"]
+    q = (Rot.from_quat(sc["gt_frame_q"]) * Rot.from_rotvec(rng.normal(size=(F, 3)) * np.deg2rad(perturb[1]))).as_quat()
+    t = sc["gt_frame_p"] + rng.normal(size=(F, 3)) * perturb[0]
+    poses = np.ascontiguousarray(np.concatenate([q, t], axis=1))
+    # feature velocities
+    ob = sc["obs_begin"]
+    vel = np.zeros_like(sc["uv"])
+    for f in range(F - 1):
+        a0, a1, b0, b1 = ob[f], ob[f + 1], ob[f + 1], ob[f + 2]
+        nxt = {int(l): k for k, l in zip(range(b0, b1), sc["lm_index"][b0:b1])}
+        dt = cam_ts[f + 1] - cam_ts[f]
+        for k in range(a0, a1):
+            j = nxt.get(int(sc["lm_index"][k]))
+            if j is not None:
+                vel[k] = (sc["uv"][j] - sc["uv"][k]) / dt
+    # IMU samples containing the edges of every consecutive pair
+    ti = sc["imu_t_ns"] * 1e-9
+    imu = []
+    for f in range(F - 1):
+        t0, t1 = ts_imu[f], ts_imu[f + 1]
+        if ti.size == 0 or ti[0] > t0 or ti[-1] < t1:
+            continue
+        k0 = int(np.searchsorted(ti, t0, side="right")) - 1       # last sample with t <= t0
+        k1 = int(np.searchsorted(ti, t1, side="right"))            # first sample with t > t1
+        k1 = min(k1, ti.size - 1)
+        imu.append((f, ti[k0:k1 + 1].copy(), sc["imu_gyr"][k0:k1 + 1].copy(), sc["imu_acc"][k0:k1 + 1].copy()))
+    # global positions
+    t_gp = sc["gp_t_ns"] * 1e-9
+    t_gp_imu_init = sc["t_offset_cam_imu"] - sc["t_s_gp"]
+    f0 = np.searchsorted(ts_imu, t_gp + t_gp_imu_init, side="right") - 1     # first state with ts > t, minus one
+    ok = (f0 >= 0) & (f0 < F - 1)
+    return dict(cam_model=sc["cam_model"], intr=sc["intr"], dist=sc["dist"], q_bc=sc["q_bc"], p_bc=sc["p_bc"], t_offset_cam_imu=sc["t_offset_cam_imu"],
+                width=sc["width"], height=sc["height"], poses=poses, cam_ts=cam_ts, gt_poses=np.concatenate([sc["gt_frame_q"], sc["gt_frame_p"]], axis=1),
+                landmarks=sc["landmarks"], scale=sc["scale"], p_bp=sc["p_bp"], t_offset_gs_imu=t_gp_imu_init, g_W=sc["g"],
+                state_ids=np.arange(F, dtype=np.int32), obs_begin=ob, uv=sc["uv"], vel=vel, lm_index=sc["lm_index"], sigma_reproj_px=sc["sigma_reproj_px"],
+                imu=imu, gyro_noise_density=sc["sigma_omega_c"], acc_noise_density=sc["sigma_acc_c"], gyro_random_walk=gyro_random_walk, acc_random_walk=acc_random_walk,
+                gp_t=t_gp[ok], gp_pos=np.ascontiguousarray(sc["gp_pos"][ok]), gp_frame0=f0[ok].astype(np.int32), gp_std=sc["gp_std"],
+                flags=(sc["flags"][0], sc["flags"][1], sc["flags"][3], sc["flags"][4]))
