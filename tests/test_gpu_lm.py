@@ -149,7 +149,8 @@ def test_pcg_step_equals_cholesky_step(pkg, scene, shape):
         g = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=0)
         pkg.load_scene(g, sc)
         g.setOption("linear_solver", solver)
-        g.setOption("pcg_tol", 1e-11)
+        g.setOption("pcg_tol", 1e-12 if shape == "gvi" else 1e-11)    # the 1e6-weighted gravity-norm row of the G+V+I shape needs the tighter residual
+        g.setOption("pcg_max_iters", 40000)
         s = g.optimize(5)
         out.append((s["iterations"], g.getKnots()[1], g.getStat("pcg_iterations") if solver else 0))
         g.close()
@@ -157,4 +158,4 @@ def test_pcg_step_equals_cholesky_step(pkg, scene, shape):
     assert ia.shape == ib.shape and (ia[:, 6] == ib[:, 6]).all()
     np.testing.assert_allclose(ib[:, 0], ia[:, 0], rtol=1e-8)
     assert np.abs(pa - pb).max() < 1e-4, np.abs(pa - pb).max()     # 0.1 mm: the 1 mm trajectory gate with a margin (weakly observed end knots move most)
-    assert 0 < nit <= 20000, nit
+    assert 0 < nit <= 40000, nit
