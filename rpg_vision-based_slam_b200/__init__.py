@@ -34,6 +34,15 @@ EXPORTS = [
 ]
 
 
+EXPORTS_DT = [
+    "ctba_dt_create", "ctba_dt_destroy", "ctba_dt_last_error", "ctba_dt_set_camera", "ctba_dt_set_imu", "ctba_dt_initialize_states",
+    "ctba_dt_initialize_linear_velocity", "ctba_dt_set_speed_and_bias", "ctba_dt_set_states", "ctba_dt_get_states", "ctba_dt_set_landmarks",
+    "ctba_dt_get_landmarks", "ctba_dt_set_globals", "ctba_dt_set_corrections", "ctba_dt_get_globals", "ctba_dt_set_flags", "ctba_dt_add_frames",
+    "ctba_dt_add_imu", "ctba_dt_add_gp", "ctba_dt_counts", "ctba_dt_evaluate", "ctba_dt_cost", "ctba_dt_evaluate_errors", "ctba_dt_imu_redo_count",
+    "ctba_dt_solve", "ctba_dt_set_option", "ctba_dt_get_stat",
+]
+
+
 class CtbaError(RuntimeError):
     pass
 
@@ -400,6 +409,171 @@ def load_scene(prob, sc, with_imu=True, with_gp=True, with_frames=True, with_bia
     if with_imu and with_bias_cost and sc["imu_t_ns"].size:
         n["bias"] = prob.addImuBiasCost(sc["bias_err_freq_hz"], sc["bias_err_dt_s"], sc["sigma_acc_bias_c"], sc["sigma_omega_bias_c"])
     return n
+
+
+class DiscreteTimeEstimator:
+    """GPU-resident discrete-time problem (include/ctba_dt.h): per-frame SE3 + [v, b_g, b_a] states, reprojection / pre-integrated IMU /
+    interpolated global-position terms, LM solve.  Method names follow include/discrete_time_estimator/estimator.h; poses are Sophus SE3
+    blocks [qx qy qz qw tx ty tz]."""
+
+    def __init__(self, device=0):
+        self.L = lib()
+        self.L.ctba_dt_last_error.restype = C.c_char_p
+        self.L.ctba_dt_last_error.argtypes = [C.c_void_p]
+        self.h = C.c_void_p()
+        rc = self.L.ctba_dt_create(int(device), C.byref(self.h))
+        if rc != 0:
+            self.h = None
+            raise CtbaError(f"ctba_dt_create failed with code {rc} (no CUDA device); there is no CPU fallback")
+        self.F = 0
+        self._nlm = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.ctba_dt_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _chk(self, rc):
+        if rc < 0:
+            raise CtbaError(f"ctba_dt error {rc}: {self.L.ctba_dt_last_error(self.h).decode()}")
+        return rc
+
+    def setCamera(self, model, intr, dist, q_bc, p_bc, t_offset_cam_imu, width, height):
+        a = [_d(v) for v in (intr, dist, q_bc, p_bc)]
+        self._chk(self.L.ctba_dt_set_camera(self.h, int(model), *[_p(v) for v in a], C.c_double(t_offset_cam_imu), C.c_double(width), C.c_double(height)))
+
+    def setImu(self, gyro_noise_density, acc_noise_density, gyro_random_walk, acc_random_walk, g_W, g_max=7.8, a_max=150.0):
+        g = _d(g_W)
+        self._chk(self.L.ctba_dt_set_imu(self.h, C.c_double(gyro_noise_density), C.c_double(acc_noise_density), C.c_double(gyro_random_walk), C.c_double(acc_random_walk),
+                                         C.c_double(g_max), C.c_double(a_max), _p(g)))
+
+    def initializeStates(self, poses, cam_ts):
+        P, t = _d(poses), _d(cam_ts)
+        assert P.shape == (len(t), 7)
+        self.F = len(t)
+        self._chk(self.L.ctba_dt_initialize_states(self.h, self.F, _p(P), _p(t)))
+
+    def initializeLinearVelocity(self):
+        self._chk(self.L.ctba_dt_initialize_linear_velocity(self.h))
+
+    def initializeStatesKeep(self, poses, sb):
+        P, x = _d(poses), _d(sb)
+        assert P.shape == (self.F, 7) and x.shape == (self.F, 9)
+        self._chk(self.L.ctba_dt_set_states(self.h, _p(P), _p(x)))
+
+    def setSpeedAndBias(self, sb):
+        x = _d(sb)
+        assert x.shape == (self.F, 9)
+        self._chk(self.L.ctba_dt_set_speed_and_bias(self.h, _p(x)))
+
+    def getStates(self):
+        P, sb = np.zeros((self.F, 7)), np.zeros((self.F, 9))
+        self._chk(self.L.ctba_dt_get_states(self.h, _p(P), _p(sb)))
+        return P, sb
+
+    def set3DPoints(self, xyz):
+        x = _d(xyz)
+        self._nlm = len(x)
+        self._chk(self.L.ctba_dt_set_landmarks(self.h, len(x), _p(x)))
+
+    def get3DPoints(self):
+        x = np.zeros((self._nlm, 3))
+        self._chk(self.L.ctba_dt_get_landmarks(self.h, _p(x)))
+        return x
+
+    def setGlobals(self, scale, p_bp, t_offset_globsens_imu):
+        self._scale, self._t_gs = float(scale), float(t_offset_globsens_imu)
+        self._chk(self.L.ctba_dt_set_globals(self.h, C.c_double(scale), _p(_d(p_bp)), C.c_double(t_offset_globsens_imu)))
+
+    def setPbp(self, p_bp):
+        """setPbp (estimator.h:731): scale and the time offset keep the values of the last setGlobals"""
+        self._chk(self.L.ctba_dt_set_globals(self.h, C.c_double(self._scale), _p(_d(p_bp)), C.c_double(self._t_gs)))
+
+    def setCorrections(self, corr9, t_gs_corr=0.0):
+        c = _d(corr9)
+        assert c.size == 9
+        self._chk(self.L.ctba_dt_set_corrections(self.h, _p(c), C.c_double(t_gs_corr)))
+
+    def getGlobals(self):
+        o = np.zeros(13)
+        self._chk(self.L.ctba_dt_get_globals(self.h, _p(o)))
+        return o
+
+    def setFlags(self, optimize_scale, optimize_pbp, optimize_camimu_extrinsics, optimize_t_offset_globsens_imu):
+        self._chk(self.L.ctba_dt_set_flags(self.h, int(optimize_scale), int(optimize_pbp), int(optimize_camimu_extrinsics), int(optimize_t_offset_globsens_imu)))
+
+    def addFrames(self, state_ids, obs_begin, uv, vel, lm_index, sigma_px):
+        sid = np.ascontiguousarray(state_ids, dtype=np.int32); ob = np.ascontiguousarray(obs_begin, dtype=np.int32)
+        u, v = _d(uv), _d(vel); li = np.ascontiguousarray(lm_index, dtype=np.int32)
+        return self._chk(self.L.ctba_dt_add_frames(self.h, len(sid), _p(sid), _p(ob), _p(u), _p(v), _p(li), C.c_double(sigma_px)))
+
+    def addImuMeasurements(self, frame0, t, gyr, acc):
+        t, g, a = _d(t), _d(gyr), _d(acc)
+        self._chk(self.L.ctba_dt_add_imu(self.h, int(frame0), len(t), _p(t), _p(g), _p(a)))
+
+    def addGlobalSensMeasurements(self, t, pos, frame0, sigma):
+        t, x = _d(t), _d(pos); f0 = np.ascontiguousarray(frame0, dtype=np.int32)
+        return self._chk(self.L.ctba_dt_add_gp(self.h, len(t), _p(t), _p(x), _p(f0), C.c_double(sigma)))
+
+    def counts(self):
+        c = np.zeros(5, dtype=np.int64)
+        self._chk(self.L.ctba_dt_counts(self.h, _p(c)))
+        return dict(zip(["frames", "obs", "imu", "gp", "cols"], [int(v) for v in c]))
+
+    def evaluate(self, kind, jac=True):
+        c = self.counts()
+        nres, w = [(2 * c["obs"], 17), (15 * c["imu"], 30), (3 * c["gp"], 17)][kind]
+        r = np.zeros(nres); J = np.zeros((nres, w)) if jac else None
+        self._chk(self.L.ctba_dt_evaluate(self.h, int(kind), _p(r), _p(J) if jac else None))
+        return r, J
+
+    def cost(self):
+        o = np.zeros(4)
+        self._chk(self.L.ctba_dt_cost(self.h, _p(o)))
+        return o
+
+    def evaluateReprojectionErrors(self):
+        o = np.zeros(self.counts()["obs"]); self._chk(self.L.ctba_dt_evaluate_errors(self.h, 0, _p(o))); return o
+
+    def evaluateImuErrors(self):
+        o = np.zeros((self.counts()["imu"], 15)); self._chk(self.L.ctba_dt_evaluate_errors(self.h, 1, _p(o))); return o
+
+    def evaluateGlobalPosErrors(self):
+        o = np.zeros(self.counts()["gp"]); self._chk(self.L.ctba_dt_evaluate_errors(self.h, 2, _p(o))); return o
+
+    def imuRedoCount(self, k):
+        v = C.c_int(0)
+        self._chk(self.L.ctba_dt_imu_redo_count(self.h, int(k), C.byref(v)))
+        return v.value
+
+    def optimize(self, max_num_iterations):
+        cap = max_num_iterations + 2
+        its = (_Iteration * cap)()
+        s = _Summary()
+        s.iterations = C.cast(its, C.POINTER(_Iteration))
+        s.iterations_capacity = cap
+        self._chk(self.L.ctba_dt_solve(self.h, int(max_num_iterations), C.byref(s)))
+        n = min(s.num_iterations, cap)
+        log = np.array([[its[i].cost, its[i].cost_change, its[i].gradient_max_norm, its[i].step_norm, its[i].tr_ratio, its[i].tr_radius,
+                         its[i].successful] for i in range(n)]).reshape(n, 7)
+        return dict(termination_type=s.termination_type, initial_cost=s.initial_cost, final_cost=s.final_cost,
+                    num_successful_steps=s.num_successful_steps, num_unsuccessful_steps=s.num_unsuccessful_steps, iterations=log,
+                    time_total_s=s.time_total_s, time_eval_s=s.time_eval_s, time_build_s=s.time_build_s, time_solve_s=s.time_solve_s,
+                    kernel_launches=int(s.kernel_launches))
+
+    def setOption(self, name, value):
+        self._chk(self.L.ctba_dt_set_option(self.h, name.encode(), C.c_double(value)))
+
+    def getStat(self, name):
+        v = C.c_double(0.0)
+        self._chk(self.L.ctba_dt_get_stat(self.h, name.encode(), C.byref(v)))
+        return v.value
 
 
 def load_dt_scene(prob, d, with_imu=True, with_gp=True, with_frames=True):
