@@ -431,6 +431,46 @@ int orc_dt_solve(void* h, int max_iters, int num_threads, double* summary, doubl
   }
   return 0;
 }
+// Sparse LM on the discrete-time problem (sparse_lm.h): band = 15 scalars per state [pose tangent 6 | speed-and-bias 9] in time order.
+int orc_dt_solve_sparse(void* h, int max_iters, int num_threads, int no_termination, double* summary, double* iter_log, int iter_cap, double* timings) {
+  auto* p = (DtProblem*)h; p->build();
+  // band indices in time order over the blocks that are in the problem (a state without IMU factor has no speed-and-bias block)
+  const size_t F = p->numStates();
+  auto in_pose = [p](const double* ptr) { return !p->pose.empty() && ptr >= p->pose.data() && ptr < p->pose.data() + p->pose.size(); };
+  auto in_sb = [p](const double* ptr) { return !p->sb.empty() && ptr >= p->sb.data() && ptr < p->sb.data() + p->sb.size(); };
+  std::vector<char> has_pose(F, 0), has_sb(F, 0);
+  for (const auto& q : p->mp.params) {
+    if (q.col < 0) continue;
+    if (in_pose(q.ptr)) has_pose[(q.ptr - p->pose.data()) / 7] = 1;
+    else if (in_sb(q.ptr)) has_sb[(q.ptr - p->sb.data()) / 9] = 1;
+  }
+  std::vector<int> pose_base(F, -1), sb_base(F, -1);
+  int nb = 0;
+  for (size_t i = 0; i < F; ++i) { if (has_pose[i]) { pose_base[i] = nb; nb += 6; } if (has_sb[i]) { sb_base[i] = nb; nb += 9; } }
+  SparseSpec spec;
+  spec.n_band = nb;
+  spec.lm = &p->lm;
+  spec.band_base = [&](const double* ptr) -> int {
+    if (in_pose(ptr)) return pose_base[(ptr - p->pose.data()) / 7];
+    if (in_sb(ptr)) return sb_base[(ptr - p->sb.data()) / 9];
+    return -1;
+  };
+  SparseTimings tm;
+  SolveSummary s = solveLMSparseSpec(p->mp, spec, max_iters, num_threads, &tm, no_termination != 0);
+  summary[0] = s.termination_type; summary[1] = s.initial_cost; summary[2] = s.final_cost;
+  summary[3] = s.num_successful_steps; summary[4] = s.num_unsuccessful_steps; summary[5] = (double)s.iterations.size();
+  for (size_t i = 0; i < s.iterations.size() && (int)i < iter_cap; ++i) {
+    const auto& it = s.iterations[i];
+    double* o = iter_log + 7 * i;
+    o[0] = it.cost; o[1] = it.cost_change; o[2] = it.gradient_max_norm; o[3] = it.step_norm; o[4] = it.tr_ratio; o[5] = it.tr_radius; o[6] = it.successful;
+  }
+  if (timings) {
+    const double t[12] = {tm.eval_jac_s, tm.eval_res_s, tm.build_s, tm.factor_s, tm.total_s, (double)tm.jac_evals, (double)tm.res_evals, (double)tm.solves,
+                          (double)tm.n_band, (double)tm.half_bandwidth, (double)tm.n_globals, (double)tm.n_landmarks};
+    std::memcpy(timings, t, sizeof(t));
+  }
+  return 0;
+}
 // one IMU factor at the current state: weighted residual (15) and the reference's MINIMAL Jacobians (15 x 30, jacobians_minimal)
 int orc_dt_imu_minimal(void* h, int k, double* r15, double* jmin) {
   auto* p = (DtProblem*)h;

@@ -377,6 +377,16 @@ class OracleDiscrete:
         return dict(termination_type=int(s[0]), initial_cost=s[1], final_cost=s[2], num_successful_steps=int(s[3]), num_unsuccessful_steps=int(s[4]),
                     iterations=log[:min(n, cap)].copy())
 
+    def optimizeSparse(self, max_num_iterations, num_threads=1, no_termination=False):
+        """sparse LM (oracle/sparse_lm.h) on the discrete-time problem: what bench.py's CPU legs time at BASELINE sizes"""
+        s = np.zeros(6); cap = max_num_iterations + 2; log = np.zeros((cap, 7)); tm = np.zeros(12)
+        self.L.orc_dt_solve_sparse(self.h, int(max_num_iterations), int(num_threads), int(bool(no_termination)), s.ctypes.data_as(C.c_void_p), log.ctypes.data_as(C.c_void_p), cap,
+                                   tm.ctypes.data_as(C.c_void_p))
+        n = int(s[5])
+        keys = ["eval_jac_s", "eval_res_s", "build_s", "factor_s", "total_s", "jac_evals", "res_evals", "solves", "n_band", "half_bandwidth", "n_globals", "n_landmarks"]
+        return dict(termination_type=int(s[0]), initial_cost=s[1], final_cost=s[2], num_successful_steps=int(s[3]), num_unsuccessful_steps=int(s[4]),
+                    iterations=log[:min(n, cap)].copy(), timings=dict(zip(keys, [float(v) for v in tm])))
+
     def imuMinimal(self, k):
         r = np.zeros(15); J = np.zeros((15, 30))
         self.L.orc_dt_imu_minimal(self.h, int(k), r.ctypes.data_as(C.c_void_p), J.ctypes.data_as(C.c_void_p))

@@ -17,6 +17,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstring>
+#include <functional>
 #include <thread>
 #include <vector>
 #include "lm.h"
@@ -204,8 +205,16 @@ inline bool band_solve(BandSystem& S, std::vector<double>& x, int nthreads) {
 
 }  // namespace sparse_detail
 
-// Sparse LM on a SplineProblem.  Same constants, control flow and iteration log as solveLM (lm.h).
-inline SolveSummary solveLMSparse(SplineProblem& sp, int max_num_iterations, int num_threads, SparseTimings* tm_out = nullptr, bool no_termination = false) {
+// Where each parameter block lives in the elimination order: landmarks (eliminated first), band blocks in time order, the rest = globals.
+struct SparseSpec {
+  int n_band = 0;
+  const std::vector<double>* lm = nullptr;            // landmark table (3 doubles per landmark)
+  std::function<int(const double*)> band_base;        // >= 0: first band index of the block at this address; -1: not a band block
+};
+
+// Sparse LM on a MiniProblem with the given elimination order.  Same constants, control flow and iteration log as solveLM (lm.h).
+inline SolveSummary solveLMSparseSpec(MiniProblem& mp, const SparseSpec& spec, int max_num_iterations, int num_threads, SparseTimings* tm_out = nullptr,
+                                      bool no_termination = false) {
   using namespace sparse_detail;
   const double initial_radius = 1e4, max_radius = 1e16, min_radius = 1e-32;
   const double min_relative_decrease = 1e-3, min_lm_diagonal = 1e-6, max_lm_diagonal = 1e32;
@@ -213,41 +222,27 @@ inline SolveSummary solveLMSparse(SplineProblem& sp, int max_num_iterations, int
   const int max_consecutive_invalid = 5;
   SparseTimings tm;
   const double t_begin = now_s();
-  sp.build();
-  MiniProblem& mp = sp.mp;
   const int ncol = mp.num_cols;
   const int T = std::max(1, num_threads);
   const size_t nblocks = mp.blocks.size();
 
   // ---- structure: tangent column -> unified index (band | border) or landmark ----
-  const size_t K = sp.numKnots(), Kb = sp.numBiasKnots(), L = sp.lm.size() / 3;
+  static const std::vector<double> no_lm;
+  const std::vector<double>& lmv = spec.lm ? *spec.lm : no_lm;
+  const size_t L = lmv.size() / 3;
   auto in = [](const double* p, const std::vector<double>& v) { return !v.empty() && p >= v.data() && p < v.data() + v.size(); };
-  // nodes in time order: spline knot i at i * dt, bias knot j at j * dt_bias (ties: spline knot first)
-  std::vector<int> node_of_knot(K), node_of_bias(Kb);
-  {
-    bool use_bias = false;
-    for (const auto& p : mp.params) if (p.col >= 0 && (in(p.ptr, sp.acc_bias) || in(p.ptr, sp.gyr_bias))) use_bias = true;
-    const size_t Kb_use = use_bias ? Kb : 0;
-    size_t i = 0, j = 0; int node = 0;
-    while (i < K || j < Kb_use) {
-      const double ti = i < K ? (double)i * (double)sp.dt_ns : 1e300, tj = j < Kb_use ? (double)j * (double)sp.dt_ns_bias : 1e300;
-      if (ti <= tj) node_of_knot[i++] = node++; else node_of_bias[j++] = node++;
-    }
-    tm.n_band = 6 * node;
-  }
+  tm.n_band = spec.n_band;
   const int n_band = tm.n_band;
   std::vector<int> uidx(ncol, -1);       // band / border index; <= -2 for landmark columns
   std::vector<int> lm_first_col(L, -1);
   int ng = 0;
   for (const auto& p : mp.params) {
     if (p.col < 0) continue;
-    int base;
-    if (in(p.ptr, sp.so3)) base = 6 * node_of_knot[(p.ptr - sp.so3.data()) / 4];
-    else if (in(p.ptr, sp.r3)) base = 6 * node_of_knot[(p.ptr - sp.r3.data()) / 3] + 3;
-    else if (in(p.ptr, sp.acc_bias)) base = 6 * node_of_bias[(p.ptr - sp.acc_bias.data()) / 3];
-    else if (in(p.ptr, sp.gyr_bias)) base = 6 * node_of_bias[(p.ptr - sp.gyr_bias.data()) / 3] + 3;
-    else if (in(p.ptr, sp.lm)) { const size_t l = (p.ptr - sp.lm.data()) / 3; lm_first_col[l] = p.col; for (int k = 0; k < 3; ++k) uidx[p.col + k] = -2 - 3 * (int)l - k; continue; }
-    else { base = n_band + ng; ng += p.lsize(); }
+    int base = spec.band_base(p.ptr);
+    if (base < 0) {
+      if (in(p.ptr, lmv)) { const size_t l = (p.ptr - lmv.data()) / 3; lm_first_col[l] = p.col; for (int k = 0; k < 3; ++k) uidx[p.col + k] = -2 - 3 * (int)l - k; continue; }
+      base = n_band + ng; ng += p.lsize();
+    }
     for (int k = 0; k < p.lsize(); ++k) uidx[p.col + k] = base + k;
   }
   tm.n_globals = ng; tm.n_landmarks = (int)L;
@@ -273,7 +268,7 @@ inline SolveSummary solveLMSparse(SplineProblem& sp, int max_num_iterations, int
           const int u = uidx[p.col + k];
           if (u < n_band) { lo = std::min(lo, u); hi = std::max(hi, u); }
         }
-      } else if (b.kind == 0 && in(p.ptr, sp.lm)) { m.lm_local.push_back(l0); m.lm_col.push_back(-1); }   // keeps observation index == list position
+      } else if (b.kind == 0 && in(p.ptr, lmv)) { m.lm_local.push_back(l0); m.lm_col.push_back(-1); }   // keeps observation index == list position
       l0 += p.lsize();
     }
     blk_lo[bi] = lo; blk_hi[bi] = hi;
@@ -555,6 +550,38 @@ inline SolveSummary solveLMSparse(SplineProblem& sp, int max_num_iterations, int
     }
   }
   return finish();
+}
+
+
+// Sparse LM on a SplineProblem: spline / bias knots in time order form the band.
+inline SolveSummary solveLMSparse(SplineProblem& sp, int max_num_iterations, int num_threads, SparseTimings* tm_out = nullptr, bool no_termination = false) {
+  sp.build();
+  MiniProblem& mp = sp.mp;
+  const size_t K = sp.numKnots(), Kb = sp.numBiasKnots();
+  auto in = [](const double* p, const std::vector<double>& v) { return !v.empty() && p >= v.data() && p < v.data() + v.size(); };
+  // nodes in time order: spline knot i at i * dt, bias knot j at j * dt_bias (ties: spline knot first)
+  std::vector<int> node_of_knot(K), node_of_bias(Kb);
+  SparseSpec spec;
+  {
+    bool use_bias = false;
+    for (const auto& p : mp.params) if (p.col >= 0 && (in(p.ptr, sp.acc_bias) || in(p.ptr, sp.gyr_bias))) use_bias = true;
+    const size_t Kb_use = use_bias ? Kb : 0;
+    size_t i = 0, j = 0; int node = 0;
+    while (i < K || j < Kb_use) {
+      const double ti = i < K ? (double)i * (double)sp.dt_ns : 1e300, tj = j < Kb_use ? (double)j * (double)sp.dt_ns_bias : 1e300;
+      if (ti <= tj) node_of_knot[i++] = node++; else node_of_bias[j++] = node++;
+    }
+    spec.n_band = 6 * node;
+  }
+  spec.lm = &sp.lm;
+  spec.band_base = [&](const double* ptr) -> int {
+    if (in(ptr, sp.so3)) return 6 * node_of_knot[(ptr - sp.so3.data()) / 4];
+    if (in(ptr, sp.r3)) return 6 * node_of_knot[(ptr - sp.r3.data()) / 3] + 3;
+    if (in(ptr, sp.acc_bias)) return 6 * node_of_bias[(ptr - sp.acc_bias.data()) / 3];
+    if (in(ptr, sp.gyr_bias)) return 6 * node_of_bias[(ptr - sp.gyr_bias.data()) / 3] + 3;
+    return -1;
+  };
+  return solveLMSparseSpec(mp, spec, max_num_iterations, num_threads, tm_out, no_termination);
 }
 
 }  // namespace oracle

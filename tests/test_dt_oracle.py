@@ -172,3 +172,23 @@ def test_imu_factor_local_jacobian_is_what_the_reference_computes_not_the_deriva
     np.testing.assert_allclose(J[rows, 21:30], Jn[:, 21:30], rtol=1e-4, atol=1e-5 * np.abs(Jn).max())
     # pose columns: J_minimal * liftJacobian([q, t] read as [t, q]) * Dx_this_mul_exp_x_at_0 — not the derivative (SURVEY §8(a), D-row hazard)
     assert np.abs(J[rows, :6] - Jn[:, :6]).max() > 1e-2 * np.abs(Jn[:, :6]).max()
+
+
+@pytest.mark.parametrize("shape", ["gvi", "gv"])
+def test_sparse_lm_equals_dense_lm(oracle, pkg, scene, shape):
+    """the sparse LM that bench.py's CPU legs time on the discrete-time problem (oracle/sparse_lm.h with 15-scalar state nodes) against the
+    dense LM of lm.h: same accept / reject sequence, per-iteration cost 1e-9, same final states"""
+    res = []
+    for sparse in (False, True):
+        sc = scene.make_scene(order=6, duration_s=3.0, n_landmarks=120, track_len=8, imu_hz=200, gp_hz=10, cam_hz=10.0, seed=5, flags=(False, True, False, True, True))
+        d = scene.dt_scene_from(sc, perturb=(0.005, 0.1) if shape == "gvi" else (0.02, 0.5))
+        o = oracle.OracleDiscrete()
+        pkg.load_dt_scene(o, d, with_imu=shape == "gvi")
+        s = o.optimizeSparse(8, 4) if sparse else o.optimize(8, 4)
+        res.append((s, o.getStates(), o.get3DPoints(), o.getGlobals()))
+    (sa, (Pa, sba), la, ga), (sb_, (Pb, sbb), lb, gb) = res
+    assert sa["iterations"].shape == sb_["iterations"].shape
+    assert (sa["iterations"][:, 6] == sb_["iterations"][:, 6]).all() and sa["num_successful_steps"] >= 2
+    np.testing.assert_allclose(sb_["iterations"][:, 0], sa["iterations"][:, 0], rtol=1e-9)
+    np.testing.assert_allclose(Pb, Pa, atol=1e-8); np.testing.assert_allclose(sbb, sba, atol=1e-7)
+    np.testing.assert_allclose(lb, la, atol=1e-7); np.testing.assert_allclose(gb, ga, atol=1e-8)
