@@ -29,6 +29,10 @@ enum { CTBA_DT_REPROJ = 0, CTBA_DT_IMU = 1, CTBA_DT_GP = 2 };
 int ctba_dt_create(int device, ctba_dt_problem** out);
 int ctba_dt_destroy(ctba_dt_problem* p);
 const char* ctba_dt_last_error(const ctba_dt_problem* p);
+/* Use an existing CUDA stream (cudaStream_t passed as void*) for all work of this handle; 0 = own stream. */
+int ctba_dt_set_stream(ctba_dt_problem* p, void* cuda_stream);
+/* The host-side copies become authoritative again: the next compute call uploads state and measurements (bench.py's end-to-end leg). */
+int ctba_dt_invalidate_device(ctba_dt_problem* p);
 
 /* setCameras (one camera; the functor reads cameras_[0])               estimator.h:718, sensor/camera.h
  * model: 4 radtan | 5 equidistant | 7 FOV (colmap ids, as ctba_set_camera); intr = fx fy cx cy; dist = 4; q_bc = x y z w; width, height = image size

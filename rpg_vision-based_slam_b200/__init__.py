@@ -35,7 +35,7 @@ EXPORTS = [
 
 
 EXPORTS_DT = [
-    "ctba_dt_create", "ctba_dt_destroy", "ctba_dt_last_error", "ctba_dt_set_camera", "ctba_dt_set_imu", "ctba_dt_initialize_states",
+    "ctba_dt_create", "ctba_dt_destroy", "ctba_dt_last_error", "ctba_dt_set_stream", "ctba_dt_invalidate_device", "ctba_dt_set_camera", "ctba_dt_set_imu", "ctba_dt_initialize_states",
     "ctba_dt_initialize_linear_velocity", "ctba_dt_set_speed_and_bias", "ctba_dt_set_states", "ctba_dt_get_states", "ctba_dt_set_landmarks",
     "ctba_dt_get_landmarks", "ctba_dt_set_globals", "ctba_dt_set_corrections", "ctba_dt_get_globals", "ctba_dt_set_flags", "ctba_dt_add_frames",
     "ctba_dt_add_imu", "ctba_dt_add_gp", "ctba_dt_counts", "ctba_dt_evaluate", "ctba_dt_cost", "ctba_dt_evaluate_errors", "ctba_dt_imu_redo_count",
@@ -546,6 +546,12 @@ class DiscreteTimeEstimator:
 
     def evaluateGlobalPosErrors(self):
         o = np.zeros(self.counts()["gp"]); self._chk(self.L.ctba_dt_evaluate_errors(self.h, 2, _p(o))); return o
+
+    def setStream(self, cuda_stream):
+        self._chk(self.L.ctba_dt_set_stream(self.h, C.c_void_p(int(cuda_stream))))
+
+    def invalidateDevice(self):
+        self._chk(self.L.ctba_dt_invalidate_device(self.h))
 
     def imuRedoCount(self, k):
         v = C.c_int(0)

@@ -91,7 +91,12 @@ struct ctba_dt_problem {
   Dev<uint8_t> d_sb_active, d_lm_active;
   Dev<double> f_w;                          // per measurement frame sqrt(rho')
   Dev<double> grad, diag, jscale, dvec;     // n_pad + 16 each
-  Dev<double> V0, gl, jscale_lm, Vi, WgS, Wp, delta_lm, rhs_acc;   // 6L, 3L, 3L, 6L, 24L, 18M, 3L, n_pad+16
+  Dev<double> V0, gl, jscale_lm, Vi, Vg, WgS, Wp, Yp, delta_lm, rhs_acc;   // 6L, 3L, 3L, 6L, 3L, 24L, 18M, 18M, 3L, n_pad+16
+  Dev<double> cp_frame, cp_lm, cp_gp;       // partials of the global corner / gradient: 44 per frame, 44 per landmark, 20 per GP run
+  Dev<int64_t> d_key_begin;                 // (state, distance) key -> its landmark pairs (CSR)
+  Dev<int2> d_pairs;                        // (reprojection at the later state, reprojection at the earlier state)
+  Dev<int32_t> d_run_begin, d_gp_order;     // GP samples grouped by first state
+  int T1 = 1;                               // largest state distance coupled through a landmark, + 1
   Dev<double> scal;
   int64_t launches = 0;
   size_t F() const { return ts_cam.size(); }
@@ -194,44 +199,77 @@ __global__ void __launch_bounds__(1024) k_dt_cost(double cauchy_a, int nF, const
   }
 }
 
-// ================= gradient, diag(J^T J), landmark blocks =================
+// ================= direct normal equations of an accepted state: H0, gradient =================
+// Determinism rule of this file: within one kernel pass every output entry has exactly ONE writer, and the passes run in stream order —
+// so the floating-point sums have a fixed order although the writes use atomicAdd (IMU factors and global-position runs of even / odd
+// first state go in separate passes; many-to-one sums are tree reductions over partial buffers).
 __global__ void k_dt_frame_w(double cauchy_a, int nF, const double* __restrict__ f_sq, double* __restrict__ f_w) {
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f < nF) f_w[f] = sqrt(1.0 / (1.0 + f_sq[f] / (cauchy_a * cauchy_a)));   // rho'' < 0: residual and Jacobian scaled by sqrt(rho')
 }
-// one warp per measurement frame: pose and global parts of g = J^T r and diag(J^T J)
-__global__ void __launch_bounds__(128) k_dt_gd_reproj(int nF, int n_pad, const int32_t* __restrict__ f_state, const int32_t* __restrict__ f_obs_begin,
-                                                      const double* __restrict__ f_w, const double* __restrict__ rec, GAct ga, double* __restrict__ grad, double* __restrict__ diag) {
-  const int f = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (f >= nF) return;
-  double g[14], d[14];
-#pragma unroll
-  for (int k = 0; k < 14; ++k) { g[k] = 0.0; d[k] = 0.0; }
-  for (int o = f_obs_begin[f] + lane; o < f_obs_begin[f + 1]; o += 32) {
-    const double* R = rec + 36 * (size_t)o;
-#pragma unroll
-    for (int k = 0; k < 14; ++k) { g[k] += R[2 + k] * R[0] + R[19 + k] * R[1]; d[k] += R[2 + k] * R[2 + k] + R[19 + k] * R[19 + k]; }
+// one block per measurement frame, one thread per output entry: pose block (21), pose x global (48), gradient (6 + 8), global x global
+// partial (36).  All threads walk the frame's records together (broadcast loads).
+constexpr int kCpFrame = 44;   // per-frame / per-landmark partial: 36 corner entries (8 x 8 lower) + 8 gradient / rhs entries
+__global__ void __launch_bounds__(128) k_dt_direct_frame(BandLayout H0, int nF, const int32_t* __restrict__ f_state, const int32_t* __restrict__ f_obs_begin,
+                                                         const double* __restrict__ f_w, const double* __restrict__ rec, GAct ga, int any_global,
+                                                         double* __restrict__ grad, double* __restrict__ cp_frame) {
+  const int f = blockIdx.x, e = threadIdx.x;
+  int ci, cj = -1, kind;   // kind 0: H entry (ci, cj) ; 1: gradient of column ci
+  if (e < 21) { int i = 0; while ((i + 1) * (i + 2) / 2 <= e) ++i; ci = i; cj = e - i * (i + 1) / 2; kind = 0; }
+  else if (e < 69) { ci = 6 + (e - 21) % 8; cj = (e - 21) / 8; kind = 0; }
+  else if (e < 75) { ci = e - 69; kind = 1; }
+  else if (e < 83) { ci = 6 + (e - 75); kind = 1; }
+  else if (e < 119) { const int q = e - 83; int i = 0; while ((i + 1) * (i + 2) / 2 <= q) ++i; ci = 6 + i; cj = 6 + q - i * (i + 1) / 2; kind = 0; }
+  else return;
+  const bool glob = ci >= 6;
+  if (glob && (!any_global || !ga.a[ci - 6] || (cj >= 6 && !ga.a[cj - 6]))) {
+    if (e >= 83 && any_global) cp_frame[(size_t)f * kCpFrame + (e - 83)] = 0.0;
+    if (e >= 75 && e < 83 && any_global) cp_frame[(size_t)f * kCpFrame + 36 + (e - 75)] = 0.0;
+    return;
+  }
+  double v0 = 0.0, v1 = 0.0;
+  const int o0 = f_obs_begin[f], o1 = f_obs_begin[f + 1];
+  if (kind == 0) {
+    int o = o0;
+    for (; o + 1 < o1; o += 2) {
+      const double* R = rec + 36 * (size_t)o;
+      v0 += R[2 + ci] * R[2 + cj] + R[19 + ci] * R[19 + cj];
+      v1 += R[38 + ci] * R[38 + cj] + R[55 + ci] * R[55 + cj];
+    }
+    if (o < o1) { const double* R = rec + 36 * (size_t)o; v0 += R[2 + ci] * R[2 + cj] + R[19 + ci] * R[19 + cj]; }
+  } else {
+    for (int o = o0; o < o1; ++o) { const double* R = rec + 36 * (size_t)o; v0 += R[2 + ci] * R[0] + R[19 + ci] * R[1]; }
   }
   const double w2 = f_w[f] * f_w[f];
-#pragma unroll
-  for (int k = 0; k < 14; ++k) { g[k] = warp_sum(g[k]) * w2; d[k] = warp_sum(d[k]) * w2; }
-  if (lane == 0) {
-    const size_t base = 15 * (size_t)f_state[f];
-    for (int k = 0; k < 6; ++k) { atomicAdd(grad + base + k, g[k]); atomicAdd(diag + base + k, d[k]); }
-    for (int k = 0; k < 8; ++k) if (ga.a[k]) { atomicAdd(grad + n_pad + k, g[6 + k]); atomicAdd(diag + n_pad + k, d[6 + k]); }
-  }
+  const double v = (v0 + v1) * w2;
+  const int base = 15 * f_state[f];
+  if (e < 21) atomicAdd(H0.band + band_addr(H0, base + ci, base + cj), v);
+  else if (e < 69) atomicAdd(H0.border + (size_t)(ci - 6) * H0.n_pad + base + cj, v);
+  else if (e < 75) atomicAdd(grad + base + ci, v);
+  else if (e < 83) cp_frame[(size_t)f * kCpFrame + 36 + (e - 75)] = v;
+  else cp_frame[(size_t)f * kCpFrame + (e - 83)] = v;
 }
-// one thread per (factor, local column)
-__global__ void k_dt_gd_imu(int nI, const int32_t* __restrict__ i_frame0, const double* __restrict__ r, const double* __restrict__ J, double* __restrict__ grad,
-                            double* __restrict__ diag) {
-  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= 30 * (size_t)nI) return;
-  const size_t k = t / 30; const int c = (int)(t % 30);
-  const double* Jk = J + 450 * k; const double* rk = r + 15 * k;
-  double g = 0, d = 0;
-  for (int row = 0; row < 15; ++row) { const double v = Jk[30 * row + c]; g += v * rk[row]; d += v * v; }
-  const size_t idx = 15 * (size_t)i_frame0[k] + c;
-  atomicAdd(grad + idx, g); atomicAdd(diag + idx, d);
+// one warp per IMU factor whose first state has the given parity: 30 x 30 block of J^T J (lower part) and J^T r
+__global__ void __launch_bounds__(128) k_dt_direct_imu(BandLayout H0, int nI, int parity, const int32_t* __restrict__ i_frame0, const double* __restrict__ r,
+                                                       const double* __restrict__ J, double* __restrict__ grad) {
+  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (k >= nI || (i_frame0[k] & 1) != parity) return;
+  const double* Jk = J + 450 * (size_t)k; const double* rk = r + 15 * (size_t)k;
+  const int base = 15 * i_frame0[k];
+  for (int e = lane; e < 465; e += 32) {
+    int i = (int)((sqrt(8.0 * e + 1.0) - 1.0) * 0.5);
+    while ((i + 1) * (i + 2) / 2 <= e) ++i;
+    while (i * (i + 1) / 2 > e) --i;
+    const int j = e - i * (i + 1) / 2;
+    double v = 0;
+    for (int row = 0; row < 15; ++row) v += Jk[30 * row + i] * Jk[30 * row + j];
+    atomicAdd(H0.band + band_addr(H0, base + i, base + j), v);
+  }
+  if (lane < 30) {
+    double g = 0;
+    for (int row = 0; row < 15; ++row) g += Jk[30 * row + lane] * rk[row];
+    atomicAdd(grad + base + lane, g);
+  }
 }
 __device__ __forceinline__ int gp_index(int c, int f0, int n_pad) {   // local column of the GP term -> unified index
   if (c < 6) return 15 * f0 + c;
@@ -240,16 +278,35 @@ __device__ __forceinline__ int gp_index(int c, int f0, int n_pad) {   // local c
   if (c == 13) return n_pad + DGT_TGS;
   return n_pad + DGT_PBP + (c - 14);
 }
-__global__ void k_dt_gd_gp(int nG, int n_pad, const int32_t* __restrict__ g_frame0, const double* __restrict__ r, const double* __restrict__ J, GAct ga,
-                           double* __restrict__ grad, double* __restrict__ diag) {
-  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= 17 * (size_t)nG) return;
-  const size_t i = t / 17; const int c = (int)(t % 17);
-  const int idx = gp_index(c, g_frame0[i], n_pad);
-  if (idx >= n_pad && !ga.a[idx - n_pad]) return;
-  double g = 0, d = 0;
-  for (int row = 0; row < 3; ++row) { const double v = J[51 * i + 17 * row + c]; g += v * r[3 * i + row]; d += v * v; }
-  atomicAdd(grad + idx, g); atomicAdd(diag + idx, d);
+// one block per run of global-position samples between the same two states (first state of the given parity), one thread per output
+// entry: 17 x 17 lower (153) + gradient (17); the samples of the run are summed in their stored order.  Global x global entries and the
+// globals' gradient go to the run's partial (15 + 5).
+constexpr int kCpGp = 20;
+__global__ void __launch_bounds__(192) k_dt_direct_gp(BandLayout H0, int nRuns, int parity, const int32_t* __restrict__ run_begin, const int32_t* __restrict__ gp_order,
+                                                      const double* __restrict__ r, const double* __restrict__ J, GAct ga, double* __restrict__ grad,
+                                                      double* __restrict__ cp_gp) {
+  const int f0 = blockIdx.x, e = threadIdx.x;
+  if (f0 >= nRuns || (f0 & 1) != parity || e >= 170) return;
+  const int b0 = run_begin[f0], b1 = run_begin[f0 + 1];
+  int i, j = -1;
+  if (e < 153) { i = 0; while ((i + 1) * (i + 2) / 2 <= e) ++i; j = e - i * (i + 1) / 2; } else i = e - 153;
+  const int ui = gp_index(i, f0, H0.n_pad), uj = j >= 0 ? gp_index(j, f0, H0.n_pad) : -1;
+  const bool off = (ui >= H0.n_pad && !ga.a[ui - H0.n_pad]) || (uj >= H0.n_pad && !ga.a[uj - H0.n_pad]);
+  double v = 0.0;
+  if (!off)
+    for (int q = b0; q < b1; ++q) {
+      const size_t s = gp_order[q];
+      const double* Js = J + 51 * s;
+      if (j >= 0) v += Js[i] * Js[j] + Js[17 + i] * Js[17 + j] + Js[34 + i] * Js[34 + j];
+      else v += Js[i] * r[3 * s] + Js[17 + i] * r[3 * s + 1] + Js[34 + i] * r[3 * s + 2];
+    }
+  if (j >= 0) {
+    if (i >= 12 && j >= 12) { const int gi = i - 12, gj = j - 12; cp_gp[(size_t)f0 * kCpGp + gi * (gi + 1) / 2 + gj] = v; }
+    else if (!off && b1 > b0) add_sym(H0, ui, uj, v);
+  } else {
+    if (i >= 12) cp_gp[(size_t)f0 * kCpGp + 15 + (i - 12)] = v;
+    else if (b1 > b0) atomicAdd(grad + ui, v);
+  }
 }
 // one thread per landmark: V0 = sum J_l^T J_l (xx xy xz yy yz zz), gl = sum J_l^T r   (list order: fixed)
 __global__ void k_dt_lm_blocks(int L, const int32_t* __restrict__ lm_begin, const int32_t* __restrict__ lm_obs, const int32_t* __restrict__ o_frame,
@@ -269,6 +326,50 @@ __global__ void k_dt_lm_blocks(int L, const int32_t* __restrict__ lm_begin, cons
   for (int k = 0; k < 6; ++k) V0[6 * (size_t)l + k] = V[k];
   for (int k = 0; k < 3; ++k) gl[3 * (size_t)l + k] = g[k];
 }
+// Tree reductions (fixed order) of the per-source partials into the 12 x 12 global corner and the globals' gradient / right-hand side.
+// One block per output: corner entry (t1 >= t2) q = t1 (t1+1)/2 + t2 < 78, or gradient entry 78 + t.
+//   mode 0 (accepted state): corner = frames + GP runs -> H.corner (=), grad[n_pad + t] (=)
+//   mode 1 (LM iteration):   landmark partials          -> H.corner (+=), rhs_acc[n_pad + t] (=)
+__global__ void __launch_bounds__(256) k_dt_corner_reduce(int mode, BandLayout H, int nA, const double* __restrict__ cpA /* frames | landmarks: 44 each */, int nRuns,
+                                                          const double* __restrict__ cp_gp, double* __restrict__ vec /* grad | rhs_acc */) {
+  __shared__ double sh[256];
+  const int q = blockIdx.x;
+  int t1, t2 = -1;
+  if (q < 78) { t1 = 0; while ((t1 + 1) * (t1 + 2) / 2 <= q) ++t1; t2 = q - t1 * (t1 + 1) / 2; } else t1 = q - 78;
+  double s = 0.0;
+  if (cpA && t1 < 8) {
+    const int idx = t2 >= 0 ? t1 * (t1 + 1) / 2 + t2 : 36 + t1;
+    for (int i = threadIdx.x; i < nA; i += 256) s += cpA[(size_t)i * kCpFrame + idx];
+  }
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }
+  double total = sh[0];
+  __syncthreads();
+  if (mode == 0 && cp_gp) {
+    auto g_of = [](int t) { return t == DGT_SCALE ? 0 : t == DGT_TGS ? 1 : (t >= DGT_PBP && t < DGT_PBP + 3) ? 2 + (t - DGT_PBP) : -1; };
+    const int g1 = g_of(t1), g2 = t2 >= 0 ? g_of(t2) : 0;
+    if (g1 >= 0 && g2 >= 0) {
+      const int a = g1 > g2 ? g1 : g2, b = g1 > g2 ? g2 : g1;
+      const int idx = t2 >= 0 ? a * (a + 1) / 2 + b : 15 + g1;
+      double s2 = 0.0;
+      for (int i = threadIdx.x; i < nRuns; i += 256) s2 += cp_gp[(size_t)i * kCpGp + idx];
+      sh[threadIdx.x] = s2;
+      __syncthreads();
+      for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }
+      total += sh[0];
+    }
+  }
+  if (threadIdx.x == 0) {
+    if (t2 >= 0) { if (mode == 0) H.corner[t1 * kBorder + t2] = total; else H.corner[t1 * kBorder + t2] += total; }
+    else vec[H.n_pad + t1] = total;
+  }
+}
+__global__ void k_dt_diag(BandLayout H0, double* __restrict__ diag) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < H0.n_pad) diag[i] = H0.band[band_addr(H0, i, i)];
+  else if (i < H0.n_pad + kBorder) { const int t = i - H0.n_pad; diag[i] = t < GT_SIZE ? H0.corner[t * kBorder + t] : 0.0; }
+}
 __global__ void k_dt_jscale(int n, const double* __restrict__ diag, int L, const double* __restrict__ V0, double* __restrict__ jscale, double* __restrict__ jscale_lm) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) jscale[i] = 1.0 / (1.0 + sqrt(fmax(diag[i], 0.0)));
@@ -278,84 +379,40 @@ __global__ void k_dt_jscale(int n, const double* __restrict__ diag, int L, const
   }
 }
 
-// ================= normal equations of one LM iteration =================
+// ================= normal equations of one LM iteration: Hw = H0 + D - Schur(radius) =================
 __device__ __forceinline__ double lm_damping(double h, double sc, double radius) { return fmin(fmax(h * sc * sc, 1e-6), 1e32) / (radius * sc * sc); }
-
-// one warp per IMU factor: the 30 x 30 block of J^T J (lower part) into the band
-__global__ void __launch_bounds__(128) k_dt_asm_imu(BandLayout B, int nI, const int32_t* __restrict__ i_frame0, const double* __restrict__ J) {
-  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (k >= nI) return;
-  const double* Jk = J + 450 * (size_t)k;
-  const int base = 15 * i_frame0[k];
-  for (int e = lane; e < 465; e += 32) {
-    int i = (int)((sqrt(8.0 * e + 1.0) - 1.0) * 0.5);
-    while ((i + 1) * (i + 2) / 2 <= e) ++i;
-    while (i * (i + 1) / 2 > e) --i;
-    const int j = e - i * (i + 1) / 2;
-    double v = 0;
-    for (int row = 0; row < 15; ++row) v += Jk[30 * row + i] * Jk[30 * row + j];
-    atomicAdd(B.band + band_addr(B, base + i, base + j), v);
-  }
+__device__ __forceinline__ void sym3_mul(const double* Vi, double x, double y, double z, double* o) {   // o = V^-1 [x y z]
+  o[0] = Vi[0] * x + Vi[1] * y + Vi[2] * z; o[1] = Vi[1] * x + Vi[3] * y + Vi[4] * z; o[2] = Vi[2] * x + Vi[4] * y + Vi[5] * z;
 }
-// one thread per (sample, entry of the lower 17 x 17)
-__global__ void k_dt_asm_gp(BandLayout B, int nG, const int32_t* __restrict__ g_frame0, const double* __restrict__ J, GAct ga) {
-  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= 153 * (size_t)nG) return;
-  const size_t s = t / 153; const int e = (int)(t % 153);
-  int i = (int)((sqrt(8.0 * e + 1.0) - 1.0) * 0.5);
-  while ((i + 1) * (i + 2) / 2 <= e) ++i;
-  while (i * (i + 1) / 2 > e) --i;
-  const int j = e - i * (i + 1) / 2;
-  const int f0 = g_frame0[s];
-  const int ui = gp_index(i, f0, B.n_pad), uj = gp_index(j, f0, B.n_pad);
-  if ((ui >= B.n_pad && !ga.a[ui - B.n_pad]) || (uj >= B.n_pad && !ga.a[uj - B.n_pad])) return;
-  const double* Js = J + 51 * s;
-  double v = 0;
-  for (int row = 0; row < 3; ++row) v += Js[17 * row + i] * Js[17 * row + j];
-  add_sym(B, ui, uj, v);
-}
-// one warp per measurement frame: the direct (landmark-free) part of the reprojection term — pose block (21), pose x global (48),
-// global x global (36) — reduced over the frame's points in registers
-__global__ void __launch_bounds__(128) k_dt_asm_frame(BandLayout B, int nF, const int32_t* __restrict__ f_state, const int32_t* __restrict__ f_obs_begin,
-                                                      const double* __restrict__ f_w, const double* __restrict__ rec, GAct ga, int any_global) {
-  const int f = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (f >= nF) return;
-  const int nc = any_global ? 14 : 6;
-  const double w2 = f_w[f] * f_w[f];
-  const int base = 15 * f_state[f];
-  // column pair (i >= j) handled in chunks to bound the register count: i outer, j inner, one reduction per pair
-  for (int i = 0; i < nc; ++i) {
-    if (i >= 6 && !ga.a[i - 6]) continue;
-    for (int j = 0; j <= i; ++j) {
-      if (j >= 6 && !ga.a[j - 6]) continue;
-      double v = 0;
-      for (int o = f_obs_begin[f] + lane; o < f_obs_begin[f + 1]; o += 32) {
-        const double* R = rec + 36 * (size_t)o;
-        v += R[2 + i] * R[2 + j] + R[19 + i] * R[19 + j];
-      }
-      v = warp_sum(v) * w2;
-      if (lane == 0) add_sym(B, i < 6 ? base + i : B.n_pad + (i - 6), j < 6 ? base + j : B.n_pad + (j - 6), v);
-    }
-  }
-}
-// one warp per landmark, pass 1: V^-1 (damped), W_p per point (pose coupling, 6 x 3), summed global coupling W_g (8 x 3)
+// one warp per landmark: V^-1 (damped), V^-1 g, per point W_p (pose coupling 6 x 3) and Y_p = W_p V^-1, summed global coupling W_g (8 x 3),
+// the landmark's partial of the global corner / right-hand side
 __global__ void __launch_bounds__(128) k_dt_schur_prepare(int L, double radius, const int32_t* __restrict__ lm_begin, const int32_t* __restrict__ lm_obs,
                                                           const int32_t* __restrict__ o_frame, const double* __restrict__ f_w, const double* __restrict__ rec,
-                                                          const double* __restrict__ V0, const double* __restrict__ jscale_lm, GAct ga, int any_global,
-                                                          double* __restrict__ Vi, double* __restrict__ WgS, double* __restrict__ Wp, int32_t* __restrict__ flag) {
+                                                          const double* __restrict__ V0, const double* __restrict__ gl, const double* __restrict__ jscale_lm, GAct ga,
+                                                          int any_global, double* __restrict__ Vi, double* __restrict__ Vg, double* __restrict__ WgS,
+                                                          double* __restrict__ Wp, double* __restrict__ Yp, double* __restrict__ cp_lm, int32_t* __restrict__ flag) {
   const int l = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (l >= L) return;
   const int e0 = lm_begin[l], e1 = lm_begin[l + 1];
-  if (e0 == e1) return;
-  if (lane == 0) {
+  if (e0 == e1) {
+    if (any_global) for (int k = lane; k < kCpFrame; k += 32) cp_lm[(size_t)l * kCpFrame + k] = 0.0;
+    return;
+  }
+  double Vinv[6];
+  {
     const double* V = V0 + 6 * (size_t)l; const double* s = jscale_lm + 3 * (size_t)l;
     const double a = V[0] + lm_damping(V[0], s[0], radius), b = V[1], c = V[2], d = V[3] + lm_damping(V[3], s[1], radius), e = V[4], f = V[5] + lm_damping(V[5], s[2], radius);
     const double c00 = d * f - e * e, c01 = c * e - b * f, c02 = b * e - c * d;
     const double det = a * c00 + b * c01 + c * c02;
-    if (!(det > 0.0) || !isfinite(det)) atomicExch(flag, 1);
+    if (lane == 0 && (!(det > 0.0) || !isfinite(det))) atomicExch(flag, 1);
     const double id = 1.0 / det;
-    double* o = Vi + 6 * (size_t)l;
-    o[0] = c00 * id; o[1] = c01 * id; o[2] = c02 * id; o[3] = (a * f - c * c) * id; o[4] = (b * c - a * e) * id; o[5] = (a * d - b * b) * id;
+    Vinv[0] = c00 * id; Vinv[1] = c01 * id; Vinv[2] = c02 * id; Vinv[3] = (a * f - c * c) * id; Vinv[4] = (b * c - a * e) * id; Vinv[5] = (a * d - b * b) * id;
+  }
+  double vg[3];
+  sym3_mul(Vinv, gl[3 * (size_t)l], gl[3 * (size_t)l + 1], gl[3 * (size_t)l + 2], vg);
+  if (lane == 0) {
+    for (int k = 0; k < 6; ++k) Vi[6 * (size_t)l + k] = Vinv[k];
+    for (int k = 0; k < 3; ++k) Vg[3 * (size_t)l + k] = vg[k];
   }
   double wg[24];
 #pragma unroll
@@ -365,11 +422,15 @@ __global__ void __launch_bounds__(128) k_dt_schur_prepare(int L, double radius, 
     const double w = f_w[o_frame[o]], w2 = w * w;
     const double* R = rec + 36 * (size_t)o;
     const double a0 = R[16], a1 = R[17], a2 = R[18], b0 = R[33], b1 = R[34], b2 = R[35];
-    double* W = Wp + 18 * (size_t)o;
+    double* W = Wp + 18 * (size_t)o; double* Y = Yp + 18 * (size_t)o;
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
       const double ja = w2 * R[2 + k], jb = w2 * R[19 + k];
-      W[3 * k] = ja * a0 + jb * b0; W[3 * k + 1] = ja * a1 + jb * b1; W[3 * k + 2] = ja * a2 + jb * b2;
+      const double x = ja * a0 + jb * b0, y = ja * a1 + jb * b1, z = ja * a2 + jb * b2;
+      W[3 * k] = x; W[3 * k + 1] = y; W[3 * k + 2] = z;
+      double yy[3];
+      sym3_mul(Vinv, x, y, z, yy);
+      Y[3 * k] = yy[0]; Y[3 * k + 1] = yy[1]; Y[3 * k + 2] = yy[2];
     }
     if (any_global) {
 #pragma unroll
@@ -381,71 +442,81 @@ __global__ void __launch_bounds__(128) k_dt_schur_prepare(int L, double radius, 
   }
   if (any_global) {
 #pragma unroll
-    for (int k = 0; k < 24; ++k) wg[k] = warp_sum(wg[k]);
-    if (lane == 0) for (int k = 0; k < 24; ++k) WgS[24 * (size_t)l + k] = ga.a[k / 3] ? wg[k] : 0.0;
-  }
-}
-__device__ __forceinline__ void sym3_mul(const double* Vi, double x, double y, double z, double* o) {   // o = V^-1 [x y z]
-  o[0] = Vi[0] * x + Vi[1] * y + Vi[2] * z; o[1] = Vi[1] * x + Vi[3] * y + Vi[4] * z; o[2] = Vi[2] * x + Vi[4] * y + Vi[5] * z;
-}
-// one warp per landmark, pass 2: lanes over the point pairs (i >= j, list sorted by state): -W_i V^-1 W_j^T into the band; the diagonal
-// pairs also carry the pose x global border part and the right-hand side; lane 0 adds the global x global corner part
-__global__ void __launch_bounds__(128) k_dt_schur_pairs(BandLayout B, int L, const int32_t* __restrict__ lm_begin, const int32_t* __restrict__ lm_obs,
-                                                        const int32_t* __restrict__ o_frame, const int32_t* __restrict__ f_state, const double* __restrict__ Vi,
-                                                        const double* __restrict__ WgS, const double* __restrict__ Wp, const double* __restrict__ gl, int any_global,
-                                                        double* __restrict__ rhs_acc) {
-  const int l = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (l >= L) return;
-  const int e0 = lm_begin[l], t = lm_begin[l + 1] - e0;
-  if (t == 0) return;
-  double V[6], g[3], Vg[3];
+    for (int k = 0; k < 24; ++k) { wg[k] = warp_sum(wg[k]); if (!ga.a[k / 3]) wg[k] = 0.0; }
+    if (lane == 0) for (int k = 0; k < 24; ++k) WgS[24 * (size_t)l + k] = wg[k];
+    // partial of the corner: -W_g V^-1 W_g^T (lower 36) and of the right-hand side: -W_g V^-1 g (8)
+    double yg[24];
 #pragma unroll
-  for (int k = 0; k < 6; ++k) V[k] = Vi[6 * (size_t)l + k];
-#pragma unroll
-  for (int k = 0; k < 3; ++k) g[k] = gl[3 * (size_t)l + k];
-  sym3_mul(V, g[0], g[1], g[2], Vg);
-  const int npairs = t * (t + 1) / 2;
-  for (int pr = lane; pr < npairs; pr += 32) {
-    int i = (int)((sqrt(8.0 * pr + 1.0) - 1.0) * 0.5);
-    while ((i + 1) * (i + 2) / 2 <= pr) ++i;
-    while (i * (i + 1) / 2 > pr) --i;
-    const int j = pr - i * (i + 1) / 2;
-    const int oi = lm_obs[e0 + i], oj = lm_obs[e0 + j];
-    const int bi = 15 * f_state[o_frame[oi]], bj = 15 * f_state[o_frame[oj]];
-    const double* Wi = Wp + 18 * (size_t)oi; const double* Wj = Wp + 18 * (size_t)oj;
-    double Y[18];
-#pragma unroll
-    for (int a = 0; a < 6; ++a) sym3_mul(V, Wi[3 * a], Wi[3 * a + 1], Wi[3 * a + 2], Y + 3 * a);
-#pragma unroll
-    for (int a = 0; a < 6; ++a)
-#pragma unroll
-      for (int b = 0; b < 6; ++b) {
-        if (i == j && b > a) continue;
-        const double v = -(Y[3 * a] * Wj[3 * b] + Y[3 * a + 1] * Wj[3 * b + 1] + Y[3 * a + 2] * Wj[3 * b + 2]);
-        atomicAdd(B.band + band_addr(B, bi + a, bj + b), v);
-      }
-    if (i == j) {
-#pragma unroll
-      for (int a = 0; a < 6; ++a) atomicAdd(rhs_acc + bi + a, -(Wi[3 * a] * Vg[0] + Wi[3 * a + 1] * Vg[1] + Wi[3 * a + 2] * Vg[2]));
-      if (any_global) {
-        const double* G = WgS + 24 * (size_t)l;
-        for (int b = 0; b < 8; ++b) {
-          const double g0 = G[3 * b], g1 = G[3 * b + 1], g2 = G[3 * b + 2];
-          if (g0 == 0.0 && g1 == 0.0 && g2 == 0.0) continue;
-#pragma unroll
-          for (int a = 0; a < 6; ++a) atomicAdd(B.border + (size_t)b * B.n_pad + bi + a, -(Y[3 * a] * g0 + Y[3 * a + 1] * g1 + Y[3 * a + 2] * g2));
-        }
-      }
+    for (int k = 0; k < 8; ++k) sym3_mul(Vinv, wg[3 * k], wg[3 * k + 1], wg[3 * k + 2], yg + 3 * k);
+    if (lane == 0) {
+      double* cp = cp_lm + (size_t)l * kCpFrame;
+      int q = 0;
+      for (int t1 = 0; t1 < 8; ++t1) for (int t2 = 0; t2 <= t1; ++t2) cp[q++] = -(yg[3 * t1] * wg[3 * t2] + yg[3 * t1 + 1] * wg[3 * t2 + 1] + yg[3 * t1 + 2] * wg[3 * t2 + 2]);
+      for (int t = 0; t < 8; ++t) cp[36 + t] = -(wg[3 * t] * vg[0] + wg[3 * t + 1] * vg[1] + wg[3 * t + 2] * vg[2]);
     }
   }
-  if (any_global && lane < 8) {
-    const double* G = WgS + 24 * (size_t)l;
-    double Yg[3];
-    sym3_mul(V, G[3 * lane], G[3 * lane + 1], G[3 * lane + 2], Yg);
-    if (G[3 * lane] != 0.0 || G[3 * lane + 1] != 0.0 || G[3 * lane + 2] != 0.0) {
-      for (int b = 0; b <= lane; ++b) atomicAdd(B.corner + lane * kBorder + b, -(Yg[0] * G[3 * b] + Yg[1] * G[3 * b + 1] + Yg[2] * G[3 * b + 2]));
-      atomicAdd(rhs_acc + B.n_pad + lane, -(G[3 * lane] * Vg[0] + G[3 * lane + 1] * Vg[1] + G[3 * lane + 2] * Vg[2]));
+}
+// one warp per (state, distance) key: the 6 x 6 pose block -sum Y_i W_j^T over the landmarks seen from both states, summed in the stored
+// order, one writer per entry.  distance 0: lower triangle only.
+__global__ void __launch_bounds__(128) k_dt_schur_gather(BandLayout B, int nKeys, int T1, const int64_t* __restrict__ key_begin, const int2* __restrict__ pairs,
+                                                         const double* __restrict__ Wp, const double* __restrict__ Yp) {
+  const int key = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (key >= nKeys) return;
+  const int64_t b0 = key_begin[key], b1 = key_begin[key + 1];
+  if (b0 == b1) return;
+  const int si = key / T1, d = key % T1;
+  double acc[36];
+#pragma unroll
+  for (int k = 0; k < 36; ++k) acc[k] = 0.0;
+  for (int64_t q = b0 + lane; q < b1; q += 32) {
+    const int2 pr = pairs[q];
+    const double* Y = Yp + 18 * (size_t)pr.x; const double* W = Wp + 18 * (size_t)pr.y;
+    double w[18];
+#pragma unroll
+    for (int k = 0; k < 18; ++k) w[k] = W[k];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) {
+      const double y0 = Y[3 * a], y1 = Y[3 * a + 1], y2 = Y[3 * a + 2];
+#pragma unroll
+      for (int b = 0; b < 6; ++b) acc[6 * a + b] -= y0 * w[3 * b] + y1 * w[3 * b + 1] + y2 * w[3 * b + 2];
     }
+  }
+  double mine = 0.0, mine2 = 0.0;   // lane k holds entry k, lanes 0..3 also hold entries 32..35
+#pragma unroll
+  for (int k = 0; k < 36; ++k) { const double v = warp_sum(acc[k]); if (k < 32) { if (lane == k) mine = v; } else if (lane == k - 32) mine2 = v; }
+  const int bi = 15 * si, bj = 15 * (si - d);
+  {
+    const int a = lane / 6, b = lane % 6;
+    if (!(d == 0 && b > a)) atomicAdd(B.band + band_addr(B, bi + a, bj + b), mine);
+  }
+  if (lane < 4) {
+    const int k = 32 + lane, a = k / 6, b = k % 6;
+    if (!(d == 0 && b > a)) atomicAdd(B.band + band_addr(B, bi + a, bj + b), mine2);
+  }
+}
+// one block per measurement frame, one thread per output entry: Schur part of pose x global (48) and of the right-hand side (6)
+__global__ void __launch_bounds__(64) k_dt_schur_frame(BandLayout B, int nF, const int32_t* __restrict__ f_state, const int32_t* __restrict__ f_obs_begin,
+                                                       const int32_t* __restrict__ o_lm, const double* __restrict__ Wp, const double* __restrict__ Yp,
+                                                       const double* __restrict__ WgS, const double* __restrict__ Vg, GAct ga, int any_global, double* __restrict__ rhs_acc) {
+  const int f = blockIdx.x, e = threadIdx.x;
+  if (e >= 54) return;
+  const int base = 15 * f_state[f];
+  double v = 0.0;
+  if (e < 48) {
+    const int a = e % 6, b = e / 6;
+    if (!any_global || !ga.a[b]) return;
+    for (int o = f_obs_begin[f]; o < f_obs_begin[f + 1]; ++o) {
+      const double* Y = Yp + 18 * (size_t)o + 3 * a; const double* G = WgS + 24 * (size_t)o_lm[o] + 3 * b;
+      v -= Y[0] * G[0] + Y[1] * G[1] + Y[2] * G[2];
+    }
+    atomicAdd(B.border + (size_t)b * B.n_pad + base + a, v);
+  } else {
+    const int a = e - 48;
+    for (int o = f_obs_begin[f]; o < f_obs_begin[f + 1]; ++o) {
+      const double* W = Wp + 18 * (size_t)o + 3 * a; const double* g = Vg + 3 * (size_t)o_lm[o];
+      v -= W[0] * g[0] + W[1] * g[1] + W[2] * g[2];
+    }
+    atomicAdd(rhs_acc + base + a, v);
   }
 }
 // damping, unit rows for the padding / inactive unknowns, right-hand side
@@ -718,6 +789,40 @@ int dt_structure(ctba_dt_problem* p) {
     span = std::max(span, 15 * (o_state[*(e - 1)] - o_state[*b]) + 5);
   }
   for (size_t k = 0; k < p->nI(); ++k) { sb_active[p->i_frame0[k]] = 1; sb_active[p->i_frame0[k] + 1] = 1; }
+  // (state, distance) keys -> the landmark pairs that couple the two poses: counting sort of all (i >= j) pairs of every landmark list
+  int T = 0;
+  for (size_t l = 0; l < L; ++l) if (lm_begin[l + 1] > lm_begin[l]) T = std::max(T, o_state[lm_obs[lm_begin[l + 1] - 1]] - o_state[lm_obs[lm_begin[l]]]);
+  p->T1 = T + 1;
+  const size_t nKeys = F * (size_t)p->T1;
+  std::vector<int64_t> key_begin(nKeys + 1, 0);
+  for (size_t l = 0; l < L; ++l)
+    for (int i = lm_begin[l]; i < lm_begin[l + 1]; ++i) {
+      const int si = o_state[lm_obs[i]];
+      for (int j = lm_begin[l]; j <= i; ++j) key_begin[(size_t)si * p->T1 + (si - o_state[lm_obs[j]]) + 1]++;
+    }
+  for (size_t k = 0; k < nKeys; ++k) key_begin[k + 1] += key_begin[k];
+  std::vector<int2> pairs((size_t)key_begin[nKeys]);
+  {
+    std::vector<int64_t> cur(key_begin.begin(), key_begin.end() - 1);
+    for (size_t l = 0; l < L; ++l)
+      for (int i = lm_begin[l]; i < lm_begin[l + 1]; ++i) {
+        const int oi = lm_obs[i], si = o_state[oi];
+        for (int j = lm_begin[l]; j <= i; ++j) { const int oj = lm_obs[j]; pairs[(size_t)cur[(size_t)si * p->T1 + (si - o_state[oj])]++] = make_int2(oi, oj); }
+      }
+  }
+  // measurement frames must map to distinct states (one writer per pose block and pass)
+  {
+    std::vector<uint8_t> seen(F, 0);
+    for (int f = 0; f < nFm; ++f) { if (seen[p->f_state[f]]) { p->err = "two measurement frames at one state"; return CTBA_E_ARG; } seen[p->f_state[f]] = 1; }
+  }
+  // global-position samples grouped by their first state, in the order they were added
+  std::vector<int32_t> run_begin(F + 1, 0), gp_order(p->nG());
+  for (size_t i = 0; i < p->nG(); ++i) run_begin[p->g_frame0[i] + 1]++;
+  for (size_t f = 0; f < F; ++f) run_begin[f + 1] += run_begin[f];
+  {
+    std::vector<int32_t> cur(run_begin.begin(), run_begin.end() - 1);
+    for (size_t i = 0; i < p->nG(); ++i) gp_order[cur[p->g_frame0[i]]++] = (int32_t)i;
+  }
   // free global blocks, as DiscreteTimeEstimator wires them (estimator.h:149-165, 373-519)
   const bool has_fr = M > 0, has_gp = p->nG() > 0;
   for (int t = 0; t < GT_SIZE; ++t) p->gactive[t] = 0;
@@ -732,11 +837,15 @@ int dt_structure(ctba_dt_problem* p) {
   if (p->nbw < 1) p->nbw = std::min(1, p->n_pad / kNB - 1);
   DT_CUDA(p, p->d_lm_begin.upload(lm_begin, st)); DT_CUDA(p, p->d_lm_obs.upload(lm_obs, st));
   DT_CUDA(p, p->d_sb_active.upload(sb_active, st)); DT_CUDA(p, p->d_lm_active.upload(lm_active, st));
+  DT_CUDA(p, p->d_key_begin.upload(key_begin, st)); DT_CUDA(p, p->d_pairs.upload(pairs, st));
+  DT_CUDA(p, p->d_run_begin.upload(run_begin, st)); DT_CUDA(p, p->d_gp_order.upload(gp_order, st));
   DT_CUDA(p, cudaStreamSynchronize(st));
   const size_t nu = (size_t)p->n_pad + kBorder;
   DT_CUDA(p, p->f_w.resize(nFm)); DT_CUDA(p, p->grad.resize(nu)); DT_CUDA(p, p->diag.resize(nu)); DT_CUDA(p, p->jscale.resize(nu)); DT_CUDA(p, p->dvec.resize(nu));
   DT_CUDA(p, p->rhs_acc.resize(nu));
   DT_CUDA(p, p->V0.resize(6 * L)); DT_CUDA(p, p->gl.resize(3 * L)); DT_CUDA(p, p->jscale_lm.resize(3 * L)); DT_CUDA(p, p->Vi.resize(6 * L)); DT_CUDA(p, p->WgS.resize(24 * L));
+  DT_CUDA(p, p->Vg.resize(3 * L)); DT_CUDA(p, p->Yp.resize(18 * M)); DT_CUDA(p, p->cp_frame.resize((size_t)kCpFrame * nFm)); DT_CUDA(p, p->cp_lm.resize((size_t)kCpFrame * L));
+  DT_CUDA(p, p->cp_gp.resize((size_t)kCpGp * F));
   DT_CUDA(p, p->Wp.resize(18 * M)); DT_CUDA(p, p->delta_lm.resize(3 * L)); DT_CUDA(p, p->scal.resize(DSC_COUNT));
   DT_CUDA(p, p->cand.pose.resize(7 * F)); DT_CUDA(p, p->cand.sb.resize(9 * F)); DT_CUDA(p, p->cand.lm.resize(3 * L)); DT_CUDA(p, p->cand.glb.resize(DG_SIZE));
   if (p->WgS.p) DT_CUDA(p, cudaMemsetAsync(p->WgS.p, 0, 24 * L * 8, st));
@@ -749,6 +858,8 @@ int dt_structure(ctba_dt_problem* p) {
   B.n_band = p->n_band; B.n_pad = p->n_pad; B.nbc = p->n_pad / kNB; B.nbw = p->nbw;
   DT_CUDA(p, sd->bandw.resize(B.band_elems())); DT_CUDA(p, sd->borderw.resize((size_t)kBorder * B.n_pad)); DT_CUDA(p, sd->cornerw.resize(kBorder * kBorder));
   B.band = sd->bandw.p; B.border = sd->borderw.p; B.corner = sd->cornerw.p;
+  DT_CUDA(p, sd->band0.resize(B.band_elems())); DT_CUDA(p, sd->border0.resize((size_t)kBorder * B.n_pad)); DT_CUDA(p, sd->corner0.resize(kBorder * kBorder));
+  sd->H0 = B; sd->H0.band = sd->band0.p; sd->H0.border = sd->border0.p; sd->H0.corner = sd->corner0.p;
   DT_CUDA(p, sd->delta.resize(nu)); DT_CUDA(p, sd->flag.resize(4));
   DT_CUDA(p, cudaMemsetAsync(sd->delta.p, 0, nu * 8, st));
   sd->built = true;
@@ -756,45 +867,59 @@ int dt_structure(ctba_dt_problem* p) {
   return CTBA_OK;
 }
 
-// gradient, diag(J^T J), landmark blocks from the evaluation buffers of the current state
+// direct normal equations H0 (IMU, global position, landmark-free part of the reprojections), gradient, diag(J^T J), landmark blocks
+// from the evaluation buffers of the current state
 int dt_build(ctba_dt_problem* p, DtEval& ev) {
   cudaStream_t st = p->stream;
-  const int nF = (int)p->f_state.size(), nI = (int)p->nI(), nG = (int)p->nG(), L = p->Lm;
-  const size_t nu = (size_t)p->n_pad + kBorder;
-  const GAct ga = dt_gact(p);
-  DT_CUDA(p, cudaMemsetAsync(p->grad.p, 0, nu * 8, st)); DT_CUDA(p, cudaMemsetAsync(p->diag.p, 0, nu * 8, st));
-  if (nF) {
-    k_dt_frame_w<<<cdiv(nF, 128), 128, 0, st>>>(p->K.cauchy_a, nF, ev.f_sq.p, p->f_w.p);
-    k_dt_gd_reproj<<<cdiv((size_t)nF * 32, 128), 128, 0, st>>>(nF, p->n_pad, p->d_f_state.p, p->d_f_obs_begin.p, p->f_w.p, ev.rec.p, ga, p->grad.p, p->diag.p);
-    p->launches += 2;
-  }
-  if (nI) { k_dt_gd_imu<<<cdiv(30 * (size_t)nI, 128), 128, 0, st>>>(nI, p->d_i_frame0.p, ev.r_imu.p, ev.J_imu.p, p->grad.p, p->diag.p); ++p->launches; }
-  if (nG) { k_dt_gd_gp<<<cdiv(17 * (size_t)nG, 128), 128, 0, st>>>(nG, p->n_pad, p->d_g_frame0.p, ev.r_gp.p, ev.J_gp.p, ga, p->grad.p, p->diag.p); ++p->launches; }
-  if (L) { k_dt_lm_blocks<<<cdiv(L, 128), 128, 0, st>>>(L, p->d_lm_begin.p, p->d_lm_obs.p, p->d_o_frame.p, p->f_w.p, ev.rec.p, p->V0.p, p->gl.p); ++p->launches; }
-  DT_CUDA(p, cudaGetLastError());
-  return CTBA_OK;
-}
-int dt_assemble(ctba_dt_problem* p, DtEval& ev, double radius) {
-  cudaStream_t st = p->stream;
   SolverData* sd = p->ctx->solver;
-  BandLayout& B = sd->Hw;
-  const int nF = (int)p->f_state.size(), nI = (int)p->nI(), nG = (int)p->nG(), L = p->Lm;
+  BandLayout& H0 = sd->H0;
+  const int nF = (int)p->f_state.size(), nI = (int)p->nI(), nG = (int)p->nG(), L = p->Lm, F = (int)p->F();
   const size_t nu = (size_t)p->n_pad + kBorder;
   const GAct ga = dt_gact(p);
   int any_global = 0;
   for (int t = 0; t < 8; ++t) any_global |= ga.a[t];
-  DT_CUDA(p, cudaMemsetAsync(B.band, 0, B.band_elems() * 8, st)); DT_CUDA(p, cudaMemsetAsync(B.border, 0, (size_t)kBorder * B.n_pad * 8, st));
-  DT_CUDA(p, cudaMemsetAsync(B.corner, 0, kBorder * kBorder * 8, st)); DT_CUDA(p, cudaMemsetAsync(p->rhs_acc.p, 0, nu * 8, st));
-  DT_CUDA(p, cudaMemsetAsync(sd->flag.p, 0, 4 * sizeof(int32_t), st));
-  if (nI) { k_dt_asm_imu<<<cdiv((size_t)nI * 32, 128), 128, 0, st>>>(B, nI, p->d_i_frame0.p, ev.J_imu.p); ++p->launches; }
-  if (nG) { k_dt_asm_gp<<<cdiv(153 * (size_t)nG, 128), 128, 0, st>>>(B, nG, p->d_g_frame0.p, ev.J_gp.p, ga); ++p->launches; }
+  DT_CUDA(p, cudaMemsetAsync(H0.band, 0, H0.band_elems() * 8, st)); DT_CUDA(p, cudaMemsetAsync(H0.border, 0, (size_t)kBorder * H0.n_pad * 8, st));
+  DT_CUDA(p, cudaMemsetAsync(H0.corner, 0, kBorder * kBorder * 8, st)); DT_CUDA(p, cudaMemsetAsync(p->grad.p, 0, nu * 8, st));
   if (nF) {
-    k_dt_asm_frame<<<cdiv((size_t)nF * 32, 128), 128, 0, st>>>(B, nF, p->d_f_state.p, p->d_f_obs_begin.p, p->f_w.p, ev.rec.p, ga, any_global);
-    k_dt_schur_prepare<<<cdiv((size_t)L * 32, 128), 128, 0, st>>>(L, radius, p->d_lm_begin.p, p->d_lm_obs.p, p->d_o_frame.p, p->f_w.p, ev.rec.p, p->V0.p, p->jscale_lm.p, ga, any_global,
-                                                                  p->Vi.p, p->WgS.p, p->Wp.p, sd->flag.p + 2);
-    k_dt_schur_pairs<<<cdiv((size_t)L * 32, 128), 128, 0, st>>>(B, L, p->d_lm_begin.p, p->d_lm_obs.p, p->d_o_frame.p, p->d_f_state.p, p->Vi.p, p->WgS.p, p->Wp.p, p->gl.p, any_global,
-                                                                p->rhs_acc.p);
+    k_dt_frame_w<<<cdiv(nF, 128), 128, 0, st>>>(p->K.cauchy_a, nF, ev.f_sq.p, p->f_w.p);
+    k_dt_direct_frame<<<nF, 128, 0, st>>>(H0, nF, p->d_f_state.p, p->d_f_obs_begin.p, p->f_w.p, ev.rec.p, ga, any_global, p->grad.p, p->cp_frame.p);
+    p->launches += 2;
+  }
+  if (nI) for (int par = 0; par < 2; ++par) { k_dt_direct_imu<<<cdiv((size_t)nI * 32, 128), 128, 0, st>>>(H0, nI, par, p->d_i_frame0.p, ev.r_imu.p, ev.J_imu.p, p->grad.p); ++p->launches; }
+  if (nG) for (int par = 0; par < 2; ++par) {
+    k_dt_direct_gp<<<F - 1, 192, 0, st>>>(H0, F - 1, par, p->d_run_begin.p, p->d_gp_order.p, ev.r_gp.p, ev.J_gp.p, ga, p->grad.p, p->cp_gp.p);
+    ++p->launches;
+  }
+  if (L) { k_dt_lm_blocks<<<cdiv(L, 128), 128, 0, st>>>(L, p->d_lm_begin.p, p->d_lm_obs.p, p->d_o_frame.p, p->f_w.p, ev.rec.p, p->V0.p, p->gl.p); ++p->launches; }
+  k_dt_corner_reduce<<<90, 256, 0, st>>>(0, H0, (nF && any_global) ? nF : 0, (nF && any_global) ? p->cp_frame.p : nullptr, nG ? F - 1 : 0, nG ? p->cp_gp.p : nullptr, p->grad.p);
+  k_dt_diag<<<cdiv(nu, 128), 128, 0, st>>>(H0, p->diag.p);
+  p->launches += 2;
+  DT_CUDA(p, cudaGetLastError());
+  return CTBA_OK;
+}
+int dt_assemble(ctba_dt_problem* p, DtEval& ev, double radius) {
+  (void)ev;
+  cudaStream_t st = p->stream;
+  SolverData* sd = p->ctx->solver;
+  BandLayout& B = sd->Hw; BandLayout& H0 = sd->H0;
+  const int nF = (int)p->f_state.size(), L = p->Lm, F = (int)p->F();
+  const size_t nu = (size_t)p->n_pad + kBorder;
+  const GAct ga = dt_gact(p);
+  int any_global = 0;
+  for (int t = 0; t < 8; ++t) any_global |= ga.a[t];
+  DT_CUDA(p, cudaMemcpyAsync(B.band, H0.band, B.band_elems() * 8, cudaMemcpyDeviceToDevice, st));
+  DT_CUDA(p, cudaMemcpyAsync(B.border, H0.border, (size_t)kBorder * B.n_pad * 8, cudaMemcpyDeviceToDevice, st));
+  DT_CUDA(p, cudaMemcpyAsync(B.corner, H0.corner, kBorder * kBorder * 8, cudaMemcpyDeviceToDevice, st));
+  DT_CUDA(p, cudaMemsetAsync(p->rhs_acc.p, 0, nu * 8, st));
+  DT_CUDA(p, cudaMemsetAsync(sd->flag.p, 0, 4 * sizeof(int32_t), st));
+  if (nF && L) {
+    k_dt_schur_prepare<<<cdiv((size_t)L * 32, 128), 128, 0, st>>>(L, radius, p->d_lm_begin.p, p->d_lm_obs.p, p->d_o_frame.p, p->f_w.p, p->ev.rec.p, p->V0.p, p->gl.p, p->jscale_lm.p, ga,
+                                                                  any_global, p->Vi.p, p->Vg.p, p->WgS.p, p->Wp.p, p->Yp.p, p->cp_lm.p, sd->flag.p + 2);
+    const size_t nKeys = (size_t)F * p->T1;
+    k_dt_schur_gather<<<cdiv(nKeys * 32, 128), 128, 0, st>>>(B, (int)nKeys, p->T1, p->d_key_begin.p, p->d_pairs.p, p->Wp.p, p->Yp.p);
+    k_dt_schur_frame<<<nF, 64, 0, st>>>(B, nF, p->d_f_state.p, p->d_f_obs_begin.p, p->d_o_lm.p, p->Wp.p, p->Yp.p, p->WgS.p, p->Vg.p, ga, any_global, p->rhs_acc.p);
     p->launches += 3;
+    if (any_global) { k_dt_corner_reduce<<<90, 256, 0, st>>>(1, B, L, p->cp_lm.p, 0, nullptr, p->rhs_acc.p); ++p->launches; }
   }
   k_dt_finish<<<cdiv(nu, 128), 128, 0, st>>>(B, p->n_band, p->d_sb_active.p, p->jscale.p, p->diag.p, p->grad.p, p->rhs_acc.p, radius, ga, p->dvec.p);
   ++p->launches;
@@ -974,6 +1099,21 @@ int ctba_dt_destroy(ctba_dt_problem* p) {
   return ctba_destroy(ctx);
 }
 const char* ctba_dt_last_error(const ctba_dt_problem* p) { return p ? p->err.c_str() : "null handle"; }
+int ctba_dt_set_stream(ctba_dt_problem* p, void* cuda_stream) {
+  DT_CHECK(p);
+  cudaStreamSynchronize(p->stream);
+  const int rc = ctba_set_stream(p->ctx, cuda_stream);
+  if (rc) { p->err = p->ctx->err; return rc; }
+  p->stream = p->ctx->stream;
+  return CTBA_OK;
+}
+// the host arrays are authoritative again: the next compute call uploads state and measurements (end-to-end timing through host buffers)
+int ctba_dt_invalidate_device(ctba_dt_problem* p) {
+  DT_CHECK(p);
+  const int rc = dt_download(p); if (rc) return rc;
+  p->meas_dirty = p->state_dirty = true;
+  return CTBA_OK;
+}
 
 int ctba_dt_set_camera(ctba_dt_problem* p, int model, const double* intr, const double* dist, const double* q_bc, const double* p_bc, double t_off, double width,
                        double height) {

@@ -214,6 +214,9 @@ def config_scene(cfg, **over):
     elif cfg == 3:  # optimize_gv_continuous_time: 1 h, 10k frames, 5M obs (500 per frame), GP 10 Hz; 270k landmarks of 28 frames each, of which ~18.5 project inside the image
         kw = dict(order=6, dt_s=0.1, duration_s=3600.0, cam_hz=10000.0 / 3600.0, imu_hz=0.0, gp_hz=10.0, n_landmarks=270000, track_len=28,
                   cam="euroc", seed=20240104, flags=(False, True, False, True, True))
+    elif cfg == 4:  # optimize_discrete_time on the configs[2] scene: the same frames / landmarks / observations plus a 100 Hz IMU for the pre-integrated factors
+        kw = dict(order=6, dt_s=0.1, duration_s=3600.0, cam_hz=10000.0 / 3600.0, imu_hz=100.0, gp_hz=10.0, n_landmarks=270000, track_len=28,
+                  cam="euroc", seed=20240104, flags=(False, True, False, True, True))
     elif cfg == 5:  # knot-spacing / spline-order sweep at a fixed 2 M observations: the configs[2] recipe over 1440 s (4000 frames x 500); pass dt_s, order
         kw = dict(order=6, dt_s=0.1, duration_s=1440.0, cam_hz=10000.0 / 3600.0, imu_hz=0.0, gp_hz=10.0, n_landmarks=108000, track_len=28,
                   cam="euroc", seed=20240106, flags=(False, True, False, True, True))
@@ -241,12 +244,15 @@ def dt_scene_from(sc, perturb=(0.02, 0.5), seed=7, gyro_random_walk=4.0e-5, acc_
     vel = np.zeros_like(sc["uv"])
     for f in range(F - 1):
         a0, a1, b0, b1 = ob[f], ob[f + 1], ob[f + 1], ob[f + 2]
-        nxt = {int(l): k for k, l in zip(range(b0, b1), sc["lm_index"][b0:b1])}
-        dt = cam_ts[f + 1] - cam_ts[f]
-        for k in range(a0, a1):
-            j = nxt.get(int(sc["lm_index"][k]))
-            if j is not None:
-                vel[k] = (sc["uv"][j] - sc["uv"][k]) / dt
+        if a1 == a0 or b1 == b0:
+            continue
+        la, lb = sc["lm_index"][a0:a1], sc["lm_index"][b0:b1]
+        order = np.argsort(lb, kind="stable")
+        pos = np.searchsorted(lb[order], la)
+        pos_c = np.minimum(pos, lb.size - 1)
+        hit = lb[order][pos_c] == la
+        j = b0 + order[pos_c[hit]]
+        vel[a0:a1][hit] = (sc["uv"][j] - sc["uv"][a0:a1][hit]) / (cam_ts[f + 1] - cam_ts[f])
     # IMU samples containing the edges of every consecutive pair
     ti = sc["imu_t_ns"] * 1e-9
     imu = []
