@@ -39,7 +39,7 @@ int ctba_dt_invalidate_device(ctba_dt_problem* p);
  * used by the out-of-image gate of the shifted feature (reprojection_cost_functor.h:87-94). */
 int ctba_dt_set_camera(ctba_dt_problem* p, int model, const double* intr, const double* dist, const double* q_bc, const double* p_bc,
                        double t_offset_cam_imu_s, double width, double height);
-/* setImu (noise densities, random walks, saturation limits) + setGravity    estimator.h:715, 728; sensor/imu.h ImuCalibration */
+/* setImu (noise densities, random walks, saturation limits) + setGravity    estimator.h:715, 728; sensor/imu_calib.h:13-43 */
 int ctba_dt_set_imu(ctba_dt_problem* p, double gyro_noise_density, double acc_noise_density, double gyro_random_walk, double acc_random_walk,
                     double g_max, double a_max, const double* g_W);
 /* initializeStates(init_poses, cam_ts): F states, ts_imu = ts_cam + t_offset_cam_imu, speed-and-bias zero     estimator.h:88-103 */
