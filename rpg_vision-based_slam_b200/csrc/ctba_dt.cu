@@ -97,7 +97,7 @@ struct ctba_dt_problem {
   Dev<int2> d_pairs;                        // (reprojection at the later state, reprojection at the earlier state)
   Dev<int32_t> d_run_begin, d_gp_order;     // GP samples grouped by first state
   int T1 = 1;                               // largest state distance coupled through a landmark, + 1
-  Dev<double> scal;
+  Dev<double> scal, scal_part;
   int64_t launches = 0;
   size_t F() const { return ts_cam.size(); }
   size_t M() const { return o_lm.size(); }
@@ -117,6 +117,18 @@ namespace {
 inline int cdiv(size_t a, int b) { return (int)((a + b - 1) / b); }
 
 struct GAct { int a[GT_SIZE]; };
+
+// 256-bit accesses (32-byte aligned): one sector per request instead of four 8-byte requests
+__device__ __forceinline__ void ld256(const double* p, double* v) {
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3]) : "l"(p));
+}
+__device__ __forceinline__ void ld256c(const double* p, double* v) {   // coherent: data written earlier by another kernel of the same graph / stream is fine either way; kept for buffers rewritten every iteration
+  asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3]) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void st256(double* p, const double* v) {
+  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(v[0]), "d"(v[1]), "d"(v[2]), "d"(v[3]) : "memory");
+}
+constexpr int kWS = 20;   // stride of the per-reprojection W / Y records: 18 doubles padded to 160 B = 5 sectors
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
@@ -141,15 +153,16 @@ __global__ void __launch_bounds__(128) k_dt_reproj(DtConst K, int nF, const int3
   double sq = 0.0;
   for (int o = f_obs_begin[f] + lane; o < f_obs_begin[f + 1]; o += 32) {
     const double* pw = S.lm + 3 * (size_t)o_lm[o];
-    double r[2], J[34];
-    dt_reproj_point<JAC>(K, fc, v3{pw[0], pw[1], pw[2]}, o_uv + 2 * (size_t)o, o_vel + 2 * (size_t)o, inv_std, r, J);
+    double R[36];
+    dt_reproj_point<JAC>(K, fc, v3{pw[0], pw[1], pw[2]}, o_uv + 2 * (size_t)o, o_vel + 2 * (size_t)o, inv_std, R, R + 2);
     double* out = rec + 36 * (size_t)o;
-    out[0] = r[0]; out[1] = r[1];
     if (JAC) {
 #pragma unroll
-      for (int k = 0; k < 34; ++k) out[2 + k] = J[k];
+      for (int k = 0; k < 9; ++k) st256(out + 4 * k, R + 4 * k);
+    } else {
+      out[0] = R[0]; out[1] = R[1];
     }
-    sq += r[0] * r[0] + r[1] * r[1];
+    sq += R[0] * R[0] + R[1] * R[1];
   }
   sq = warp_sum(sq);
   if (lane == 0) f_sq[f] = sq;
@@ -214,32 +227,49 @@ __global__ void __launch_bounds__(128) k_dt_direct_frame(BandLayout H0, int nF, 
                                                          const double* __restrict__ f_w, const double* __restrict__ rec, GAct ga, int any_global,
                                                          double* __restrict__ grad, double* __restrict__ cp_frame) {
   const int f = blockIdx.x, e = threadIdx.x;
-  int ci, cj = -1, kind;   // kind 0: H entry (ci, cj) ; 1: gradient of column ci
+  constexpr int kTile = 64;
+  __shared__ double tile[kTile * 36];
+  int ci = 0, cj = -1, kind = 0;   // kind 0: H entry (ci, cj) ; 1: gradient of column ci
+  bool live = true;
   if (e < 21) { int i = 0; while ((i + 1) * (i + 2) / 2 <= e) ++i; ci = i; cj = e - i * (i + 1) / 2; kind = 0; }
   else if (e < 69) { ci = 6 + (e - 21) % 8; cj = (e - 21) / 8; kind = 0; }
   else if (e < 75) { ci = e - 69; kind = 1; }
   else if (e < 83) { ci = 6 + (e - 75); kind = 1; }
   else if (e < 119) { const int q = e - 83; int i = 0; while ((i + 1) * (i + 2) / 2 <= q) ++i; ci = 6 + i; cj = 6 + q - i * (i + 1) / 2; kind = 0; }
-  else return;
+  else live = false;
   const bool glob = ci >= 6;
-  if (glob && (!any_global || !ga.a[ci - 6] || (cj >= 6 && !ga.a[cj - 6]))) {
+  if (live && glob && (!any_global || !ga.a[ci - 6] || (cj >= 6 && !ga.a[cj - 6]))) {
     if (e >= 83 && any_global) cp_frame[(size_t)f * kCpFrame + (e - 83)] = 0.0;
     if (e >= 75 && e < 83 && any_global) cp_frame[(size_t)f * kCpFrame + 36 + (e - 75)] = 0.0;
-    return;
+    live = false;
   }
   double v0 = 0.0, v1 = 0.0;
   const int o0 = f_obs_begin[f], o1 = f_obs_begin[f + 1];
-  if (kind == 0) {
-    int o = o0;
-    for (; o + 1 < o1; o += 2) {
-      const double* R = rec + 36 * (size_t)o;
-      v0 += R[2 + ci] * R[2 + cj] + R[19 + ci] * R[19 + cj];
-      v1 += R[38 + ci] * R[38 + cj] + R[55 + ci] * R[55 + cj];
+  for (int t0 = o0; t0 < o1; t0 += kTile) {
+    const int nt = min(kTile, o1 - t0);
+    __syncthreads();
+    // the tile's records, copied by the whole block with 256-bit accesses (contiguous in memory)
+    for (int q = threadIdx.x; q < nt * 9; q += 128) {
+      double v[4];
+      ld256c(rec + 36 * (size_t)t0 + 4 * q, v);
+      tile[4 * q] = v[0]; tile[4 * q + 1] = v[1]; tile[4 * q + 2] = v[2]; tile[4 * q + 3] = v[3];
     }
-    if (o < o1) { const double* R = rec + 36 * (size_t)o; v0 += R[2 + ci] * R[2 + cj] + R[19 + ci] * R[19 + cj]; }
-  } else {
-    for (int o = o0; o < o1; ++o) { const double* R = rec + 36 * (size_t)o; v0 += R[2 + ci] * R[0] + R[19 + ci] * R[1]; }
+    __syncthreads();
+    if (live) {
+      if (kind == 0) {
+        int o = 0;
+        for (; o + 1 < nt; o += 2) {
+          const double* R = tile + 36 * o;
+          v0 += R[2 + ci] * R[2 + cj] + R[19 + ci] * R[19 + cj];
+          v1 += R[38 + ci] * R[38 + cj] + R[55 + ci] * R[55 + cj];
+        }
+        if (o < nt) { const double* R = tile + 36 * o; v0 += R[2 + ci] * R[2 + cj] + R[19 + ci] * R[19 + cj]; }
+      } else {
+        for (int o = 0; o < nt; ++o) { const double* R = tile + 36 * o; v0 += R[2 + ci] * R[0] + R[19 + ci] * R[1]; }
+      }
+    }
   }
+  if (!live) return;
   const double w2 = f_w[f] * f_w[f];
   const double v = (v0 + v1) * w2;
   const int base = 15 * f_state[f];
@@ -420,18 +450,21 @@ __global__ void __launch_bounds__(128) k_dt_schur_prepare(int L, double radius, 
   for (int e = e0 + lane; e < e1; e += 32) {
     const int o = lm_obs[e];
     const double w = f_w[o_frame[o]], w2 = w * w;
-    const double* R = rec + 36 * (size_t)o;
+    double R[36];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) ld256c(rec + 36 * (size_t)o + 4 * k, R + 4 * k);
     const double a0 = R[16], a1 = R[17], a2 = R[18], b0 = R[33], b1 = R[34], b2 = R[35];
-    double* W = Wp + 18 * (size_t)o; double* Y = Yp + 18 * (size_t)o;
+    double Wl[kWS], Yl[kWS];
+    Wl[18] = Wl[19] = Yl[18] = Yl[19] = 0.0;
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
       const double ja = w2 * R[2 + k], jb = w2 * R[19 + k];
       const double x = ja * a0 + jb * b0, y = ja * a1 + jb * b1, z = ja * a2 + jb * b2;
-      W[3 * k] = x; W[3 * k + 1] = y; W[3 * k + 2] = z;
-      double yy[3];
-      sym3_mul(Vinv, x, y, z, yy);
-      Y[3 * k] = yy[0]; Y[3 * k + 1] = yy[1]; Y[3 * k + 2] = yy[2];
+      Wl[3 * k] = x; Wl[3 * k + 1] = y; Wl[3 * k + 2] = z;
+      sym3_mul(Vinv, x, y, z, Yl + 3 * k);
     }
+#pragma unroll
+    for (int k = 0; k < 5; ++k) { st256(Wp + kWS * (size_t)o + 4 * k, Wl + 4 * k); st256(Yp + kWS * (size_t)o + 4 * k, Yl + 4 * k); }
     if (any_global) {
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
@@ -470,10 +503,9 @@ __global__ void __launch_bounds__(128) k_dt_schur_gather(BandLayout B, int nKeys
   for (int k = 0; k < 36; ++k) acc[k] = 0.0;
   for (int64_t q = b0 + lane; q < b1; q += 32) {
     const int2 pr = pairs[q];
-    const double* Y = Yp + 18 * (size_t)pr.x; const double* W = Wp + 18 * (size_t)pr.y;
-    double w[18];
+    double w[kWS], Y[kWS];
 #pragma unroll
-    for (int k = 0; k < 18; ++k) w[k] = W[k];
+    for (int k = 0; k < 5; ++k) { ld256c(Yp + kWS * (size_t)pr.x + 4 * k, Y + 4 * k); ld256c(Wp + kWS * (size_t)pr.y + 4 * k, w + 4 * k); }
 #pragma unroll
     for (int a = 0; a < 6; ++a) {
       const double y0 = Y[3 * a], y1 = Y[3 * a + 1], y2 = Y[3 * a + 2];
@@ -494,29 +526,42 @@ __global__ void __launch_bounds__(128) k_dt_schur_gather(BandLayout B, int nKeys
     if (!(d == 0 && b > a)) atomicAdd(B.band + band_addr(B, bi + a, bj + b), mine2);
   }
 }
-// one block per measurement frame, one thread per output entry: Schur part of pose x global (48) and of the right-hand side (6)
-__global__ void __launch_bounds__(64) k_dt_schur_frame(BandLayout B, int nF, const int32_t* __restrict__ f_state, const int32_t* __restrict__ f_obs_begin,
-                                                       const int32_t* __restrict__ o_lm, const double* __restrict__ Wp, const double* __restrict__ Yp,
-                                                       const double* __restrict__ WgS, const double* __restrict__ Vg, GAct ga, int any_global, double* __restrict__ rhs_acc) {
-  const int f = blockIdx.x, e = threadIdx.x;
-  if (e >= 54) return;
-  const int base = 15 * f_state[f];
-  double v = 0.0;
-  if (e < 48) {
-    const int a = e % 6, b = e / 6;
-    if (!any_global || !ga.a[b]) return;
-    for (int o = f_obs_begin[f]; o < f_obs_begin[f + 1]; ++o) {
-      const double* Y = Yp + 18 * (size_t)o + 3 * a; const double* G = WgS + 24 * (size_t)o_lm[o] + 3 * b;
-      v -= Y[0] * G[0] + Y[1] * G[1] + Y[2] * G[2];
+// one block per measurement frame: Schur part of pose x global (48) and of the right-hand side (6).  Threads take the frame's points
+// round-robin and keep the 54 sums in registers; lanes are combined by a shuffle tree, warps in warp order (fixed order).
+__global__ void __launch_bounds__(128) k_dt_schur_frame(BandLayout B, int nF, const int32_t* __restrict__ f_state, const int32_t* __restrict__ f_obs_begin,
+                                                        const int32_t* __restrict__ o_lm, const double* __restrict__ Wp, const double* __restrict__ Yp,
+                                                        const double* __restrict__ WgS, const double* __restrict__ Vg, GAct ga, int any_global, double* __restrict__ rhs_acc) {
+  __shared__ double sh[4][54];
+  const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double acc[54];
+#pragma unroll
+  for (int k = 0; k < 54; ++k) acc[k] = 0.0;
+  for (int o = f_obs_begin[f] + tid; o < f_obs_begin[f + 1]; o += 128) {
+    double W[kWS], Y[kWS];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) { ld256c(Wp + kWS * (size_t)o + 4 * k, W + 4 * k); ld256c(Yp + kWS * (size_t)o + 4 * k, Y + 4 * k); }
+    const int l = o_lm[o];
+    const double g0 = Vg[3 * (size_t)l], g1 = Vg[3 * (size_t)l + 1], g2 = Vg[3 * (size_t)l + 2];
+#pragma unroll
+    for (int a = 0; a < 6; ++a) acc[48 + a] -= W[3 * a] * g0 + W[3 * a + 1] * g1 + W[3 * a + 2] * g2;
+    if (any_global) {
+      double G[24];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) ld256c(WgS + 24 * (size_t)l + 4 * k, G + 4 * k);
+#pragma unroll
+      for (int b = 0; b < 8; ++b)
+#pragma unroll
+        for (int a = 0; a < 6; ++a) acc[6 * b + a] -= Y[3 * a] * G[3 * b] + Y[3 * a + 1] * G[3 * b + 1] + Y[3 * a + 2] * G[3 * b + 2];
     }
-    atomicAdd(B.border + (size_t)b * B.n_pad + base + a, v);
-  } else {
-    const int a = e - 48;
-    for (int o = f_obs_begin[f]; o < f_obs_begin[f + 1]; ++o) {
-      const double* W = Wp + 18 * (size_t)o + 3 * a; const double* g = Vg + 3 * (size_t)o_lm[o];
-      v -= W[0] * g[0] + W[1] * g[1] + W[2] * g[2];
-    }
-    atomicAdd(rhs_acc + base + a, v);
+  }
+#pragma unroll
+  for (int k = 0; k < 54; ++k) { const double v = warp_sum(acc[k]); if (lane == 0) sh[warp][k] = v; }
+  __syncthreads();
+  if (tid < 54) {
+    const double v = ((sh[0][tid] + sh[1][tid]) + sh[2][tid]) + sh[3][tid];
+    const int base = 15 * f_state[f];
+    if (tid < 48) { const int a = tid % 6, b = tid / 6; if (any_global && ga.a[b]) atomicAdd(B.border + (size_t)b * B.n_pad + base + a, v); }
+    else atomicAdd(rhs_acc + base + (tid - 48), v);
   }
 }
 // damping, unit rows for the padding / inactive unknowns, right-hand side
@@ -561,7 +606,7 @@ __global__ void k_dt_backsub(int L, const int32_t* __restrict__ lm_begin, const 
   for (int e = lm_begin[l]; e < lm_begin[l + 1]; ++e) {
     const int o = lm_obs[e];
     const double* d = delta + 15 * (size_t)f_state[o_frame[o]];
-    const double* W = Wp + 18 * (size_t)o;
+    const double* W = Wp + kWS * (size_t)o;
 #pragma unroll
     for (int a = 0; a < 6; ++a) { s[0] += W[3 * a] * d[a]; s[1] += W[3 * a + 1] * d[a]; s[2] += W[3 * a + 2] * d[a]; }
   }
@@ -647,10 +692,22 @@ __global__ void __launch_bounds__(256) k_dt_step(int mode, int F, int L, int n_p
   model = warp_sum(model); step2 = warp_sum(step2); xn2 = warp_sum(xn2);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) gmax = fmax(gmax, __shfl_xor_sync(0xffffffffu, gmax, o));
-  if ((threadIdx.x & 31) == 0) {
-    if (mode == 0) { if (model != 0.0) atomicAdd(scal + DSC_MODEL, 0.5 * model); if (step2 != 0.0) atomicAdd(scal + DSC_STEP2, step2); }
-    else { if (xn2 != 0.0) atomicAdd(scal + DSC_XNORM2, xn2); if (gmax > 0.0) atomic_max_nonneg(scal + DSC_GMAX, gmax); }
+  if ((threadIdx.x & 31) == 0) {   // per-warp partials; k_dt_scal_reduce sums them in warp order
+    double* o = scal + 4 * (size_t)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    o[0] = 0.5 * model; o[1] = step2; o[2] = xn2; o[3] = gmax;
   }
+}
+__global__ void __launch_bounds__(256) k_dt_scal_reduce(int nw, const double* __restrict__ part, double* __restrict__ scal) {
+  __shared__ double sh[4][256];
+  double a[4] = {0, 0, 0, 0};
+  for (int i = threadIdx.x; i < nw; i += 256) { a[0] += part[4 * (size_t)i]; a[1] += part[4 * (size_t)i + 1]; a[2] += part[4 * (size_t)i + 2]; a[3] = fmax(a[3], part[4 * (size_t)i + 3]); }
+  for (int k = 0; k < 4; ++k) sh[k][threadIdx.x] = a[k];
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) { for (int k = 0; k < 3; ++k) sh[k][threadIdx.x] += sh[k][threadIdx.x + o]; sh[3][threadIdx.x] = fmax(sh[3][threadIdx.x], sh[3][threadIdx.x + o]); }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { scal[DSC_MODEL] = sh[0][0]; scal[DSC_STEP2] = sh[1][0]; scal[DSC_XNORM2] = sh[2][0]; scal[DSC_GMAX] = sh[3][0]; }
 }
 
 // unit-noise error norms for evaluate*Errors
@@ -844,9 +901,9 @@ int dt_structure(ctba_dt_problem* p) {
   DT_CUDA(p, p->f_w.resize(nFm)); DT_CUDA(p, p->grad.resize(nu)); DT_CUDA(p, p->diag.resize(nu)); DT_CUDA(p, p->jscale.resize(nu)); DT_CUDA(p, p->dvec.resize(nu));
   DT_CUDA(p, p->rhs_acc.resize(nu));
   DT_CUDA(p, p->V0.resize(6 * L)); DT_CUDA(p, p->gl.resize(3 * L)); DT_CUDA(p, p->jscale_lm.resize(3 * L)); DT_CUDA(p, p->Vi.resize(6 * L)); DT_CUDA(p, p->WgS.resize(24 * L));
-  DT_CUDA(p, p->Vg.resize(3 * L)); DT_CUDA(p, p->Yp.resize(18 * M)); DT_CUDA(p, p->cp_frame.resize((size_t)kCpFrame * nFm)); DT_CUDA(p, p->cp_lm.resize((size_t)kCpFrame * L));
+  DT_CUDA(p, p->Vg.resize(3 * L)); DT_CUDA(p, p->Yp.resize((size_t)kWS * M)); DT_CUDA(p, p->cp_frame.resize((size_t)kCpFrame * nFm)); DT_CUDA(p, p->cp_lm.resize((size_t)kCpFrame * L));
   DT_CUDA(p, p->cp_gp.resize((size_t)kCpGp * F));
-  DT_CUDA(p, p->Wp.resize(18 * M)); DT_CUDA(p, p->delta_lm.resize(3 * L)); DT_CUDA(p, p->scal.resize(DSC_COUNT));
+  DT_CUDA(p, p->Wp.resize((size_t)kWS * M)); DT_CUDA(p, p->delta_lm.resize(3 * L)); DT_CUDA(p, p->scal.resize(DSC_COUNT));
   DT_CUDA(p, p->cand.pose.resize(7 * F)); DT_CUDA(p, p->cand.sb.resize(9 * F)); DT_CUDA(p, p->cand.lm.resize(3 * L)); DT_CUDA(p, p->cand.glb.resize(DG_SIZE));
   if (p->WgS.p) DT_CUDA(p, cudaMemsetAsync(p->WgS.p, 0, 24 * L * 8, st));
   // band solver context
@@ -917,7 +974,7 @@ int dt_assemble(ctba_dt_problem* p, DtEval& ev, double radius) {
                                                                   any_global, p->Vi.p, p->Vg.p, p->WgS.p, p->Wp.p, p->Yp.p, p->cp_lm.p, sd->flag.p + 2);
     const size_t nKeys = (size_t)F * p->T1;
     k_dt_schur_gather<<<cdiv(nKeys * 32, 128), 128, 0, st>>>(B, (int)nKeys, p->T1, p->d_key_begin.p, p->d_pairs.p, p->Wp.p, p->Yp.p);
-    k_dt_schur_frame<<<nF, 64, 0, st>>>(B, nF, p->d_f_state.p, p->d_f_obs_begin.p, p->d_o_lm.p, p->Wp.p, p->Yp.p, p->WgS.p, p->Vg.p, ga, any_global, p->rhs_acc.p);
+    k_dt_schur_frame<<<nF, 128, 0, st>>>(B, nF, p->d_f_state.p, p->d_f_obs_begin.p, p->d_o_lm.p, p->Wp.p, p->Yp.p, p->WgS.p, p->Vg.p, ga, any_global, p->rhs_acc.p);
     p->launches += 3;
     if (any_global) { k_dt_corner_reduce<<<90, 256, 0, st>>>(1, B, L, p->cp_lm.p, 0, nullptr, p->rhs_acc.p); ++p->launches; }
   }
@@ -930,10 +987,12 @@ int dt_scalars(ctba_dt_problem* p, int mode, const DtStateP& S, const DtStateP& 
   cudaStream_t st = p->stream;
   SolverData* sd = p->ctx->solver;
   const int F = (int)p->F(), L = p->Lm;
-  DT_CUDA(p, cudaMemsetAsync(p->scal.p, 0, DSC_COUNT * 8, st));
-  k_dt_step<<<cdiv((size_t)F + L + 1, 256), 256, 0, st>>>(mode, F, L, p->n_pad, p->d_sb_active.p, p->d_lm_active.p, dt_gact(p), S, C, sd->delta.p, p->delta_lm.p, p->grad.p, p->gl.p,
-                                                          p->dvec.p, p->V0.p, p->jscale_lm.p, radius, p->scal.p);
-  ++p->launches;
+  const int nblk = cdiv((size_t)F + L + 1, 256);
+  DT_CUDA(p, p->scal_part.resize((size_t)nblk * 8 * 4));
+  k_dt_step<<<nblk, 256, 0, st>>>(mode, F, L, p->n_pad, p->d_sb_active.p, p->d_lm_active.p, dt_gact(p), S, C, sd->delta.p, p->delta_lm.p, p->grad.p, p->gl.p,
+                                  p->dvec.p, p->V0.p, p->jscale_lm.p, radius, p->scal_part.p);
+  k_dt_scal_reduce<<<1, 256, 0, st>>>(nblk * 8, p->scal_part.p, p->scal.p);
+  p->launches += 2;
   DT_CUDA(p, cudaMemcpyAsync(host_sc, p->scal.p, DSC_COUNT * 8, cudaMemcpyDeviceToHost, st));
   DT_CUDA(p, cudaStreamSynchronize(st));
   return CTBA_OK;
