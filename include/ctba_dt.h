@@ -73,6 +73,11 @@ int ctba_dt_add_imu(ctba_dt_problem* p, int frame0, int n, const double* t_s, co
 /* addGlobalSensMeasurement for n measurements: frame0 = GlobalPosMeasurement::closest_frame_id                            estimator.h:461-519 */
 int ctba_dt_add_gp(ctba_dt_problem* p, int n, const double* t_s, const double* pos /*3n*/, const int32_t* frame0, double sigma_m);
 
+/* computeValidReprojections(frames): the grid-based choice of the reprojections that enter the problem, frame k judged at state k's
+ * CURRENT pose (30 cm / behind-the-camera test).  Same arrays as ctba_compute_valid_reprojections.  Host pass, sequential over frames.   estimator.h:167-291 */
+int ctba_dt_compute_valid_reprojections(ctba_dt_problem* p, int F, const int32_t* pt_begin, const double* uv /*2M*/, const int32_t* lm_index /*M*/,
+                                        int width, int height, int cell_size_px, uint8_t* valid /*M*/, int32_t* n_valid /*F*/);
+
 /* counts5 = frames with points, valid reprojections, IMU factors, global positions, unknowns (tangent size of the free blocks) */
 int ctba_dt_counts(ctba_dt_problem* p, int64_t* counts5);
 

@@ -431,6 +431,27 @@ int orc_dt_solve(void* h, int max_iters, int num_threads, double* summary, doubl
   }
   return 0;
 }
+// DiscreteTimeEstimator::computeValidReprojections + computeFeatureVelocity (select.h), frames as CSR; vel (2 per point) may be NULL
+int orc_dt_compute_valid_reprojections(void* h, int F, const double* ts, const int32_t* pt_begin, const double* uv, const int32_t* lm_index, int width, int height,
+                                       int cell_size_px, uint8_t* valid, int32_t* n_valid, double* vel) {
+  auto* p = (DtProblem*)h;
+  std::vector<orc_select::Frame> frames(F);
+  for (int f = 0; f < F; ++f) {
+    frames[f].setGrid(width, height, cell_size_px);
+    for (int q = pt_begin[f]; q < pt_begin[f + 1]; ++q) frames[f].addPoint2D(uv[2 * q], uv[2 * q + 1], (uint64_t)lm_index[q]);
+  }
+  orc_select::computeValidReprojectionsDt(*p, frames);
+  if (vel) orc_select::computeFeatureVelocity(frames, std::vector<double>(ts, ts + F));
+  for (int f = 0; f < F; ++f) {
+    n_valid[f] = frames[f].n_valid_reprojections;
+    for (int q = pt_begin[f]; q < pt_begin[f + 1]; ++q) {
+      const auto& pt = frames[f].points2D[q - pt_begin[f]];
+      valid[q] = pt.is_reproj_valid ? 1 : 0;
+      if (vel) { vel[2 * q] = pt.vel_u; vel[2 * q + 1] = pt.vel_v; }
+    }
+  }
+  return 0;
+}
 // Sparse LM on the discrete-time problem (sparse_lm.h): band = 15 scalars per state [pose tangent 6 | speed-and-bias 9] in time order.
 int orc_dt_solve_sparse(void* h, int max_iters, int num_threads, int no_termination, double* summary, double* iter_log, int iter_cap, double* timings) {
   auto* p = (DtProblem*)h; p->build();

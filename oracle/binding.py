@@ -377,6 +377,20 @@ class OracleDiscrete:
         return dict(termination_type=int(s[0]), initial_cost=s[1], final_cost=s[2], num_successful_steps=int(s[3]), num_unsuccessful_steps=int(s[4]),
                     iterations=log[:min(n, cap)].copy())
 
+    def computeValidReprojections(self, pt_begin, uv, lm_index, width, height, cell_size_px, cam_ts=None):
+        """computeValidReprojections (+ computeFeatureVelocity when cam_ts is given: returns (valid, n_valid, velocity))"""
+        pb = np.ascontiguousarray(pt_begin, dtype=np.int32); u = _d(uv); li = np.ascontiguousarray(lm_index, dtype=np.int32)
+        F = pb.size - 1
+        valid = np.zeros(max(li.size, 1), dtype=np.uint8); nv = np.zeros(max(F, 1), dtype=np.int32)
+        ts = _d(cam_ts) if cam_ts is not None else np.zeros(max(F, 1))
+        vel = np.zeros((max(li.size, 1), 2)) if cam_ts is not None else None
+        self.L.orc_dt_compute_valid_reprojections(self.h, int(F), ts.ctypes.data_as(C.c_void_p), pb.ctypes.data_as(C.c_void_p), u.ctypes.data_as(C.c_void_p),
+                                                  li.ctypes.data_as(C.c_void_p), int(width), int(height), int(cell_size_px), valid.ctypes.data_as(C.c_void_p),
+                                                  nv.ctypes.data_as(C.c_void_p), vel.ctypes.data_as(C.c_void_p) if vel is not None else None)
+        if vel is None:
+            return valid[:li.size].astype(bool), nv[:F]
+        return valid[:li.size].astype(bool), nv[:F], vel[:li.size]
+
     def optimizeSparse(self, max_num_iterations, num_threads=1, no_termination=False):
         """sparse LM (oracle/sparse_lm.h) on the discrete-time problem: what bench.py's CPU legs time at BASELINE sizes"""
         s = np.zeros(6); cap = max_num_iterations + 2; log = np.zeros((cap, 7)); tm = np.zeros(12)

@@ -9,6 +9,7 @@
 #include <cstdint>
 #include <vector>
 #include "problem.h"
+#include "dt_problem.h"
 
 namespace orc_select {
 using namespace oracle;
@@ -17,6 +18,7 @@ struct Point2D {                      // camera.h:96-111
   double u, v;
   uint64_t point3d_id;
   bool is_reproj_valid = false;
+  double vel_u = 0.0, vel_v = 0.0;    // Point2D::velocity
 };
 
 struct Frame {                        // camera.h:114-184
@@ -112,6 +114,80 @@ inline void computeValidReprojections(SplineProblem& sp, std::vector<Frame>& fra
     for (size_t cell_id = 0; cell_id < n_cells; cell_id++) grid_k_min_1[cell_id].clear();
     for (size_t cell_id = 0; cell_id < n_cells; cell_id++)
       for (size_t point_id = 0; point_id < grid_k[cell_id].size(); point_id++) grid_k_min_1[cell_id].push_back(grid_k[cell_id][point_id]);
+  }
+}
+
+// DiscreteTimeEstimator::computeValidReprojections   /root/reference/include/discrete_time_estimator/estimator.h:179-291
+// frame k is judged at state k's pose; no frame is skipped (the reference asserts that frame and state times agree)
+inline void computeValidReprojectionsDt(DtProblem& dp, std::vector<Frame>& frames) {
+  if (frames.empty()) return;
+  const int cell_size_px_ = frames[0].cell_size_px, n_grid_columns_ = frames[0].n_grid_columns, n_grid_rows_ = frames[0].n_grid_rows;   // initializeGrid :167-172
+  const size_t n_cells = (size_t)n_grid_columns_ * n_grid_rows_;
+  std::vector<std::vector<Point2D*>> grid_k_min_1(n_cells);
+  int k = 0;
+  for (auto frame = frames.begin(); frame != frames.end(); ++frame) {
+    std::vector<std::vector<Point2D*>> grid_k(n_cells);
+    for (size_t cell_id = 0; cell_id < n_cells; cell_id++) {
+      for (size_t point_id = 0; point_id < grid_k_min_1[cell_id].size(); point_id++) {
+        const uint64_t point3D_id = grid_k_min_1[cell_id][point_id]->point3d_id;
+        auto it = std::find(frame->points3D_ids.begin(), frame->points3D_ids.end(), point3D_id);
+        if (it != frame->points3D_ids.end()) {
+          const size_t point3D_idx = it - frame->points3D_ids.begin();
+          Point2D* p = &frame->points2D[point3D_idx];
+          p->is_reproj_valid = true;
+          int idx_clmn = p->u / cell_size_px_;
+          int idx_row = p->v / cell_size_px_;
+          grid_k[idx_clmn + idx_row * n_grid_columns_].push_back(p);
+        }
+      }
+    }
+    for (size_t cell_id = 0; cell_id < n_cells; cell_id++) {
+      if (grid_k[cell_id].size() > 0) continue;
+      if (frame->grid[cell_id].size() == 0) continue;
+      Point2D* p = &frame->points2D[frame->grid[cell_id][0]];
+      p->is_reproj_valid = true;
+      grid_k[cell_id].push_back(p);
+    }
+    // :243-250
+    const double* T = &dp.pose[7 * (size_t)k];
+    const SO3<double> R_wb{T[0], T[1], T[2], T[3]};
+    const SO3<double> R_bc{dp.camera.cam.q_bc[0], dp.camera.cam.q_bc[1], dp.camera.cam.q_bc[2], dp.camera.cam.q_bc[3]};
+    const SO3<double> R_wc = R_wb * R_bc;
+    const double scale = dp.scale + dp.scale_corr;
+    const V3<double> rb = R_wb.act(V3<double>{dp.camera.cam.p_bc[0], dp.camera.cam.p_bc[1], dp.camera.cam.p_bc[2]});
+    const V3<double> p_wc{scale * rb.x + T[4], scale * rb.y + T[5], scale * rb.z + T[6]};
+    const SO3<double> R_cw = R_wc.inverse();
+    size_t n_reprojs = 0;
+    for (size_t cell_id = 0; cell_id < n_cells; cell_id++) {
+      for (size_t point_id = 0; point_id < grid_k[cell_id].size(); point_id++) {
+        const uint64_t l = grid_k[cell_id][point_id]->point3d_id;
+        const V3<double> d{dp.lm[3 * l] - p_wc.x, dp.lm[3 * l + 1] - p_wc.y, dp.lm[3 * l + 2] - p_wc.z};
+        const V3<double> p_CLi = R_cw.act(d);
+        const double nrm = std::sqrt(p_CLi.x * p_CLi.x + p_CLi.y * p_CLi.y + p_CLi.z * p_CLi.z);
+        if ((nrm < 0.3) || (p_CLi.z < 0.0)) grid_k[cell_id][point_id]->is_reproj_valid = false;
+        else n_reprojs += 1;
+      }
+    }
+    frame->n_valid_reprojections = (int)n_reprojs;
+    for (size_t cell_id = 0; cell_id < n_cells; cell_id++) grid_k_min_1[cell_id].clear();
+    for (size_t cell_id = 0; cell_id < n_cells; cell_id++)
+      for (size_t point_id = 0; point_id < grid_k[cell_id].size(); point_id++) grid_k_min_1[cell_id].push_back(grid_k[cell_id][point_id]);
+    k++;
+  }
+}
+// DiscreteTimeEstimator::computeFeatureVelocity   estimator.h:293-325 (frame times in seconds)
+inline void computeFeatureVelocity(std::vector<Frame>& frames, const std::vector<double>& ts) {
+  for (size_t f = 0; f + 1 < frames.size(); ++f) {
+    Frame& frame = frames[f]; Frame& next = frames[f + 1];
+    const double dt = ts[f + 1] - ts[f];
+    for (auto& point2D : frame.points2D) {
+      if (!point2D.is_reproj_valid) continue;
+      auto it = std::find(next.points3D_ids.begin(), next.points3D_ids.end(), point2D.point3d_id);
+      if (it != next.points3D_ids.end()) {
+        const Point2D& n2 = next.points2D[it - next.points3D_ids.begin()];
+        point2D.vel_u = (n2.u - point2D.u) / dt; point2D.vel_v = (n2.v - point2D.v) / dt;
+      }
+    }
   }
 }
 

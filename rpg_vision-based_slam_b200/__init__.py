@@ -38,7 +38,7 @@ EXPORTS_DT = [
     "ctba_dt_create", "ctba_dt_destroy", "ctba_dt_last_error", "ctba_dt_set_stream", "ctba_dt_invalidate_device", "ctba_dt_set_camera", "ctba_dt_set_imu", "ctba_dt_initialize_states",
     "ctba_dt_initialize_linear_velocity", "ctba_dt_set_speed_and_bias", "ctba_dt_set_states", "ctba_dt_get_states", "ctba_dt_set_landmarks",
     "ctba_dt_get_landmarks", "ctba_dt_set_globals", "ctba_dt_set_corrections", "ctba_dt_get_globals", "ctba_dt_set_flags", "ctba_dt_add_frames",
-    "ctba_dt_add_imu", "ctba_dt_add_gp", "ctba_dt_counts", "ctba_dt_evaluate", "ctba_dt_cost", "ctba_dt_evaluate_errors", "ctba_dt_imu_redo_count",
+    "ctba_dt_add_imu", "ctba_dt_add_gp", "ctba_dt_compute_valid_reprojections", "ctba_dt_counts", "ctba_dt_evaluate", "ctba_dt_cost", "ctba_dt_evaluate_errors", "ctba_dt_imu_redo_count",
     "ctba_dt_solve", "ctba_dt_set_option", "ctba_dt_get_stat",
 ]
 
@@ -520,6 +520,13 @@ class DiscreteTimeEstimator:
     def addGlobalSensMeasurements(self, t, pos, frame0, sigma):
         t, x = _d(t), _d(pos); f0 = np.ascontiguousarray(frame0, dtype=np.int32)
         return self._chk(self.L.ctba_dt_add_gp(self.h, len(t), _p(t), _p(x), _p(f0), C.c_double(sigma)))
+
+    def computeValidReprojections(self, pt_begin, uv, lm_index, width, height, cell_size_px):
+        pb = np.ascontiguousarray(pt_begin, dtype=np.int32); u = _d(uv); li = np.ascontiguousarray(lm_index, dtype=np.int32)
+        F = pb.size - 1
+        valid = np.zeros(max(li.size, 1), dtype=np.uint8); nv = np.zeros(max(F, 1), dtype=np.int32)
+        self._chk(self.L.ctba_dt_compute_valid_reprojections(self.h, int(F), _p(pb), _p(u), _p(li), int(width), int(height), int(cell_size_px), _p(valid), _p(nv)))
+        return valid[:li.size].astype(bool), nv[:F]
 
     def counts(self):
         c = np.zeros(5, dtype=np.int64)

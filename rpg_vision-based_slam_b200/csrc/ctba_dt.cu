@@ -23,6 +23,7 @@
 #include "../../include/ctba_dt.h"
 #include "ctba_dt_math.h"
 #include "ctba_solver.h"
+#include "ctba_select_core.h"
 
 using namespace ctba;
 
@@ -1326,6 +1327,24 @@ int ctba_dt_add_gp(ctba_dt_problem* p, int n, const double* t, const double* pos
   }
   p->meas_dirty = p->struct_dirty = true;
   return n;
+}
+int ctba_dt_compute_valid_reprojections(ctba_dt_problem* p, int F, const int32_t* pt_begin, const double* uv, const int32_t* lm_index, int width, int height,
+                                          int cell_size_px, uint8_t* valid, int32_t* n_valid) {
+  DT_CHECK(p);
+  if (F < 0 || !pt_begin || !valid || !n_valid || width <= 0 || height <= 0 || cell_size_px <= 1) { p->err = "compute_valid_reprojections: bad arguments"; return CTBA_E_ARG; }
+  if ((size_t)F > p->F()) { p->err = "compute_valid_reprojections: more frames than states (frame k belongs to state k, estimator.h:192-194)"; return CTBA_E_ARG; }
+  int rc = dt_download(p); if (rc) return rc;
+  const m3 R_bc = quat_matrix(quat{p->K.q_bc0[0], p->K.q_bc0[1], p->K.q_bc0[2], p->K.q_bc0[3]});
+  const v3 p_bc{p->K.p_bc0[0], p->K.p_bc0[1], p->K.p_bc0[2]};
+  const double scale = p->K.scale + p->glb[DG_SCALE];   // getScale(), estimator.h:744
+  auto pose = [&](int f, m3* R_wb, v3* p_wb) -> bool {   // frame k is judged at state k's pose (estimator.h:243-250)
+    const double* T = &p->pose[7 * (size_t)f];
+    *R_wb = quat_matrix(quat{T[0], T[1], T[2], T[3]});
+    *p_wb = v3{T[4], T[5], T[6]};
+    return true;
+  };
+  return select_valid_reprojections(F, pt_begin, uv, lm_index, (int64_t)p->lm.size() / 3, p->lm.data(), width, height, cell_size_px, R_bc, p_bc, scale, pose, valid, n_valid,
+                                    &p->err);
 }
 int ctba_dt_counts(ctba_dt_problem* p, int64_t* c) {
   DT_CHECK(p);

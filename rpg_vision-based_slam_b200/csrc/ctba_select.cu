@@ -9,6 +9,7 @@
 #include <cmath>
 #include <vector>
 #include "ctba_solver.h"
+#include "ctba_select_core.h"
 
 using namespace ctba;
 
@@ -98,78 +99,23 @@ int ctba_compute_valid_reprojections(ctba_problem* p, int F, const int64_t* t_ns
   if (F < 0 || !t_ns || !pt_begin || !valid || !n_valid || width <= 0 || height <= 0 || cell_size_px <= 1) { p->err = "compute_valid_reprojections: bad arguments"; return CTBA_E_ARG; }
   if (p->host_state_stale) { p->err = "compute_valid_reprojections: read the state back first (ctba_get_knots)"; return CTBA_E_STATE; }
   const int N = p->N;
-  const int64_t L = (int64_t)p->lm.size() / 3;
-  // Frame::setGrid  camera.h:172-184
-  const int ncol = width / cell_size_px + (width % cell_size_px > 0 ? 1 : 0);
-  const int nrow = height / cell_size_px + (height % cell_size_px > 0 ? 1 : 0);
-  const int ncell = ncol * nrow;
-  const int M = pt_begin[F];
-  for (int i = 0; i < M; ++i) valid[i] = 0;             // Point2D ctor: is_reproj_valid(false)
-  for (int f = 0; f < F; ++f) n_valid[f] = 0;
-  auto cell_of = [&](int q) -> int {
-    const int cx = (int)(uv[2 * (size_t)q] / cell_size_px), cy = (int)(uv[2 * (size_t)q + 1] / cell_size_px);   // :448-450, camera.h:163-165
-    if (cx < 0 || cx >= ncol || cy < 0 || cy >= nrow || uv[2 * (size_t)q] < 0 || uv[2 * (size_t)q + 1] < 0) return -1;
-    return cx + cy * ncol;
-  };
   SplineTables tb;
   fill_tables(N, &tb);
   const m3 R_bc = quat_matrix(quat{p->q_bc0[0], p->q_bc0[1], p->q_bc0[2], p->q_bc0[3]});
   const v3 p_bc{p->p_bc0[0], p->p_bc0[1], p->p_bc0[2]};
   const double scale = p->scale + p->glb[GLB_SCALE_CORR];   // getScale() :1881
-  std::vector<int32_t> stamp((size_t)std::max<int64_t>(L, 1), -1), where((size_t)std::max<int64_t>(L, 1), 0);
-  std::vector<int32_t> prev;                               // grid_{k-1}, cell-major
-  std::vector<std::vector<int32_t>> grid(ncell);
-  std::vector<int32_t> first(ncell);
-  for (int f = 0; f < F; ++f) {
+  // frame -> pose of the spline at its time; frames outside the spline are skipped (:418, :422)
+  auto pose = [&](int f, m3* R_wb, v3* p_wb) -> bool {
     const int64_t st_ns = t_ns[f] - p->start_t_ns;
-    if (st_ns < 0) continue;                               // :418
+    if (st_ns < 0) return false;
     const int64_t s = st_ns / p->dt_ns;
-    if ((size_t)(s + N) > p->numKnots()) continue;         // :422
+    if ((size_t)(s + N) > p->numKnots()) return false;
     const double u = double(st_ns % p->dt_ns) / double(p->dt_ns);
-    for (auto& g : grid) g.clear();
-    for (int c = 0; c < ncell; ++c) first[c] = -1;
-    for (int q = pt_begin[f]; q < pt_begin[f + 1]; ++q) {
-      const int l = lm_index[q];
-      if (l < 0 || l >= L) { p->err = "compute_valid_reprojections: Point 3D not found (bspline_so3r3.h:466)"; return CTBA_E_ARG; }
-      const int c = cell_of(q);
-      if (c < 0) { p->err = "compute_valid_reprojections: feature outside the image grid"; return CTBA_E_ARG; }
-      if (stamp[l] != f) { stamp[l] = f; where[l] = q; }   // std::find: first occurrence
-      if (first[c] < 0) first[c] = q;                      // Frame::grid[c][0]
-    }
-    // track the 2-D points of the previous grid (:427-456)
-    for (int32_t q0 : prev) {
-      const int l = lm_index[q0];
-      if (stamp[l] != f) continue;
-      const int q = where[l];
-      valid[q] = 1;
-      grid[cell_of(q)].push_back(q);
-    }
-    // one new point per free cell (:459-473)
-    for (int c = 0; c < ncell; ++c) {
-      if (!grid[c].empty() || first[c] < 0) continue;
-      valid[first[c]] = 1;
-      grid[c].push_back(first[c]);
-    }
-    // drop points closer than 30 cm to the camera or behind it, at the CURRENT pose (:477-502)
-    m3 R_wb; v3 p_wb;
-    if (N == 4) host_pose<4>(p, tb, s, u, &R_wb, &p_wb); else host_pose<6>(p, tb, s, u, &R_wb, &p_wb);
-    const m3 R_wc = mul(R_wb, R_bc);
-    const v3 p_wc = scale * mul(R_wb, p_bc) + p_wb;
-    const m3 R_cw = transpose(R_wc);
-    int n = 0;
-    for (int c = 0; c < ncell; ++c)
-      for (int32_t q : grid[c]) {
-        const int l = lm_index[q];
-        const v3 pl{p->lm[3 * (size_t)l], p->lm[3 * (size_t)l + 1], p->lm[3 * (size_t)l + 2]};
-        const v3 pc = mul(R_cw, pl - p_wc);
-        const double nn = std::sqrt(pc.x * pc.x + pc.y * pc.y + pc.z * pc.z);
-        if (nn < 0.3 || pc.z < 0.0) valid[q] = 0; else ++n;
-      }
-    n_valid[f] = n;
-    prev.clear();
-    for (int c = 0; c < ncell; ++c) for (int32_t q : grid[c]) prev.push_back(q);   // :505-517 (rejected points stay in the grid)
-  }
-  return CTBA_OK;
+    if (N == 4) host_pose<4>(p, tb, s, u, R_wb, p_wb); else host_pose<6>(p, tb, s, u, R_wb, p_wb);
+    return true;
+  };
+  return select_valid_reprojections(F, pt_begin, uv, lm_index, (int64_t)p->lm.size() / 3, p->lm.data(), width, height, cell_size_px, R_bc, p_bc, scale, pose, valid, n_valid,
+                                    &p->err);
 }
 
 int ctba_evaluate_errors(ctba_problem* p, int kind, double* errors) {
