@@ -134,3 +134,19 @@ def test_solve_is_bitwise_reproducible(oracle, pkg, scene):
     assert ia.shape[0] >= 4
     assert np.array_equal(ia, ib)
     assert np.array_equal(Pa, Pb) and np.array_equal(sa, sb) and np.array_equal(la, lb) and np.array_equal(ga, gb)
+
+
+def test_compute_valid_reprojections_vs_oracle(oracle, pkg, scene):
+    """DiscreteTimeEstimator::computeValidReprojections (estimator.h:179-291): flat-array product code against the oracle's restatement in the
+    reference's shape — bit-exact flags and counts."""
+    o, g, d = _pair(oracle, pkg, scene, duration_s=4.0, n_landmarks=300)
+    ob = d["obs_begin"]; uv = d["uv"]; li = d["lm_index"]
+    keep = (uv[:, 0] >= 0) & (uv[:, 0] < d["width"]) & (uv[:, 1] >= 0) & (uv[:, 1] < d["height"])
+    nb = np.zeros_like(ob); nb[1:] = np.cumsum([keep[ob[f]:ob[f + 1]].sum() for f in range(len(ob) - 1)])
+    uv = np.ascontiguousarray(uv[keep]); li = np.ascontiguousarray(li[keep])
+    for cell in (32, 80):
+        vo, no = o.computeValidReprojections(nb, uv, li, int(d["width"]), int(d["height"]), cell)
+        vg, ng = g.computeValidReprojections(nb, uv, li, int(d["width"]), int(d["height"]), cell)
+        assert 0 < vo.sum() < vo.size
+        assert (vo == vg).all() and (no == ng).all()
+    g.close()
