@@ -224,6 +224,29 @@ int ctba_comm_init_local(ctba_problem** handles, int world);
 int ctba_shard_plan(ctba_problem* p, int world, int rank, int64_t* plan, int32_t* lm_owner, int32_t* imu_owner, int32_t* gp_owner,
                     int32_t* bias_owner);
 
+/* ---- allocation-free entry point ----------------------------------------------------------------------------------------
+ * NO counterpart in the reference: added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  It calls no cudaMalloc / cudaFree / allocating library routine.
+ *
+ * Normal equations of the world-alignment problem (what one LM iteration of ctba_solve accumulates on a handle that holds alignment
+ * measurements: GlobalPositionSensorWithAlignmentCorrectionCostFunctor under CauchyLoss(cauchy_a), every knot constant) at the
+ * alignment state x12 = [t_s_gp_corr | scale_corr | R_w_g_corr x y z w | p_w_g_corr | p_bp], 11 tangent unknowns in the same order
+ * (rotation: right tangent):
+ *     d_sys78 = [ upper triangle of J^T J, row-major (66) | J^T r (11) | cost (1) ]      (DEVICE memory, written on `cuda_stream`)
+ * T_wg7 ([q x y z w | p]) and x12 are HOST arrays read before the call returns; d_knot_q (4 n_knots), d_knot_p (3 n_knots), d_t_ns (n),
+ * d_pos (3n) and d_sys78 are DEVICE pointers on `device`, owned by the caller.  Measurements before the spline start or beyond the last
+ * window are skipped like ctba_add_alignment_measurements does.  The call only enqueues two kernels on `cuda_stream` (no
+ * synchronisation): the caller synchronises before reading d_sys78.
+ * Scratch: per-CTA partial sums live in ONE file-scope static __device__ array of 296 x 78 doubles (184 704 bytes per GPU that loads the
+ * library, held until exit).  Limit: n <= CTBA_NOALLOC_MAX_MEASUREMENTS, larger n is CTBA_E_ARG with a message in `err` (optional
+ * buffer of err_len bytes).  Every call shares the array (it needs no clearing: a call reads only what it wrote), so calls that OVERLAP
+ * on the GPU — two streams, two host threads — race: serialise them. */
+#define CTBA_NOALLOC_MAX_MEASUREMENTS (1 << 20)
+int ctba_align_system_noalloc(int order, int64_t dt_ns, int64_t start_t_ns, int device, void* cuda_stream, double scale, double t_s_gp_s,
+                              const double* T_wg7, const double* x12, double cauchy_a, int n_knots, const double* d_knot_q,
+                              const double* d_knot_p, int n, const int64_t* d_t_ns, const double* d_pos, double noise, double* d_sys78,
+                              char* err, int err_len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -31,6 +31,7 @@ EXPORTS = [
     "ctba_relinearize_time_offsets", "ctba_bench_evaluate", "ctba_set_option", "ctba_get_stat", "ctba_invalidate_device", "ctba_transfer_bytes",
     "ctba_bench_reproj", "ctba_compute_valid_reprojections", "ctba_evaluate_errors", "ctba_sample", "ctba_comm_unique_id", "ctba_comm_init_nccl", "ctba_comm_init_local", "ctba_shard_plan",
     "ctba_set_world_alignment", "ctba_get_world_alignment", "ctba_add_alignment_measurements", "ctba_num_alignment_measurements",
+    "ctba_align_system_noalloc",   # allocation-free entry point (no reference counterpart; tests/test_zz_no_alloc.py binds it by hand)
 ]
 
 
