@@ -2,6 +2,7 @@
 // Problem-assembly semantics (timestamp -> spline window, skip rules, clamps) restate
 // /root/reference/include/spline/bspline_so3r3.h:355-369, 523-1046, 1807-1875 (cited per function in ctba.h).
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include "ctba_solver.h"
 
@@ -678,6 +679,9 @@ int ctba_set_option(ctba_problem* p, const char* name, double value) {
   if (!std::strcmp(name, "relinearize_mask")) { p->relinearize_mask = (int)value & 3; return CTBA_OK; }
   if (!std::strcmp(name, "band_partitions")) { p->band_partitions = (int)value; return CTBA_OK; }
   if (!std::strcmp(name, "schur_two_stage")) { p->schur_two_stage = value != 0.0; return CTBA_OK; }
+  if (!std::strcmp(name, "schur_mask")) { p->schur_sorted = value != 0.0; return CTBA_OK; }
+  if (!std::strcmp(name, "schur_threads")) { p->schur_threads = (int)value; return CTBA_OK; }
+  if (!std::strcmp(name, "schur_list_a")) { p->schur_list_a = value != 0.0; return CTBA_OK; }
   if (!std::strcmp(name, "schur_compact")) { p->schur_compact = value != 0.0; return CTBA_OK; }
   if (!std::strcmp(name, "band_nested")) { p->band_nested = value != 0.0; return CTBA_OK; }
   if (!std::strcmp(name, "band_graph")) { p->band_graph = value != 0.0; return CTBA_OK; }

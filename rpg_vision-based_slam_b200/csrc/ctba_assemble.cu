@@ -646,14 +646,20 @@ __global__ void __launch_bounds__(kFsThreads) k_frame_schur(int F, int T, const 
 // d = p_w - p_wb(f):   Y_a^T Z_b = [H_a^T ; -I] M [H_b | -I],  M = A_a Vi A_b  (3x3),  d_b = d_a + p_wb(f) - p_wb(f2)  (same landmark),
 // so a partner observation costs 48 B of gathered L2 traffic instead of the 144 B of its Z block, and the frame's own data is
 // 15 doubles per observation (A, d, Vi) in shared memory.
+// Al (optional): the same blocks in the order of the landmarks' observation lists (slot o_pos[o]), so that k_frame_schur_c can fetch a
+// partner's block from the list slot it already knows instead of through the slot's observation index (one dependent load less).
 __global__ void k_obs_a(int M, const int32_t* __restrict__ o_frame, const double* __restrict__ Jl, const double2* __restrict__ r,
-                        const double* __restrict__ f_w, double* __restrict__ Ao) {
+                        const double* __restrict__ f_w, double* __restrict__ Ao, const int32_t* __restrict__ o_pos, double* __restrict__ Al) {
   const int o = blockIdx.x * blockDim.x + threadIdx.x;
   if (o >= M) return;
   double A[6], b[3];
   obs_Ab(Jl, r, f_w, M, o, o_frame[o], A, b);
   double2* dst = reinterpret_cast<double2*>(Ao + 6 * (size_t)o);
   dst[0] = make_double2(A[0], A[1]); dst[1] = make_double2(A[2], A[3]); dst[2] = make_double2(A[4], A[5]);
+  if (Al) {
+    double2* dl = reinterpret_cast<double2*>(Al + 6 * (size_t)o_pos[o]);
+    dl[0] = make_double2(A[0], A[1]); dl[1] = make_double2(A[2], A[3]); dl[2] = make_double2(A[4], A[5]);
+  }
 }
 
 __device__ __forceinline__ void sym_mul_sym(const double S[6], const double B[6], double W[9]) {   // W = S * B, both symmetric (xx xy xz yy yz zz)
@@ -719,12 +725,13 @@ __device__ __forceinline__ void schur_pair_m(const double Mm[9], double dax, dou
 // end of the list (negative: the list has two observations in one frame)}, frame of the landmark's last observation.
 constexpr int kFcThreads = 128;
 constexpr int kFcRows = 14;
-template <int N>
+template <int N, bool LISTA>
 __global__ void __launch_bounds__(kFcThreads, 3) k_frame_schur_c(int F, int T, const FramePose<N>* __restrict__ fps, const double* __restrict__ lm,
                                                                  const int32_t* __restrict__ obs_begin, const int32_t* __restrict__ o_lm,
                                                                  const int32_t* __restrict__ o_pos, const int32_t* __restrict__ o_end,
                                                                  const int32_t* __restrict__ lm_obs, const int32_t* __restrict__ lm_frame,
-                                                                 const double* __restrict__ Ao, const double* __restrict__ Vi_all,
+                                                                 const double* __restrict__ Ao, const double* __restrict__ Al,
+                                                                 const double* __restrict__ Vi_all,
                                                                  const double* __restrict__ vig_all, const double* __restrict__ ViYg_all, bool any_g,
                                                                  int n_pad, double* __restrict__ Sp, double* __restrict__ Sb, double* __restrict__ rp) {
   __shared__ double red[kFcThreads / 32][48];
@@ -843,6 +850,7 @@ __global__ void __launch_bounds__(kFcThreads, 3) k_frame_schur_c(int F, int T, c
       };
       for (int i0 = lane; i0 < n; i0 += 64) {
         int bsel[2] = {-1, -1};
+        double Ab[2][6];
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
           const int i = i0 + 32 * u;
@@ -851,18 +859,28 @@ __global__ void __launch_bounds__(kFcThreads, 3) k_frame_schur_c(int F, int T, c
           if (pe.y < 0) { slow(i, pe.x, -pe.y); continue; }
           if (f2 > sLast[i]) continue;
           const int j = min(pe.x + df, pe.y - 1);
-          const int fj = lm_frame[j], bj = lm_obs[j];
-          if (fj == f2) bsel[u] = bj;              // strictly increasing frames: the only partner
-          else slow(i, pe.x + 1, j);               // a gap in the track: the partner, if any, sits before slot j
-        }
-        double Ab[2][6];
-#pragma unroll
-        for (int u = 0; u < 2; ++u)
-          if (bsel[u] >= 0) {
-            const double2* Ap = reinterpret_cast<const double2*>(Ao + 6 * (size_t)bsel[u]);
+          if (LISTA) {   // the block of list slot j travels together with the slot's frame index: ONE L2 round trip per partner
+            const int fj = lm_frame[j];
+            const double2* Ap = reinterpret_cast<const double2*>(Al + 6 * (size_t)j);
             const double2 a0 = Ap[0], a1 = Ap[1], a2 = Ap[2];
             Ab[u][0] = a0.x; Ab[u][1] = a0.y; Ab[u][2] = a1.x; Ab[u][3] = a1.y; Ab[u][4] = a2.x; Ab[u][5] = a2.y;
+            if (fj == f2) bsel[u] = j;
+            else slow(i, pe.x + 1, j);
+          } else {
+            const int fj = lm_frame[j], bj = lm_obs[j];
+            if (fj == f2) bsel[u] = bj;              // strictly increasing frames: the only partner
+            else slow(i, pe.x + 1, j);               // a gap in the track: the partner, if any, sits before slot j
           }
+        }
+        if (!LISTA) {
+#pragma unroll
+          for (int u = 0; u < 2; ++u)
+            if (bsel[u] >= 0) {
+              const double2* Ap = reinterpret_cast<const double2*>(Ao + 6 * (size_t)bsel[u]);
+              const double2 a0 = Ap[0], a1 = Ap[1], a2 = Ap[2];
+              Ab[u][0] = a0.x; Ab[u][1] = a0.y; Ab[u][2] = a1.x; Ab[u][3] = a1.y; Ab[u][4] = a2.x; Ab[u][5] = a2.y;
+            }
+        }
 #pragma unroll
         for (int u = 0; u < 2; ++u)
           if (bsel[u] >= 0) {
@@ -870,6 +888,207 @@ __global__ void __launch_bounds__(kFcThreads, 3) k_frame_schur_c(int F, int T, c
             own(i0 + 32 * u, Ca, d);
             schur_pair_c(Ca, Ab[u], d[0], d[1], d[2], d[0] + ex, d[1] + ey, d[2] + ez, acc);
           }
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < 36; ++e) {
+      double v = acc[e];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      acc[e] = v;
+    }
+    double* dst = Sp + ((size_t)f * (T + 1) + df) * 36;
+#pragma unroll
+    for (int e = 0; e < 36; ++e) if (lane == e % 32 && (e < 32 || lane < 4)) dst[e] = -acc[e];
+  }
+}
+
+// ---- the same gather with a TRACK BITMASK per observation and warp-level compaction (default) -------------------------------------
+// k_frame_schur_c walks all n observations of the frame for every frame distance df; a lane whose landmark is not seen in frame f + df
+// idles, and a landmark whose track has gaps sends its lane into a serial search of the observation list (ncu, config 3: 17.8 of 32
+// threads active per instruction, long-scoreboard stalls 3.6 per issue, 5.4 ms).  Here every observation carries a 64-bit mask, bit d set
+// iff its landmark is seen again d frames later (bit 0 = itself; host-built, fixed per structure), so that
+//     partner slot of (observation, df) = own slot + popc(mask & (2 << df) - 1) - 1
+// needs no look-up at all, and the partner's block comes from the copy in landmark-list order (Al): ONE L2 round trip per pair, no
+// search.  Each warp owns a frame distance, scans the frame's masks 32 at a time and queues the observations that have a partner
+// (ballot + popc into a warp-private shared-memory queue); whenever 32 are queued they are processed by a full warp.  Landmarks seen twice
+// in one frame (o_end < 0) keep the general search of k_frame_schur_c.  Fixed summation order: bit-reproducible.
+template <int N, int kFsmThreads>
+__global__ void __launch_bounds__(kFsmThreads, 2) k_frame_schur_m(int F, int T, const FramePose<N>* __restrict__ fps, const double* __restrict__ lm,
+                                                                  const int32_t* __restrict__ obs_begin, const int32_t* __restrict__ o_lm,
+                                                                  const unsigned long long* __restrict__ o_mask, const int32_t* __restrict__ o_pos,
+                                                                  const int32_t* __restrict__ o_end, const int32_t* __restrict__ lm_obs,
+                                                                  const int32_t* __restrict__ lm_frame, const double* __restrict__ Ao,
+                                                                  const double* __restrict__ Al, const double* __restrict__ Vi_all,
+                                                                  const double* __restrict__ vig_all, const double* __restrict__ ViYg_all, bool any_g,
+                                                                  int n_pad, double* __restrict__ Sp, double* __restrict__ Sb, double* __restrict__ rp) {
+  constexpr int kWarps = kFsmThreads / 32;
+  __shared__ double red[kWarps][48];
+  __shared__ int queue[kWarps][64];
+  __shared__ int s_dup;
+  extern __shared__ double sO[];
+  const int f = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b0 = obs_begin[f], n = obs_begin[f + 1] - b0;
+  const double px = fps[f].p_wb[0], py = fps[f].p_wb[1], pz = fps[f].p_wb[2];
+  unsigned long long* sMask = reinterpret_cast<unsigned long long*>(sO + 12 * (size_t)n_pad);   // 0 for landmarks seen twice in one frame
+  int* sPos = reinterpret_cast<int*>(sO + 13 * (size_t)n_pad);
+  if (threadIdx.x == 0) s_dup = 0;
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += kFsmThreads) {
+    const int a = b0 + i, l = o_lm[a];
+    const double2* Ap = reinterpret_cast<const double2*>(Ao + 6 * (size_t)a);
+    const double2* Vp = reinterpret_cast<const double2*>(Vi_all + 6 * (size_t)l);
+    const double2 a0 = Ap[0], a1 = Ap[1], a2 = Ap[2], v0 = Vp[0], v1 = Vp[1], v2 = Vp[2];
+    {
+      const double A6[6] = {a0.x, a0.y, a1.x, a1.y, a2.x, a2.y}, V6[6] = {v0.x, v0.y, v1.x, v1.y, v2.x, v2.y};
+      double C9[9];
+      sym_mul_sym(A6, V6, C9);
+#pragma unroll
+      for (int c = 0; c < 9; ++c) sO[c * n_pad + i] = C9[c];
+    }
+    sO[9 * n_pad + i] = lm[3 * (size_t)l] - px; sO[10 * n_pad + i] = lm[3 * (size_t)l + 1] - py; sO[11 * n_pad + i] = lm[3 * (size_t)l + 2] - pz;
+    const bool dup = o_end[a] < 0;
+    sMask[i] = dup ? 0ull : o_mask[a];
+    sPos[i] = o_pos[a];
+    if (dup) s_dup = 1;
+  }
+  __syncthreads();
+  // ---- pose right-hand side and pose x globals block:  Y_a^T v = [ (A v) x d ; -(A v) ]
+  {
+    double acc[48];
+#pragma unroll
+    for (int e = 0; e < 48; ++e) acc[e] = 0.0;
+    for (int i = threadIdx.x; i < n; i += kFsmThreads) {
+      const int l = o_lm[b0 + i];
+      const double2* Ap = reinterpret_cast<const double2*>(Ao + 6 * (size_t)(b0 + i));
+      const double2 q0 = Ap[0], q1 = Ap[1], q2 = Ap[2];
+      const double A[6] = {q0.x, q0.y, q1.x, q1.y, q2.x, q2.y};
+      const double dx = sO[9 * n_pad + i], dy = sO[10 * n_pad + i], dz = sO[11 * n_pad + i];
+      auto apply = [&](const double v[3], double out[6]) {
+        double w[3];
+        symmul3(A, v, w);
+        out[0] = w[1] * dz - w[2] * dy; out[1] = w[2] * dx - w[0] * dz; out[2] = w[0] * dy - w[1] * dx;
+        out[3] = -w[0]; out[4] = -w[1]; out[5] = -w[2];
+      };
+      const double v[3] = {vig_all[3 * (size_t)l], vig_all[3 * (size_t)l + 1], vig_all[3 * (size_t)l + 2]};
+      double o6[6];
+      apply(v, o6);
+#pragma unroll
+      for (int m = 0; m < 6; ++m) acc[m] -= o6[m];
+      if (any_g) {
+        const double* W = ViYg_all + 21 * (size_t)l;
+#pragma unroll
+        for (int g = 0; g < 7; ++g) {
+          const double vg[3] = {W[g], W[7 + g], W[14 + g]};
+          apply(vg, o6);
+#pragma unroll
+          for (int m = 0; m < 6; ++m) acc[6 + 7 * m + g] -= o6[m];
+        }
+      }
+    }
+    const int nv = any_g ? 48 : 6;
+#pragma unroll
+    for (int e = 0; e < 48; ++e) {
+      if (e < nv) {
+        double v = acc[e];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) red[warp][e] = v;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < nv) {
+      double v = 0.0;
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) v += red[w][threadIdx.x];
+      if (threadIdx.x < 6) rp[6 * (size_t)f + threadIdx.x] = v;
+      else Sb[42 * (size_t)f + (threadIdx.x - 6)] = v;
+    }
+    if (!any_g && threadIdx.x < 42) Sb[42 * (size_t)f + threadIdx.x] = 0.0;
+  }
+  const bool have_dup = s_dup != 0;
+  int* q = queue[warp];
+  // ---- pose-space blocks: warp per frame distance ----
+  for (int df = warp; df <= T; df += kWarps) {
+    const int f2 = f + df;
+    double acc[36];
+#pragma unroll
+    for (int e = 0; e < 36; ++e) acc[e] = 0.0;
+    if (f2 < F) {
+      const double ex = px - fps[f2].p_wb[0], ey = py - fps[f2].p_wb[1], ez = pz - fps[f2].p_wb[2];   // d_b = d_a + e
+      const unsigned long long below = (2ull << df) - 1ull;     // bits 0 .. df
+      // One pair per lane is kept PENDING: the partner block of a batch is requested as soon as the batch is full and consumed when the
+      // next one is (or at the end), so its L2 round trip overlaps the scan and the arithmetic of the previous batch.
+      auto request = [&](int i, double Ab[6]) {                    // partner block of observation i in frame f2 (list order)
+        const int slot = sPos[i] + __popcll(sMask[i] & below) - 1;
+        const double2* Ap = reinterpret_cast<const double2*>(Al + 6 * (size_t)slot);
+        const double2 a0 = Ap[0], a1 = Ap[1], a2 = Ap[2];
+        Ab[0] = a0.x; Ab[1] = a0.y; Ab[2] = a1.x; Ab[3] = a1.y; Ab[4] = a2.x; Ab[5] = a2.y;
+      };
+      auto consume = [&](int i, const double Ab[6]) {
+        double Ca[9];
+#pragma unroll
+        for (int c = 0; c < 9; ++c) Ca[c] = sO[c * n_pad + i];
+        const double d0 = sO[9 * n_pad + i], d1 = sO[10 * n_pad + i], d2 = sO[11 * n_pad + i];
+        schur_pair_c(Ca, Ab, d0, d1, d2, d0 + ex, d1 + ey, d2 + ez, acc);
+      };
+      int qn = 0, pend = -1;
+      double pA[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+      for (int i0 = 0; i0 < n; i0 += 32) {
+        const int i = i0 + lane;
+        const bool act = i < n && ((sMask[i] >> df) & 1ull);
+        const unsigned bal = __ballot_sync(0xffffffffu, act);
+        if (act) q[qn + __popc(bal & ((1u << lane) - 1u))] = i;
+        qn += __popc(bal);
+        __syncwarp();
+        if (qn >= 32) {
+          const int mine = q[lane];
+          const int carry = (lane + 32 < qn) ? q[lane + 32] : 0;
+          __syncwarp();
+          if (lane + 32 < qn) q[lane] = carry;
+          qn -= 32;
+          __syncwarp();
+          double nA[6];
+          request(mine, nA);
+          if (pend >= 0) consume(pend, pA);
+          pend = mine;
+#pragma unroll
+          for (int c = 0; c < 6; ++c) pA[c] = nA[c];
+        }
+      }
+      {
+        double nA[6];
+        const int last = lane < qn ? q[lane] : -1;
+        if (last >= 0) request(last, nA);
+        if (pend >= 0) consume(pend, pA);
+        if (last >= 0) consume(last, nA);
+      }
+      __syncwarp();
+      if (have_dup) {   // landmarks seen twice in one frame: the general search over the landmark's list
+        for (int i = lane; i < n; i += 32) {
+          const int a = b0 + i;
+          const int e = o_end[a];
+          if (e >= 0) continue;
+          double Aa[6], Vi[6];
+          const double d[3] = {sO[9 * n_pad + i], sO[10 * n_pad + i], sO[11 * n_pad + i]};
+          {
+            const int l = o_lm[a];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) { Aa[c] = Ao[6 * (size_t)a + c]; Vi[c] = Vi_all[6 * (size_t)l + c]; }
+          }
+          for (int pos = sPos[i]; pos < -e; ++pos) {
+            const int fb = lm_frame[pos];
+            if (fb > f2) break;
+            if (fb < f2) continue;
+            const int b = lm_obs[pos];
+            const double2* Ap = reinterpret_cast<const double2*>(Al + 6 * (size_t)pos);
+            const double2 a0 = Ap[0], a1 = Ap[1], a2 = Ap[2];
+            const double Ab[6] = {a0.x, a0.y, a1.x, a1.y, a2.x, a2.y};
+            schur_pair(Aa, Vi, Ab, d[0], d[1], d[2], d[0] + ex, d[1] + ey, d[2] + ez, acc);
+            if (b != a && df == 0) schur_pair(Ab, Vi, Aa, d[0], d[1], d[2], d[0], d[1], d[2], acc);   // same frame, same landmark: the transposed product too
+          }
+        }
       }
     }
 #pragma unroll
@@ -1539,6 +1758,18 @@ void analyse_structure(const ctba_problem* p, const GlobalStructure* gs, HostStr
   }
   hs->max_frame_obs = 1;
   for (int f = 0; f < F; ++f) hs->max_frame_obs = std::max(hs->max_frame_obs, (int)(p->f_obs_begin[f + 1] - p->f_obs_begin[f]));
+  // per observation: bit d set iff its landmark is seen again d frames later (bit 0 = itself), d < 64 (k_frame_schur_m)
+  hs->omask.assign(std::max(M, 1), 0ull);
+  for (int l = 0; l < L; ++l)
+    for (int i = lob[l]; i < lob[l + 1]; ++i) {
+      unsigned long long m = 0ull;
+      for (int k = i; k < lob[l + 1]; ++k) {
+        const int d = hs->lmf[k] - hs->lmf[i];
+        if (d >= 64) break;
+        m |= 1ull << d;
+      }
+      hs->omask[lobs[i]] = m;
+    }
   int T = 0, KD = N - 1;
   hs->lm_smin.assign(std::max(L, 1), -1);
   for (int l = 0; l < L; ++l) {
@@ -1633,7 +1864,7 @@ int assemble_structure(ctba_problem* p) {
   CTBA_CUDA(p, sd->d_node_of_knot.upload(sd->node_of_knot, st)); CTBA_CUDA(p, sd->d_node_of_bias.upload(sd->node_of_bias, st));
   CTBA_CUDA(p, sd->d_lm_obs_begin.upload(hs.lob, st)); CTBA_CUDA(p, sd->d_lm_obs.upload(hs.lobs, st));
   CTBA_CUDA(p, sd->d_lm_frame.upload(hs.lmf, st));
-  CTBA_CUDA(p, sd->d_o_pos.upload(hs.opos, st)); CTBA_CUDA(p, sd->d_o_end.upload(hs.oend, st));
+  CTBA_CUDA(p, sd->d_o_pos.upload(hs.opos, st)); CTBA_CUDA(p, sd->d_o_end.upload(hs.oend, st)); CTBA_CUDA(p, sd->d_o_mask.upload(hs.omask, st));
   CTBA_CUDA(p, sd->d_imu_seg.upload(hs.imu_seg, st)); CTBA_CUDA(p, sd->d_gp_seg.upload(hs.gp_seg, st));
   CTBA_CUDA(p, sd->d_prior_seg.upload(hs.prior_seg, st));
   sd->n_imu_seg = (int)hs.imu_seg.size() - 1; sd->n_gp_seg = (int)hs.gp_seg.size() - 1; sd->n_prior_seg = (int)hs.prior_seg.size() - 1; CTBA_CUDA(p, sd->d_kf_begin.upload(hs.kfb, st)); CTBA_CUDA(p, sd->d_kf_list.upload(hs.kfl, st));
@@ -1753,13 +1984,29 @@ static int assemble_schur_T(ctba_problem* p, double radius) {
                                          sd->Vi.p, sd->vig.p, sd->ViYg.p, sd->lm_corner_partial.p);
     if (any_g) { k_corner_reduce<<<1, 64, 0, st>>>(nlb, sd->lm_corner_partial.p, Hw, rhs_acc + n_pad); p->launches++; }
     if (p->schur_compact) {
-      k_obs_a<<<cdiv(M, 256), 256, 0, st>>>(M, p->d_o_frame.p, p->ev.Jl.p, (const double2*)p->ev.r_reproj.p, p->ev.f_w.p, sd->Yo.p);
+      double* Al = p->schur_list_a ? sd->Zo.p : nullptr;   // Zo (18 M doubles) is free in the compact path
+      k_obs_a<<<cdiv(M, 256), 256, 0, st>>>(M, p->d_o_frame.p, p->ev.Jl.p, (const double2*)p->ev.r_reproj.p, p->ev.f_w.p, sd->Yo.p, sd->d_o_pos.p, Al);
       const int n_pad = (sd->max_frame_obs + 1) & ~1;
       const size_t fs_smem = (size_t)n_pad * kFcRows * sizeof(double);
-      if (fs_smem > 48 * 1024) CTBA_CUDA(p, cudaFuncSetAttribute(k_frame_schur_c<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs_smem));
-      k_frame_schur_c<N><<<F, kFcThreads, fs_smem, st>>>(F, T, fps, S.lm, p->d_f_obs_begin.p, p->d_o_lm.p, sd->d_o_pos.p, sd->d_o_end.p, sd->d_lm_obs.p,
-                                                         sd->d_lm_frame.p, sd->Yo.p, sd->Vi.p, sd->vig.p, sd->ViYg.p, any_g, n_pad, sd->Sp.p, sd->Sb.p,
-                                                         sd->rp.p);
+      if (Al && p->schur_sorted && T + 1 <= 64) {
+        const size_t sm_smem = (size_t)n_pad * 14 * sizeof(double);   // C (9) + d (3) + track mask (1) rows of doubles, list slot (int)
+        auto launch = [&](auto kern, int threads) -> int {
+          if (sm_smem > 48 * 1024) CTBA_CUDA(p, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_smem));
+          kern<<<F, threads, sm_smem, st>>>(F, T, fps, S.lm, p->d_f_obs_begin.p, p->d_o_lm.p, sd->d_o_mask.p, sd->d_o_pos.p, sd->d_o_end.p, sd->d_lm_obs.p,
+                                            sd->d_lm_frame.p, sd->Yo.p, Al, sd->Vi.p, sd->vig.p, sd->ViYg.p, any_g, n_pad, sd->Sp.p, sd->Sb.p, sd->rp.p);
+          return CTBA_OK;
+        };
+        int rc;
+        if (p->schur_threads == 128) rc = launch(k_frame_schur_m<N, 128>, 128);
+        else if (p->schur_threads == 192) rc = launch(k_frame_schur_m<N, 192>, 192);
+        else rc = launch(k_frame_schur_m<N, 256>, 256);
+        if (rc) return rc;
+      } else {
+        auto kfc = Al ? k_frame_schur_c<N, true> : k_frame_schur_c<N, false>;
+        if (fs_smem > 48 * 1024) CTBA_CUDA(p, cudaFuncSetAttribute(kfc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs_smem));
+        kfc<<<F, kFcThreads, fs_smem, st>>>(F, T, fps, S.lm, p->d_f_obs_begin.p, p->d_o_lm.p, sd->d_o_pos.p, sd->d_o_end.p, sd->d_lm_obs.p,
+                                            sd->d_lm_frame.p, sd->Yo.p, Al, sd->Vi.p, sd->vig.p, sd->ViYg.p, any_g, n_pad, sd->Sp.p, sd->Sb.p, sd->rp.p);
+      }
     } else {
       k_obs_yz<N><<<cdiv(M, 128), 128, 0, st>>>(G, S.glb, fps, S.lm, M, p->d_o_frame.p, p->d_o_lm.p, p->ev.Jl.p, (const double2*)p->ev.r_reproj.p,
                                                 p->ev.f_w.p, sd->Vi.p, sd->Yo.p, sd->Zo.p);

@@ -29,7 +29,7 @@ void solver_free(SolverData* sd) {
   for (auto* d : dd) d->release();
   DBuf<int32_t>* di[] = {&sd->d_node_of_knot, &sd->d_node_of_bias, &sd->d_lm_obs_begin, &sd->d_lm_obs, &sd->d_o_pos, &sd->d_o_end, &sd->d_imu_seg, &sd->d_gp_seg, &sd->d_prior_seg, &sd->d_lm_frame, &sd->d_kf_begin, &sd->d_kf_list, &sd->flag, &sd->d_lm_owner};
   for (auto* d : di) d->release();
-  sd->d_touch_knot.release(); sd->d_touch_bias.release(); sd->d_touch_lm.release();
+  sd->d_touch_knot.release(); sd->d_touch_bias.release(); sd->d_touch_lm.release(); sd->d_o_mask.release();
   delete sd;
 }
 

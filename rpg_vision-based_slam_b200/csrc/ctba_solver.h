@@ -46,6 +46,7 @@ struct HostStructure {
   int K = 0, Kb = 0, L = 0, F = 0, M = 0, nodes = 0, hbn = 0, T = 0, KD = 0, max_frame_obs = 1, n_band = 0, n_pad = 0, nbw = 0;
   bool has_imu = false;
   std::vector<int32_t> node_of_knot, node_of_bias, lob, lobs, opos, oend, imu_seg, gp_seg, prior_seg, lmf, kfb, kfl, lm_smin;
+  std::vector<unsigned long long> omask;   // per observation: frames ahead in which its landmark is seen again
   std::vector<uint8_t> tk, tb, tl;
   int gactive[GT_SIZE] = {0};
 };
@@ -63,7 +64,8 @@ struct SolverData {
   double frames_per_knot = 0.0;   // average number of frames whose window contains a knot (over the knots that have any)
   DBuf<int32_t> d_imu_seg, d_gp_seg, d_prior_seg;   // runs of samples with the same unknowns (CSR offsets)
   int n_imu_seg = 0, n_gp_seg = 0, n_prior_seg = 0;
-  DBuf<int32_t> d_o_pos, d_o_end, d_kf_begin, d_kf_list;   // observation -> slot in its landmark's list; knot -> frames (CSR)
+  DBuf<int32_t> d_o_pos, d_o_end, d_kf_begin, d_kf_list;
+  DBuf<unsigned long long> d_o_mask;   // track bitmask per observation (k_frame_schur_m)   // observation -> slot in its landmark's list; knot -> frames (CSR)
   DBuf<double> Vi, vig, ViYg, Yo, Zo, lm_corner_partial;   // Schur gather scratch (ctba_assemble.cu)
   DBuf<uint8_t> d_touch_knot, d_touch_bias, d_touch_lm;  // bit0 rot/acc, bit1 pos/gyr
   int gactive[GT_SIZE] = {0};

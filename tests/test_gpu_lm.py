@@ -166,3 +166,38 @@ def test_pcg_step_equals_cholesky_step(pkg, scene, shape):
     inner = slice(3, -4)
     assert np.abs(pa[inner] - pb[inner]).max() < 1e-4, np.abs(pa[inner] - pb[inner]).max()
     assert 0 < nit <= 40000, nit
+
+
+def _gappy_scene_with_duplicates(scene, seed=31):
+    """Tracks with gaps (40 % of the observations dropped at random) and a few landmarks observed TWICE in one frame (a second, slightly
+    shifted detection): the cases the landmark Schur gather treats apart — track bitmask / list search / same-frame pairs."""
+    sc = scene.make_scene(order=6, duration_s=6.0, n_landmarks=260, track_len=14, imu_hz=0, gp_hz=10, seed=seed, flags=(False, True, False, True, True))
+    rng = np.random.default_rng(seed)
+    F = len(sc["frame_t_ns"])
+    ob, uv, li = sc["obs_begin"], sc["uv"], sc["lm_index"]
+    fi = np.repeat(np.arange(F), np.diff(ob))
+    keep = rng.random(len(li)) > 0.4
+    fi, uv, li = fi[keep], uv[keep], li[keep]
+    dup = rng.choice(len(li), 25, replace=False)                       # the same landmark once more in the same frame
+    fi = np.r_[fi, fi[dup]]; li = np.r_[li, li[dup]]; uv = np.vstack([uv, uv[dup] + rng.normal(size=(len(dup), 2)) * 0.7])
+    o = np.lexsort((li, fi))
+    fi, li, uv = fi[o], li[o], uv[o]
+    ob2 = np.zeros(F + 1, dtype=np.int32); np.add.at(ob2, fi + 1, 1)
+    sc = dict(sc, obs_begin=np.cumsum(ob2).astype(np.int32), uv=np.ascontiguousarray(uv), lm_index=li.astype(np.int32))
+    return sc
+
+
+@pytest.mark.parametrize("opts", [{}, {"schur_threads": 256}, {"schur_threads": 128}, {"schur_mask": 0}, {"schur_mask": 0, "schur_list_a": 0},
+                                  {"schur_compact": 0}])
+def test_lm_gappy_tracks_and_duplicate_observations(pkg, scene, oracle, opts):
+    """Every variant of the landmark Schur gather (track-bitmask kernel at its three CTA sizes, list-order / observation-order partner
+    blocks, the Y/Z path) on tracks with gaps and same-frame duplicates: LM trace against the oracle."""
+    sc = _gappy_scene_with_duplicates(scene)
+    gpu = pkg.BSplineSO3R3(sc["order"], sc["dt_ns"], sc["start_t_ns"], device=0)
+    cpu = oracle.OracleSpline(sc["order"], sc["dt_ns"], sc["start_t_ns"])
+    pkg.load_scene(gpu, sc); pkg.load_scene(cpu, sc)
+    for k, v in opts.items():
+        gpu.setOption(k, v)
+    sg, so = gpu.optimize(6), cpu.optimize(6, 8)
+    assert so["num_successful_steps"] >= 2
+    _check(gpu, cpu, sg, so)
