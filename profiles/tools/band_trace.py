@@ -49,3 +49,30 @@ for t in range(200, 208):
 for t in range(192, 216, 8):
     if valid[2][t]:
         print(f"border chunk t0={t}: [{(int(buf[2, t, 0]) - t0) * 1e-3:9.2f}, {(int(buf[2, t, 1]) - t0) * 1e-3:9.2f}]")
+# ---- whole-factorisation view: where the solve time goes (level-0 steps are those with t above the interface level's step count) ----
+st, en, v = P
+lvl0 = v >= 150
+d = np.diff(st[lvl0])
+print("level-0 panel steps t>=150: n", lvl0.sum(), "span ms", (en[lvl0].max() - st[lvl0].min()) * 1e-3, "start-to-start us: p10/p50/p90/max",
+      np.percentile(d, 10), np.percentile(d, 50), np.percentile(d, 90), d.max())
+for a in range(150, int(v.max()), 150):
+    m = (v >= a) & (v < a + 150)
+    if m.sum() > 2:
+        print(f"   t in [{a},{a + 150}): start-to-start median {np.median(np.diff(st[m])):.2f} us, panel duration median {np.median(en[m] - st[m]):.2f}")
+vu = np.nonzero(valid[1])[0]; vu = vu[vu >= 150]
+if vu.size:
+    su = (buf[1, vu, 0].astype(np.int64) - t0) * 1e-3; eu = (buf[1, vu, 1].astype(np.int64) - t0) * 1e-3
+    print("update kernel duration us (t>=150): p10/p50/p90", np.percentile(eu - su, 10), np.percentile(eu - su, 50), np.percentile(eu - su, 90))
+vb = np.nonzero(valid[2])[0]
+if vb.size:
+    sb = (buf[2, vb, 0].astype(np.int64) - t0) * 1e-3; eb = (buf[2, vb, 1].astype(np.int64) - t0) * 1e-3
+    print("border chunks:", vb.size, "duration us p10/p50/p90", np.percentile(eb - sb, 10), np.percentile(eb - sb, 50), np.percentile(eb - sb, 90),
+          "busy fraction of the level-0 span", (eb - sb).sum() / (en[lvl0].max() - st[lvl0].min()), "last border end ms", eb.max() * 1e-3)
+    # lag of the border pipeline behind the panel chain: chunk starting at step t can start after panel step t+7
+    lag = [sb[i] - en[np.nonzero(v == min(vb[i] + 7, v.max()))[0][0]] for i in range(vb.size) if (v == min(vb[i] + 7, v.max())).any()]
+    print("border chunk start minus end of its last panel step, us: p10/p50/p90", np.percentile(lag, 10), np.percentile(lag, 50), np.percentile(lag, 90))
+low = v < 150
+if low.any():
+    print("interface-level steps (t<150, overwrite level 0): n", low.sum(), "span ms", (en[low].max() - st[low].min()) * 1e-3, "starts at ms", st[low].min() * 1e-3,
+          "start-to-start median us", np.median(np.diff(st[low])))
+print("first event 0, last panel/update/border end ms:", en.max() * 1e-3)
