@@ -916,3 +916,160 @@ def test_align_colmap_to_imu_tool(pkg, scene, tmp_path):
     R_ig = R_IB * R_gb.inv(); p_ig = -R_ig.apply(p_gb)
     T_IG = np.loadtxt(os.path.join(d, "aci_out", "T_IG.txt"))
     np.testing.assert_allclose(T_IG[:3, :3], R_ig.as_matrix(), atol=2e-9); np.testing.assert_allclose(T_IG[:3, 3], p_ig, rtol=2e-8, atol=2e-9)
+
+
+# ---- optimize_discrete_time (BASELINE configs[3]): src/optimize_discrete_time.cpp:195-726 ---------------------------------------------
+def _write_dt_dataset(d, sc, dd, T_wg_q, T_wg_p, flags):
+    """A scene of scene.make_scene + its discrete-time view (scene.dt_scene_from: the perturbed frame poses) as the files
+    optimize_discrete_time reads: EuRoC-format calibration, imu.txt, gp.txt, the COLMAP export (images.bin written in REVERSED order, so
+    that the driver's sort by image name matters), the COLMAP camera trajectory T_GC, T_wg.txt / scale.txt of the alignment step."""
+    _write_vi_dataset(d, sc, 6, T_wg_q, T_wg_p, (flags[0], flags[1], False, True, flags[3]))       # calib.yaml, imu.txt, gp.txt (+ files this tool ignores)
+    R_wg = Rot.from_quat(T_wg_q); R_bc = Rot.from_quat(sc["q_bc"])
+    F = len(sc["frame_t_ns"])
+    R_wb = Rot.from_quat(dd["poses"][:, :4]); p_wb = dd["poses"][:, 4:]
+    R_gb = R_wg.inv() * R_wb; p_gb = R_wg.inv().apply(p_wb - T_wg_p) / sc["scale"]
+    R_gc = R_gb * R_bc; p_gc = R_gb.apply(sc["p_bc"]) + p_gb                                          # T_GC = T_GB T_BC
+    with open(os.path.join(d, "colmap_traj.txt"), "w") as f:
+        f.write("# timestamp tx ty tz qx qy qz qw\n")
+        for i in range(F):
+            f.write(" ".join(f"{v:.17g}" for v in [sc["frame_t_ns"][i] * 1e-9, *p_gc[i], *R_gc[i].as_quat()]) + "\n")
+    lm_g = R_wg.inv().apply(sc["landmarks"] - T_wg_p) / sc["scale"]
+    ids = [10 + 3 * i for i in range(len(lm_g))]
+    cams = [dict(id=1, model=sc["cam_model"], w=sc["width"], h=sc["height"], params=list(sc["intr"]) + list(sc["dist"]))]
+    images = []
+    for f_ in reversed(range(F)):
+        b, e = sc["obs_begin"][f_], sc["obs_begin"][f_ + 1]
+        pts = [(float(sc["uv"][q, 0]), float(sc["uv"][q, 1]), ids[sc["lm_index"][q]]) for q in range(b, e)]
+        images.append(dict(id=F - f_, qwxyz=[1.0, 0, 0, 0], t=[0.0, 0, 0], cam=1, name=f"img_{f_:06d}.png", pts=pts))
+    points = [dict(id=ids[i], xyz=list(lm_g[i]), err=0.5, track=[]) for i in range(len(lm_g))]
+    os.makedirs(os.path.join(d, "colmap_dt"))
+    _write_colmap_bin(os.path.join(d, "colmap_dt"), cams, images, points)
+    os.makedirs(os.path.join(d, "align_dt"))
+    _write_pose(os.path.join(d, "align_dt", "T_wg.txt"), T_wg_q, T_wg_p, digits=17)
+    open(os.path.join(d, "align_dt", "scale.txt"), "w").write(f"{sc['scale']:.17g}\n")
+    cam_ts = sc["frame_t_ns"] * 1e-9
+    start_t, end_t = cam_ts[1] - 1e-4, cam_ts[-2] + 1e-4                                               # the first and the last frame stay out
+    yml = os.path.join(d, "dt.yaml")
+    with open(yml, "w") as f:
+        f.write(f"""dataset: Custom
+cam_id: 0
+camimu_calib_fn: "{d}/calib.yaml"
+imu_fn: "{d}/imu.txt"
+gp_fn: "{d}/gp.txt"
+colmap_dir: "{d}/colmap_dt/"
+colmap_fn: "{d}/colmap_traj.txt"
+alignment_dir: "{d}/align_dt"
+full_batch_optimization_dir: "{d}/full_batch_dt"
+start_t: {start_t:.17g}
+end_t: {end_t:.17g}
+grid_cell_size: 30
+gp_std: {sc['gp_std']}
+sigma_reproj_px: {sc['sigma_reproj_px']}
+sigma_acc_c: {sc['sigma_acc_c']}
+sigma_acc_bias_c: {sc['sigma_acc_bias_c']}
+sigma_omega_c: {sc['sigma_omega_c']}
+sigma_omega_bias_c: {sc['sigma_omega_bias_c']}
+t_offset_cam_gp_init: {sc['t_s_gp']:.17g}
+p_BP: [{sc['p_bp'][0]:.17g}, {sc['p_bp'][1]:.17g}, {sc['p_bp'][2]:.17g}]
+optimize_scale: {'true' if flags[0] else 'false'}
+optimize_pBP: {'true' if flags[1] else 'false'}
+optimize_t_offset_globsens_imu: {'true' if flags[3] else 'false'}
+n_max_iters: 8
+n_threads: 4
+""")
+    return yml, os.path.join(d, "full_batch_dt", "discrete_time"), (R_gc, p_gc, lm_g)
+
+
+def _dt_scene(scene):
+    sc = scene.make_scene(order=6, duration_s=3.0, n_landmarks=140, track_len=8, imu_hz=200, gp_hz=10, cam_hz=10.0, seed=23, flags=(False, True, True, True, True),
+                          outlier_frac=0.03)
+    dd = scene.dt_scene_from(sc, perturb=(0.002, 0.05))
+    return sc, dd, (False, True, True, True)       # scale, p_BP, extrinsics (the driver never sets it: constructor default true), time offset
+
+
+def test_dt_driver_builds_and_fails_loudly_without_gpu(pkg, scene, tmp_path):
+    import torch
+    exe = _gxx(os.path.join(ROOT, "drivers", "optimize_discrete_time.cpp"), str(tmp_path / "dt"), pkg)
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    sc, dd, flags = _dt_scene(scene)
+    yml, _, _ = _write_dt_dataset(str(tmp_path), sc, dd, Rot.from_rotvec([0.2, -0.4, 1.0]).as_quat(), np.array([3.0, -2.0, 1.0]), flags)
+    out = subprocess.run([exe, yml], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 3 and "no CPU fallback" in out.stderr, out.stdout + out.stderr
+    # everything up to the construction of the estimator ran: calibration, measurements, COLMAP export, trajectory, alignment
+    assert f"Loaded {len(sc['imu_t_ns'])} imu measurements" in out.stdout and f"Loaded {len(sc['gp_t_ns'])} global measurements" in out.stdout
+    assert f"Full trajectory contains: {len(sc['frame_t_ns'])} images" in out.stdout and f"Full 3D map contains: {len(sc['landmarks'])} 3D points" in out.stdout
+
+
+@pytest.mark.gpu
+def test_dt_driver_end_to_end_on_gpu(pkg, oracle, scene, tmp_path):
+    exe = _gxx(os.path.join(ROOT, "drivers", "optimize_discrete_time.cpp"), str(tmp_path / "dt"), pkg)
+    sc, dd, flags = _dt_scene(scene)
+    T_q, T_p = Rot.from_rotvec([0.2, -0.4, 1.0]).as_quat(), np.array([3.0, -2.0, 1.0])
+    yml, res, (R_gc, p_gc, lm_g) = _write_dt_dataset(str(tmp_path), sc, dd, T_q, T_p, flags)
+    out = subprocess.run([exe, yml, "0"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    # the oracle through the same steps (src/optimize_discrete_time.cpp:339-570)
+    R_wg = Rot.from_quat(T_q); R_bc = Rot.from_quat(sc["q_bc"])
+    sl = slice(1, len(sc["frame_t_ns"]) - 1)
+    cam_ts = (sc["frame_t_ns"] * 1e-9)[sl]
+    R_gb = R_gc[sl] * R_bc.inv(); p_gb = p_gc[sl] - R_gb.apply(sc["p_bc"])                             # T_GB = T_GC T_CB
+    poses = np.concatenate([(R_wg * R_gb).as_quat(), sc["scale"] * R_wg.apply(p_gb) + T_p], axis=1)
+    o = oracle.OracleDiscrete()
+    o.setCamera(sc["cam_model"], sc["intr"], sc["dist"], sc["q_bc"], sc["p_bc"], sc["t_offset_cam_imu"], sc["width"], sc["height"])
+    o.setImu(sc["sigma_omega_c"], sc["sigma_acc_c"], sc["sigma_omega_bias_c"], sc["sigma_acc_bias_c"], np.array([0.0, 0.0, 9.80665]))
+    o.initializeStates(poses, cam_ts)
+    o.initializeLinearVelocity()
+    t_gp_imu_init = sc["t_offset_cam_imu"] - sc["t_s_gp"]
+    o.setGlobals(sc["scale"], sc["p_bp"], t_gp_imu_init)
+    o.setFlags(*flags)
+    o.set3DPoints(sc["scale"] * R_wg.apply(lm_g) + T_p)
+    b0, b1 = sc["obs_begin"][1], sc["obs_begin"][-2]
+    pt_begin = (sc["obs_begin"][1:-1] - b0).astype(np.int32); uv = sc["uv"][b0:b1]; li = sc["lm_index"][b0:b1]
+    valid, nv, vel = o.computeValidReprojections(pt_begin, uv, li, sc["width"], sc["height"], 30, cam_ts)
+    ts_imu = cam_ts + sc["t_offset_cam_imu"]
+    ti = sc["imu_t_ns"] * 1e-9
+    n_fac = 0
+    for f in range(len(cam_ts) - 1):
+        t0, t1 = ts_imu[f], ts_imu[f + 1]
+        if ti[0] > t0 or ti[-1] < t1: continue
+        k0 = int(np.searchsorted(ti, t0, side="right")) - 1; k1 = min(int(np.searchsorted(ti, t1, side="right")), ti.size - 1)
+        o.addImuMeasurements(f, ti[k0:k1 + 1], sc["imu_gyr"][k0:k1 + 1], sc["imu_acc"][k0:k1 + 1]); n_fac += 1
+    ob = np.r_[0, np.cumsum([valid[pt_begin[f]:pt_begin[f + 1]].sum() for f in range(len(cam_ts))])].astype(np.int32)
+    o.addFrames(np.arange(len(cam_ts), dtype=np.int32), ob, uv[valid], vel[valid], li[valid], sc["sigma_reproj_px"])
+    t_gp = sc["gp_t_ns"] * 1e-9
+    f0 = np.array([next((i - 1 for i in range(len(ts_imu)) if ts_imu[i] > t + t_gp_imu_init), -1) for t in t_gp])
+    ok = f0 >= 0
+    o.addGlobalSensMeasurements(t_gp[ok], sc["gp_pos"][ok], f0[ok].astype(np.int32), sc["gp_std"])
+    assert f"valid reprojections: {int(valid.sum())}, IMU factors: {n_fac}\n" in out.stdout
+    assert f"Global positions in the problem: {int(ok.sum())} of {len(t_gp)}\n" in out.stdout
+    so = o.optimize(8, 8)
+    line = [l for l in out.stdout.splitlines() if l.startswith("solve: ")][0]
+    got0, got1 = [float(v) for v in line.split("cost ")[1].split(",")[0].split(" -> ")]
+    assert abs(got0 - so["initial_cost"]) <= 1e-8 * so["initial_cost"] and abs(got1 - so["final_cost"]) <= 1e-6 * so["final_cost"]
+    assert f"iterations {len(so['iterations'])} (successful {so['num_successful_steps']}, unsuccessful {so['num_unsuccessful_steps']})" in line
+    P, sb = o.getStates()
+    tr = np.loadtxt(os.path.join(res, "trajectory.txt"))
+    assert tr.shape == (len(cam_ts), 8)
+    np.testing.assert_allclose(tr[:, 0], ts_imu, atol=1e-9)
+    np.testing.assert_allclose(tr[:, 1:4], P[:, 4:], atol=1e-5)                                        # north_star: 1 mm / 0.01 deg
+    assert (Rot.from_quat(tr[:, 4:]).inv() * Rot.from_quat(P[:, :4])).magnitude().max() < np.deg2rad(0.001)
+    np.testing.assert_allclose(np.loadtxt(os.path.join(res, "velocity.txt"))[:, 1:], sb[:, 0:3], atol=1e-5)
+    np.testing.assert_allclose(np.loadtxt(os.path.join(res, "gyro_bias.txt"))[:, 1:], sb[:, 3:6], atol=1e-6)
+    np.testing.assert_allclose(np.loadtxt(os.path.join(res, "acc_bias.txt"))[:, 1:], sb[:, 6:9], atol=1e-5)
+    g = o.getGlobals()
+    assert abs(float(open(os.path.join(res, "scale.txt")).read()) - (sc["scale"] + g[0])) < 1e-7
+    assert abs(float(open(os.path.join(res, "cam_imu_time_offset.txt")).read()) - (sc["t_offset_cam_imu"] + g[8])) < 1e-7
+    assert abs(float(open(os.path.join(res, "globalsensor_imu_time_offset.txt")).read()) - (t_gp_imu_init + g[9])) < 1e-7
+    np.testing.assert_allclose(np.loadtxt(os.path.join(res, "p_BP.txt")), g[10:13], atol=1e-6)
+    T_bc = np.loadtxt(os.path.join(res, "T_BC.txt"))
+    R_o = (R_bc * Rot.from_quat(g[1:5])).as_matrix(); p_o = sc["p_bc"] + R_bc.apply(g[5:8])
+    np.testing.assert_allclose(T_bc[:3, :3], R_o, atol=1e-6); np.testing.assert_allclose(T_bc[:3, 3], p_o, atol=1e-6)
+    np.testing.assert_allclose(np.loadtxt(os.path.join(res, "points3D.txt")), o.get3DPoints(), atol=1e-5)
+    init = np.loadtxt(os.path.join(res, "initial_trajectory.txt"))
+    np.testing.assert_allclose(init[:, 1:4], poses[:, 4:], atol=1e-9)
+    assert len(np.loadtxt(os.path.join(res, "reprojection_errors.txt"))) == int(valid.sum())
+    assert len(np.loadtxt(os.path.join(res, "global_position_errors.txt"))) == int(ok.sum())
+    for fn in ("initial_velocity.txt", "initial_acc_bias.txt", "initial_gyro_bias.txt", "initial_scale.txt", "initial_p_BP.txt", "initial_T_BC.txt", "gravity.txt",
+               "initial_points3D.txt", "initial_reprojection_errors.txt", "initial_global_position_errors.txt"):
+        assert os.path.exists(os.path.join(res, fn))
