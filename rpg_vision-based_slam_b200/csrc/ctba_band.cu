@@ -237,8 +237,11 @@ __device__ __forceinline__ unsigned long long trace_now() { unsigned long long t
 #ifdef CTBA_BAND_TIMING
 __device__ long long g_band_clk[8];
 #define BAND_CLK(k) do { if (j == 100 && b == 1 && tid == 0) g_band_clk[k] = clock64(); } while (0)
+__device__ long long g_border_clk[8][8];   // [column of the chunk][phase] of one border CTA (blockIdx 30, chunk starting at step 304)
+#define BORDER_CLK(k) do { if (blockIdx.x == 30 && t0 == 304 && threadIdx.x == 0) g_border_clk[t - t0][k] = clock64(); } while (0)
 #else
 #define BAND_CLK(k) do {} while (0)
+#define BORDER_CLK(k) do {} while (0)
 #endif
 
 // Two launches per step t (they run concurrently, on two streams / two graph branches): every partition p advances to its block column
@@ -436,6 +439,28 @@ __device__ __forceinline__ void kloop(double (&acc)[4][4][2], const double* pa, 
     kfrag_mma(acc, f1);
   }
 }
+// The same sum over the SAME half (fragment columns 8 t + 4 half .. + 3) of every second block: n half-blocks starting at pa / pb, the next one
+// a_step / b_step further.  Used by the border pipeline to deal the k range to its 4 warps in half-blocks (warps 0, 1: the two halves of the
+// even blocks, warps 2, 3: of the odd blocks), so that 21 blocks split 11 / 11 / 10 / 10 half-blocks instead of 12 / 10 / 10 / 10.
+template <bool COHERENT>
+__device__ __forceinline__ void kloop_half(double (&acc)[4][4][2], const double* pa, size_t a_rs, size_t a_step, const double* __restrict__ pb,
+                                           size_t b_step, int n, int half, int rows_a) {
+  if (n <= 0) return;
+  KFrag f0, f1;
+  kfrag_load<COHERENT>(f0, pa, a_rs, pb, half, rows_a);
+  for (int i = 0; i < n; i += 2) {
+    if (i + 1 < n) kfrag_load<COHERENT>(f1, pa + a_step, a_rs, pb + b_step, half, rows_a);
+    kfrag_mma(acc, f0);
+    pa += 2 * a_step; pb += 2 * b_step;
+    if (i + 1 < n) {
+      if (i + 2 < n) kfrag_load<COHERENT>(f0, pa, a_rs, pb, half, rows_a);
+      kfrag_mma(acc, f1);
+    }
+  }
+}
+__device__ __forceinline__ void cp_async16(double* dst_smem, const double* src) {   // 16 bytes global -> shared, through L2, no registers
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
 constexpr int kLdS = 36;   // shared-memory leading dimension: (4 g + t) mod 16 distinct -> conflict-free 8-byte fragment reads (col = 4 ks + t)
 __device__ __forceinline__ void acc_to_smem(double* sP, const double (&acc)[4][4][2], int g, int tq) {
 #pragma unroll
@@ -456,10 +481,13 @@ __device__ __forceinline__ void acc_to_smem(double* sP, const double (&acc)[4][4
 // in order; every dependency is either final (L, L_jj^-1 from the panel kernel) or the CTA's own earlier output.  4 warps split the k range,
 // the partial sums meet in shared memory, then the product with L_jj^-1 (staged in shared memory while the k loop runs) gives the block.
 constexpr int kBorderThreads = 128;
+constexpr size_t kBorderSmem = (size_t)6 * kNB * kLdS * sizeof(double);   // 4 partial sums + L_jj^-1 + FB(r, j)
 __global__ void __launch_bounds__(kBorderThreads) k_band_border(BandLayout B, const __grid_constant__ BandParts PS, int t0, int t1,
                                                                 const double* __restrict__ dinv) {
-  __shared__ double sP[4][kNB * kLdS];     // per-warp partial sums; sP[0] becomes the block T = FB - sum
-  __shared__ double sL[kNB * kLdS];        // L_jj^-1
+  extern __shared__ __align__(16) double border_smem[];   // kBorderSmem bytes (above the 48 KB a kernel may declare statically)
+  double (*sP)[kNB * kLdS] = reinterpret_cast<double (*)[kNB * kLdS]>(border_smem);   // [4] per-warp partial sums; sP[0] becomes T = FB - sum
+  double* sL = border_smem + 4 * kNB * kLdS;              // L_jj^-1
+  double* sF = border_smem + 5 * kNB * kLdS;              // FB(r, j), the column's own block before the update
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tq = lane & 3;
   const int nb1 = B.nbw + 1;
   int u = blockIdx.x, pi = 0;
@@ -472,24 +500,38 @@ __global__ void __launch_bounds__(kBorderThreads) k_band_border(BandLayout B, co
   for (int t = t0; t < tend; ++t) {
     const int j = Q.c0 + t;
     const int k_lo = Q.c0 > j - B.nbw ? Q.c0 : j - B.nbw;
-    // L_jj^-1 -> shared memory (overlaps with the k loop; consumed after the barriers below)
-    for (int e = threadIdx.x; e < kNB * kNB; e += kBorderThreads) sL[(e >> 5) * kLdS + (e & 31)] = dinv[(size_t)j * 1024 + e];
+    BORDER_CLK(0);
+    // L_jj^-1 and the column's own block -> shared memory by cp.async: in flight during the k loop, no registers, consumed after the barriers
+    // below (the in-kernel clocks showed ~1000 cycles of exposed latency for a register-staged L_jj^-1 before the k loop could start and
+    // ~1700 for the global read of FB(r, j) between the two barriers)
+    double* Fj = F + (size_t)t * kNB;
+    for (int e = threadIdx.x; e < kNB * kNB / 2; e += kBorderThreads) {
+      const int r = e >> 4, c = (e & 15) << 1;
+      cp_async16(&sL[r * kLdS + c], dinv + (size_t)j * 1024 + r * kNB + c);
+      cp_async16(&sF[r * kLdS + c], Fj + (size_t)r * Q.ld + c);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    BORDER_CLK(1);
     double acc[4][4][2];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
       for (int h = 0; h < 4; ++h) acc[i][h][0] = acc[i][h][1] = 0.0;
-    const int nk_all = j - k_lo, nk = warp < nk_all ? (nk_all - warp + 3) / 4 : 0;
-    kloop<true>(acc, F + (size_t)g * Q.ld + (size_t)(k_lo + warp - Q.c0) * kNB + 8 * tq, Q.ld, 4 * kNB,
-                B.band + ((size_t)(k_lo + warp) * nb1 + (j - k_lo - warp)) * 1024 + (size_t)g * kNB + 8 * tq, (size_t)4 * (nb1 - 1) * 1024, nk, kNB);
+    // warp w: half w & 1 of the blocks k_lo + (w >> 1), + 2, + 4, ...
+    const int nk_all = j - k_lo, b0 = warp >> 1, nh = b0 < nk_all ? (nk_all - b0 + 1) / 2 : 0;
+    kloop_half<true>(acc, F + (size_t)g * Q.ld + (size_t)(k_lo + b0 - Q.c0) * kNB + 8 * tq, Q.ld, 2 * kNB,
+                     B.band + ((size_t)(k_lo + b0) * nb1 + (j - k_lo - b0)) * 1024 + (size_t)g * kNB + 8 * tq, (size_t)2 * (nb1 - 1) * 1024, nh, warp & 1, kNB);
+    BORDER_CLK(2);
     acc_to_smem(sP[warp], acc, g, tq);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
-    double* Fj = F + (size_t)t * kNB;
+    BORDER_CLK(3);
     for (int e = threadIdx.x; e < kNB * kNB; e += kBorderThreads) {
       const int r = e >> 5, c = e & 31, o = r * kLdS + c;
-      sP[0][o] = Fj[(size_t)r * Q.ld + c] - ((sP[0][o] + sP[1][o]) + (sP[2][o] + sP[3][o]));
+      sP[0][o] = sF[o] - ((sP[0][o] + sP[1][o]) + (sP[2][o] + sP[3][o]));
     }
     __syncthreads();
+    BORDER_CLK(4);
     // W(r, j) = T L_jj^-T:  X[r][c] = sum_k T[r][k] Linv[c][k];  warp w: row group w, all four column groups; natural k layout (col = 4 ks + t)
     double x[4][2][2];
 #pragma unroll
@@ -503,7 +545,9 @@ __global__ void __launch_bounds__(kBorderThreads) k_band_border(BandLayout B, co
 #pragma unroll
     for (int h = 0; h < 4; ++h)
       *reinterpret_cast<double2*>(Fj + (size_t)(8 * warp + g) * Q.ld + 8 * h + 2 * tq) = make_double2(x[h][0][0] + x[h][1][0], x[h][0][1] + x[h][1][1]);
+    BORDER_CLK(5);
     __syncthreads();   // the block is visible to the whole CTA before the next column reads it back; sP / sL may be overwritten
+    BORDER_CLK(6);
   }
   BAND_TRACE_END(2, t0);
 }
@@ -1133,7 +1177,8 @@ static int enqueue_steps(ctba_problem* p, cudaStream_t st, const BandLayout& B, 
     }
     if (nborder && t < max_panel && (t + 1 - chunk_begin == kBorderChunk || t + 1 == max_panel)) {
       CTBA_CUDA(p, cudaStreamWaitEvent(s3, evA, 0));   // evA: the most recent panel step = the chunk's last
-      k_band_border<<<nborder, kBorderThreads, 0, s3>>>(B, PS, chunk_begin, t + 1, dinv); ++*nl;
+      CTBA_CUDA(p, cudaFuncSetAttribute(k_band_border, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBorderSmem));
+      k_band_border<<<nborder, kBorderThreads, kBorderSmem, s3>>>(B, PS, chunk_begin, t + 1, dinv); ++*nl;
       CTBA_CUDA(p, cudaEventRecord(evC, s3));
       chunk_begin = t + 1;
     }
@@ -1286,6 +1331,9 @@ int band_factor_solve(ctba_problem* p) {
 }  // namespace ctba
 
 #ifdef CTBA_BAND_TIMING
+extern "C" int ctba_debug_border_clocks(long long* out64) {
+  return cudaMemcpyFromSymbol(out64, ctba::g_border_clk, sizeof(long long) * 64) == cudaSuccess ? 0 : -2;
+}
 extern "C" int ctba_debug_band_clocks(long long* out8) {
   return cudaMemcpyFromSymbol(out8, ctba::g_band_clk, sizeof(long long) * 8) == cudaSuccess ? 0 : -2;
 }
