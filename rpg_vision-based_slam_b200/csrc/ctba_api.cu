@@ -680,6 +680,7 @@ int ctba_set_option(ctba_problem* p, const char* name, double value) {
   if (!std::strcmp(name, "band_partitions")) { p->band_partitions = (int)value; return CTBA_OK; }
   if (!std::strcmp(name, "schur_two_stage")) { p->schur_two_stage = value != 0.0; return CTBA_OK; }
   if (!std::strcmp(name, "schur_mask")) { p->schur_sorted = value != 0.0; return CTBA_OK; }
+  if (!std::strcmp(name, "schur_thread_below")) { p->schur_thread_below = value; return CTBA_OK; }
   if (!std::strcmp(name, "schur_threads")) { p->schur_threads = (int)value; return CTBA_OK; }
   if (!std::strcmp(name, "schur_list_a")) { p->schur_list_a = value != 0.0; return CTBA_OK; }
   if (!std::strcmp(name, "schur_compact")) { p->schur_compact = value != 0.0; return CTBA_OK; }

@@ -481,11 +481,15 @@ __global__ void __launch_bounds__(128) k_lm_prepare(const __grid_constant__ Glob
 }
 
 // corner / global right-hand side: deterministic sum of the per-block partials (one CTA)
-__global__ void __launch_bounds__(64) k_corner_reduce(int nblk, const double* __restrict__ partial, BandLayout Hw, double* __restrict__ rhs_glob) {
-  const int e = threadIdx.x;
+// one warp (= one CTA) per value: lanes take the per-block partials in a fixed stride, then a fixed shuffle tree (bit-reproducible)
+__global__ void __launch_bounds__(32) k_corner_reduce(int nblk, const double* __restrict__ partial, BandLayout Hw, double* __restrict__ rhs_glob) {
+  const int e = blockIdx.x, lane = threadIdx.x;
   if (e >= kCornerVals) return;
   double s = 0.0;
-  for (int b = 0; b < nblk; ++b) s += partial[(size_t)b * kCornerVals + e];
+  for (int b = lane; b < nblk; b += 32) s += partial[(size_t)b * kCornerVals + e];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane != 0) return;
   if (e < 28) {
     int a = 0;
     while ((a + 1) * (a + 2) / 2 <= e) ++a;
@@ -1672,11 +1676,17 @@ __global__ void __launch_bounds__(256) k_step_scalars(int K, int Kb, int L, cons
   }
   if (threadIdx.x == 0) for (int k = 0; k < 4; ++k) partial[4 * blockIdx.x + k] = sh[k][0];
 }
+// one warp: lanes take the per-block partials in a fixed stride, then a fixed shuffle tree (bit-reproducible)
 __global__ void k_step_scalars_final(int nblocks, const double* __restrict__ partial, double* __restrict__ out) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  if (blockIdx.x != 0 || threadIdx.x >= 32) return;
   double model = 0, step2 = 0, xn2 = 0, gmx = 0;
-  for (int b = 0; b < nblocks; ++b) { model += partial[4 * b]; step2 += partial[4 * b + 1]; xn2 += partial[4 * b + 2]; gmx = fmax(gmx, partial[4 * b + 3]); }
-  out[SC_MODEL] = 0.5 * model; out[SC_STEP2] = step2; out[SC_XNORM2] = xn2; out[SC_GMAX] = gmx;
+  for (int b = threadIdx.x; b < nblocks; b += 32) { model += partial[4 * b]; step2 += partial[4 * b + 1]; xn2 += partial[4 * b + 2]; gmx = fmax(gmx, partial[4 * b + 3]); }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    model += __shfl_xor_sync(0xffffffffu, model, o); step2 += __shfl_xor_sync(0xffffffffu, step2, o);
+    xn2 += __shfl_xor_sync(0xffffffffu, xn2, o); gmx = fmax(gmx, __shfl_xor_sync(0xffffffffu, gmx, o));
+  }
+  if (threadIdx.x == 0) { out[SC_MODEL] = 0.5 * model; out[SC_STEP2] = step2; out[SC_XNORM2] = xn2; out[SC_GMAX] = gmx; }
 }
 
 // ================================================== host side =====================================================
@@ -1982,7 +1992,7 @@ static int assemble_schur_T(ctba_problem* p, double radius) {
     k_lm_prepare<N><<<nlb, 128, 0, st>>>(G, S.glb, fps, S.lm, L, sd->d_lm_obs_begin.p, sd->d_lm_obs.p, p->d_o_frame.p, p->ev.Jl.p,
                                          (const double2*)p->ev.r_reproj.p, p->ev.f_w.p, M, sd->V0.p, sd->gl.p, sd->jscale_lm.p, radius, gm, any_g,
                                          sd->Vi.p, sd->vig.p, sd->ViYg.p, sd->lm_corner_partial.p);
-    if (any_g) { k_corner_reduce<<<1, 64, 0, st>>>(nlb, sd->lm_corner_partial.p, Hw, rhs_acc + n_pad); p->launches++; }
+    if (any_g) { k_corner_reduce<<<kCornerVals, 32, 0, st>>>(nlb, sd->lm_corner_partial.p, Hw, rhs_acc + n_pad); p->launches++; }
     if (p->schur_compact) {
       double* Al = p->schur_list_a ? sd->Zo.p : nullptr;   // Zo (18 M doubles) is free in the compact path
       k_obs_a<<<cdiv(M, 256), 256, 0, st>>>(M, p->d_o_frame.p, p->ev.Jl.p, (const double2*)p->ev.r_reproj.p, p->ev.f_w.p, sd->Yo.p, sd->d_o_pos.p, Al);
@@ -2017,7 +2027,7 @@ static int assemble_schur_T(ctba_problem* p, double radius) {
     }
     // frames per knot = F N / K; a task pairs the frames of two knots
     const double fpk = sd->frames_per_knot;
-    if (fpk * fpk < 16.0)
+    if (fpk * fpk < p->schur_thread_below)
       k_knot_schur_thread<N><<<cdiv((size_t)sd->K * (sd->KD + 1), 128), 128, 0, st>>>(fps, sd->K, sd->KD, T, p->d_f_s.p, sd->d_kf_begin.p,
                                                                                        sd->d_kf_list.p, sd->d_node_of_knot.p, sd->Sp.p, Hw);
     else if (p->schur_two_stage) {

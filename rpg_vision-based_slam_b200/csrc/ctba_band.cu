@@ -1010,8 +1010,8 @@ int band_partition_layout(int nbc, int nbw, int requested, int world, int nested
       P = (int)lround(std::sqrt((double)nbc / (1.2 * nbw)));
       // wide bands are throughput-bound, not latency-bound: one partition-step is ~8 ns * nbw^2 of DMMA work against a ~8.5 us
       // launch-chain floor, and beyond ~2.5x that many concurrent partitions more partitions only add interface steps
-      // (measured on config 3, nbw = 20: P = 17 -> 34.5 ms, P = 6..8 -> 31 ms)
-      if (world == 1) P = std::min(P, std::max(2, (int)lround(2650.0 / ((double)nbw * nbw))));
+      // (measured on config 3, nbw = 21, solve phase: P = 6 -> 24.5, 8 -> 24.1, 9 -> 23.9, 10 -> 24.0, 12 -> 24.2, 14 -> 24.6, 17 -> 25.3, 20 -> 25.8 ms)
+      if (world == 1) P = std::min(P, std::max(2, (int)lround(4000.0 / ((double)nbw * nbw))));
       P = std::max(1, std::min(P, kMaxParts));
       if (world > 1) P = std::max(world, (P / world) * world);
       while (P > (world > 1 ? world : 1) && !fits(P)) P -= (world > 1 ? world : 1);

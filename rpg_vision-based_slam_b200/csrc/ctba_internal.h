@@ -103,6 +103,7 @@ struct ctba_problem {
   int band_nested = 0;     // 1: interface systems are reduced recursively (odd-even over the separators); 0: one flat interface system
   bool schur_two_stage = true;   // knot-space expansion of the Schur blocks through U(f, kc) (false: one pass over all frame pairs per knot pair)
   bool schur_sorted = true;    // compact gather with per-observation track bitmasks + warp compaction (k_frame_schur_m); option name "schur_mask"
+  double schur_thread_below = 16.0;   // (frames per knot)^2 below which the knot-space expansion runs one thread per (knot, distance) instead of the two-stage gather
   int schur_threads = 192;     // CTA size of k_frame_schur_m (128 / 192 / 256)
   bool schur_list_a = true;    // compact gather: partner blocks fetched from a copy in landmark-list order (one dependent load less per partner)
   bool schur_compact = true;   // landmark Schur gather from the 6-double A blocks (false: from the 18-double Y / Z blocks)
