@@ -284,6 +284,7 @@ def main():
     ap.add_argument("--no-also", action="store_true", help="skip the configs[0] / configs[1] rates")
     ap.add_argument("--dt", type=float, default=None, help="config 5: knot spacing in seconds (0.02 .. 0.2)")
     ap.add_argument("--order", type=int, default=None, help="config 5: spline order (4 or 6)")
+    ap.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE", help="ctba_set_option on the benchmarked handle (tuning runs, e.g. band_partitions=16)")
     ap.add_argument("--linear-solver", default="cholesky", choices=["cholesky", "pcg"], help="bordered band Cholesky (exact step) or block-Jacobi PCG on the same reduced system")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -335,6 +336,9 @@ def main():
     g.setOption("bench_no_termination", 1)
     if a.linear_solver == "pcg":
         g.setOption("linear_solver", 1)
+    for kv in a.opt:
+        k, v = kv.split("=")
+        g.setOption(k, float(v))
     if world > 1:
         uid = torch.zeros(128, dtype=torch.uint8, device=f"cuda:{local_rank}")
         if rank == 0:
