@@ -43,11 +43,25 @@ static void swap_state(DeviceState& a, DeviceState& b) {
   std::swap(a.lm, b.lm); std::swap(a.glb, b.glb);
 }
 
-struct EvTimer {   // RAII: the events are released on every path, also on early error returns
-  cudaEvent_t a = nullptr, b = nullptr; cudaStream_t st; double* acc;
-  EvTimer(cudaStream_t s, double* t) : st(s), acc(t) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, st); }
-  void stop() { cudaEventRecord(b, st); cudaEventSynchronize(b); float ms = 0; cudaEventElapsedTime(&ms, a, b); *acc += ms * 1e-3; }
-  ~EvTimer() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+// Phase timers that never stall the stream: a scope records two events from a small pool and the elapsed time is read back at the next
+// point where the LM loop synchronises anyway (EvTimers::flush after the read-back of the step scalars / of the candidate cost).  The
+// loop's only host round trips are the ones its decisions need: [factorisation flag + step scalars], [candidate cost], [gradient norm of
+// the accepted state].
+struct EvTimers {
+  static constexpr int kPairs = 16;
+  cudaEvent_t a[kPairs], b[kPairs]; double* acc[kPairs]; int n = 0, made = 0; cudaStream_t st;
+  explicit EvTimers(cudaStream_t s) : st(s) {}
+  ~EvTimers() { for (int i = 0; i < made; ++i) { cudaEventDestroy(a[i]); cudaEventDestroy(b[i]); } }
+  int begin(double* t) {
+    if (n == kPairs) { cudaEventSynchronize(b[n - 1]); flush(); }
+    if (n == made) { cudaEventCreate(&a[made]); cudaEventCreate(&b[made]); ++made; }
+    acc[n] = t; cudaEventRecord(a[n], st); return n++;
+  }
+  void end(int i) { cudaEventRecord(b[i], st); }
+  void flush() {   // call after a stream synchronisation: every recorded pair has completed
+    for (int i = 0; i < n; ++i) { float ms = 0; if (cudaEventElapsedTime(&ms, a[i], b[i]) == cudaSuccess) *acc[i] += ms * 1e-3; }
+    n = 0;
+  }
 };
 
 int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
@@ -72,19 +86,21 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
     if (out->iterations && nit < out->iterations_capacity) out->iterations[nit] = {cost, cc, gmax, sn, ratio, radius, ok};
     ++nit;
   };
+  EvTimers timers(st);
   auto eval_at = [&](EvalBuffers& ev, const StatePtrs& S, bool jac, double* cost) -> int {
-    EvTimer t(st, &out->time_eval_s);
+    const int t = timers.begin(&out->time_eval_s);
     int r = launch_evaluate(p, ev, S, jac); if (r) return r;
     r = launch_cost(p, ev); if (r) return r;
-    r = shard_reduce_cost(p, ev, host_cost); if (r) return r;   // single GPU: plain read-back of the 7 cost terms
-    t.stop();
+    timers.end(t);
+    r = shard_reduce_cost(p, ev, host_cost); if (r) return r;   // single GPU: plain read-back of the 7 cost terms (synchronises the stream)
+    timers.flush();
     *cost = host_cost[6];
     return CTBA_OK;
   };
   auto build_at = [&]() -> int {  // direct normal equations + gradient at the current state (evaluation buffers hold its Jacobians)
-    EvTimer t(st, &out->time_build_s);
+    const int t = timers.begin(&out->time_build_s);
     int r = assemble_direct(p);
-    t.stop();
+    timers.end(t);
     return r;
   };
   auto scalars = [&](const StatePtrs& S, const StatePtrs& C, double radius) -> int {
@@ -92,6 +108,7 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
     if (!p->sharded) {
       CTBA_CUDA(p, cudaMemcpyAsync(host_sc, sd->scal.p, SC_COUNT * sizeof(double), cudaMemcpyDeviceToHost, st));
       CTBA_CUDA(p, cudaStreamSynchronize(st));
+      timers.flush();
       return CTBA_OK;
     }
     // sharded: every rank holds the sums over the nodes / landmarks it owns; combined in rank order so that all ranks take the same decisions
@@ -101,6 +118,7 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
     std::vector<double> h((size_t)W * SC_COUNT);
     CTBA_CUDA(p, cudaMemcpyAsync(h.data(), p->d_gather.p, h.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
     CTBA_CUDA(p, cudaStreamSynchronize(st));
+    timers.flush();
     for (int c = 0; c < SC_COUNT; ++c) host_sc[c] = 0.0;
     for (int rk = 0; rk < W; ++rk) {
       host_sc[SC_MODEL] += h[(size_t)rk * SC_COUNT + SC_MODEL]; host_sc[SC_STEP2] += h[(size_t)rk * SC_COUNT + SC_STEP2];
@@ -128,23 +146,25 @@ int solver_solve(ctba_problem* p, int max_num_iterations, ctba_summary* out) {
     if (radius < min_radius) { if (p->bench_no_termination) radius = initial_radius; else { out->termination_type = 0; break; } }
     ++iter;
     {
-      EvTimer tb(st, &out->time_build_s);
+      const int tb = timers.begin(&out->time_build_s);
       rc = assemble_schur(p, radius);
-      tb.stop();
+      timers.end(tb);
       if (rc) return rc;
     }
     {
-      EvTimer ts(st, &out->time_solve_s);
+      const int ts = timers.begin(&out->time_solve_s);
       rc = p->linear_solver ? band_pcg_solve(p) : band_factor_solve(p);
       if (rc) return rc;
       CTBA_CUDA(p, cudaMemcpyAsync(host_flag, sd->flag.p, sizeof(host_flag), cudaMemcpyDeviceToHost, st));
-      ts.stop();
+      timers.end(ts);
     }
+    // The candidate and the step scalars are enqueued without waiting for the factorisation flag: one round trip reads both.  After a
+    // failed factorisation they are garbage that is never used (the candidate buffers are only swapped in by an accepted step).
+    rc = backsub_and_candidate(p, p->dstate.ptrs(), sd->cand.ptrs(), radius); if (rc) return rc;
+    rc = scalars(p->dstate.ptrs(), sd->cand.ptrs(), radius); if (rc) return rc;
     bool ok = host_flag[0] == 0;
     double model_cost_change = 0.0, step_norm = 0.0;
     if (ok) {
-      rc = backsub_and_candidate(p, p->dstate.ptrs(), sd->cand.ptrs(), radius); if (rc) return rc;
-      rc = scalars(p->dstate.ptrs(), sd->cand.ptrs(), radius); if (rc) return rc;
       model_cost_change = host_sc[SC_MODEL];
       step_norm = std::sqrt(host_sc[SC_STEP2]);
       if (!std::isfinite(model_cost_change) || !std::isfinite(step_norm)) ok = false;
@@ -198,6 +218,7 @@ done:
   out->num_iterations = nit;
   out->kernel_launches = p->launches - launches0;
   CTBA_CUDA(p, cudaStreamSynchronize(st));
+  timers.flush();
   out->time_total_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
   return CTBA_OK;
 }
