@@ -201,3 +201,15 @@ def test_lm_gappy_tracks_and_duplicate_observations(pkg, scene, oracle, opts):
     sg, so = gpu.optimize(6), cpu.optimize(6, 8)
     assert so["num_successful_steps"] >= 2
     _check(gpu, cpu, sg, so)
+
+
+def test_lm_tracks_longer_than_the_bitmask(pkg, scene, oracle):
+    """Landmarks tracked over 70 frames: beyond the 64-bit track mask of k_frame_schur_m, so the gather falls back to the list search of
+    k_frame_schur_c (with the list-ordered partner blocks); same LM trace as the oracle."""
+    sc = scene.make_scene(order=4, duration_s=4.0, cam_hz=25.0, n_landmarks=60, track_len=70, imu_hz=0, gp_hz=10, seed=17, flags=(False, True, False, True, True))
+    F = len(sc["frame_t_ns"])
+    fi = np.repeat(np.arange(F), np.diff(sc["obs_begin"]))
+    span = max(fi[sc["lm_index"] == l].max() - fi[sc["lm_index"] == l].min() for l in np.unique(sc["lm_index"]))
+    assert span >= 64, span          # the scene really has tracks that the mask cannot hold
+    gpu, cpu, sg, so = _run(pkg, oracle, sc, 5)
+    _check(gpu, cpu, sg, so)
