@@ -187,7 +187,11 @@ int ctba_relinearize_time_offsets(ctba_problem* p);
 int ctba_set_option(ctba_problem* p, const char* name, double value);
 /* More options: "linear_solver" (0 = bordered band Cholesky, the exact step of the reference's SPARSE_NORMAL_CHOLESKY, bspline_so3r3.h:1771;
  * 1 = block-Jacobi PCG on the same reduced system, the ITERATIVE_SCHUR-style alternative for bands too wide to factor), "pcg_tol"
- * (|r| <= tol |b|, default 1e-10), "pcg_max_iters", "band_partitions", "bench_accept_all".
+ * (|r| <= tol |b|, default 1e-10), "pcg_max_iters", "band_partitions", "band_nested", "bench_accept_all".
+ * Implementation switches of the landmark Schur gather, all exact and bit-reproducible, kept for A/B measurements:
+ * "schur_mask" (1 = per-observation track bitmask + warp compaction, default; 0 = list search), "schur_threads" (128 / 192 / 256 threads
+ * per frame, default 192), "schur_list_a" (partner blocks from the list-ordered copy, default 1), "schur_compact", "schur_two_stage",
+ * "schur_thread_below".
  * ctba_get_stat: read-only facts about the last solve — "pcg_iterations", "pcg_rel_residual", "band_block_columns",
  * "band_half_width_blocks", "band_launches". */
 int ctba_get_stat(ctba_problem* p, const char* name, double* value);
