@@ -907,6 +907,64 @@ __global__ void __launch_bounds__(kFcThreads, 3) k_frame_schur_c(int F, int T, c
   }
 }
 
+// Sum of 36 per-lane values over the 32 lanes of a warp by recursive halving: in every round a lane keeps one half of its values and hands
+// the other half to its partner (37 exchanges instead of the 36 x 5 of a butterfly per value).  On return the lane holds the warp totals
+// of entries idx0 .. idx0 + nv - 1 (nv in {0, 1, 2}) in a[0], a[1]; every entry ends on exactly one lane.  Fixed order: bit-reproducible.
+__device__ __forceinline__ void warp_sum36(double (&a)[36], int lane, int& idx0, int& nv) {
+  const unsigned full = 0xffffffffu;
+  int base = 0;
+  {
+    const bool up = lane & 16;
+#pragma unroll
+    for (int k = 0; k < 18; ++k) {
+      const double keep = up ? a[k + 18] : a[k], send = up ? a[k] : a[k + 18];
+      a[k] = keep + __shfl_xor_sync(full, send, 16);
+    }
+    base += up ? 18 : 0;
+  }
+  {
+    const bool up = lane & 8;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      const double keep = up ? a[k + 9] : a[k], send = up ? a[k] : a[k + 9];
+      a[k] = keep + __shfl_xor_sync(full, send, 8);
+    }
+    base += up ? 9 : 0;
+  }
+  int n;
+  {   // 9 -> 5 | 4
+    const bool up = lane & 4;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const double keep = up ? a[k + 5] : a[k], send = up ? a[k] : a[k + 5];
+      a[k] = keep + __shfl_xor_sync(full, send, 4);
+    }
+    const double r4 = __shfl_xor_sync(full, a[4], 4);
+    a[4] = up ? 0.0 : a[4] + r4;
+    base += up ? 5 : 0; n = up ? 4 : 5;
+  }
+  {   // 5 (or 4) -> 3 | 2 (or 1)
+    const bool up = lane & 2;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const double keep = up ? a[k + 3] : a[k], send = up ? a[k] : a[k + 3];
+      a[k] = keep + __shfl_xor_sync(full, send, 2);
+    }
+    const double r2 = __shfl_xor_sync(full, a[2], 2);
+    a[2] = up ? 0.0 : a[2] + r2;
+    base += up ? 3 : 0; n = up ? n - 3 : 3;
+  }
+  {   // 3 (or 2, 1) -> 2 | 1 (or 0)
+    const bool up = lane & 1;
+    const double keep = up ? a[2] : a[0], send = up ? a[0] : a[2];
+    a[0] = keep + __shfl_xor_sync(full, send, 1);
+    const double r1 = __shfl_xor_sync(full, a[1], 1);
+    a[1] = up ? 0.0 : a[1] + r1;
+    base += up ? 2 : 0; n = up ? n - 2 : (n < 2 ? n : 2);
+  }
+  idx0 = base; nv = n < 0 ? 0 : n;
+}
+
 // ---- the same gather with a TRACK BITMASK per observation and warp-level compaction (default) -------------------------------------
 // k_frame_schur_c walks all n observations of the frame for every frame distance df; a lane whose landmark is not seen in frame f + df
 // idles, and a landmark whose track has gaps sends its lane into a serial search of the observation list (ncu, config 3: 17.8 of 32
@@ -1095,16 +1153,11 @@ __global__ void __launch_bounds__(kFsmThreads, 2) k_frame_schur_m(int F, int T, 
         }
       }
     }
-#pragma unroll
-    for (int e = 0; e < 36; ++e) {
-      double v = acc[e];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      acc[e] = v;
-    }
+    int idx0, nv;
+    warp_sum36(acc, lane, idx0, nv);
     double* dst = Sp + ((size_t)f * (T + 1) + df) * 36;
-#pragma unroll
-    for (int e = 0; e < 36; ++e) if (lane == e % 32 && (e < 32 || lane < 4)) dst[e] = -acc[e];
+    if (nv > 0) dst[idx0] = -acc[0];
+    if (nv > 1) dst[idx0 + 1] = -acc[1];
   }
 }
 
