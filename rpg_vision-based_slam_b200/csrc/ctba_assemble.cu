@@ -1374,10 +1374,22 @@ __global__ void __launch_bounds__(128) k_knot_schur_cols(const FramePose<N>* __r
   }
   if (!any) return;
   const int r0 = 6 * node_of_knot[kr], c0 = 6 * node_of_knot[kc];
+  if (dk > 0) {   // off-diagonal 6 x 6 block: whole rows, two columns at a time (c0 is even, so a pair never straddles a 32-column block)
 #pragma unroll
-  for (int e = 0; e < 36; ++e) {
-    const int a = e / 6, c = e % 6;
-    if (dk > 0 || c <= a) Hw.band[band_addr(Hw, r0 + a, c0 + c)] += C[e];
+    for (int a = 0; a < 6; ++a)
+#pragma unroll
+      for (int q = 0; q < 3; ++q) {
+        double2* d = reinterpret_cast<double2*>(Hw.band + band_addr(Hw, r0 + a, c0 + 2 * q));
+        double2 v = *d;
+        v.x += C[6 * a + 2 * q]; v.y += C[6 * a + 2 * q + 1];
+        *d = v;
+      }
+  } else {        // diagonal block: lower triangle only
+#pragma unroll
+    for (int e = 0; e < 36; ++e) {
+      const int a = e / 6, c = e % 6;
+      if (c <= a) Hw.band[band_addr(Hw, r0 + a, c0 + c)] += C[e];
+    }
   }
 }
 
@@ -1411,10 +1423,22 @@ __global__ void __launch_bounds__(128) k_knot_schur_thread(const FramePose<N>* _
   }
   if (!any) return;
   const int r0 = 6 * node_of_knot[kr], c0 = 6 * node_of_knot[kc];
+  if (dk > 0) {   // off-diagonal 6 x 6 block: whole rows, two columns at a time (c0 is even, so a pair never straddles a 32-column block)
 #pragma unroll
-  for (int e = 0; e < 36; ++e) {
-    const int a = e / 6, c = e % 6;
-    if (dk > 0 || c <= a) Hw.band[band_addr(Hw, r0 + a, c0 + c)] += C[e];
+    for (int a = 0; a < 6; ++a)
+#pragma unroll
+      for (int q = 0; q < 3; ++q) {
+        double2* d = reinterpret_cast<double2*>(Hw.band + band_addr(Hw, r0 + a, c0 + 2 * q));
+        double2 v = *d;
+        v.x += C[6 * a + 2 * q]; v.y += C[6 * a + 2 * q + 1];
+        *d = v;
+      }
+  } else {        // diagonal block: lower triangle only
+#pragma unroll
+    for (int e = 0; e < 36; ++e) {
+      const int a = e / 6, c = e % 6;
+      if (c <= a) Hw.band[band_addr(Hw, r0 + a, c0 + c)] += C[e];
+    }
   }
 }
 
