@@ -32,8 +32,8 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 // layout (column 4 ks + t: eight 8-byte loads per lane, each touching 8 cache lines per warp) the L1 sees a quarter of the requests,
 // and L1 request throughput is what bounds these kernels (ncu: l1tex 87-99 % busy before the change).
 __device__ __forceinline__ void load_frag8(const double* __restrict__ p, double v[8]) {
-  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3]) : "l"(p));
-  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[4]), "=d"(v[5]), "=d"(v[6]), "=d"(v[7]) : "l"(p + 4));
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[0]), "=d"(v[1]), "=d"(v[2]), "=d"(v[3]) : "l"(p));
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[4]), "=d"(v[5]), "=d"(v[6]), "=d"(v[7]) : "l"(p + 4));
 }
 // One 8x8 tile of  P = A * Bm^T  over K = 32:  A rows [8*tr, 8*tr+8) (row stride lda), Bm rows [8*tc, 8*tc+8) (row stride ldb).
 // Operands are read straight from global memory / L2.
@@ -408,12 +408,12 @@ __device__ __forceinline__ void kfrag_load(KFrag& f, const double* pa, size_t a_
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     if (8 * i < rows_a) {
-      if (COHERENT) asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(f.a[i][0]), "=d"(f.a[i][1]), "=d"(f.a[i][2]), "=d"(f.a[i][3]) : "l"(pa + (size_t)(8 * i) * a_rs + 4 * half) : "memory");
+      if (COHERENT) asm volatile("ld.global.L1::evict_last.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(f.a[i][0]), "=d"(f.a[i][1]), "=d"(f.a[i][2]), "=d"(f.a[i][3]) : "l"(pa + (size_t)(8 * i) * a_rs + 4 * half) : "memory");
       else asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(f.a[i][0]), "=d"(f.a[i][1]), "=d"(f.a[i][2]), "=d"(f.a[i][3]) : "l"(pa + (size_t)(8 * i) * a_rs + 4 * half));
     } else {
       f.a[i][0] = f.a[i][1] = f.a[i][2] = f.a[i][3] = 0.0;
     }
-    asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(f.b[i][0]), "=d"(f.b[i][1]), "=d"(f.b[i][2]), "=d"(f.b[i][3]) : "l"(pb + (size_t)(8 * i) * kNB + 4 * half));
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(f.b[i][0]), "=d"(f.b[i][1]), "=d"(f.b[i][2]), "=d"(f.b[i][3]) : "l"(pb + (size_t)(8 * i) * kNB + 4 * half));
   }
 }
 __device__ __forceinline__ void kfrag_mma(double (&acc)[4][4][2], const KFrag& f) {
@@ -443,8 +443,8 @@ __device__ __forceinline__ void kloop(double (&acc)[4][4][2], const double* pa, 
 // a_step / b_step further.  Used by the border pipeline to deal the k range to its 4 warps in half-blocks (warps 0, 1: the two halves of the
 // even blocks, warps 2, 3: of the odd blocks), so that 21 blocks split 11 / 11 / 10 / 10 half-blocks instead of 12 / 10 / 10 / 10.
 template <bool COHERENT>
-__device__ __forceinline__ void kloop_half(double (&acc)[4][4][2], const double* pa, size_t a_rs, size_t a_step, const double* __restrict__ pb,
-                                           size_t b_step, int n, int half, int rows_a) {
+__device__ __forceinline__ void kloop_half(double (&acc)[4][4][2], const double* pa, size_t a_rs, ptrdiff_t a_step, const double* __restrict__ pb,
+                                           ptrdiff_t b_step, int n, int half, int rows_a) {
   if (n <= 0) return;
   KFrag f0, f1;
   kfrag_load<COHERENT>(f0, pa, a_rs, pb, half, rows_a);
@@ -519,8 +519,16 @@ __global__ void __launch_bounds__(kBorderThreads) k_band_border(BandLayout B, co
       for (int h = 0; h < 4; ++h) acc[i][h][0] = acc[i][h][1] = 0.0;
     // warp w: half w & 1 of the blocks k_lo + (w >> 1), + 2, + 4, ...
     const int nk_all = j - k_lo, b0 = warp >> 1, nh = b0 < nk_all ? (nk_all - b0 + 1) / 2 : 0;
-    kloop_half<true>(acc, F + (size_t)g * Q.ld + (size_t)(k_lo + b0 - Q.c0) * kNB + 8 * tq, Q.ld, 2 * kNB,
-                     B.band + ((size_t)(k_lo + b0) * nb1 + (j - k_lo - b0)) * 1024 + (size_t)g * kNB + 8 * tq, (size_t)2 * (nb1 - 1) * 1024, nh, warp & 1, kNB);
+    // The CTA re-reads its own last nbw blocks W(r, k) every column (they are the A operand): those loads allocate in L1 with evict-last, the
+    // L blocks and every other fragment stream of the factorisation do not allocate, and the k order alternates from column to column
+    // (ascending on even t, descending on odd t) so that a working set slightly larger than L1 still hits on the blocks used last.
+    {
+      const double* pa0 = F + (size_t)g * Q.ld + (size_t)(k_lo + b0 - Q.c0) * kNB + 8 * tq;
+      const double* pb0 = B.band + ((size_t)(k_lo + b0) * nb1 + (j - k_lo - b0)) * 1024 + (size_t)g * kNB + 8 * tq;
+      const ptrdiff_t as = 2 * kNB, bs = (ptrdiff_t)2 * (nb1 - 1) * 1024;
+      const bool down = (t & 1) && nh > 0;
+      kloop_half<true>(acc, down ? pa0 + (nh - 1) * as : pa0, Q.ld, down ? -as : as, down ? pb0 + (nh - 1) * bs : pb0, down ? -bs : bs, nh, warp & 1, kNB);
+    }
     BORDER_CLK(2);
     acc_to_smem(sP[warp], acc, g, tq);
     asm volatile("cp.async.wait_group 0;" ::: "memory");
